@@ -1,0 +1,368 @@
+"""Column expressions evaluated per partition with ``pyarrow.compute``.
+
+Parity: the pyspark ``Column`` operators the reference's examples and tests use --
+arithmetic / comparison on ``col(...)`` (reference ``examples/data_process.py:10-24,63-68``),
+``alias``, ``cast``, ``isNull``, ``desc`` and python UDFs (``@udf("int")`` reference
+``examples/data_process.py:35-49``).  An expression is a small picklable tree; executors
+evaluate it against one Arrow table (a partition) at a time, so the hot loops are Arrow's C++
+kernels, not Python.
+"""
+from __future__ import annotations
+
+import datetime as _dt
+from typing import Any, Callable, Dict, List, Optional, Sequence
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute as pc
+
+from raydp_b200.sql import types as T
+
+
+class EvalContext:
+    """Per-partition evaluation state (partition index drives rand seeds and row ids)."""
+
+    def __init__(self, partition_index: int = 0, session_tz: str = "UTC"):
+        self.partition_index = partition_index
+        self.session_tz = session_tz
+
+
+def _to_array(value, n: int):
+    if isinstance(value, (pa.Array, pa.ChunkedArray)):
+        return value
+    if isinstance(value, pa.Scalar):
+        value = value.as_py()
+    return pa.array([value] * n) if not isinstance(value, (int, float, bool)) or n < 0 else \
+        pa.repeat(pa.scalar(value), n)
+
+
+def _is_arrayish(v) -> bool:
+    return isinstance(v, (pa.Array, pa.ChunkedArray))
+
+
+class Column:
+    """A node of the expression tree: ``kind`` + ``args`` (+ optional output name)."""
+
+    def __init__(self, kind: str, args: tuple = (), name: Optional[str] = None):
+        self._kind = kind
+        self._args = args
+        self._name = name
+
+    # ------------------------------------------------------------------ naming
+    def alias(self, name: str) -> "Column":
+        return Column(self._kind, self._args, name)
+
+    name = alias
+
+    def _output_name(self) -> str:
+        if self._name is not None:
+            return self._name
+        if self._kind == "col":
+            return self._args[0]
+        if self._kind == "lit":
+            return str(self._args[0])
+        if self._kind == "call":
+            inner = ", ".join(a._output_name() if isinstance(a, Column) else str(a) for a in self._args[1])
+            return f"{self._args[0]}({inner})"
+        if self._kind == "binop":
+            return f"({self._args[1]._output_name()} {self._args[0]} {self._args[2]._output_name()})"
+        if self._kind == "udf":
+            return f"{self._args[0].__name__}(...)"
+        return self._kind
+
+    # ------------------------------------------------------------------ operators
+    def _bin(self, op: str, other, reverse: bool = False) -> "Column":
+        other = other if isinstance(other, Column) else Column("lit", (other,))
+        return Column("binop", (op, other, self) if reverse else (op, self, other))
+
+    def __add__(self, o): return self._bin("+", o)
+    def __radd__(self, o): return self._bin("+", o, True)
+    def __sub__(self, o): return self._bin("-", o)
+    def __rsub__(self, o): return self._bin("-", o, True)
+    def __mul__(self, o): return self._bin("*", o)
+    def __rmul__(self, o): return self._bin("*", o, True)
+    def __truediv__(self, o): return self._bin("/", o)
+    def __rtruediv__(self, o): return self._bin("/", o, True)
+    def __mod__(self, o): return self._bin("%", o)
+    def __pow__(self, o): return self._bin("**", o)
+    def __lt__(self, o): return self._bin("<", o)
+    def __le__(self, o): return self._bin("<=", o)
+    def __gt__(self, o): return self._bin(">", o)
+    def __ge__(self, o): return self._bin(">=", o)
+    def __eq__(self, o): return self._bin("==", o)  # type: ignore[override]
+    def __ne__(self, o): return self._bin("!=", o)  # type: ignore[override]
+    def __and__(self, o): return self._bin("&", o)
+    def __or__(self, o): return self._bin("|", o)
+    def __invert__(self): return Column("call", ("not", (self,)))
+    def __neg__(self): return Column("call", ("negate", (self,)))
+    __hash__ = object.__hash__
+
+    def __bool__(self):
+        raise ValueError("Cannot convert column into bool: use '&' for 'and', '|' for 'or', "
+                         "'~' for 'not' when building DataFrame boolean expressions.")
+
+    def cast(self, data_type) -> "Column":
+        return Column("cast", (self, T.parse_type(data_type)), self._name)
+
+    astype = cast
+
+    def isNull(self) -> "Column":
+        return Column("call", ("is_null", (self,)))
+
+    def isNotNull(self) -> "Column":
+        return Column("call", ("is_valid", (self,)))
+
+    def isin(self, *values) -> "Column":
+        if len(values) == 1 and isinstance(values[0], (list, tuple, set)):
+            values = tuple(values[0])
+        return Column("isin", (self, tuple(values)))
+
+    def between(self, lo, hi) -> "Column":
+        return (self >= lo) & (self <= hi)
+
+    def desc(self) -> "Column":
+        return Column("sort", (self, "descending"))
+
+    def asc(self) -> "Column":
+        return Column("sort", (self, "ascending"))
+
+    def over(self, window) -> "Column":
+        return Column("window", (self, window), self._name)
+
+    def __repr__(self):
+        return f"Column<'{self._output_name()}'>"
+
+    # ------------------------------------------------------------------ evaluation
+    def references(self) -> List[str]:
+        out: List[str] = []
+
+        def walk(node):
+            if isinstance(node, Column):
+                if node._kind == "col":
+                    out.append(node._args[0])
+                for a in node._args:
+                    walk(a)
+            elif isinstance(node, (tuple, list)):
+                for a in node:
+                    walk(a)
+        walk(self)
+        return out
+
+    def evaluate(self, table: pa.Table, ctx: Optional[EvalContext] = None):
+        """Return an Arrow array (or scalar for pure literals) for this partition."""
+        ctx = ctx or EvalContext()
+        k, a = self._kind, self._args
+        n = table.num_rows
+        if k == "col":
+            if a[0] not in table.column_names:
+                raise KeyError(f"cannot resolve column '{a[0]}' given input columns {table.column_names}")
+            return table.column(a[0])
+        if k == "lit":
+            return pa.scalar(a[0])
+        if k == "binop":
+            return _binop(a[0], a[1].evaluate(table, ctx), a[2].evaluate(table, ctx))
+        if k == "cast":
+            value = a[0].evaluate(table, ctx)
+            return pc.cast(value, a[1].arrow, safe=False)
+        if k == "isin":
+            return pc.is_in(a[0].evaluate(table, ctx), value_set=pa.array(list(a[1])))
+        if k == "call":
+            return _call(a[0], [x.evaluate(table, ctx) if isinstance(x, Column) else x for x in a[1]],
+                         n, ctx)
+        if k == "udf":
+            func, rtype, arg_cols = a
+            arrays = [c.evaluate(table, ctx) for c in arg_cols]
+            cols = [(_to_array(x, n) if _is_arrayish(x) else None, x) for x in arrays]
+            pylists = [c.to_pylist() if c is not None else [s.as_py()] * n for c, s in cols]
+            out = [func(*row) for row in zip(*pylists)] if pylists else [func() for _ in range(n)]
+            return pa.array(out, type=rtype.arrow)
+        if k == "vudf":  # vectorised: func(numpy arrays...) -> numpy array
+            func, rtype, arg_cols = a
+            arrays = [c.evaluate(table, ctx) for c in arg_cols]
+            nps = [np.asarray(_to_array(x, n)) if _is_arrayish(x) else np.full(n, x.as_py())
+                   for x in arrays]
+            return pa.array(np.asarray(func(*nps)), type=rtype.arrow)
+        if k == "sort":
+            return a[0].evaluate(table, ctx)
+        if k == "when":
+            branches, otherwise = a
+            result = otherwise.evaluate(table, ctx) if otherwise is not None else pa.scalar(None)
+            for cond, value in reversed(branches):
+                result = pc.if_else(_full(cond.evaluate(table, ctx), n),
+                                    value.evaluate(table, ctx), result)
+            return result
+        raise NotImplementedError(f"expression kind {k!r} cannot be evaluated per partition")
+
+    def evaluate_array(self, table: pa.Table, ctx: Optional[EvalContext] = None):
+        out = self.evaluate(table, ctx)
+        return _full(out, table.num_rows)
+
+    def when(self, condition: "Column", value) -> "Column":
+        if self._kind != "when":
+            raise TypeError("when() can only be applied on a Column previously generated by when()")
+        value = value if isinstance(value, Column) else Column("lit", (value,))
+        return Column("when", (self._args[0] + ((condition, value),), self._args[1]))
+
+    def otherwise(self, value) -> "Column":
+        value = value if isinstance(value, Column) else Column("lit", (value,))
+        return Column("when", (self._args[0], value))
+
+
+def _full(value, n: int):
+    """Broadcast scalars to a length-``n`` array."""
+    if _is_arrayish(value):
+        return value
+    if isinstance(value, pa.Scalar):
+        if not value.is_valid and pa.types.is_null(value.type):
+            return pa.nulls(n)
+        return pa.repeat(value, n)
+    return pa.repeat(pa.scalar(value), n)
+
+
+_ARITH = {"+": "add", "-": "subtract", "*": "multiply", "**": "power"}
+_CMP = {"<": "less", "<=": "less_equal", ">": "greater", ">=": "greater_equal",
+        "==": "equal", "!=": "not_equal"}
+
+
+def _binop(op: str, left, right):
+    if op in _ARITH:
+        return getattr(pc, _ARITH[op])(left, right)
+    if op == "/":
+        # Spark's `/` is always floating-point division
+        return pc.divide(pc.cast(left, pa.float64()), pc.cast(right, pa.float64()))
+    if op == "%":
+        l_np, r_np = _np(left), _np(right)
+        return pa.array(np.fmod(l_np, r_np))
+    if op in _CMP:
+        return getattr(pc, _CMP[op])(left, right)
+    if op == "&":
+        return pc.and_kleene(left, right)
+    if op == "|":
+        return pc.or_kleene(left, right)
+    raise NotImplementedError(op)
+
+
+def _np(value):
+    if _is_arrayish(value):
+        return value.to_numpy(zero_copy_only=False) if isinstance(value, pa.Array) else \
+            value.combine_chunks().to_numpy(zero_copy_only=False)
+    return value.as_py() if isinstance(value, pa.Scalar) else value
+
+
+def _ts(value, ctx: EvalContext):
+    """Normalise timestamps/strings to timestamp[us] in the session time zone (UTC default)."""
+    if _is_arrayish(value):
+        t = value.type
+    else:
+        t = value.type
+    if pa.types.is_string(t) or pa.types.is_large_string(t):
+        value = parse_timestamp_strings(value)
+    elif pa.types.is_date(t):
+        value = pc.cast(value, pa.timestamp("us"))
+    if pa.types.is_timestamp(value.type) and value.type.tz is not None:
+        value = pc.cast(value, pa.timestamp("us"))  # stored as UTC instants
+    return value
+
+
+def parse_timestamp_strings(value):
+    """Parse ``2011-11-28 23:11:35 UTC`` / ISO strings (reference ``examples/fake_nyctaxi.csv``)."""
+    cleaned = pc.replace_substring_regex(value, r"\s*(UTC|Z)$", "")
+    cleaned = pc.replace_substring_regex(cleaned, r"T", " ")
+    cleaned = pc.replace_substring_regex(cleaned, r"\.\d+$", "")
+    return pc.strptime(cleaned, format="%Y-%m-%d %H:%M:%S", unit="us", error_is_null=True)
+
+
+def _call(fn: str, args: list, n: int, ctx: EvalContext):
+    x = args[0] if args else None
+    if fn == "abs":
+        return pc.abs(x)
+    if fn == "negate":
+        return pc.negate(x)
+    if fn == "not":
+        return pc.invert(x)
+    if fn == "is_null":
+        return pc.is_null(x)
+    if fn == "is_valid":
+        return pc.is_valid(x)
+    if fn == "log":
+        if len(args) == 2:  # log(base, x)
+            return pc.divide(pc.ln(pc.cast(args[1], pa.float64())), pc.ln(pc.cast(x, pa.float64())))
+        return pc.ln(pc.cast(x, pa.float64()))
+    if fn in ("log1p", "exp", "sqrt", "floor", "ceil", "sin", "cos", "log2", "log10"):
+        return getattr(pc, fn)(pc.cast(x, pa.float64()))
+    if fn == "round":
+        return pc.round(x, ndigits=args[1] if len(args) > 1 else 0)
+    if fn == "pow":
+        return pc.power(pc.cast(x, pa.float64()), args[1])
+    if fn == "rand":
+        seed = args[0] if args and args[0] is not None else 0x5eed
+        rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index])
+        return pa.array(rng.random(n))
+    if fn == "randn":
+        seed = args[0] if args and args[0] is not None else 0x5eed
+        rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index, 1])
+        return pa.array(rng.standard_normal(n))
+    if fn == "monotonically_increasing_id":
+        base = ctx.partition_index << 33
+        return pa.array(np.arange(base, base + n, dtype=np.int64))
+    if fn == "spark_partition_id":
+        return pa.array(np.full(n, ctx.partition_index, dtype=np.int32))
+    if fn in ("hour", "minute", "second", "month", "quarter", "year"):
+        return pc.cast(getattr(pc, fn)(_ts(x, ctx)), pa.int32())
+    if fn == "dayofmonth":
+        return pc.cast(pc.day(_ts(x, ctx)), pa.int32())
+    if fn == "dayofyear":
+        return pc.cast(pc.day_of_year(_ts(x, ctx)), pa.int32())
+    if fn == "dayofweek":  # Spark: 1 = Sunday ... 7 = Saturday
+        return pc.cast(pc.day_of_week(_ts(x, ctx), count_from_zero=False, week_start=7), pa.int32())
+    if fn == "weekofyear":
+        return pc.cast(pc.iso_week(_ts(x, ctx)), pa.int32())
+    if fn == "to_timestamp":
+        return _ts(x, ctx)
+    if fn == "unix_timestamp":
+        return pc.cast(pc.divide(pc.cast(_ts(x, ctx), pa.int64()), 1000000), pa.int64())
+    if fn == "coalesce":
+        return pc.coalesce(*[_full(a, n) for a in args])
+    if fn == "concat":
+        return pc.binary_join_element_wise(*[pc.cast(_full(a, n), pa.string()) for a in args], "")
+    if fn in ("upper", "lower"):
+        return getattr(pc, "utf8_" + fn)(x)
+    if fn == "length":
+        return pc.utf8_length(x)
+    if fn == "greatest":
+        return pc.max_element_wise(*args)
+    if fn == "least":
+        return pc.min_element_wise(*args)
+    if fn == "hash":
+        # deterministic 32-bit mix of the argument columns (feature crossing helper)
+        acc = np.full(n, 42, dtype=np.uint64)
+        for a in args:
+            v = _np(_full(a, n))
+            if v.dtype.kind in "OUS":
+                v = np.array([hash_str(s) for s in v], dtype=np.uint64)
+            else:
+                v = v.astype(np.int64, copy=False).view(np.uint64)
+            acc = (acc ^ v) * np.uint64(0x9E3779B97F4A7C15)
+            acc ^= acc >> np.uint64(29)
+        return pa.array((acc & np.uint64(0x7FFFFFFF)).astype(np.int32))
+    if fn == "array":
+        cols = [_np(_full(a, n)) for a in args]
+        stacked = np.stack(cols, axis=1)
+        return pa.FixedSizeListArray.from_arrays(pa.array(stacked.reshape(-1)), len(cols)).cast(
+            pa.list_(pa.from_numpy_dtype(stacked.dtype)))
+    raise NotImplementedError(f"SQL function {fn!r} is not supported by the built-in engine")
+
+
+def hash_str(s) -> int:
+    h = 1469598103934665603
+    for ch in str(s).encode():
+        h = ((h ^ ch) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def as_column(value) -> Column:
+    if isinstance(value, Column):
+        return value
+    if isinstance(value, str):
+        return Column("col", (value,))
+    return Column("lit", (value,))

@@ -1,0 +1,333 @@
+"""Physical plan of the built-in DataFrame engine: a partitioned source + narrow operators.
+
+This is the part of the reference's JVM layer that matters for training: turning rows into
+Arrow record batches on executors (reference ``ObjectStoreWriter.scala:172-174``
+``df.toArrowBatchRdd``).  Here partitions *are* Arrow tables from the start, every narrow
+operator is a ``pyarrow.compute`` call on one partition, and wide operators (repartition,
+groupBy, join, sort) are two-stage jobs assembled by ``dataframe.py``.
+"""
+from __future__ import annotations
+
+import glob as _glob
+import os
+import re
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute as pc
+
+from raydp_b200.sql import types as T
+from raydp_b200.sql.column import Column, EvalContext, _full, parse_timestamp_strings
+
+
+def strip_scheme(path: str) -> str:
+    return re.sub(r"^file:(//)?", "", path)
+
+
+# --------------------------------------------------------------------------- sources
+class Source:
+    num_partitions: int = 1
+
+    def load(self, idx: int) -> pa.Table:
+        raise NotImplementedError
+
+    def schema(self) -> pa.Schema:
+        return self.load(0).schema
+
+
+class RangeSource(Source):
+    def __init__(self, start: int, end: int, step: int, num_partitions: int):
+        self.start, self.end, self.step = int(start), int(end), int(step)
+        total = max(0, -(-(self.end - self.start) // self.step))
+        self.total = total
+        self.num_partitions = max(1, min(int(num_partitions), max(1, total)))
+
+    def bounds(self, idx: int) -> Tuple[int, int]:
+        per, rem = divmod(self.total, self.num_partitions)
+        lo = idx * per + min(idx, rem)
+        return lo, lo + per + (1 if idx < rem else 0)
+
+    def load(self, idx: int) -> pa.Table:
+        lo, hi = self.bounds(idx)
+        ids = np.arange(self.start + lo * self.step, self.start + hi * self.step, self.step,
+                        dtype=np.int64)
+        return pa.table({"id": ids})
+
+    def schema(self) -> pa.Schema:
+        return pa.schema([pa.field("id", pa.int64(), nullable=False)])
+
+
+class LocalSource(Source):
+    """Tables that travel inside the plan (``createDataFrame`` of driver-side data)."""
+
+    def __init__(self, tables: List[pa.Table]):
+        self.tables = tables
+        self.num_partitions = max(1, len(tables))
+
+    def load(self, idx: int) -> pa.Table:
+        return self.tables[idx]
+
+    def schema(self) -> pa.Schema:
+        return self.tables[0].schema
+
+
+class RefSource(Source):
+    """Partitions stored in the object store: partition i = concat(refs[i])."""
+
+    def __init__(self, refs: List[List[Any]], schema: pa.Schema):
+        self.refs = refs
+        self._schema = schema
+        self.num_partitions = max(1, len(refs))
+
+    def load(self, idx: int) -> pa.Table:
+        from raydp_b200 import runtime
+        if not self.refs:
+            return self._schema.empty_table()
+        parts = [runtime.get(r) for r in self.refs[idx]]
+        parts = [p if isinstance(p, pa.Table) else pa.ipc.open_stream(p).read_all() for p in parts]
+        if not parts:
+            return self._schema.empty_table()
+        return parts[0] if len(parts) == 1 else pa.concat_tables(parts)
+
+    def schema(self) -> pa.Schema:
+        return self._schema
+
+
+_TS_RE = re.compile(r"^\d{4}-\d{2}-\d{2}[ T]\d{2}:\d{2}:\d{2}(\.\d+)?( ?(UTC|Z))?$")
+
+
+def _infer_timestamps(table: pa.Table) -> pa.Table:
+    for i, field in enumerate(table.schema):
+        if not pa.types.is_string(field.type) or table.num_rows == 0:
+            continue
+        sample = [v for v in table.column(i).slice(0, 32).to_pylist() if v is not None]
+        if sample and all(_TS_RE.match(v) and "." not in v for v in sample):
+            table = table.set_column(i, field.name, parse_timestamp_strings(table.column(i)))
+    return table
+
+
+class CsvSource(Source):
+    def __init__(self, files: List[str], header: bool, infer: bool, sep: str,
+                 schema: Optional[T.StructType]):
+        self.files = files
+        self.header, self.infer, self.sep = header, infer, sep
+        self.user_schema = schema
+        self.num_partitions = max(1, len(files))
+        self._cached_schema: Optional[pa.Schema] = None
+
+    def load(self, idx: int) -> pa.Table:
+        import pyarrow.csv as pacsv
+        names = None if self.header else (
+            self.user_schema.names if self.user_schema is not None else None)
+        read_opts = pacsv.ReadOptions(column_names=names, autogenerate_column_names=(
+            names is None and not self.header))
+        parse_opts = pacsv.ParseOptions(delimiter=self.sep)
+        types = None
+        if self.user_schema is not None:
+            types = {f.name: f.dataType.arrow for f in self.user_schema}
+        elif not self.infer:
+            # Spark without inferSchema reads everything as string
+            head = pacsv.read_csv(self.files[idx], read_options=read_opts, parse_options=parse_opts)
+            types = {n: pa.string() for n in head.column_names}
+        conv = pacsv.ConvertOptions(column_types=types, strings_can_be_null=True,
+                                    null_values=["", "NULL", "null", "NaN"] if types is None else [""])
+        table = pacsv.read_csv(self.files[idx], read_options=read_opts, parse_options=parse_opts,
+                               convert_options=conv)
+        if self.user_schema is None and self.infer:
+            table = _infer_timestamps(table)
+            cols = []
+            for f in table.schema:  # Spark infers int (32-bit) when values fit
+                c = table.column(f.name)
+                if pa.types.is_int64(f.type) and table.num_rows:
+                    mm = pc.min_max(c).as_py()
+                    if mm["min"] is not None and -2 ** 31 <= mm["min"] and mm["max"] < 2 ** 31:
+                        c = pc.cast(c, pa.int32())
+                cols.append(c)
+            table = pa.table(cols, names=table.column_names)
+        if not self.header and names is None:
+            table = table.rename_columns([f"_c{i}" for i in range(table.num_columns)])
+        return table
+
+    def schema(self) -> pa.Schema:
+        if self._cached_schema is None:
+            self._cached_schema = self.load(0).schema
+        return self._cached_schema
+
+
+class ParquetSource(Source):
+    def __init__(self, files: List[str], columns: Optional[List[str]] = None):
+        self.files = files
+        self.columns = columns
+        self.num_partitions = max(1, len(files))
+
+    def load(self, idx: int) -> pa.Table:
+        import pyarrow.parquet as pq
+        return pq.read_table(self.files[idx], columns=self.columns)
+
+    def schema(self) -> pa.Schema:
+        import pyarrow.parquet as pq
+        return pq.read_schema(self.files[0])
+
+
+class FuncSource(Source):
+    """``parallelize`` / RDD-style source: partition i = fn(i) -> pa.Table."""
+
+    def __init__(self, fn: Callable[[int], pa.Table], num_partitions: int, schema: pa.Schema):
+        self.fn = fn
+        self.num_partitions = num_partitions
+        self._schema = schema
+
+    def load(self, idx: int) -> pa.Table:
+        return self.fn(idx)
+
+    def schema(self) -> pa.Schema:
+        return self._schema
+
+
+def list_data_files(path: str, suffixes: Sequence[str]) -> List[str]:
+    path = strip_scheme(path)
+    if os.path.isdir(path):
+        files = sorted(f for f in _glob.glob(os.path.join(path, "**", "*"), recursive=True)
+                       if os.path.isfile(f) and not os.path.basename(f).startswith(("_", "."))
+                       and (not suffixes or f.endswith(tuple(suffixes))))
+    else:
+        files = sorted(_glob.glob(path)) or [path]
+    if not files:
+        raise FileNotFoundError(f"Path does not exist: {path}")
+    return files
+
+
+# --------------------------------------------------------------------------- operators
+def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
+    kind = op[0]
+    n = table.num_rows
+    if kind == "with_column":
+        _, name, expr = op
+        arr = _full(expr.evaluate(table, ctx), n)
+        if name in table.column_names:
+            return table.set_column(table.column_names.index(name), name, arr)
+        return table.append_column(name, arr)
+    if kind == "filter":
+        mask = _full(op[1].evaluate(table, ctx), n)
+        return table.filter(pc.fill_null(mask, False))
+    if kind == "select":
+        arrays, names = [], []
+        for expr in op[1]:
+            if expr._kind == "col" and expr._args[0] == "*":
+                arrays.extend(table.columns)
+                names.extend(table.column_names)
+                continue
+            arrays.append(_full(expr.evaluate(table, ctx), n))
+            names.append(expr._output_name())
+        return pa.table(arrays, names=names) if arrays else table.select([])
+    if kind == "drop":
+        keep = [c for c in table.column_names if c not in op[1]]
+        return table.select(keep)
+    if kind == "rename":
+        return table.rename_columns([op[2] if c == op[1] else c for c in table.column_names])
+    if kind == "rename_all":
+        return table.rename_columns(list(op[1]))
+    if kind == "fillna":
+        _, value, subset = op
+        cols = []
+        for f in table.schema:
+            c = table.column(f.name)
+            if (subset is None or f.name in subset) and c.null_count:
+                v = value.get(f.name) if isinstance(value, dict) else value
+                if v is not None and _compatible(v, f.type):
+                    c = pc.fill_null(c, pa.scalar(v).cast(f.type))
+            cols.append(c)
+        return pa.table(cols, names=table.column_names)
+    if kind == "dropna":
+        _, subset = op
+        mask = None
+        for name in (subset or table.column_names):
+            valid = pc.is_valid(table.column(name))
+            mask = valid if mask is None else pc.and_(mask, valid)
+        return table.filter(mask) if mask is not None else table
+    if kind == "sort_within":
+        return table.sort_by(op[1])
+    if kind == "split":  # randomSplit piece: uniform draw in [lo, hi)
+        _, lo, hi, seed = op
+        rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index, 7])
+        draw = rng.random(n)
+        return table.filter(pa.array((draw >= lo) & (draw < hi)))
+    if kind == "sample":
+        _, fraction, seed = op
+        rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index, 11])
+        return table.filter(pa.array(rng.random(n) < fraction))
+    if kind == "limit_local":
+        return table.slice(0, op[1])
+    if kind == "map_arrow":
+        return op[1](table)
+    if kind == "map_pandas":
+        _, fn, schema = op
+        import pandas as pd
+        frames = list(fn(iter([table.to_pandas()])))
+        if not frames:
+            return schema.empty_table()
+        out = pa.Table.from_pandas(pd.concat(frames, ignore_index=True), preserve_index=False)
+        return out.select(schema.names).cast(schema, safe=False) if schema is not None else out
+    if kind == "join":
+        _, right, keys, how, right_keys = op
+        how = {"inner": "inner", "left": "left outer", "left_outer": "left outer",
+               "leftouter": "left outer", "right": "right outer", "right_outer": "right outer",
+               "outer": "full outer", "full": "full outer", "full_outer": "full outer",
+               "left_semi": "left semi", "leftsemi": "left semi", "left_anti": "left anti",
+               "leftanti": "left anti"}[how]
+        return table.join(right, keys=keys, right_keys=right_keys, join_type=how,
+                          use_threads=False)
+    if kind == "distinct":
+        return table.group_by(table.column_names, use_threads=False).aggregate([])
+    if kind == "cast_schema":
+        return table.cast(op[1], safe=False)
+    if kind == "posexplode":
+        _, expr, keep = op
+        arr = _full(expr.evaluate(table, ctx), n)
+        if isinstance(arr, pa.ChunkedArray):
+            arr = arr.combine_chunks()
+        flat = pc.list_flatten(arr)
+        parent = pc.list_parent_indices(arr)
+        offsets = np.asarray(arr.offsets)
+        pos = np.arange(len(flat), dtype=np.int64) - offsets[:-1][np.asarray(parent)]
+        base = table.select(keep).take(parent)
+        return base.append_column("pos", pa.array(pos.astype(np.int32))).append_column("col", flat)
+    raise NotImplementedError(f"operator {kind!r}")
+
+
+def _compatible(value, arrow_type: pa.DataType) -> bool:
+    if isinstance(value, bool):
+        return pa.types.is_boolean(arrow_type)
+    if isinstance(value, (int, float)):
+        return pa.types.is_integer(arrow_type) or pa.types.is_floating(arrow_type)
+    if isinstance(value, str):
+        return pa.types.is_string(arrow_type)
+    return False
+
+
+class Plan:
+    def __init__(self, source: Source, ops: Tuple[tuple, ...] = ()):
+        self.source = source
+        self.ops = tuple(ops)
+
+    @property
+    def num_partitions(self) -> int:
+        return self.source.num_partitions
+
+    def with_op(self, op: tuple) -> "Plan":
+        return Plan(self.source, self.ops + (op,))
+
+    def compute(self, idx: int) -> pa.Table:
+        ctx = EvalContext(partition_index=idx)
+        table = self.source.load(idx)
+        for op in self.ops:
+            table = _apply(op, table, ctx)
+        return table
+
+    def schema(self) -> pa.Schema:
+        ctx = EvalContext(partition_index=0)
+        table = self.source.schema().empty_table()
+        for op in self.ops:
+            table = _apply(op, table, ctx)
+        return table.schema

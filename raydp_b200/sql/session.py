@@ -1,0 +1,364 @@
+"""``SparkSession`` / ``SparkContext`` of the built-in engine.
+
+Parity: what the reference gets from pyspark after ``SparkSession.builder...master("ray://...")
+.getOrCreate()`` (reference ``spark/ray_cluster.py:191-201``): ``range``, ``createDataFrame``,
+``read`` (csv with header/inferSchema/sep/schema, parquet), ``conf.set/get``,
+``sparkContext.{appName, applicationId, getConf, parallelize, setLogLevel, defaultParallelism}``,
+``stop``.  ``enable_hive`` / ``spark.sql`` need a JVM and raise clearly.
+"""
+from __future__ import annotations
+
+import os
+import threading
+import uuid
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Union
+
+import numpy as np
+import pyarrow as pa
+
+from raydp_b200.sql import types as T
+from raydp_b200.sql.backend import Backend, ClusterBackend, LocalBackend
+from raydp_b200.sql.dataframe import DataFrame, _split_table
+from raydp_b200.sql.plan import (CsvSource, FuncSource, LocalSource, ParquetSource, Plan,
+                                 RangeSource, list_data_files)
+
+_active_lock = threading.RLock()
+_active_session: Optional["SparkSession"] = None
+_builder_options: Dict[str, str] = {}
+
+
+class SparkConf:
+    def __init__(self, values: Optional[Dict[str, str]] = None):
+        self._values: Dict[str, str] = dict(values or {})
+
+    def set(self, key: str, value) -> "SparkConf":
+        self._values[key] = str(value)
+        return self
+
+    def setAll(self, pairs) -> "SparkConf":
+        for k, v in pairs:
+            self.set(k, v)
+        return self
+
+    def get(self, key: str, defaultValue: Optional[str] = None) -> Optional[str]:
+        return self._values.get(key, defaultValue)
+
+    def getAll(self):
+        return list(self._values.items())
+
+    def contains(self, key: str) -> bool:
+        return key in self._values
+
+
+class RuntimeConfig:
+    def __init__(self, conf: SparkConf):
+        self._conf = conf
+
+    def set(self, key: str, value) -> None:
+        self._conf.set(key, value)
+
+    def get(self, key: str, default: Optional[str] = None) -> Optional[str]:
+        value = self._conf.get(key, default)
+        if value is None and default is None and not self._conf.contains(key):
+            raise KeyError(f"[SQL_CONF_NOT_FOUND] The SQL config \"{key}\" cannot be found.")
+        return value
+
+    def unset(self, key: str) -> None:
+        self._conf._values.pop(key, None)
+
+
+class SparkContext:
+    def __init__(self, session: "SparkSession"):
+        self._session = session
+        self.appName = session._app_name
+        self.applicationId = session._app_id
+        self.master = session._master
+
+    def getConf(self) -> SparkConf:
+        return self._session._conf
+
+    @property
+    def defaultParallelism(self) -> int:
+        return self._session._backend.default_parallelism
+
+    def setLogLevel(self, level: str) -> None:
+        self._session._conf.set("spark.log.level", level)
+
+    def parallelize(self, data: Iterable, numSlices: Optional[int] = None):
+        from raydp_b200.sql.rdd import RDD
+        items = list(data)
+        n = max(1, min(numSlices or self.defaultParallelism, max(1, len(items))))
+        per, rem = divmod(len(items), n)
+        parts, off = [], 0
+        for i in range(n):
+            size = per + (1 if i < rem else 0)
+            parts.append(items[off:off + size])
+            off += size
+        return RDD(self._session, parts)
+
+    @property
+    def uiWebUrl(self):
+        return None
+
+    def stop(self) -> None:
+        self._session.stop()
+
+
+class DataFrameReader:
+    def __init__(self, session: "SparkSession"):
+        self._session = session
+        self._format = "parquet"
+        self._options: Dict[str, str] = {}
+        self._schema: Optional[T.StructType] = None
+
+    def format(self, source: str) -> "DataFrameReader":
+        self._format = source.lower()
+        return self
+
+    def option(self, key: str, value) -> "DataFrameReader":
+        self._options[key.lower()] = str(value)
+        return self
+
+    def options(self, **opts) -> "DataFrameReader":
+        for k, v in opts.items():
+            self.option(k, v)
+        return self
+
+    def schema(self, schema: Union[T.StructType, str]) -> "DataFrameReader":
+        if isinstance(schema, str):
+            fields = []
+            for part in schema.split(","):
+                name, tname = part.strip().split()
+                fields.append(T.StructField(name, T.parse_type(tname)))
+            schema = T.StructType(fields)
+        self._schema = schema
+        return self
+
+    def load(self, path: Optional[str] = None, format: Optional[str] = None, **opts) -> DataFrame:  # noqa: A002
+        if format:
+            self.format(format)
+        self.options(**opts)
+        if self._format == "csv":
+            return self.csv(path)
+        if self._format == "parquet":
+            return self.parquet(path)
+        raise NotImplementedError(f"data source format {self._format!r} is not supported")
+
+    def _flag(self, key: str, default: bool = False) -> bool:
+        return str(self._options.get(key.lower(), default)).lower() == "true"
+
+    def csv(self, path: Union[str, List[str]], header=None, inferSchema=None, sep=None,
+            schema=None) -> DataFrame:
+        if header is not None:
+            self.option("header", header)
+        if inferSchema is not None:
+            self.option("inferSchema", inferSchema)
+        if sep is not None:
+            self.option("sep", sep)
+        if schema is not None:
+            self.schema(schema)
+        paths = [path] if isinstance(path, str) else list(path)
+        files = [f for p in paths for f in list_data_files(p, ())]
+        delim = self._options.get("sep", self._options.get("delimiter", ","))
+        src = CsvSource(files, self._flag("header"), self._flag("inferschema"), delim, self._schema)
+        return DataFrame(self._session, Plan(src))
+
+    def parquet(self, *paths: str) -> DataFrame:
+        files = [f for p in paths for f in list_data_files(p, (".parquet",))]
+        return DataFrame(self._session, Plan(ParquetSource(files)))
+
+    def table(self, name: str):
+        raise NotImplementedError("catalog tables need a Hive metastore/JVM; not available")
+
+
+class _Builder:
+    def __init__(self):
+        self._opts: Dict[str, str] = {}
+
+    def master(self, url: str) -> "_Builder":
+        self._opts["spark.master"] = url
+        return self
+
+    def appName(self, name: str) -> "_Builder":
+        self._opts["spark.app.name"] = name
+        return self
+
+    def config(self, key=None, value=None, conf: Optional[SparkConf] = None, map=None) -> "_Builder":  # noqa: A002
+        if conf is not None:
+            self._opts.update(dict(conf.getAll()))
+        if map is not None:
+            self._opts.update({k: str(v) for k, v in map.items()})
+        if key is not None:
+            self._opts[key] = str(value)
+        return self
+
+    def enableHiveSupport(self) -> "_Builder":
+        self._opts["spark.sql.catalogImplementation"] = "hive"
+        return self
+
+    def getOrCreate(self) -> "SparkSession":
+        global _active_session
+        with _active_lock:
+            if _active_session is not None and not _active_session._stopped:
+                for k, v in self._opts.items():
+                    _active_session._conf.set(k, v)
+                return _active_session
+            opts = dict(_builder_options)
+            opts.update(self._opts)
+            _builder_options.update(self._opts)
+            session = SparkSession(opts)
+            _active_session = session
+            return session
+
+
+class _BuilderDescriptor:
+    def __get__(self, obj, owner) -> _Builder:
+        return _Builder()
+
+
+class SparkSession:
+    builder = _BuilderDescriptor()
+
+    def __init__(self, options: Dict[str, str]):
+        self._conf = SparkConf(options)
+        self._app_name = options.get("spark.app.name", "raydp-b200-app")
+        self._master = options.get("spark.master", "local[*]")
+        self._app_id = f"app-{uuid.uuid4().hex[:16]}"
+        self._stopped = False
+        self._tracked_refs: List[Any] = []
+        self._conf.set("spark.app.id", self._app_id)
+        self._conf.set("spark.sql.session.timeZone", options.get("spark.sql.session.timeZone", "UTC"))
+        if self._master.startswith("local"):
+            spec = self._master[len("local"):].strip("[]")
+            threads = (os.cpu_count() or 1) if spec in ("", "*") else int(spec.split(",")[0])
+            self._backend: Backend = LocalBackend(threads)
+        elif self._master.startswith("ray"):
+            self._backend = ClusterBackend(self._master, self._app_name, dict(options))
+            self._app_id = self._backend.app_id
+            self._conf.set("spark.app.id", self._app_id)
+        else:
+            raise ValueError(f"Could not parse Master URL: '{self._master}'")
+        self.sparkContext = SparkContext(self)
+        self.conf = RuntimeConfig(self._conf)
+        self.version = "3.5.0-raydp-b200"
+
+    # ------------------------------------------------------------------ factories
+    @classmethod
+    def getActiveSession(cls) -> Optional["SparkSession"]:
+        return _active_session if _active_session is not None and not _active_session._stopped else None
+
+    @property
+    def _jvm(self):
+        raise NotImplementedError("there is no JVM in raydp_b200; use the Python API")
+
+    @property
+    def read(self) -> DataFrameReader:
+        return DataFrameReader(self)
+
+    def range(self, start: int, end: Optional[int] = None, step: int = 1,
+              numPartitions: Optional[int] = None) -> DataFrame:
+        if end is None:
+            start, end = 0, start
+        n = numPartitions or self._backend.default_parallelism
+        return DataFrame(self, Plan(RangeSource(start, end, step, n)))
+
+    def _from_tables(self, tables: List[pa.Table]) -> DataFrame:
+        return DataFrame(self, Plan(LocalSource(list(tables))))
+
+    def _track_refs(self, refs: List[Any]) -> None:
+        self._tracked_refs.extend(refs)
+
+    def createDataFrame(self, data, schema=None, samplingRatio=None, verifySchema=True) -> DataFrame:
+        from raydp_b200.sql.rdd import RDD
+        names: Optional[List[str]] = None
+        arrow_schema: Optional[pa.Schema] = None
+        if isinstance(schema, T.StructType):
+            arrow_schema = schema.to_arrow_schema()
+            names = schema.names
+        elif isinstance(schema, (list, tuple)):
+            names = list(schema)
+        elif isinstance(schema, str):
+            fields = [p.strip().split() for p in schema.replace(":", " ").split(",")]
+            st = T.StructType([T.StructField(n, T.parse_type(t)) for n, t in fields])
+            arrow_schema, names = st.to_arrow_schema(), st.names
+        if isinstance(data, RDD):
+            parts = data._collect_partitions()
+            tables = [_rows_to_table(p, names, arrow_schema) for p in parts if p]
+            if not tables:
+                tables = [_rows_to_table([], names, arrow_schema)]
+            unified = pa.unify_schemas([t.schema for t in tables]) if arrow_schema is None else arrow_schema
+            return self._from_tables([t.cast(unified) for t in tables])
+        try:
+            import pandas as pd
+            if isinstance(data, pd.DataFrame):
+                table = pa.Table.from_pandas(data, preserve_index=False)
+                if names:
+                    table = table.rename_columns(names)
+                if arrow_schema is not None:
+                    table = table.cast(arrow_schema, safe=False)
+                return self._from_tables(_split_table(table, self._backend.default_parallelism))
+        except ImportError:  # pragma: no cover
+            pass
+        if isinstance(data, pa.Table):
+            return self._from_tables(_split_table(data, self._backend.default_parallelism))
+        table = _rows_to_table(list(data), names, arrow_schema)
+        return self._from_tables(_split_table(table, self._backend.default_parallelism))
+
+    def sql(self, query: str):
+        raise NotImplementedError("spark.sql() needs Spark's SQL parser (JVM); use the DataFrame API")
+
+    def table(self, name: str):
+        raise NotImplementedError("catalog tables need a Hive metastore/JVM; not available")
+
+    def newSession(self) -> "SparkSession":
+        return self
+
+    def stop(self) -> None:
+        global _active_session
+        if self._stopped:
+            return
+        self._stopped = True
+        try:
+            if self._tracked_refs:
+                from raydp_b200 import runtime
+                if runtime.is_initialized():
+                    runtime.free(self._tracked_refs)
+            self._backend.stop()
+        finally:
+            with _active_lock:
+                if _active_session is self:
+                    _active_session = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.stop()
+
+
+def reset_builder_singletons() -> None:
+    """Forget builder options and the active session (reference ``context.py:33-51`` clears
+    pyspark's builder ``_options`` so the next ``init_spark`` starts clean)."""
+    global _active_session
+    with _active_lock:
+        _builder_options.clear()
+        _active_session = None
+
+
+def _rows_to_table(rows: List[Any], names: Optional[List[str]], schema: Optional[pa.Schema]) -> pa.Table:
+    if rows and isinstance(rows[0], dict):
+        names = names or list(rows[0].keys())
+        rows = [tuple(r.get(n) for n in names) for r in rows]
+    elif rows and isinstance(rows[0], T.Row) and rows[0].__fields__ and not names:
+        names = list(rows[0].__fields__)
+    elif rows and not isinstance(rows[0], (tuple, list)):
+        rows = [(r,) for r in rows]
+    width = len(rows[0]) if rows else (len(names) if names else 0)
+    names = names or [f"_{i + 1}" for i in range(width)]
+    cols = list(zip(*rows)) if rows else [[] for _ in names]
+    arrays = []
+    for i, name in enumerate(names):
+        typ = schema.field(name).type if schema is not None else None
+        values = list(cols[i]) if rows else []
+        arrays.append(pa.array(values, type=typ))
+    return pa.table(arrays, names=names)

@@ -1,0 +1,227 @@
+"""Spark-SQL-shaped data types over Arrow.
+
+Parity: the pyspark type surface the reference touches -- ``StructType``/``StructField``
+schemas iterated for ``field.name`` (reference ``examples/pytorch_nyctaxi.py:66``), explicit
+schemas for ``spark.read.schema(...)`` (DLRM notebook cell 13) and Arrow<->Spark schema
+conversion in ``ray_dataset_to_spark_dataframe`` (reference ``spark/dataset.py:298-305``).
+"""
+from __future__ import annotations
+
+from typing import Iterator, List, Optional, Sequence, Union
+
+import pyarrow as pa
+
+
+class DataType:
+    arrow: pa.DataType = pa.null()
+    name = "null"
+
+    def simpleString(self) -> str:
+        return self.name
+
+    def typeName(self) -> str:
+        return self.name
+
+    def __eq__(self, other):
+        return type(self) is type(other) and self.__dict__ == other.__dict__
+
+    def __hash__(self):
+        return hash(type(self).__name__)
+
+    def __repr__(self):
+        return f"{type(self).__name__}()"
+
+
+def _simple(cls_name: str, arrow_type: pa.DataType, simple: str):
+    return type(cls_name, (DataType,), {"arrow": arrow_type, "name": simple})
+
+
+NullType = _simple("NullType", pa.null(), "void")
+BooleanType = _simple("BooleanType", pa.bool_(), "boolean")
+ByteType = _simple("ByteType", pa.int8(), "tinyint")
+ShortType = _simple("ShortType", pa.int16(), "smallint")
+IntegerType = _simple("IntegerType", pa.int32(), "int")
+LongType = _simple("LongType", pa.int64(), "bigint")
+FloatType = _simple("FloatType", pa.float32(), "float")
+DoubleType = _simple("DoubleType", pa.float64(), "double")
+StringType = _simple("StringType", pa.string(), "string")
+BinaryType = _simple("BinaryType", pa.binary(), "binary")
+DateType = _simple("DateType", pa.date32(), "date")
+TimestampType = _simple("TimestampType", pa.timestamp("us"), "timestamp")
+
+
+class ArrayType(DataType):
+    name = "array"
+
+    def __init__(self, elementType: DataType, containsNull: bool = True):
+        self.elementType = elementType
+        self.containsNull = containsNull
+
+    @property
+    def arrow(self):  # type: ignore[override]
+        return pa.list_(self.elementType.arrow)
+
+    def simpleString(self):
+        return f"array<{self.elementType.simpleString()}>"
+
+
+class StructField:
+    def __init__(self, name: str, dataType: DataType, nullable: bool = True, metadata=None):
+        self.name = name
+        self.dataType = dataType
+        self.nullable = nullable
+        self.metadata = metadata or {}
+
+    def __repr__(self):
+        return f"StructField('{self.name}', {self.dataType!r}, {self.nullable})"
+
+    def __eq__(self, other):
+        return (isinstance(other, StructField) and other.name == self.name
+                and other.dataType == self.dataType)
+
+
+class StructType(DataType):
+    name = "struct"
+
+    def __init__(self, fields: Optional[Sequence[StructField]] = None):
+        self.fields: List[StructField] = list(fields or [])
+
+    def add(self, field: Union[str, StructField], data_type: Optional[DataType] = None,
+            nullable: bool = True) -> "StructType":
+        if isinstance(field, StructField):
+            self.fields.append(field)
+        else:
+            self.fields.append(StructField(field, data_type or StringType(), nullable))
+        return self
+
+    @property
+    def names(self) -> List[str]:
+        return [f.name for f in self.fields]
+
+    def fieldNames(self) -> List[str]:
+        return self.names
+
+    def __iter__(self) -> Iterator[StructField]:
+        return iter(self.fields)
+
+    def __len__(self):
+        return len(self.fields)
+
+    def __getitem__(self, key):
+        if isinstance(key, str):
+            for f in self.fields:
+                if f.name == key:
+                    return f
+            raise KeyError(key)
+        return self.fields[key]
+
+    @property
+    def arrow(self):  # type: ignore[override]
+        return pa.struct([pa.field(f.name, f.dataType.arrow) for f in self.fields])
+
+    def to_arrow_schema(self) -> pa.Schema:
+        return pa.schema([pa.field(f.name, f.dataType.arrow, f.nullable) for f in self.fields])
+
+    def simpleString(self):
+        inner = ",".join(f"{f.name}:{f.dataType.simpleString()}" for f in self.fields)
+        return f"struct<{inner}>"
+
+    def __repr__(self):
+        return f"StructType([{', '.join(repr(f) for f in self.fields)}])"
+
+
+_BY_NAME = {
+    "boolean": BooleanType, "bool": BooleanType, "tinyint": ByteType, "byte": ByteType,
+    "smallint": ShortType, "short": ShortType, "int": IntegerType, "integer": IntegerType,
+    "bigint": LongType, "long": LongType, "float": FloatType, "double": DoubleType,
+    "string": StringType, "str": StringType, "binary": BinaryType, "date": DateType,
+    "timestamp": TimestampType,
+}
+
+
+def parse_type(spec: Union[str, DataType, pa.DataType]) -> DataType:
+    """``"int"``, ``IntegerType()`` or an Arrow type -> DataType."""
+    if isinstance(spec, DataType):
+        return spec
+    if isinstance(spec, pa.DataType):
+        return from_arrow_type(spec)
+    key = str(spec).strip().lower()
+    if key in _BY_NAME:
+        return _BY_NAME[key]()
+    raise ValueError(f"unsupported data type string: {spec!r}")
+
+
+def from_arrow_type(t: pa.DataType) -> DataType:
+    if pa.types.is_boolean(t):
+        return BooleanType()
+    if pa.types.is_int8(t) or pa.types.is_uint8(t):
+        return ByteType()
+    if pa.types.is_int16(t) or pa.types.is_uint16(t):
+        return ShortType()
+    if pa.types.is_int32(t) or pa.types.is_uint32(t):
+        return IntegerType()
+    if pa.types.is_integer(t):
+        return LongType()
+    if pa.types.is_float32(t) or pa.types.is_float16(t):
+        return FloatType()
+    if pa.types.is_floating(t):
+        return DoubleType()
+    if pa.types.is_string(t) or pa.types.is_large_string(t):
+        return StringType()
+    if pa.types.is_binary(t) or pa.types.is_large_binary(t):
+        return BinaryType()
+    if pa.types.is_date(t):
+        return DateType()
+    if pa.types.is_timestamp(t):
+        return TimestampType()
+    if pa.types.is_list(t) or pa.types.is_large_list(t):
+        return ArrayType(from_arrow_type(t.value_type))
+    if pa.types.is_struct(t):
+        return StructType([StructField(f.name, from_arrow_type(f.type)) for f in t])
+    if pa.types.is_null(t):
+        return NullType()
+    if pa.types.is_dictionary(t):
+        return from_arrow_type(t.value_type)
+    raise TypeError(f"Arrow type {t} has no Spark SQL equivalent")
+
+
+def from_arrow_schema(schema: pa.Schema) -> StructType:
+    return StructType([StructField(f.name, from_arrow_type(f.type), f.nullable) for f in schema])
+
+
+class Row(tuple):
+    """Immutable row with attribute / key access, like ``pyspark.sql.Row``."""
+
+    def __new__(cls, *values, **named):
+        if named:
+            row = tuple.__new__(cls, tuple(named.values()))
+            row.__fields__ = list(named.keys())
+        else:
+            row = tuple.__new__(cls, values)
+            row.__fields__ = None
+        return row
+
+    @classmethod
+    def _make(cls, fields: Sequence[str], values: Sequence) -> "Row":
+        row = tuple.__new__(cls, tuple(values))
+        row.__fields__ = list(fields)
+        return row
+
+    def asDict(self) -> dict:
+        return dict(zip(self.__fields__ or [], self))
+
+    def __getattr__(self, item):
+        fields = self.__dict__.get("__fields__")
+        if fields and item in fields:
+            return self[fields.index(item)]
+        raise AttributeError(item)
+
+    def __getitem__(self, item):
+        if isinstance(item, str):
+            return tuple.__getitem__(self, self.__fields__.index(item))
+        return tuple.__getitem__(self, item)
+
+    def __repr__(self):
+        if self.__fields__:
+            return "Row(" + ", ".join(f"{k}={v!r}" for k, v in zip(self.__fields__, self)) + ")"
+        return "Row" + tuple.__repr__(self)
