@@ -1,0 +1,149 @@
+"""CPU batch iterator behind ``Dataset.to_torch`` plus a background prefetcher.
+
+Parity: ``dataset.to_torch(...)`` as consumed by reference ``torch/estimator.py:226-241`` and the
+``PrefetchedDataLoader`` capability of reference ``torch/torch_ml_dataset.py:69-111``
+(background thread + bounded queue).  Columns are converted block-wise Arrow -> numpy without
+pandas; the GPU ingestion path (``raydp_b200.ops.ingest``) replaces this on CUDA workers.
+"""
+from __future__ import annotations
+
+import queue
+import threading
+from typing import Any, Dict, Iterator, List, Optional, Sequence, Union
+
+import numpy as np
+import pyarrow as pa
+
+
+def _column_numpy(table: pa.Table, name: str) -> np.ndarray:
+    col = table.column(name)
+    if col.null_count:
+        col = col.fill_null(0)
+    arr = col.combine_chunks() if isinstance(col, pa.ChunkedArray) else col
+    if pa.types.is_timestamp(arr.type) or pa.types.is_date(arr.type):
+        arr = arr.cast(pa.int64())
+    if pa.types.is_boolean(arr.type):
+        arr = arr.cast(pa.int8())
+    return arr.to_numpy(zero_copy_only=False)
+
+
+def _np_dtype(torch_dtype):
+    import torch
+    if torch_dtype is None:
+        return None
+    return {torch.float32: np.float32, torch.float64: np.float64, torch.float16: np.float16,
+            torch.int64: np.int64, torch.int32: np.int32, torch.int16: np.int16,
+            torch.int8: np.int8, torch.uint8: np.uint8, torch.bool: np.bool_,
+            torch.bfloat16: np.float32}.get(torch_dtype, None)
+
+
+def block_to_arrays(table: pa.Table, feature_columns: Sequence[str], feature_dtype,
+                    label_column: Optional[str], label_dtype):
+    """One Arrow block -> ``([n, F] features, [n, 1] label)`` numpy arrays."""
+    f_np = _np_dtype(feature_dtype) or np.float32
+    feats = np.empty((table.num_rows, len(feature_columns)), dtype=f_np)
+    for j, name in enumerate(feature_columns):
+        feats[:, j] = _column_numpy(table, name)
+    label = None
+    if label_column is not None:
+        l_np = _np_dtype(label_dtype) or np.float32
+        label = _column_numpy(table, label_column).astype(l_np, copy=False).reshape(-1, 1)
+    return feats, label
+
+
+class TorchBatchIterable:
+    def __init__(self, dataset, label_column, feature_columns, label_column_dtype,
+                 feature_column_dtypes, batch_size: int, drop_last: bool,
+                 unsqueeze_label: bool = True):
+        import torch
+        self._ds = dataset
+        self._label = label_column
+        names = dataset.columns()
+        if feature_columns is None:
+            feature_columns = [n for n in names if n != label_column]
+        self._features: List[str] = list(feature_columns)
+        self._label_dtype = label_column_dtype
+        self._multi = isinstance(feature_column_dtypes, (list, tuple))
+        if self._multi and len(feature_column_dtypes) != len(self._features):
+            raise ValueError("feature_column_dtypes must have one dtype per feature column")
+        self._feature_dtypes = feature_column_dtypes
+        self._batch = int(batch_size)
+        self._drop_last = drop_last
+        self._unsqueeze = unsqueeze_label
+        self._torch = torch
+
+    def __len__(self) -> int:
+        n = self._ds.count()
+        return n // self._batch if self._drop_last else -(-n // self._batch)
+
+    def _convert(self, table: pa.Table):
+        torch = self._torch
+        if self._multi:
+            feats = []
+            for name, dt in zip(self._features, self._feature_dtypes):
+                arr = _column_numpy(table, name)
+                t = torch.as_tensor(np.ascontiguousarray(arr)).reshape(-1, 1)
+                feats.append(t.to(dt) if dt is not None else t)
+            label = None
+            if self._label is not None:
+                label = torch.as_tensor(np.ascontiguousarray(_column_numpy(table, self._label)))
+                label = label.to(self._label_dtype) if self._label_dtype is not None else label
+                label = label.reshape(-1, 1) if self._unsqueeze else label
+            return feats, label
+        f, l = block_to_arrays(table, self._features, self._feature_dtypes, self._label,
+                               self._label_dtype)
+        ft = torch.from_numpy(f)
+        if self._feature_dtypes is not None and ft.dtype != self._feature_dtypes:
+            ft = ft.to(self._feature_dtypes)
+        lt = None
+        if l is not None:
+            lt = torch.from_numpy(np.ascontiguousarray(l))
+            if self._label_dtype is not None and lt.dtype != self._label_dtype:
+                lt = lt.to(self._label_dtype)
+            if not self._unsqueeze:
+                lt = lt.reshape(-1)
+        return ft, lt
+
+    def __iter__(self) -> Iterator[Any]:
+        cols = self._features + ([self._label] if self._label is not None else [])
+        for table in self._ds.iter_batches(self._batch, "pyarrow", self._drop_last):
+            yield self._convert(table.select(cols))
+
+
+class PrefetchedLoader:
+    """Wrap any iterable; a daemon thread keeps up to ``max_size`` items ready."""
+
+    _END = object()
+
+    def __init__(self, base, max_size: int = 5):
+        self._base = base
+        self._max = max_size
+
+    def __len__(self):
+        return len(self._base)
+
+    def __iter__(self):
+        q: "queue.Queue" = queue.Queue(maxsize=self._max)
+        stop = threading.Event()
+
+        def work():
+            try:
+                for item in self._base:
+                    if stop.is_set():
+                        return
+                    q.put(item)
+                q.put(self._END)
+            except BaseException as exc:  # noqa: BLE001
+                q.put(exc)
+        thread = threading.Thread(target=work, name="rdp-prefetch", daemon=True)
+        thread.start()
+        try:
+            while True:
+                item = q.get()
+                if item is self._END:
+                    return
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+        finally:
+            stop.set()

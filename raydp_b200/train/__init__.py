@@ -1,0 +1,8 @@
+"""Training runtime: worker group, sessions, checkpoints (the Ray Train surface RayDP uses)."""
+from raydp_b200.train.checkpoint import Checkpoint, TorchCheckpoint  # noqa: F401
+from raydp_b200.train.config import (CheckpointConfig, FailureConfig, RunConfig,  # noqa: F401
+                                     ScalingConfig, TorchConfig)
+from raydp_b200.train.session import (get_checkpoint, get_context, get_dataset_shard,  # noqa: F401
+                                      report)
+from raydp_b200.train.torch_utils import get_device, prepare_model  # noqa: F401
+from raydp_b200.train.trainer import Result, TorchTrainer, TrainingFailedError  # noqa: F401
