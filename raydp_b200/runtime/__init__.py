@@ -134,7 +134,9 @@ def _rpc(op: str, **kwargs):
 
 def _auto_init() -> None:
     if _client is None:
-        init()
+        with _state_lock:
+            if _client is None:
+                init(ignore_reinit_error=True)
 
 
 # --------------------------------------------------------------------------- objects
@@ -271,7 +273,8 @@ class RemoteFunction:
                    resources=_normalise_resources(self._opts, 1.0),
                    max_retries=int(self._opts.get("max_retries", 3)),
                    name=getattr(self._func, "__name__", "task"),
-                   placement_group=pg, bundle_index=bundle)
+                   placement_group=pg, bundle_index=bundle,
+                   prefer_ip=self._opts.get("_prefer_node_ip"))
         return ObjectRef(oid)
 
     def __call__(self, *args, **kwargs):

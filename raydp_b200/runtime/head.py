@@ -171,6 +171,10 @@ class Head:
         self.address = os.path.join(self.dir, "head.sock")
         self.authkey = os.urandom(16)
         self._listener = Listener(self.address, family="AF_UNIX", authkey=self.authkey)
+        try:  # accept() must wake up periodically so shutdown can end the accept thread
+            self._listener._listener._socket.settimeout(0.5)
+        except AttributeError:
+            pass
         self._lock = threading.RLock()
         self._pool = ThreadPoolExecutor(max_workers=256, thread_name_prefix="rdp-head")
         self._nodes: Dict[str, _Node] = {}
@@ -183,6 +187,7 @@ class Head:
         self._task_queue: "collections.deque[_Task]" = collections.deque()
         self._pending_actors: "collections.deque[_Actor]" = collections.deque()
         self._shutdown = False
+        self._freed: set = set()
         if num_cpus is None:
             num_cpus = os.cpu_count() or 1
         if num_gpus is None:
@@ -242,6 +247,8 @@ class Head:
         while not self._shutdown:
             try:
                 conn = self._listener.accept()
+            except TimeoutError:
+                continue
             except (OSError, EOFError):
                 if self._shutdown:
                     return
@@ -341,6 +348,8 @@ class Head:
         return True
 
     def op_get(self, info, oid: str, timeout: Optional[float] = None):
+        if oid in self._freed:
+            raise P.ObjectLostError(f"object {oid} was freed (its owner cleaned it up)")
         obj = self._obj(oid)
         deadline = None if timeout is None else time.time() + timeout
         while True:
@@ -405,6 +414,7 @@ class Head:
     def op_free(self, info, oids: List[str]):
         with self._lock:
             objs = [self._objects.pop(o, None) for o in oids]
+            self._freed.update(oids)
         for obj in objs:
             if obj is not None and obj.desc is not None and obj.desc[0] == "shm":
                 store.delete(obj.desc[1])
@@ -421,10 +431,11 @@ class Head:
 
     # tasks ------------------------------------------------------------------
     def op_submit_task(self, info, func_blob, args_blob, resources, max_retries, name,
-                       placement_group=None, bundle_index=-1):
+                       placement_group=None, bundle_index=-1, prefer_ip=None):
         oid = P.new_id()
         task = _Task(oid, func_blob, args_blob, resources, max_retries, name,
                      placement_group, bundle_index)
+        task.prefer_ip = prefer_ip
         obj = self._obj(oid)
         obj.lineage = task
         task.running = True
@@ -516,7 +527,9 @@ class Head:
         extra_env = (actor.opts.get("env") if actor else None) or {}
         env.update({k: str(v) for k, v in extra_env.items()})
         root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-        env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
+        # workers see the driver's import path (functions/classes are pickled by reference)
+        driver_path = [p for p in sys.path if p and os.path.isdir(p)]
+        env["PYTHONPATH"] = os.pathsep.join([root] + driver_path + [env.get("PYTHONPATH", "")])
         tag = f"actor-{actor.name or actor.actor_id[:8]}" if actor else "task"
         log = open(os.path.join(self.log_dir, f"worker-{tag}-{worker_id}.log"), "ab")
         proc = subprocess.Popen([sys.executable, "-m", "raydp_b200.runtime.worker"],
@@ -532,7 +545,12 @@ class Head:
         return worker
 
     def _try_start_task(self, task: _Task) -> bool:
-        got = self._reserve(task.resources, task.pg, task.bundle)
+        prefer = None
+        if getattr(task, "prefer_ip", None):
+            with self._lock:
+                prefer = next((n.node_id for n in self._nodes.values()
+                               if n.alive and n.ip == task.prefer_ip), None)
+        got = self._reserve(task.resources, task.pg, task.bundle, prefer=prefer)
         if got is None:
             return False
         node, holds = got

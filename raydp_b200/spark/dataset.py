@@ -110,12 +110,22 @@ def from_spark_recoverable(df: DataFrame, storage_level: StorageLevel = StorageL
     prefix = C.RECOVERABLE_FETCH_TASK_RESOURCE_PREFIX
     fetch_cpus = float(conf.get(prefix + ".CPU", "0"))
     fetch_memory = float(conf.get(prefix + ".memory", "0"))
-    task = _fetch_arrow_table_from_executor.options(num_cpus=fetch_cpus, memory=fetch_memory or None)
-    refs = rdata._in_waves(
-        lambda i: task.remote(C.EXECUTOR_NAME_PREFIX + str(locations[i]), rdd_id, i), n)
+    app = runtime.get(master.application_info.remote(backend.app_id))
+    node_of = {info["actor"]: info["node_ip"] for info in app.get("executors", {}).values()}
+
+    def submit(i):
+        # run the fetch next to the executor that caches the partition (block locality)
+        # (a soft preference: after a node loss the retry may run anywhere)
+        task = _fetch_arrow_table_from_executor.options(
+            num_cpus=fetch_cpus, memory=fetch_memory or None,
+            _prefer_node_ip=node_of.get(locations[i]))
+        return task.remote(C.EXECUTOR_NAME_PREFIX + str(locations[i]), rdd_id, i)
+    refs = rdata._in_waves(submit, n)
     runtime.wait(refs, num_returns=len(refs), timeout=None)
     _recoverable_rdd_ids[df] = rdd_id
-    session._track_refs(refs)
+    # the master actor (object holder) owns the converted blocks: they die with
+    # stop_spark(cleanup_data=True) and survive stop_spark(cleanup_data=False)
+    runtime.get(master.add_objects.remote(f"rdd-{rdd_id}-{uuid.uuid4().hex[:8]}", list(refs)))
     metadata = [rdata.BlockMetadata(rows, nbytes, schema) for rows, nbytes in stats]
     return rdata.from_arrow_refs(refs, metadata)
 

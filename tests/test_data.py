@@ -1,0 +1,57 @@
+"""Dataset surface (ray.data stand-in)."""
+import numpy as np
+import pyarrow as pa
+import pytest
+import torch
+
+from raydp_b200 import data as rdata
+
+
+def test_constructors_and_metadata(ray_cluster, tmp_path):
+    ds = rdata.from_items([{"a": i, "b": float(i)} for i in range(100)], parallelism=4)
+    assert ds.count() == 100 and ds.num_blocks() == 4
+    assert ds.schema().names == ["a", "b"]
+    assert ds.schema().base_schema.field("b").type == pa.float64()
+    assert ds.take(2) == [{"a": 0, "b": 0.0}, {"a": 1, "b": 1.0}]
+    assert rdata.range(10, parallelism=2).count() == 10
+    ds.write_parquet(str(tmp_path / "pq"))
+    back = rdata.read_parquet(str(tmp_path / "pq"))
+    assert back.count() == 100 and sorted(r["a"] for r in back.take_all()) == list(range(100))
+
+
+def test_split_shuffle_and_batches(ray_cluster):
+    ds = rdata.from_arrow([pa.table({"x": np.arange(i * 100, (i + 1) * 100)}) for i in range(5)])
+    parts = ds.split(3, equal=True)
+    assert [p.count() for p in parts] == [166, 166, 166]
+    seen = np.concatenate([p.to_arrow().column("x").to_numpy() for p in parts])
+    assert len(set(seen.tolist())) == 498                  # views, no duplicated rows
+    a, b = ds.split_at_indices([120])
+    assert a.count() == 120 and b.count() == 380 and b.take(1)[0]["x"] == 120
+    sh = ds.random_shuffle(seed=5)
+    vals = sh.to_arrow().column("x").to_numpy()
+    assert sorted(vals.tolist()) == list(range(500)) and vals.tolist() != list(range(500))
+    assert sh.to_arrow().column("x").to_numpy().tolist() != ds.random_shuffle(seed=6).to_arrow().column("x").to_numpy().tolist()
+    sizes = [b.num_rows for b in ds.iter_batches(batch_size=128)]
+    assert sizes == [128, 128, 128, 116]
+    assert [b.num_rows for b in ds.iter_batches(batch_size=128, drop_last=True)] == [128, 128, 128]
+    mapped = ds.map_batches(lambda t: t.append_column("y", pa.array(t.column("x").to_numpy() * 2)))
+    assert mapped.take(1)[0] == {"x": 0, "y": 0}
+
+
+def test_to_torch_single_and_per_column_dtypes(ray_cluster):
+    ds = rdata.from_arrow(pa.table({"f1": np.arange(10, dtype=np.float64),
+                                    "f2": np.arange(10, dtype=np.int64),
+                                    "y": np.arange(10, dtype=np.float64) * 3}))
+    it = ds.to_torch(label_column="y", feature_columns=["f1", "f2"], feature_column_dtypes=torch.float,
+                     label_column_dtype=torch.float, batch_size=4)
+    batches = list(it)
+    assert len(batches) == 3 == len(it)
+    x, y = batches[0]
+    assert x.shape == (4, 2) and x.dtype == torch.float32 and y.shape == (4, 1)
+    assert torch.equal(y[:, 0], torch.tensor([0., 3., 6., 9.]))
+    multi = ds.to_torch(label_column="y", feature_columns=["f1", "f2"],
+                        feature_column_dtypes=[torch.float, torch.long],
+                        label_column_dtype=torch.float, batch_size=5, drop_last=True)
+    feats, y = next(iter(multi))
+    assert isinstance(feats, list) and feats[0].dtype == torch.float32 and feats[1].dtype == torch.int64
+    assert feats[1].shape == (5, 1)

@@ -1,0 +1,125 @@
+"""Actor runtime: tasks, actors, restart policy, placement groups, node loss."""
+import os
+import signal
+import time
+
+import pyarrow as pa
+import pytest
+
+from raydp_b200 import runtime as rt
+from raydp_b200.runtime.cluster_utils import Cluster
+
+
+@rt.remote
+def _add(a, b):
+    return a + b
+
+
+@rt.remote
+class _Counter:
+    def __init__(self, start=0):
+        self.v = start
+
+    def inc(self, n=1):
+        self.v += n
+        return self.v
+
+    def pid(self):
+        return os.getpid()
+
+    def table(self, n):
+        return pa.table({"x": list(range(n))})
+
+    def restarted(self):
+        return rt.get_runtime_context().was_current_actor_reconstructed
+
+    def boom(self):
+        raise ValueError("boom")
+
+    def leave(self):
+        rt.exit_actor()
+
+
+def test_tasks_and_object_refs(ray_cluster):
+    assert rt.get(_add.remote(1, 2)) == 3
+    ref = rt.put(40)
+    assert rt.get(_add.remote(ref, 2)) == 42          # top-level refs are resolved
+    refs = [_add.remote(i, i) for i in range(4)]
+    ready, rest = rt.wait(refs, num_returns=4, timeout=30)
+    assert len(ready) == 4 and not rest
+    assert rt.get(refs) == [0, 2, 4, 6]
+
+
+def test_actor_basics_and_errors(ray_cluster):
+    c = _Counter.options(name="cnt").remote(10)
+    assert rt.get(c.inc.remote()) == 11
+    assert rt.get(rt.get_actor("cnt").inc.remote(4)) == 15
+    t = rt.get(c.table.remote(50000))                 # large result travels through shm
+    assert isinstance(t, pa.Table) and t.num_rows == 50000
+    with pytest.raises(rt.TaskError, match="boom"):
+        rt.get(c.boom.remote())
+    with pytest.raises(ValueError):
+        _Counter.options(name="cnt").remote()
+    rt.get(c.leave.remote())
+    time.sleep(0.3)
+    with pytest.raises(rt.ActorDiedError):
+        rt.get(c.inc.remote())
+    with pytest.raises(ValueError):
+        rt.get_actor("cnt")
+
+
+def test_actor_restart_keeps_name(ray_cluster):
+    c = _Counter.options(name="phoenix", max_restarts=-1, max_task_retries=-1).remote(5)
+    pid = rt.get(c.pid.remote())
+    os.kill(pid, signal.SIGKILL)
+    assert rt.get(c.inc.remote(), timeout=60) == 6     # state rebuilt from ctor args
+    assert rt.get(c.restarted.remote()) is True
+    assert rt.get(c.pid.remote()) != pid
+    assert rt.list_actors([("name", "=", "phoenix")])[0]["num_restarts"] == 1
+
+
+def test_resources_and_placement_groups(ray_cluster):
+    base = rt.available_resources()["CPU"]
+    c = _Counter.options(num_cpus=0.5, resources={}).remote()
+    rt.get(c.inc.remote())
+    assert rt.available_resources()["CPU"] == pytest.approx(base - 0.5)
+    rt.kill(c)
+    for strategy in ("PACK", "SPREAD", "STRICT_PACK"):
+        pg = rt.placement_group([{"CPU": 1}, {"CPU": 1}], strategy=strategy)
+        assert pg.wait(10)
+        assert rt.placement_group_table(pg)["state"] == "CREATED"
+        assert pg.bundle_count == 2
+        rt.remove_placement_group(pg)
+        assert rt.placement_group_table(pg)["state"] == "REMOVED"
+    deadline = time.time() + 5
+    while rt.available_resources().get("CPU") != base and time.time() < deadline:
+        time.sleep(0.05)
+    assert rt.available_resources()["CPU"] == base
+    # STRICT_SPREAD needs as many nodes as bundles: stays pending on a single node
+    pg = rt.placement_group([{"CPU": 1}, {"CPU": 1}], strategy="STRICT_SPREAD")
+    assert not pg.wait(0.5)
+    rt.remove_placement_group(pg)
+
+
+def test_custom_resource_node_affinity_and_node_loss():
+    rt.shutdown()
+    cluster = Cluster(initialize_head=True, head_node_args={"num_cpus": 2})
+    try:
+        node = cluster.add_node(num_cpus=2, resources={"special": 2})
+        c = _Counter.options(resources={"special": 1}, max_restarts=-1).remote()
+        rt.get(c.inc.remote())
+        rec = [a for a in rt.list_actors() if a["actor_id"] == c._actor_id][0]
+        assert rec["node_id"] == node.node_id and rec["node_ip"] == "127.0.0.2"
+
+        @rt.remote(resources={"special": 0.001}, max_retries=-1)
+        def make():
+            return pa.table({"v": list(range(100000))})
+
+        ref = make.remote()
+        assert rt.get(ref).num_rows == 100000
+        cluster.remove_node(node)                       # block and actor are lost
+        cluster.add_node(num_cpus=2, resources={"special": 2})
+        assert rt.get(ref, timeout=60).num_rows == 100000   # rebuilt from lineage
+        assert rt.get(c.inc.remote(), timeout=60) == 1      # actor restarted elsewhere
+    finally:
+        cluster.shutdown()

@@ -1,0 +1,175 @@
+"""DataFrame engine on the local[2] backend (SURVEY.md Appendix C surface)."""
+import os
+
+import pyarrow as pa
+import pytest
+
+from raydp_b200.sql import SparkSession, Window, functions as F, types as T
+from raydp_b200.sql.backend import get_initial_target_executor_number
+from raydp_b200.sql.functions import col, lit, udf
+
+REF_CSV = "/root/reference/examples/fake_nyctaxi.csv"
+
+
+def test_range_count_partitions(spark_session):
+    df = spark_session.range(0, 1000, numPartitions=4)
+    assert df.count() == 1000
+    assert df.rdd.getNumPartitions() == 4
+    assert [f.name for f in df.schema] == ["id"]
+    assert spark_session.range(10).count() == 10
+    assert spark_session.range(0, 10, 3).collect()[-1].id == 9
+
+
+def test_expressions_filter_select(spark_session):
+    df = spark_session.range(0, 100).withColumn("x", col("id") * 2 + 1) \
+        .withColumn("half", col("id") / 2).filter((col("x") > 10) & (col("id") < 50))
+    rows = df.select("id", (col("x") - 1).alias("y"), F.abs(lit(-3)).alias("three")).collect()
+    assert len(rows) == 45
+    assert rows[0].y == rows[0].id * 2 and rows[0].three == 3
+    assert dict(df.dtypes)["half"] == "double"
+    assert df.drop("x").columns == ["id", "half"]
+    assert df.withColumnRenamed("x", "xx").columns == ["id", "xx", "half"]
+
+
+def test_rand_is_deterministic_and_split_is_a_partition(spark_session):
+    df = spark_session.range(0, 2000, numPartitions=3).withColumn("r", F.rand(7))
+    a = [r.r for r in df.collect()]
+    b = [r.r for r in df.collect()]
+    assert a == b and 0 <= min(a) and max(a) < 1
+    s1, s2 = df.randomSplit([0.8, 0.2], seed=3)
+    ids1, ids2 = {r.id for r in s1.collect()}, {r.id for r in s2.collect()}
+    assert not (ids1 & ids2) and len(ids1 | ids2) == 2000
+    assert 1400 < len(ids1) < 1800
+
+
+def test_udf_and_time_functions(spark_session):
+    @udf("int")
+    def night(hour, weekday):
+        return int(1) if (16 <= hour <= 20) and (weekday < 5) else int(0)
+
+    df = spark_session.createDataFrame(
+        [("2011-11-28 23:11:35 UTC",), ("2013-10-29 18:00:01 UTC",)], ["ts"])
+    out = df.withColumn("h", F.hour(col("ts"))).withColumn("dow", F.dayofweek(col("ts")) - 2) \
+        .withColumn("dom", F.dayofmonth(col("ts"))).withColumn("woy", F.weekofyear(col("ts"))) \
+        .withColumn("q", F.quarter(col("ts"))).withColumn("y", F.year(col("ts"))) \
+        .withColumn("m", F.month(col("ts"))).withColumn("night", night("h", "dow")).collect()
+    assert (out[0].h, out[0].dow, out[0].dom, out[0].woy, out[0].q, out[0].y, out[0].m) == \
+        (23, 0, 28, 48, 4, 2011, 11)
+    assert (out[1].h, out[1].dow, out[1].night) == (18, 1, 1)
+
+
+def test_groupby_agg_join_sort(spark_session):
+    df = spark_session.range(0, 99).withColumn("k", col("id") % 3)
+    g = df.groupBy("k").agg(F.count("*").alias("n"), F.avg("id"), F.max("id"), F.sum("id"))
+    rows = {r.k: r for r in g.collect()}
+    assert rows[0].n == 33 and rows[1]["avg(id)"] == 49.0 and rows[2]["max(id)"] == 98
+    assert df.groupBy("k").count().count() == 3
+    assert df.agg(F.count("*").alias("c")).collect()[0].c == 99
+    j = df.join(g.select("k", "n"), "k", "left")
+    assert j.count() == 99 and set(j.columns) == {"id", "k", "n"}
+    top = df.orderBy(col("id").desc()).take(2)
+    assert [r.id for r in top] == [98, 97]
+    w = Window.partitionBy("k").orderBy(F.desc("id"))
+    ranked = df.withColumn("rn", F.row_number().over(w)).filter(col("rn") == 1).collect()
+    assert sorted(r.id for r in ranked) == [96, 97, 98]
+
+
+def test_repartition_fillna_sample_distinct(spark_session):
+    df = spark_session.range(0, 1000, numPartitions=2)
+    rp = df.repartition(5)
+    assert rp.rdd.getNumPartitions() == 5 and rp.count() == 1000
+    assert sorted(r.id for r in rp.collect()) == list(range(1000))
+    byk = df.withColumn("k", col("id") % 4).repartition(3, "k")
+    assert byk.count() == 1000
+    nulls = spark_session.createDataFrame([(1, None), (2, 3.0)], T.StructType([
+        T.StructField("a", T.IntegerType()), T.StructField("b", T.DoubleType())]))
+    assert [r.b for r in nulls.fillna(0, ["b"]).collect()] == [0.0, 3.0]
+    assert nulls.dropna().count() == 1
+    assert 50 < df.sample(fraction=0.1, seed=1).count() < 160
+    assert df.withColumn("k", col("id") % 7).select("k").distinct().count() == 7
+    assert df.sortWithinPartitions("id", ascending=False).take(1)[0].id in (499, 999)
+
+
+def test_cache_persist_unpersist(spark_session):
+    df = spark_session.range(0, 100).withColumn("r", F.rand())
+    df.cache()
+    assert df.is_cached
+    first = [r.r for r in df.collect()]
+    assert [r.r for r in df.collect()] == first
+    df.unpersist()
+    assert not df.is_cached and df.count() == 100
+
+
+def test_csv_reader_infers_reference_schema(spark_session):
+    if not os.path.exists(REF_CSV):
+        pytest.skip("reference example csv not mounted")
+    data = spark_session.read.format("csv").option("header", "true") \
+        .option("inferSchema", "true").load("file://" + REF_CSV)
+    types = dict(data.dtypes)
+    assert types["fare_amount"] == "double" and types["passenger_count"] == "int"
+    assert types["pickup_datetime"] == "timestamp" and types["key"] == "string"
+    assert data.count() == 500
+
+
+def test_parquet_roundtrip_and_modes(spark_session, tmp_path):
+    path = str(tmp_path / "pq")
+    df = spark_session.range(0, 100, numPartitions=3).withColumn("v", col("id") * 1.5)
+    df.write.parquet(path, compression="snappy")
+    with pytest.raises(FileExistsError):
+        df.write.parquet(path)
+    df.write.mode("overwrite").parquet(path)
+    back = spark_session.read.parquet(path)
+    assert back.count() == 100 and back.rdd.getNumPartitions() == 3
+    assert os.path.exists(os.path.join(path, "_SUCCESS"))
+    tsv = tmp_path / "x.tsv"
+    tsv.write_text("1\t2.5\n3\t4.5\n")
+    schema = T.StructType([T.StructField("a", T.IntegerType()), T.StructField("b", T.DoubleType())])
+    got = spark_session.read.schema(schema).option("sep", "\t").csv(str(tsv)).collect()
+    assert [(r.a, r.b) for r in got] == [(1, 2.5), (3, 4.5)]
+
+
+def test_rdd_and_create_dataframe(spark_session):
+    sc = spark_session.sparkContext
+    rdd = sc.parallelize([1, 2, 3, 4, 5, 6], 3)
+    assert rdd.getNumPartitions() == 3
+    assert rdd.map(lambda x: x * 2).collect() == [2, 4, 6, 8, 10, 12]
+    assert rdd.mapPartitions(lambda it: [sum(it)]).collect() == [3, 7, 11]
+    df = spark_session.createDataFrame(sc.parallelize([(1, "a"), (2, "b")]), ["n", "s"])
+    assert [tuple(r) for r in df.collect()] == [(1, "a"), (2, "b")]
+    pdf = df.toPandas()
+    assert list(pdf.columns) == ["n", "s"]
+    assert spark_session.createDataFrame(pdf).count() == 2
+
+
+def test_map_in_pandas_and_posexplode(spark_session):
+    df = spark_session.range(0, 10)
+    schema = T.StructType([T.StructField("id", T.LongType()), T.StructField("sq", T.LongType())])
+
+    def fn(frames):
+        for pdf in frames:
+            pdf["sq"] = pdf["id"] ** 2
+            yield pdf
+    assert [r.sq for r in df.mapInPandas(fn, schema).collect()] == [i * i for i in range(10)]
+    ex = df.filter(col("id") < 2).withColumn("b", col("id") + 10) \
+        .select("id", F.posexplode(F.array("id", "b")))
+    assert [(r.id, r.pos, r.col) for r in ex.collect()] == [(0, 0, 0), (0, 1, 10), (1, 0, 1), (1, 1, 11)]
+
+
+def test_conf_and_context(spark_session):
+    spark_session.conf.set("spark.sql.session.timeZone", "UTC")
+    assert spark_session.conf.get("spark.sql.session.timeZone") == "UTC"
+    sc = spark_session.sparkContext
+    assert sc.appName == "RayDP test" and sc.applicationId.startswith("app-")
+    assert sc.getConf().get("does.not.exist", "dflt") == "dflt"
+    with pytest.raises(NotImplementedError):
+        spark_session.sql("select 1")
+
+
+def test_initial_executor_number():
+    # same four cases as reference TestRayCoarseGrainedSchedulerBackend.java:32-65
+    assert get_initial_target_executor_number({}) == 2
+    assert get_initial_target_executor_number({"spark.executor.instances": "-1"}) == 2
+    assert get_initial_target_executor_number({"spark.executor.instances": "5"}) == 5
+    dyn = {"spark.dynamicAllocation.enabled": "true", "spark.dynamicAllocation.minExecutors": "1",
+           "spark.dynamicAllocation.initialExecutors": "3", "spark.dynamicAllocation.maxExecutors": "4"}
+    assert get_initial_target_executor_number(dyn) == 3
