@@ -1,0 +1,485 @@
+// K6: tcgen05 / TMEM GEMMs fed by TMA, with fused epilogues.
+//
+// Replaces the cuBLAS calls behind nn.Linear forward / backward in the reference's training
+// loop (reference python/raydp/torch/estimator.py:276-286 -> model(inputs), loss.backward()).
+//
+//  * rdp_gemm_tn   : C[M,N] = A[M,K] . B[N,K]^T  (both operands K-major: forward with W[N,K],
+//                    dgrad with a pre-transposed weight).  Persistent, warp-specialised:
+//                    warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread issues
+//                    tcgen05.mma), warps 2-5 = epilogue (tcgen05.ld from a double-buffered TMEM
+//                    accumulator so the epilogue of tile i overlaps the MMAs of tile i+1).
+//                    Epilogue options: +bias, ReLU, ReLU-mask by an aux matrix, bf16/fp32 store,
+//                    and per-column batch statistics (sum & sum-of-squares, or sum & sum(v*aux))
+//                    accumulated in shared memory and flushed once per CTA -- this is what lets
+//                    BatchNorm's batch statistics ride on the GEMM instead of re-reading the
+//                    activations.
+//  * rdp_gemm_wgrad: D[Mw,Nw] += sum_r G[r,Mw] . X[r,Nw]  (reduction over the batch dimension,
+//                    both operands MN-major straight out of the row-major activations, split
+//                    over CTAs along the batch, fp32 atomics into D).
+#include "common.cuh"
+#include "raydp_b200.h"
+
+namespace rdp {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;          // 64 bf16 = 128 B = one swizzle row
+constexpr int kMaxNTile = 256;
+constexpr int kStages = 4;
+constexpr int kGemmThreads = 192;    // 6 warps
+constexpr int kStatsCols = 1024;
+
+struct GemmTnParams {
+  int M, N, K;
+  int n_tile;
+  int num_m_tiles, num_n_tiles, num_k_blocks;
+  const float* bias;
+  int relu;
+  void* out;
+  int out_f32;
+  int ldc;
+  const __nv_bfloat16* aux;
+  int ld_aux;
+  int aux_relu_mask;
+  int stats_mode;   // 0 none | 1: sum(v), sum(v*v) | 2: sum(v), sum(v*aux)
+  float* stats;     // [2, N]
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const GemmTnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve shared memory: [stage tiles][barriers][tmem ptr][stats]
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t a_bytes = kBlockM * kBlockK * 2;                 // 16 KB
+  const uint32_t b_bytes = uint32_t(p.n_tile) * kBlockK * 2;      // n_tile * 128 B
+  const uint32_t stage_bytes = a_bytes + ((b_bytes + 1023) & ~1023u);
+  uint8_t* tiles = smem;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + kStages * stage_bytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* s_stats = reinterpret_cast<float*>(tmem_ptr + 4);        // [2][kStatsCols]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (p.stats_mode) {
+    for (int i = threadIdx.x; i < 2 * kStatsCols; i += blockDim.x) s_stats[i] = 0.f;
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], 128);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = tiles + stage * stage_bytes;
+          uint8_t* b_dst = a_dst + a_bytes;
+          mbar_expect_tx(&full_bar[stage], a_bytes + b_bytes);
+          tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * kBlockK, m_blk * kBlockM);
+          tma_load_2d(b_dst, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * p.n_tile);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(kBlockM, uint32_t(p.n_tile), false, false);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + uint32_t(acc) * kMaxNTile;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(tiles + stage * stage_bytes);
+          const uint32_t b_addr = a_addr + a_bytes;
+          const uint64_t a_desc = umma_smem_desc(a_addr, 16, 1024);
+          const uint64_t b_desc = umma_smem_desc(b_addr, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            // advance 16 elements (32 B) along K inside the 128-byte swizzle row
+            umma_bf16(d_tmem, a_desc + uint64_t(k * 2), b_desc + uint64_t(k * 2), idesc,
+                      (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);           // frees the smem slot when the MMAs retire
+          if (kb == p.num_k_blocks - 1) umma_commit(&tmem_full[acc]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5) =====================
+    const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
+      const int row = m_blk * kBlockM + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (uint32_t(quad * 32) << 16) + uint32_t(acc) * kMaxNTile;
+      const int n0 = n_blk * p.n_tile;
+      for (int c = 0; c < p.n_tile; c += 32) {
+        const int col0 = n0 + c;
+        if (col0 >= p.N) break;
+        const int ncols = min(32, min(p.n_tile - c, p.N - col0));   // 16 or 32
+        uint32_t raw[32];
+        tmem_ld_32x32(t_row + uint32_t(c), raw);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += (j < ncols) ? __ldg(p.bias + col0 + j) : 0.f;
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        float aux[32];
+        const bool need_aux = (p.aux != nullptr) && (p.aux_relu_mask || p.stats_mode == 2);
+        if (need_aux) {
+          if (row_ok) {
+            const uint4* ap = reinterpret_cast<const uint4*>(p.aux + size_t(row) * p.ld_aux + col0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              if (q * 8 < ncols) {
+                uint4 u = __ldg(ap + q);
+                float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y);
+                float2 f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+                aux[q * 8 + 0] = f0.x; aux[q * 8 + 1] = f0.y; aux[q * 8 + 2] = f1.x; aux[q * 8 + 3] = f1.y;
+                aux[q * 8 + 4] = f2.x; aux[q * 8 + 5] = f2.y; aux[q * 8 + 6] = f3.x; aux[q * 8 + 7] = f3.y;
+              } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) aux[q * 8 + j] = 0.f;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) aux[j] = 0.f;
+          }
+          if (p.aux_relu_mask) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = aux[j] > 0.f ? v[j] : 0.f;
+          }
+        }
+        if (!row_ok) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        }
+        // ---- store ----
+        if (row_ok) {
+          if (p.out_f32) {
+            float4* op = reinterpret_cast<float4*>(static_cast<float*>(p.out) + size_t(row) * p.ldc + col0);
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              if (q * 4 < ncols) op[q] = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+          } else {
+            uint4* op = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + size_t(row) * p.ldc + col0);
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              if (q * 8 < ncols)
+                op[q] = make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
+                                   pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+          }
+        }
+        // ---- per-column batch statistics ----
+        if (p.stats_mode) {
+          float w[32];
+          if (p.stats_mode == 1) {
+            // statistics of what the next layer will read: the bf16-rounded activation
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              float r = p.out_f32 ? v[j] : __bfloat162float(__float2bfloat16_rn(v[j]));
+              v[j] = r;
+              w[j] = r * r;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) w[j] = v[j] * aux[j];
+          }
+          const float s0 = warp_transpose_reduce32(v, lane);
+          const float s1 = warp_transpose_reduce32(w, lane);
+          if (lane < ncols) {
+            const int col = col0 + lane;
+            if (col < kStatsCols) {
+              atomicAdd(&s_stats[col], s0);
+              atomicAdd(&s_stats[kStatsCols + col], s1);
+            } else {
+              atomicAdd(&p.stats[col], s0);
+              atomicAdd(&p.stats[p.N + col], s1);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (p.stats_mode) {
+    const int ncol = min(p.N, kStatsCols);
+    for (int i = threadIdx.x; i < ncol; i += blockDim.x) {
+      const float a = s_stats[i], b = s_stats[kStatsCols + i];
+      if (a != 0.f) atomicAdd(&p.stats[i], a);
+      if (b != 0.f) atomicAdd(&p.stats[p.N + i], b);
+    }
+  }
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// wgrad: D[Mw, Nw] += sum over batch rows of G[r, :Mw]^T X[r, :Nw]   (both MN-major)
+// ----------------------------------------------------------------------------------------------
+struct WgradParams {
+  int rows;            // batch rows (reduction length)
+  int Mw, Nw;          // output extents (Mw <= 128 per CTA tile, Nw <= 256 per CTA tile)
+  int n_tile;          // multiple of 16, <= 256
+  int rows_per_split;  // multiple of 64
+  float* out;          // [Mw_total, ldo] fp32, accumulated with atomics
+  int ldo;
+  float* colsum;       // optional [Mw_total]: sum over rows of G (bias gradient), or null
+};
+
+constexpr int kWgradThreads = 192;
+constexpr int kWgradStages = 4;
+
+__global__ void __launch_bounds__(kWgradThreads, 1)
+gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_constant__ CUtensorMap tmap_x,
+                  const WgradParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int n_chunks = (p.n_tile + 63) / 64;                 // 64-wide MN chunks of the X operand
+  const uint32_t chunk_bytes = kBlockK * 128;                // 64 k-rows x 128 B = 8 KB
+  const uint32_t a_bytes = 2 * chunk_bytes;                  // 128 output rows = 2 chunks of G
+  const uint32_t b_bytes = uint32_t(n_chunks) * chunk_bytes;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  uint8_t* tiles = smem;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + kWgradStages * stage_bytes);
+  uint64_t* empty_bar = full_bar + kWgradStages;
+  uint64_t* tmem_full = empty_bar + kWgradStages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int split = blockIdx.x;
+  const int m_blk = blockIdx.y;
+  const int n_blk = blockIdx.z;
+  const int r_begin = split * p.rows_per_split;
+  const int r_end = min(p.rows, r_begin + p.rows_per_split);
+  const int num_kb = (r_end > r_begin) ? (r_end - r_begin + kBlockK - 1) / kBlockK : 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_g);
+    tma_prefetch_desc(&tmap_x);
+    for (int s = 0; s < kWgradStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<256>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (num_kb > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = tiles + stage * stage_bytes;
+          uint8_t* b_dst = a_dst + a_bytes;
+          mbar_expect_tx(&full_bar[stage], stage_bytes);
+          const int r = r_begin + kb * kBlockK;
+          // rows past r_end inside the last k-block belong to the next split: they are loaded
+          // by that split too, so clamp by giving this split whole k-blocks only (host side
+          // guarantees rows_per_split % 64 == 0, hence no overlap); rows >= p.rows read as 0.
+          tma_load_2d(a_dst, &tmap_g, &full_bar[stage], m_blk * 128, r);
+          tma_load_2d(a_dst + chunk_bytes, &tmap_g, &full_bar[stage], m_blk * 128 + 64, r);
+          for (int ch = 0; ch < n_chunks; ++ch)
+            tma_load_2d(b_dst + ch * chunk_bytes, &tmap_x, &full_bar[stage], n_blk * p.n_tile + ch * 64, r);
+          if (++stage == kWgradStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        const uint32_t idesc = umma_idesc_bf16(128, uint32_t(p.n_tile), true, true);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(tiles + stage * stage_bytes);
+          const uint32_t b_addr = a_addr + a_bytes;
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            // 16 reduction rows = 2048 B further down the tile; chunks are LBO = 8 KB apart
+            const uint64_t a_desc = umma_smem_desc(a_addr + k * 2048, chunk_bytes, 1024);
+            const uint64_t b_desc = umma_smem_desc(b_addr + k * 2048, chunk_bytes, 1024);
+            umma_bf16(tmem_base, a_desc, b_desc, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (kb == num_kb - 1) umma_commit(tmem_full);
+          if (++stage == kWgradStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else {
+      const int quad = warp & 3;
+      const int m = m_blk * 128 + quad * 32 + lane;
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (uint32_t(quad * 32) << 16);
+      for (int c = 0; c < p.n_tile; c += 32) {
+        const int col0 = n_blk * p.n_tile + c;
+        if (col0 >= p.Nw) break;
+        uint32_t raw[32];
+        tmem_ld_32x32(t_row + uint32_t(c), raw);
+        tmem_ld_wait();
+        if (m < p.Mw) {
+          float* dst = p.out + size_t(m) * p.ldo + col0;
+          const int ncols = min(32, min(p.n_tile - c, p.Nw - col0));
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < ncols) atomicAdd(dst + j, __uint_as_float(raw[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<256>(tmem_base);
+  }
+}
+
+static size_t gemm_tn_smem_bytes(int n_tile) {
+  const size_t a_bytes = kBlockM * kBlockK * 2;
+  const size_t b_bytes = (size_t(n_tile) * kBlockK * 2 + 1023) & ~size_t(1023);
+  return kStages * (a_bytes + b_bytes) + 256 + 2 * kStatsCols * sizeof(float) + 1024;
+}
+
+}  // namespace rdp
+
+using namespace rdp;
+
+extern "C" {
+
+int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int out_f32,
+                int M, int N, int K, const float* bias, int relu, const void* aux, int ld_aux,
+                int aux_relu_mask, int stats_mode, float* stats, void* stream) {
+  RDP_REQUIRE(M > 0 && N > 0 && K > 0, "rdp_gemm_tn: empty problem %dx%dx%d", M, N, K);
+  RDP_REQUIRE(N % 16 == 0, "rdp_gemm_tn: N=%d must be a multiple of 16", N);
+  RDP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "rdp_gemm_tn: pitches must be multiples of 8");
+  RDP_REQUIRE(stats_mode == 0 || stats != nullptr, "rdp_gemm_tn: stats buffer missing");
+  RDP_REQUIRE(!(stats_mode == 2 || aux_relu_mask) || (aux != nullptr && ld_aux % 8 == 0),
+              "rdp_gemm_tn: aux matrix missing or mis-pitched");
+  GemmTnParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.n_tile = N >= kMaxNTile ? kMaxNTile : N;
+  if (N > kMaxNTile && N % kMaxNTile != 0) p.n_tile = (N % 128 == 0) ? 128 : ((N % 64 == 0) ? 64 : 16);
+  p.num_m_tiles = (M + kBlockM - 1) / kBlockM;
+  p.num_n_tiles = (N + p.n_tile - 1) / p.n_tile;
+  p.num_k_blocks = (K + kBlockK - 1) / kBlockK;
+  p.bias = bias; p.relu = relu; p.out = out; p.out_f32 = out_f32; p.ldc = ldc;
+  p.aux = static_cast<const __nv_bfloat16*>(aux); p.ld_aux = ld_aux; p.aux_relu_mask = aux_relu_mask;
+  p.stats_mode = stats_mode; p.stats = stats;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d_bf16(&ta, a, M, K, lda, kBlockM, kBlockK);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tb, b, N, K, ldb, p.n_tile, kBlockK);
+  if (rc) return rc;
+  const size_t smem = gemm_tn_smem_bytes(p.n_tile);
+  static bool attr_set = false;
+  if (!attr_set) {
+    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_tn_kernel<<<grid, kGemmThreads, smem, static_cast<cudaStream_t>(stream)>>>(ta, tb, p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
+                   int Mw, int Nw, void* stream) {
+  RDP_REQUIRE(rows > 0 && Mw > 0 && Nw > 0, "rdp_gemm_wgrad: empty problem");
+  RDP_REQUIRE(ldg % 8 == 0 && ldx % 8 == 0, "rdp_gemm_wgrad: pitches must be multiples of 8");
+  WgradParams p;
+  p.rows = rows; p.Mw = Mw; p.Nw = Nw;
+  int n_tile = ((Nw + 15) / 16) * 16;
+  if (n_tile > 256) n_tile = 256;
+  p.n_tile = n_tile;
+  const int m_tiles = (Mw + 127) / 128;
+  const int n_tiles = (Nw + n_tile - 1) / n_tile;
+  int splits = num_sms() / (m_tiles * n_tiles);
+  if (splits < 1) splits = 1;
+  int rps = (rows + splits - 1) / splits;
+  rps = ((rps + kBlockK - 1) / kBlockK) * kBlockK;
+  if (rps < 4 * kBlockK) rps = 4 * kBlockK;
+  splits = (rows + rps - 1) / rps;
+  p.rows_per_split = rps;
+  p.out = out; p.ldo = ldo; p.colsum = nullptr;
+  CUtensorMap tg, tx;
+  int rc = make_tmap_2d_bf16(&tg, g, rows, Mw, ldg, kBlockK, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tx, x, rows, Nw, ldx, kBlockK, 64);
+  if (rc) return rc;
+  const int n_chunks = (n_tile + 63) / 64;
+  const size_t smem = size_t(kWgradStages) * (2 + n_chunks) * (kBlockK * 128) + 256 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  dim3 grid(splits, m_tiles, n_tiles);
+  gemm_wgrad_kernel<<<grid, kWgradThreads, smem, static_cast<cudaStream_t>(stream)>>>(tg, tx, p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,454 @@
+// K7 / K8 and the glue around K6 for Linear -> ReLU -> BatchNorm1d chains (workload A of
+// reference examples/pytorch_nyctaxi.py:69-92).
+//
+// Design: BatchNorm is never materialised.  The GEMM epilogue emits per-column sum / sum-sq of
+// the ReLU output z_l (rdp_gemm_tn stats_mode 1); rdp_bn_fold turns them into (a, c) with
+// y_l = a*z_l + c and folds that affine map into the *next* layer's weights
+// (W' = W diag(a), b' = b + W c), so the next GEMM reads z_l directly.  Backward mirrors it:
+// the dgrad GEMM epilogue emits sum(dy) and sum(dy*z) (stats_mode 2), rdp_bn_relu_bwd applies
+// the BatchNorm + ReLU backward in one pass, and rdp_grad_fixup maps weight gradients taken
+// against z back to gradients against y.  rdp_mlp_head fuses the last Linear (-> 1 output),
+// the loss, its derivative and the metric sums (A5-A7: no per-step host sync).
+#include "common.cuh"
+#include "raydp_b200.h"
+
+namespace rdp {
+
+// ------------------------------------------------------------------------------------------
+// BN finalize + fold into the next Linear
+// ------------------------------------------------------------------------------------------
+struct BnFoldParams {
+  const float* stats;   // [2, K]  sum(z), sum(z*z) over the batch  (null when use_running)
+  float count;          // batch rows
+  const float* gamma;   // [K]
+  const float* beta;    // [K]
+  float* running_mean;  // [K] updated in place when training
+  float* running_var;   // [K]
+  float momentum, eps;
+  int use_running;      // eval mode
+  float* a;             // [K] out: gamma * rstd
+  float* c;             // [K] out: beta - mean * a
+  float* mean;          // [K] out
+  float* rstd;          // [K] out
+  const float* w;       // [N, K] next layer master weight (fp32)
+  const float* b;       // [N]
+  int N, K;
+  __nv_bfloat16* w_folded;    // [N, ldw]   W * diag(a)
+  int ldw;
+  __nv_bfloat16* w_folded_t;  // [K, ldwt]  transposed copy for dgrad (may be null)
+  int ldwt;
+  float* b_folded;            // [N]
+};
+
+__global__ void bn_fold_kernel(const BnFoldParams p) {
+  // one block per output row n of the next layer (+ extra blocks are not needed: N >= 1)
+  extern __shared__ float sh[];
+  float* s_a = sh;
+  float* s_c = sh + p.K;
+  for (int k = threadIdx.x; k < p.K; k += blockDim.x) {
+    float mean, var;
+    if (p.use_running) {
+      mean = p.running_mean[k];
+      var = p.running_var[k];
+    } else {
+      mean = p.stats[k] / p.count;
+      var = fmaxf(p.stats[p.K + k] / p.count - mean * mean, 0.f);
+    }
+    const float rstd = rsqrtf(var + p.eps);
+    const float a = p.gamma[k] * rstd;
+    const float c = p.beta[k] - mean * a;
+    s_a[k] = a;
+    s_c[k] = c;
+    if (blockIdx.x == 0) {
+      p.a[k] = a; p.c[k] = c; p.mean[k] = mean; p.rstd[k] = rstd;
+      if (!p.use_running && p.running_mean != nullptr) {
+        const float unbiased = p.count > 1.f ? var * p.count / (p.count - 1.f) : var;
+        p.running_mean[k] = (1.f - p.momentum) * p.running_mean[k] + p.momentum * mean;
+        p.running_var[k] = (1.f - p.momentum) * p.running_var[k] + p.momentum * unbiased;
+      }
+    }
+  }
+  __syncthreads();
+  const int n = blockIdx.x;
+  if (n >= p.N) return;
+  float dot = 0.f;
+  for (int k = threadIdx.x; k < p.K; k += blockDim.x) {
+    const float w = p.w[size_t(n) * p.K + k];
+    const __nv_bfloat16 wf = __float2bfloat16_rn(w * s_a[k]);
+    p.w_folded[size_t(n) * p.ldw + k] = wf;
+    if (p.w_folded_t != nullptr) p.w_folded_t[size_t(k) * p.ldwt + n] = wf;
+    dot += w * s_c[k];
+  }
+  __shared__ float red[32];
+  dot = warp_sum(dot);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = dot;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x + 31) / 32 ? red[threadIdx.x] : 0.f;
+    v = warp_sum(v);
+    if (threadIdx.x == 0) p.b_folded[n] = p.b[n] + v;
+  }
+}
+
+// fp32 master weight -> bf16 (optionally padded pitch) + optional transposed copy
+__global__ void cast_weight_kernel(const float* __restrict__ w, int N, int K, __nv_bfloat16* out,
+                                   int ldo, __nv_bfloat16* out_t, int ldt) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * K) return;
+  const int n = idx / K, k = idx % K;
+  const __nv_bfloat16 v = __float2bfloat16_rn(w[idx]);
+  out[size_t(n) * ldo + k] = v;
+  if (out_t != nullptr) out_t[size_t(k) * ldt + n] = v;
+}
+
+// ------------------------------------------------------------------------------------------
+// BatchNorm + ReLU backward (elementwise, with column sums of the result for the bias grad)
+// ------------------------------------------------------------------------------------------
+struct BnReluBwdParams {
+  const __nv_bfloat16* dy;   // [B, N] grad w.r.t. the BN output
+  const __nv_bfloat16* z;    // [B, N] ReLU output (BN input)
+  __nv_bfloat16* dpre;       // [B, N] grad w.r.t. the Linear output (pre-ReLU)
+  int B, N, ld;
+  const float* stats2;       // [2, N] sum(dy), sum(dy*z)
+  const float* mean;         // [N]
+  const float* rstd;         // [N]
+  const float* a;            // [N] gamma*rstd
+  float* dgamma;             // [N] out (=)
+  float* dbeta;              // [N] out (=)
+  float* dbias;              // [N] out (+=, must be zeroed): column sums of dpre
+  int has_bn;                // 0: plain ReLU backward (dpre = dy * (z > 0))
+};
+
+__global__ void __launch_bounds__(256)
+bn_relu_bwd_kernel(const BnReluBwdParams p) {
+  // thread -> 8 consecutive columns (one 16-byte vector); blockDim.x = 256
+  const int vec_per_row = p.N / 8;
+  const int tcol = threadIdx.x % vec_per_row;
+  const int trow = threadIdx.x / vec_per_row;
+  const int rows_per_block = blockDim.x / vec_per_row;
+  const int c0 = tcol * 8;
+  float m1[8], m2[8], mu[8], rs[8], aa[8], acc[8];
+  const float invB = 1.f / float(p.B);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    acc[j] = 0.f;
+    if (p.has_bn) {
+      const float sdy = p.stats2[c0 + j], sdyz = p.stats2[p.N + c0 + j];
+      mu[j] = p.mean[c0 + j];
+      rs[j] = p.rstd[c0 + j];
+      aa[j] = p.a[c0 + j];
+      const float sdyzh = rs[j] * (sdyz - mu[j] * sdy);     // sum(dy * zhat)
+      m1[j] = sdy * invB;
+      m2[j] = sdyzh * invB;
+      if (blockIdx.x == 0 && trow == 0) {
+        p.dgamma[c0 + j] = sdyzh;
+        p.dbeta[c0 + j] = sdy;
+      }
+    }
+  }
+  for (int r = blockIdx.x * rows_per_block + trow; r < p.B; r += gridDim.x * rows_per_block) {
+    const uint4 udy = __ldg(reinterpret_cast<const uint4*>(p.dy + size_t(r) * p.ld + c0));
+    const uint4 uz = __ldg(reinterpret_cast<const uint4*>(p.z + size_t(r) * p.ld + c0));
+    const uint32_t dyw[4] = {udy.x, udy.y, udy.z, udy.w};
+    const uint32_t zw[4] = {uz.x, uz.y, uz.z, uz.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 d = unpack_bf16x2(dyw[q]);
+      const float2 zz = unpack_bf16x2(zw[q]);
+      float o0, o1;
+      if (p.has_bn) {
+        const float zh0 = (zz.x - mu[2 * q]) * rs[2 * q];
+        const float zh1 = (zz.y - mu[2 * q + 1]) * rs[2 * q + 1];
+        o0 = zz.x > 0.f ? aa[2 * q] * (d.x - m1[2 * q] - zh0 * m2[2 * q]) : 0.f;
+        o1 = zz.y > 0.f ? aa[2 * q + 1] * (d.y - m1[2 * q + 1] - zh1 * m2[2 * q + 1]) : 0.f;
+      } else {
+        o0 = zz.x > 0.f ? d.x : 0.f;
+        o1 = zz.y > 0.f ? d.y : 0.f;
+      }
+      ow[q] = pack_bf16x2(o0, o1);
+      const float2 rounded = unpack_bf16x2(ow[q]);
+      acc[2 * q] += rounded.x;
+      acc[2 * q + 1] += rounded.y;
+    }
+    *reinterpret_cast<uint4*>(p.dpre + size_t(r) * p.ld + c0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+  extern __shared__ float s_col[];   // [N]
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x) s_col[i] = 0.f;
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 8; ++j) atomicAdd(&s_col[c0 + j], acc[j]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x)
+    if (s_col[i] != 0.f) atomicAdd(&p.dbias[i], s_col[i]);
+}
+
+// ------------------------------------------------------------------------------------------
+// head: y = (a*z + c) . w + b ; loss ; dloss ; metrics ; dy = dpred * w ; reductions
+// ------------------------------------------------------------------------------------------
+struct HeadParams {
+  const __nv_bfloat16* z;   // [B, K] last hidden activation (ReLU output)
+  int B, K, ld;
+  const float* a;           // [K] BN fold of the last BatchNorm (null -> identity)
+  const float* c;           // [K]
+  const float* w;           // [K] last Linear weight (fp32 master)
+  const float* bias;        // [1]
+  const float* target;      // [B]
+  int loss_kind;            // 0 MSE, 1 SmoothL1 (beta 1), 2 BCEWithLogits
+  float grad_scale;         // 1/B for mean reduction (0 in eval mode: no backward outputs)
+  float* pred;              // [B] out (may be null)
+  float* accum;             // [8]: loss_sum, abs_err_sum, sq_err_sum, count, correct, -, -, -
+  __nv_bfloat16* dy;        // [B, K] out: grad w.r.t. the BN output of the last hidden layer
+  float* stats2;            // [2, K] out (+=): sum(dy), sum(dy*z)
+  float* dw;                // [K] out (+=): grad of w
+  float* db;                // [1] out (+=)
+};
+
+template <int kK>
+__global__ void __launch_bounds__(256)
+mlp_head_kernel(const HeadParams p) {
+  float wf[kK], cw = 0.f;          // folded weight w*a and constant c.w
+#pragma unroll
+  for (int k = 0; k < kK; ++k) {
+    const float a = p.a ? p.a[k] : 1.f, c = p.c ? p.c[k] : 0.f;
+    wf[k] = p.w[k] * a;
+    cw += p.w[k] * c;
+  }
+  const float bias = p.bias[0] + cw;
+  float s_loss = 0.f, s_abs = 0.f, s_sq = 0.f, s_cnt = 0.f, s_corr = 0.f, s_dp = 0.f;
+  float s_dpz[kK];
+#pragma unroll
+  for (int k = 0; k < kK; ++k) s_dpz[k] = 0.f;
+  const bool train = p.grad_scale != 0.f;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < p.B; r += gridDim.x * blockDim.x) {
+    float zr[kK];
+    const uint4* zp = reinterpret_cast<const uint4*>(p.z + size_t(r) * p.ld);
+#pragma unroll
+    for (int q = 0; q < kK / 8; ++q) {
+      const uint4 u = __ldg(zp + q);
+      const float2 f0 = unpack_bf16x2(u.x), f1 = unpack_bf16x2(u.y), f2 = unpack_bf16x2(u.z), f3 = unpack_bf16x2(u.w);
+      zr[q * 8 + 0] = f0.x; zr[q * 8 + 1] = f0.y; zr[q * 8 + 2] = f1.x; zr[q * 8 + 3] = f1.y;
+      zr[q * 8 + 4] = f2.x; zr[q * 8 + 5] = f2.y; zr[q * 8 + 6] = f3.x; zr[q * 8 + 7] = f3.y;
+    }
+    float y = bias;
+#pragma unroll
+    for (int k = 0; k < kK; ++k) y = fmaf(zr[k], wf[k], y);
+    const float t = p.target[r];
+    float loss, dl;
+    if (p.loss_kind == 2) {                      // BCE with logits, numerically stable
+      loss = fmaxf(y, 0.f) - y * t + log1pf(__expf(-fabsf(y)));
+      const float sig = 1.f / (1.f + __expf(-y));
+      dl = sig - t;
+      s_corr += ((y >= 0.f) == (t >= 0.5f)) ? 1.f : 0.f;
+    } else {
+      const float e = y - t;
+      if (p.loss_kind == 0) { loss = e * e; dl = 2.f * e; }
+      else { const float ae = fabsf(e); loss = ae < 1.f ? 0.5f * e * e : ae - 0.5f; dl = ae < 1.f ? e : (e > 0.f ? 1.f : -1.f); }
+    }
+    const float e = y - t;
+    s_loss += loss; s_abs += fabsf(e); s_sq += e * e; s_cnt += 1.f;
+    if (p.pred) p.pred[r] = y;
+    if (train) {
+      const float dp = dl * p.grad_scale;
+      s_dp += dp;
+      uint4* dyp = reinterpret_cast<uint4*>(p.dy + size_t(r) * p.ld);
+#pragma unroll
+      for (int q = 0; q < kK / 8; ++q) {
+        uint32_t o[4];
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const int k = q * 8 + h * 2;
+          // dy is the gradient w.r.t. the (virtual) BN output: dpred * w (unfolded weight)
+          o[h] = pack_bf16x2(dp * p.w[k], dp * p.w[k + 1]);
+        }
+        dyp[q] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+#pragma unroll
+      for (int k = 0; k < kK; ++k) s_dpz[k] = fmaf(dp, zr[k], s_dpz[k]);
+    }
+  }
+  // block reduction -> global atomics
+  __shared__ float red[8][6 + kK];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float vals[6] = {s_loss, s_abs, s_sq, s_cnt, s_corr, s_dp};
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const float v = warp_sum(vals[i]);
+    if (lane == 0) red[wid][i] = v;
+  }
+#pragma unroll
+  for (int k = 0; k < kK; ++k) {
+    const float v = warp_sum(s_dpz[k]);
+    if (lane == 0) red[wid][6 + k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6 + kK) {
+    float v = 0.f;
+    for (int w8 = 0; w8 < 8; ++w8) v += red[w8][threadIdx.x];
+    const int i = threadIdx.x;
+    if (i < 5) atomicAdd(&p.accum[i], v);
+    else if (train) {
+      if (i == 5) {
+        atomicAdd(p.db, v);
+        // sum over batch of dy[:, k] = w[k] * sum(dp); and dw picks up the c term
+        for (int k = 0; k < kK; ++k) {
+          atomicAdd(&p.stats2[k], p.w[k] * v);
+          atomicAdd(&p.dw[k], (p.c ? p.c[k] : 0.f) * v);
+        }
+      } else {
+        const int k = i - 6;
+        atomicAdd(&p.stats2[kK + k], p.w[k] * v);            // sum(dy * z)
+        atomicAdd(&p.dw[k], (p.a ? p.a[k] : 1.f) * v);       // dw = a * sum(dp * z) + c * sum(dp)
+      }
+    }
+  }
+}
+
+// dW[n,k] = dWraw[n,k] * a[k] + db[n] * c[k]   (gradient taken against z mapped to y = a z + c)
+__global__ void grad_fixup_kernel(float* dw, const float* db, const float* a, const float* c, int N, int K) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * K) return;
+  const int n = idx / K, k = idx % K;
+  dw[idx] = dw[idx] * a[k] + db[n] * c[k];
+}
+
+// ------------------------------------------------------------------------------------------
+// fused optimizers over the flat parameter buffer
+// ------------------------------------------------------------------------------------------
+struct AdamParams {
+  float* p; const float* g; float* m; float* v;
+  int64_t n;
+  float lr, beta1, beta2, eps, weight_decay;
+  float bc1, bc2;        // 1 - beta1^t, 1 - beta2^t
+  float grad_scale;      // e.g. 1/world_size
+  int adamw;
+};
+
+__device__ __forceinline__ float adam_update(float p, float g, float& m, float& v, const AdamParams& a) {
+  g *= a.grad_scale;
+  if (a.weight_decay != 0.f) { if (a.adamw) p *= (1.f - a.lr * a.weight_decay); else g += a.weight_decay * p; }
+  m = a.beta1 * m + (1.f - a.beta1) * g;
+  v = a.beta2 * v + (1.f - a.beta2) * g * g;
+  const float denom = sqrtf(v) / sqrtf(a.bc2) + a.eps;
+  return p - (a.lr / a.bc1) * (m / denom);
+}
+
+__global__ void adam_kernel(const AdamParams a) {
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < a.n; i += int64_t(gridDim.x) * blockDim.x) {
+    float m = a.m[i], v = a.v[i];
+    a.p[i] = adam_update(a.p[i], a.g[i], m, v, a);
+    a.m[i] = m; a.v[i] = v;
+  }
+}
+
+struct SgdParams {
+  float* p; const float* g; float* buf;   // momentum buffer or null
+  int64_t n;
+  float lr, momentum, dampening, weight_decay, grad_scale;
+  int nesterov, first_step;
+};
+
+__global__ void sgd_kernel(const SgdParams s) {
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < s.n; i += int64_t(gridDim.x) * blockDim.x) {
+    float p = s.p[i];
+    float g = s.g[i] * s.grad_scale;
+    if (s.weight_decay != 0.f) g += s.weight_decay * p;
+    if (s.buf != nullptr && s.momentum != 0.f) {
+      float b = s.first_step ? g : s.momentum * s.buf[i] + (1.f - s.dampening) * g;
+      s.buf[i] = b;
+      g = s.nesterov ? g + s.momentum * b : b;
+    }
+    s.p[i] = p - s.lr * g;
+  }
+}
+
+}  // namespace rdp
+
+using namespace rdp;
+
+extern "C" {
+
+int rdp_bn_fold(const float* stats, float count, const float* gamma, const float* beta,
+                float* running_mean, float* running_var, float momentum, float eps, int use_running,
+                float* a, float* c, float* mean, float* rstd, const float* w, const float* b, int N, int K,
+                void* w_folded, int ldw, void* w_folded_t, int ldwt, float* b_folded, void* stream) {
+  RDP_REQUIRE(K > 0 && N > 0 && K <= 8192, "rdp_bn_fold: bad shape N=%d K=%d", N, K);
+  BnFoldParams p{stats, count, gamma, beta, running_mean, running_var, momentum, eps, use_running,
+                 a, c, mean, rstd, w, b, N, K, static_cast<__nv_bfloat16*>(w_folded), ldw,
+                 static_cast<__nv_bfloat16*>(w_folded_t), ldwt, b_folded};
+  const int threads = K >= 256 ? 256 : (K >= 128 ? 128 : 64);
+  bn_fold_kernel<<<N, threads, 2 * K * sizeof(float), static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_cast_weight(const float* w, int N, int K, void* out, int ldo, void* out_t, int ldt, void* stream) {
+  const int total = N * K;
+  cast_weight_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w, N, K, static_cast<__nv_bfloat16*>(out), ldo, static_cast<__nv_bfloat16*>(out_t), ldt);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_bn_relu_bwd(const void* dy, const void* z, void* dpre, int B, int N, int ld, const float* stats2,
+                    const float* mean, const float* rstd, const float* a, float* dgamma, float* dbeta,
+                    float* dbias, int has_bn, void* stream) {
+  RDP_REQUIRE(N % 8 == 0 && N <= 2048 && ld % 8 == 0, "rdp_bn_relu_bwd: N=%d must be a multiple of 8 and <= 2048", N);
+  RDP_REQUIRE(256 % (N / 8) == 0 || N / 8 > 256, "rdp_bn_relu_bwd: N/8=%d must divide 256", N / 8);
+  BnReluBwdParams p{static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z),
+                    static_cast<__nv_bfloat16*>(dpre), B, N, ld, stats2, mean, rstd, a, dgamma, dbeta, dbias, has_bn};
+  const int rows_per_block = 256 / (N / 8);
+  int grid = (B + rows_per_block - 1) / rows_per_block;
+  const int cap = num_sms() * 8;
+  if (grid > cap) grid = cap;
+  bn_relu_bwd_kernel<<<grid, 256, N * sizeof(float), static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const float* c, const float* w,
+                 const float* bias, const float* target, int loss_kind, float grad_scale, float* pred,
+                 float* accum, void* dy, float* stats2, float* dw, float* db, void* stream) {
+  RDP_REQUIRE(K == 16 || K == 32 || K == 64, "rdp_mlp_head: K=%d (supported: 16, 32, 64)", K);
+  HeadParams p{static_cast<const __nv_bfloat16*>(z), B, K, ld, a, c, w, bias, target, loss_kind, grad_scale,
+               pred, accum, static_cast<__nv_bfloat16*>(dy), stats2, dw, db};
+  int grid = (B + 255) / 256;
+  const int cap = num_sms() * 4;
+  if (grid > cap) grid = cap;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (K == 16) mlp_head_kernel<16><<<grid, 256, 0, s>>>(p);
+  else if (K == 32) mlp_head_kernel<32><<<grid, 256, 0, s>>>(p);
+  else mlp_head_kernel<64><<<grid, 256, 0, s>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, int N, int K, void* stream) {
+  const int total = N * K;
+  grad_fixup_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(dw, db, a, c, N, K);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                  float eps, float weight_decay, int step, float grad_scale, int adamw, void* stream) {
+  AdamParams a{p, g, m, v, n, lr, beta1, beta2, eps, weight_decay,
+               1.f - powf(beta1, float(step)), 1.f - powf(beta2, float(step)), grad_scale, adamw};
+  int grid = int((n + 255) / 256);
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  adam_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float dampening,
+                 float weight_decay, int nesterov, int first_step, float grad_scale, void* stream) {
+  SgdParams s{p, g, buf, n, lr, momentum, dampening, weight_decay, grad_scale, nesterov, first_step};
+  int grid = int((n + 255) / 256);
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  sgd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// C ABI of librdp_kernels.so: every hand-written sm_100a kernel of raydp_b200.
+//
+// Conventions: all pointers are device pointers unless a comment says "host"; `stream` is a
+// cudaStream_t passed as void*; every function returns 0 on success or a negative code, with a
+// message available from rdp_last_error().  The reference (pang-wu/raydp) ships no native code
+// at all, so each group cites the *implicit library op* of the reference's training loop that
+// the kernel replaces.
+#pragma once
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+// ---- common --------------------------------------------------------------------------------
+const char* rdp_last_error(void);
+int rdp_cuda_init(int device);   // cudaSetDevice + capability check; returns the SM count
+int rdp_num_sms(void);
+
+// ---- K6: tcgen05/TMEM GEMMs (cuBLAS behind nn.Linear; reference torch/estimator.py:276-286) --
+// C[M,N] = A[M,K] . B[N,K]^T, bf16 operands, fp32 accumulate.  Epilogue: +bias[N], ReLU,
+// ReLU-mask by aux[M,N] (aux > 0), bf16 or fp32 store, per-column statistics into stats[2,N]
+// (mode 1: sum(v), sum(v^2); mode 2: sum(v), sum(v*aux)); stats must be zeroed by the caller.
+int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int out_f32,
+                int M, int N, int K, const float* bias, int relu, const void* aux, int ld_aux,
+                int aux_relu_mask, int stats_mode, float* stats, void* stream);
+// out[Mw,Nw] (fp32, += with atomics; zero it first) = sum_r g[r,:Mw]^T x[r,:Nw].
+int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
+                   int Mw, int Nw, void* stream);
+
+// ---- K7: BatchNorm1d folded into the neighbouring GEMMs (cuDNN/ATen batch_norm) -------------
+int rdp_bn_fold(const float* stats, float count, const float* gamma, const float* beta,
+                float* running_mean, float* running_var, float momentum, float eps, int use_running,
+                float* a, float* c, float* mean, float* rstd, const float* w, const float* b, int N, int K,
+                void* w_folded, int ldw, void* w_folded_t, int ldwt, float* b_folded, void* stream);
+int rdp_cast_weight(const float* w, int N, int K, void* out, int ldo, void* out_t, int ldt, void* stream);
+int rdp_bn_relu_bwd(const void* dy, const void* z, void* dpre, int B, int N, int ld, const float* stats2,
+                    const float* mean, const float* rstd, const float* a, float* dgamma, float* dbeta,
+                    float* dbias, int has_bn, void* stream);
+int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, int N, int K, void* stream);
+
+// ---- K8: last Linear + loss + dloss + metric sums (ATen losses, torchmetrics, loss.item()) --
+// loss_kind: 0 MSE, 1 SmoothL1(beta=1), 2 BCEWithLogits.  accum[8] += {loss, |err|, err^2, n,
+// correct, 0, 0, 0}.  grad_scale = 1/B trains; 0 evaluates (no backward outputs written).
+int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const float* c, const float* w,
+                 const float* bias, const float* target, int loss_kind, float grad_scale, float* pred,
+                 float* accum, void* dy, float* stats2, float* dw, float* db, void* stream);
+
+// ---- fused optimizers over a flat fp32 parameter buffer (torch.optim.Adam / SGD) ------------
+int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                  float eps, float weight_decay, int step, float grad_scale, int adamw, void* stream);
+int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float dampening,
+                 float weight_decay, int nesterov, int first_step, float grad_scale, void* stream);
+
+// ---- K5: ingestion (pandas/numpy `to_torch` on the CPU; reference torch/estimator.py:227-232)
+// cols / dtypes / table_rows / cross_* are HOST arrays (copied into the launch parameters).
+// dtype codes: 0 f32, 1 f64, 2 i32, 3 i64, 4 i16, 5 i8.
+int rdp_ingest_pack(const void* const* cols, const int* dtypes, int n_cols, int64_t rows, int64_t src_offset,
+                    void* out, int ld, int out_f32, const float* shift, const float* scale,
+                    const void* label, int label_dtype, float* label_out, void* stream);
+int rdp_ingest_indices(const void* const* cols, const int* dtypes, int n_cols, int64_t rows, int64_t src_offset,
+                       const int* table_rows, int n_cross, const int* cross_a, const int* cross_b,
+                       const int* cross_rows, int* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif

@@ -1,0 +1,165 @@
+"""Python bindings of the sm_100a kernels (``librdp_kernels.so``, C ABI in ``include/raydp_b200.h``).
+
+Every wrapper takes torch CUDA tensors, passes raw device pointers plus the *current* torch
+stream, and raises with the library's message on failure -- there is no eager/PyTorch
+fallback: on a GPU box a missing or broken extension is an error, not a slow path.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence
+
+import torch
+
+from raydp_b200._native import kernels_lib
+
+_initialised_devices = set()
+
+
+class KernelError(RuntimeError):
+    pass
+
+
+def lib():
+    handle = kernels_lib()
+    dev = torch.cuda.current_device()
+    if dev not in _initialised_devices:
+        rc = handle.rdp_cuda_init(dev)
+        if rc < 0:
+            raise KernelError(handle.rdp_last_error().decode())
+        _initialised_devices.add(dev)
+    return handle
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise KernelError(f"raydp_b200 kernel call failed ({rc}): {kernels_lib().rdp_last_error().decode()}")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def num_sms() -> int:
+    return lib().rdp_num_sms()
+
+
+def _pitch(t: torch.Tensor) -> int:
+    assert t.dim() == 2 and t.stride(1) == 1, "row-major 2-D tensor required"
+    return t.stride(0)
+
+
+def gemm_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *,
+            bias: Optional[torch.Tensor] = None, relu: bool = False, aux: Optional[torch.Tensor] = None,
+            aux_relu_mask: bool = False, stats_mode: int = 0, stats: Optional[torch.Tensor] = None,
+            out_dtype: torch.dtype = torch.bfloat16, n: Optional[int] = None, k: Optional[int] = None) -> torch.Tensor:
+    """``out[M,N] = a[M,K] @ b[N,K].T`` on tcgen05 tensor cores with a fused epilogue."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    M = a.shape[0]
+    K = k if k is not None else a.shape[1]
+    N = n if n is not None else b.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    _check(lib().rdp_gemm_tn(_ptr(a), _pitch(a), _ptr(b), _pitch(b), _ptr(out), _pitch(out),
+                             1 if out.dtype == torch.float32 else 0, M, N, K, _ptr(bias),
+                             1 if relu else 0, _ptr(aux), _pitch(aux) if aux is not None else 0,
+                             1 if aux_relu_mask else 0, stats_mode, _ptr(stats), _stream()))
+    return out
+
+
+def gemm_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, *, mw: Optional[int] = None,
+               nw: Optional[int] = None) -> torch.Tensor:
+    """``out[Mw,Nw] += g[:, :Mw].T @ x[:, :Nw]`` (fp32 accumulate over the batch rows)."""
+    assert g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and out.dtype == torch.float32
+    rows = g.shape[0]
+    Mw = mw if mw is not None else g.shape[1]
+    Nw = nw if nw is not None else x.shape[1]
+    _check(lib().rdp_gemm_wgrad(_ptr(g), _pitch(g), _ptr(x), _pitch(x), _ptr(out), _pitch(out),
+                                rows, Mw, Nw, _stream()))
+    return out
+
+
+def bn_fold(stats, count, gamma, beta, running_mean, running_var, momentum, eps, use_running,
+            a, c, mean, rstd, w, b, w_folded, w_folded_t, b_folded) -> None:
+    N, K = w.shape
+    _check(lib().rdp_bn_fold(_ptr(stats), float(count), _ptr(gamma), _ptr(beta), _ptr(running_mean),
+                             _ptr(running_var), float(momentum), float(eps), 1 if use_running else 0,
+                             _ptr(a), _ptr(c), _ptr(mean), _ptr(rstd), _ptr(w), _ptr(b), N, K,
+                             _ptr(w_folded), _pitch(w_folded), _ptr(w_folded_t),
+                             _pitch(w_folded_t) if w_folded_t is not None else 0, _ptr(b_folded), _stream()))
+
+
+def cast_weight(w: torch.Tensor, out: torch.Tensor, out_t: Optional[torch.Tensor] = None) -> None:
+    N, K = w.shape
+    _check(lib().rdp_cast_weight(_ptr(w), N, K, _ptr(out), _pitch(out), _ptr(out_t),
+                                 _pitch(out_t) if out_t is not None else 0, _stream()))
+
+
+def bn_relu_bwd(dy, z, dpre, stats2, mean, rstd, a, dgamma, dbeta, dbias, has_bn: bool = True) -> None:
+    B, N = dy.shape
+    _check(lib().rdp_bn_relu_bwd(_ptr(dy), _ptr(z), _ptr(dpre), B, N, _pitch(dy), _ptr(stats2), _ptr(mean),
+                                 _ptr(rstd), _ptr(a), _ptr(dgamma), _ptr(dbeta), _ptr(dbias),
+                                 1 if has_bn else 0, _stream()))
+
+
+def grad_fixup(dw, db, a, c) -> None:
+    N, K = dw.shape
+    _check(lib().rdp_grad_fixup(_ptr(dw), _ptr(db), _ptr(a), _ptr(c), N, K, _stream()))
+
+
+LOSS_KINDS = {"mse": 0, "smooth_l1": 1, "bce_logits": 2}
+
+
+def mlp_head(z, a, c, w, bias, target, loss_kind: int, grad_scale: float, pred, accum, dy, stats2, dw, db) -> None:
+    B, K = z.shape
+    _check(lib().rdp_mlp_head(_ptr(z), B, K, _pitch(z), _ptr(a), _ptr(c), _ptr(w), _ptr(bias), _ptr(target),
+                              loss_kind, float(grad_scale), _ptr(pred), _ptr(accum), _ptr(dy), _ptr(stats2),
+                              _ptr(dw), _ptr(db), _stream()))
+
+
+def adam_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, adamw=False) -> None:
+    _check(lib().rdp_adam_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), lr, beta1, beta2, eps,
+                               weight_decay, step, grad_scale, 1 if adamw else 0, _stream()))
+
+
+def sgd_step(p, g, buf, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
+             first_step=False, grad_scale=1.0) -> None:
+    _check(lib().rdp_sgd_step(_ptr(p), _ptr(g), _ptr(buf), p.numel(), lr, momentum, dampening, weight_decay,
+                              1 if nesterov else 0, 1 if first_step else 0, grad_scale, _stream()))
+
+
+_DTYPE_CODE = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.int16: 4,
+               torch.int8: 5, torch.uint8: 5, torch.bool: 5}
+
+
+def dtype_code(dtype) -> int:
+    return _DTYPE_CODE[dtype]
+
+
+def ingest_pack(col_ptrs: Sequence[int], dtype_codes: Sequence[int], rows: int, src_offset: int,
+                out: torch.Tensor, shift=None, scale=None, label_ptr: int = 0, label_code: int = 0,
+                label_out: Optional[torch.Tensor] = None) -> None:
+    n = len(col_ptrs)
+    ptrs = (ctypes.c_void_p * max(1, n))(*col_ptrs)
+    codes = (ctypes.c_int * max(1, n))(*dtype_codes)
+    _check(lib().rdp_ingest_pack(ptrs, codes, n, rows, src_offset, _ptr(out), _pitch(out),
+                                 1 if out.dtype == torch.float32 else 0, _ptr(shift), _ptr(scale),
+                                 ctypes.c_void_p(label_ptr) if label_ptr else None, label_code,
+                                 _ptr(label_out), _stream()))
+
+
+def ingest_indices(col_ptrs, dtype_codes, rows, src_offset, table_rows, out: torch.Tensor,
+                   crosses: Sequence = ()) -> None:
+    n = len(col_ptrs)
+    ptrs = (ctypes.c_void_p * n)(*col_ptrs)
+    codes = (ctypes.c_int * n)(*dtype_codes)
+    trows = (ctypes.c_int * n)(*[int(t) for t in table_rows])
+    nc = len(crosses)
+    ca = (ctypes.c_int * max(1, nc))(*[c[0] for c in crosses])
+    cb = (ctypes.c_int * max(1, nc))(*[c[1] for c in crosses])
+    cr = (ctypes.c_int * max(1, nc))(*[c[2] for c in crosses])
+    _check(lib().rdp_ingest_indices(ptrs, codes, n, rows, src_offset, trows, nc, ca, cb, cr, _ptr(out), _stream()))

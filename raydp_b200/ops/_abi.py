@@ -1,0 +1,37 @@
+"""ctypes signatures of ``include/raydp_b200.h`` (kept in one place, checked at load time)."""
+import ctypes as C
+
+VP, I, I64, F = C.c_void_p, C.c_int, C.c_int64, C.c_float
+
+SIGNATURES = {
+    "rdp_last_error": (C.c_char_p, []),
+    "rdp_cuda_init": (I, [I]),
+    "rdp_num_sms": (I, []),
+    "rdp_gemm_tn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP, I, VP, I, I, I, VP, VP]),
+    "rdp_gemm_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, VP]),
+    "rdp_bn_fold": (I, [VP, F, VP, VP, VP, VP, F, F, I, VP, VP, VP, VP, VP, VP, I, I, VP, I, VP, I, VP, VP]),
+    "rdp_cast_weight": (I, [VP, I, I, VP, I, VP, I, VP]),
+    "rdp_bn_relu_bwd": (I, [VP, VP, VP, I, I, I, VP, VP, VP, VP, VP, VP, VP, I, VP]),
+    "rdp_grad_fixup": (I, [VP, VP, VP, VP, I, I, VP]),
+    "rdp_mlp_head": (I, [VP, I, I, I, VP, VP, VP, VP, VP, I, F, VP, VP, VP, VP, VP, VP, VP]),
+    "rdp_adam_step": (I, [VP, VP, VP, VP, I64, F, F, F, F, F, I, F, I, VP]),
+    "rdp_sgd_step": (I, [VP, VP, VP, I64, F, F, F, F, I, I, F, VP]),
+    "rdp_ingest_pack": (I, [VP, VP, I, I64, I64, VP, I, I, VP, VP, VP, I, VP, VP]),
+    "rdp_ingest_indices": (I, [VP, VP, I, I64, I64, VP, I, VP, VP, VP, VP, VP]),
+}
+
+OPTIONAL = {}
+
+
+def declare(lib) -> None:
+    missing = []
+    for name, (res, args) in {**SIGNATURES, **OPTIONAL}.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            if name in SIGNATURES:
+                missing.append(name)
+            continue
+        fn.restype = res
+        fn.argtypes = args
+    if missing:
+        raise RuntimeError(f"librdp_kernels.so is stale, missing symbols: {missing}; rebuild it")
