@@ -35,7 +35,7 @@ struct BnFoldParams {
   int N, K;
   __nv_bfloat16* w_folded;    // [N, ldw]   W * diag(a)
   int ldw;
-  __nv_bfloat16* w_folded_t;  // [K, ldwt]  transposed copy for dgrad (may be null)
+  __nv_bfloat16* w_folded_t;  // [K, ldwt]  transposed UNFOLDED weight for dgrad (may be null)
   int ldwt;
   float* b_folded;            // [N]
 };
@@ -76,7 +76,8 @@ __global__ void bn_fold_kernel(const BnFoldParams p) {
     const float w = p.w[size_t(n) * p.K + k];
     const __nv_bfloat16 wf = __float2bfloat16_rn(w * s_a[k]);
     p.w_folded[size_t(n) * p.ldw + k] = wf;
-    if (p.w_folded_t != nullptr) p.w_folded_t[size_t(k) * p.ldwt + n] = wf;
+    // dgrad needs dL/dy (y = BN output), i.e. the *unfolded* weight, transposed to K-major
+    if (p.w_folded_t != nullptr) p.w_folded_t[size_t(k) * p.ldwt + n] = __float2bfloat16_rn(w);
     dot += w * s_c[k];
   }
   __shared__ float red[32];

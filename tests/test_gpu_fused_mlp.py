@@ -1,0 +1,154 @@
+"""Fused MLP step vs the same model in plain PyTorch fp32 (autograd, BatchNorm1d, SmoothL1)."""
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(B=4096, cols=20, loss="smooth_l1", seed=0):
+    from raydp_b200.models import NYCTaxiMLP
+    from raydp_b200.ops.fused_mlp import FusedMLP
+    torch.manual_seed(seed)
+    model = NYCTaxiMLP(cols).cuda()
+    fused = FusedMLP(model.fused_spec(), B, torch.device("cuda"), loss=loss)
+    fused.load_state_dict(model.state_dict())
+    x = torch.randn(B, cols, device="cuda")
+    y = (x[:, :3].sum(1) * 2 + 1 + 0.1 * torch.randn(B, device="cuda"))
+    return model, fused, x, y
+
+
+def _rel(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+@pytest.mark.parametrize("loss_name,crit", [("smooth_l1", nn.SmoothL1Loss()), ("mse", nn.MSELoss())])
+def test_forward_backward_matches_autograd(loss_name, crit):
+    model, fused, x, y = _setup(loss=loss_name)
+    xb = fused.pack_input(x)
+    fused.train_step(xb, y)
+    # the reference sees the same bf16-rounded inputs
+    out = model(xb[:, :20].float())
+    loss = crit(out[:, 0], y)
+    loss.backward()
+    torch.cuda.synchronize()
+    acc = fused.accum.cpu()
+    assert acc[3].item() == x.shape[0]
+    assert abs(acc[0].item() / acc[3].item() - loss.item()) < 2e-2 * max(1.0, abs(loss.item()))
+    assert _rel(fused.pred[:x.shape[0]], out[:, 0].detach()) < 2e-2
+    sd = dict(model.named_parameters())
+    worst = {}
+    for l in range(4):
+        worst[f"W{l}"] = _rel(fused.view(f"W{l}", True), sd[f"fc{l + 1}.weight"].grad)
+        worst[f"b{l}"] = _rel(fused.view(f"b{l}", True), sd[f"fc{l + 1}.bias"].grad)
+        worst[f"g{l}"] = _rel(fused.view(f"g{l}", True), sd[f"bn{l + 1}.weight"].grad)
+        worst[f"be{l}"] = _rel(fused.view(f"be{l}", True), sd[f"bn{l + 1}.bias"].grad)
+    worst["Wh"] = _rel(fused.view("Wh", True).reshape(-1), sd["fc5.weight"].grad.reshape(-1))
+    worst["bh"] = _rel(fused.view("bh", True), sd["fc5.bias"].grad)
+    # bias / beta gradients in front of a BatchNorm are near-cancelling sums: looser bound
+    bad = {k: v for k, v in worst.items() if not v < (6e-2 if k.startswith(("W", "g")) else 0.15)}
+    assert not bad, worst
+    for l in range(4):
+        bn = getattr(model, f"bn{l + 1}")
+        assert _rel(fused.running_mean[l], bn.running_mean) < 2e-2
+        assert _rel(fused.running_var[l], bn.running_var) < 2e-2
+
+
+def test_training_converges_like_torch_adam():
+    from raydp_b200 import ops
+    model, fused, x, y = _setup(B=8192, seed=1)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    crit = nn.SmoothL1Loss()
+    m = torch.zeros_like(fused.params)
+    v = torch.zeros_like(fused.params)
+    xb = fused.pack_input(x)
+    ref_losses, fused_losses = [], []
+    for step in range(1, 41):
+        opt.zero_grad()
+        loss = crit(model(xb[:, :20].float())[:, 0], y)
+        loss.backward()
+        opt.step()
+        ref_losses.append(loss.item())
+        fused.accum.zero_()
+        fused.train_step(xb, y)
+        ops.adam_step(fused.params, fused.grads, m, v, 1e-3, 0.9, 0.999, 1e-8, 0.0, step)
+        fused_losses.append((fused.accum[0] / fused.accum[3]).item())
+    assert fused_losses[-1] < fused_losses[0] * 0.9
+    assert abs(fused_losses[-1] - ref_losses[-1]) < 0.05 * ref_losses[0]
+    # parameters stay close to the fp32 reference trajectory
+    assert _rel(fused.view("W1"), model.fc2.weight.detach()) < 5e-2
+    # checkpoint layout is loadable by the plain module
+    from raydp_b200.models import NYCTaxiMLP
+    fresh = NYCTaxiMLP(20)
+    fresh.load_state_dict(fused.state_dict())
+    fresh = fresh.cuda().eval()
+    pred_ref = fresh(xb[:, :20].float())[:, 0]
+    pred_fused = fused.predict(xb)
+    assert _rel(pred_fused, pred_ref.detach()) < 3e-2
+
+
+def test_bce_head_and_eval_mode():
+    model, fused, x, y = _setup(loss="bce_logits", seed=2)
+    t = (y > y.median()).float()
+    xb = fused.pack_input(x)
+    fused.train_step(xb, t)
+    out = model(xb[:, :20].float())[:, 0]
+    loss = nn.BCEWithLogitsLoss()(out, t)
+    torch.cuda.synchronize()
+    assert abs((fused.accum[0] / fused.accum[3]).item() - loss.item()) < 2e-2
+    model.eval()
+    fused.load_state_dict(model.state_dict())
+    fused.accum.zero_()
+    pred = fused.eval_step(xb, t)
+    assert _rel(pred, model(xb[:, :20].float())[:, 0].detach()) < 3e-2
+
+
+def test_optimizer_kernels_match_torch():
+    from raydp_b200 import ops
+    torch.manual_seed(0)
+    n = 100003
+    p0 = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda")
+    for wd, adamw in ((0.0, False), (0.01, False), (0.01, True)):
+        p_ref = p0.clone().requires_grad_(True)
+        opt = (torch.optim.AdamW if adamw else torch.optim.Adam)([p_ref], lr=1e-2, weight_decay=wd)
+        p, m, v = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+        for step in range(1, 4):
+            p_ref.grad = g.clone()
+            opt.step()
+            ops.adam_step(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, wd, step, 1.0, adamw)
+        assert torch.allclose(p, p_ref.detach(), rtol=1e-5, atol=1e-6)
+    p_ref = p0.clone().requires_grad_(True)
+    opt = torch.optim.SGD([p_ref], lr=0.1, momentum=0.9, nesterov=True, weight_decay=1e-3)
+    p, buf = p0.clone(), torch.zeros(n, device="cuda")
+    for step in range(3):
+        p_ref.grad = g.clone()
+        opt.step()
+        ops.sgd_step(p, g, buf, 0.1, 0.9, 0.0, 1e-3, True, step == 0)
+    assert torch.allclose(p, p_ref.detach(), rtol=1e-5, atol=1e-6)
+
+
+def test_ingest_pack_matches_torch():
+    from raydp_b200 import ops
+    rows = 10007
+    cols = [torch.randn(rows + 5, device="cuda", dtype=torch.float64),
+            torch.randn(rows + 5, device="cuda", dtype=torch.float32),
+            torch.randint(-50, 50, (rows + 5,), device="cuda", dtype=torch.int32),
+            torch.randint(-50, 50, (rows + 5,), device="cuda", dtype=torch.int64)]
+    label = torch.randn(rows + 5, device="cuda", dtype=torch.float64)
+    shift = torch.tensor([0.5, 0.0, 1.0, -2.0], device="cuda")
+    scale = torch.tensor([2.0, 1.0, 0.1, 0.5], device="cuda")
+    out = torch.full((rows, 8), 7.0, device="cuda", dtype=torch.bfloat16)
+    lab = torch.empty(rows, device="cuda")
+    ops.ingest_pack([c.data_ptr() for c in cols], [ops.dtype_code(c.dtype) for c in cols], rows, 5, out,
+                    shift, scale, label.data_ptr(), ops.dtype_code(label.dtype), lab)
+    ref = torch.stack([(c[5:].float() - shift[i]) * scale[i] for i, c in enumerate(cols)], 1)
+    assert torch.allclose(out[:, :4].float(), ref.to(torch.bfloat16).float())
+    assert (out[:, 4:] == 0).all()
+    assert torch.allclose(lab, label[5:].float())
+    idx_out = torch.empty(rows, 3, device="cuda", dtype=torch.int32)
+    ops.ingest_indices([cols[2].data_ptr(), cols[3].data_ptr()], [2, 3], rows, 5, [7, 0], idx_out,
+                       crosses=[(0, 1, 1000)])
+    assert torch.equal(idx_out[:, 0].long(), cols[2][5:].long() % 7)
+    assert torch.equal(idx_out[:, 1].long(), cols[3][5:])
+    assert int(idx_out[:, 2].min()) >= 0 and int(idx_out[:, 2].max()) < 1000
