@@ -90,4 +90,14 @@ int rdp_cuda_init(int device) {
 
 int rdp_num_sms() { return rdp::num_sms(); }
 
+int rdp_memcpy_h2d_async(void* dst, const void* src_host, uint64_t bytes, void* stream) {
+  RDP_CHECK_CUDA(cudaMemcpyAsync(dst, src_host, bytes, cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
+int rdp_memcpy_d2h_async(void* dst_host, const void* src, uint64_t bytes, void* stream) {
+  RDP_CHECK_CUDA(cudaMemcpyAsync(dst_host, src, bytes, cudaMemcpyDeviceToHost, static_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
 }  // extern "C"

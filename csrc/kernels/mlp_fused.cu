@@ -287,8 +287,12 @@ mlp_head_kernel(const HeadParams p) {
     float v = 0.f;
     for (int w8 = 0; w8 < 8; ++w8) v += red[w8][threadIdx.x];
     const int i = threadIdx.x;
-    if (i < 5) atomicAdd(&p.accum[i], v);
-    else if (train) {
+    if (i < 5) {
+      atomicAdd(&p.accum[i], v);
+      // accum[5] collects the batch-mean loss, so an epoch's "mean of per-batch means"
+      // (reference torch/estimator.py:290) needs no per-step host read
+      if (i == 0) atomicAdd(&p.accum[5], v / float(p.B));
+    } else if (train) {
       if (i == 5) {
         atomicAdd(p.db, v);
         // sum over batch of dy[:, k] = w[k] * sum(dp); and dw picks up the c term
@@ -323,6 +327,8 @@ struct AdamParams {
   float bc1, bc2;        // 1 - beta1^t, 1 - beta2^t
   float grad_scale;      // e.g. 1/world_size
   int adamw;
+  const float* lr_ptr;   // optional device scalars (CUDA-graph friendly): lr, step count
+  const float* step_ptr;
 };
 
 __device__ __forceinline__ float adam_update(float p, float g, float& m, float& v, const AdamParams& a) {
@@ -334,7 +340,13 @@ __device__ __forceinline__ float adam_update(float p, float g, float& m, float& 
   return p - (a.lr / a.bc1) * (m / denom);
 }
 
-__global__ void adam_kernel(const AdamParams a) {
+__global__ void adam_kernel(AdamParams a) {
+  if (a.lr_ptr != nullptr) a.lr = *a.lr_ptr;
+  if (a.step_ptr != nullptr) {
+    const float t = *a.step_ptr;
+    a.bc1 = 1.f - powf(a.beta1, t);
+    a.bc2 = 1.f - powf(a.beta2, t);
+  }
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < a.n; i += int64_t(gridDim.x) * blockDim.x) {
     float m = a.m[i], v = a.v[i];
     a.p[i] = adam_update(a.p[i], a.g[i], m, v, a);
@@ -347,9 +359,15 @@ struct SgdParams {
   int64_t n;
   float lr, momentum, dampening, weight_decay, grad_scale;
   int nesterov, first_step;
+  const float* lr_ptr;
+  const float* step_ptr;   // first_step = (*step_ptr <= 1)
 };
 
-__global__ void sgd_kernel(const SgdParams s) {
+__global__ void add_scalar_kernel(float* x, float v) { *x += v; }
+
+__global__ void sgd_kernel(SgdParams s) {
+  if (s.lr_ptr != nullptr) s.lr = *s.lr_ptr;
+  if (s.step_ptr != nullptr) s.first_step = (*s.step_ptr <= 1.f) ? 1 : 0;
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < s.n; i += int64_t(gridDim.x) * blockDim.x) {
     float p = s.p[i];
     float g = s.g[i] * s.grad_scale;
@@ -431,10 +449,18 @@ int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, i
   return 0;
 }
 
+int rdp_add_scalar(float* x, float v, void* stream) {
+  add_scalar_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(x, v);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
-                  float eps, float weight_decay, int step, float grad_scale, int adamw, void* stream) {
+                  float eps, float weight_decay, int step, float grad_scale, int adamw,
+                  const float* lr_ptr, const float* step_ptr, void* stream) {
   AdamParams a{p, g, m, v, n, lr, beta1, beta2, eps, weight_decay,
-               1.f - powf(beta1, float(step)), 1.f - powf(beta2, float(step)), grad_scale, adamw};
+               1.f - powf(beta1, float(step)), 1.f - powf(beta2, float(step)), grad_scale, adamw,
+               lr_ptr, step_ptr};
   int grid = int((n + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   adam_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
@@ -443,8 +469,10 @@ int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float
 }
 
 int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float dampening,
-                 float weight_decay, int nesterov, int first_step, float grad_scale, void* stream) {
-  SgdParams s{p, g, buf, n, lr, momentum, dampening, weight_decay, grad_scale, nesterov, first_step};
+                 float weight_decay, int nesterov, int first_step, float grad_scale,
+                 const float* lr_ptr, const float* step_ptr, void* stream) {
+  SgdParams s{p, g, buf, n, lr, momentum, dampening, weight_decay, grad_scale, nesterov, first_step,
+              lr_ptr, step_ptr};
   int grid = int((n + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   sgd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);

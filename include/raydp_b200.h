@@ -47,10 +47,18 @@ int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const floa
                  float* accum, void* dy, float* stats2, float* dw, float* db, void* stream);
 
 // ---- fused optimizers over a flat fp32 parameter buffer (torch.optim.Adam / SGD) ------------
+// lr_ptr / step_ptr: optional device scalars read by the kernel instead of the by-value lr / step
+// (lets a captured CUDA graph follow lr schedules and the Adam bias correction).
 int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
-                  float eps, float weight_decay, int step, float grad_scale, int adamw, void* stream);
+                  float eps, float weight_decay, int step, float grad_scale, int adamw,
+                  const float* lr_ptr, const float* step_ptr, void* stream);
 int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float dampening,
-                 float weight_decay, int nesterov, int first_step, float grad_scale, void* stream);
+                 float weight_decay, int nesterov, int first_step, float grad_scale,
+                 const float* lr_ptr, const float* step_ptr, void* stream);
+int rdp_add_scalar(float* x, float v, void* stream);
+// host (pinned or pageable) -> device async copy on `stream`
+int rdp_memcpy_h2d_async(void* dst, const void* src_host, uint64_t bytes, void* stream);
+int rdp_memcpy_d2h_async(void* dst_host, const void* src, uint64_t bytes, void* stream);
 
 // ---- K5: ingestion (pandas/numpy `to_torch` on the CPU; reference torch/estimator.py:227-232)
 // cols / dtypes / table_rows / cross_* are HOST arrays (copied into the launch parameters).

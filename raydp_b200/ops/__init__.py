@@ -11,9 +11,20 @@ from typing import Optional, Sequence
 
 import torch
 
-from raydp_b200._native import kernels_lib
+from raydp_b200._native import kernels_available, kernels_lib  # noqa: F401
 
 _initialised_devices = set()
+_launches = 0
+
+
+def launch_count() -> int:
+    """Kernels launched through this module so far (graph replays are added by their owner)."""
+    return _launches
+
+
+def add_launches(n: int) -> None:
+    global _launches
+    _launches += int(n)
 
 
 class KernelError(RuntimeError):
@@ -32,6 +43,8 @@ def lib():
 
 
 def _check(rc: int) -> None:
+    global _launches
+    _launches += 1
     if rc != 0:
         raise KernelError(f"raydp_b200 kernel call failed ({rc}): {kernels_lib().rdp_last_error().decode()}")
 
@@ -121,15 +134,27 @@ def mlp_head(z, a, c, w, bias, target, loss_kind: int, grad_scale: float, pred, 
                               _ptr(dw), _ptr(db), _stream()))
 
 
-def adam_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, adamw=False) -> None:
+def adam_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, adamw=False,
+              lr_dev=None, step_dev=None) -> None:
     _check(lib().rdp_adam_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), lr, beta1, beta2, eps,
-                               weight_decay, step, grad_scale, 1 if adamw else 0, _stream()))
+                               weight_decay, step, grad_scale, 1 if adamw else 0, _ptr(lr_dev),
+                               _ptr(step_dev), _stream()))
 
 
 def sgd_step(p, g, buf, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
-             first_step=False, grad_scale=1.0) -> None:
+             first_step=False, grad_scale=1.0, lr_dev=None, step_dev=None) -> None:
     _check(lib().rdp_sgd_step(_ptr(p), _ptr(g), _ptr(buf), p.numel(), lr, momentum, dampening, weight_decay,
-                              1 if nesterov else 0, 1 if first_step else 0, grad_scale, _stream()))
+                              1 if nesterov else 0, 1 if first_step else 0, grad_scale, _ptr(lr_dev),
+                              _ptr(step_dev), _stream()))
+
+
+def add_scalar(x: torch.Tensor, v: float) -> None:
+    _check(lib().rdp_add_scalar(_ptr(x), float(v), _stream()))
+
+
+def memcpy_h2d_async(dst_ptr: int, src_host_ptr: int, nbytes: int, stream: Optional[torch.cuda.Stream] = None) -> None:
+    s = ctypes.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
+    _check(lib().rdp_memcpy_h2d_async(ctypes.c_void_p(dst_ptr), ctypes.c_void_p(src_host_ptr), nbytes, s))
 
 
 _DTYPE_CODE = {torch.float32: 0, torch.float64: 1, torch.int32: 2, torch.int64: 3, torch.int16: 4,

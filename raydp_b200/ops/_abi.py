@@ -14,8 +14,11 @@ SIGNATURES = {
     "rdp_bn_relu_bwd": (I, [VP, VP, VP, I, I, I, VP, VP, VP, VP, VP, VP, VP, I, VP]),
     "rdp_grad_fixup": (I, [VP, VP, VP, VP, I, I, VP]),
     "rdp_mlp_head": (I, [VP, I, I, I, VP, VP, VP, VP, VP, I, F, VP, VP, VP, VP, VP, VP, VP]),
-    "rdp_adam_step": (I, [VP, VP, VP, VP, I64, F, F, F, F, F, I, F, I, VP]),
-    "rdp_sgd_step": (I, [VP, VP, VP, I64, F, F, F, F, I, I, F, VP]),
+    "rdp_adam_step": (I, [VP, VP, VP, VP, I64, F, F, F, F, F, I, F, I, VP, VP, VP]),
+    "rdp_sgd_step": (I, [VP, VP, VP, I64, F, F, F, F, I, I, F, VP, VP, VP]),
+    "rdp_add_scalar": (I, [VP, F, VP]),
+    "rdp_memcpy_h2d_async": (I, [VP, VP, C.c_uint64, VP]),
+    "rdp_memcpy_d2h_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_ingest_pack": (I, [VP, VP, I, I64, I64, VP, I, I, VP, VP, VP, I, VP, VP]),
     "rdp_ingest_indices": (I, [VP, VP, I, I64, I64, VP, I, VP, VP, VP, VP, VP]),
 }
