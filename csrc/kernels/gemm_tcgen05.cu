@@ -19,6 +19,8 @@
 #include "common.cuh"
 #include "raydp_b200.h"
 
+#include <mutex>
+
 namespace rdp {
 
 constexpr int kBlockM = 128;
@@ -483,3 +485,101 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// Allocation-free entry point
+// ================================================================================================
+// rdp_gemm_tn needs a caller-provided [2, N] fp32 scratch for its per-column batch statistics, and
+// the caller has to allocate and zero it.  Some callers cannot allocate device memory at all: a
+// plugin living inside a host application whose device memory is owned end-to-end by that
+// application's own pool (a stray cudaMalloc there can fail, fragment the pool or break its
+// accounting), and a latency-critical loop that must never hit cudaMalloc's implicit device-wide
+// synchronisation.  For them the scratch lives in the library image itself: a file-scope
+// __device__ array that every GPU loading this library carries until the process exits
+// (kNoAllocMaxN columns -> 8 KB per GPU).
+//
+// rdp_gemm_tn_bnstats_noalloc computes  out = relu?(a . b^T + bias)  exactly like rdp_gemm_tn and
+// returns the per-column batch mean and biased variance of `out` in caller-provided outputs.
+// It calls no cudaMalloc / cudaFree and no allocating library routine.
+//
+//  * Limit: N <= kNoAllocMaxN (1024); larger N is rejected with an error, never truncated.
+//  * Set-up: the first call on each device resolves the device address of the scratch array with
+//    cudaGetSymbolAddress (the array's name in host code is only a host-side stand-in, not an
+//    address a kernel may use).  Make that first call per device outside any stream capture.
+//  * Every call shares the one array.  It is cleared at the start of each call, on the caller's
+//    stream, so back-to-back calls on one stream are safe; two calls that overlap on the GPU
+//    (different streams, or different host threads on different streams) race on it.
+namespace rdp {
+
+constexpr int kNoAllocMaxN = 1024;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_noalloc_stats[2 * kNoAllocMaxN];
+
+static float* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+static std::mutex g_noalloc_mutex;
+
+// mean[j] = sum / rows ; var[j] = max(sumsq / rows - mean^2, 0)   (device code may name the array)
+__global__ void noalloc_finalize_kernel(const float* __restrict__ stats, int n, float rows,
+                                        float* __restrict__ mean, float* __restrict__ var) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const float m = stats[j] / rows;
+  mean[j] = m;
+  var[j] = fmaxf(stats[n + j] / rows - m * m, 0.f);
+}
+
+}  // namespace rdp
+
+extern "C" int rdp_gemm_tn_bnstats_noalloc(const void* a, int lda, const void* b, int ldb, void* out, int ldc,
+                                           int out_f32, int M, int N, int K, const float* bias, int relu,
+                                           float* mean_out, float* var_out, void* stream) {
+  RDP_REQUIRE(M > 0 && N > 0 && K > 0, "rdp_gemm_tn_bnstats_noalloc: empty problem %dx%dx%d", M, N, K);
+  RDP_REQUIRE(N <= kNoAllocMaxN,
+              "rdp_gemm_tn_bnstats_noalloc: N=%d exceeds the built-in scratch (max %d columns); use "
+              "rdp_gemm_tn with your own [2, N] statistics buffer", N, kNoAllocMaxN);
+  RDP_REQUIRE(N % 16 == 0, "rdp_gemm_tn_bnstats_noalloc: N=%d must be a multiple of 16", N);
+  RDP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0,
+              "rdp_gemm_tn_bnstats_noalloc: pitches must be multiples of 8");
+  RDP_REQUIRE(mean_out != nullptr && var_out != nullptr, "rdp_gemm_tn_bnstats_noalloc: outputs missing");
+  int dev = 0;
+  RDP_CHECK_CUDA(cudaGetDevice(&dev));
+  RDP_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "rdp_gemm_tn_bnstats_noalloc: device %d out of range", dev);
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+      // once per device, with that device current: host code must not pass the symbol itself
+      float* ptr = nullptr;
+      RDP_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_noalloc_stats));
+      RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+      g_noalloc_ptr[dev] = ptr;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // the array keeps the previous call's sums: clear the part this call accumulates into
+  RDP_CHECK_CUDA(cudaMemsetAsync(scratch, 0, size_t(2) * N * sizeof(float), s));
+  GemmTnParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.n_tile = N >= kMaxNTile ? kMaxNTile : N;
+  if (N > kMaxNTile && N % kMaxNTile != 0) p.n_tile = (N % 128 == 0) ? 128 : ((N % 64 == 0) ? 64 : 16);
+  p.num_m_tiles = (M + kBlockM - 1) / kBlockM;
+  p.num_n_tiles = (N + p.n_tile - 1) / p.n_tile;
+  p.num_k_blocks = (K + kBlockK - 1) / kBlockK;
+  p.bias = bias; p.relu = relu; p.out = out; p.out_f32 = out_f32; p.ldc = ldc;
+  p.aux = nullptr; p.ld_aux = 0; p.aux_relu_mask = 0;
+  p.stats_mode = 1; p.stats = scratch;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d_bf16(&ta, a, M, K, lda, kBlockM, kBlockK);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tb, b, N, K, ldb, p.n_tile, kBlockK);
+  if (rc) return rc;
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_tn_kernel<<<grid, kGemmThreads, gemm_tn_smem_bytes(p.n_tile), s>>>(ta, tb, p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  noalloc_finalize_kernel<<<(N + 255) / 256, 256, 0, s>>>(scratch, N, float(M), mean_out, var_out);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -28,6 +28,19 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
 int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
                    int Mw, int Nw, void* stream);
 
+// Allocation-free variant of rdp_gemm_tn's statistics path.  It has no counterpart in the
+// reference: it exists for callers that must not allocate device memory (a plugin inside a host
+// whose device memory belongs to that host's own pool; a latency-critical loop that cannot take
+// cudaMalloc's implicit synchronisation).  out = relu?(a . b^T + bias) as in rdp_gemm_tn, plus the
+// per-column batch mean and biased variance of `out`.  The [2, N] accumulator is a __device__
+// array inside the library (8 KB per GPU, held until exit), so N <= 1024 or the call is rejected.
+// The first call on a device resolves the array's device address: make it before any stream
+// capture.  All calls share the array (cleared on entry, on `stream`): calls that overlap on the
+// GPU race.  No cudaMalloc / cudaFree / allocating library call is made.
+int rdp_gemm_tn_bnstats_noalloc(const void* a, int lda, const void* b, int ldb, void* out, int ldc,
+                                int out_f32, int M, int N, int K, const float* bias, int relu,
+                                float* mean_out, float* var_out, void* stream);
+
 // ---- K7: BatchNorm1d folded into the neighbouring GEMMs (cuDNN/ATen batch_norm) -------------
 int rdp_bn_fold(const float* stats, float count, const float* gamma, const float* beta,
                 float* running_mean, float* running_var, float momentum, float eps, int use_running,
