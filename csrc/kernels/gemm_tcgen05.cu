@@ -27,7 +27,8 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;          // 64 bf16 = 128 B = one swizzle row
 constexpr int kMaxNTile = 256;
 constexpr int kStages = 4;
-constexpr int kGemmThreads = 192;    // 6 warps
+constexpr int kEpiGroups = 3;        // column groups: 3 x 4 quadrant warps = 12 epilogue warps
+constexpr int kGemmThreads = 64 + kEpiGroups * 128;   // TMA warp + MMA warp + epilogue warps
 constexpr int kStatsCols = 1024;
 
 struct GemmTnParams {
@@ -62,12 +63,17 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
   float* s_stats = reinterpret_cast<float*>(tmem_ptr + 4);        // [2][kStatsCols]
+  float* s_bias = s_stats + 2 * kStatsCols;                       // [kStatsCols]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   if (p.stats_mode) {
     for (int i = threadIdx.x; i < 2 * kStatsCols; i += blockDim.x) s_stats[i] = 0.f;
+  }
+  const bool bias_in_smem = p.bias != nullptr && p.N <= kStatsCols;
+  if (bias_in_smem) {
+    for (int i = threadIdx.x; i < p.N; i += blockDim.x) s_bias[i] = p.bias[i];
   }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -78,7 +84,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);
-      mbar_init(&tmem_empty[a], 128);
+      mbar_init(&tmem_empty[a], kEpiGroups * 128);
     }
     mbar_fence_init();
   }
@@ -140,8 +146,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       }
     }
   } else {
-    // ===================== epilogue warps (2..5) =====================
+    // ===================== epilogue warps (2..13) =====================
+    // 12 warps: the SM's four schedulers each get three epilogue warps, which is what hides the
+    // TMEM-load / shuffle / store latencies (one warp per scheduler was issue-latency bound).
     const int quad = warp & 3;                       // TMEM lane quadrant this warp may read
+    const int group = (warp - 2) >> 2;               // which 32-column chunks this warp owns
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
@@ -152,7 +161,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       tc_fence_after();
       const uint32_t t_row = tmem_base + (uint32_t(quad * 32) << 16) + uint32_t(acc) * kMaxNTile;
       const int n0 = n_blk * p.n_tile;
-      for (int c = 0; c < p.n_tile; c += 32) {
+      for (int c = group * 32; c < p.n_tile; c += kEpiGroups * 32) {
         const int col0 = n0 + c;
         if (col0 >= p.N) break;
         const int ncols = min(32, min(p.n_tile - c, p.N - col0));   // 16 or 32
@@ -162,7 +171,16 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         float v[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(raw[j]);
-        if (p.bias != nullptr) {
+        if (bias_in_smem) {
+          const float4* b4 = reinterpret_cast<const float4*>(s_bias + col0);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            if (q * 4 < ncols) {
+              const float4 bb = b4[q];
+              v[q * 4] += bb.x; v[q * 4 + 1] += bb.y; v[q * 4 + 2] += bb.z; v[q * 4 + 3] += bb.w;
+            }
+          }
+        } else if (p.bias != nullptr) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] += (j < ncols) ? __ldg(p.bias + col0 + j) : 0.f;
         }
@@ -202,6 +220,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           for (int j = 0; j < 32; ++j) v[j] = 0.f;
         }
         // ---- store ----
+        uint32_t packed[16];
+        if (!p.out_f32) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) packed[i] = pack_bf16x2(v[2 * i], v[2 * i + 1]);
+        }
         if (row_ok) {
           if (p.out_f32) {
             float4* op = reinterpret_cast<float4*>(static_cast<float*>(p.out) + size_t(row) * p.ldc + col0);
@@ -213,8 +236,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
             for (int q = 0; q < 4; ++q)
               if (q * 8 < ncols)
-                op[q] = make_uint4(pack_bf16x2(v[q * 8], v[q * 8 + 1]), pack_bf16x2(v[q * 8 + 2], v[q * 8 + 3]),
-                                   pack_bf16x2(v[q * 8 + 4], v[q * 8 + 5]), pack_bf16x2(v[q * 8 + 6], v[q * 8 + 7]));
+                op[q] = make_uint4(packed[q * 4], packed[q * 4 + 1], packed[q * 4 + 2], packed[q * 4 + 3]);
           }
         }
         // ---- per-column batch statistics ----
@@ -222,12 +244,15 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           float w[32];
           if (p.stats_mode == 1) {
             // statistics of what the next layer will read: the bf16-rounded activation
+            if (!p.out_f32) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float r = p.out_f32 ? v[j] : __bfloat162float(__float2bfloat16_rn(v[j]));
-              v[j] = r;
-              w[j] = r * r;
+              for (int i = 0; i < 16; ++i) {      // bf16 -> fp32 is a shift / mask of the packed pair
+                v[2 * i] = __uint_as_float(packed[i] << 16);
+                v[2 * i + 1] = __uint_as_float(packed[i] & 0xffff0000u);
+              }
             }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) w[j] = v[j] * v[j];
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j) w[j] = v[j] * aux[j];
@@ -266,6 +291,335 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Specialised fast path (bf16 output, N % 64 == 0, N <= kStatsCols).
+//
+// The generic kernel's epilogue is row-per-thread: every 16-byte store / aux load of a warp touches
+// 32 different 128-byte lines, and the L1 wavefronts of those accesses -- not DRAM -- bound it
+// (ncu: dram 2 %, long/short scoreboard stalls).  Here every byte moves by TMA:
+//   * the aux tile (BatchNorm input z for the backward statistics / ReLU mask) is loaded by the
+//     producer warp into a swizzled smem tile,
+//   * the epilogue warps write the bf16 output tile into a double-buffered swizzled smem tile and
+//     one thread issues `cp.async.bulk.tensor` stores (fully coalesced, asynchronous),
+//   * 16 epilogue warps (4 per SM scheduler), epilogue compiled per (statistics mode, aux use),
+//   * the per-column batch statistics are computed BY THE TENSOR CORES: the staged bf16 output
+//     tile is exactly an MN-major UMMA operand, so the MMA warp issues two extra accumulating
+//     MMAs per tile, D_s += Ones . C (every row = column sums) and D_g += C^T . C (mode 1) or
+//     C^T . X (mode 2), whose diagonals are sum(v), sum(v^2) / sum(v * aux).  They accumulate in
+//     TMEM across all tiles of the CTA and are read out once at the end, which removes the
+//     shuffle-transpose reduction (2/3 of the epilogue's instructions) altogether.
+// ----------------------------------------------------------------------------------------------
+constexpr int kFastGroups = 4;
+constexpr int kFastThreads = 64 + kFastGroups * 128;
+constexpr int kFastNTile = 128;
+constexpr uint32_t kChunkTileBytes = 128 * 128;      // one [128 rows x 64 cols] bf16 swizzled block
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int32_t c0, int32_t c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kPending) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void epi_barrier() {
+  asm volatile("bar.sync 1, %0;" ::"n"(kFastGroups * 128) : "memory");
+}
+
+template <int kStats, bool kAux>
+__global__ void __launch_bounds__(kFastThreads, 1)
+gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_x,
+                    const GemmTnParams p) {
+  constexpr int kS = kAux ? 2 : 3;                    // operand pipeline depth
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t a_bytes = kBlockM * kBlockK * 2;                      // 16 KB
+  const uint32_t b_bytes = uint32_t(p.n_tile) * kBlockK * 2;           // <= 16 KB
+  const uint32_t stage_bytes = a_bytes + kFastNTile * kBlockK * 2;     // 32 KB
+  const int n_chunks64 = p.n_tile / 64;                                // 1 or 2
+  const uint32_t c_bytes = kChunkTileBytes * 2;                        // one staging buffer (<= 128 cols)
+  uint8_t* tiles = smem;
+  uint8_t* c_stage = tiles + kS * stage_bytes;                         // 2 buffers
+  uint8_t* x_stage = c_stage + 2 * c_bytes;                            // 2 buffers (kAux only)
+  uint8_t* ones = x_stage + (kAux ? 2 * c_bytes : 0);                  // [128 x 128 B] of bf16 1.0 (kStats)
+  uint8_t* tail = ones + (kStats ? kChunkTileBytes : 0);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + kS;
+  uint64_t* tmem_full = empty_bar + kS;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint64_t* x_full = tmem_empty + 2;
+  uint64_t* x_empty = x_full + 2;
+  uint64_t* c_ready = x_empty + 2;       // epilogue -> MMA warp: staged tile complete
+  uint64_t* stats_done = c_ready + 2;    // MMA warp -> epilogue: statistics MMAs have read the tile
+  uint64_t* stats_final = stats_done + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(stats_final + 1);
+  float* s_bias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_ptr + 4) + 15) & ~uintptr_t(15));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  if (kStats) {
+    uint32_t* o32 = reinterpret_cast<uint32_t*>(ones);
+    for (int i = threadIdx.x; i < int(kChunkTileBytes / 4); i += blockDim.x) o32[i] = 0x3F803F80u;
+    fence_async_smem();
+  }
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x) s_bias[i] = p.bias ? p.bias[i] : 0.f;
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    tma_prefetch_desc(&tmap_c);
+    if (kAux) tma_prefetch_desc(&tmap_x);
+    for (int s = 0; s < kS; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full[a], 1);
+      mbar_init(&tmem_empty[a], kFastGroups * 128);
+      mbar_init(&x_full[a], 1);
+      mbar_init(&x_empty[a], kStats == 2 ? 1 : kFastGroups * 128);
+      mbar_init(&c_ready[a], 1);
+      mbar_init(&stats_done[a], 1);
+    }
+    mbar_init(stats_final, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc<kStats ? 512 : 256>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+
+  if (warp == 0) {
+    // ===================== TMA producer: operands + aux tile =====================
+    if (lane == 0) {
+      int stage = 0, xb = 0;
+      uint32_t phase = 0, x_phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
+        if (kAux) {
+          mbar_wait(&x_empty[xb], x_phase ^ 1);
+          mbar_expect_tx(&x_full[xb], uint32_t(n_chunks64) * kChunkTileBytes);
+          for (int ch = 0; ch < n_chunks64; ++ch)
+            tma_load_2d(x_stage + xb * c_bytes + ch * kChunkTileBytes, &tmap_x, &x_full[xb],
+                        n_blk * p.n_tile + ch * 64, m_blk * kBlockM);
+          if (++xb == 2) { xb = 0; x_phase ^= 1; }
+        }
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* a_dst = tiles + stage * stage_bytes;
+          mbar_expect_tx(&full_bar[stage], a_bytes + b_bytes);
+          tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * kBlockK, m_blk * kBlockM);
+          tma_load_2d(a_dst + a_bytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * p.n_tile);
+          if (++stage == kS) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(kBlockM, uint32_t(p.n_tile), false, false);
+      // statistics MMAs: D_s = Ones(K-major) . C(MN-major) ; D_g = C^T(MN-major) . {C | X}(MN-major)
+      const uint32_t idesc_s = umma_idesc_bf16(128, uint32_t(p.n_tile), false, true);
+      const uint32_t idesc_g = umma_idesc_bf16(128, uint32_t(p.n_tile), true, true);
+      const uint32_t d_sum = tmem_base + 2 * kFastNTile, d_gram = tmem_base + 3 * kFastNTile;
+      const uint64_t ones_desc = umma_smem_desc(smem_u32(ones), 16, 1024);
+      auto stats_mma = [&](int sacc, uint32_t sphase, bool first) {
+        mbar_wait(&c_ready[sacc], sphase);
+        tc_fence_after();
+        const uint32_t c_addr = smem_u32(c_stage + sacc * c_bytes);
+        const uint32_t o_addr = (kStats == 2) ? smem_u32(x_stage + sacc * c_bytes) : c_addr;
+#pragma unroll
+        for (int k = 0; k < 128 / 16; ++k) {
+          // 16 tile rows per MMA = 2048 B down the swizzled block; 64-column chunks are 16 KB apart
+          const uint64_t c_desc = umma_smem_desc(c_addr + k * 2048, kChunkTileBytes, 1024);
+          const uint64_t o_desc = umma_smem_desc(o_addr + k * 2048, kChunkTileBytes, 1024);
+          umma_bf16(d_sum, ones_desc, c_desc, idesc_s, !(first && k == 0));
+          umma_bf16(d_gram, c_desc, o_desc, idesc_g, !(first && k == 0));
+        }
+        umma_commit(&stats_done[sacc]);
+        if (kStats == 2) umma_commit(&x_empty[sacc]);
+      };
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      int done = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + uint32_t(acc) * kFastNTile;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(tiles + stage * stage_bytes);
+          const uint64_t a_desc = umma_smem_desc(a_addr, 16, 1024);
+          const uint64_t b_desc = umma_smem_desc(a_addr + a_bytes, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k)
+            umma_bf16(d_tmem, a_desc + uint64_t(k * 2), b_desc + uint64_t(k * 2), idesc, (kb | k) != 0);
+          umma_commit(&empty_bar[stage]);
+          if (kb == p.num_k_blocks - 1) umma_commit(&tmem_full[acc]);
+          if (++stage == kS) { stage = 0; phase ^= 1; }
+        }
+        if (kStats && done > 0) {
+          // statistics of the previous tile, whose staged output the epilogue has finished by now
+          const int pacc = acc ^ 1;
+          const uint32_t pphase = (pacc == 1) ? acc_phase ^ 1 : acc_phase;   // phase of tile done-1
+          stats_mma(pacc, (acc == 0) ? (acc_phase ^ 1) : acc_phase, done == 1);
+          (void)pphase;
+        }
+        ++done;
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+      if (kStats && done > 0) {
+        const int pacc = acc ^ 1;
+        stats_mma(pacc, (acc == 0) ? (acc_phase ^ 1) : acc_phase, done == 1);
+        umma_commit(stats_final);
+      }
+    }
+  } else {
+    // ===================== 16 epilogue warps =====================
+    const int quad = warp & 3;
+    const int group = (warp - 2) >> 2;
+    const int c = group * 32;                          // this warp's 32-column chunk of the tile
+    const bool active = c < p.n_tile;
+    const bool relu = p.relu != 0;
+    const bool mask = p.aux_relu_mask != 0;
+    const bool storer = (warp == 2 && lane == 0);
+    const int r = quad * 32 + lane;                    // tile-local row
+    // swizzled position of this thread's four 16-byte pieces inside its [128 x 128 B] block
+    const uint32_t blk_off = uint32_t(c >> 6) * kChunkTileBytes + uint32_t(r) * 128;
+    const uint32_t piece0 = uint32_t((c & 63) >> 3);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
+      const bool row_ok = (m_blk * kBlockM + r) < p.M;
+      const int n0 = n_blk * p.n_tile;
+      uint8_t* cbuf = c_stage + acc * c_bytes;
+      // the TMA store (and the statistics MMAs) that last read this staging buffer, two tiles ago,
+      // must have drained it
+      if (storer) tma_store_wait_read<1>();
+      if (kStats) mbar_wait(&stats_done[acc], acc_phase ^ 1);
+      mbar_wait(&tmem_full[acc], acc_phase);
+      if (kAux) mbar_wait(&x_full[acc], acc_phase);
+      tc_fence_after();
+      epi_barrier();
+      if (active) {
+        const int col0 = n0 + c;
+        uint32_t raw[32];
+        tmem_ld_32x32(tmem_base + (uint32_t(quad * 32) << 16) + uint32_t(acc) * kFastNTile + uint32_t(c), raw);
+        uint4 ua[4];
+        if (kAux) {
+          const uint8_t* xrow = x_stage + acc * c_bytes + blk_off;
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            ua[q] = *reinterpret_cast<const uint4*>(xrow + (((piece0 + q) ^ uint32_t(r & 7)) << 4));
+        }
+        tmem_ld_wait();
+        float v[32];
+        const float4* b4 = reinterpret_cast<const float4*>(s_bias + col0);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 bb = b4[q];
+          v[q * 4 + 0] = __uint_as_float(raw[q * 4 + 0]) + bb.x;
+          v[q * 4 + 1] = __uint_as_float(raw[q * 4 + 1]) + bb.y;
+          v[q * 4 + 2] = __uint_as_float(raw[q * 4 + 2]) + bb.z;
+          v[q * 4 + 3] = __uint_as_float(raw[q * 4 + 3]) + bb.w;
+        }
+        if (relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
+        if (kAux && mask) {
+          const uint32_t* au = reinterpret_cast<const uint32_t*>(ua);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float a0 = __uint_as_float(au[i] << 16), a1 = __uint_as_float(au[i] & 0xffff0000u);
+            v[2 * i] = a0 > 0.f ? v[2 * i] : 0.f;
+            v[2 * i + 1] = a1 > 0.f ? v[2 * i + 1] : 0.f;
+          }
+        }
+        uint32_t packed[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) packed[i] = row_ok ? pack_bf16x2(v[2 * i], v[2 * i + 1]) : 0u;
+        uint8_t* crow = cbuf + blk_off;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          *reinterpret_cast<uint4*>(crow + (((piece0 + q) ^ uint32_t(r & 7)) << 4)) =
+              make_uint4(packed[q * 4], packed[q * 4 + 1], packed[q * 4 + 2], packed[q * 4 + 3]);
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[acc]);
+      if (kAux && kStats != 2) mbar_arrive(&x_empty[acc]);
+      fence_async_smem();                       // generic-proxy smem writes -> visible to TMA / UMMA
+      epi_barrier();
+      if (storer) {
+        for (int ch = 0; ch < n_chunks64; ++ch)
+          tma_store_2d(&tmap_c, cbuf + ch * kChunkTileBytes, n0 + ch * 64, m_blk * kBlockM);
+        tma_store_commit();
+        if (kStats) mbar_arrive(&c_ready[acc]);
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if (storer) tma_store_wait_all();
+    if (kStats && group == 0 && blockIdx.x < num_tiles) {
+      // every tile of this CTA has the same n_blk (grid stride is a multiple of num_n_tiles), so the
+      // TMEM statistics accumulators cover columns [n0, n0 + n_tile).  Lane l of quadrant q owns row
+      // 32q + l: it reads the diagonal elements (32q + l, 32q + l) of D_s and D_g.
+      mbar_wait(stats_final, 0);
+      tc_fence_after();
+      const int n0 = (blockIdx.x % p.num_n_tiles) * p.n_tile;
+      if (quad * 32 < p.n_tile) {
+        uint32_t ds[32], dg[32];
+        const uint32_t lanes = uint32_t(quad * 32) << 16;
+        tmem_ld_32x32(tmem_base + lanes + 2 * kFastNTile + uint32_t(quad * 32), ds);
+        tmem_ld_32x32(tmem_base + lanes + 3 * kFastNTile + uint32_t(quad * 32), dg);
+        tmem_ld_wait();
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (lane == j) { s0 = __uint_as_float(ds[j]); s1 = __uint_as_float(dg[j]); }
+        }
+        const int col = n0 + quad * 32 + lane;
+        atomicAdd(&p.stats[col], s0);
+        atomicAdd(&p.stats[p.N + col], s1);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kStats ? 512 : 256>(tmem_base);
+  }
+}
+
+template <int kStats, bool kAux>
+static int launch_fast(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+                       const GemmTnParams& p, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_fast_kernel<kStats, kAux>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  const size_t smem = size_t(kAux ? 2 : 3) * (16384 + kFastNTile * 128) + (kAux ? 4 : 2) * 2 * kChunkTileBytes +
+                      (kStats ? kChunkTileBytes : 0) + 256 + kStatsCols * sizeof(float) + 1024;
+  const int tiles = p.num_m_tiles * p.num_n_tiles;
+  // a CTA must only ever see one n_blk (its TMEM statistics accumulators are per column block)
+  int grid = (num_sms() / p.num_n_tiles) * p.num_n_tiles;
+  if (grid < p.num_n_tiles) grid = p.num_n_tiles;
+  if (tiles < grid) grid = tiles;
+  gemm_tn_fast_kernel<kStats, kAux><<<grid, kFastThreads, smem, stream>>>(ta, tb, tc, tx, p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -383,9 +737,26 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
         if (m < p.Mw) {
           float* dst = p.out + size_t(m) * p.ldo + col0;
           const int ncols = min(32, min(p.n_tile - c, p.Nw - col0));
+          if ((p.ldo & 3) == 0) {
+            // red.global.add.v4.f32: a quarter of the reduction instructions of scalar atomics
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < ncols) atomicAdd(dst + j, __uint_as_float(raw[j]));
+            for (int q = 0; q < 8; ++q) {
+              if (q * 4 + 3 < ncols) {
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + q * 4),
+                             "f"(__uint_as_float(raw[q * 4])), "f"(__uint_as_float(raw[q * 4 + 1])),
+                             "f"(__uint_as_float(raw[q * 4 + 2])), "f"(__uint_as_float(raw[q * 4 + 3]))
+                             : "memory");
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (q * 4 + j < ncols) atomicAdd(dst + q * 4 + j, __uint_as_float(raw[q * 4 + j]));
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < ncols) atomicAdd(dst + j, __uint_as_float(raw[j]));
+          }
         }
       }
     }
@@ -401,7 +772,7 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
 static size_t gemm_tn_smem_bytes(int n_tile) {
   const size_t a_bytes = kBlockM * kBlockK * 2;
   const size_t b_bytes = (size_t(n_tile) * kBlockK * 2 + 1023) & ~size_t(1023);
-  return kStages * (a_bytes + b_bytes) + 256 + 2 * kStatsCols * sizeof(float) + 1024;
+  return kStages * (a_bytes + b_bytes) + 256 + 3 * kStatsCols * sizeof(float) + 1024;
 }
 
 }  // namespace rdp
@@ -442,7 +813,28 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
   }
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_tn_kernel<<<grid, kGemmThreads, smem, static_cast<cudaStream_t>(stream)>>>(ta, tb, p);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  const bool use_aux = (stats_mode == 2) || aux_relu_mask;
+  if (!out_f32 && N % 64 == 0 && N <= kStatsCols) {
+    GemmTnParams f = p;
+    f.n_tile = (N % kFastNTile == 0) ? kFastNTile : 64;
+    f.num_n_tiles = N / f.n_tile;
+    CUtensorMap fb, fc, fx;
+    rc = make_tmap_2d_bf16(&fb, b, N, K, ldb, f.n_tile, kBlockK);
+    if (rc) return rc;
+    rc = make_tmap_2d_bf16(&fc, out, M, N, ldc, kBlockM, 64);
+    if (rc) return rc;
+    fx = fc;
+    if (use_aux) {
+      rc = make_tmap_2d_bf16(&fx, aux, M, N, ld_aux, kBlockM, 64);
+      if (rc) return rc;
+    }
+    if (stats_mode == 0 && !use_aux) return launch_fast<0, false>(ta, fb, fc, fx, f, cs);
+    if (stats_mode == 1 && !use_aux) return launch_fast<1, false>(ta, fb, fc, fx, f, cs);
+    if (stats_mode == 2) return launch_fast<2, true>(ta, fb, fc, fx, f, cs);
+    if (stats_mode == 0 && use_aux) return launch_fast<0, true>(ta, fb, fc, fx, f, cs);
+  }
+  gemm_tn_kernel<<<grid, kGemmThreads, smem, cs>>>(ta, tb, p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -147,38 +147,67 @@ bn_relu_bwd_kernel(const BnReluBwdParams p) {
       }
     }
   }
-  for (int r = blockIdx.x * rows_per_block + trow; r < p.B; r += gridDim.x * rows_per_block) {
-    const uint4 udy = __ldg(reinterpret_cast<const uint4*>(p.dy + size_t(r) * p.ld + c0));
-    const uint4 uz = __ldg(reinterpret_cast<const uint4*>(p.z + size_t(r) * p.ld + c0));
-    const uint32_t dyw[4] = {udy.x, udy.y, udy.z, udy.w};
-    const uint32_t zw[4] = {uz.x, uz.y, uz.z, uz.w};
-    uint32_t ow[4];
+  // four rows per thread per trip: all eight 16-byte loads are in flight before the first use
+  const int row_stride = gridDim.x * rows_per_block;
+  for (int r0 = blockIdx.x * rows_per_block + trow; r0 < p.B; r0 += 4 * row_stride) {
+    uint4 udy[4], uz[4];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float2 d = unpack_bf16x2(dyw[q]);
-      const float2 zz = unpack_bf16x2(zw[q]);
-      float o0, o1;
-      if (p.has_bn) {
-        const float zh0 = (zz.x - mu[2 * q]) * rs[2 * q];
-        const float zh1 = (zz.y - mu[2 * q + 1]) * rs[2 * q + 1];
-        o0 = zz.x > 0.f ? aa[2 * q] * (d.x - m1[2 * q] - zh0 * m2[2 * q]) : 0.f;
-        o1 = zz.y > 0.f ? aa[2 * q + 1] * (d.y - m1[2 * q + 1] - zh1 * m2[2 * q + 1]) : 0.f;
-      } else {
-        o0 = zz.x > 0.f ? d.x : 0.f;
-        o1 = zz.y > 0.f ? d.y : 0.f;
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + u * row_stride;
+      if (r < p.B) {
+        udy[u] = __ldg(reinterpret_cast<const uint4*>(p.dy + size_t(r) * p.ld + c0));
+        uz[u] = __ldg(reinterpret_cast<const uint4*>(p.z + size_t(r) * p.ld + c0));
       }
-      ow[q] = pack_bf16x2(o0, o1);
-      const float2 rounded = unpack_bf16x2(ow[q]);
-      acc[2 * q] += rounded.x;
-      acc[2 * q + 1] += rounded.y;
     }
-    *reinterpret_cast<uint4*>(p.dpre + size_t(r) * p.ld + c0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + u * row_stride;
+      if (r >= p.B) break;
+      const uint32_t dyw[4] = {udy[u].x, udy[u].y, udy[u].z, udy[u].w};
+      const uint32_t zw[4] = {uz[u].x, uz[u].y, uz[u].z, uz[u].w};
+      uint32_t ow[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 d = unpack_bf16x2(dyw[q]);
+        const float2 zz = unpack_bf16x2(zw[q]);
+        float o0, o1;
+        if (p.has_bn) {
+          const float zh0 = (zz.x - mu[2 * q]) * rs[2 * q];
+          const float zh1 = (zz.y - mu[2 * q + 1]) * rs[2 * q + 1];
+          o0 = zz.x > 0.f ? aa[2 * q] * (d.x - m1[2 * q] - zh0 * m2[2 * q]) : 0.f;
+          o1 = zz.y > 0.f ? aa[2 * q + 1] * (d.y - m1[2 * q + 1] - zh1 * m2[2 * q + 1]) : 0.f;
+        } else {
+          o0 = zz.x > 0.f ? d.x : 0.f;
+          o1 = zz.y > 0.f ? d.y : 0.f;
+        }
+        ow[q] = pack_bf16x2(o0, o1);
+        const float2 rounded = unpack_bf16x2(ow[q]);
+        acc[2 * q] += rounded.x;
+        acc[2 * q + 1] += rounded.y;
+      }
+      *reinterpret_cast<uint4*>(p.dpre + size_t(r) * p.ld + c0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
   }
   extern __shared__ float s_col[];   // [N]
   for (int i = threadIdx.x; i < p.N; i += blockDim.x) s_col[i] = 0.f;
   __syncthreads();
+  // lanes that own the same columns (narrow layers: several rows per warp) combine first, so
+  // the shared-memory atomics see at most one add per column per warp
+  bool leader = true;
+  if (vec_per_row < 32) {
 #pragma unroll
-  for (int j = 0; j < 8; ++j) atomicAdd(&s_col[c0 + j], acc[j]);
+    for (int o = 16; o >= 1; o >>= 1) {
+      if (o >= vec_per_row) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+      }
+    }
+    leader = (threadIdx.x & 31) < vec_per_row;
+  }
+  if (leader) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&s_col[c0 + j], acc[j]);
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < p.N; i += blockDim.x)
     if (s_col[i] != 0.f) atomicAdd(&p.dbias[i], s_col[i]);
@@ -417,9 +446,10 @@ int rdp_bn_relu_bwd(const void* dy, const void* z, void* dpre, int B, int N, int
   BnReluBwdParams p{static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z),
                     static_cast<__nv_bfloat16*>(dpre), B, N, ld, stats2, mean, rstd, a, dgamma, dbeta, dbias, has_bn};
   const int rows_per_block = 256 / (N / 8);
-  int grid = (B + rows_per_block - 1) / rows_per_block;
+  int grid = (B + 4 * rows_per_block - 1) / (4 * rows_per_block);
   const int cap = num_sms() * 8;
   if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
   bn_relu_bwd_kernel<<<grid, 256, N * sizeof(float), static_cast<cudaStream_t>(stream)>>>(p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -432,7 +462,7 @@ int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const floa
   HeadParams p{static_cast<const __nv_bfloat16*>(z), B, K, ld, a, c, w, bias, target, loss_kind, grad_scale,
                pred, accum, static_cast<__nv_bfloat16*>(dy), stats2, dw, db};
   int grid = (B + 255) / 256;
-  const int cap = num_sms() * 4;
+  const int cap = num_sms() * 2;
   if (grid > cap) grid = cap;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (K == 16) mlp_head_kernel<16><<<grid, 256, 0, s>>>(p);
