@@ -68,7 +68,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -77,12 +77,17 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
-    def stop(self) -> dict:
+    def wait_first_sample(self, timeout: float = 3.0) -> None:
+        t0 = time.time()
+        while not self.lines and time.time() - t0 < timeout:
+            time.sleep(0.01)
+
+    def stop(self, t_begin: float = 0.0, t_end: float = float("inf")) -> dict:
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.06)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -90,7 +95,12 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.lines:
+        inside = [l for ts, l in self.lines if t_begin <= ts <= t_end + 0.03]
+        window = "timed region"
+        if not inside:      # region shorter than the sampling period: use the samples taken under load
+            inside = [l for ts, l in self.lines if ts >= t_begin - 0.25]
+            window = "warm-up + timed region (timed region shorter than the 20 ms sampling period)"
+        for line in inside:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) < 6:
                 continue
@@ -104,7 +114,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 def dist_setup(n):
@@ -193,20 +203,23 @@ def run_ours_device(args, rank, world, local):
         y.copy_(pool_y[i % pool_n])
         engine._train_step(x, y)
 
+    sampler = ClockSampler(local)
+    sampler.start()
+    sampler.wait_first_sample()
     for i in range(max(args.warmup, 3)):
         step(i)
     barrier(world)
     launches0 = ops.launch_count()
-    sampler = ClockSampler(local)
-    sampler.start()
+    t_begin = time.time()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
     for i in range(args.steps):
         step(i)
     end.record()
     torch.cuda.synchronize()
+    t_end = time.time()
     barrier(world)
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_begin, t_end)
     ms = max_over_ranks(start.elapsed_time(end), world)
     launches = ops.launch_count() - launches0
     loss = float((engine.fused.accum[0] / engine.fused.accum[3]).item())
@@ -308,11 +321,13 @@ def run_standin(args, rank, world, local):
         return total
 
     w = max(args.warmup, 3)
+    sampler = ClockSampler(local)
+    sampler.start()
+    sampler.wait_first_sample()
     for i in range(w):
         step(i)
     barrier(world)
-    sampler = ClockSampler(local)
-    sampler.start()
+    t_begin = time.time()
     t0 = time.perf_counter()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
@@ -321,8 +336,9 @@ def run_standin(args, rank, world, local):
     end.record()
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
+    t_end = time.time()
     barrier(world)
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_begin, t_end)
     secs = max_over_ranks(max(wall, start.elapsed_time(end) / 1e3), world)
     value = world * B * args.steps / secs
     return {"ms_per_step": secs * 1e3 / args.steps, "value": value, "clocks": clocks, "gpu_launches": 0,

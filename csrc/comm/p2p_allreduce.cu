@@ -1,0 +1,328 @@
+// K1 / K2: gradient all-reduce over NVLink peer memory, fused with the optimizer
+// (SURVEY.md section 5.8, section 8 rows K1, K2, S2).
+//
+// Replaces the NCCL all-reduce that torch DDP issues for the reference
+// (`train.torch.prepare_model` -> DDP, reference python/raydp/torch/estimator.py:243) plus the
+// separate `optimizer.step()` (`:284-286`).  One process per GPU; every rank owns a *symmetric*
+// cudaMalloc region that all peers map through CUDA IPC:
+//
+//     [ send[0] | send[1] | recv[0] | recv[1] | flags ]
+//
+//  * one-shot (small messages, e.g. the 48 513-parameter NYC-taxi MLP): copy the local gradient
+//    into send[e&1], signal every peer, wait for every peer, then each rank pulls all W copies
+//    straight over NVLink, sums in registers and -- in the fused variant -- applies 1/W scaling
+//    and the Adam / SGD update in the same pass.  One kernel, one flag round.
+//  * two-shot (large messages): rank r reduces slice r from all peers (reduce-scatter by pull)
+//    and pushes the reduced slice into recv[e&1] of every peer (all-gather by push), a second
+//    flag round publishes it, and the optimizer epilogue reads recv[] locally.
+//
+// Flags are monotonically increasing epochs (no reset races); buffers alternate on epoch parity
+// so a rank can start filling the next step's buffer while a slow peer still reads this one.
+// The epoch lives in device memory and is advanced by the kernel, so a captured CUDA graph can
+// replay the step.  Blocks of one launch wait on other GPUs, never on each other's *launches*:
+// the grid is capped so that all its blocks are resident at once.
+//
+// Single-GPU emulation (tests): gridDim.y = world, blockIdx.y = rank, all "peer" pointers local,
+// launched cooperatively so every rank's blocks are co-resident.
+#include "common.cuh"
+#include "raydp_b200.h"
+
+#include <string.h>
+
+namespace rdp {
+
+constexpr int kMaxRanks = 8;
+constexpr int kArThreads = 512;
+
+struct OptSpec {
+  int kind;            // 0 none (write the sum * scale to out), 1 Adam/AdamW, 2 SGD
+  float* p;            // parameters (fp32)
+  float* m;            // Adam m / SGD momentum buffer
+  float* v;            // Adam v
+  float lr, beta1, beta2, eps, weight_decay, momentum, dampening;
+  int adamw, nesterov;
+  const float* lr_ptr;     // optional device scalars
+  const float* step_ptr;
+};
+
+struct RankArgs {
+  const float* in;                 // local gradient (n floats)
+  float* out;                      // local result (may alias `in`)
+  float* send[2][kMaxRanks];       // send[b][q]: rank q's send buffer, as mapped in THIS rank
+  float* recv[2][kMaxRanks];       // recv[b][q]
+  uint32_t* flags[kMaxRanks];      // flags[q]: rank q's flag array (2 * kMaxRanks words)
+  uint32_t* epoch;                 // local: last completed epoch
+  uint32_t* counters;              // local: [0] copy-done, [1] finished, [2] reduce-done
+  OptSpec opt;
+};
+
+struct ArParams {
+  RankArgs rank[kMaxRanks];        // indexed by blockIdx.y in emulation, [0] otherwise
+  int rank_base;                   // this process' rank (0 in emulation)
+  int world;
+  int64_t n;                       // floats
+  float scale;                     // applied to the sum (1/world for averaging)
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer(const float* p) {
+  float4 v;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+// All blocks of this rank's grid have finished their part -> the last one signals `slot` on every
+// peer; then every block waits until all ranks have signalled epoch e on OUR flag array.
+__device__ __forceinline__ void grid_signal_and_wait(const RankArgs& a, int my_rank, int world, uint32_t e,
+                                                     int slot, uint32_t* counter, int nblocks) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(counter, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      *counter = 0;
+      __threadfence_system();
+      for (int q = 0; q < world; ++q) st_release_sys(a.flags[q] + slot * kMaxRanks + my_rank, e);
+    }
+  }
+  if (int(threadIdx.x) < world) {
+    const uint32_t* f = a.flags[my_rank] + slot * kMaxRanks + threadIdx.x;
+    while (int32_t(ld_acquire_sys(f) - e) < 0) {
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void apply_update(const OptSpec& o, int64_t i, float4 g, float bc1, float bc2, float lr,
+                                             bool first_step, float* out) {
+  float gs[4] = {g.x, g.y, g.z, g.w};
+  if (o.kind == 0) {
+    *reinterpret_cast<float4*>(out + i) = g;
+    return;
+  }
+  float4 p4 = *reinterpret_cast<float4*>(o.p + i);
+  float ps[4] = {p4.x, p4.y, p4.z, p4.w};
+  if (o.kind == 1) {
+    float4 m4 = *reinterpret_cast<float4*>(o.m + i), v4 = *reinterpret_cast<float4*>(o.v + i);
+    float ms[4] = {m4.x, m4.y, m4.z, m4.w}, vs[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float gk = gs[k];
+      if (o.weight_decay != 0.f) { if (o.adamw) ps[k] *= (1.f - lr * o.weight_decay); else gk += o.weight_decay * ps[k]; }
+      ms[k] = o.beta1 * ms[k] + (1.f - o.beta1) * gk;
+      vs[k] = o.beta2 * vs[k] + (1.f - o.beta2) * gk * gk;
+      ps[k] -= (lr / bc1) * (ms[k] / (sqrtf(vs[k]) / sqrtf(bc2) + o.eps));
+    }
+    *reinterpret_cast<float4*>(o.m + i) = make_float4(ms[0], ms[1], ms[2], ms[3]);
+    *reinterpret_cast<float4*>(o.v + i) = make_float4(vs[0], vs[1], vs[2], vs[3]);
+  } else {
+    float4 b4 = o.m ? *reinterpret_cast<float4*>(o.m + i) : make_float4(0, 0, 0, 0);
+    float bs[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float gk = gs[k] + o.weight_decay * ps[k];
+      if (o.m != nullptr && o.momentum != 0.f) {
+        bs[k] = first_step ? gk : o.momentum * bs[k] + (1.f - o.dampening) * gk;
+        gk = o.nesterov ? gk + o.momentum * bs[k] : bs[k];
+      }
+      ps[k] -= lr * gk;
+    }
+    if (o.m) *reinterpret_cast<float4*>(o.m + i) = make_float4(bs[0], bs[1], bs[2], bs[3]);
+  }
+  *reinterpret_cast<float4*>(o.p + i) = make_float4(ps[0], ps[1], ps[2], ps[3]);
+  if (out != nullptr) *reinterpret_cast<float4*>(out + i) = g;
+}
+
+template <bool kTwoShot>
+__global__ void __launch_bounds__(kArThreads)
+allreduce_kernel(const __grid_constant__ ArParams P) {
+  const RankArgs& a = P.rank[blockIdx.y];
+  const int my_rank = P.rank_base + blockIdx.y;
+  const int world = P.world;
+  const int nblocks = gridDim.x;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(a.epoch) + 1u;
+  const int b = e & 1;
+  const int64_t n4 = P.n / 4;                      // n is padded to a multiple of 4 by the host
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  const int64_t nthreads = int64_t(nblocks) * blockDim.x;
+
+  // optimizer scalars (device-resident so CUDA graphs follow lr schedules / bias correction)
+  float lr = a.opt.lr, bc1 = 1.f, bc2 = 1.f;
+  bool first_step = false;
+  if (a.opt.kind) {
+    if (a.opt.lr_ptr) lr = *a.opt.lr_ptr;
+    const float t = a.opt.step_ptr ? *a.opt.step_ptr : 1.f;
+    bc1 = 1.f - powf(a.opt.beta1, t);
+    bc2 = 1.f - powf(a.opt.beta2, t);
+    first_step = t <= 1.f;
+  }
+
+  // phase 1: publish my gradient in my send buffer
+  float* mine = a.send[b][my_rank];
+  for (int64_t i = tid; i < n4; i += nthreads)
+    reinterpret_cast<float4*>(mine)[i] = reinterpret_cast<const float4*>(a.in)[i];
+  grid_signal_and_wait(a, my_rank, world, e, 0, a.counters + 0, nblocks);
+
+  if (!kTwoShot) {
+    // phase 2: pull every rank's copy over NVLink, sum in registers, update.  The sum runs in rank
+    // order on every rank so that all replicas compute bit-identical parameters.
+    for (int64_t i = tid; i < n4; i += nthreads) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+      for (int q = 0; q < world; ++q) {
+        const float4 v = ld_peer(a.send[b][q] + i * 4);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+      s.x *= P.scale; s.y *= P.scale; s.z *= P.scale; s.w *= P.scale;
+      apply_update(a.opt, i * 4, s, bc1, bc2, lr, first_step, a.out);
+    }
+  } else {
+    // phase 2: reduce-scatter by pull (slice my_rank), all-gather by push into every recv[b]
+    const int64_t per = (n4 + world - 1) / world;
+    const int64_t lo = per * my_rank, hi = min(n4, lo + per);
+    for (int64_t i = lo + tid; i < hi; i += nthreads) {
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+      for (int q = 0; q < world; ++q) {
+        const float4 v = ld_peer(a.send[b][(my_rank + q) % world] + i * 4);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+      s.x *= P.scale; s.y *= P.scale; s.z *= P.scale; s.w *= P.scale;
+#pragma unroll 4
+      for (int q = 0; q < world; ++q)
+        reinterpret_cast<float4*>(a.recv[b][(my_rank + q) % world])[i] = s;
+    }
+    grid_signal_and_wait(a, my_rank, world, e, 1, a.counters + 2, nblocks);
+    // phase 3: optimizer epilogue (or copy-out) from the locally complete recv buffer
+    const float* full = a.recv[b][my_rank];
+    for (int64_t i = tid; i < n4; i += nthreads)
+      apply_update(a.opt, i * 4, reinterpret_cast<const float4*>(full)[i], bc1, bc2, lr, first_step, a.out);
+  }
+
+  // the last block to finish advances the epoch for the next launch
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(a.counters + 1, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      a.counters[1] = 0;
+      *a.epoch = e;
+    }
+  }
+}
+
+}  // namespace rdp
+
+using namespace rdp;
+
+extern "C" {
+
+// ---- symmetric memory plumbing (host) -----------------------------------------------------------
+int rdp_comm_alloc(uint64_t bytes, void** out) {
+  RDP_CHECK_CUDA(cudaMalloc(out, bytes));
+  RDP_CHECK_CUDA(cudaMemset(*out, 0, bytes));
+  RDP_CHECK_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+
+int rdp_comm_free(void* ptr) {
+  RDP_CHECK_CUDA(cudaFree(ptr));
+  return 0;
+}
+
+int rdp_comm_ipc_handle(void* ptr, void* handle64) {
+  cudaIpcMemHandle_t h;
+  RDP_CHECK_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  memcpy(handle64, &h, sizeof(h));
+  return 0;
+}
+
+int rdp_comm_ipc_open(const void* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  RDP_CHECK_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+int rdp_comm_ipc_close(void* ptr) {
+  RDP_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+
+int rdp_comm_can_access_peer(int dev, int peer) {
+  int ok = 0;
+  if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) return 0;
+  return ok;
+}
+
+// ---- all-reduce -----------------------------------------------------------------------------------
+// Layout of one rank's symmetric region, in floats: send[0] | send[1] | recv[0] | recv[1] | flags.
+// `bases[q]` = rank q's region as mapped in this process.  In emulation (n_local_ranks == world)
+// every per-rank array has `world` entries and all pointers are local.
+int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
+                  const float* const* ins, float* const* outs, uint32_t* const* epochs,
+                  uint32_t* const* counters, const rdp_opt_args* opts, int64_t n, float scale,
+                  int algo, void* stream) {
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks, "rdp_allreduce: world=%d (max %d)", world, kMaxRanks);
+  RDP_REQUIRE(n_local_ranks == 1 || n_local_ranks == world, "rdp_allreduce: bad n_local_ranks");
+  RDP_REQUIRE(n % 4 == 0, "rdp_allreduce: n=%lld must be a multiple of 4 (pad the flat buffer)", (long long)n);
+  RDP_REQUIRE(n > 0 && uint64_t(n) <= slot_floats && slot_floats % 4 == 0,
+              "rdp_allreduce: n=%lld exceeds the symmetric slot (%llu floats)", (long long)n,
+              (unsigned long long)slot_floats);
+  ArParams P;
+  memset(&P, 0, sizeof(P));
+  P.rank_base = n_local_ranks == 1 ? rank : 0;
+  P.world = world;
+  P.n = (n + 3) / 4 * 4;
+  P.scale = scale;
+  for (int l = 0; l < n_local_ranks; ++l) {
+    RankArgs& a = P.rank[l];
+    a.in = ins[l];
+    a.out = outs[l];
+    a.epoch = epochs[l];
+    a.counters = counters[l];
+    for (int q = 0; q < world; ++q) {
+      float* base = static_cast<float*>(bases[q]);
+      a.send[0][q] = base;
+      a.send[1][q] = base + slot_floats;
+      a.recv[0][q] = base + 2 * slot_floats;
+      a.recv[1][q] = base + 3 * slot_floats;
+      a.flags[q] = reinterpret_cast<uint32_t*>(base + 4 * slot_floats);
+    }
+    if (opts != nullptr) {
+      const rdp_opt_args& o = opts[l];
+      a.opt = OptSpec{o.kind, o.p, o.m, o.v, o.lr, o.beta1, o.beta2, o.eps, o.weight_decay, o.momentum,
+                      o.dampening, o.adamw, o.nesterov, o.lr_ptr, o.step_ptr};
+    }
+  }
+  const bool two_shot = algo == 2 || (algo == 0 && n * 4 > (1 << 20));
+  int64_t work = two_shot ? P.n / 4 / world : P.n / 4;
+  int blocks = int((work + kArThreads - 1) / kArThreads);
+  int cap = two_shot ? num_sms() / 2 : 32;
+  if (n_local_ranks > 1) cap = max(1, (num_sms() / 2) / world);      // emulation: all ranks share one GPU
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  dim3 grid(blocks, n_local_ranks);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  void* args[] = {&P};
+  if (n_local_ranks > 1) {
+    // ranks of an emulated world wait on each other inside one grid: co-residency must be guaranteed
+    if (two_shot) RDP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)allreduce_kernel<true>, grid, dim3(kArThreads), args, 0, s));
+    else RDP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)allreduce_kernel<false>, grid, dim3(kArThreads), args, 0, s));
+  } else {
+    if (two_shot) allreduce_kernel<true><<<grid, kArThreads, 0, s>>>(P);
+    else allreduce_kernel<false><<<grid, kArThreads, 0, s>>>(P);
+  }
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -83,6 +83,33 @@ int rdp_ingest_indices(const void* const* cols, const int* dtypes, int n_cols, i
                        const int* table_rows, int n_cross, const int* cross_a, const int* cross_b,
                        const int* cross_rows, int* out, void* stream);
 
+// ---- K1 / K2: peer-memory gradient all-reduce fused with the optimizer ---------------------------
+// (NCCL all-reduce issued by DDP + torch.optim step; reference torch/estimator.py:243, :284-286)
+// Symmetric region of one rank, in floats: send[0] | send[1] | recv[0] | recv[1] | flags(64 B);
+// allocate 4 * slot_floats * 4 + 256 bytes with rdp_comm_alloc, exchange rdp_comm_ipc_handle blobs
+// (64 bytes) between the ranks' processes and map them with rdp_comm_ipc_open.
+int rdp_comm_alloc(uint64_t bytes, void** out);
+int rdp_comm_free(void* ptr);
+int rdp_comm_ipc_handle(void* ptr, void* handle64);
+int rdp_comm_ipc_open(const void* handle64, void** out);
+int rdp_comm_ipc_close(void* ptr);
+int rdp_comm_can_access_peer(int dev, int peer);
+struct rdp_opt_args {
+  int kind;                      // 0: out = scale * sum ; 1: Adam / AdamW ; 2: SGD
+  float* p; float* m; float* v;  // parameters and optimizer state (fp32, n floats)
+  float lr, beta1, beta2, eps, weight_decay, momentum, dampening;
+  int adamw, nesterov;
+  const float* lr_ptr; const float* step_ptr;   // optional device scalars (override lr / step)
+};
+// bases[q]: rank q's symmetric region as mapped in this process (host array of `world` pointers).
+// n_local_ranks = 1 (normal: ins/outs/epochs/counters/opts have one entry) or = world (single-GPU
+// emulation of all ranks in one cooperative launch).  epochs[l] -> one uint32, counters[l] -> four
+// uint32, both zero-initialised device memory owned by the caller.  algo: 0 auto, 1 one-shot, 2 two-shot.
+int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
+                  const float* const* ins, float* const* outs, uint32_t* const* epochs,
+                  uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,
+                  int algo, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

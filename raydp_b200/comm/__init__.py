@@ -1,0 +1,160 @@
+"""Communicator over NVLink peer memory.
+
+The reference never calls a collective itself: DDP/NCCL do it implicitly behind
+``train.torch.prepare_model`` (reference ``torch/estimator.py:243``).  Here the gradient
+all-reduce is a hand-written kernel (``csrc/comm/p2p_allreduce.cu``) over *symmetric memory*:
+every rank ``cudaMalloc``s one region, the 64-byte CUDA IPC handles travel through the
+``torch.distributed`` store, and each rank maps all peers' regions, after which ranks read
+and write each other's HBM directly through NVSwitch.  ``torch.distributed`` (NCCL) stays the
+bootstrap and the baseline.
+
+``SymmetricMemory``  -- allocation + handle exchange.
+``P2PReducer``       -- ``allreduce_()`` (sum in place) and ``allreduce_step_()`` (sum, scale and
+                       Adam/SGD update in the same kernel).
+``LocalEmulation``   -- all ranks of a world on ONE GPU in one cooperative launch: how the
+                       flag protocol is tested where only a single GPU is available.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from raydp_b200 import ops
+from raydp_b200.ops._abi import OptArgs
+
+FLAG_BYTES = 256
+ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2}
+
+
+def p2p_available() -> bool:
+    """True when every GPU of this host's ranks can map every other one."""
+    if not torch.cuda.is_available() or not dist.is_initialized():
+        return False
+    n = torch.cuda.device_count()
+    me = torch.cuda.current_device()
+    lib = ops.lib()
+    ok = all(lib.rdp_comm_can_access_peer(me, d) for d in range(n) if d != me) and n >= dist.get_world_size()
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return bool(flag.item())
+
+
+class SymmetricMemory:
+    """One region per rank, mapped by all ranks.  ``bases[q]`` is rank q's region in this process."""
+
+    def __init__(self, nbytes: int, group=None):
+        self.lib = ops.lib()
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.nbytes = int(nbytes)
+        ptr = ctypes.c_void_p()
+        ops._check(self.lib.rdp_comm_alloc(self.nbytes, ctypes.byref(ptr)))
+        self.local = ptr.value
+        handle = ctypes.create_string_buffer(64)
+        ops._check(self.lib.rdp_comm_ipc_handle(ctypes.c_void_p(self.local), handle))
+        gathered: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(gathered, bytes(handle.raw), group=group)
+        self.bases: List[int] = []
+        self._opened: List[int] = []
+        for q, blob in enumerate(gathered):
+            if q == self.rank:
+                self.bases.append(self.local)
+                continue
+            out = ctypes.c_void_p()
+            buf = ctypes.create_string_buffer(blob, 64)
+            ops._check(self.lib.rdp_comm_ipc_open(buf, ctypes.byref(out)))
+            self.bases.append(out.value)
+            self._opened.append(out.value)
+        dist.barrier(group)
+
+    def close(self) -> None:
+        if self.local is None:
+            return
+        torch.cuda.synchronize()
+        try:
+            dist.barrier()
+        except Exception:  # noqa: BLE001
+            pass
+        for ptr in self._opened:
+            self.lib.rdp_comm_ipc_close(ctypes.c_void_p(ptr))
+        self.lib.rdp_comm_free(ctypes.c_void_p(self.local))
+        self.local = None
+
+
+def _opt_args(kind: int = 0, p=None, m=None, v=None, lr=0.0, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
+              momentum=0.0, dampening=0.0, adamw=False, nesterov=False, lr_dev=None, step_dev=None) -> OptArgs:
+    ptr = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
+    return OptArgs(kind, ptr(p), ptr(m), ptr(v), lr, betas[0], betas[1], eps, weight_decay, momentum,
+                   dampening, 1 if adamw else 0, 1 if nesterov else 0, ptr(lr_dev), ptr(step_dev))
+
+
+def _launch(lib, bases: Sequence[int], slot_floats: int, rank: int, world: int, ins, outs, epochs, counters,
+            opts: Optional[Sequence[OptArgs]], n: int, scale: float, algo: int) -> None:
+    nl = len(ins)
+    vp = ctypes.c_void_p
+    arr = lambda xs: (vp * len(xs))(*[vp(x) for x in xs])  # noqa: E731
+    opt_arr = (OptArgs * nl)(*opts) if opts is not None else None
+    ops._check(lib.rdp_allreduce(arr(bases), slot_floats, rank, world, nl,
+                                 arr([t.data_ptr() for t in ins]), arr([t.data_ptr() for t in outs]),
+                                 arr([t.data_ptr() for t in epochs]), arr([t.data_ptr() for t in counters]),
+                                 opt_arr, n, scale, algo,
+                                 vp(torch.cuda.current_stream().cuda_stream)))
+
+
+class P2PReducer:
+    """Gradient all-reduce for one flat fp32 buffer."""
+
+    kind = "p2p"
+
+    def __init__(self, grads: torch.Tensor, device: torch.device, group=None, algo: str = "auto"):
+        assert grads.dtype == torch.float32 and grads.is_contiguous()
+        assert grads.numel() % 4 == 0 and grads.data_ptr() % 16 == 0, "flat buffer must be 16-byte granular"
+        self.grads = grads
+        self.n = grads.numel()
+        self.slot = (self.n + 3) // 4 * 4
+        self.algo = ALGO[algo]
+        self.sym = SymmetricMemory(4 * self.slot * 4 + FLAG_BYTES, group)
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
+        self.counters = torch.zeros(4, dtype=torch.int32, device=device)
+        self.world = self.sym.world
+        self.rank = self.sym.rank
+
+    def allreduce_(self, scale: float = 1.0) -> None:
+        """In-place sum (times ``scale``) of ``grads`` over all ranks."""
+        _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
+                [self.epoch], [self.counters], None, self.n, scale, self.algo)
+
+    def allreduce_step_(self, opt: OptArgs, scale: float) -> None:
+        """All-reduce fused with the optimizer update: parameters are updated in the same kernel
+        that pulls the peers' gradients; ``grads`` receives the reduced gradient."""
+        _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
+                [self.epoch], [self.counters], [opt], self.n, scale, self.algo)
+
+    def close(self) -> None:
+        self.sym.close()
+
+
+class LocalEmulation:
+    """``world`` ranks on one GPU: separate "symmetric regions" in local memory, one cooperative
+    launch whose ``blockIdx.y`` is the rank.  Exercises exactly the device code of the multi-GPU
+    path (flags, epochs, buffer parity, fused optimizer) without a second GPU."""
+
+    def __init__(self, world: int, n: int, device: torch.device):
+        self.world, self.n = world, n
+        self.slot = (n + 3) // 4 * 4
+        self.lib = ops.lib()
+        words = 4 * self.slot + FLAG_BYTES // 4
+        self.regions = [torch.zeros(words, dtype=torch.float32, device=device) for _ in range(world)]
+        self.epochs = [torch.zeros(1, dtype=torch.int32, device=device) for _ in range(world)]
+        self.counters = [torch.zeros(4, dtype=torch.int32, device=device) for _ in range(world)]
+
+    def allreduce(self, ins: Sequence[torch.Tensor], outs: Sequence[torch.Tensor], scale: float = 1.0,
+                  algo: str = "auto", opts: Optional[Sequence[OptArgs]] = None) -> None:
+        _launch(self.lib, [r.data_ptr() for r in self.regions], self.slot, 0, self.world, list(ins), list(outs),
+                self.epochs, self.counters, opts, self.n, scale, ALGO[algo])
+
+
+make_opt_args = _opt_args

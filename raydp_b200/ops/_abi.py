@@ -23,6 +23,23 @@ SIGNATURES = {
     "rdp_ingest_indices": (I, [VP, VP, I, I64, I64, VP, I, VP, VP, VP, VP, VP]),
 }
 
+class OptArgs(C.Structure):
+    _fields_ = [("kind", I), ("p", VP), ("m", VP), ("v", VP), ("lr", F), ("beta1", F), ("beta2", F),
+                ("eps", F), ("weight_decay", F), ("momentum", F), ("dampening", F), ("adamw", I),
+                ("nesterov", I), ("lr_ptr", VP), ("step_ptr", VP)]
+
+
+SIGNATURES.update({
+    "rdp_comm_alloc": (I, [C.c_uint64, C.POINTER(VP)]),
+    "rdp_comm_free": (I, [VP]),
+    "rdp_comm_ipc_handle": (I, [VP, VP]),
+    "rdp_comm_ipc_open": (I, [VP, C.POINTER(VP)]),
+    "rdp_comm_ipc_close": (I, [VP]),
+    "rdp_comm_can_access_peer": (I, [I, I]),
+    "rdp_allreduce": (I, [C.POINTER(VP), C.c_uint64, I, I, I, C.POINTER(VP), C.POINTER(VP), C.POINTER(VP),
+                          C.POINTER(VP), C.POINTER(OptArgs), I64, F, I, VP]),
+})
+
 OPTIONAL = {}
 
 

@@ -93,7 +93,7 @@ class FusedMLP:
                 take(f"be{l}", (dims[l + 1],))
         take("Wh", (1, dims[-1]))
         take("bh", (1,))
-        self.n_params = off
+        self.n_params = _round_up(off, 4)      # the all-reduce kernel moves 16-byte vectors
         f32 = dict(dtype=torch.float32, device=device)
         bf16 = dict(dtype=torch.bfloat16, device=device)
         self.params = torch.zeros(self.n_params, **f32)

@@ -520,9 +520,9 @@ class Head:
         if actor is not None:
             env["RAYDP_B200_ACTOR_ID"] = actor.actor_id
         if gpus:
-            env["CUDA_VISIBLE_DEVICES"] = ",".join(str(g) for g in gpus)
-        elif actor is not None and node.total.get("GPU", 0) > 0 and "GPU" not in actor.resources:
-            pass  # CPU actor: leave device visibility alone (it will not touch CUDA)
+            # Assigned device ids are advertised, not enforced through CUDA_VISIBLE_DEVICES: the
+            # peer-memory collectives map every rank's GPU, so all devices must stay visible.
+            env["RAYDP_B200_GPUS"] = ",".join(str(g) for g in gpus)
         env.setdefault("PYTHONUNBUFFERED", "1")
         extra_env = (actor.opts.get("env") if actor else None) or {}
         env.update({k: str(v) for k, v in extra_env.items()})

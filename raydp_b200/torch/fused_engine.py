@@ -118,9 +118,24 @@ class FusedEngine:
         g = self.optimizer.param_groups[0]
         ops.add_scalar(self.step_dev, 1.0)
         scale = 1.0 / self.world
+        adam = self.opt_kind in ("adam", "adamw")
+        if self.reducer is not None and self.reducer.kind == "p2p":
+            # K1/K2: pull the peers' gradients over NVLink, scale, and apply the optimizer in ONE kernel
+            from raydp_b200.comm import make_opt_args
+            if adam:
+                opt = make_opt_args(1, self.fused.params, self.m, self.v, betas=g["betas"], eps=g["eps"],
+                                    weight_decay=g["weight_decay"], adamw=self.opt_kind == "adamw",
+                                    lr_dev=self.lr_dev, step_dev=self.step_dev)
+            else:
+                opt = make_opt_args(2, self.fused.params, self.m if g["momentum"] else None, None,
+                                    weight_decay=g["weight_decay"], momentum=g["momentum"],
+                                    dampening=g["dampening"], nesterov=g["nesterov"],
+                                    lr_dev=self.lr_dev, step_dev=self.step_dev)
+            self.reducer.allreduce_step_(opt, scale)
+            return
         if self.reducer is not None:
-            self.reducer.allreduce_()                      # sum over ranks, in place
-        if self.opt_kind in ("adam", "adamw"):
+            self.reducer.allreduce_()                      # NCCL baseline: sum over ranks, in place
+        if adam:
             b1, b2 = g["betas"]
             ops.adam_step(self.fused.params, self.fused.grads, self.m, self.v, 0.0, b1, b2, g["eps"],
                           g["weight_decay"], 1, scale, self.opt_kind == "adamw", self.lr_dev, self.step_dev)

@@ -113,7 +113,11 @@ class TrainWorker:
 
     def run(self, train_func, config, master_addr, master_port, backend, use_gpu, shards,
             run_name, storage_dir):
-        return run_worker(train_func, config, self.rank, self.world, 0 if use_gpu else self.rank,
+        local_rank = self.rank
+        if use_gpu:
+            gpus = runtime.get_runtime_context().get_assigned_gpus()
+            local_rank = int(gpus[0]) if gpus else self.rank
+        return run_worker(train_func, config, self.rank, self.world, local_rank,
                           master_addr, master_port, backend, use_gpu, shards, run_name, storage_dir)
 
     def shutdown(self):

@@ -1,0 +1,73 @@
+"""Peer-memory all-reduce kernels.
+
+With one GPU the ranks are emulated inside one cooperative launch (blockIdx.y = rank): the same
+device code (flag rounds, epoch parity, fused optimizer) runs, only the "peers" are local.  The
+real multi-process / multi-GPU path is covered by ``test_multigpu_allreduce`` (needs >= 2 GPUs).
+"""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("algo,n", [("one_shot", 48516), ("two_shot", 48516), ("two_shot", 3 * 1024 * 1024 + 8)])
+def test_emulated_allreduce_matches_sum(world, algo, n):
+    from raydp_b200.comm import LocalEmulation
+    dev = torch.device("cuda")
+    emu = LocalEmulation(world, n, dev)
+    for step in range(3):            # several epochs: flag monotonicity and buffer parity
+        g = torch.Generator(device=dev).manual_seed(100 * step + world)
+        ins = [torch.randn(n, device=dev, generator=g) for _ in range(world)]
+        outs = [torch.empty(n, device=dev) for _ in range(world)]
+        ref = torch.stack(ins).sum(0) / world
+        emu.allreduce(ins, outs, scale=1.0 / world, algo=algo)
+        torch.cuda.synchronize()
+        for o in outs:
+            assert torch.allclose(o, ref, rtol=1e-5, atol=1e-5)
+
+
+def test_emulated_allreduce_fused_adam_matches_torch():
+    from raydp_b200.comm import LocalEmulation, make_opt_args
+    dev = torch.device("cuda")
+    world, n = 4, 48516
+    emu = LocalEmulation(world, n, dev)
+    torch.manual_seed(0)
+    p0 = torch.randn(n, device=dev)
+    params = [p0.clone() for _ in range(world)]
+    ms = [torch.zeros(n, device=dev) for _ in range(world)]
+    vs = [torch.zeros(n, device=dev) for _ in range(world)]
+    step_dev = torch.zeros(1, device=dev)
+    lr_dev = torch.full((1,), 1e-2, device=dev)
+    p_ref = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([p_ref], lr=1e-2)
+    for step in range(1, 4):
+        grads = [torch.randn(n, device=dev) for _ in range(world)]
+        p_ref.grad = torch.stack(grads).mean(0)
+        opt.step()
+        step_dev.fill_(float(step))
+        opts = [make_opt_args(1, params[r], ms[r], vs[r], lr_dev=lr_dev, step_dev=step_dev) for r in range(world)]
+        emu.allreduce(grads, grads, scale=1.0 / world, algo="one_shot", opts=opts)
+        torch.cuda.synchronize()
+    for r in range(world):
+        assert torch.allclose(params[r], p_ref.detach(), rtol=1e-5, atol=1e-6)
+        assert torch.equal(params[r], params[0])          # replicas stay bit-identical
+
+
+@pytest.mark.multigpu
+def test_multigpu_allreduce():
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(n_gpus, 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "bench", "allreduce_bench.py"),
+           "--check", "--sizes", "48516,1048576"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "CHECK OK" in out.stdout
