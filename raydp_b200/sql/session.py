@@ -204,7 +204,22 @@ class _Builder:
                     _active_session._conf.set(k, v)
                 return _active_session
             opts = dict(_builder_options)
+            submitted = os.environ.get("RAYDP_SUBMIT_CONF")
+            if submitted:                       # running under raydp-submit
+                import json
+                opts.update(json.loads(submitted))
             opts.update(self._opts)
+            if opts.get("spark.master", "") == "ray":
+                # master URL "ray" = create the app master here (reference
+                # RayCoarseGrainedSchedulerBackend.scala:84-96): delegate to init_spark
+                from raydp_b200.context import init_spark
+                extra = {k: v for k, v in opts.items() if k not in (
+                    "spark.master", "spark.app.name", "spark.executor.instances", "spark.executor.cores",
+                    "spark.executor.memory")}
+                return init_spark(opts.get("spark.app.name", "raydp-submit"),
+                                  int(opts.get("spark.executor.instances", "1")),
+                                  int(opts.get("spark.executor.cores", "1")),
+                                  opts.get("spark.executor.memory", "1g"), configs=extra)
             _builder_options.update(self._opts)
             session = SparkSession(opts)
             _active_session = session
