@@ -219,11 +219,45 @@ allreduce_kernel(const __grid_constant__ ArParams P) {
   }
 }
 
+// One flag round between all ranks (slot 2 of the flag area): everything this GPU wrote before the
+// barrier kernel started -- including peer stores of earlier kernels on the stream -- is ordered
+// before the flag, and the kernel returns only after every rank has signalled the same epoch.
+struct BarrierParams {
+  uint32_t* flags[kMaxRanks];
+  int rank, world;
+  uint32_t* epoch;
+};
+
+__global__ void barrier_kernel(const __grid_constant__ BarrierParams p) {
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
+  __threadfence_system();
+  if (int(threadIdx.x) < p.world) {
+    st_release_sys(p.flags[threadIdx.x] + 2 * kMaxRanks + p.rank, e);
+    const uint32_t* f = p.flags[p.rank] + 2 * kMaxRanks + threadIdx.x;
+    while (int32_t(ld_acquire_sys(f) - e) < 0) {
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *p.epoch = e;
+}
+
 }  // namespace rdp
 
 using namespace rdp;
 
 extern "C" {
+
+int rdp_comm_barrier(void* const* bases, uint64_t flag_offset_bytes, int rank, int world, uint32_t* epoch,
+                     void* stream) {
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks, "rdp_comm_barrier: world=%d", world);
+  BarrierParams p;
+  for (int q = 0; q < world; ++q)
+    p.flags[q] = reinterpret_cast<uint32_t*>(static_cast<char*>(bases[q]) + flag_offset_bytes);
+  p.rank = rank; p.world = world; p.epoch = epoch;
+  barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
 
 // ---- symmetric memory plumbing (host) -----------------------------------------------------------
 int rdp_comm_alloc(uint64_t bytes, void** out) {

@@ -1,0 +1,275 @@
+// K4 / K9 and the DLRM loss (workload B of SURVEY.md section 2.6: reference
+// examples/pytorch_dlrm.ipynb cell 9 -- MultiTableEmbeddings, DotInteraction -- and cell 14).
+//
+// K4  embedding lookup fused with the model-parallel all-to-all.  Tables are sharded table-wise
+//     across ranks.  The owner of a table reads the *requesting* rank's index column straight out
+//     of that rank's memory, gathers the rows from its local shard and stores them directly into
+//     the requesting rank's feature slab [B, 1+T, D] -- index dispatch, gather and combine are one
+//     kernel and there are no staging buffers (`idx` / `feats` pointers of remote ranks are
+//     NVLink peer mappings; with one rank they are simply local).  Backward mirrors it: the owner
+//     pulls the gradient rows from every rank's dfeats slab and applies the sparse SGD update
+//     with fp32 atomics (duplicate indices accumulate), so the embedding gradient never exists as
+//     a tensor (reference: nn.Embedding(sparse=True) + DDP, which NCCL cannot all-reduce at all).
+// K9  dot interaction: per sample the 27x27 Gram of the feature vectors, lower triangle (351
+//     values, row-major i > j like torch.tril_indices(offset=-1)), concatenated after the dense
+//     vector and zero-padded to 384 -- written in the layout the top-MLP GEMM reads through TMA.
+#include "common.cuh"
+#include "raydp_b200.h"
+
+namespace rdp {
+
+constexpr int kMaxSrc = 8;
+constexpr int kMaxLocalTables = 32;
+
+struct EmbParams {
+  float* table[kMaxLocalTables];        // local shard: table[t] is [rows_t, D] fp32
+  int slot[kMaxLocalTables];            // global feature slot (1-based row inside the slab)
+  int col[kMaxLocalTables];             // column of this table inside the index matrix
+  int n_tables;
+  const int* idx[kMaxSrc];              // idx[s]: rank s' index matrix [B_s, idx_ld] int32
+  __nv_bfloat16* feats[kMaxSrc];        // feats[s]: rank s' slab [B_s, S, D] (fwd: written, bwd: read)
+  int batch[kMaxSrc];
+  int n_src;
+  int idx_ld, S, D;
+  float scale;                          // bwd: -lr * grad_scale
+};
+
+// one warp per (source rank, sample, local table) row; lanes cover D in steps of 32
+__global__ void __launch_bounds__(256)
+embedding_fwd_kernel(const __grid_constant__ EmbParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  int64_t total = 0;
+  for (int s = 0; s < p.n_src; ++s) total += int64_t(p.batch[s]) * p.n_tables;
+  for (int64_t w = warp; w < total; w += nwarps) {
+    int64_t rem = w;
+    int s = 0;
+    while (rem >= int64_t(p.batch[s]) * p.n_tables) { rem -= int64_t(p.batch[s]) * p.n_tables; ++s; }
+    const int b = int(rem / p.n_tables), t = int(rem % p.n_tables);
+    const int row = p.idx[s][size_t(b) * p.idx_ld + p.col[t]];           // peer load (tiny)
+    const float* src = p.table[t] + size_t(row) * p.D;
+    __nv_bfloat16* dst = p.feats[s] + (size_t(b) * p.S + p.slot[t]) * p.D; // peer store
+    for (int d = lane; d < p.D; d += 32) dst[d] = __float2bfloat16_rn(__ldg(src + d));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+embedding_bwd_sgd_kernel(const __grid_constant__ EmbParams p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * int64_t(blockDim.x) + threadIdx.x) >> 5;
+  const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
+  int64_t total = 0;
+  for (int s = 0; s < p.n_src; ++s) total += int64_t(p.batch[s]) * p.n_tables;
+  for (int64_t w = warp; w < total; w += nwarps) {
+    int64_t rem = w;
+    int s = 0;
+    while (rem >= int64_t(p.batch[s]) * p.n_tables) { rem -= int64_t(p.batch[s]) * p.n_tables; ++s; }
+    const int b = int(rem / p.n_tables), t = int(rem % p.n_tables);
+    const int row = p.idx[s][size_t(b) * p.idx_ld + p.col[t]];
+    const __nv_bfloat16* g = p.feats[s] + (size_t(b) * p.S + p.slot[t]) * p.D;   // peer load
+    float* dst = p.table[t] + size_t(row) * p.D;
+    for (int d = lane; d < p.D; d += 32) atomicAdd(dst + d, p.scale * __bfloat162float(g[d]));
+  }
+}
+
+// ---- dot interaction ---------------------------------------------------------------------------
+constexpr int kMaxS = 32;
+
+__global__ void __launch_bounds__(128)
+dot_interaction_fwd_kernel(const __nv_bfloat16* __restrict__ feats, __nv_bfloat16* __restrict__ out, int B,
+                           int S, int D, int ld_out) {
+  extern __shared__ float sh[];            // [S][D + 1]
+  const int n_pairs = S * (S - 1) / 2;
+  const int width = D + n_pairs;
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    const __nv_bfloat16* f = feats + size_t(b) * S * D;
+    for (int i = threadIdx.x; i < S * D; i += blockDim.x) sh[(i / D) * (D + 1) + (i % D)] = __bfloat162float(f[i]);
+    __syncthreads();
+    __nv_bfloat16* o = out + size_t(b) * ld_out;
+    for (int c = threadIdx.x; c < ld_out; c += blockDim.x) {
+      float v = 0.f;
+      if (c < D) {
+        v = sh[c];                                       // dense vector = feature row 0
+      } else if (c < width) {
+        const int q = c - D;                             // pair (i, j), i > j, q = i (i - 1) / 2 + j
+        int i = int((1.f + sqrtf(1.f + 8.f * float(q))) * 0.5f);
+        while (i * (i - 1) / 2 > q) --i;
+        while ((i + 1) * i / 2 <= q) ++i;
+        const int j = q - i * (i - 1) / 2;
+        const float* fi = sh + i * (D + 1);
+        const float* fj = sh + j * (D + 1);
+#pragma unroll 8
+        for (int d = 0; d < D; ++d) v = fmaf(fi[d], fj[d], v);
+      }
+      o[c] = __float2bfloat16_rn(v);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+dot_interaction_bwd_kernel(const __nv_bfloat16* __restrict__ feats, const __nv_bfloat16* __restrict__ dout,
+                           __nv_bfloat16* __restrict__ dfeats, int B, int S, int D, int ld_out) {
+  extern __shared__ float sh[];            // feats [S][D + 1] | dpair [S][S] (symmetric, zero diagonal)
+  float* sf = sh;
+  float* sp = sh + S * (D + 1);
+  const int n_pairs = S * (S - 1) / 2;
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    const __nv_bfloat16* f = feats + size_t(b) * S * D;
+    const __nv_bfloat16* go = dout + size_t(b) * ld_out;
+    for (int i = threadIdx.x; i < S * D; i += blockDim.x) sf[(i / D) * (D + 1) + (i % D)] = __bfloat162float(f[i]);
+    for (int i = threadIdx.x; i < S * S; i += blockDim.x) sp[i] = 0.f;
+    __syncthreads();
+    for (int q = threadIdx.x; q < n_pairs; q += blockDim.x) {
+      int i = int((1.f + sqrtf(1.f + 8.f * float(q))) * 0.5f);
+      while (i * (i - 1) / 2 > q) --i;
+      while ((i + 1) * i / 2 <= q) ++i;
+      const int j = q - i * (i - 1) / 2;
+      const float g = __bfloat162float(go[D + q]);
+      sp[i * S + j] = g;
+      sp[j * S + i] = g;
+    }
+    __syncthreads();
+    __nv_bfloat16* df = dfeats + size_t(b) * S * D;
+    for (int e = threadIdx.x; e < S * D; e += blockDim.x) {
+      const int i = e / D, d = e % D;
+      float v = (i == 0) ? __bfloat162float(go[d]) : 0.f;     // dense passthrough
+      const float* pr = sp + i * S;
+#pragma unroll 9
+      for (int j = 0; j < S; ++j) v = fmaf(pr[j], sf[j * (D + 1) + d], v);
+      df[e] = __float2bfloat16_rn(v);
+    }
+    __syncthreads();
+  }
+}
+
+// ---- BCE-with-logits on a strided logit column -------------------------------------------------
+__global__ void __launch_bounds__(256)
+bce_logits_kernel(const __nv_bfloat16* __restrict__ logits, int ld, const float* __restrict__ target,
+                  __nv_bfloat16* __restrict__ dlogits, int ld_d, int width_d, float* accum, int B, float grad_scale,
+                  float* dbias) {
+  float s_loss = 0.f, s_corr = 0.f, s_cnt = 0.f, s_dl = 0.f;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < B; r += gridDim.x * blockDim.x) {
+    const float y = __bfloat162float(logits[size_t(r) * ld]);
+    const float t = target[r];
+    s_loss += fmaxf(y, 0.f) - y * t + log1pf(__expf(-fabsf(y)));
+    s_corr += ((y >= 0.f) == (t >= 0.5f)) ? 1.f : 0.f;
+    s_cnt += 1.f;
+    if (dlogits != nullptr) {
+      const float sig = 1.f / (1.f + __expf(-y));
+      __nv_bfloat16* d = dlogits + size_t(r) * ld_d;
+      const __nv_bfloat16 dl = __float2bfloat16_rn((sig - t) * grad_scale);
+      d[0] = dl;
+      s_dl += __bfloat162float(dl);
+      for (int c = 1; c < width_d; ++c) d[c] = __float2bfloat16_rn(0.f);
+    }
+  }
+  s_loss = warp_sum(s_loss); s_corr = warp_sum(s_corr); s_cnt = warp_sum(s_cnt); s_dl = warp_sum(s_dl);
+  __shared__ float red[8][4];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { red[wid][0] = s_loss; red[wid][1] = s_corr; red[wid][2] = s_cnt; red[wid][3] = s_dl; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, c = 0.f, n = 0.f, dl = 0.f;
+    for (int w = 0; w < 8; ++w) { a += red[w][0]; c += red[w][1]; n += red[w][2]; dl += red[w][3]; }
+    if (dbias != nullptr) atomicAdd(dbias, dl);
+    atomicAdd(&accum[0], a);
+    atomicAdd(&accum[3], n);
+    atomicAdd(&accum[4], c);
+    atomicAdd(&accum[5], a / float(B));
+  }
+}
+
+static int fill_emb(EmbParams& p, float* const* tables, const int* slots, const int* cols, int n_tables,
+                    const int* const* idx, void* const* feats, const int* batch, int n_src, int idx_ld, int S, int D) {
+  RDP_REQUIRE(n_tables >= 0 && n_tables <= kMaxLocalTables, "embedding: at most %d local tables (got %d)",
+              kMaxLocalTables, n_tables);
+  RDP_REQUIRE(n_src >= 1 && n_src <= kMaxSrc, "embedding: n_src=%d (max %d)", n_src, kMaxSrc);
+  for (int t = 0; t < n_tables; ++t) { p.table[t] = tables[t]; p.slot[t] = slots[t]; p.col[t] = cols[t]; }
+  p.n_tables = n_tables;
+  for (int s = 0; s < n_src; ++s) {
+    p.idx[s] = idx[s];
+    p.feats[s] = static_cast<__nv_bfloat16*>(feats[s]);
+    p.batch[s] = batch[s];
+  }
+  p.n_src = n_src; p.idx_ld = idx_ld; p.S = S; p.D = D; p.scale = 0.f;
+  return 0;
+}
+
+}  // namespace rdp
+
+using namespace rdp;
+
+extern "C" {
+
+int rdp_embedding_fwd(float* const* tables, const int* slots, const int* cols, int n_tables, const int* const* idx,
+                      void* const* feats, const int* batch, int n_src, int idx_ld, int S, int D, void* stream) {
+  if (n_tables == 0) return 0;
+  EmbParams p;
+  int rc = fill_emb(p, tables, slots, cols, n_tables, idx, feats, batch, n_src, idx_ld, S, D);
+  if (rc) return rc;
+  int64_t rows = 0;
+  for (int s = 0; s < n_src; ++s) rows += int64_t(batch[s]) * n_tables;
+  int grid = int((rows + 7) / 8);
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  if (grid < 1) grid = 1;
+  embedding_fwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_embedding_bwd_sgd(float* const* tables, const int* slots, const int* cols, int n_tables,
+                          const int* const* idx, void* const* dfeats, const int* batch, int n_src, int idx_ld,
+                          int S, int D, float lr, float grad_scale, void* stream) {
+  if (n_tables == 0) return 0;
+  EmbParams p;
+  int rc = fill_emb(p, tables, slots, cols, n_tables, idx, dfeats, batch, n_src, idx_ld, S, D);
+  if (rc) return rc;
+  p.scale = -lr * grad_scale;
+  int64_t rows = 0;
+  for (int s = 0; s < n_src; ++s) rows += int64_t(batch[s]) * n_tables;
+  int grid = int((rows + 7) / 8);
+  if (grid > num_sms() * 8) grid = num_sms() * 8;
+  if (grid < 1) grid = 1;
+  embedding_bwd_sgd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, int ld_out, void* stream) {
+  RDP_REQUIRE(S <= kMaxS && D <= 128 && ld_out >= D + S * (S - 1) / 2, "dot_interaction: bad shape S=%d D=%d ld=%d", S, D, ld_out);
+  int grid = B < num_sms() * 8 ? B : num_sms() * 8;
+  dot_interaction_fwd_kernel<<<grid, 128, S * (D + 1) * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(feats), static_cast<__nv_bfloat16*>(out), B, S, D, ld_out);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_dot_interaction_bwd(const void* feats, const void* dout, void* dfeats, int B, int S, int D, int ld_out,
+                            void* stream) {
+  RDP_REQUIRE(S <= kMaxS && D <= 128, "dot_interaction: bad shape S=%d D=%d", S, D);
+  int grid = B < num_sms() * 4 ? B : num_sms() * 4;
+  const size_t smem = (S * (D + 1) + S * S) * sizeof(float);
+  dot_interaction_bwd_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(feats), static_cast<const __nv_bfloat16*>(dout),
+      static_cast<__nv_bfloat16*>(dfeats), B, S, D, ld_out);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_bce_logits(const void* logits, int ld, const float* target, void* dlogits, int ld_d, int width_d,
+                   float* accum, int B, float grad_scale, float* dbias, void* stream) {
+  int grid = (B + 255) / 256;
+  if (grid > num_sms() * 2) grid = num_sms() * 2;
+  bce_logits_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(logits), ld, target, static_cast<__nv_bfloat16*>(dlogits), ld_d, width_d,
+      accum, B, grad_scale, dbias);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// One flag round between all ranks on `stream` (used between the phases of the embedding exchange).
+// Implemented in csrc/comm/p2p_allreduce.cu.
+
+}  // extern "C"

@@ -833,6 +833,7 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
     if (stats_mode == 1 && !use_aux) return launch_fast<1, false>(ta, fb, fc, fx, f, cs);
     if (stats_mode == 2) return launch_fast<2, true>(ta, fb, fc, fx, f, cs);
     if (stats_mode == 0 && use_aux) return launch_fast<0, true>(ta, fb, fc, fx, f, cs);
+    if (stats_mode == 1 && use_aux) return launch_fast<1, true>(ta, fb, fc, fx, f, cs);   // ReLU-masked dgrad + column sums
   }
   gemm_tn_kernel<<<grid, kGemmThreads, smem, cs>>>(ta, tb, p);
   RDP_CHECK_CUDA(cudaGetLastError());

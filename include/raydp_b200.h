@@ -110,6 +110,32 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
                   uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,
                   int algo, void* stream);
 
+// One flag round between all ranks on `stream`; the flag area (>= 256 bytes, zero-initialised) sits at
+// bases[q] + flag_offset_bytes in every rank's symmetric region; `epoch` is a local device uint32.
+int rdp_comm_barrier(void* const* bases, uint64_t flag_offset_bytes, int rank, int world, uint32_t* epoch,
+                     void* stream);
+
+// ---- K4: embedding lookup fused with the model-parallel all-to-all (nn.Embedding + [absent] a2a) ---
+// tables[t]: local fp32 [rows, D]; slots[t]: feature row (1..S-1) in the slab; cols[t]: column in the
+// index matrix.  idx[s] / feats[s]: source rank s' int32 index matrix [batch[s], idx_ld] and bf16 slab
+// [batch[s], S, D] (peer mappings for remote ranks).  Host arrays; copied into the launch parameters.
+int rdp_embedding_fwd(float* const* tables, const int* slots, const int* cols, int n_tables, const int* const* idx,
+                      void* const* feats, const int* batch, int n_src, int idx_ld, int S, int D, void* stream);
+// Pull gradient rows from every rank's dfeats slab and apply table[row] += -lr * grad_scale * g.
+int rdp_embedding_bwd_sgd(float* const* tables, const int* slots, const int* cols, int n_tables,
+                          const int* const* idx, void* const* dfeats, const int* batch, int n_src, int idx_ld,
+                          int S, int D, float lr, float grad_scale, void* stream);
+// ---- K9: DLRM dot interaction (torch.bmm + tril gather + cat + pad) ---------------------------------
+// feats [B, S, D] bf16 -> out [B, ld_out] bf16 = [row 0 (D) | S(S-1)/2 pair dots, i > j row-major | 0 pad].
+int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, int ld_out, void* stream);
+int rdp_dot_interaction_bwd(const void* feats, const void* dout, void* dfeats, int B, int S, int D, int ld_out,
+                            void* stream);
+// BCEWithLogits(mean) on column 0 of a bf16 logit matrix; writes dlogits[:, 0] (other width_d-1 columns 0);
+// accum[0] += loss sum, [3] += count, [4] += correct, [5] += batch-mean loss.  dlogits may be null (eval);
+// dbias (optional, +=) receives sum(dlogits[:, 0]), the bias gradient of the last Linear.
+int rdp_bce_logits(const void* logits, int ld, const float* target, void* dlogits, int ld_d, int width_d,
+                   float* accum, int B, float grad_scale, float* dbias, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -188,3 +188,48 @@ def ingest_indices(col_ptrs, dtype_codes, rows, src_offset, table_rows, out: tor
     cb = (ctypes.c_int * max(1, nc))(*[c[1] for c in crosses])
     cr = (ctypes.c_int * max(1, nc))(*[c[2] for c in crosses])
     _check(lib().rdp_ingest_indices(ptrs, codes, n, rows, src_offset, trows, nc, ca, cb, cr, _ptr(out), _stream()))
+
+
+# ---- DLRM: embedding exchange, dot interaction, BCE loss ------------------------------------------
+def _vp_arr(ptrs):
+    return (ctypes.c_void_p * max(1, len(ptrs)))(*[ctypes.c_void_p(int(x)) for x in ptrs])
+
+
+def _i_arr(vals):
+    return (ctypes.c_int * max(1, len(vals)))(*[int(v) for v in vals])
+
+
+def embedding_fwd(table_ptrs, slots, cols, idx_ptrs, feats_ptrs, batches, idx_ld: int, S: int, D: int) -> None:
+    _check(lib().rdp_embedding_fwd(_vp_arr(table_ptrs), _i_arr(slots), _i_arr(cols), len(table_ptrs),
+                                   _vp_arr(idx_ptrs), _vp_arr(feats_ptrs), _i_arr(batches), len(idx_ptrs),
+                                   idx_ld, S, D, _stream()))
+
+
+def embedding_bwd_sgd(table_ptrs, slots, cols, idx_ptrs, dfeats_ptrs, batches, idx_ld: int, S: int, D: int,
+                      lr: float, grad_scale: float) -> None:
+    _check(lib().rdp_embedding_bwd_sgd(_vp_arr(table_ptrs), _i_arr(slots), _i_arr(cols), len(table_ptrs),
+                                       _vp_arr(idx_ptrs), _vp_arr(dfeats_ptrs), _i_arr(batches), len(idx_ptrs),
+                                       idx_ld, S, D, float(lr), float(grad_scale), _stream()))
+
+
+def dot_interaction_fwd(feats: torch.Tensor, out: torch.Tensor) -> None:
+    B, S, D = feats.shape
+    _check(lib().rdp_dot_interaction_fwd(_ptr(feats), _ptr(out), B, S, D, _pitch(out), _stream()))
+
+
+def dot_interaction_bwd(feats: torch.Tensor, dout: torch.Tensor, dfeats: torch.Tensor) -> None:
+    B, S, D = feats.shape
+    _check(lib().rdp_dot_interaction_bwd(_ptr(feats), _ptr(dout), _ptr(dfeats), B, S, D, _pitch(dout), _stream()))
+
+
+def bce_logits(logits: torch.Tensor, target: torch.Tensor, dlogits: Optional[torch.Tensor], accum: torch.Tensor,
+               grad_scale: float, dbias: Optional[torch.Tensor] = None) -> None:
+    B = logits.shape[0]
+    _check(lib().rdp_bce_logits(_ptr(logits), _pitch(logits), _ptr(target), _ptr(dlogits),
+                                _pitch(dlogits) if dlogits is not None else 0,
+                                dlogits.shape[1] if dlogits is not None else 0, _ptr(accum), B, float(grad_scale),
+                                _ptr(dbias), _stream()))
+
+
+def comm_barrier(bases, flag_offset: int, rank: int, world: int, epoch: torch.Tensor) -> None:
+    _check(lib().rdp_comm_barrier(_vp_arr(bases), int(flag_offset), rank, world, _ptr(epoch), _stream()))

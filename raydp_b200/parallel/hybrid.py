@@ -1,0 +1,260 @@
+"""Hybrid parallel DLRM: dense layers data-parallel, embedding tables model-parallel.
+
+New capability relative to the reference (the reference keeps all 26 tables
+replicated under DDP, ``examples/pytorch_dlrm.ipynb`` cell 9; ``BASELINE.json`` config 3 asks for
+table-wise sharding with the all-to-all fused into the lookup).
+
+* Tables are dealt round-robin to ranks.  Forward: the owner reads each requesting rank's index
+  column over NVLink, gathers from its shard and stores rows straight into that rank's feature slab
+  (``rdp_embedding_fwd``); backward: the owner pulls gradient rows from every rank's slab and applies
+  sparse SGD (``rdp_embedding_bwd_sgd``).  Three flag rounds per step delimit the phases.
+* Bottom / top MLPs run on the tcgen05 GEMM with bias+ReLU epilogues; the backward dgrad GEMM applies
+  the ReLU mask in its epilogue and its tensor-core column sums are the bias gradients.
+* Interaction: ``rdp_dot_interaction_fwd/bwd``; loss: ``rdp_bce_logits``.
+* Dense gradients: peer-memory all-reduce fused with SGD (``raydp_b200.comm``), or a local SGD step.
+
+``LocalWorld`` runs W ranks sequentially on one GPU with all "peer" pointers local: the same
+kernels and the same sharding logic, used by the tests where only one GPU exists.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from raydp_b200 import ops
+from raydp_b200.models.dlrm import DLRMSpec
+
+
+def _r8(v: int) -> int:
+    return (v + 7) // 8 * 8
+
+
+class FusedDLRM:
+    """One rank's share of the model plus its workspaces."""
+
+    def __init__(self, spec: DLRMSpec, batch: int, device: torch.device, rank: int = 0, world: int = 1):
+        self.spec, self.B, self.device, self.rank, self.world = spec, int(batch), device, rank, world
+        D, T = spec.embedding_dim, len(spec.table_sizes)
+        self.D, self.T, self.S = D, T, T + 1
+        self.kpad = _r8(spec.num_dense)
+        self.inter_w = _r8(self.S * (self.S - 1) // 2 + D + 1)
+        f32 = dict(dtype=torch.float32, device=device)
+        bf = dict(dtype=torch.bfloat16, device=device)
+        # ---- sharded tables ------------------------------------------------------------------
+        self.owned = [t for t in range(T) if t % world == rank]
+        self.tables: Dict[int, torch.Tensor] = {t: torch.zeros(spec.table_sizes[t], D, **f32) for t in self.owned}
+        # ---- dense parameters: flat fp32 [W, b] per layer, bottom then top --------------------
+        bdims = [spec.num_dense] + list(spec.bottom)
+        tdims = [self.inter_w] + list(spec.top)
+        self.layers = [("bottom", i, bdims[i], bdims[i + 1]) for i in range(len(spec.bottom))] + \
+                      [("top", i, tdims[i], tdims[i + 1]) for i in range(len(spec.top))]
+        self.nb = len(spec.bottom)
+        off, self.slices = 0, []
+        for _, _, k, n in self.layers:
+            self.slices.append((off, off + n * k, off + n * k + n))
+            off += n * k + n
+        self.n_params = (off + 3) // 4 * 4
+        self.params = torch.zeros(self.n_params, **f32)
+        self.grads = torch.zeros(self.n_params, **f32)
+        self.momentum_buf: Optional[torch.Tensor] = None
+        # bf16 operand copies (K padded to 8 for TMA pitch; last layer padded to 16 outputs)
+        self.w_bf, self.w_t, self.npad = [], [], []
+        for li, (_, _, k, n) in enumerate(self.layers):
+            npad = n if n % 16 == 0 else _r8(max(n, 16) + 8) // 16 * 16
+            kp = _r8(k)
+            self.npad.append(npad)
+            self.w_bf.append(torch.zeros(npad, kp, **bf))
+            self.w_t.append(torch.zeros(kp, npad, **bf))
+        self.bias_pad = [torch.zeros(np_, **f32) for np_ in self.npad]
+        # ---- activations ---------------------------------------------------------------------
+        B = self.B
+        self.feats = torch.zeros(B, self.S, D, **bf)
+        self.dfeats = torch.zeros(B, self.S, D, **bf)
+        self.idx = torch.zeros(B, T, dtype=torch.int32, device=device)
+        self.act = [torch.zeros(B, self.npad[i], **bf) for i in range(len(self.layers))]
+        self.dact = [torch.zeros(B, self.npad[i], **bf) for i in range(len(self.layers))]
+        self.zint = torch.zeros(B, self.inter_w, **bf)
+        self.dzint = torch.zeros(B, self.inter_w, **bf)
+        self.stats = [torch.zeros(2, max(self.npad[i], 64), **f32) for i in range(len(self.layers))]
+        self.stats_bottom_last = torch.zeros(2, max(D, 8), **f32)
+        self.accum = torch.zeros(8, **f32)
+        self.ones32 = torch.ones(D, **f32)
+        self.zeros32 = torch.zeros(D, **f32)
+        # peers (filled by the owner of the world: symmetric memory or LocalWorld)
+        self.peer_idx: List[int] = [self.idx.data_ptr()]
+        self.peer_feats: List[int] = [self.feats.data_ptr()]
+        self.peer_dfeats: List[int] = [self.dfeats.data_ptr()]
+        self.peer_batch: List[int] = [B]
+
+    # ------------------------------------------------------------------ parameters
+    def weight(self, li: int, grad: bool = False) -> torch.Tensor:
+        _, _, k, n = self.layers[li]
+        a, b, _ = self.slices[li]
+        return (self.grads if grad else self.params)[a:b].view(n, k)
+
+    def bias(self, li: int, grad: bool = False) -> torch.Tensor:
+        _, b, c = self.slices[li]
+        return (self.grads if grad else self.params)[b:c]
+
+    def load_from_module(self, module) -> None:
+        with torch.no_grad():
+            lins = list(module.bottom) + list(module.top)
+            for li, lin in enumerate(lins):
+                self.weight(li).copy_(lin.weight)
+                self.bias(li).copy_(lin.bias)
+            for t in self.owned:
+                self.tables[t].copy_(module.embeddings[t].weight)
+
+    def dense_state_dict(self) -> Dict[str, torch.Tensor]:
+        out = {}
+        for li, (part, i, _, _) in enumerate(self.layers):
+            out[f"{part}.{i}.weight"] = self.weight(li).detach().cpu().clone()
+            out[f"{part}.{i}.bias"] = self.bias(li).detach().cpu().clone()
+        return out
+
+    def table_state_dict(self) -> Dict[str, torch.Tensor]:
+        return {f"embeddings.{t}.weight": w.detach().cpu().clone() for t, w in self.tables.items()}
+
+    # ------------------------------------------------------------------ pieces of a step
+    def _refresh_weights(self) -> None:
+        for li in range(len(self.layers)):
+            _, _, k, n = self.layers[li]
+            ops.cast_weight(self.weight(li), self.w_bf[li], self.w_t[li])
+            self.bias_pad[li][:n].copy_(self.bias(li))
+
+    def _gemm_fwd(self, li: int, x: torch.Tensor, out: torch.Tensor, relu: bool) -> None:
+        ops.gemm_tn(x, self.w_bf[li], out, bias=self.bias_pad[li], relu=relu, n=self.npad[li],
+                    k=self.w_bf[li].shape[1])
+
+    def bottom_forward(self, dense: torch.Tensor) -> None:
+        """dense [B, kpad] bf16 -> feats[:, 0, :]"""
+        B = dense.shape[0]
+        x = dense
+        for li in range(self.nb):
+            last = li == self.nb - 1
+            out = self.feats.view(self.B, self.S * self.D)[:B, :self.D] if last else self.act[li][:B]
+            self._gemm_fwd(li, x, out, relu=True)
+            x = out
+
+    def embedding_forward(self) -> None:
+        """Push rows of the tables this rank owns into every rank's feature slab."""
+        ops.embedding_fwd([self.tables[t].data_ptr() for t in self.owned], [t + 1 for t in self.owned],
+                          self.owned, self.peer_idx, self.peer_feats, self.peer_batch, self.T, self.S, self.D)
+
+    def top_forward_backward(self, target: Optional[torch.Tensor], B: int, train: bool) -> torch.Tensor:
+        ops.dot_interaction_fwd(self.feats[:B], self.zint[:B])
+        x = self.zint[:B]
+        n_layers = len(self.layers)
+        for li in range(self.nb, n_layers):
+            last = li == n_layers - 1
+            self._gemm_fwd(li, x, self.act[li][:B], relu=not last)
+            x = self.act[li][:B]
+        logits = self.act[-1][:B]
+        if not train:
+            if target is not None:
+                ops.bce_logits(logits, target, None, self.accum, 0.0)
+            return logits
+        self.grads.zero_()
+        dl = self.dact[-1][:B]
+        ops.bce_logits(logits, target, dl, self.accum, 1.0 / B, self.bias(n_layers - 1, True))
+        # ---- top backward ----
+        for li in range(n_layers - 1, self.nb - 1, -1):
+            inp = self.zint[:B] if li == self.nb else self.act[li - 1][:B]
+            g = self.dact[li][:B]
+            _, _, k, n = self.layers[li]
+            ops.gemm_wgrad(g, inp, self.weight(li, True), mw=n, nw=k)
+            if li > self.nb:
+                prev = li - 1
+                self.stats[prev].zero_()
+                # dgrad with the ReLU mask of the previous activation fused in the epilogue; the
+                # tensor-core column sums of the result are that layer's bias gradient
+                ops.gemm_tn(g, self.w_t[li], self.dact[prev][:B], aux=self.act[prev][:B], aux_relu_mask=True,
+                            stats_mode=1, stats=self.stats[prev], n=self.npad[prev], k=self.npad[li])
+                self.bias(prev, True).copy_(self.stats[prev][0, :self.layers[prev][3]])
+            else:
+                ops.gemm_tn(g, self.w_t[li], self.dzint[:B], n=self.inter_w, k=self.npad[li])
+        ops.dot_interaction_bwd(self.feats[:B], self.dzint[:B], self.dfeats[:B])
+        return logits
+
+    def embedding_backward(self, lr: float, grad_scale: float) -> None:
+        ops.embedding_bwd_sgd([self.tables[t].data_ptr() for t in self.owned], [t + 1 for t in self.owned],
+                              self.owned, self.peer_idx, self.peer_dfeats, self.peer_batch, self.T, self.S, self.D,
+                              lr, grad_scale)
+
+    def bottom_backward(self, dense: torch.Tensor) -> None:
+        B = dense.shape[0]
+        last = self.nb - 1
+        pitch = self.S * self.D
+        dy = self.dfeats.view(self.B, pitch)[:B, :self.D]
+        z = self.feats.view(self.B, pitch)[:B, :self.D]
+        # ReLU backward of the bottom output (in place on the slab view) + its bias gradient
+        ops.bn_relu_bwd(dy, z, dy, self.stats_bottom_last, self.zeros32, self.ones32, self.ones32,
+                        self.zeros32, self.zeros32, self.bias(last, True), has_bn=False)
+        g = dy
+        for li in range(last, -1, -1):
+            inp = dense if li == 0 else self.act[li - 1][:B]
+            _, _, k, n = self.layers[li]
+            ops.gemm_wgrad(g, inp, self.weight(li, True), mw=n, nw=k)
+            if li > 0:
+                prev = li - 1
+                self.stats[prev].zero_()
+                ops.gemm_tn(g, self.w_t[li], self.dact[prev][:B], aux=self.act[prev][:B], aux_relu_mask=True,
+                            stats_mode=1, stats=self.stats[prev], n=self.npad[prev],
+                            k=self.npad[li] if li != last else self.D)
+                self.bias(prev, True).copy_(self.stats[prev][0, :self.layers[prev][3]])
+                g = self.dact[prev][:B]
+
+    def sgd(self, lr: float, scale: float = 1.0, momentum: float = 0.0, weight_decay: float = 0.0) -> None:
+        if momentum and self.momentum_buf is None:
+            self.momentum_buf = torch.zeros_like(self.params)
+        ops.sgd_step(self.params, self.grads, self.momentum_buf if momentum else None, lr, momentum, 0.0,
+                     weight_decay, False, False, scale)
+
+
+class LocalWorld:
+    """W model-parallel ranks on one device, stepped in lock step (single-GPU tests / emulation)."""
+
+    def __init__(self, spec: DLRMSpec, batch_per_rank: int, world: int, device: torch.device):
+        self.world = world
+        self.ranks = [FusedDLRM(spec, batch_per_rank, device, r, world) for r in range(world)]
+        for r in self.ranks:
+            r.peer_idx = [q.idx.data_ptr() for q in self.ranks]
+            r.peer_feats = [q.feats.data_ptr() for q in self.ranks]
+            r.peer_dfeats = [q.dfeats.data_ptr() for q in self.ranks]
+            r.peer_batch = [q.B for q in self.ranks]
+
+    def load_from_module(self, module) -> None:
+        for r in self.ranks:
+            r.load_from_module(module)
+
+    def train_step(self, dense: Sequence[torch.Tensor], idx: Sequence[torch.Tensor],
+                   target: Sequence[torch.Tensor], lr: float) -> None:
+        W = self.world
+        for r, d, i in zip(self.ranks, dense, idx):
+            r._refresh_weights()
+            r.idx[:i.shape[0]].copy_(i)
+            r.bottom_forward(d)
+        for r in self.ranks:                       # (flag round 1 in the multi-GPU engine)
+            r.embedding_forward()
+        for r, d, t in zip(self.ranks, dense, target):   # (flag round 2)
+            r.top_forward_backward(t, d.shape[0], True)
+        for r in self.ranks:                       # (flag round 3)
+            r.embedding_backward(lr, 1.0 / W)
+        for r, d in zip(self.ranks, dense):
+            r.bottom_backward(d)
+        # dense gradients: average over ranks (all-reduce), identical SGD on every replica
+        total = torch.stack([r.grads for r in self.ranks]).sum(0)
+        for r in self.ranks:
+            r.grads.copy_(total)
+            r.sgd(lr, 1.0 / W)
+
+    def predict(self, dense: Sequence[torch.Tensor], idx: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+        for r, d, i in zip(self.ranks, dense, idx):
+            r._refresh_weights()
+            r.idx[:i.shape[0]].copy_(i)
+            r.bottom_forward(d)
+        for r in self.ranks:
+            r.embedding_forward()
+        return [r.top_forward_backward(None, d.shape[0], False)[:, 0].float().clone()
+                for r, d in zip(self.ranks, dense)]
