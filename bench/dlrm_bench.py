@@ -1,0 +1,109 @@
+"""DLRM throughput: hybrid-parallel fused path vs replicated-embedding DDP stand-in.
+
+    python bench/dlrm_bench.py --batch 8192                                   # 1 GPU
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29544 bench/dlrm_bench.py --batch 8192 [--impl standin]
+
+Criteo-shaped synthetic data (13 dense + 26 categorical), random-init weights, per-GPU batch fixed
+(weak scaling), device-timed with CUDA events, max over ranks.
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+import torch.nn as nn  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=8192)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--rows", type=int, default=100000, help="rows per embedding table")
+    ap.add_argument("--impl", default="ours", choices=["ours", "standin"])
+    args = ap.parse_args()
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank = dist.get_rank() if world > 1 else 0
+    dev = torch.device("cuda", local)
+    from raydp_b200.models import DLRM
+    sizes = [args.rows] * 26
+    torch.manual_seed(0)
+    B = args.batch
+    g = torch.Generator(device=dev).manual_seed(1 + rank)
+    pool = []
+    for _ in range(4):
+        dense = torch.randn(B, 13, device=dev, generator=g)
+        idx = torch.randint(0, args.rows, (B, 26), device=dev, generator=g, dtype=torch.int32)
+        y = (torch.rand(B, device=dev, generator=g) < 0.25).float()
+        pool.append((dense, idx, y))
+
+    if args.impl == "ours":
+        from raydp_b200.parallel.hybrid import DistributedDLRM
+        model = DLRM(13, sizes, 32, sparse_grad=False)
+        eng = DistributedDLRM(model.fused_spec(), B, dev)
+        eng.core.load_from_module(model.to(dev))
+        del model
+        packed = []
+        for dense, idx, y in pool:
+            d = torch.zeros(B, eng.core.kpad, device=dev, dtype=torch.bfloat16)
+            d[:, :13] = dense.to(torch.bfloat16)
+            packed.append((d, idx, y))
+
+        def step(i):
+            d, idx, y = packed[i % len(packed)]
+            eng.train_step(d, idx, y, 0.01)
+    else:
+        model = DLRM(13, sizes, 32, sparse_grad=False).to(dev)     # replicated tables, dense grads (NCCL-reducible)
+        ddp = nn.parallel.DistributedDataParallel(model, device_ids=[local]) if world > 1 else model
+        opt = torch.optim.SGD(ddp.parameters(), lr=0.01)
+        crit = nn.BCEWithLogitsLoss()
+
+        def step(i):
+            dense, idx, y = pool[i % len(pool)]
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = ddp(dense, idx.long())
+            loss = crit(out[:, 0].float(), y)
+            loss.item()
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+
+    for i in range(args.warmup):
+        step(i)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for i in range(args.steps):
+        step(i)
+    e.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([s.elapsed_time(e)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    if rank == 0:
+        print(json.dumps({"impl": args.impl, "metric": "DLRM train samples/sec", "n_gpus": world,
+                          "per_gpu_batch": B, "table_rows": args.rows, "steps": args.steps,
+                          "ms_per_step": ms / args.steps, "value": world * B * args.steps / (ms / 1e3),
+                          "parallelism": "dense dp + table-wise embedding mp" if args.impl == "ours" else "ddp, replicated tables"}),
+              flush=True)
+    if args.impl == "ours":
+        eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

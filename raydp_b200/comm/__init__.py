@@ -29,6 +29,25 @@ FLAG_BYTES = 256
 ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2}
 
 
+class _RawCudaBuffer:
+    """Exposes a raw device pointer through ``__cuda_array_interface__`` (zero-copy torch view)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+_TYPESTR = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1", torch.int16: "<i2"}
+
+
+def tensor_from_ptr(ptr: int, shape, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+    """Torch tensor over memory this process did not get from torch (symmetric / IPC regions).
+    bf16 has no array-interface typestr: it is viewed through int16."""
+    if dtype == torch.bfloat16:
+        return torch.as_tensor(_RawCudaBuffer(ptr, shape, "<i2"), device=device).view(torch.bfloat16)
+    return torch.as_tensor(_RawCudaBuffer(ptr, shape, _TYPESTR[dtype]), device=device)
+
+
 def p2p_available() -> bool:
     """True when every GPU of this host's ranks can map every other one."""
     if not torch.cuda.is_available() or not dist.is_initialized():

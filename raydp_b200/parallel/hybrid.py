@@ -258,3 +258,129 @@ class LocalWorld:
             r.embedding_forward()
         return [r.top_forward_backward(None, d.shape[0], False)[:, 0].float().clone()
                 for r, d in zip(self.ranks, dense)]
+
+
+class DistributedDLRM:
+    """One process per GPU: symmetric slabs for the embedding exchange, flag rounds between the
+    phases, peer-memory all-reduce fused with SGD for the dense gradients."""
+
+    def __init__(self, spec: DLRMSpec, batch: int, device: torch.device, group=None, momentum: float = 0.0,
+                 weight_decay: float = 0.0):
+        import torch.distributed as dist
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.core = FusedDLRM(spec, batch, device, self.rank, self.world)
+        self.device = device
+        self.momentum, self.weight_decay = momentum, weight_decay
+        self.step_count = 0
+        self.lr_dev = torch.zeros(1, dtype=torch.float32, device=device)
+        self.step_dev = torch.zeros(1, dtype=torch.float32, device=device)
+        self.sym = None
+        self.reducer = None
+        if self.world > 1:
+            from raydp_b200.comm import P2PReducer, SymmetricMemory, tensor_from_ptr
+            c = self.core
+            B, T, S, D = c.B, c.T, c.S, c.D
+            idx_bytes = (B * T * 4 + 255) // 256 * 256
+            slab_bytes = (B * S * D * 2 + 255) // 256 * 256
+            per_parity = idx_bytes + 2 * slab_bytes
+            self.flag_off = 2 * per_parity
+            self.sym = SymmetricMemory(self.flag_off + 256, group)
+            self.barrier_epoch = torch.zeros(1, dtype=torch.int32, device=device)
+            self.views, self.peer_ptrs = [], []
+            for p in range(2):
+                base = p * per_parity
+                local = self.sym.local + base
+                self.views.append((tensor_from_ptr(local, (B, T), torch.int32, device),
+                                   tensor_from_ptr(local + idx_bytes, (B, S, D), torch.bfloat16, device),
+                                   tensor_from_ptr(local + idx_bytes + slab_bytes, (B, S, D), torch.bfloat16, device)))
+                self.peer_ptrs.append(([b + base for b in self.sym.bases],
+                                       [b + base + idx_bytes for b in self.sym.bases],
+                                       [b + base + idx_bytes + slab_bytes for b in self.sym.bases]))
+            self.core.peer_batch = [B] * self.world
+            self.reducer = P2PReducer(self.core.grads, device, group, algo="auto")
+            dist.broadcast(self.core.params, src=0)
+
+    def _select(self, parity: int) -> None:
+        c = self.core
+        c.idx, c.feats, c.dfeats = self.views[parity]
+        c.peer_idx, c.peer_feats, c.peer_dfeats = self.peer_ptrs[parity]
+
+    def _barrier(self) -> None:
+        ops.comm_barrier(self.sym.bases, self.flag_off, self.rank, self.world, self.barrier_epoch)
+
+    def train_step(self, dense: torch.Tensor, idx: torch.Tensor, target: torch.Tensor, lr: float) -> None:
+        c = self.core
+        B = dense.shape[0]
+        multi = self.world > 1
+        if multi:
+            assert B == c.B, "model-parallel embeddings need equal, full batches on every rank (drop_last=True)"
+            self._select(self.step_count & 1)
+        self.step_count += 1
+        c._refresh_weights()
+        c.idx[:B].copy_(idx)
+        c.bottom_forward(dense)
+        if multi:
+            self._barrier()
+        c.embedding_forward()
+        if multi:
+            self._barrier()
+        c.top_forward_backward(target, B, True)
+        if multi:
+            self._barrier()
+        c.embedding_backward(lr, 1.0 / self.world)
+        c.bottom_backward(dense)
+        if multi:
+            from raydp_b200.comm import make_opt_args
+            if self.momentum and c.momentum_buf is None:
+                c.momentum_buf = torch.zeros_like(c.params)
+            self.lr_dev.fill_(lr)
+            self.step_dev.fill_(float(self.step_count))
+            opt = make_opt_args(2, c.params, c.momentum_buf if self.momentum else None, None,
+                                weight_decay=self.weight_decay, momentum=self.momentum, lr_dev=self.lr_dev,
+                                step_dev=self.step_dev)
+            self.reducer.allreduce_step_(opt, 1.0 / self.world)
+        else:
+            c.sgd(lr, 1.0, self.momentum, self.weight_decay)
+
+    def eval_step(self, dense: torch.Tensor, idx: torch.Tensor, target: Optional[torch.Tensor]) -> torch.Tensor:
+        c = self.core
+        B = dense.shape[0]
+        multi = self.world > 1
+        if multi:
+            assert B == c.B
+            self._select(self.step_count & 1)
+        self.step_count += 1
+        c._refresh_weights()
+        c.idx[:B].copy_(idx)
+        c.bottom_forward(dense)
+        if multi:
+            self._barrier()
+        c.embedding_forward()
+        if multi:
+            self._barrier()
+        out = c.top_forward_backward(target, B, False)
+        if multi:
+            self._barrier()          # keeps the parity protocol's three rounds per step
+        return out
+
+    def full_state_dict(self) -> Dict[str, torch.Tensor]:
+        """Rank 0 gets the whole model (dense + every table shard); other ranks get {}."""
+        import torch.distributed as dist
+        state = self.core.dense_state_dict() if self.rank == 0 else {}
+        tables = self.core.table_state_dict()
+        if self.world > 1:
+            gathered = [None] * self.world if self.rank == 0 else None
+            dist.gather_object(tables, gathered, dst=0)
+            if self.rank == 0:
+                for part in gathered:
+                    state.update(part)
+        else:
+            state.update(tables)
+        return state
+
+    def close(self) -> None:
+        if self.reducer is not None:
+            self.reducer.close()
+        if self.sym is not None:
+            self.sym.close()

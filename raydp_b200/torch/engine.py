@@ -111,8 +111,10 @@ class StockEngine:
 def make_engine(config, sess, model, optimizer, criterion, scheduler, metrics):
     choice = config.get("engine", "auto")
     if sess.device.type == "cuda" and choice in ("auto", "fused"):
-        from raydp_b200.torch.fused_engine import FusedEngine, fused_supported
+        from raydp_b200.torch.fused_engine import DLRMEngine, FusedEngine, _is_dlrm, fused_supported
         ok, why = fused_supported(config, model, optimizer, criterion)
+        if ok and _is_dlrm(model):
+            return DLRMEngine(config, sess, model, optimizer, criterion, scheduler, metrics)
         if ok:
             return FusedEngine(config, sess, model, optimizer, criterion, scheduler, metrics)
         if choice == "fused":

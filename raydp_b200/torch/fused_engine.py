@@ -51,9 +51,22 @@ def _optimizer_kind(optimizer) -> Optional[str]:
     return None
 
 
+def _is_dlrm(model) -> bool:
+    from raydp_b200.models.dlrm import DLRMSpec
+    return hasattr(model, "fused_spec") and isinstance(model.fused_spec(), DLRMSpec)
+
+
 def fused_supported(config, model, optimizer, criterion) -> Tuple[bool, str]:
     if not hasattr(model, "fused_spec"):
         return False, "model does not describe a fusable layer chain (no fused_spec())"
+    if _is_dlrm(model):
+        if type(criterion) is not torch.nn.BCEWithLogitsLoss or _loss_kind(criterion) != "bce_logits":
+            return False, "the fused DLRM path needs BCEWithLogitsLoss(mean)"
+        if _optimizer_kind(optimizer) != "sgd" or optimizer.param_groups[0].get("nesterov"):
+            return False, "the fused DLRM path needs torch.optim.SGD (sparse embedding updates are SGD)"
+        if not ops.kernels_available():
+            raise RuntimeError("CUDA worker without librdp_kernels.so: run __graft_entry__.build() first")
+        return True, ""
     if isinstance(config.get("feature_types"), (list, tuple)):
         return False, "per-column feature dtypes need the generic path"
     if _loss_kind(criterion) is None:
@@ -254,3 +267,86 @@ class FusedEngine:
     def close(self) -> None:
         if self.reducer is not None:
             self.reducer.close()
+
+
+class DLRMEngine:
+    """Estimator engine for :class:`raydp_b200.models.DLRM` (hybrid parallel, see
+    ``raydp_b200.parallel.hybrid``): dense columns first, then one categorical column per table."""
+
+    name = "fused-dlrm"
+
+    def __init__(self, config, sess, model, optimizer, criterion, scheduler, metrics):
+        from raydp_b200.parallel.hybrid import DistributedDLRM
+        self.config, self.sess, self.device = config, sess, sess.device
+        self.optimizer, self.scheduler, self.metrics = optimizer, scheduler, metrics
+        self.batch = int(config["batch_size"])
+        g = optimizer.param_groups[0]
+        self.spec = model.fused_spec()
+        self.dlrm = DistributedDLRM(self.spec, self.batch, self.device, momentum=g.get("momentum", 0.0),
+                                    weight_decay=g.get("weight_decay", 0.0))
+        self.dlrm.core.load_from_module(model.to(self.device))
+        model.to("cpu")
+        cols = list(config["feature_columns"])
+        self.dense_cols = cols[:self.spec.num_dense]
+        self.sparse_cols = cols[self.spec.num_dense:]
+        assert len(self.sparse_cols) == len(self.spec.table_sizes), "one categorical column per embedding table"
+        self._accum_host = torch.zeros(8, dtype=torch.float32).pin_memory()
+        self._loaders = {}
+
+    def _loader(self, shard):
+        if id(shard) not in self._loaders:
+            c = self.config
+            self._loaders[id(shard)] = ArrowGpuLoader(
+                shard, self.dense_cols, c["label_column"], self.batch, c["drop_last"] or self.sess.world_size > 1,
+                self.device, ld=self.dlrm.core.kpad, sparse_columns=self.sparse_cols,
+                table_rows=list(self.spec.table_sizes))
+        return self._loaders[id(shard)]
+
+    def _results(self, acc, steps):
+        count = max(1.0, acc[3])
+        res = {}
+        for name in self.metrics.names:
+            if name in ("Accuracy", "BinaryAccuracy"):
+                res[name] = float(acc[4] / count)
+        return res, float(acc[5] / max(1, steps))
+
+    def train_epoch(self, shard):
+        loader = self._loader(shard)
+        core = self.dlrm.core
+        core.accum.zero_()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        start.record()
+        steps = samples = 0
+        h2d0 = loader.h2d_bytes
+        for dense, idx, y in loader:
+            self.dlrm.train_step(dense, idx, y, float(self.optimizer.param_groups[0]["lr"]))
+            if self.scheduler is not None:
+                self.scheduler.step()
+            self._accum_host.copy_(core.accum, non_blocking=True)
+            steps += 1
+            samples += dense.shape[0]
+        end.record()
+        torch.cuda.current_stream().synchronize()
+        res, loss = self._results(self._accum_host.tolist(), steps)
+        timing = {"time_this_iter_s": time.perf_counter() - t0, "device_time_s": start.elapsed_time(end) / 1e3,
+                  "samples_this_iter": samples, "steps_this_iter": steps, "engine": self.name,
+                  "h2d_bytes_this_iter": loader.h2d_bytes - h2d0, "d2h_bytes_this_iter": 32 * steps}
+        return res, loss, timing
+
+    def evaluate_epoch(self, shard):
+        loader = self._loader(shard)
+        core = self.dlrm.core
+        core.accum.zero_()
+        steps = 0
+        for dense, idx, y in loader:
+            self.dlrm.eval_step(dense, idx, y)
+            steps += 1
+        return self._results(core.accum.tolist(), steps)
+
+    def state_dict(self):
+        torch.cuda.current_stream().synchronize()
+        return self.dlrm.full_state_dict()
+
+    def close(self):
+        self.dlrm.close()

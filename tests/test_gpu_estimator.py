@@ -77,3 +77,42 @@ def test_fused_estimator_data_parallel(ray_cluster):
     train = [h for h in est.results.metrics_history if "train_loss" in h]
     assert train[0]["engine"] == "fused" and train[-1]["train_loss"] < train[0]["train_loss"] * 0.8
     raydp.stop_spark()
+
+
+def test_dlrm_estimator_single_gpu(ray_cluster):
+    """DLRM through TorchEstimator: dense + categorical columns, fused hybrid engine, full checkpoint."""
+    import numpy as np
+    import pyarrow as pa
+    import raydp_b200 as raydp
+    from raydp_b200 import data as rdata
+    from raydp_b200.models import DLRM
+    from raydp_b200.torch import TorchEstimator
+    rng = np.random.default_rng(0)
+    n, sizes = 16384, [50 + 7 * t for t in range(26)]
+    cols = {f"d{i}": rng.standard_normal(n).astype(np.float32) for i in range(13)}
+    for t, s in enumerate(sizes):
+        cols[f"c{t}"] = rng.integers(0, s, n).astype(np.int64)
+    logit = cols["d0"] * 1.5 - cols["d1"] + (cols["c0"] % 2) * 2.0 - 1.0
+    cols["label"] = (rng.random(n) < 1 / (1 + np.exp(-logit))).astype(np.float32)
+    ds = rdata.from_arrow([pa.table({k: v[i::2] for k, v in cols.items()}) for i in range(2)])
+    model = DLRM(13, sizes, 32, sparse_grad=False)
+    features = [f"d{i}" for i in range(13)] + [f"c{t}" for t in range(26)]
+    est = TorchEstimator(num_workers=1, resources_per_worker={"GPU": 1}, model=model,
+                         optimizer=torch.optim.SGD(model.parameters(), lr=0.1), loss=nn.BCEWithLogitsLoss(),
+                         feature_columns=features, feature_types=[torch.float] * 13 + [torch.long] * 26,
+                         label_column="label", label_type=torch.float, batch_size=1024, num_epochs=5,
+                         shuffle=False, drop_last=True, metrics_name=["Accuracy"])
+    est.fit(ds, ds)
+    train = [h for h in est.results.metrics_history if "train_loss" in h]
+    assert train[0]["engine"] == "fused-dlrm"
+    assert train[-1]["train_loss"] < train[0]["train_loss"] - 0.02
+    assert train[-1]["train_res"]["Accuracy"] > 0.6
+    trained = est.get_model()
+    state = torch.load(os.path.join(est.results.checkpoint.path, "model.pt"), weights_only=True)
+    assert state["embeddings.25.weight"].shape == (sizes[25], 32) and "top.4.bias" in state
+    trained.eval()
+    x = torch.tensor(np.stack([cols[f"d{i}"] for i in range(13)], 1)[:2048])
+    s = torch.tensor(np.stack([cols[f"c{t}"] for t in range(26)], 1)[:2048])
+    with torch.no_grad():
+        acc = ((trained(x, s)[:, 0] > 0).float() == torch.tensor(cols["label"][:2048])).float().mean().item()
+    assert acc > 0.6
