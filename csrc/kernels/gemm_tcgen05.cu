@@ -404,14 +404,8 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       uint32_t phase = 0, x_phase = 0;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
-        if (kAux) {
-          mbar_wait(&x_empty[xb], x_phase ^ 1);
-          mbar_expect_tx(&x_full[xb], uint32_t(n_chunks64) * kChunkTileBytes);
-          for (int ch = 0; ch < n_chunks64; ++ch)
-            tma_load_2d(x_stage + xb * c_bytes + ch * kChunkTileBytes, &tmap_x, &x_full[xb],
-                        n_blk * p.n_tile + ch * 64, m_blk * kBlockM);
-          if (++xb == 2) { xb = 0; x_phase ^= 1; }
-        }
+        // operands first: the MMA of this tile must never wait behind the aux buffer, whose release
+        // depends on the epilogue + statistics MMAs of two tiles ago
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* a_dst = tiles + stage * stage_bytes;
@@ -419,6 +413,14 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           tma_load_2d(a_dst, &tmap_a, &full_bar[stage], kb * kBlockK, m_blk * kBlockM);
           tma_load_2d(a_dst + a_bytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * p.n_tile);
           if (++stage == kS) { stage = 0; phase ^= 1; }
+        }
+        if (kAux) {
+          mbar_wait(&x_empty[xb], x_phase ^ 1);
+          mbar_expect_tx(&x_full[xb], uint32_t(n_chunks64) * kChunkTileBytes);
+          for (int ch = 0; ch < n_chunks64; ++ch)
+            tma_load_2d(x_stage + xb * c_bytes + ch * kChunkTileBytes, &tmap_x, &x_full[xb],
+                        n_blk * p.n_tile + ch * 64, m_blk * kBlockM);
+          if (++xb == 2) { xb = 0; x_phase ^= 1; }
         }
       }
     }

@@ -90,7 +90,7 @@ class ArrowGpuLoader:
         self.device = device
         self.ld = ld or (max(8, len(self.features)) + 7) // 8 * 8
         self.out_dtype = out_dtype
-        self.chunk_rows = int(chunk_rows or max(self.batch, 1 << 18))
+        self.chunk_rows = int(chunk_rows or max(self.batch, 1 << 18))   # staging granularity of the DMA pipeline
         self.shift, self.scale = shift, scale
         self.copy_stream = torch.cuda.Stream(device=device)
         self._cols = self.features + self.sparse + ([self.label] if self.label else [])
