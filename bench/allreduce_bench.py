@@ -42,8 +42,11 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     rank, world = dist.get_rank(), dist.get_world_size()
-    from raydp_b200.comm import P2PReducer, p2p_available
+    from raydp_b200.comm import NvlsReducer, P2PReducer, nvls_available, p2p_available
     assert p2p_available(), "peer access unavailable"
+    use_nvls = nvls_available(torch.device("cuda", local))
+    if rank == 0:
+        print(f"# NVLS multicast support: {use_nvls}", flush=True)
     rows = []
     for n in [int(x) for x in args.sizes.split(",")]:
         n = (n + 3) // 4 * 4
@@ -63,6 +66,23 @@ def main():
                     err = (red.grads - ref).abs().max().item()
                     assert err <= 1e-4 * max(1.0, ref.abs().max().item()), (algo, n, rep, err)
                 red.close()
+            red = P2PReducer(x.clone(), torch.device("cuda", local), algo="two_shot")
+            for rep in range(3):
+                red.next_send_buffer().copy_(x)
+                got = red.allreduce_registered_()
+                torch.cuda.synchronize()
+                err = (got - ref).abs().max().item()
+                assert err <= 1e-4 * max(1.0, ref.abs().max().item()), ("registered", n, rep, err)
+            red.close()
+            if use_nvls:
+                nv = NvlsReducer(n, torch.device("cuda", local))
+                for rep in range(3):
+                    nv.buffer.copy_(x)
+                    nv.allreduce_()
+                    torch.cuda.synchronize()
+                    err = (nv.buffer - ref).abs().max().item()
+                    assert err <= 1e-4 * max(1.0, ref.abs().max().item()), ("nvls", n, rep, err)
+                nv.close()
             continue
         iters = 200 if n <= (1 << 20) else (50 if n <= (1 << 24) else 10)
         buf = x.clone()
@@ -74,6 +94,16 @@ def main():
             red = P2PReducer(x.clone(), torch.device("cuda", local), algo=algo)
             res[f"{algo}_us"] = timed(lambda: red.allreduce_(), iters)
             red.close()
+        if n >= (1 << 18):
+            red = P2PReducer(x.clone(), torch.device("cuda", local), algo="two_shot")
+            red.next_send_buffer().copy_(x)
+            res["two_shot_registered_us"] = timed(lambda: red.allreduce_registered_(), iters)
+            red.close()
+        if use_nvls:
+            nv = NvlsReducer(n, torch.device("cuda", local))
+            nv.buffer.copy_(x)
+            res["nvls_us"] = timed(lambda: nv.allreduce_(), iters)
+            nv.close()
         best = min(v for k, v in res.items() if k.endswith("_us") and k != "nccl_us")
         factor = 2 * (world - 1) / world * n * 4
         res["p2p_best_us"] = best

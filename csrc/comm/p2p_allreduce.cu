@@ -167,8 +167,10 @@ allreduce_kernel(const __grid_constant__ ArParams P) {
 
   // phase 1: publish my gradient in my send buffer
   float* mine = a.send[b][my_rank];
-  for (int64_t i = tid; i < n4; i += nthreads)
-    reinterpret_cast<float4*>(mine)[i] = reinterpret_cast<const float4*>(a.in)[i];
+  if (a.in != mine) {      // registered mode: the gradient was produced straight into the send buffer
+    for (int64_t i = tid; i < n4; i += nthreads)
+      reinterpret_cast<float4*>(mine)[i] = reinterpret_cast<const float4*>(a.in)[i];
+  }
   grid_signal_and_wait(a, my_rank, world, e, 0, a.counters + 0, nblocks);
 
   if (!kTwoShot) {
@@ -188,23 +190,35 @@ allreduce_kernel(const __grid_constant__ ArParams P) {
     // phase 2: reduce-scatter by pull (slice my_rank), all-gather by push into every recv[b]
     const int64_t per = (n4 + world - 1) / world;
     const int64_t lo = per * my_rank, hi = min(n4, lo + per);
-    for (int64_t i = lo + tid; i < hi; i += nthreads) {
-      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i0 = lo + tid; i0 < hi; i0 += 2 * nthreads) {
+      const int64_t i1 = i0 + nthreads;
+      const bool two = i1 < hi;
+      float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;
 #pragma unroll 4
       for (int q = 0; q < world; ++q) {
-        const float4 v = ld_peer(a.send[b][(my_rank + q) % world] + i * 4);
-        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        const float* src = a.send[b][(my_rank + q) % world];
+        const float4 v0 = ld_peer(src + i0 * 4);
+        float4 v1 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (two) v1 = ld_peer(src + i1 * 4);
+        s0.x += v0.x; s0.y += v0.y; s0.z += v0.z; s0.w += v0.w;
+        s1.x += v1.x; s1.y += v1.y; s1.z += v1.z; s1.w += v1.w;
       }
-      s.x *= P.scale; s.y *= P.scale; s.z *= P.scale; s.w *= P.scale;
+      s0.x *= P.scale; s0.y *= P.scale; s0.z *= P.scale; s0.w *= P.scale;
+      s1.x *= P.scale; s1.y *= P.scale; s1.z *= P.scale; s1.w *= P.scale;
 #pragma unroll 4
-      for (int q = 0; q < world; ++q)
-        reinterpret_cast<float4*>(a.recv[b][(my_rank + q) % world])[i] = s;
+      for (int q = 0; q < world; ++q) {
+        float4* dst = reinterpret_cast<float4*>(a.recv[b][(my_rank + q) % world]);
+        dst[i0] = s0;
+        if (two) dst[i1] = s1;
+      }
     }
     grid_signal_and_wait(a, my_rank, world, e, 1, a.counters + 2, nblocks);
     // phase 3: optimizer epilogue (or copy-out) from the locally complete recv buffer
     const float* full = a.recv[b][my_rank];
-    for (int64_t i = tid; i < n4; i += nthreads)
-      apply_update(a.opt, i * 4, reinterpret_cast<const float4*>(full)[i], bc1, bc2, lr, first_step, a.out);
+    if (a.opt.kind != 0 || (a.out != nullptr && a.out != full)) {   // else: the caller reads recv[] in place
+      for (int64_t i = tid; i < n4; i += nthreads)
+        apply_update(a.opt, i * 4, reinterpret_cast<const float4*>(full)[i], bc1, bc2, lr, first_step, a.out);
+    }
   }
 
   // the last block to finish advances the epoch for the next launch
@@ -340,7 +354,7 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
   const bool two_shot = algo == 2 || (algo == 0 && n * 4 > (1 << 20));
   int64_t work = two_shot ? P.n / 4 / world : P.n / 4;
   int blocks = int((work + kArThreads - 1) / kArThreads);
-  int cap = two_shot ? num_sms() / 2 : 32;
+  int cap = two_shot ? num_sms() : 32;
   if (n_local_ranks > 1) cap = max(1, (num_sms() / 2) / world);      // emulation: all ranks share one GPU
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
@@ -360,3 +374,132 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// K3: NVLS all-reduce -- the reduction happens inside the NVSwitch
+// ================================================================================================
+// `mc` is a *multicast* mapping of every rank's symmetric buffer (created with
+// torch.distributed._symmetric_memory, which only does the cuMulticast* / handle-exchange
+// plumbing; the kernel below is ours).  Rank r owns slice r: one `multimem.ld_reduce` pulls the
+// sum of all W copies of a 16-byte vector through the switch, one `multimem.st` broadcasts the
+// result into all W buffers.  Per rank that is S/W bytes in and S/W bytes out instead of the
+// 2 (W-1)/W * S of the pull/push two-shot, so large messages are no longer bound by this GPU's
+// link bandwidth.  Two flag rounds delimit the kernel; the result is in place in every buffer.
+namespace rdp {
+
+struct NvlsParams {
+  float* mc;                       // multicast address of the buffer
+  float* local;                    // this rank's unicast address (optimizer epilogue reads it)
+  uint32_t* flags[kMaxRanks];      // peer-mapped flag words (unicast), 4 slots x kMaxRanks
+  int rank, world;
+  int64_t n;                       // floats, multiple of 4
+  float scale;
+  uint32_t* epoch;
+  uint32_t* counters;              // [0] arrive-A, [1] finished, [2] arrive-B
+  OptSpec opt;
+  float* out;                      // optional separate output (null: leave the result in `local`)
+};
+
+__device__ __forceinline__ void flags_signal_and_wait(uint32_t* const* flags, int my_rank, int world, uint32_t e,
+                                                      int slot, uint32_t* counter, int nblocks) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(counter, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      *counter = 0;
+      __threadfence_system();
+      for (int q = 0; q < world; ++q) st_release_sys(flags[q] + slot * kMaxRanks + my_rank, e);
+    }
+  }
+  if (int(threadIdx.x) < world) {
+    const uint32_t* f = flags[my_rank] + slot * kMaxRanks + threadIdx.x;
+    while (int32_t(ld_acquire_sys(f) - e) < 0) {
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kArThreads)
+nvls_allreduce_kernel(const __grid_constant__ NvlsParams p) {
+  const int nblocks = gridDim.x;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
+  const int64_t n4 = p.n / 4;
+  const int64_t per = (n4 + p.world - 1) / p.world;
+  const int64_t lo = per * p.rank, hi = min(n4, lo + per);
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  const int64_t nthreads = int64_t(nblocks) * blockDim.x;
+  float lr = p.opt.lr, bc1 = 1.f, bc2 = 1.f;
+  bool first_step = false;
+  if (p.opt.kind) {
+    if (p.opt.lr_ptr) lr = *p.opt.lr_ptr;
+    const float t = p.opt.step_ptr ? *p.opt.step_ptr : 1.f;
+    bc1 = 1.f - powf(p.opt.beta1, t);
+    bc2 = 1.f - powf(p.opt.beta2, t);
+    first_step = t <= 1.f;
+  }
+  // round A: every rank's contribution is in its buffer
+  flags_signal_and_wait(p.flags, p.rank, p.world, e, 0, p.counters + 0, nblocks);
+  // four independent switch reductions in flight per thread before the first broadcast store
+  constexpr int kU = 4;
+  for (int64_t i0 = lo + tid; i0 < hi; i0 += nthreads * kU) {
+    float4 v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t i = i0 + u * nthreads;
+      if (i < hi)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(p.mc + i * 4) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t i = i0 + u * nthreads;
+      if (i < hi)
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(p.mc + i * 4), "f"(v[u].x * p.scale), "f"(v[u].y * p.scale), "f"(v[u].z * p.scale),
+                       "f"(v[u].w * p.scale) : "memory");
+    }
+  }
+  // round B: every slice has been broadcast into every buffer
+  flags_signal_and_wait(p.flags, p.rank, p.world, e, 1, p.counters + 2, nblocks);
+  if (p.opt.kind || p.out != nullptr) {
+    for (int64_t i = tid; i < n4; i += nthreads)
+      apply_update(p.opt, i * 4, reinterpret_cast<const float4*>(p.local)[i], bc1, bc2, lr, first_step, p.out);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(p.counters + 1, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      p.counters[1] = 0;
+      *p.epoch = e;
+    }
+  }
+}
+
+}  // namespace rdp
+
+extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
+                                  uint32_t* epoch, uint32_t* counters, const rdp_opt_args* opt, float* out,
+                                  int64_t n, float scale, void* stream) {
+  using namespace rdp;
+  RDP_REQUIRE(mc_ptr != nullptr, "rdp_allreduce_nvls: no multicast mapping (NVLS unsupported on this system)");
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks && n > 0 && n % 4 == 0, "rdp_allreduce_nvls: bad world/n");
+  NvlsParams p;
+  memset(&p, 0, sizeof(p));
+  p.mc = static_cast<float*>(mc_ptr);
+  p.local = static_cast<float*>(local_ptr);
+  for (int q = 0; q < world; ++q) p.flags[q] = static_cast<uint32_t*>(flag_ptrs[q]);
+  p.rank = rank; p.world = world; p.n = n; p.scale = scale; p.epoch = epoch; p.counters = counters; p.out = out;
+  if (opt != nullptr)
+    p.opt = OptSpec{opt->kind, opt->p, opt->m, opt->v, opt->lr, opt->beta1, opt->beta2, opt->eps, opt->weight_decay,
+                    opt->momentum, opt->dampening, opt->adamw, opt->nesterov, opt->lr_ptr, opt->step_ptr};
+  int64_t work = n / 4 / world / 4;
+  int blocks = int((work + kArThreads - 1) / kArThreads);
+  const int cap = num_sms();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  nvls_allreduce_kernel<<<blocks, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

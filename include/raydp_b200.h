@@ -110,6 +110,15 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
                   uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,
                   int algo, void* stream);
 
+// ---- K3: NVLS all-reduce (multimem.ld_reduce + multimem.st through the NVSwitch) ------------------
+// mc_ptr: multicast mapping of all ranks' buffers; local_ptr: this rank's unicast mapping;
+// flag_ptrs[q]: 256 zero-initialised bytes inside rank q's buffer (unicast, peer-mapped).
+// In place: every rank's buffer ends up holding scale * sum.  opt (optional) applies Adam/SGD from
+// the reduced buffer in the same kernel; out (optional) receives a copy of the reduced gradient.
+int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
+                       uint32_t* epoch, uint32_t* counters, const struct rdp_opt_args* opt, float* out,
+                       int64_t n, float scale, void* stream);
+
 // One flag round between all ranks on `stream`; the flag area (>= 256 bytes, zero-initialised) sits at
 // bases[q] + flag_offset_bytes in every rank's symmetric region; `epoch` is a local device uint32.
 int rdp_comm_barrier(void* const* bases, uint64_t flag_offset_bytes, int rank, int world, uint32_t* epoch,

@@ -140,17 +140,38 @@ class P2PReducer:
         self.counters = torch.zeros(4, dtype=torch.int32, device=device)
         self.world = self.sym.world
         self.rank = self.sym.rank
+        self._calls = 0           # host mirror of the device epoch (selects the buffer parity)
 
     def allreduce_(self, scale: float = 1.0) -> None:
         """In-place sum (times ``scale``) of ``grads`` over all ranks."""
+        self._calls += 1
         _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
                 [self.epoch], [self.counters], None, self.n, scale, self.algo)
 
     def allreduce_step_(self, opt: OptArgs, scale: float) -> None:
         """All-reduce fused with the optimizer update: parameters are updated in the same kernel
         that pulls the peers' gradients; ``grads`` receives the reduced gradient."""
+        self._calls += 1
         _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
                 [self.epoch], [self.counters], [opt], self.n, scale, self.algo)
+
+    # ---- registered (zero-copy) mode for large buffers, two-shot only -----------------------------
+    def next_send_buffer(self) -> torch.Tensor:
+        """View of the symmetric send buffer the NEXT ``allreduce_registered_`` call will reduce:
+        produce the gradient straight into it and the kernel skips its copy-in pass."""
+        b = (self._calls + 1) & 1
+        return tensor_from_ptr(self.sym.local + b * self.slot * 4, (self.n,), torch.float32, self.grads.device)
+
+    def allreduce_registered_(self, scale: float = 1.0) -> torch.Tensor:
+        """Two-shot all-reduce of ``next_send_buffer()``; returns a view of the receive buffer holding
+        the result (valid until the call after next).  No copy-in, no copy-out."""
+        src = self.next_send_buffer()
+        b = (self._calls + 1) & 1
+        dst = tensor_from_ptr(self.sym.local + (2 + b) * self.slot * 4, (self.n,), torch.float32, self.grads.device)
+        _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [src], [dst],
+                [self.epoch], [self.counters], None, self.n, scale, ALGO["two_shot"])
+        self._calls += 1
+        return dst
 
     def close(self) -> None:
         self.sym.close()
@@ -177,3 +198,54 @@ class LocalEmulation:
 
 
 make_opt_args = _opt_args
+
+
+class NvlsReducer:
+    """K3: all-reduce with the reduction done inside the NVSwitch (``multimem.ld_reduce`` /
+    ``multimem.st``).  The buffer is allocated as *symmetric memory with a multicast mapping* through
+    ``torch.distributed._symmetric_memory`` (plumbing only: cuMulticast object, handle exchange,
+    mappings); the kernel is ``rdp_allreduce_nvls``.  ``buffer`` is the gradient buffer itself, so
+    there is no copy-in and the result is in place on every rank."""
+
+    kind = "nvls"
+
+    def __init__(self, n: int, device: torch.device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        assert n % 4 == 0
+        self.n = n
+        self.lib = ops.lib()
+        group = group or dist.group.WORLD
+        self._t = symm_mem.empty(n + FLAG_BYTES // 4, dtype=torch.float32, device=device)
+        self._t.zero_()
+        self._hdl = symm_mem.rendezvous(self._t, group)
+        self.rank, self.world = self._hdl.rank, self._hdl.world_size
+        self.mc_ptr = int(self._hdl.multicast_ptr or 0)
+        if not self.mc_ptr:
+            raise RuntimeError("this system exposes no NVLS multicast mapping")
+        self.buffer = self._t[:n]
+        self.flag_ptrs = [int(p) + n * 4 for p in self._hdl.buffer_ptrs]
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
+        self.counters = torch.zeros(4, dtype=torch.int32, device=device)
+        torch.cuda.synchronize()
+        dist.barrier(group)
+
+    def allreduce_(self, scale: float = 1.0, opt: Optional[OptArgs] = None, out: Optional[torch.Tensor] = None) -> None:
+        vp = ctypes.c_void_p
+        flags = (vp * self.world)(*[vp(p) for p in self.flag_ptrs])
+        ops._check(self.lib.rdp_allreduce_nvls(vp(self.mc_ptr), vp(self.buffer.data_ptr()), flags, self.rank,
+                                               self.world, vp(self.epoch.data_ptr()), vp(self.counters.data_ptr()),
+                                               ctypes.byref(opt) if opt is not None else None,
+                                               vp(out.data_ptr()) if out is not None else None, self.n, scale,
+                                               vp(torch.cuda.current_stream().cuda_stream)))
+
+    def close(self) -> None:
+        torch.cuda.synchronize()
+
+
+def nvls_available(device: torch.device) -> bool:
+    try:
+        from torch._C._autograd import DeviceType
+        from torch._C._distributed_c10d import _SymmetricMemory
+        return bool(_SymmetricMemory.has_multicast_support(DeviceType.CUDA, device.index or 0))
+    except Exception:  # noqa: BLE001
+        return False
