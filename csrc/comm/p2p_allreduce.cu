@@ -503,3 +503,76 @@ extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* fl
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ================================================================================================
+// All-to-all over peer memory (the standalone form of the K4 exchange)
+// ================================================================================================
+// Rank r stores chunk q of its input straight into slot r of rank q's receive buffer (NVSwitch gives
+// every pair full bandwidth, so there is no schedule beyond a per-rank rotation of the start peer).
+namespace rdp {
+
+struct A2AParams {
+  const float4* in;                // [world][chunk4]
+  float* recv[kMaxRanks];          // recv[q]: rank q's receive buffer [world][chunk4 * 4 floats]
+  uint32_t* flags[kMaxRanks];
+  int rank, world;
+  int64_t chunk4;                  // float4 vectors per (src, dst) pair
+  uint32_t* epoch;
+  uint32_t* counters;
+};
+
+__global__ void __launch_bounds__(kArThreads)
+alltoall_kernel(const __grid_constant__ A2AParams p) {
+  const int nblocks = gridDim.x;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  const int64_t nthreads = int64_t(nblocks) * blockDim.x;
+  // round A (slot 3): every rank has entered the call, so last call's receive buffers are consumed
+  flags_signal_and_wait(p.flags, p.rank, p.world, e, 3, p.counters + 0, nblocks);
+  for (int q = 0; q < p.world; ++q) {
+    const int dst = (p.rank + q) % p.world;
+    const float4* src = p.in + int64_t(dst) * p.chunk4;
+    float4* out = reinterpret_cast<float4*>(p.recv[dst]) + int64_t(p.rank) * p.chunk4;
+    for (int64_t i0 = tid; i0 < p.chunk4; i0 += 4 * nthreads) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (i0 + u * nthreads < p.chunk4) v[u] = src[i0 + u * nthreads];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) if (i0 + u * nthreads < p.chunk4) out[i0 + u * nthreads] = v[u];
+    }
+  }
+  // round B (slot 4): all pushes have landed
+  flags_signal_and_wait(p.flags, p.rank, p.world, e, 4, p.counters + 2, nblocks);
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(p.counters + 1, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      p.counters[1] = 0;
+      *p.epoch = e;
+    }
+  }
+}
+
+}  // namespace rdp
+
+extern "C" int rdp_alltoall(const void* in, void* const* recv_bases, void* const* flag_ptrs, int rank, int world,
+                            int64_t floats_per_pair, uint32_t* epoch, uint32_t* counters, void* stream) {
+  using namespace rdp;
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks && floats_per_pair > 0 && floats_per_pair % 4 == 0,
+              "rdp_alltoall: bad world / chunk (%lld floats per pair must be a multiple of 4)", (long long)floats_per_pair);
+  A2AParams p;
+  memset(&p, 0, sizeof(p));
+  p.in = static_cast<const float4*>(in);
+  for (int q = 0; q < world; ++q) {
+    p.recv[q] = static_cast<float*>(recv_bases[q]);
+    p.flags[q] = static_cast<uint32_t*>(flag_ptrs[q]);
+  }
+  p.rank = rank; p.world = world; p.chunk4 = floats_per_pair / 4; p.epoch = epoch; p.counters = counters;
+  int64_t work = p.chunk4 / 4;
+  int blocks = int((work + kArThreads - 1) / kArThreads);
+  if (blocks > num_sms()) blocks = num_sms();
+  if (blocks < 1) blocks = 1;
+  alltoall_kernel<<<blocks, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -119,6 +119,11 @@ int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, in
                        uint32_t* epoch, uint32_t* counters, const struct rdp_opt_args* opt, float* out,
                        int64_t n, float scale, void* stream);
 
+// All-to-all over peer memory: chunk q of `in` ([world][floats_per_pair]) lands in slot `rank` of rank q's
+// receive buffer (recv_bases[q], [world][floats_per_pair]); flag_ptrs[q] as for rdp_allreduce_nvls.
+int rdp_alltoall(const void* in, void* const* recv_bases, void* const* flag_ptrs, int rank, int world,
+                 int64_t floats_per_pair, uint32_t* epoch, uint32_t* counters, void* stream);
+
 // One flag round between all ranks on `stream`; the flag area (>= 256 bytes, zero-initialised) sits at
 // bases[q] + flag_offset_bytes in every rank's symmetric region; `epoch` is a local device uint32.
 int rdp_comm_barrier(void* const* bases, uint64_t flag_offset_bytes, int rank, int world, uint32_t* epoch,

@@ -249,3 +249,32 @@ def nvls_available(device: torch.device) -> bool:
         return bool(_SymmetricMemory.has_multicast_support(DeviceType.CUDA, device.index or 0))
     except Exception:  # noqa: BLE001
         return False
+
+
+class P2PAllToAll:
+    """All-to-all of fp32 chunks by direct peer stores (``rdp_alltoall``).  ``recv`` is this rank's
+    receive buffer ``[world, floats_per_pair]`` inside symmetric memory."""
+
+    def __init__(self, floats_per_pair: int, device: torch.device, group=None):
+        assert floats_per_pair % 4 == 0
+        self.chunk = floats_per_pair
+        self.lib = ops.lib()
+        world = dist.get_world_size(group)
+        self.sym = SymmetricMemory(world * floats_per_pair * 4 + FLAG_BYTES, group)
+        self.rank, self.world = self.sym.rank, self.sym.world
+        self.recv = tensor_from_ptr(self.sym.local, (world, floats_per_pair), torch.float32, device)
+        self._flag_ptrs = [b + world * floats_per_pair * 4 for b in self.sym.bases]
+        self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
+        self.counters = torch.zeros(4, dtype=torch.int32, device=device)
+
+    def __call__(self, send: torch.Tensor) -> torch.Tensor:
+        assert send.dtype == torch.float32 and send.numel() == self.world * self.chunk and send.is_contiguous()
+        vp = ctypes.c_void_p
+        arr = lambda xs: (vp * len(xs))(*[vp(x) for x in xs])  # noqa: E731
+        ops._check(self.lib.rdp_alltoall(vp(send.data_ptr()), arr(self.sym.bases), arr(self._flag_ptrs), self.rank,
+                                         self.world, self.chunk, vp(self.epoch.data_ptr()),
+                                         vp(self.counters.data_ptr()), vp(torch.cuda.current_stream().cuda_stream)))
+        return self.recv
+
+    def close(self) -> None:
+        self.sym.close()

@@ -42,6 +42,7 @@ SIGNATURES.update({
 
 SIGNATURES.update({
     "rdp_comm_barrier": (I, [C.POINTER(VP), C.c_uint64, I, I, VP, VP]),
+    "rdp_alltoall": (I, [VP, C.POINTER(VP), C.POINTER(VP), I, I, I64, VP, VP, VP]),
     "rdp_allreduce_nvls": (I, [VP, VP, C.POINTER(VP), I, I, VP, VP, C.POINTER(OptArgs), VP, I64, F, VP]),
     "rdp_embedding_fwd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),
                               C.POINTER(I), I, I, I, I, VP]),

@@ -71,3 +71,17 @@ def test_multigpu_allreduce():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "CHECK OK" in out.stdout
+
+
+@pytest.mark.multigpu
+def test_multigpu_alltoall():
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(n_gpus, 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29534", os.path.join(ROOT, "bench", "alltoall_bench.py"),
+           "--check", "--sizes", "1024,1048576"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "CHECK OK" in out.stdout
