@@ -62,6 +62,7 @@ struct ArParams {
   int world;
   int64_t n;                       // floats
   float scale;                     // applied to the sum (1/world for averaging)
+  int fixed_buffer;                // two-shot only: always use send[0] / recv[0] (see rdp_allreduce, algo 3)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -149,7 +150,7 @@ allreduce_kernel(const __grid_constant__ ArParams P) {
   const int world = P.world;
   const int nblocks = gridDim.x;
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(a.epoch) + 1u;
-  const int b = e & 1;
+  const int b = P.fixed_buffer ? 0 : int(e & 1);
   const int64_t n4 = P.n / 4;                      // n is padded to a multiple of 4 by the host
   const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
   const int64_t nthreads = int64_t(nblocks) * blockDim.x;
@@ -351,7 +352,10 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
                       o.dampening, o.adamw, o.nesterov, o.lr_ptr, o.step_ptr};
     }
   }
-  const bool two_shot = algo == 2 || (algo == 0 && n * 4 > (1 << 20));
+  // algo 3: two-shot on send[0]/recv[0] only.  Safe without parity: the second flag round ends after every
+  // rank has finished reading all send buffers, and recv is rewritten only after the next call's first round.
+  const bool two_shot = algo == 2 || algo == 3 || (algo == 0 && n * 4 > (1 << 20));
+  P.fixed_buffer = algo == 3 ? 1 : 0;
   int64_t work = two_shot ? P.n / 4 / world : P.n / 4;
   int blocks = int((work + kArThreads - 1) / kArThreads);
   int cap = two_shot ? num_sms() : 32;

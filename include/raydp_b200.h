@@ -104,7 +104,8 @@ struct rdp_opt_args {
 // bases[q]: rank q's symmetric region as mapped in this process (host array of `world` pointers).
 // n_local_ranks = 1 (normal: ins/outs/epochs/counters/opts have one entry) or = world (single-GPU
 // emulation of all ranks in one cooperative launch).  epochs[l] -> one uint32, counters[l] -> four
-// uint32, both zero-initialised device memory owned by the caller.  algo: 0 auto, 1 one-shot, 2 two-shot.
+// uint32, both zero-initialised device memory owned by the caller.  algo: 0 auto, 1 one-shot, 2 two-shot,
+// 3 two-shot on send[0]/recv[0] only (registered gradient buffers: `ins[l]` may BE send[0], no copy-in).
 int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
                   const float* const* ins, float* const* outs, uint32_t* const* epochs,
                   uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,

@@ -26,7 +26,7 @@ from raydp_b200 import ops
 from raydp_b200.ops._abi import OptArgs
 
 FLAG_BYTES = 256
-ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2}
+ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2, "two_shot_fixed": 3}
 
 
 class _RawCudaBuffer:
@@ -117,7 +117,8 @@ def _launch(lib, bases: Sequence[int], slot_floats: int, rank: int, world: int, 
     arr = lambda xs: (vp * len(xs))(*[vp(x) for x in xs])  # noqa: E731
     opt_arr = (OptArgs * nl)(*opts) if opts is not None else None
     ops._check(lib.rdp_allreduce(arr(bases), slot_floats, rank, world, nl,
-                                 arr([t.data_ptr() for t in ins]), arr([t.data_ptr() for t in outs]),
+                                 arr([t.data_ptr() for t in ins]),
+                                 arr([t.data_ptr() if t is not None else 0 for t in outs]),
                                  arr([t.data_ptr() for t in epochs]), arr([t.data_ptr() for t in counters]),
                                  opt_arr, n, scale, algo,
                                  vp(torch.cuda.current_stream().cuda_stream)))
@@ -128,14 +129,20 @@ class P2PReducer:
 
     kind = "p2p"
 
-    def __init__(self, grads: torch.Tensor, device: torch.device, group=None, algo: str = "auto"):
-        assert grads.dtype == torch.float32 and grads.is_contiguous()
-        assert grads.numel() % 4 == 0 and grads.data_ptr() % 16 == 0, "flat buffer must be 16-byte granular"
-        self.grads = grads
-        self.n = grads.numel()
+    def __init__(self, grads: Optional[torch.Tensor], device: torch.device, group=None, algo: str = "auto",
+                 n: Optional[int] = None):
+        """``grads``: the flat fp32 gradient buffer to reduce, or None with ``n`` given for *registered*
+        mode, where ``self.grads`` IS the symmetric send buffer (``algo="two_shot_fixed"``)."""
+        self.n = grads.numel() if grads is not None else int(n)
+        assert self.n % 4 == 0, "flat buffer must be 16-byte granular"
         self.slot = (self.n + 3) // 4 * 4
         self.algo = ALGO[algo]
         self.sym = SymmetricMemory(4 * self.slot * 4 + FLAG_BYTES, group)
+        if grads is None:
+            grads = tensor_from_ptr(self.sym.local, (self.n,), torch.float32, device)
+            self.recv0 = tensor_from_ptr(self.sym.local + 2 * self.slot * 4, (self.n,), torch.float32, device)
+        assert grads.dtype == torch.float32 and grads.is_contiguous() and grads.data_ptr() % 16 == 0
+        self.grads = grads
         self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
         self.counters = torch.zeros(4, dtype=torch.int32, device=device)
         self.world = self.sym.world
@@ -152,7 +159,8 @@ class P2PReducer:
         """All-reduce fused with the optimizer update: parameters are updated in the same kernel
         that pulls the peers' gradients; ``grads`` receives the reduced gradient."""
         self._calls += 1
-        _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
+        out = None if self.algo == ALGO["two_shot_fixed"] else self.grads
+        _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [out],
                 [self.epoch], [self.counters], [opt], self.n, scale, self.algo)
 
     # ---- registered (zero-copy) mode for large buffers, two-shot only -----------------------------

@@ -20,6 +20,13 @@ import torch.distributed as dist
 logger = logging.getLogger(__name__)
 
 
+def __getattr__(name):
+    if name == "FusedDataParallel":
+        from raydp_b200.parallel.data_parallel import FusedDataParallel
+        return FusedDataParallel
+    raise AttributeError(name)
+
+
 class NcclReducer:
     kind = "nccl"
 

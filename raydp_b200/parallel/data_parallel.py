@@ -1,0 +1,174 @@
+"""``FusedDataParallel``: data parallelism for arbitrary modules with the all-reduce fused into the
+optimizer and overlapped with backward.
+
+Replaces torch DDP + ``optimizer.step()`` as the reference gets them through
+``train.torch.prepare_model`` (reference ``torch/estimator.py:243,284-286``) for models that are not on
+the fully fused MLP path.
+
+* Parameters are re-homed into flat fp32 buckets (reverse registration order = backward order);
+  gradients are views of **registered symmetric memory**, so backward writes them where the peers
+  read them -- no bucket copy.
+* When the last gradient of a bucket lands, the bucket's kernel (two-shot reduce-scatter by pull +
+  all-gather by push over NVLink, then Adam/SGD on the reduced gradient, one launch) is enqueued on
+  a communication stream, behind an event from the compute stream: buckets of late layers reduce
+  and update while earlier layers are still in backward.
+* ``world_size == 1`` degenerates to the fused flat optimizer.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from raydp_b200 import ops
+
+
+class _Bucket:
+    def __init__(self, params: List[nn.Parameter], device: torch.device, world: int):
+        self.params = params
+        self.offsets, off = [], 0
+        for p in params:
+            self.offsets.append(off)
+            off += (p.numel() + 3) // 4 * 4
+        self.n = off
+        f32 = dict(dtype=torch.float32, device=device)
+        self.flat = torch.zeros(self.n, **f32)
+        self.m = torch.zeros(self.n, **f32)
+        self.v = torch.zeros(self.n, **f32)
+        self.reducer = None
+        if world > 1:
+            from raydp_b200.comm import P2PReducer
+            self.reducer = P2PReducer(None, device, algo="two_shot_fixed", n=self.n)
+            self.grads = self.reducer.grads
+        else:
+            self.grads = torch.zeros(self.n, **f32)
+        with torch.no_grad():
+            for p, o in zip(params, self.offsets):
+                self.flat[o:o + p.numel()].copy_(p.detach().reshape(-1))
+                p.data = self.flat[o:o + p.numel()].view(p.shape)
+                p.grad = self.grads[o:o + p.numel()].view(p.shape)
+        self.pending = len(params)
+        self.done_event: Optional[torch.cuda.Event] = None
+
+
+class FusedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, optimizer: torch.optim.Optimizer, device: Optional[torch.device] = None,
+                 bucket_mb: int = 512, overlap: bool = True):
+        super().__init__()
+        self.module = module
+        self.device = device or next(module.parameters()).device
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.overlap = overlap
+        g = optimizer.param_groups[0]
+        if type(optimizer) in (torch.optim.Adam, torch.optim.AdamW):
+            self.kind = 1
+            self.hp = dict(betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
+                           adamw=type(optimizer) is torch.optim.AdamW)
+        elif type(optimizer) is torch.optim.SGD:
+            self.kind = 2
+            self.hp = dict(weight_decay=g["weight_decay"], momentum=g["momentum"], dampening=g["dampening"],
+                           nesterov=g["nesterov"])
+        else:
+            raise TypeError("FusedDataParallel fuses Adam / AdamW / SGD; wrap other optimizers with stock DDP")
+        self.optimizer = optimizer
+        params = [p for p in module.parameters() if p.requires_grad]
+        if self.world > 1:
+            for p in params:
+                dist.broadcast(p.data, src=0)
+        limit = bucket_mb * (1 << 20) // 4
+        self.buckets: List[_Bucket] = []
+        cur, size = [], 0
+        for p in reversed(params):
+            if cur and size + p.numel() > limit:
+                self.buckets.append(_Bucket(cur, self.device, self.world))
+                cur, size = [], 0
+            cur.append(p)
+            size += p.numel()
+        if cur:
+            self.buckets.append(_Bucket(cur, self.device, self.world))
+        self._bucket_of: Dict[int, _Bucket] = {id(p): b for b in self.buckets for p in b.params}
+        f32 = dict(dtype=torch.float32, device=self.device)
+        self.step_dev = torch.zeros(1, **f32)
+        self.lr_dev = torch.zeros(1, **f32)
+        self.comm_stream = torch.cuda.Stream(device=self.device)
+        from raydp_b200.ops.linear import FusedLinear
+        self._fused_linears = [m for m in module.modules() if isinstance(m, FusedLinear)]
+        fused_w = {id(m.weight) for m in self._fused_linears}
+        fused_b = {id(m.bias) for m in self._fused_linears if m.bias is not None}
+        for m in self._fused_linears:
+            m._grad_ready_hooks.append(self._fused_linear_ready)
+        for p in params:
+            if id(p) not in fused_w and id(p) not in fused_b:
+                p.register_post_accumulate_grad_hook(self._param_ready)
+
+    # ------------------------------------------------------------------ hooks
+    def _fused_linear_ready(self, layer) -> None:
+        self._param_ready(layer.weight)
+        if layer.bias is not None:
+            self._param_ready(layer.bias)
+
+    def _param_ready(self, p) -> None:
+        b = self._bucket_of[id(p)]
+        b.pending -= 1
+        if b.pending == 0:
+            self._reduce_and_update(b)
+
+    def _opt_args(self, b: _Bucket):
+        from raydp_b200.comm import make_opt_args
+        if self.kind == 1:
+            return make_opt_args(1, b.flat, b.m, b.v, lr_dev=self.lr_dev, step_dev=self.step_dev, **self.hp)
+        return make_opt_args(2, b.flat, b.m if self.hp["momentum"] else None, None, lr_dev=self.lr_dev,
+                             step_dev=self.step_dev, **self.hp)
+
+    def _reduce_and_update(self, b: _Bucket) -> None:
+        compute = torch.cuda.current_stream(self.device)
+        stream = self.comm_stream if (self.overlap and self.world > 1) else compute
+        if stream is not compute:
+            ready = torch.cuda.Event()
+            ready.record(compute)
+            stream.wait_event(ready)
+        with torch.cuda.stream(stream):
+            if b.reducer is not None:
+                b.reducer.allreduce_step_(self._opt_args(b), 1.0 / self.world)
+            elif self.kind == 1:
+                ops.adam_step(b.flat, b.grads, b.m, b.v, 0.0, self.hp["betas"][0], self.hp["betas"][1], self.hp["eps"],
+                              self.hp["weight_decay"], 1, 1.0, self.hp["adamw"], self.lr_dev, self.step_dev)
+            else:
+                ops.sgd_step(b.flat, b.grads, b.m if self.hp["momentum"] else None, 0.0, self.hp["momentum"],
+                             self.hp["dampening"], self.hp["weight_decay"], self.hp["nesterov"], False, 1.0,
+                             self.lr_dev, self.step_dev)
+            b.grads.zero_()
+            b.done_event = torch.cuda.Event()
+            b.done_event.record(stream)
+
+    # ------------------------------------------------------------------ step API
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)
+
+    def backward_and_step(self, loss: torch.Tensor) -> None:
+        """``loss.backward()`` with bucket all-reduce + optimizer fused in; returns with every update
+        ordered before later work on the current stream."""
+        self.lr_dev.fill_(float(self.optimizer.param_groups[0]["lr"]))
+        ops.add_scalar(self.step_dev, 1.0)
+        for b in self.buckets:
+            b.pending = len(b.params)
+        loss.backward()
+        compute = torch.cuda.current_stream(self.device)
+        for b in self.buckets:
+            if b.pending != 0:                      # parameters that got no gradient this step
+                b.pending = 0
+                self._reduce_and_update(b)
+            if b.done_event is not None:
+                compute.wait_event(b.done_event)
+        for m in self._fused_linears:
+            m.invalidate_shadow()                   # parameters were updated by our kernel, not by torch
+
+    def state_dict(self, *args, **kwargs):
+        return self.module.state_dict(*args, **kwargs)
+
+    def close(self) -> None:
+        for b in self.buckets:
+            if b.reducer is not None:
+                b.reducer.close()

@@ -85,3 +85,20 @@ def test_multigpu_alltoall():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "CHECK OK" in out.stdout
+
+
+def test_fused_data_parallel_single_rank_matches_torch():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench", "bigmlp_bench.py"), "--check"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.multigpu
+def test_fused_data_parallel_multi_rank_matches_torch():
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("needs >= 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29536", os.path.join(ROOT, "bench", "bigmlp_bench.py"), "--check"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
