@@ -524,7 +524,12 @@ class Head:
             # peer-memory collectives map every rank's GPU, so all devices must stay visible.
             env["RAYDP_B200_GPUS"] = ",".join(str(g) for g in gpus)
         env.setdefault("PYTHONUNBUFFERED", "1")
-        extra_env = (actor.opts.get("env") if actor else None) or {}
+        if "OMP_NUM_THREADS" not in os.environ:
+            # One intra-op thread per reserved CPU (1 for tasks and zero-CPU actors): several
+            # workers share a node, and unbounded OpenMP pools oversubscribe it.
+            cpus = actor.resources.get("CPU", 0) if actor is not None else 1
+            env["OMP_NUM_THREADS"] = str(max(1, int(cpus)))
+        extra_env =(actor.opts.get("env") if actor else None) or {}
         env.update({k: str(v) for k, v in extra_env.items()})
         root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
         # workers see the driver's import path (functions/classes are pickled by reference)
