@@ -26,6 +26,7 @@ import threading
 import time
 from typing import Any, Dict, List, Optional
 
+from raydp_b200.exceptions import RayDPException
 from raydp_b200.spark import configs as C
 
 logger = logging.getLogger(__name__)
@@ -110,6 +111,7 @@ class RayDPSparkMaster:
         self._name = runtime.get_runtime_context().get_actor_name()
         self._started = False
         self._app_seq = 0
+        self._shuffle_services: Dict[str, Any] = {}   # node ip -> service actor handle
 
     # ------------------------------------------------------------------ lifecycle
     def start_up(self, resources: Optional[Dict[str, float]] = None) -> str:
@@ -207,8 +209,29 @@ class RayDPSparkMaster:
                 if executor_id in app.executors:
                     ok = app.register_executor(executor_id, node_ip, pid)
                     app.mark_started(executor_id)   # ExecutorStarted follows immediately
+                    self._ensure_shuffle_service(app, node_ip)
                     return ok
         return False
+
+    def _ensure_shuffle_service(self, app: ApplicationInfo, node_ip: str) -> None:
+        """One external shuffle service actor per node, started with the first executor that
+        registers from it (reference ``RayAppMaster.scala:151-167``)."""
+        conf = app.desc.get("conf", {})
+        if str(conf.get(C.SHUFFLE_SERVICE_ENABLED, "false")).lower() != "true":
+            return
+        if node_ip in self._shuffle_services:
+            return
+        from raydp_b200 import runtime
+        from raydp_b200.spark.shuffle_service import RayExternalShuffleService, service_name
+        handle = runtime.remote(RayExternalShuffleService).options(
+            name=service_name(self._name, node_ip), num_cpus=0,
+            resources={f"node:{node_ip}": 0.01}, max_concurrency=4).remote(node_ip, conf)
+        self._shuffle_services[node_ip] = handle
+        handle.start.remote()
+
+    def shuffle_service_nodes(self) -> List[str]:
+        with self._lock:
+            return sorted(self._shuffle_services)
 
     def request_add_pending_restarted_executor(self, actor_executor_id: int) -> int:
         """A restarted executor actor asks for a fresh executor id but keeps its actor name."""
@@ -223,7 +246,7 @@ class RayDPSparkMaster:
                 ex.executor_id, ex.registered, ex.started = new_id, False, False
                 app.executors[new_id] = ex
                 return new_id
-        raise RuntimeError(f"executor actor {actor_executor_id} is not known to the app master")
+        raise RayDPException(f"executor actor {actor_executor_id} is not known to the app master")
 
     def get_restarted_executors(self) -> Dict[int, int]:
         with self._lock:
@@ -313,6 +336,12 @@ class RayDPSparkMaster:
         for app_id in list(self._apps):
             self.unregister_application(app_id)
         self._recoverable.clear()
+        for handle in self._shuffle_services.values():
+            try:
+                handle.stop.remote()
+            except Exception:  # noqa: BLE001
+                pass
+        self._shuffle_services.clear()
         if cleanup_data:
             refs = [r for objs in self._objects.values() for r in objs]
             self._objects.clear()

@@ -231,7 +231,9 @@ class DataFrame:
             numPartitions = self.rdd.getNumPartitions()
         keys = [c if isinstance(c, str) else c._output_name() for c in cols]
         schema = self._arrow_schema()
-        pieces = self._run("shuffle_map", {"n_out": numPartitions, "keys": keys or None})
+        import uuid
+        pieces = self._run("shuffle_map", {"n_out": numPartitions, "keys": keys or None,
+                                           "shuffle_id": uuid.uuid4().hex[:12]})
         refs = [[row[d] for row in pieces if row[d] is not None] for d in range(numPartitions)]
         out = DataFrame(self._session, Plan(RefSource(refs, schema)))
         out._cached_refs = refs

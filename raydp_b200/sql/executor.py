@@ -10,6 +10,7 @@ process; a partition task is a pickled :class:`~raydp_b200.sql.plan.Plan` plus a
 from __future__ import annotations
 
 import os
+import time
 import threading
 from typing import Any, Dict, List, Optional, Tuple
 
@@ -17,6 +18,7 @@ import numpy as np
 import pyarrow as pa
 import pyarrow.compute as pc
 
+from raydp_b200.exceptions import RayDPException
 from raydp_b200.sql.plan import Plan
 
 EXECUTOR_NAME_PREFIX = "raydp-executor-"
@@ -110,7 +112,8 @@ def execute_action(plan: Plan, idx: int, action: str, args: Dict[str, Any], bloc
         out = []
         for d in range(n_out):
             piece = table.filter(pa.array(dest == d)) if table.num_rows else table
-            out.append(runtime.put(piece.combine_chunks()) if piece.num_rows else None)
+            out.append(runtime.put(piece.combine_chunks(), _owner=args.get("_shuffle_owner"))
+                       if piece.num_rows else None)
         return out
     if action == "agg_partial":
         return _partial_agg(table, args["keys"], args["aggs"])
@@ -159,11 +162,39 @@ class SparkExecutor:
                     return
             except Exception as exc:  # noqa: BLE001
                 last_exc = exc
-        raise RuntimeError(f"executor {self.executor_id} could not register with app master: {last_exc}")
+        raise RayDPException(f"executor {self.executor_id} could not register with app master: {last_exc}")
 
     # ------------------------------------------------------------------ tasks
     def run_partition(self, plan: Plan, idx: int, action: str, args: Optional[dict] = None):
-        return execute_action(plan, idx, action, args or {}, self.blocks)
+        args = dict(args or {})
+        service = self._shuffle_service() if action == "shuffle_map" else None
+        if service is not None:
+            args["_shuffle_owner"] = service        # blocks outlive this executor
+        out = execute_action(plan, idx, action, args, self.blocks)
+        if service is not None:
+            from raydp_b200 import runtime
+            refs = [r for r in out if r is not None]
+            if refs:
+                runtime.get(service.register_blocks.remote(str(args.get("shuffle_id", "0")), refs), timeout=60)
+        return out
+
+    def _shuffle_service(self):
+        """Handle of this node's external shuffle service when ``spark.shuffle.service.enabled``."""
+        if str(self.conf.get("spark.shuffle.service.enabled", "false")).lower() != "true":
+            return None
+        if getattr(self, "_shuffle_handle", None) is None:
+            from raydp_b200 import runtime
+            from raydp_b200.spark.shuffle_service import service_name
+            deadline = time.time() + 30
+            while True:
+                try:
+                    self._shuffle_handle = runtime.get_actor(service_name(self.master_name, self.node_ip))
+                    break
+                except Exception:  # noqa: BLE001  (the master starts it right after registration)
+                    if time.time() > deadline:
+                        raise
+                    time.sleep(0.05)
+        return self._shuffle_handle
 
     def ping(self) -> Dict[str, Any]:
         return {"executor_id": self.executor_id, "actor_executor_id": self.actor_executor_id,
@@ -183,7 +214,7 @@ class SparkExecutor:
             master = runtime.get_actor(self.master_name)
             plan = runtime.get(master.get_recoverable_plan.remote(rdd_id), timeout=60)
             if plan is None:
-                raise RuntimeError(
+                raise RayDPException(
                     f"Still cannot get the block rdd_{rdd_id}_{partition_id} after recache: the "
                     "recoverable RDD was released")
             table = plan.compute(partition_id).combine_chunks()

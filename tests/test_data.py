@@ -55,3 +55,29 @@ def test_to_torch_single_and_per_column_dtypes(ray_cluster):
     feats, y = next(iter(multi))
     assert isinstance(feats, list) and feats[0].dtype == torch.float32 and feats[1].dtype == torch.int64
     assert feats[1].shape == (5, 1)
+
+
+def test_legacy_torch_ml_dataset_and_prefetcher(ray_cluster):
+    """Reference names ``TorchMLDataset`` / ``PrefetchedDataLoader`` (``torch_ml_dataset.py:30-111``)."""
+    import pyarrow as pa
+    import torch
+    from torch.utils.data import DataLoader
+    from raydp_b200 import data as rdata
+    from raydp_b200.torch.torch_ml_dataset import PrefetchedDataLoader, TorchMLDataset
+    ds = rdata.from_arrow(pa.table({"a": [float(i) for i in range(100)], "b": [2.0 * i for i in range(100)],
+                                    "y": [3.0 * i for i in range(100)]}))
+    parts = [TorchMLDataset(ds, world_size=2, world_rank=r, feature_columns=["a", "b"], label_column="y")
+             for r in range(2)]
+    assert len(parts[0]) + len(parts[1]) == 100
+    seen = 0
+    for x, y in PrefetchedDataLoader(DataLoader(parts[0], batch_size=16), max_size=2):
+        assert x.shape[1] == 2 and torch.allclose(x[:, 0] * 3, y.reshape(-1))
+        seen += x.shape[0]
+    assert seen == len(parts[0])
+
+
+def test_legacy_parallel_iterator_worker():
+    from raydp_b200.spark.parallel_iterator_worker import ParallelIteratorWorkerWithLen
+    w = ParallelIteratorWorkerWithLen(lambda: range(3), repeat=True, num_records=3)
+    w.par_iter_init([lambda it: (v * 10 for v in it)])
+    assert [w.par_iter_next() for _ in range(5)] == [0, 10, 20, 0, 10] and len(w) == 3

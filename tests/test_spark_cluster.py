@@ -229,3 +229,24 @@ def test_dynamic_allocation_request_and_kill(ray_cluster):
     backend.kill_executors([1])
     assert backend.executor_actor_ids() == [0, 2]
     assert spark.range(0, 1000, numPartitions=6).count() == 1000
+    raydp.stop_spark()
+
+
+def test_external_shuffle_service_keeps_blocks_after_executor_kill(ray_cluster):
+    """``spark.shuffle.service.enabled``: one service actor per node owns the shuffle output, so it
+    stays readable after dynamic allocation kills the executor that wrote it (reference
+    ``RayAppMaster.scala:151-167``, ``RayExternalShuffleService.scala:26-57``)."""
+    from raydp_b200.spark.shuffle_service import service_name
+    spark = raydp.init_spark("shuf", 2, 1, "300M", configs={
+        "spark.dynamicAllocation.enabled": "true", "spark.dynamicAllocation.maxExecutors": "2",
+        "spark.dynamicAllocation.initialExecutors": "2", "spark.shuffle.service.enabled": "true"})
+    master = rt.get_actor("shuf_SPARK_MASTER")
+    nodes = rt.get(master.shuffle_service_nodes.remote())
+    assert len(nodes) == 1
+    service = rt.get_actor(service_name("shuf_SPARK_MASTER", nodes[0]))
+    shuffled = spark.range(0, 4000, numPartitions=4).repartition(3, "id")
+    assert rt.get(service.block_count.remote()) >= 3
+    spark._backend.kill_executors([1])
+    assert spark._backend.executor_actor_ids() == [0]
+    assert shuffled.count() == 4000 and shuffled.rdd.getNumPartitions() == 3
+    raydp.stop_spark()
