@@ -45,6 +45,12 @@ int num_sms();
 int make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
                       uint64_t pitch_elems, uint32_t box_rows, uint32_t box_cols);
 
+// CTA-pair (cta_group::2) large-GEMM kernels, gemm_2cta.cu
+int gemm2_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
+             const float* bias, int relu, cudaStream_t stream);
+int gemm2_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw, int Nw,
+                cudaStream_t stream);
+
 #ifdef __CUDACC__
 // ------------------------------------------------------------------------------------------
 // device helpers

@@ -27,6 +27,13 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
 // out[Mw,Nw] (fp32, += with atomics; zero it first) = sum_r g[r,:Mw]^T x[r,:Nw].
 int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
                    int Mw, int Nw, void* stream);
+// CTA-pair (cta_group::2, 256 x 256 cluster tile) kernels for large problems.  rdp_gemm_tn and
+// rdp_gemm_wgrad dispatch to them on their own (plain bf16 output, N % 256 == 0, >= 37 tiles); these
+// entry points force the path.  rdp_gemm2_tn: out (bf16) = relu?(a . b^T + bias), N % 256 == 0.
+int rdp_gemm2_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
+                 const float* bias, int relu, void* stream);
+int rdp_gemm2_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
+                    int Mw, int Nw, void* stream);
 
 // Allocation-free variant of rdp_gemm_tn's statistics path.  It has no counterpart in the
 // reference: it exists for callers that must not allocate device memory (a plugin inside a host

@@ -96,6 +96,27 @@ def gemm_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, *, mw: Optio
     return out
 
 
+def gemm2_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *,
+             bias: Optional[torch.Tensor] = None, relu: bool = False) -> torch.Tensor:
+    """``gemm_tn`` forced onto the CTA-pair (cta_group::2) kernel; ``b.shape[0] % 256 == 0``."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    M, K = a.shape
+    N = b.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    _check(lib().rdp_gemm2_tn(_ptr(a), _pitch(a), _ptr(b), _pitch(b), _ptr(out), _pitch(out), M, N, K,
+                              _ptr(bias), 1 if relu else 0, _stream()))
+    return out
+
+
+def gemm2_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """``gemm_wgrad`` forced onto the CTA-pair kernel."""
+    assert g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and out.dtype == torch.float32
+    _check(lib().rdp_gemm2_wgrad(_ptr(g), _pitch(g), _ptr(x), _pitch(x), _ptr(out), _pitch(out),
+                                 g.shape[0], g.shape[1], x.shape[1], _stream()))
+    return out
+
+
 def bn_fold(stats, count, gamma, beta, running_mean, running_var, momentum, eps, use_running,
             a, c, mean, rstd, w, b, w_folded, w_folded_t, b_folded) -> None:
     N, K = w.shape

@@ -9,6 +9,8 @@ SIGNATURES = {
     "rdp_num_sms": (I, []),
     "rdp_gemm_tn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP, I, VP, I, I, I, VP, VP]),
     "rdp_gemm_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, VP]),
+    "rdp_gemm2_tn": (I, [VP, I, VP, I, VP, I, I, I, I, VP, I, VP]),
+    "rdp_gemm2_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, VP]),
     "rdp_bn_fold": (I, [VP, F, VP, VP, VP, VP, F, F, I, VP, VP, VP, VP, VP, VP, I, I, VP, I, VP, I, VP, VP]),
     "rdp_cast_weight": (I, [VP, I, I, VP, I, VP, I, VP]),
     "rdp_bn_relu_bwd": (I, [VP, VP, VP, I, I, I, VP, VP, VP, VP, VP, VP, VP, I, VP]),

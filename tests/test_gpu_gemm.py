@@ -65,3 +65,46 @@ def test_gemm_wgrad(rows, Mw, Nw):
     torch.cuda.synchronize()
     err = (out - ref).abs().max().item()
     assert err <= 5e-3 * ref.abs().max().item() + 0.05, (rows, Mw, Nw, err)
+
+
+# ---- CTA-pair (cta_group::2) kernels ------------------------------------------------------------
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 512, 320), (300, 256, 128), (4096, 2560, 256),
+                                   (1000, 768, 1032)])
+def test_gemm2_tn_pair_kernel(M, N, K):
+    ops = _ops()
+    a, b = _rand(M, K), _rand(N, K)
+    bias = torch.randn(N, device="cuda")
+    out = ops.gemm2_tn(a, b, bias=bias, relu=True)
+    ref = torch.relu(a.float() @ b.float().t() + bias)
+    torch.cuda.synchronize()
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 0.02 * ref.abs().max().item() + 0.05, (M, N, K, err)
+    plain = ops.gemm2_tn(a, b)
+    ref2 = a.float() @ b.float().t()
+    assert (plain.float() - ref2).abs().max().item() <= 0.02 * ref2.abs().max().item() + 0.05
+
+
+@pytest.mark.parametrize("rows,Mw,Nw", [(64, 256, 256), (1000, 512, 768), (4096, 384, 264), (2048, 2304, 2048)])
+def test_gemm2_wgrad_pair_kernel(rows, Mw, Nw):
+    ops = _ops()
+    g, x = _rand(rows, Mw), _rand(rows, Nw)
+    out = torch.full((Mw, Nw), 0.25, device="cuda")
+    ops.gemm2_wgrad(g, x, out)
+    ref = g.float().t() @ x.float() + 0.25
+    torch.cuda.synchronize()
+    err = (out - ref).abs().max().item()
+    assert err <= 2e-3 * ref.abs().max().item() + 1e-2, (rows, Mw, Nw, err)
+
+
+def test_large_gemm_dispatches_to_pair_kernel_and_matches():
+    """rdp_gemm_tn / rdp_gemm_wgrad choose the pair kernels for big plain problems."""
+    ops = _ops()
+    a, b = _rand(2048, 1024), _rand(4096, 1024)
+    out = ops.gemm_tn(a, b)
+    ref = a.float() @ b.float().t()
+    assert (out.float() - ref).abs().max().item() <= 0.02 * ref.abs().max().item() + 0.05
+    g, x = _rand(1024, 4096), _rand(1024, 2048)
+    w = torch.zeros(4096, 2048, device="cuda")
+    ops.gemm_wgrad(g, x, w)
+    refw = g.float().t() @ x.float()
+    assert (w - refw).abs().max().item() <= 2e-3 * refw.abs().max().item() + 1e-2
