@@ -32,6 +32,8 @@ def main():
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--bucket-mb", type=int, default=512)
     ap.add_argument("--check", action="store_true", help="small model: compare against fp32 torch + all_reduce")
+    ap.add_argument("--breakdown", action="store_true",
+                    help="after timing, print the per-kernel time of one step (torch profiler; not a bench number)")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -132,6 +134,14 @@ def main():
         print(json.dumps({"impl": args.impl, "metric": "BigMLP train samples/sec", "n_gpus": world, "params": nparams,
                           "per_gpu_batch": B, "ms_per_step": ms, "value": world * B / (ms / 1e3),
                           "tflops_per_gpu": flops / (ms / 1e3) / 1e12, "overlap": not args.no_overlap}), flush=True)
+    if args.breakdown and rank == 0:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            step(0)
+            torch.cuda.synchronize()
+        rows = sorted(prof.key_averages(), key=lambda k: -k.device_time_total)[:14]
+        for k in rows:
+            print(f"  {k.device_time_total / 1e3:8.2f} ms  x{k.count:<4d} {k.key[:90]}", flush=True)
     if args.impl == "ours":
         dp.close()
     _finish(world)

@@ -42,20 +42,32 @@ def main():
     b = (torch.randn(N, K, device=dev) * 0.1).to(torch.bfloat16)
     out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
     flops = 2.0 * M * N * K
+
+    def compare(variants, rounds=3):
+        """Interleave the variants so clock/thermal drift hits all of them alike; report the median."""
+        got = {k: [] for k in variants}
+        for _ in range(rounds):
+            for name, fn in variants.items():
+                got[name].append(flops / timed(fn, args.iters) / 1e9)
+        return {k + "_tflops": round(sorted(v)[len(v) // 2], 1) for k, v in got.items()}
+
     res = {"op": "gemm_tn", "M": M, "N": N, "K": K}
-    res["pair_tflops"] = flops / timed(lambda: ops.gemm2_tn(a, b, out), args.iters) / 1e9
-    res["cublas_tflops"] = flops / timed(lambda: torch.matmul(a, b.t(), out=out), args.iters) / 1e9
+    res.update(compare({"pair256": lambda: ops.gemm2_tn(a, b, out, mh=1),
+                        "pair512": lambda: ops.gemm2_tn(a, b, out, mh=2),
+                        "cublas": lambda: torch.matmul(a, b.t(), out=out)}))
     ref = torch.matmul(a, b.t())
     ops.gemm2_tn(a, b, out)
     res["max_abs_diff_vs_cublas"] = float((out.float() - ref.float()).abs().max())
     print(json.dumps(res), flush=True)
+    del ref
     # wgrad: dW[N, K] += g[M, N]^T x[M, K]
     g = (torch.randn(M, N, device=dev) * 0.1).to(torch.bfloat16)
     w = torch.zeros(N, K, device=dev)
-    res = {"op": "gemm_wgrad", "rows": M, "Mw": N, "Nw": K}
-    res["pair_tflops"] = flops / timed(lambda: ops.gemm2_wgrad(g, a, w), args.iters) / 1e9
     wb = torch.empty(N, K, dtype=torch.bfloat16, device=dev)
-    res["cublas_tflops"] = flops / timed(lambda: torch.matmul(g.t(), a, out=wb), args.iters) / 1e9
+    res = {"op": "gemm_wgrad", "rows": M, "Mw": N, "Nw": K}
+    res.update(compare({"pair256": lambda: ops.gemm2_wgrad(g, a, w, mh=1),
+                        "pair512": lambda: ops.gemm2_wgrad(g, a, w, mh=2),
+                        "cublas_bf16_out": lambda: torch.matmul(g.t(), a, out=wb)}))
     w.zero_()
     ops.gemm2_wgrad(g, a, w)
     res["max_rel_diff_vs_cublas"] = float((w - torch.matmul(g.t(), a).float()).abs().max() / w.abs().max())

@@ -27,6 +27,7 @@
 #include "common.cuh"
 #include "raydp_b200.h"
 
+#include <cuda_bf16.h>
 #include <string.h>
 
 namespace rdp {
@@ -43,6 +44,7 @@ struct OptSpec {
   int adamw, nesterov;
   const float* lr_ptr;     // optional device scalars
   const float* step_ptr;
+  __nv_bfloat16* shadow;   // optional bf16 copy of the updated parameters (GEMM operand), n elements
 };
 
 struct RankArgs {
@@ -139,6 +141,10 @@ __device__ __forceinline__ void apply_update(const OptSpec& o, int64_t i, float4
     if (o.m) *reinterpret_cast<float4*>(o.m + i) = make_float4(bs[0], bs[1], bs[2], bs[3]);
   }
   *reinterpret_cast<float4*>(o.p + i) = make_float4(ps[0], ps[1], ps[2], ps[3]);
+  if (o.shadow != nullptr) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(ps[0], ps[1]), hi = __floats2bfloat162_rn(ps[2], ps[3]);
+    *reinterpret_cast<uint2*>(o.shadow + i) = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+  }
   if (out != nullptr) *reinterpret_cast<float4*>(out + i) = g;
 }
 
@@ -349,7 +355,8 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
     if (opts != nullptr) {
       const rdp_opt_args& o = opts[l];
       a.opt = OptSpec{o.kind, o.p, o.m, o.v, o.lr, o.beta1, o.beta2, o.eps, o.weight_decay, o.momentum,
-                      o.dampening, o.adamw, o.nesterov, o.lr_ptr, o.step_ptr};
+                      o.dampening, o.adamw, o.nesterov, o.lr_ptr, o.step_ptr,
+                      static_cast<__nv_bfloat16*>(o.shadow)};
     }
   }
   // algo 3: two-shot on send[0]/recv[0] only.  Safe without parity: the second flag round ends after every
@@ -497,7 +504,8 @@ extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* fl
   p.rank = rank; p.world = world; p.n = n; p.scale = scale; p.epoch = epoch; p.counters = counters; p.out = out;
   if (opt != nullptr)
     p.opt = OptSpec{opt->kind, opt->p, opt->m, opt->v, opt->lr, opt->beta1, opt->beta2, opt->eps, opt->weight_decay,
-                    opt->momentum, opt->dampening, opt->adamw, opt->nesterov, opt->lr_ptr, opt->step_ptr};
+                    opt->momentum, opt->dampening, opt->adamw, opt->nesterov, opt->lr_ptr, opt->step_ptr,
+                    static_cast<__nv_bfloat16*>(opt->shadow)};
   int64_t work = n / 4 / world / 4;
   int blocks = int((work + kArThreads - 1) / kArThreads);
   const int cap = num_sms();

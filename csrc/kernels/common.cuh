@@ -47,9 +47,11 @@ int make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_
 
 // CTA-pair (cta_group::2) large-GEMM kernels, gemm_2cta.cu
 int gemm2_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
-             const float* bias, int relu, cudaStream_t stream);
+             const float* bias, int relu, int mh, cudaStream_t stream);
+int gemm2_nn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K, int mh,
+             cudaStream_t stream);
 int gemm2_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw, int Nw,
-                cudaStream_t stream);
+                int mh, cudaStream_t stream);
 
 #ifdef __CUDACC__
 // ------------------------------------------------------------------------------------------

@@ -820,7 +820,7 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
   // large plain GEMMs: CTA-pair kernel, 256 x 256 tiles (at least half a wave of clusters, deep K)
   if (!out_f32 && stats_mode == 0 && !use_aux && N % 256 == 0 && K >= 512 &&
       ((M + 255) / 256) * (N / 256) >= num_sms() / 4)
-    return gemm2_tn(a, lda, b, ldb, out, ldc, M, N, K, bias, relu, cs);
+    return gemm2_tn(a, lda, b, ldb, out, ldc, M, N, K, bias, relu, 0, cs);
   if (!out_f32 && N % 64 == 0 && N <= kStatsCols) {
     GemmTnParams f = p;
     f.n_tile = (N % kFastNTile == 0) ? kFastNTile : 64;
@@ -851,7 +851,7 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
   RDP_REQUIRE(rows > 0 && Mw > 0 && Nw > 0, "rdp_gemm_wgrad: empty problem");
   RDP_REQUIRE(ldg % 8 == 0 && ldx % 8 == 0, "rdp_gemm_wgrad: pitches must be multiples of 8");
   if (ldo % 4 == 0 && Nw % 4 == 0 && rows >= 512 && ((Mw + 255) / 256) * ((Nw + 255) / 256) >= num_sms() / 4)
-    return gemm2_wgrad(g, ldg, x, ldx, out, ldo, rows, Mw, Nw, static_cast<cudaStream_t>(stream));
+    return gemm2_wgrad(g, ldg, x, ldx, out, ldo, rows, Mw, Nw, 0, static_cast<cudaStream_t>(stream));
   WgradParams p;
   p.rows = rows; p.Mw = Mw; p.Nw = Nw;
   int n_tile = ((Nw + 15) / 16) * 16;

@@ -102,6 +102,68 @@ __global__ void cast_weight_kernel(const float* __restrict__ w, int N, int K, __
   if (out_t != nullptr) out_t[size_t(k) * ldt + n] = v;
 }
 
+// contiguous fp32 -> bf16, 8 elements per thread (no transposed copy)
+__global__ void cast_bf16_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int64_t n8) {
+  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n8; i += int64_t(gridDim.x) * blockDim.x) {
+    const float4 a = reinterpret_cast<const float4*>(w)[2 * i], b = reinterpret_cast<const float4*>(w)[2 * i + 1];
+    reinterpret_cast<uint4*>(out)[i] = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w),
+                                                  pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// ReLU backward + bias gradient for generic Linear(+ReLU) layers: one pass over [M, N]
+//   g_out = (act > 0) ? g : 0   (act = the layer's ReLU output; skipped when act == nullptr)
+//   dbias[col] += sum over rows of g_out
+// Block = 32 column lanes (8 bf16 columns each = 256 columns) x 8 row lanes.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) relu_bwd_bias_kernel(const __nv_bfloat16* __restrict__ g,
+                                                            const __nv_bfloat16* __restrict__ act,
+                                                            __nv_bfloat16* __restrict__ g_out, float* __restrict__ dbias,
+                                                            int M, int N, int ld, int rows_per_block) {
+  __shared__ float red[8][256];
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cl) * 8;
+  const int r_begin = blockIdx.y * rows_per_block;
+  const int r_end = min(M, r_begin + rows_per_block);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (col < N) {
+    for (int r = r_begin + rl; r < r_end; r += 8) {
+      const size_t off = size_t(r) * ld + col;
+      uint4 gv = *reinterpret_cast<const uint4*>(g + off);
+      uint32_t* gu = reinterpret_cast<uint32_t*>(&gv);
+      if (act != nullptr) {
+        const uint4 av = *reinterpret_cast<const uint4*>(act + off);
+        const uint32_t* au = reinterpret_cast<const uint32_t*>(&av);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          // bf16 > 0  <=>  sign bit clear and magnitude non-zero
+          const uint32_t lo = au[i] & 0xffffu, hi = au[i] >> 16;
+          const uint32_t keep = (((lo & 0x8000u) == 0 && (lo & 0x7fffu) != 0) ? 0x0000ffffu : 0u) |
+                                (((hi & 0x8000u) == 0 && (hi & 0x7fffu) != 0) ? 0xffff0000u : 0u);
+          gu[i] &= keep;
+        }
+        *reinterpret_cast<uint4*>(g_out + off) = gv;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[2 * i] += __uint_as_float(gu[i] << 16);
+        acc[2 * i + 1] += __uint_as_float(gu[i] & 0xffff0000u);
+      }
+    }
+  }
+  if (dbias == nullptr) return;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[rl][cl * 8 + i] = acc[i];
+  __syncthreads();
+  const int c = threadIdx.x;                 // 256 threads <-> 256 columns of the block
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sum += red[j][c];
+  const int gc = blockIdx.x * 256 + c;
+  if (gc < N) atomicAdd(dbias + gc, sum);
+}
+
 // ------------------------------------------------------------------------------------------
 // BatchNorm + ReLU backward (elementwise, with column sums of the result for the bias grad)
 // ------------------------------------------------------------------------------------------
@@ -358,6 +420,7 @@ struct AdamParams {
   int adamw;
   const float* lr_ptr;   // optional device scalars (CUDA-graph friendly): lr, step count
   const float* step_ptr;
+  __nv_bfloat16* shadow; // optional bf16 copy of the updated parameters
 };
 
 __device__ __forceinline__ float adam_update(float p, float g, float& m, float& v, const AdamParams& a) {
@@ -369,6 +432,8 @@ __device__ __forceinline__ float adam_update(float p, float g, float& m, float& 
   return p - (a.lr / a.bc1) * (m / denom);
 }
 
+// kVec: 4 elements per thread with 16-byte accesses (pointers 16-byte aligned; the host checks)
+template <bool kVec>
 __global__ void adam_kernel(AdamParams a) {
   if (a.lr_ptr != nullptr) a.lr = *a.lr_ptr;
   if (a.step_ptr != nullptr) {
@@ -376,10 +441,32 @@ __global__ void adam_kernel(AdamParams a) {
     a.bc1 = 1.f - powf(a.beta1, t);
     a.bc2 = 1.f - powf(a.beta2, t);
   }
-  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < a.n; i += int64_t(gridDim.x) * blockDim.x) {
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, nth = int64_t(gridDim.x) * blockDim.x;
+  int64_t tail_begin = 0;
+  if (kVec) {
+    const int64_t n4 = a.n / 4;
+    for (int64_t i = tid; i < n4; i += nth) {
+      float4 p4 = reinterpret_cast<float4*>(a.p)[i], m4 = reinterpret_cast<float4*>(a.m)[i];
+      float4 v4 = reinterpret_cast<float4*>(a.v)[i];
+      const float4 g4 = reinterpret_cast<const float4*>(a.g)[i];
+      p4.x = adam_update(p4.x, g4.x, m4.x, v4.x, a);
+      p4.y = adam_update(p4.y, g4.y, m4.y, v4.y, a);
+      p4.z = adam_update(p4.z, g4.z, m4.z, v4.z, a);
+      p4.w = adam_update(p4.w, g4.w, m4.w, v4.w, a);
+      reinterpret_cast<float4*>(a.p)[i] = p4;
+      reinterpret_cast<float4*>(a.m)[i] = m4;
+      reinterpret_cast<float4*>(a.v)[i] = v4;
+      if (a.shadow != nullptr)
+        reinterpret_cast<uint2*>(a.shadow)[i] = make_uint2(pack_bf16x2(p4.x, p4.y), pack_bf16x2(p4.z, p4.w));
+    }
+    tail_begin = n4 * 4;
+  }
+  for (int64_t i = tail_begin + tid; i < a.n; i += nth) {
     float m = a.m[i], v = a.v[i];
-    a.p[i] = adam_update(a.p[i], a.g[i], m, v, a);
+    const float pn = adam_update(a.p[i], a.g[i], m, v, a);
+    a.p[i] = pn;
     a.m[i] = m; a.v[i] = v;
+    if (a.shadow != nullptr) a.shadow[i] = __float2bfloat16_rn(pn);
   }
 }
 
@@ -390,24 +477,53 @@ struct SgdParams {
   int nesterov, first_step;
   const float* lr_ptr;
   const float* step_ptr;   // first_step = (*step_ptr <= 1)
+  __nv_bfloat16* shadow;   // optional bf16 copy of the updated parameters
 };
 
 __global__ void add_scalar_kernel(float* x, float v) { *x += v; }
 
+__device__ __forceinline__ float sgd_update(float p, float g, float* buf, int64_t i, const SgdParams& s) {
+  g *= s.grad_scale;
+  if (s.weight_decay != 0.f) g += s.weight_decay * p;
+  if (buf != nullptr && s.momentum != 0.f) {
+    const float b = s.first_step ? g : s.momentum * buf[i] + (1.f - s.dampening) * g;
+    buf[i] = b;
+    g = s.nesterov ? g + s.momentum * b : b;
+  }
+  return p - s.lr * g;
+}
+
+template <bool kVec>
 __global__ void sgd_kernel(SgdParams s) {
   if (s.lr_ptr != nullptr) s.lr = *s.lr_ptr;
   if (s.step_ptr != nullptr) s.first_step = (*s.step_ptr <= 1.f) ? 1 : 0;
-  for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < s.n; i += int64_t(gridDim.x) * blockDim.x) {
-    float p = s.p[i];
-    float g = s.g[i] * s.grad_scale;
-    if (s.weight_decay != 0.f) g += s.weight_decay * p;
-    if (s.buf != nullptr && s.momentum != 0.f) {
-      float b = s.first_step ? g : s.momentum * s.buf[i] + (1.f - s.dampening) * g;
-      s.buf[i] = b;
-      g = s.nesterov ? g + s.momentum * b : b;
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, nth = int64_t(gridDim.x) * blockDim.x;
+  int64_t tail_begin = 0;
+  if (kVec) {
+    const int64_t n4 = s.n / 4;
+    for (int64_t i = tid; i < n4; i += nth) {
+      float4 p4 = reinterpret_cast<float4*>(s.p)[i];
+      const float4 g4 = reinterpret_cast<const float4*>(s.g)[i];
+      p4.x = sgd_update(p4.x, g4.x, s.buf, 4 * i, s);
+      p4.y = sgd_update(p4.y, g4.y, s.buf, 4 * i + 1, s);
+      p4.z = sgd_update(p4.z, g4.z, s.buf, 4 * i + 2, s);
+      p4.w = sgd_update(p4.w, g4.w, s.buf, 4 * i + 3, s);
+      reinterpret_cast<float4*>(s.p)[i] = p4;
+      if (s.shadow != nullptr)
+        reinterpret_cast<uint2*>(s.shadow)[i] = make_uint2(pack_bf16x2(p4.x, p4.y), pack_bf16x2(p4.z, p4.w));
     }
-    s.p[i] = p - s.lr * g;
+    tail_begin = n4 * 4;
   }
+  for (int64_t i = tail_begin + tid; i < s.n; i += nth) {
+    const float pn = sgd_update(s.p[i], s.g[i], s.buf, i, s);
+    s.p[i] = pn;
+    if (s.shadow != nullptr) s.shadow[i] = __float2bfloat16_rn(pn);
+  }
+}
+
+static inline bool aligned16(const void* a, const void* b, const void* c, const void* d, const void* e) {
+  return ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c) |
+           reinterpret_cast<uintptr_t>(d)) & 15) == 0 && (reinterpret_cast<uintptr_t>(e) & 7) == 0;
 }
 
 }  // namespace rdp
@@ -432,6 +548,15 @@ int rdp_bn_fold(const float* stats, float count, const float* gamma, const float
 
 int rdp_cast_weight(const float* w, int N, int K, void* out, int ldo, void* out_t, int ldt, void* stream) {
   const int total = N * K;
+  if (out_t == nullptr && ldo == K && total % 8 == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+    const int64_t n8 = total / 8;
+    int grid = int((n8 + 255) / 256);
+    if (grid > num_sms() * 16) grid = num_sms() * 16;
+    cast_bf16_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(w, static_cast<__nv_bfloat16*>(out), n8);
+    RDP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   cast_weight_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       w, N, K, static_cast<__nv_bfloat16*>(out), ldo, static_cast<__nv_bfloat16*>(out_t), ldt);
   RDP_CHECK_CUDA(cudaGetLastError());
@@ -487,25 +612,49 @@ int rdp_add_scalar(float* x, float v, void* stream) {
 
 int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                   float eps, float weight_decay, int step, float grad_scale, int adamw,
-                  const float* lr_ptr, const float* step_ptr, void* stream) {
+                  const float* lr_ptr, const float* step_ptr, void* shadow, void* stream) {
   AdamParams a{p, g, m, v, n, lr, beta1, beta2, eps, weight_decay,
                1.f - powf(beta1, float(step)), 1.f - powf(beta2, float(step)), grad_scale, adamw,
-               lr_ptr, step_ptr};
-  int grid = int((n + 255) / 256);
+               lr_ptr, step_ptr, static_cast<__nv_bfloat16*>(shadow)};
+  const bool vec = aligned16(p, g, m, v, shadow) && n >= 4;
+  int grid = int(((vec ? n / 4 : n) + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
-  adam_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  if (grid < 1) grid = 1;
+  if (vec) adam_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  else adam_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float dampening,
                  float weight_decay, int nesterov, int first_step, float grad_scale,
-                 const float* lr_ptr, const float* step_ptr, void* stream) {
+                 const float* lr_ptr, const float* step_ptr, void* shadow, void* stream) {
   SgdParams s{p, g, buf, n, lr, momentum, dampening, weight_decay, grad_scale, nesterov, first_step,
-              lr_ptr, step_ptr};
-  int grid = int((n + 255) / 256);
+              lr_ptr, step_ptr, static_cast<__nv_bfloat16*>(shadow)};
+  const bool vec = aligned16(p, g, buf, nullptr, shadow) && n >= 4;
+  int grid = int(((vec ? n / 4 : n) + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
-  sgd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);
+  if (grid < 1) grid = 1;
+  if (vec) sgd_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);
+  else sgd_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// g_out = relu'(act) * g (skipped when act is NULL), dbias[N] += column sums of the result.
+int rdp_relu_bwd_bias(const void* g, const void* act, void* g_out, float* dbias, int M, int N, int ld, void* stream) {
+  RDP_REQUIRE(N % 8 == 0 && ld % 8 == 0, "rdp_relu_bwd_bias: N=%d and ld=%d must be multiples of 8", N, ld);
+  RDP_REQUIRE(act == nullptr || g_out != nullptr, "rdp_relu_bwd_bias: g_out missing");
+  const int col_blocks = (N + 255) / 256;
+  int row_blocks = (num_sms() * 8 + col_blocks - 1) / col_blocks;
+  int rows_per_block = (M + row_blocks - 1) / row_blocks;
+  rows_per_block = ((rows_per_block + 7) / 8) * 8;
+  if (rows_per_block < 8) rows_per_block = 8;
+  row_blocks = (M + rows_per_block - 1) / rows_per_block;
+  dim3 grid(col_blocks, row_blocks);
+  relu_bwd_bias_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(g), static_cast<const __nv_bfloat16*>(act),
+      static_cast<__nv_bfloat16*>(g_out), dbias, M, N, ld, rows_per_block);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -30,10 +30,15 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
 // CTA-pair (cta_group::2, 256 x 256 cluster tile) kernels for large problems.  rdp_gemm_tn and
 // rdp_gemm_wgrad dispatch to them on their own (plain bf16 output, N % 256 == 0, >= 37 tiles); these
 // entry points force the path.  rdp_gemm2_tn: out (bf16) = relu?(a . b^T + bias), N % 256 == 0.
+// mh: 0 = choose, 1 = 256-row cluster tiles (TMEM double-buffered), 2 = 512-row cluster tiles.
 int rdp_gemm2_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
-                 const float* bias, int relu, void* stream);
+                 const float* bias, int relu, int mh, void* stream);
 int rdp_gemm2_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
-                    int Mw, int Nw, void* stream);
+                    int Mw, int Nw, int mh, void* stream);
+// out[M, N] (bf16) = a[M, K] . b[K, N] with b row-major (MN-major B operand): dgrad dX = dY . W straight
+// from the row-major weight, no transposed copy.  N % 256 == 0.
+int rdp_gemm2_nn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K, int mh,
+                 void* stream);
 
 // Allocation-free variant of rdp_gemm_tn's statistics path.  It has no counterpart in the
 // reference: it exists for callers that must not allocate device memory (a plugin inside a host
@@ -71,10 +76,15 @@ int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const floa
 // (lets a captured CUDA graph follow lr schedules and the Adam bias correction).
 int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                   float eps, float weight_decay, int step, float grad_scale, int adamw,
-                  const float* lr_ptr, const float* step_ptr, void* stream);
+                  const float* lr_ptr, const float* step_ptr, void* shadow, void* stream);
 int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float dampening,
                  float weight_decay, int nesterov, int first_step, float grad_scale,
-                 const float* lr_ptr, const float* step_ptr, void* stream);
+                 const float* lr_ptr, const float* step_ptr, void* shadow, void* stream);
+// (`shadow`: optional bf16 copy of the updated parameters, written by the same kernel so the GEMM
+//  operands never need a separate fp32 -> bf16 cast pass; NULL to skip.)
+// Generic Linear(+ReLU) backward helper: g_out = (act > 0) ? g : 0 (skipped when act == NULL) and
+// dbias[N] += column sums of the result, one pass over the [M, N] bf16 matrices.
+int rdp_relu_bwd_bias(const void* g, const void* act, void* g_out, float* dbias, int M, int N, int ld, void* stream);
 int rdp_add_scalar(float* x, float v, void* stream);
 // host (pinned or pageable) -> device async copy on `stream`
 int rdp_memcpy_h2d_async(void* dst, const void* src_host, uint64_t bytes, void* stream);
@@ -107,6 +117,7 @@ struct rdp_opt_args {
   float lr, beta1, beta2, eps, weight_decay, momentum, dampening;
   int adamw, nesterov;
   const float* lr_ptr; const float* step_ptr;   // optional device scalars (override lr / step)
+  void* shadow;                  // optional bf16 copy of the updated parameters (n elements), or NULL
 };
 // bases[q]: rank q's symmetric region as mapped in this process (host array of `world` pointers).
 // n_local_ranks = 1 (normal: ins/outs/epochs/counters/opts have one entry) or = world (single-GPU

@@ -104,10 +104,12 @@ class SymmetricMemory:
 
 
 def _opt_args(kind: int = 0, p=None, m=None, v=None, lr=0.0, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
-              momentum=0.0, dampening=0.0, adamw=False, nesterov=False, lr_dev=None, step_dev=None) -> OptArgs:
+              momentum=0.0, dampening=0.0, adamw=False, nesterov=False, lr_dev=None, step_dev=None,
+              shadow=None) -> OptArgs:
+    """``shadow``: optional bf16 tensor (same numel as ``p``) that receives the updated parameters."""
     ptr = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None  # noqa: E731
     return OptArgs(kind, ptr(p), ptr(m), ptr(v), lr, betas[0], betas[1], eps, weight_decay, momentum,
-                   dampening, 1 if adamw else 0, 1 if nesterov else 0, ptr(lr_dev), ptr(step_dev))
+                   dampening, 1 if adamw else 0, 1 if nesterov else 0, ptr(lr_dev), ptr(step_dev), ptr(shadow))
 
 
 def _launch(lib, bases: Sequence[int], slot_floats: int, rank: int, world: int, ins, outs, epochs, counters,

@@ -97,23 +97,24 @@ def gemm_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, *, mw: Optio
 
 
 def gemm2_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *,
-             bias: Optional[torch.Tensor] = None, relu: bool = False) -> torch.Tensor:
-    """``gemm_tn`` forced onto the CTA-pair (cta_group::2) kernel; ``b.shape[0] % 256 == 0``."""
+             bias: Optional[torch.Tensor] = None, relu: bool = False, mh: int = 0) -> torch.Tensor:
+    """``gemm_tn`` forced onto the CTA-pair (cta_group::2) kernel; ``b.shape[0] % 256 == 0``.
+    ``mh``: 0 = choose, 1 = 256-row cluster tiles, 2 = 512-row cluster tiles."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     M, K = a.shape
     N = b.shape[0]
     if out is None:
         out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
     _check(lib().rdp_gemm2_tn(_ptr(a), _pitch(a), _ptr(b), _pitch(b), _ptr(out), _pitch(out), M, N, K,
-                              _ptr(bias), 1 if relu else 0, _stream()))
+                              _ptr(bias), 1 if relu else 0, mh, _stream()))
     return out
 
 
-def gemm2_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+def gemm2_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, mh: int = 0) -> torch.Tensor:
     """``gemm_wgrad`` forced onto the CTA-pair kernel."""
     assert g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and out.dtype == torch.float32
     _check(lib().rdp_gemm2_wgrad(_ptr(g), _pitch(g), _ptr(x), _pitch(x), _ptr(out), _pitch(out),
-                                 g.shape[0], g.shape[1], x.shape[1], _stream()))
+                                 g.shape[0], g.shape[1], x.shape[1], mh, _stream()))
     return out
 
 
@@ -156,17 +157,42 @@ def mlp_head(z, a, c, w, bias, target, loss_kind: int, grad_scale: float, pred, 
 
 
 def adam_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, adamw=False,
-              lr_dev=None, step_dev=None) -> None:
+              lr_dev=None, step_dev=None, shadow=None) -> None:
+    """Fused Adam/AdamW over flat fp32 buffers; ``shadow`` (bf16, same numel) receives the updated
+    parameters in the same pass."""
     _check(lib().rdp_adam_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), lr, beta1, beta2, eps,
                                weight_decay, step, grad_scale, 1 if adamw else 0, _ptr(lr_dev),
-                               _ptr(step_dev), _stream()))
+                               _ptr(step_dev), _ptr(shadow), _stream()))
 
 
 def sgd_step(p, g, buf, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
-             first_step=False, grad_scale=1.0, lr_dev=None, step_dev=None) -> None:
+             first_step=False, grad_scale=1.0, lr_dev=None, step_dev=None, shadow=None) -> None:
     _check(lib().rdp_sgd_step(_ptr(p), _ptr(g), _ptr(buf), p.numel(), lr, momentum, dampening, weight_decay,
                               1 if nesterov else 0, 1 if first_step else 0, grad_scale, _ptr(lr_dev),
-                              _ptr(step_dev), _stream()))
+                              _ptr(step_dev), _ptr(shadow), _stream()))
+
+
+def relu_bwd_bias(g: torch.Tensor, act: Optional[torch.Tensor], dbias: Optional[torch.Tensor],
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out = where(act > 0, g, 0)`` (skipped when ``act`` is None) and ``dbias += out.sum(0)`` in one pass."""
+    assert g.dtype == torch.bfloat16 and g.dim() == 2
+    if act is not None and out is None:
+        out = torch.empty_like(g)
+    M, N = g.shape
+    _check(lib().rdp_relu_bwd_bias(_ptr(g), _ptr(act), _ptr(out), _ptr(dbias), M, N, _pitch(g), _stream()))
+    return out if act is not None else g
+
+
+def gemm2_nn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, mh: int = 0) -> torch.Tensor:
+    """``out[M,N] = a[M,K] @ b[K,N]`` (``b`` row-major: MN-major UMMA operand) on the CTA-pair kernel."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    M, K = a.shape
+    N = b.shape[1]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=a.device)
+    _check(lib().rdp_gemm2_nn(_ptr(a), _pitch(a), _ptr(b), _pitch(b), _ptr(out), _pitch(out), M, N, K, mh,
+                              _stream()))
+    return out
 
 
 def add_scalar(x: torch.Tensor, v: float) -> None:

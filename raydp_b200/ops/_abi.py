@@ -9,15 +9,17 @@ SIGNATURES = {
     "rdp_num_sms": (I, []),
     "rdp_gemm_tn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP, I, VP, I, I, I, VP, VP]),
     "rdp_gemm_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, VP]),
-    "rdp_gemm2_tn": (I, [VP, I, VP, I, VP, I, I, I, I, VP, I, VP]),
-    "rdp_gemm2_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, VP]),
+    "rdp_gemm2_tn": (I, [VP, I, VP, I, VP, I, I, I, I, VP, I, I, VP]),
+    "rdp_gemm2_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP]),
     "rdp_bn_fold": (I, [VP, F, VP, VP, VP, VP, F, F, I, VP, VP, VP, VP, VP, VP, I, I, VP, I, VP, I, VP, VP]),
     "rdp_cast_weight": (I, [VP, I, I, VP, I, VP, I, VP]),
     "rdp_bn_relu_bwd": (I, [VP, VP, VP, I, I, I, VP, VP, VP, VP, VP, VP, VP, I, VP]),
     "rdp_grad_fixup": (I, [VP, VP, VP, VP, I, I, VP]),
     "rdp_mlp_head": (I, [VP, I, I, I, VP, VP, VP, VP, VP, I, F, VP, VP, VP, VP, VP, VP, VP]),
-    "rdp_adam_step": (I, [VP, VP, VP, VP, I64, F, F, F, F, F, I, F, I, VP, VP, VP]),
-    "rdp_sgd_step": (I, [VP, VP, VP, I64, F, F, F, F, I, I, F, VP, VP, VP]),
+    "rdp_adam_step": (I, [VP, VP, VP, VP, I64, F, F, F, F, F, I, F, I, VP, VP, VP, VP]),
+    "rdp_sgd_step": (I, [VP, VP, VP, I64, F, F, F, F, I, I, F, VP, VP, VP, VP]),
+    "rdp_relu_bwd_bias": (I, [VP, VP, VP, VP, I, I, I, VP]),
+    "rdp_gemm2_nn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP]),
     "rdp_add_scalar": (I, [VP, F, VP]),
     "rdp_memcpy_h2d_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_memcpy_d2h_async": (I, [VP, VP, C.c_uint64, VP]),
@@ -28,7 +30,7 @@ SIGNATURES = {
 class OptArgs(C.Structure):
     _fields_ = [("kind", I), ("p", VP), ("m", VP), ("v", VP), ("lr", F), ("beta1", F), ("beta2", F),
                 ("eps", F), ("weight_decay", F), ("momentum", F), ("dampening", F), ("adamw", I),
-                ("nesterov", I), ("lr_ptr", VP), ("step_ptr", VP)]
+                ("nesterov", I), ("lr_ptr", VP), ("step_ptr", VP), ("shadow", VP)]
 
 
 SIGNATURES.update({

@@ -18,6 +18,9 @@ import torch.nn as nn
 from raydp_b200 import ops
 
 
+_PAIR_MIN_OUT = 37 * 256 * 256      # outputs below this stay on the 1-CTA kernels
+
+
 class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, layer, relu):
@@ -25,7 +28,7 @@ class _LinearFn(torch.autograd.Function):
         if x2.dtype != torch.bfloat16:
             x2 = x2.to(torch.bfloat16)
         x2 = x2.contiguous()
-        w_bf, _ = layer._shadows()
+        w_bf, _ = layer._shadows(need_transpose=False)
         out = torch.empty(x2.shape[0], layer.out_features, dtype=torch.bfloat16, device=x.device)
         ops.gemm_tn(x2, w_bf, out, bias=bias, relu=relu)
         ctx.layer, ctx.relu = layer, relu
@@ -41,25 +44,30 @@ class _LinearFn(torch.autograd.Function):
         if g.dtype != torch.bfloat16:
             g = g.to(torch.bfloat16)
         g = g.contiguous()
-        if ctx.relu:
-            g = torch.where(out > 0, g, torch.zeros_like(g))
-        _, w_t = layer._shadows()
+        # one pass: ReLU mask (when the layer is fused with ReLU) + bias gradient column sums
+        db = None
+        if layer.bias is not None:
+            if layer.bias.grad is None:
+                layer.bias.grad = torch.zeros_like(layer.bias)
+            db = layer.bias.grad
+        if ctx.relu or db is not None:
+            g = ops.relu_bwd_bias(g, out if ctx.relu else None, db)
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty(x2.shape[0], layer.in_features, dtype=torch.bfloat16, device=g.device)
-            ops.gemm_tn(g, w_t, dx)
+            if layer.in_features % 256 == 0 and x2.shape[0] * layer.in_features >= _PAIR_MIN_OUT:
+                # dX = dY . W with the row-major weight as an MN-major operand: no transposed copy
+                w_bf, _ = layer._shadows(need_transpose=False)
+                ops.gemm2_nn(g, w_bf, dx)
+            else:
+                _, w_t = layer._shadows(need_transpose=True)
+                ops.gemm_tn(g, w_t, dx)
             dx = dx.reshape(ctx.in_shape)
         # fp32 accumulation straight into the parameter's gradient buffer
         w = layer.weight
         if w.grad is None:
             w.grad = torch.zeros_like(w)
         ops.gemm_wgrad(g, x2, w.grad)
-        if layer.bias is not None:
-            db = g.float().sum(0)
-            if layer.bias.grad is None:
-                layer.bias.grad = db
-            else:
-                layer.bias.grad.add_(db)
         layer._fire_grad_hooks()
         return dx, None, None, None, None
 
@@ -79,22 +87,47 @@ class FusedLinear(nn.Module):
         self._w_bf: Optional[torch.Tensor] = None
         self._w_t: Optional[torch.Tensor] = None
         self._shadow_version = -1
+        self._external: Optional[torch.Tensor] = None
+        self._t_version, self._t_stale = -1, True
         self._grad_ready_hooks = []
 
-    def _shadows(self):
+    def _shadows(self, need_transpose: bool = True):
+        """bf16 operand copies of the weight: ``(w_bf [out, in], w_t [in, out] or None)``.  With an
+        external shadow (see :meth:`use_external_shadow`) ``w_bf`` is maintained by the optimizer
+        kernel and never re-cast here; the transposed copy is only built for shapes whose dgrad
+        cannot take the row-major weight directly."""
         w = self.weight
+        if self._external is not None:
+            if need_transpose:
+                if self._w_t is None:
+                    self._w_t = torch.empty(self.in_features, self.out_features, dtype=torch.bfloat16, device=w.device)
+                if self._t_version != w._version or self._t_stale:
+                    self._w_t.copy_(self._external.t())
+                    self._t_version, self._t_stale = w._version, False
+            return self._external, self._w_t
         if self._w_bf is None or self._w_bf.device != w.device:
             self._w_bf = torch.empty(self.out_features, self.in_features, dtype=torch.bfloat16, device=w.device)
+            self._shadow_version = -1
+        if need_transpose and (self._w_t is None or self._w_t.device != w.device):
             self._w_t = torch.empty(self.in_features, self.out_features, dtype=torch.bfloat16, device=w.device)
             self._shadow_version = -1
-        if self._shadow_version != w._version:
-            ops.cast_weight(w.detach(), self._w_bf, self._w_t)
+        if self._shadow_version != w._version or (need_transpose and self._t_stale):
+            ops.cast_weight(w.detach(), self._w_bf, self._w_t if need_transpose else None)
             self._shadow_version = w._version
+            self._t_stale = not need_transpose
         return self._w_bf, self._w_t
+
+    def use_external_shadow(self, shadow: torch.Tensor) -> None:
+        """``shadow``: a bf16 ``[out, in]`` tensor that some other kernel (the fused optimizer) keeps
+        equal to the weight; it must already hold the current values."""
+        assert shadow.shape == self.weight.shape and shadow.dtype == torch.bfloat16
+        self._external = shadow
+        self._w_bf = None
 
     def invalidate_shadow(self) -> None:
         """Call after the parameter storage was updated by a kernel torch does not see."""
         self._shadow_version = -1
+        self._t_stale = True
 
     def _fire_grad_hooks(self) -> None:
         for hook in self._grad_ready_hooks:

@@ -31,12 +31,15 @@ class _Bucket:
         self.offsets, off = [], 0
         for p in params:
             self.offsets.append(off)
-            off += (p.numel() + 3) // 4 * 4
+            off += (p.numel() + 7) // 8 * 8      # 16-byte aligned in the bf16 shadow too (TMA base)
         self.n = off
         f32 = dict(dtype=torch.float32, device=device)
         self.flat = torch.zeros(self.n, **f32)
         self.m = torch.zeros(self.n, **f32)
         self.v = torch.zeros(self.n, **f32)
+        # bf16 copy of the parameters, rewritten by the optimizer kernel itself: FusedLinear layers
+        # take their GEMM operands from it, so no fp32 -> bf16 cast pass runs per step
+        self.shadow = torch.zeros(self.n, dtype=torch.bfloat16, device=device)
         self.reducer = None
         if world > 1:
             from raydp_b200.comm import P2PReducer
@@ -49,6 +52,11 @@ class _Bucket:
                 self.flat[o:o + p.numel()].copy_(p.detach().reshape(-1))
                 p.data = self.flat[o:o + p.numel()].view(p.shape)
                 p.grad = self.grads[o:o + p.numel()].view(p.shape)
+            self.shadow.copy_(self.flat)
+
+    def shadow_of(self, p: nn.Parameter) -> torch.Tensor:
+        o = self.offsets[[id(q) for q in self.params].index(id(p))]
+        return self.shadow[o:o + p.numel()].view(p.shape)
         self.pending = len(params)
         self.done_event: Optional[torch.cuda.Event] = None
 
@@ -99,6 +107,7 @@ class FusedDataParallel(nn.Module):
         fused_b = {id(m.bias) for m in self._fused_linears if m.bias is not None}
         for m in self._fused_linears:
             m._grad_ready_hooks.append(self._fused_linear_ready)
+            m.use_external_shadow(self._bucket_of[id(m.weight)].shadow_of(m.weight))
         for p in params:
             if id(p) not in fused_w and id(p) not in fused_b:
                 p.register_post_accumulate_grad_hook(self._param_ready)
@@ -118,9 +127,10 @@ class FusedDataParallel(nn.Module):
     def _opt_args(self, b: _Bucket):
         from raydp_b200.comm import make_opt_args
         if self.kind == 1:
-            return make_opt_args(1, b.flat, b.m, b.v, lr_dev=self.lr_dev, step_dev=self.step_dev, **self.hp)
+            return make_opt_args(1, b.flat, b.m, b.v, lr_dev=self.lr_dev, step_dev=self.step_dev, shadow=b.shadow,
+                                 **self.hp)
         return make_opt_args(2, b.flat, b.m if self.hp["momentum"] else None, None, lr_dev=self.lr_dev,
-                             step_dev=self.step_dev, **self.hp)
+                             step_dev=self.step_dev, shadow=b.shadow, **self.hp)
 
     def _reduce_and_update(self, b: _Bucket) -> None:
         compute = torch.cuda.current_stream(self.device)
@@ -134,11 +144,12 @@ class FusedDataParallel(nn.Module):
                 b.reducer.allreduce_step_(self._opt_args(b), 1.0 / self.world)
             elif self.kind == 1:
                 ops.adam_step(b.flat, b.grads, b.m, b.v, 0.0, self.hp["betas"][0], self.hp["betas"][1], self.hp["eps"],
-                              self.hp["weight_decay"], 1, 1.0, self.hp["adamw"], self.lr_dev, self.step_dev)
+                              self.hp["weight_decay"], 1, 1.0, self.hp["adamw"], self.lr_dev, self.step_dev,
+                              shadow=b.shadow)
             else:
                 ops.sgd_step(b.flat, b.grads, b.m if self.hp["momentum"] else None, 0.0, self.hp["momentum"],
                              self.hp["dampening"], self.hp["weight_decay"], self.hp["nesterov"], False, 1.0,
-                             self.lr_dev, self.step_dev)
+                             self.lr_dev, self.step_dev, shadow=b.shadow)
             b.grads.zero_()
             b.done_event = torch.cuda.Event()
             b.done_event.record(stream)

@@ -128,6 +128,38 @@ def test_optimizer_kernels_match_torch():
     assert torch.allclose(p, p_ref.detach(), rtol=1e-5, atol=1e-6)
 
 
+def test_optimizer_kernels_write_bf16_shadow():
+    """The fused optimizer writes the bf16 GEMM-operand copy of the parameters in the same pass
+    (vectorised body + scalar tail: n is not a multiple of 4)."""
+    from raydp_b200 import ops
+    torch.manual_seed(1)
+    n = 40007
+    p, g = torch.randn(n, device="cuda"), torch.randn(n, device="cuda")
+    m, v = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    shadow = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    ops.adam_step(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, 0.0, 1, 1.0, False, shadow=shadow)
+    assert torch.equal(shadow, p.to(torch.bfloat16))
+    buf = torch.zeros(n, device="cuda")
+    ops.sgd_step(p, g, buf, 0.1, 0.9, 0.0, 0.0, False, True, shadow=shadow)
+    assert torch.equal(shadow, p.to(torch.bfloat16))
+
+
+def test_relu_bwd_bias_kernel():
+    from raydp_b200 import ops
+    torch.manual_seed(2)
+    M, N = 3001, 520
+    g = torch.randn(M, N, device="cuda").to(torch.bfloat16)
+    act = torch.relu(torch.randn(M, N, device="cuda")).to(torch.bfloat16)
+    db = torch.full((N,), 0.5, device="cuda")
+    out = ops.relu_bwd_bias(g, act, db)
+    ref = torch.where(act > 0, g, torch.zeros_like(g))
+    assert torch.equal(out, ref)
+    assert torch.allclose(db, ref.float().sum(0) + 0.5, rtol=1e-3, atol=5e-2)
+    db2 = torch.zeros(N, device="cuda")
+    same = ops.relu_bwd_bias(g, None, db2)
+    assert same is g and torch.allclose(db2, g.float().sum(0), rtol=1e-3, atol=5e-2)
+
+
 def test_ingest_pack_matches_torch():
     from raydp_b200 import ops
     rows = 10007

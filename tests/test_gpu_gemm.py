@@ -68,28 +68,31 @@ def test_gemm_wgrad(rows, Mw, Nw):
 
 
 # ---- CTA-pair (cta_group::2) kernels ------------------------------------------------------------
+@pytest.mark.parametrize("mh", [1, 2])
 @pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 512, 320), (300, 256, 128), (4096, 2560, 256),
-                                   (1000, 768, 1032)])
-def test_gemm2_tn_pair_kernel(M, N, K):
+                                   (1000, 768, 1032), (9000, 3072, 128)])
+def test_gemm2_tn_pair_kernel(M, N, K, mh):
     ops = _ops()
     a, b = _rand(M, K), _rand(N, K)
     bias = torch.randn(N, device="cuda")
-    out = ops.gemm2_tn(a, b, bias=bias, relu=True)
+    out = ops.gemm2_tn(a, b, bias=bias, relu=True, mh=mh)
     ref = torch.relu(a.float() @ b.float().t() + bias)
     torch.cuda.synchronize()
     err = (out.float() - ref).abs().max().item()
     assert err <= 0.02 * ref.abs().max().item() + 0.05, (M, N, K, err)
-    plain = ops.gemm2_tn(a, b)
+    plain = ops.gemm2_tn(a, b, mh=mh)
     ref2 = a.float() @ b.float().t()
     assert (plain.float() - ref2).abs().max().item() <= 0.02 * ref2.abs().max().item() + 0.05
 
 
-@pytest.mark.parametrize("rows,Mw,Nw", [(64, 256, 256), (1000, 512, 768), (4096, 384, 264), (2048, 2304, 2048)])
-def test_gemm2_wgrad_pair_kernel(rows, Mw, Nw):
+@pytest.mark.parametrize("mh", [1, 2])
+@pytest.mark.parametrize("rows,Mw,Nw", [(64, 256, 256), (1000, 512, 768), (4096, 384, 264), (2048, 2304, 2048),
+                                       (512, 6144, 3328)])
+def test_gemm2_wgrad_pair_kernel(rows, Mw, Nw, mh):
     ops = _ops()
     g, x = _rand(rows, Mw), _rand(rows, Nw)
     out = torch.full((Mw, Nw), 0.25, device="cuda")
-    ops.gemm2_wgrad(g, x, out)
+    ops.gemm2_wgrad(g, x, out, mh=mh)
     ref = g.float().t() @ x.float() + 0.25
     torch.cuda.synchronize()
     err = (out - ref).abs().max().item()
@@ -108,3 +111,40 @@ def test_large_gemm_dispatches_to_pair_kernel_and_matches():
     ops.gemm_wgrad(g, x, w)
     refw = g.float().t() @ x.float()
     assert (w - refw).abs().max().item() <= 2e-3 * refw.abs().max().item() + 1e-2
+
+
+@pytest.mark.parametrize("mh", [1, 2])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (700, 512, 200), (4096, 1024, 768), (1536, 3328, 512)])
+def test_gemm2_nn_pair_kernel(M, N, K, mh):
+    """dgrad shape: out = a @ b with b row-major [K, N] (MN-major B operand, no transposed weight copy)."""
+    ops = _ops()
+    a, b = _rand(M, K), _rand(K, N)
+    out = ops.gemm2_nn(a, b, mh=mh)
+    ref = a.float() @ b.float()
+    torch.cuda.synchronize()
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 0.02 * ref.abs().max().item() + 0.05, (M, N, K, err)
+
+
+def test_fused_linear_matches_torch_on_pair_kernel_shapes():
+    """FusedLinear fwd/bwd (pair kernels: TN fwd, NN dgrad, MN-major wgrad, fused ReLU-mask + bias grad)."""
+    from raydp_b200.ops.linear import FusedLinear
+    torch.manual_seed(0)
+    lin = FusedLinear(1024, 2560, relu=True).cuda()
+    with torch.no_grad():      # bf16-representable values: the ReLU masks of both sides then agree
+        lin.weight.copy_(lin.weight.to(torch.bfloat16).float())
+    ref = torch.nn.Linear(1024, 2560).cuda()
+    ref.load_state_dict(lin.state_dict())
+    x = torch.randn(4096, 1024, device="cuda").to(torch.bfloat16).float()
+    xr = x.clone().requires_grad_(True)
+    xf = x.clone().requires_grad_(True)
+    y = lin(xf.to(torch.bfloat16))
+    yr = torch.relu(ref(xr))
+    go = torch.randn_like(yr).to(torch.bfloat16).float()
+    y.backward(go.to(torch.bfloat16))
+    yr.backward(go)
+    rel = lambda a, b: ((a.float() - b.float()).norm() / b.float().norm()).item()  # noqa: E731
+    assert rel(y, yr) < 2e-2
+    assert rel(xf.grad, xr.grad) < 3e-2
+    assert rel(lin.weight.grad, ref.weight.grad) < 3e-2
+    assert rel(lin.bias.grad, ref.bias.grad) < 3e-2
