@@ -100,7 +100,7 @@ def test_dlrm_estimator_single_gpu(ray_cluster):
     est = TorchEstimator(num_workers=1, resources_per_worker={"GPU": 1}, model=model,
                          optimizer=torch.optim.SGD(model.parameters(), lr=0.5), loss=nn.BCEWithLogitsLoss(),
                          feature_columns=features, feature_types=[torch.float] * 13 + [torch.long] * 26,
-                         label_column="label", label_type=torch.float, batch_size=1024, num_epochs=10,
+                         label_column="label", label_type=torch.float, batch_size=1024, num_epochs=24,
                          shuffle=False, drop_last=True, metrics_name=["Accuracy"])
     est.fit(ds, ds)
     train = [h for h in est.results.metrics_history if "train_loss" in h]
