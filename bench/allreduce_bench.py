@@ -103,6 +103,7 @@ def main():
             nv = NvlsReducer(n, torch.device("cuda", local))
             nv.buffer.copy_(x)
             res["nvls_us"] = timed(lambda: nv.allreduce_(), iters)
+            res["nvls_overlap_shape_us"] = timed(lambda: nv.allreduce_(overlap=True), iters)
             nv.close()
         best = min(v for k, v in res.items() if k.endswith("_us") and k != "nccl_us")
         factor = 2 * (world - 1) / world * n * 4

@@ -52,8 +52,14 @@ def main():
         return {k + "_tflops": round(sorted(v)[len(v) // 2], 1) for k, v in got.items()}
 
     res = {"op": "gemm_tn", "M": M, "N": N, "K": K}
+    def dyn512():
+        ops.set_dynamic_tiles(True)
+        ops.gemm2_tn(a, b, out, mh=2)
+        ops.set_dynamic_tiles(False)
+
     res.update(compare({"pair256": lambda: ops.gemm2_tn(a, b, out, mh=1),
                         "pair512": lambda: ops.gemm2_tn(a, b, out, mh=2),
+                        "pair512_clc": dyn512,
                         "cublas": lambda: torch.matmul(a, b.t(), out=out)}))
     ref = torch.matmul(a, b.t())
     ops.gemm2_tn(a, b, out)

@@ -431,8 +431,7 @@ __device__ __forceinline__ void flags_signal_and_wait(uint32_t* const* flags, in
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kArThreads)
-nvls_allreduce_kernel(const __grid_constant__ NvlsParams p) {
+__device__ __forceinline__ void nvls_allreduce_body(const NvlsParams& p) {
   const int nblocks = gridDim.x;
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
   const int64_t n4 = p.n / 4;
@@ -488,11 +487,24 @@ nvls_allreduce_kernel(const __grid_constant__ NvlsParams p) {
   }
 }
 
+__global__ void __launch_bounds__(kArThreads)
+nvls_allreduce_kernel(const __grid_constant__ NvlsParams p) { nvls_allreduce_body(p); }
+
+// Overlap shape: 256 threads and at most 40 registers per thread, one block per SM.  That is
+// 10 K registers, which fits NEXT TO a resident GEMM CTA (the 512-row pair kernel holds 320 x 168 =
+// 54 K of the SM's 64 K registers), so the all-reduce + optimizer of one gradient bucket really
+// runs concurrently with the backward GEMMs of the next layers instead of queueing behind their
+// persistent CTAs.  148 x 256 threads x 4 x 16 B in flight is still enough to fill the NVLink pipe.
+constexpr int kArOverlapThreads = 256;
+// (min 6 blocks/SM in the launch bounds is how the 40-register cap is expressed)
+__global__ void __launch_bounds__(kArOverlapThreads, 6)
+nvls_allreduce_overlap_kernel(const __grid_constant__ NvlsParams p) { nvls_allreduce_body(p); }
+
 }  // namespace rdp
 
 extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
                                   uint32_t* epoch, uint32_t* counters, const rdp_opt_args* opt, float* out,
-                                  int64_t n, float scale, void* stream) {
+                                  int64_t n, float scale, int overlap_shape, void* stream) {
   using namespace rdp;
   RDP_REQUIRE(mc_ptr != nullptr, "rdp_allreduce_nvls: no multicast mapping (NVLS unsupported on this system)");
   RDP_REQUIRE(world >= 1 && world <= kMaxRanks && n > 0 && n % 4 == 0, "rdp_allreduce_nvls: bad world/n");
@@ -507,11 +519,13 @@ extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* fl
                     opt->momentum, opt->dampening, opt->adamw, opt->nesterov, opt->lr_ptr, opt->step_ptr,
                     static_cast<__nv_bfloat16*>(opt->shadow)};
   int64_t work = n / 4 / world / 4;
-  int blocks = int((work + kArThreads - 1) / kArThreads);
+  const int threads = overlap_shape ? kArOverlapThreads : kArThreads;
+  int blocks = int((work + threads - 1) / threads);
   const int cap = num_sms();
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  nvls_allreduce_kernel<<<blocks, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  if (overlap_shape) nvls_allreduce_overlap_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  else nvls_allreduce_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -23,6 +23,8 @@
 // 74 clusters in flight share a small set of A/B panels in the 126 MB L2.
 #include "common.cuh"
 
+#include <stdlib.h>
+
 namespace rdp {
 
 constexpr int k2Threads = 192;
@@ -104,6 +106,57 @@ __device__ __forceinline__ void tma_store_wait_read_le1() {
   asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
 }
 
+// ---- cluster launch control: hardware work stealing for persistent clusters -------------------
+// The grid has one cluster per output tile.  A running cluster asks the hardware to cancel a cluster
+// that has not been launched yet and, if that succeeds, computes the cancelled cluster's tile
+// itself.  Unlike a static "tile += gridDim" loop this keeps working when only some clusters are
+// resident -- e.g. while blocks of an overlapped all-reduce kernel occupy a few SMs: the resident
+// clusters simply take more tiles, and the others join as SMs free up.
+// One slot: a cluster claims at most ONE tile ahead of the one it is computing (its producer warp
+// prefetches that tile's operands); deeper rings only hoard tiles and unbalance the tail.
+constexpr int kClcSlots = 1;
+__device__ __forceinline__ void clc_try_cancel(void* response16, uint64_t* bar) {
+  asm volatile(
+      "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128"
+      " [%0], [%1];" ::"r"(smem_u32(response16)), "r"(smem_u32(bar)) : "memory");
+}
+// tile index of the cancelled cluster (its first CTA id / 2), or -1 when nothing was left to cancel
+__device__ __forceinline__ int clc_decode(const void* response16) {
+  uint32_t x, valid;
+  asm volatile(
+      "{\n\t.reg .pred p1;\n\t.reg .b128 r;\n\t"
+      "ld.shared.b128 r, [%2];\n\t"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n\t"
+      "selp.u32 %1, 1, 0, p1;\n\t"
+      "mov.u32 %0, 0;\n\t"
+      "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid::x.b32.b128 %0, r;\n\t}"
+      : "=r"(x), "=r"(valid) : "r"(smem_u32(response16)) : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  return valid ? int(x >> 1) : -1;
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;"
+               ::"r"(cluster_addr), "r"(bytes) : "memory");
+}
+
+// Per-role cursor over the tiles of this cluster: static stride, or the CLC response ring.
+struct TileCursor {
+  uint8_t* resp;          // [kClcSlots][16]   (this CTA's copy of the responses)
+  uint64_t* full;         // [kClcSlots]
+  uint64_t* empty;        // [kClcSlots]       (the SCHEDULER CTA's barriers are the ones that count)
+  int slot;
+  uint32_t phase;
+  int stride, limit;      // static mode
+  __device__ __forceinline__ int next(bool dynamic, int t, bool arriving_lane) {
+    if (!dynamic) return (t + stride < limit) ? t + stride : -1;
+    mbar_wait(&full[slot], phase);
+    const int nt = clc_decode(resp + slot * 16);
+    if (arriving_lane) mbar_arrive_cluster(map_to_cta(smem_u32(&empty[slot]), 1));
+    if (++slot == kClcSlots) { slot = 0; phase ^= 1; }
+    return nt;
+  }
+};
+
 __device__ __forceinline__ void tile_coords(const Gemm2Params& p, int t, int& m_blk, int& n_blk) {
   const int per_group = p.group_m * p.num_n_tiles;
   const int g = t / per_group, in_g = t - g * per_group;
@@ -125,7 +178,7 @@ __device__ __forceinline__ void tile_coords(const Gemm2Params& p, int t, int& m_
 //        1 = wgrad (A MN-major [rows,Mw], B MN-major [rows,Nw]),  fp32 += output
 //        2 = NN  (A K-major [M,K], B MN-major [K,N]),             bf16 output -- dgrad dX = dY . W
 //            straight from the row-major weight, no transposed copy
-template <int kMode, int kMH>
+template <int kMode, int kMH, bool kDynamic>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 128 * kMH, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_c, const Gemm2Params p) {
@@ -145,6 +198,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tmem_full = empty_bar + kS;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint8_t* clc_resp = reinterpret_cast<uint8_t*>(tmem_ptr + 4);          // 16-byte aligned
+  uint64_t* clc_full = reinterpret_cast<uint64_t*>(clc_resp + kClcSlots * 16);
+  uint64_t* clc_empty = clc_full + kClcSlots;
+  constexpr uint32_t kClcConsumers = 3 + 8 * kMH;   // 2 producers + MMA warp + epilogue warps of both CTAs
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -153,6 +210,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  TileCursor cursor{clc_resp, clc_full, clc_empty, 0, 0u, num_clusters, num_tiles};
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -165,6 +223,10 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full[a], 1);           // multicast tcgen05.commit
       mbar_init(&tmem_empty[a], 2 * 4 * kMH);   // one arrival per epilogue warp of either CTA
+    }
+    for (int i = 0; i < kClcSlots; ++i) {
+      mbar_init(&clc_full[i], 1);            // armed remotely by the scheduler warp (expect_tx 16 B)
+      mbar_init(&clc_empty[i], kClcConsumers);
     }
     mbar_fence_init();
   }
@@ -179,7 +241,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      for (int t = cluster_id; t >= 0; t = cursor.next(kDynamic, t, true)) {
         int m_blk, n_blk;
         tile_coords(p, t, m_blk, n_blk);
         const int a_row = (m_blk * 2 + int(rank)) * kRowsPerCta;   // this CTA's rows of the M extent
@@ -230,7 +292,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       constexpr uint64_t kBStep = kBmn ? (2048 >> 4) : (32 >> 4);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+      for (int t = cluster_id; t >= 0; t = cursor.next(kDynamic, t, lane == 0)) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + uint32_t(acc) * 256;
@@ -255,6 +317,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
         if (++acc == kAccBufs) { acc = 0; acc_phase ^= 1; }
       }
+    } else if (kDynamic) {
+      // ===================== tile scheduler (the otherwise idle warp 1 of CTA 1) =====================
+      int slot = 0;
+      uint32_t phase = 0;
+      while (true) {
+        mbar_wait(&clc_empty[slot], phase ^ 1);              // every consumer has read the old response
+        if (lane < 2) mbar_expect_tx_cluster(map_to_cta(smem_u32(&clc_full[slot]), uint32_t(lane)), 16);
+        __syncwarp();
+        if (elect_one()) clc_try_cancel(clc_resp + slot * 16, &clc_full[slot]);
+        mbar_wait(&clc_full[slot], phase);
+        const int nt = clc_decode(clc_resp + slot * 16);
+        if (++slot == kClcSlots) { slot = 0; phase ^= 1; }
+        if (nt < 0) break;                                   // nothing left: the consumers see the same answer
+      }
     }
   } else {
     // ===================== epilogue warps (both CTAs, own rows) =====================
@@ -266,7 +342,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int bar_id = 1 + h;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = cluster_id; t < num_tiles; t += num_clusters) {
+    for (int t = cluster_id; t >= 0; t = cursor.next(kDynamic, t, lane == 0)) {
       int m_blk, n_blk;
       tile_coords(p, t, m_blk, n_blk);
       const int row0 = (m_blk * 2 + int(rank)) * kRowsPerCta + h * 128;
@@ -366,18 +442,33 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   }
 }
 
+// Tile schedule of the pair kernels.  Static (74 persistent clusters, tile += 74) wastes the least
+// at the tail when the GEMM owns the GPU; dynamic (cluster launch control) is for GEMMs that share
+// the SMs with an overlapped all-reduce.  rdp_gemm_set_dynamic_tiles() / RAYDP_B200_DYNAMIC_TILES=1.
+static int g_dynamic_tiles = -1;
+static bool dynamic_tiles() {
+  if (g_dynamic_tiles < 0) {
+    const char* e = getenv("RAYDP_B200_DYNAMIC_TILES");
+    g_dynamic_tiles = (e != nullptr && e[0] == '1') ? 1 : 0;
+  }
+  return g_dynamic_tiles == 1;
+}
+void gemm2_set_dynamic_tiles(int on) { g_dynamic_tiles = on ? 1 : 0; }
+
 template <int kMode, int kMH>
 static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, Gemm2Params p,
                        cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<kMode, kMH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        227 * 1024));
+    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<kMode, kMH, true>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<kMode, kMH, false>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
   constexpr bool kWgrad = kMode == 1;
   constexpr int kS = (kMH == 1) ? 6 : 4;
-  const size_t smem = size_t(kS) * (kMH + 1) * k2HalfBytes + (kWgrad ? 0 : 2 * k2StoreBytes) + 256 + 1024;
+  const size_t smem = size_t(kS) * (kMH + 1) * k2HalfBytes + (kWgrad ? 0 : 2 * k2StoreBytes) + 512 + 1024;
   p.num_m_tiles = (p.M + 256 * kMH - 1) / (256 * kMH);
   p.num_n_tiles = (p.N + k2Tile - 1) / k2Tile;
   // ~74 tiles in flight: a group of g row-blocks shares g A-panels and about 74/g B-panels
@@ -386,9 +477,14 @@ static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   if (g > p.num_m_tiles) g = p.num_m_tiles;
   p.group_m = g < 1 ? 1 : g;
   const int tiles = p.num_m_tiles * p.num_n_tiles;
-  int clusters = num_sms() / 2;
-  if (tiles < clusters) clusters = tiles;
-  gemm_pair_kernel<kMode, kMH><<<2 * clusters, 64 + 128 * kMH, smem, stream>>>(ta, tb, tc, p);
+  if (dynamic_tiles()) {
+    // one cluster per tile; resident clusters steal the not-yet-launched ones (cluster launch control)
+    gemm_pair_kernel<kMode, kMH, true><<<2 * tiles, 64 + 128 * kMH, smem, stream>>>(ta, tb, tc, p);
+  } else {
+    int clusters = num_sms() / 2;
+    if (tiles < clusters) clusters = tiles;
+    gemm_pair_kernel<kMode, kMH, false><<<2 * clusters, 64 + 128 * kMH, smem, stream>>>(ta, tb, tc, p);
+  }
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -461,6 +557,13 @@ int gemm2_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int 
 }  // namespace rdp
 
 extern "C" {
+
+// 1: pair kernels use hardware work stealing (cluster launch control) instead of the static persistent
+// tile loop -- for GEMMs that run concurrently with an overlapped all-reduce kernel.  Process-wide.
+int rdp_gemm_set_dynamic_tiles(int on) {
+  rdp::gemm2_set_dynamic_tiles(on);
+  return 0;
+}
 
 // Explicit entry points of the CTA-pair kernels (rdp_gemm_tn / rdp_gemm_wgrad pick them
 // automatically for large problems; these let tests and benchmarks force the path).

@@ -30,6 +30,10 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
 // CTA-pair (cta_group::2, 256 x 256 cluster tile) kernels for large problems.  rdp_gemm_tn and
 // rdp_gemm_wgrad dispatch to them on their own (plain bf16 output, N % 256 == 0, >= 37 tiles); these
 // entry points force the path.  rdp_gemm2_tn: out (bf16) = relu?(a . b^T + bias), N % 256 == 0.
+// rdp_gemm_set_dynamic_tiles(1): the pair kernels take their tiles by hardware work stealing (cluster
+// launch control) instead of a static persistent loop; use it when GEMMs share the SMs with an
+// overlapped all-reduce kernel (process-wide switch, default 0; env RAYDP_B200_DYNAMIC_TILES=1).
+int rdp_gemm_set_dynamic_tiles(int on);
 // mh: 0 = choose, 1 = 256-row cluster tiles (TMEM double-buffered), 2 = 512-row cluster tiles.
 int rdp_gemm2_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
                  const float* bias, int relu, int mh, void* stream);
@@ -136,7 +140,9 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
 // the reduced buffer in the same kernel; out (optional) receives a copy of the reduced gradient.
 int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
                        uint32_t* epoch, uint32_t* counters, const struct rdp_opt_args* opt, float* out,
-                       int64_t n, float scale, void* stream);
+                       int64_t n, float scale, int overlap_shape, void* stream);
+// overlap_shape != 0: launch 256-thread, <= 40-register blocks (one per SM) that fit beside a resident
+// tcgen05 GEMM CTA, for all-reduces meant to run concurrently with backward GEMMs.
 
 // All-to-all over peer memory: chunk q of `in` ([world][floats_per_pair]) lands in slot `rank` of rank q's
 // receive buffer (recv_bases[q], [world][floats_per_pair]); flag_ptrs[q] as for rdp_allreduce_nvls.

@@ -239,14 +239,25 @@ class NvlsReducer:
         torch.cuda.synchronize()
         dist.barrier(group)
 
-    def allreduce_(self, scale: float = 1.0, opt: Optional[OptArgs] = None, out: Optional[torch.Tensor] = None) -> None:
+    def allreduce_(self, scale: float = 1.0, opt: Optional[OptArgs] = None, out: Optional[torch.Tensor] = None,
+                   overlap: bool = False) -> None:
+        """``overlap=True`` launches the register-capped 256-thread shape that co-resides with GEMM CTAs."""
         vp = ctypes.c_void_p
         flags = (vp * self.world)(*[vp(p) for p in self.flag_ptrs])
         ops._check(self.lib.rdp_allreduce_nvls(vp(self.mc_ptr), vp(self.buffer.data_ptr()), flags, self.rank,
                                                self.world, vp(self.epoch.data_ptr()), vp(self.counters.data_ptr()),
                                                ctypes.byref(opt) if opt is not None else None,
                                                vp(out.data_ptr()) if out is not None else None, self.n, scale,
+                                               1 if overlap else 0,
                                                vp(torch.cuda.current_stream().cuda_stream)))
+
+    def allreduce_step_(self, opt: OptArgs, scale: float, overlap: bool = False) -> None:
+        """Same call shape as :meth:`P2PReducer.allreduce_step_` (all-reduce fused with the optimizer)."""
+        self.allreduce_(scale, opt=opt, overlap=overlap)
+
+    @property
+    def grads(self) -> torch.Tensor:
+        return self.buffer
 
     def close(self) -> None:
         torch.cuda.synchronize()

@@ -96,6 +96,12 @@ def gemm_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, *, mw: Optio
     return out
 
 
+def set_dynamic_tiles(on: bool) -> None:
+    """Large-GEMM tile schedule: hardware work stealing (``True``) for GEMMs that overlap with an
+    all-reduce kernel, static persistent loop (``False``, default) otherwise.  Process-wide."""
+    lib().rdp_gemm_set_dynamic_tiles(1 if on else 0)
+
+
 def gemm2_tn(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None, *,
              bias: Optional[torch.Tensor] = None, relu: bool = False, mh: int = 0) -> torch.Tensor:
     """``gemm_tn`` forced onto the CTA-pair (cta_group::2) kernel; ``b.shape[0] % 256 == 0``.

@@ -9,6 +9,7 @@ SIGNATURES = {
     "rdp_num_sms": (I, []),
     "rdp_gemm_tn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP, I, VP, I, I, I, VP, VP]),
     "rdp_gemm_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, VP]),
+    "rdp_gemm_set_dynamic_tiles": (I, [I]),
     "rdp_gemm2_tn": (I, [VP, I, VP, I, VP, I, I, I, I, VP, I, I, VP]),
     "rdp_gemm2_wgrad": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP]),
     "rdp_bn_fold": (I, [VP, F, VP, VP, VP, VP, F, F, I, VP, VP, VP, VP, VP, VP, I, I, VP, I, VP, I, VP, VP]),
@@ -47,7 +48,7 @@ SIGNATURES.update({
 SIGNATURES.update({
     "rdp_comm_barrier": (I, [C.POINTER(VP), C.c_uint64, I, I, VP, VP]),
     "rdp_alltoall": (I, [VP, C.POINTER(VP), C.POINTER(VP), I, I, I64, VP, VP, VP]),
-    "rdp_allreduce_nvls": (I, [VP, VP, C.POINTER(VP), I, I, VP, VP, C.POINTER(OptArgs), VP, I64, F, VP]),
+    "rdp_allreduce_nvls": (I, [VP, VP, C.POINTER(VP), I, I, VP, VP, C.POINTER(OptArgs), VP, I64, F, I, VP]),
     "rdp_embedding_fwd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),
                               C.POINTER(I), I, I, I, I, VP]),
     "rdp_embedding_bwd_sgd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),

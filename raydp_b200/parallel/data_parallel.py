@@ -8,15 +8,20 @@ the fully fused MLP path.
 * Parameters are re-homed into flat fp32 buckets (reverse registration order = backward order);
   gradients are views of **registered symmetric memory**, so backward writes them where the peers
   read them -- no bucket copy.
-* When the last gradient of a bucket lands, the bucket's kernel (two-shot reduce-scatter by pull +
-  all-gather by push over NVLink, then Adam/SGD on the reduced gradient, one launch) is enqueued on
-  a communication stream, behind an event from the compute stream: buckets of late layers reduce
-  and update while earlier layers are still in backward.
+* When the last gradient of a bucket lands, the bucket's kernel (NVLS ``multimem`` reduction inside
+  the NVSwitch where available, else two-shot reduce-scatter by pull + all-gather by push over
+  NVLink; then Adam/SGD on the reduced gradient and the bf16 operand shadow, one launch) is
+  enqueued on a communication stream, behind an event from the compute stream.  The kernel is
+  launched in a 256-thread / 40-register shape so its blocks are co-resident with the persistent
+  tcgen05 GEMM CTAs: buckets of late layers reduce and update while earlier layers are still in backward.
 * ``world_size == 1`` degenerates to the fused flat optimizer.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional
+
+import os
 
 import torch
 import torch.distributed as dist
@@ -42,8 +47,12 @@ class _Bucket:
         self.shadow = torch.zeros(self.n, dtype=torch.bfloat16, device=device)
         self.reducer = None
         if world > 1:
-            from raydp_b200.comm import P2PReducer
-            self.reducer = P2PReducer(None, device, algo="two_shot_fixed", n=self.n)
+            from raydp_b200.comm import NvlsReducer, P2PReducer, nvls_available
+            if nvls_available(device) and os.environ.get("RAYDP_B200_NO_NVLS") != "1":
+                # reduction inside the NVSwitch (multimem): gradients live in the multicast-mapped buffer
+                self.reducer = NvlsReducer(self.n, device)
+            else:
+                self.reducer = P2PReducer(None, device, algo="two_shot_fixed", n=self.n)
             self.grads = self.reducer.grads
         else:
             self.grads = torch.zeros(self.n, **f32)
@@ -101,6 +110,8 @@ class FusedDataParallel(nn.Module):
         self.step_dev = torch.zeros(1, **f32)
         self.lr_dev = torch.zeros(1, **f32)
         self.comm_stream = torch.cuda.Stream(device=self.device)
+        if self.world > 1 and overlap:
+            ops.set_dynamic_tiles(True)     # backward GEMMs share the SMs with the bucket all-reduces
         from raydp_b200.ops.linear import FusedLinear
         self._fused_linears = [m for m in module.modules() if isinstance(m, FusedLinear)]
         fused_w = {id(m.weight) for m in self._fused_linears}
@@ -141,7 +152,10 @@ class FusedDataParallel(nn.Module):
             stream.wait_event(ready)
         with torch.cuda.stream(stream):
             if b.reducer is not None:
-                b.reducer.allreduce_step_(self._opt_args(b), 1.0 / self.world)
+                if getattr(b.reducer, "kind", "") == "nvls":
+                    b.reducer.allreduce_step_(self._opt_args(b), 1.0 / self.world, overlap=stream is not compute)
+                else:
+                    b.reducer.allreduce_step_(self._opt_args(b), 1.0 / self.world)
             elif self.kind == 1:
                 ops.adam_step(b.flat, b.grads, b.m, b.v, 0.0, self.hp["betas"][0], self.hp["betas"][1], self.hp["eps"],
                               self.hp["weight_decay"], 1, 1.0, self.hp["adamw"], self.lr_dev, self.step_dev,

@@ -148,3 +148,28 @@ def test_fused_linear_matches_torch_on_pair_kernel_shapes():
     assert rel(xf.grad, xr.grad) < 3e-2
     assert rel(lin.weight.grad, ref.weight.grad) < 3e-2
     assert rel(lin.bias.grad, ref.bias.grad) < 3e-2
+
+
+def test_pair_kernels_with_dynamic_tile_schedule():
+    """Cluster-launch-control work stealing: same results as the static persistent loop."""
+    ops = _ops()
+    a, b = _rand(4096, 512), _rand(5120, 512)
+    bias = torch.randn(5120, device="cuda")
+    g, x = _rand(1024, 2304), _rand(1024, 2048)
+    static_out = ops.gemm2_tn(a, b, bias=bias, relu=True, mh=1)
+    ops.set_dynamic_tiles(True)
+    try:
+        for mh in (1, 2):
+            out = ops.gemm2_tn(a, b, bias=bias, relu=True, mh=mh)
+            assert torch.equal(out, static_out), mh
+            w = torch.zeros(2304, 2048, device="cuda")
+            ops.gemm2_wgrad(g, x, w, mh=mh)
+            ref = g.float().t() @ x.float()
+            assert (w - ref).abs().max().item() <= 2e-3 * ref.abs().max().item() + 1e-2
+            bt = _rand(512, 5120)
+            nn = ops.gemm2_nn(a, bt, mh=mh)
+            refn = a.float() @ bt.float()
+            assert (nn.float() - refn).abs().max().item() <= 0.02 * refn.abs().max().item() + 0.05
+        torch.cuda.synchronize()
+    finally:
+        ops.set_dynamic_tiles(False)
