@@ -134,14 +134,17 @@ def main():
         print(json.dumps({"impl": args.impl, "metric": "BigMLP train samples/sec", "n_gpus": world, "params": nparams,
                           "per_gpu_batch": B, "ms_per_step": ms, "value": world * B / (ms / 1e3),
                           "tflops_per_gpu": flops / (ms / 1e3) / 1e12, "overlap": not args.no_overlap}), flush=True)
-    if args.breakdown and rank == 0:
+    if args.breakdown:                      # every rank steps (collectives), rank 0 reports
         from torch.profiler import ProfilerActivity, profile
         with profile(activities=[ProfilerActivity.CUDA]) as prof:
             step(0)
             torch.cuda.synchronize()
-        rows = sorted(prof.key_averages(), key=lambda k: -k.device_time_total)[:14]
-        for k in rows:
-            print(f"  {k.device_time_total / 1e3:8.2f} ms  x{k.count:<4d} {k.key[:90]}", flush=True)
+        if rank == 0:
+            if os.environ.get("RAYDP_B200_TRACE"):
+                prof.export_chrome_trace(os.environ["RAYDP_B200_TRACE"])
+            rows = sorted(prof.key_averages(), key=lambda k: -k.device_time_total)[:14]
+            for k in rows:
+                print(f"  {k.device_time_total / 1e3:8.2f} ms  x{k.count:<4d} {k.key[:90]}", flush=True)
     if args.impl == "ours":
         dp.close()
     _finish(world)

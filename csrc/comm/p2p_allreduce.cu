@@ -555,16 +555,22 @@ alltoall_kernel(const __grid_constant__ A2AParams p) {
   const int64_t nthreads = int64_t(nblocks) * blockDim.x;
   // round A (slot 3): every rank has entered the call, so last call's receive buffers are consumed
   flags_signal_and_wait(p.flags, p.rank, p.world, e, 3, p.counters + 0, nblocks);
-  for (int q = 0; q < p.world; ++q) {
+  // The grid is a multiple of `world` blocks: block b pushes to destination (rank + b % world) % world, so
+  // all destinations are in flight at once (the switch gives every pair full bandwidth) and ranks start on
+  // different peers.
+  {
+    const int q = blockIdx.x % p.world;
+    const int sub = blockIdx.x / p.world, nsub = nblocks / p.world;
     const int dst = (p.rank + q) % p.world;
     const float4* src = p.in + int64_t(dst) * p.chunk4;
     float4* out = reinterpret_cast<float4*>(p.recv[dst]) + int64_t(p.rank) * p.chunk4;
-    for (int64_t i0 = tid; i0 < p.chunk4; i0 += 4 * nthreads) {
+    const int64_t stride = int64_t(nsub) * blockDim.x;
+    for (int64_t i0 = int64_t(sub) * blockDim.x + threadIdx.x; i0 < p.chunk4; i0 += 4 * stride) {
       float4 v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) if (i0 + u * nthreads < p.chunk4) v[u] = src[i0 + u * nthreads];
+      for (int u = 0; u < 4; ++u) if (i0 + u * stride < p.chunk4) v[u] = src[i0 + u * stride];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) if (i0 + u * nthreads < p.chunk4) out[i0 + u * nthreads] = v[u];
+      for (int u = 0; u < 4; ++u) if (i0 + u * stride < p.chunk4) out[i0 + u * stride] = v[u];
     }
   }
   // round B (slot 4): all pushes have landed
@@ -594,10 +600,12 @@ extern "C" int rdp_alltoall(const void* in, void* const* recv_bases, void* const
     p.flags[q] = static_cast<uint32_t*>(flag_ptrs[q]);
   }
   p.rank = rank; p.world = world; p.chunk4 = floats_per_pair / 4; p.epoch = epoch; p.counters = counters;
-  int64_t work = p.chunk4 / 4;
-  int blocks = int((work + kArThreads - 1) / kArThreads);
-  if (blocks > num_sms()) blocks = num_sms();
-  if (blocks < 1) blocks = 1;
+  const int64_t work = p.chunk4 / 4;                       // 4 vectors per thread, per destination
+  int per_dst = int((work + kArThreads - 1) / kArThreads);
+  const int cap = num_sms() / world > 0 ? num_sms() / world : 1;
+  if (per_dst > cap) per_dst = cap;
+  if (per_dst < 1) per_dst = 1;
+  const int blocks = per_dst * world;
   alltoall_kernel<<<blocks, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;

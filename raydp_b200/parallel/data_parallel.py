@@ -48,7 +48,9 @@ class _Bucket:
         self.reducer = None
         if world > 1:
             from raydp_b200.comm import NvlsReducer, P2PReducer, nvls_available
-            if nvls_available(device) and os.environ.get("RAYDP_B200_NO_NVLS") != "1":
+            # Measured (profiles/README.md): the in-switch reduction wins from 4 ranks up (8 GPUs, 1 GB:
+            # 2.28 ms vs 3.20 ms two-shot); with 2 ranks the peer-memory two-shot is faster (1.69 vs 2.7 ms).
+            if world >= 4 and nvls_available(device) and os.environ.get("RAYDP_B200_NO_NVLS") != "1":
                 # reduction inside the NVSwitch (multimem): gradients live in the multicast-mapped buffer
                 self.reducer = NvlsReducer(self.n, device)
             else:
