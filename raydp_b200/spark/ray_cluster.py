@@ -78,7 +78,30 @@ class SparkCluster(Cluster):
         return None
 
     # ------------------------------------------------------------------ configs
+    @staticmethod
+    def _load_default_properties() -> Dict[str, str]:
+        """``spark-defaults.conf`` from ``$SPARK_CONF_DIR`` or ``$SPARK_HOME/conf`` (reference: loaded by
+        the app master, ``RayAppMaster.scala:61``; precedence user dict > file, ``doc/spark_on_ray.md:92``)."""
+        import os
+        for base in (os.environ.get("SPARK_CONF_DIR"),
+                     os.path.join(os.environ["SPARK_HOME"], "conf") if os.environ.get("SPARK_HOME") else None):
+            path = os.path.join(base, "spark-defaults.conf") if base else None
+            if path and os.path.isfile(path):
+                out: Dict[str, str] = {}
+                with open(path) as f:
+                    for line in f:
+                        line = line.strip()
+                        if not line or line.startswith("#"):
+                            continue
+                        parts = line.replace("=", " ", 1).split(None, 1)
+                        if len(parts) == 2 and parts[0].startswith("spark."):
+                            out[parts[0]] = parts[1].strip()
+                return out
+        return {}
+
     def _prepare_spark_configs(self) -> None:
+        for key, value in self._load_default_properties().items():
+            self._configs.setdefault(key, value)          # the user's dict wins
         cfg = self._configs
         cfg.setdefault("spark.executor.instances", str(self._num_executors))
         cfg["spark.executor.instances"] = str(self._num_executors)

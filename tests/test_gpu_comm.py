@@ -32,6 +32,30 @@ def test_emulated_allreduce_matches_sum(world, algo, n):
             assert torch.allclose(o, ref, rtol=1e-5, atol=1e-5)
 
 
+def test_flag_protocol_stress_on_one_gpu():
+    """Epoch-flag protocol under churn: 300 back-to-back all-reduces on emulated ranks, alternating
+    one-shot / two-shot and message sizes without any host synchronisation in between (the parity
+    double buffers and monotonically increasing epochs must keep successive calls apart)."""
+    from raydp_b200.comm import LocalEmulation
+    world, n_max = 4, 1 << 16
+    dev = torch.device("cuda", 0)
+    emu = {n: LocalEmulation(world, n, dev) for n in (1024, 8192, n_max)}
+    torch.manual_seed(0)
+    ins = {n: [torch.randn(n, device=dev) for _ in range(world)] for n in emu}
+    outs = {n: [torch.empty(n, device=dev) for _ in range(world)] for n in emu}
+    sizes = list(emu)
+    for it in range(300):
+        n = sizes[it % 3]
+        for t in ins[n]:
+            t.add_(1.0)                              # new data every call, enqueued on the same stream
+        emu[n].allreduce(ins[n], outs[n], scale=1.0, algo="one_shot" if it % 2 else "two_shot")
+        if it % 50 == 49:
+            ref = torch.stack(ins[n]).sum(0)
+            for o in outs[n]:
+                assert torch.allclose(o, ref, rtol=1e-5, atol=1e-4), it
+    torch.cuda.synchronize()
+
+
 def test_emulated_allreduce_fused_adam_matches_torch():
     from raydp_b200.comm import LocalEmulation, make_opt_args
     dev = torch.device("cuda")

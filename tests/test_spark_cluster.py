@@ -250,3 +250,19 @@ def test_external_shuffle_service_keeps_blocks_after_executor_kill(ray_cluster):
     assert spark._backend.executor_actor_ids() == [0]
     assert shuffled.count() == 4000 and shuffled.rdd.getNumPartitions() == 3
     raydp.stop_spark()
+
+
+def test_spark_defaults_conf_is_loaded_with_user_precedence(ray_cluster, tmp_path, monkeypatch):
+    """``$SPARK_CONF_DIR/spark-defaults.conf`` feeds the session configuration; ``init_spark(configs=)``
+    wins on conflicts (reference ``doc/spark_on_ray.md:92``, ``RayAppMaster.scala:61``)."""
+    (tmp_path / "spark-defaults.conf").write_text(
+        "# comment\nspark.sql.shuffle.partitions  7\nspark.custom.flag=from-file\nnot.spark.key 1\n")
+    monkeypatch.setenv("SPARK_CONF_DIR", str(tmp_path))
+    spark = raydp.init_spark("defaults", 1, 1, "300M", configs={"spark.custom.flag": "from-user"})
+    try:
+        conf = spark.sparkContext.getConf()
+        assert conf.get("spark.sql.shuffle.partitions") == "7"
+        assert conf.get("spark.custom.flag") == "from-user"
+        assert conf.get("not.spark.key", "absent") == "absent"
+    finally:
+        raydp.stop_spark()
