@@ -147,7 +147,8 @@ class DataFrame:
 
     def filter(self, condition: Union[Column, str]) -> "DataFrame":
         if isinstance(condition, str):
-            raise NotImplementedError("SQL-string predicates are not supported; pass a Column")
+            from raydp_b200.sql.sqlparser import parse_expression
+            condition = parse_expression(condition)
         return self._derive(("filter", condition))
 
     where = filter
@@ -166,6 +167,21 @@ class DataFrame:
         if any(e._kind == "agg" for e in exprs):
             return self.agg(*exprs)
         return self._derive(("select", exprs))
+
+    def selectExpr(self, *exprs) -> "DataFrame":
+        from raydp_b200.sql.sqlparser import parse_expression
+        if len(exprs) == 1 and isinstance(exprs[0], (list, tuple)):
+            exprs = tuple(exprs[0])
+        cols: list = []
+        for e in exprs:
+            cols.extend(self.columns if e.strip() == "*" else [parse_expression(e)])
+        return self.select(*cols)
+
+    def createOrReplaceTempView(self, name: str) -> None:
+        self._session.catalog.register_view(name, self)
+
+    createTempView = createOrReplaceTempView
+    registerTempTable = createOrReplaceTempView
 
     def drop(self, *cols) -> "DataFrame":
         names = [c if isinstance(c, str) else c._output_name() for c in cols]
@@ -205,6 +221,8 @@ class DataFrame:
                 for i in range(len(weights))]
 
     def mapInPandas(self, func, schema) -> "DataFrame":
+        if isinstance(schema, str):
+            schema = T.parse_ddl(schema)
         arrow_schema = schema.to_arrow_schema() if isinstance(schema, T.StructType) else schema
         return self._derive(("map_pandas", func, arrow_schema))
 
@@ -615,6 +633,13 @@ class DataFrameWriter:
         self._df._run("write_parquet", {"path": target, "compression": compression,
                                         "job": uuid.uuid4().hex[:8]})
         open(os.path.join(target, "_SUCCESS"), "w").close()
+
+    def saveAsTable(self, name: str, format: Optional[str] = None, mode: Optional[str] = None, **_kw) -> None:  # noqa: A002
+        """Persist as a parquet table under the warehouse directory (see ``sqlparser.Catalog``)."""
+        self._df._session.catalog.save_table(self._df, name, (mode or self._mode))
+
+    def insertInto(self, name: str, overwrite: bool = False) -> None:
+        self._df._session.catalog.save_table(self._df, name, "overwrite" if overwrite else "append")
 
     def csv(self, path: str, mode: Optional[str] = None, header=None, **_kw) -> None:
         import os

@@ -169,3 +169,9 @@ def vectorized_udf(returnType=T.DoubleType()):
 
 
 pandas_udf = vectorized_udf
+
+
+def expr(text: str) -> Column:
+    """SQL expression string -> Column (``F.expr("a + b * 2 AS c")``)."""
+    from raydp_b200.sql.sqlparser import parse_expression
+    return parse_expression(text)

@@ -126,11 +126,7 @@ class DataFrameReader:
 
     def schema(self, schema: Union[T.StructType, str]) -> "DataFrameReader":
         if isinstance(schema, str):
-            fields = []
-            for part in schema.split(","):
-                name, tname = part.strip().split()
-                fields.append(T.StructField(name, T.parse_type(tname)))
-            schema = T.StructType(fields)
+            schema = T.parse_ddl(schema)
         self._schema = schema
         return self
 
@@ -168,7 +164,7 @@ class DataFrameReader:
         return DataFrame(self._session, Plan(ParquetSource(files)))
 
     def table(self, name: str):
-        raise NotImplementedError("catalog tables need a Hive metastore/JVM; not available")
+        return self._session.catalog.lookup(name)
 
 
 class _Builder:
@@ -319,11 +315,22 @@ class SparkSession:
         table = _rows_to_table(list(data), names, arrow_schema)
         return self._from_tables(_split_table(table, self._backend.default_parallelism))
 
-    def sql(self, query: str):
-        raise NotImplementedError("spark.sql() needs Spark's SQL parser (JVM); use the DataFrame API")
+    @property
+    def catalog(self):
+        """Temp views + parquet-backed warehouse tables (``raydp_b200.sql.sqlparser.Catalog``)."""
+        if getattr(self, "_catalog", None) is None:
+            from raydp_b200.sql.sqlparser import Catalog
+            self._catalog = Catalog(self)
+        return self._catalog
 
-    def table(self, name: str):
-        raise NotImplementedError("catalog tables need a Hive metastore/JVM; not available")
+    def sql(self, query: str) -> DataFrame:
+        """SELECT / SHOW / CREATE TABLE AS / INSERT / DROP over views and warehouse tables, parsed in
+        Python (``raydp_b200.sql.sqlparser``); joins and sub-queries need the DataFrame API."""
+        from raydp_b200.sql.sqlparser import run_sql
+        return run_sql(self, query)
+
+    def table(self, name: str) -> DataFrame:
+        return self.catalog.lookup(name)
 
     def newSession(self) -> "SparkSession":
         return self

@@ -151,6 +151,21 @@ def parse_type(spec: Union[str, DataType, pa.DataType]) -> DataType:
     raise ValueError(f"unsupported data type string: {spec!r}")
 
 
+def parse_ddl(ddl: str) -> "StructType":
+    """``"a int, b double"`` / ``"a: int, b: string"`` -> StructType (the DDL strings pyspark accepts for
+    ``mapInPandas``, ``createDataFrame(schema=...)`` and ``read.schema(...)``)."""
+    fields = []
+    for part in ddl.split(","):
+        part = part.strip()
+        if not part:
+            continue
+        name, _, tname = part.replace(":", " ", 1).partition(" ")
+        if not tname.strip():
+            raise ValueError(f"cannot parse schema field {part!r}; expected '<name> <type>'")
+        fields.append(StructField(name.strip().strip("`"), parse_type(tname.strip())))
+    return StructType(fields)
+
+
 def from_arrow_type(t: pa.DataType) -> DataType:
     if pa.types.is_boolean(t):
         return BooleanType()

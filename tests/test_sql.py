@@ -173,3 +173,52 @@ def test_initial_executor_number():
     dyn = {"spark.dynamicAllocation.enabled": "true", "spark.dynamicAllocation.minExecutors": "1",
            "spark.dynamicAllocation.initialExecutors": "3", "spark.dynamicAllocation.maxExecutors": "4"}
     assert get_initial_target_executor_number(dyn) == 3
+
+
+def test_sql_front_end_views_tables_and_expressions(spark_session, tmp_path):
+    """``spark.sql`` / ``filter(str)`` / ``selectExpr`` / ``F.expr`` / temp views / warehouse tables
+    (reference usage: ``spark.sql("select * from db.xxx")`` with ``enable_hive``, doc/spark_on_ray.md:187-202)."""
+    from raydp_b200.sql import functions as F
+    spark = spark_session
+    spark.conf.set("spark.sql.warehouse.dir", str(tmp_path / "wh"))
+    df = spark.createDataFrame([(i, i % 3, float(i) * 0.5, "n%d" % (i % 2)) for i in range(30)], ["id", "k", "v", "s"])
+    df.createOrReplaceTempView("t")
+    got = spark.sql("SELECT id, v * 2 AS w FROM t WHERE id BETWEEN 5 AND 9 AND s = 'n1' ORDER BY id DESC LIMIT 2").collect()
+    assert [(r.id, r.w) for r in got] == [(9, 9.0), (7, 7.0)]
+    agg = spark.sql("select k, count(*) as n, sum(v) as total from t group by k having n > 0 order by k").collect()
+    assert [(r.k, r.n) for r in agg] == [(0, 10), (1, 10), (2, 10)]
+    assert abs(agg[1].total - sum(i * 0.5 for i in range(30) if i % 3 == 1)) < 1e-9
+    assert spark.sql("select count(*) as n from t where not (k in (0, 1)) or id is null").collect()[0].n == 10
+    assert spark.sql("select distinct s from t order by s").collect()[1].s == "n1"
+    assert spark.sql("select case when k = 0 then 'zero' else 'other' end as c from t order by id limit 1").collect()[0].c == "zero"
+    # string predicates / expressions on the DataFrame API
+    assert df.filter("v >= 10 and k <> 2").count() == len([i for i in range(30) if i * 0.5 >= 10 and i % 3 != 2])
+    row = df.selectExpr("id", "cast(v as int) + 1 as vi", "abs(id - 10) d").filter("id = 3").collect()[0]
+    assert (row.id, row.vi, row.d) == (3, 2, 7)
+    assert df.withColumn("e", F.expr("id % 4")).filter("e = 3").count() == 7
+    # warehouse tables in a database, visible to a fresh lookup (what enable_hive sessions persist to)
+    spark.sql("create database if not exists db")
+    spark.sql("create table db.xxx as select id, v from t where id < 4")
+    spark.sql("insert into db.xxx select id, v from t where id >= 28")
+    assert sorted(r.id for r in spark.sql("select * from db.xxx").collect()) == [0, 1, 2, 3, 28, 29]
+    assert spark.table("db.xxx").count() == 6 and spark.read.table("db.xxx").count() == 6
+    df.limit(3).write.mode("overwrite").saveAsTable("plain")
+    names = {(r.tableName, r.isTemporary) for r in spark.sql("show tables").collect()}
+    assert ("plain", False) in names and ("t", True) in names
+    assert ("xxx", "db", False) in spark.catalog.listTables("db") and "db" in spark.catalog.listDatabases()
+    spark.sql("drop table if exists db.xxx")
+    assert not spark.catalog.tableExists("db.xxx")
+    import pytest as _pytest
+    with _pytest.raises(ValueError):
+        spark.sql("select * from t join u on t.id = u.id")
+
+
+def test_map_in_pandas_accepts_ddl_schema(spark_session):
+    df = spark_session.createDataFrame([(1, 2.0), (2, 3.0)], "a int, b double")
+
+    def add(it):
+        for pdf in it:
+            yield pdf.assign(z=pdf["a"] * 10)
+
+    out = df.mapInPandas(add, "a int, b double, z long").collect()
+    assert [r.z for r in out] == [10, 20]
