@@ -437,7 +437,9 @@ def _parse_select(p: _Parser, session):
         if not p.op(","):
             break
     if not p.kw("from"):
-        raise SqlError("SELECT without FROM is not supported")
+        # SELECT <constant expressions>: one row
+        one = session.range(1)
+        return one.select(*[c for c in items if not isinstance(c, str)])
     df = session.catalog.lookup(_qualified_name(p))
     if p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS:
         p.name()                                    # table alias: columns are resolved by bare name

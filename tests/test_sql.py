@@ -161,8 +161,7 @@ def test_conf_and_context(spark_session):
     sc = spark_session.sparkContext
     assert sc.appName == "RayDP test" and sc.applicationId.startswith("app-")
     assert sc.getConf().get("does.not.exist", "dflt") == "dflt"
-    with pytest.raises(NotImplementedError):
-        spark_session.sql("select 1")
+    assert spark_session.sql("select 1 as one, 2 * 3 as six").collect()[0].six == 6
 
 
 def test_initial_executor_number():
