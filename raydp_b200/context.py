@@ -1,110 +1,108 @@
 """Session lifecycle: ``init_spark`` / ``stop_spark``.
 
-Parity: reference ``python/raydp/context.py:33-257`` -- one process-global context guarded by
-an RLock (``:178-179``); ``init_spark`` auto-starts the runtime (``:215-217``), raises
-``"The spark environment has inited."`` on double init (``:240``) and tears down on failure
-(``:234-238``); placement groups are built from the strategy with one
-``{"CPU": cores, "memory": bytes}`` bundle per executor (``:119-140``) and recorded in
-``spark.ray.placement_group`` / ``spark.ray.bundle_indexes``; ``stop_spark(cleanup_data)``
-keeps the master actor -- and the data it holds -- alive when ``cleanup_data=False``
-(``:243-254``); ``atexit`` registration (``:257``).
+Behaviour kept from the reference (``python/raydp/context.py``): one session per process behind a
+re-entrant lock (``:178-179``); the runtime is started on demand (``:215-217``); a second
+``init_spark`` raises ``"The spark environment has inited."`` (``:240``); a failed start is torn down
+(``:234-238``); a placement-group *strategy* creates one ``{"CPU": cores, "memory": bytes}`` bundle per
+executor, waits for it and removes it again at stop, while an existing group is only referenced
+(``:119-140``) -- either way the executors learn about it through ``spark.ray.placement_group`` /
+``spark.ray.bundle_indexes``; ``stop_spark(cleanup_data=False)`` leaves the master actor, and the
+datasets it owns, alive (``:243-254``); ``stop_spark`` runs at interpreter exit (``:257``).
+
+The shape is different: the request is a frozen :class:`SessionRequest`, the live pieces (placement
+group, cluster, session) sit in one :class:`_LiveSession` that is built by ``start()`` and unwound by
+``shutdown()`` in reverse order, so a failure half way through start-up releases exactly what exists.
 """
 from __future__ import annotations
 
 import atexit
-from contextlib import ContextDecorator
-from threading import RLock
+import threading
+from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Union
 
 from raydp_b200 import runtime
+from raydp_b200.spark import configs as C
 from raydp_b200.spark.ray_cluster import SparkCluster
 from raydp_b200.sql.session import SparkSession, reset_builder_singletons
 from raydp_b200.utils import parse_memory_size
 
+ALREADY_STARTED = "The spark environment has inited."
 
-class _SparkContext(ContextDecorator):
-    _PLACEMENT_GROUP_CONF = "spark.ray.placement_group"
-    _BUNDLE_INDEXES_CONF = "spark.ray.bundle_indexes"
 
-    def __init__(self, app_name: str, num_executors: int, executor_cores: int,
-                 executor_memory: Union[str, int], enable_hive: bool, fault_tolerant_mode: bool,
-                 placement_group_strategy: Optional[str], placement_group,
-                 placement_group_bundle_indexes: Optional[List[int]],
-                 configs: Optional[Dict[str, str]] = None):
-        self._app_name = app_name
-        self._num_executors = num_executors
-        self._executor_cores = executor_cores
-        self._executor_memory = executor_memory
-        self._enable_hive = enable_hive
-        self._fault_tolerant_mode = fault_tolerant_mode
-        self._placement_group_strategy = placement_group_strategy
-        self._placement_group = placement_group
-        self._placement_group_bundle_indexes = placement_group_bundle_indexes
-        self._configs: Optional[Dict[str, str]] = {} if configs is None else dict(configs)
-        self._spark_cluster: Optional[SparkCluster] = None
-        self._spark_session: Optional[SparkSession] = None
+@dataclass(frozen=True)
+class SessionRequest:
+    app_name: str
+    num_executors: int
+    executor_cores: int
+    executor_memory: Union[str, int]
+    enable_hive: bool = False
+    fault_tolerant_mode: bool = True
+    placement_group_strategy: Optional[str] = None
+    placement_group: object = None
+    placement_group_bundle_indexes: Optional[List[int]] = None
+    configs: Dict[str, str] = field(default_factory=dict)
 
-    def _get_or_create_spark_cluster(self) -> SparkCluster:
-        if self._spark_cluster is None:
-            self._spark_cluster = SparkCluster(self._app_name, self._num_executors,
-                                               self._executor_cores, self._executor_memory,
-                                               self._enable_hive, self._configs)
-        return self._spark_cluster
+    def memory_bytes(self) -> int:
+        mem = self.executor_memory
+        return parse_memory_size(mem) if isinstance(mem, str) else int(mem)
 
-    def _prepare_placement_group(self) -> None:
-        if self._placement_group_strategy is not None:
-            memory = self._executor_memory
-            if isinstance(memory, str):
-                memory = parse_memory_size(memory)
-            bundles = [{"CPU": self._executor_cores, "memory": memory}
-                       for _ in range(self._num_executors)]
-            pg = runtime.placement_group(bundles, strategy=self._placement_group_strategy)
-            runtime.get(pg.ready())
-            self._placement_group = pg
-            self._placement_group_bundle_indexes = None
-        if self._placement_group is not None:
-            self._configs[self._PLACEMENT_GROUP_CONF] = self._placement_group.id.hex()
-            idxs = (list(range(self._placement_group.bundle_count))
-                    if self._placement_group_bundle_indexes is None
-                    else self._placement_group_bundle_indexes)
-            self._configs[self._BUNDLE_INDEXES_CONF] = ",".join(map(str, idxs))
 
-    def get_or_create_session(self) -> SparkSession:
-        if self._spark_session is not None:
-            return self._spark_session
-        self._prepare_placement_group()
-        cluster = self._get_or_create_spark_cluster()
-        self._spark_session = cluster.get_spark_session()
-        if self._fault_tolerant_mode:
-            cluster.connect_spark_driver_to_ray()
-        return self._spark_session
+class _LiveSession:
+    """Everything ``init_spark`` brought up, in creation order."""
 
-    def stop(self, cleanup_data: bool = True) -> None:
-        if self._spark_session is not None:
-            self._spark_session.stop()
-            self._spark_session = None
+    def __init__(self, request: SessionRequest):
+        self.request = request
+        self.configs: Dict[str, str] = dict(request.configs)
+        self.owned_group = None            # a placement group made here (strategy given) -> removed at stop
+        self.cluster: Optional[SparkCluster] = None
+        self.session: Optional[SparkSession] = None
+
+    # ---- start-up
+    def _reserve(self) -> None:
+        req = self.request
+        group, indexes = req.placement_group, req.placement_group_bundle_indexes
+        if req.placement_group_strategy is not None:
+            bundle = {"CPU": req.executor_cores, "memory": req.memory_bytes()}
+            group = runtime.placement_group([dict(bundle) for _ in range(req.num_executors)],
+                                            strategy=req.placement_group_strategy)
+            runtime.get(group.ready())
+            self.owned_group, indexes = group, None
+        if group is None:
+            return
+        if indexes is None:
+            indexes = range(group.bundle_count)
+        self.configs[C.RAY_PLACEMENT_GROUP] = group.id.hex()
+        self.configs[C.RAY_BUNDLE_INDEXES] = ",".join(str(i) for i in indexes)
+
+    def start(self) -> SparkSession:
+        req = self.request
+        self._reserve()
+        self.cluster = SparkCluster(req.app_name, req.num_executors, req.executor_cores, req.executor_memory,
+                                    req.enable_hive, self.configs)
+        self.session = self.cluster.get_spark_session()
+        if req.fault_tolerant_mode:
+            self.cluster.connect_spark_driver_to_ray()
+        return self.session
+
+    # ---- tear-down (reverse order; every step tolerates "was never created")
+    def shutdown(self, cleanup_data: bool) -> bool:
+        """Returns True when nothing is left alive (the master actor survives ``cleanup_data=False``)."""
+        if self.session is not None:
+            self.session.stop()
+            self.session = None
             reset_builder_singletons()
-        if self._spark_cluster is not None:
-            self._spark_cluster.stop(cleanup_data)
+        if self.cluster is not None:
+            self.cluster.stop(cleanup_data)
             if cleanup_data:
-                self._spark_cluster = None
-        if self._placement_group_strategy is not None:
-            if self._placement_group is not None:
-                runtime.remove_placement_group(self._placement_group)
-                self._placement_group = None
-            self._placement_group_strategy = None
-        if self._configs is not None:
-            self._configs = None
-
-    def __enter__(self):
-        self.get_or_create_session()
-
-    def __exit__(self, exc_type, exc_val, exc_tb):
-        self.stop()
+                self.cluster = None
+        if self.owned_group is not None:
+            runtime.remove_placement_group(self.owned_group)
+            self.owned_group = None
+        return self.cluster is None
 
 
-_spark_context_lock = RLock()
-_global_spark_context: Optional[_SparkContext] = None
+_lock = threading.RLock()
+_live: Optional[_LiveSession] = None
 
 
 def init_spark(app_name: str, num_executors: int, executor_cores: int,
@@ -119,41 +117,42 @@ def init_spark(app_name: str, num_executors: int, executor_cores: int,
     ``placement_group_strategy`` (PACK / SPREAD / STRICT_PACK / STRICT_SPREAD; a group is made
     and later removed for you) or an existing ``placement_group`` plus optional bundle indexes.
     """
+    global _live
+    request = SessionRequest(app_name, num_executors, executor_cores, executor_memory, enable_hive,
+                             fault_tolerant_mode, placement_group_strategy, placement_group,
+                             placement_group_bundle_indexes, dict(configs or {}))
     if not runtime.is_initialized():
         runtime.init()
-    with _spark_context_lock:
-        global _global_spark_context
-        if _global_spark_context is None:
+    with _lock:
+        if _live is not None:
+            raise Exception(ALREADY_STARTED)
+        candidate = _LiveSession(request)
+        try:
+            session = candidate.start()
+        except BaseException:
             try:
-                _global_spark_context = _SparkContext(
-                    app_name, num_executors, executor_cores, executor_memory, enable_hive,
-                    fault_tolerant_mode, placement_group_strategy, placement_group,
-                    placement_group_bundle_indexes, configs)
-                return _global_spark_context.get_or_create_session()
-            except BaseException:
-                if _global_spark_context is not None:
-                    try:
-                        _global_spark_context.stop()
-                    except Exception:  # noqa: BLE001
-                        pass
-                _global_spark_context = None
-                raise
-        else:
-            raise Exception("The spark environment has inited.")
+                candidate.shutdown(cleanup_data=True)
+            except Exception:  # noqa: BLE001  (the original error is the one worth reporting)
+                pass
+            raise
+        _live = candidate
+        return session
 
 
 def stop_spark(cleanup_data: bool = True) -> None:
     """Stop the Spark session and executors.  With ``cleanup_data=False`` the master actor and
     the converted datasets it holds stay alive until the next ``stop_spark(True)``."""
-    with _spark_context_lock:
-        global _global_spark_context
-        if _global_spark_context is not None:
-            try:
-                if runtime.is_initialized():
-                    _global_spark_context.stop(cleanup_data)
-            finally:
-                if cleanup_data or not runtime.is_initialized():
-                    _global_spark_context = None
+    global _live
+    with _lock:
+        if _live is None:
+            return
+        gone = True
+        try:
+            if runtime.is_initialized():
+                gone = _live.shutdown(cleanup_data)
+        finally:
+            if gone or not runtime.is_initialized():
+                _live = None
 
 
 atexit.register(stop_spark)

@@ -1,66 +1,79 @@
-"""Cluster service ABCs.
+"""Service interfaces of a cluster that runs on the actor runtime.
 
-Parity: reference ``python/raydp/services.py:22-107`` -- ``Cluster`` is the only one that is
-subclassed (by ``SparkCluster``); ``ClusterMaster`` / ``ClusterWorker`` are kept as the same
-extension points.
+The names are the reference's extension points (``python/raydp/services.py:22-107``): ``Cluster`` --
+subclassed by :class:`raydp_b200.spark.ray_cluster.SparkCluster` -- plus ``ClusterMaster`` and
+``ClusterWorker`` for the two kinds of service processes.  Here the two service kinds share one
+base (:class:`Service`), and ``Cluster.add_worker`` keeps count of the workers it started and
+stops the whole cluster when starting one fails, so a half-built cluster never lingers.
 """
-from abc import ABC, abstractmethod
+from __future__ import annotations
+
+import abc
 from typing import Any, Dict, Optional
 
-
-class Cluster(ABC):
-    """A cluster = one master plus workers added on demand."""
-
-    def __init__(self, master_resources_requirement: Optional[Dict[str, float]] = None):
-        self._master_resources_requirement = master_resources_requirement
-
-    @abstractmethod
-    def _set_up_master(self, resources: Optional[Dict[str, float]], kwargs: Dict[Any, Any]):
-        """Start the master and block until it is ready."""
-
-    def add_worker(self, resources_requirement: Dict[str, float], **kwargs):
-        return self._set_up_worker(resources_requirement, kwargs)
-
-    @abstractmethod
-    def _set_up_worker(self, resources: Dict[str, float], kwargs: Dict[str, str]):
-        """Start one worker with the given resources."""
-
-    @abstractmethod
-    def get_cluster_url(self) -> str:
-        """URL that clients use to connect to this cluster."""
-
-    @abstractmethod
-    def stop(self, cleanup_data: bool = True):
-        """Stop workers and master."""
+Resources = Dict[str, float]
 
 
-class ClusterMaster(ABC):
-    @abstractmethod
-    def start_up(self, resources: Optional[Dict[str, float]] = None) -> str:
-        """Start the master; returns its URL."""
+class Service(abc.ABC):
+    """A long-running process of the cluster, addressable by host."""
 
-    @abstractmethod
+    @abc.abstractmethod
+    def get_host(self) -> str:
+        ...
+
+    @abc.abstractmethod
+    def stop(self) -> None:
+        ...
+
+
+class ClusterMaster(Service):
+    @abc.abstractmethod
+    def start_up(self, resources: Optional[Resources] = None) -> str:
+        """Bring the master up; the return value is its URL."""
+
+    @abc.abstractmethod
     def get_master_url(self) -> str:
-        pass
-
-    @abstractmethod
-    def get_host(self) -> str:
-        pass
-
-    @abstractmethod
-    def stop(self):
-        pass
+        ...
 
 
-class ClusterWorker(ABC):
-    @abstractmethod
+class ClusterWorker(Service):
+    @abc.abstractmethod
     def start_up(self) -> Optional[str]:
-        pass
+        ...
 
-    @abstractmethod
-    def get_host(self) -> str:
-        pass
 
-    @abstractmethod
-    def stop(self):
-        pass
+class Cluster(abc.ABC):
+    """One master, workers added on demand."""
+
+    def __init__(self, master_resources_requirement: Optional[Resources] = None):
+        self._master_resources_requirement = master_resources_requirement
+        self._num_workers = 0
+
+    @property
+    def num_workers(self) -> int:
+        return self._num_workers
+
+    def add_worker(self, resources_requirement: Resources, **kwargs: Any):
+        try:
+            worker = self._set_up_worker(resources_requirement, kwargs)
+        except BaseException:
+            self.stop()
+            raise
+        self._num_workers += 1
+        return worker
+
+    @abc.abstractmethod
+    def _set_up_master(self, resources: Optional[Resources], kwargs: Optional[Dict[Any, Any]]):
+        """Start the master and block until it answers."""
+
+    @abc.abstractmethod
+    def _set_up_worker(self, resources: Resources, kwargs: Dict[str, Any]):
+        """Start one worker holding ``resources``."""
+
+    @abc.abstractmethod
+    def get_cluster_url(self) -> str:
+        """What clients connect to, e.g. ``ray://<master actor name>``."""
+
+    @abc.abstractmethod
+    def stop(self, cleanup_data: bool = True) -> None:
+        """Stop workers, then the master."""
