@@ -32,6 +32,8 @@ struct EmbParams {
   int n_src;
   int idx_ld, S, D;
   float scale;                          // bwd: -lr * grad_scale
+  const float* lr_ptr;                  // bwd, optional: lr read from the device (CUDA-graph friendly);
+  float grad_scale;                     //   then scale = -(*lr_ptr) * grad_scale
 };
 
 // one warp per (source rank, sample, local table) row; lanes cover D in steps of 32
@@ -61,6 +63,7 @@ embedding_bwd_sgd_kernel(const __grid_constant__ EmbParams p) {
   const int64_t nwarps = (int64_t(gridDim.x) * blockDim.x) >> 5;
   int64_t total = 0;
   for (int s = 0; s < p.n_src; ++s) total += int64_t(p.batch[s]) * p.n_tables;
+  const float scale = p.lr_ptr != nullptr ? -(*p.lr_ptr) * p.grad_scale : p.scale;
   for (int64_t w = warp; w < total; w += nwarps) {
     int64_t rem = w;
     int s = 0;
@@ -69,7 +72,7 @@ embedding_bwd_sgd_kernel(const __grid_constant__ EmbParams p) {
     const int row = p.idx[s][size_t(b) * p.idx_ld + p.col[t]];
     const __nv_bfloat16* g = p.feats[s] + (size_t(b) * p.S + p.slot[t]) * p.D;   // peer load
     float* dst = p.table[t] + size_t(row) * p.D;
-    for (int d = lane; d < p.D; d += 32) atomicAdd(dst + d, p.scale * __bfloat162float(g[d]));
+    for (int d = lane; d < p.D; d += 32) atomicAdd(dst + d, scale * __bfloat162float(g[d]));
   }
 }
 
@@ -193,7 +196,7 @@ static int fill_emb(EmbParams& p, float* const* tables, const int* slots, const 
     p.feats[s] = static_cast<__nv_bfloat16*>(feats[s]);
     p.batch[s] = batch[s];
   }
-  p.n_src = n_src; p.idx_ld = idx_ld; p.S = S; p.D = D; p.scale = 0.f;
+  p.n_src = n_src; p.idx_ld = idx_ld; p.S = S; p.D = D; p.scale = 0.f; p.lr_ptr = nullptr; p.grad_scale = 1.f;
   return 0;
 }
 
@@ -221,12 +224,14 @@ int rdp_embedding_fwd(float* const* tables, const int* slots, const int* cols, i
 
 int rdp_embedding_bwd_sgd(float* const* tables, const int* slots, const int* cols, int n_tables,
                           const int* const* idx, void* const* dfeats, const int* batch, int n_src, int idx_ld,
-                          int S, int D, float lr, float grad_scale, void* stream) {
+                          int S, int D, float lr, float grad_scale, const float* lr_ptr, void* stream) {
   if (n_tables == 0) return 0;
   EmbParams p;
   int rc = fill_emb(p, tables, slots, cols, n_tables, idx, dfeats, batch, n_src, idx_ld, S, D);
   if (rc) return rc;
   p.scale = -lr * grad_scale;
+  p.lr_ptr = lr_ptr;
+  p.grad_scale = grad_scale;
   int64_t rows = 0;
   for (int s = 0; s < n_src; ++s) rows += int64_t(batch[s]) * n_tables;
   int grid = int((rows + 7) / 8);

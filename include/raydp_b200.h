@@ -161,9 +161,10 @@ int rdp_comm_barrier(void* const* bases, uint64_t flag_offset_bytes, int rank, i
 int rdp_embedding_fwd(float* const* tables, const int* slots, const int* cols, int n_tables, const int* const* idx,
                       void* const* feats, const int* batch, int n_src, int idx_ld, int S, int D, void* stream);
 // Pull gradient rows from every rank's dfeats slab and apply table[row] += -lr * grad_scale * g.
+// lr_ptr (optional device scalar) overrides lr, so a captured CUDA graph follows lr schedules.
 int rdp_embedding_bwd_sgd(float* const* tables, const int* slots, const int* cols, int n_tables,
                           const int* const* idx, void* const* dfeats, const int* batch, int n_src, int idx_ld,
-                          int S, int D, float lr, float grad_scale, void* stream);
+                          int S, int D, float lr, float grad_scale, const float* lr_ptr, void* stream);
 // ---- K9: DLRM dot interaction (torch.bmm + tril gather + cat + pad) ---------------------------------
 // feats [B, S, D] bf16 -> out [B, ld_out] bf16 = [row 0 (D) | S(S-1)/2 pair dots, i > j row-major | 0 pad].
 int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, int ld_out, void* stream);

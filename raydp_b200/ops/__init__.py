@@ -259,10 +259,10 @@ def embedding_fwd(table_ptrs, slots, cols, idx_ptrs, feats_ptrs, batches, idx_ld
 
 
 def embedding_bwd_sgd(table_ptrs, slots, cols, idx_ptrs, dfeats_ptrs, batches, idx_ld: int, S: int, D: int,
-                      lr: float, grad_scale: float) -> None:
+                      lr: float, grad_scale: float, lr_dev: Optional[torch.Tensor] = None) -> None:
     _check(lib().rdp_embedding_bwd_sgd(_vp_arr(table_ptrs), _i_arr(slots), _i_arr(cols), len(table_ptrs),
                                        _vp_arr(idx_ptrs), _vp_arr(dfeats_ptrs), _i_arr(batches), len(idx_ptrs),
-                                       idx_ld, S, D, float(lr), float(grad_scale), _stream()))
+                                       idx_ld, S, D, float(lr), float(grad_scale), _ptr(lr_dev), _stream()))
 
 
 def dot_interaction_fwd(feats: torch.Tensor, out: torch.Tensor) -> None:

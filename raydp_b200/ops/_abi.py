@@ -52,7 +52,7 @@ SIGNATURES.update({
     "rdp_embedding_fwd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),
                               C.POINTER(I), I, I, I, I, VP]),
     "rdp_embedding_bwd_sgd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),
-                                  C.POINTER(I), I, I, I, I, F, F, VP]),
+                                  C.POINTER(I), I, I, I, I, F, F, VP, VP]),
     "rdp_dot_interaction_fwd": (I, [VP, VP, I, I, I, I, VP]),
     "rdp_dot_interaction_bwd": (I, [VP, VP, VP, I, I, I, I, VP]),
     "rdp_bce_logits": (I, [VP, I, VP, VP, I, I, VP, I, F, VP, VP]),

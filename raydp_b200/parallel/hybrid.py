@@ -177,10 +177,10 @@ class FusedDLRM:
         ops.dot_interaction_bwd(self.feats[:B], self.dzint[:B], self.dfeats[:B])
         return logits
 
-    def embedding_backward(self, lr: float, grad_scale: float) -> None:
+    def embedding_backward(self, lr: float, grad_scale: float, lr_dev: Optional[torch.Tensor] = None) -> None:
         ops.embedding_bwd_sgd([self.tables[t].data_ptr() for t in self.owned], [t + 1 for t in self.owned],
                               self.owned, self.peer_idx, self.peer_dfeats, self.peer_batch, self.T, self.S, self.D,
-                              lr, grad_scale)
+                              lr, grad_scale, lr_dev)
 
     def bottom_backward(self, dense: torch.Tensor) -> None:
         B = dense.shape[0]
@@ -205,11 +205,12 @@ class FusedDLRM:
                 self.bias(prev, True).copy_(self.stats[prev][0, :self.layers[prev][3]])
                 g = self.dact[prev][:B]
 
-    def sgd(self, lr: float, scale: float = 1.0, momentum: float = 0.0, weight_decay: float = 0.0) -> None:
+    def sgd(self, lr: float, scale: float = 1.0, momentum: float = 0.0, weight_decay: float = 0.0,
+            lr_dev: Optional[torch.Tensor] = None, step_dev: Optional[torch.Tensor] = None) -> None:
         if momentum and self.momentum_buf is None:
             self.momentum_buf = torch.zeros_like(self.params)
         ops.sgd_step(self.params, self.grads, self.momentum_buf if momentum else None, lr, momentum, 0.0,
-                     weight_decay, False, False, scale)
+                     weight_decay, False, False, scale, lr_dev, step_dev)
 
 
 class LocalWorld:
@@ -265,8 +266,15 @@ class DistributedDLRM:
     phases, peer-memory all-reduce fused with SGD for the dense gradients."""
 
     def __init__(self, spec: DLRMSpec, batch: int, device: torch.device, group=None, momentum: float = 0.0,
-                 weight_decay: float = 0.0):
+                 weight_decay: float = 0.0, use_graph: bool = True):
+        import os
         import torch.distributed as dist
+        self.use_graph = use_graph and os.environ.get("RAYDP_B200_DLRM_GRAPH", "1") != "0"
+        self._graphs = [None, None]
+        self._eager_steps = [0, 0]
+        self._graph_launches = 0
+        self._in_dense = self._in_idx = self._in_target = None
+        self._lr_host = None
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.core = FusedDLRM(spec, batch, device, self.rank, self.world)
@@ -309,14 +317,15 @@ class DistributedDLRM:
     def _barrier(self) -> None:
         ops.comm_barrier(self.sym.bases, self.flag_off, self.rank, self.world, self.barrier_epoch)
 
-    def train_step(self, dense: torch.Tensor, idx: torch.Tensor, target: torch.Tensor, lr: float) -> None:
+    def _step_body(self, dense: torch.Tensor, idx: torch.Tensor, target: torch.Tensor, parity: int) -> None:
+        """One training step as a pure stream of kernels: no host reads, no allocation, the learning
+        rate and the step count come from device scalars -- so it can be captured in a CUDA graph."""
         c = self.core
         B = dense.shape[0]
         multi = self.world > 1
         if multi:
-            assert B == c.B, "model-parallel embeddings need equal, full batches on every rank (drop_last=True)"
-            self._select(self.step_count & 1)
-        self.step_count += 1
+            self._select(parity)
+        ops.add_scalar(self.step_dev, 1.0)
         c._refresh_weights()
         c.idx[:B].copy_(idx)
         c.bottom_forward(dense)
@@ -328,20 +337,57 @@ class DistributedDLRM:
         c.top_forward_backward(target, B, True)
         if multi:
             self._barrier()
-        c.embedding_backward(lr, 1.0 / self.world)
+        c.embedding_backward(0.0, 1.0 / self.world, self.lr_dev)
         c.bottom_backward(dense)
         if multi:
             from raydp_b200.comm import make_opt_args
-            if self.momentum and c.momentum_buf is None:
-                c.momentum_buf = torch.zeros_like(c.params)
-            self.lr_dev.fill_(lr)
-            self.step_dev.fill_(float(self.step_count))
             opt = make_opt_args(2, c.params, c.momentum_buf if self.momentum else None, None,
                                 weight_decay=self.weight_decay, momentum=self.momentum, lr_dev=self.lr_dev,
                                 step_dev=self.step_dev)
             self.reducer.allreduce_step_(opt, 1.0 / self.world)
         else:
-            c.sgd(lr, 1.0, self.momentum, self.weight_decay)
+            c.sgd(0.0, 1.0, self.momentum, self.weight_decay, self.lr_dev, self.step_dev)
+
+    def train_step(self, dense: torch.Tensor, idx: torch.Tensor, target: torch.Tensor, lr: float) -> None:
+        """Full batches replay a captured CUDA graph (one per slab parity; ~100 launches of a
+        latency-bound step become one), after one eager step per parity has warmed lazy state.
+        Inputs are staged into fixed device buffers so the graphs can read them."""
+        c = self.core
+        B = dense.shape[0]
+        if self.world > 1:
+            assert B == c.B, "model-parallel embeddings need equal, full batches on every rank (drop_last=True)"
+        parity = self.step_count & 1
+        self.step_count += 1
+        if self.momentum and c.momentum_buf is None:
+            c.momentum_buf = torch.zeros_like(c.params)
+        if lr != self._lr_host:
+            self.lr_dev.fill_(lr)
+            self._lr_host = lr
+        if not (self.use_graph and B == c.B):
+            self._step_body(dense, idx, target, parity)
+            return
+        if self._in_dense is None:
+            self._in_dense = torch.zeros_like(dense)
+            self._in_idx = torch.zeros_like(idx)
+            self._in_target = torch.zeros_like(target)
+        self._in_dense.copy_(dense)
+        self._in_idx.copy_(idx)
+        self._in_target.copy_(target)
+        graph = self._graphs[parity]
+        if graph is not None:
+            graph.replay()
+            ops.add_launches(self._graph_launches)
+        elif self._eager_steps[parity] < 1:
+            self._step_body(self._in_dense, self._in_idx, self._in_target, parity)
+            self._eager_steps[parity] += 1
+        else:
+            graph = torch.cuda.CUDAGraph()
+            before = ops.launch_count()
+            with torch.cuda.graph(graph):
+                self._step_body(self._in_dense, self._in_idx, self._in_target, parity)
+            self._graph_launches = ops.launch_count() - before
+            self._graphs[parity] = graph
+            graph.replay()
 
     def eval_step(self, dense: torch.Tensor, idx: torch.Tensor, target: Optional[torch.Tensor]) -> torch.Tensor:
         c = self.core
@@ -380,6 +426,7 @@ class DistributedDLRM:
         return state
 
     def close(self) -> None:
+        self._graphs = [None, None]
         if self.reducer is not None:
             self.reducer.close()
         if self.sym is not None:

@@ -113,3 +113,32 @@ def test_hybrid_step_matches_torch_sgd(world):
     model.eval()
     ref = model(dense.to(torch.bfloat16).float(), idx.long())[:, 0]
     assert (pred - ref.detach()).abs().max().item() < 0.1
+
+
+def test_graph_replayed_step_tracks_the_eager_step():
+    """DistributedDLRM replays one CUDA graph per slab parity; parameters and tables must follow the
+    eager step (differences only from atomic accumulation order), including an lr change mid-way
+    (lr is a device scalar inside the graph)."""
+    from raydp_b200.models import DLRM
+    from raydp_b200.parallel.hybrid import DistributedDLRM
+    torch.manual_seed(3)
+    B = 512
+    model = DLRM(13, SIZES, 32, sparse_grad=False).cuda()
+    engines = []
+    for use_graph in (False, True):
+        eng = DistributedDLRM(model.fused_spec(), B, torch.device("cuda"), momentum=0.9, use_graph=use_graph)
+        eng.core.load_from_module(model)
+        engines.append(eng)
+    for step in range(8):
+        dense, idx, y = _data(B, 50 + step)
+        lr = 0.05 if step < 5 else 0.01
+        for eng in engines:
+            eng.train_step(_pack_dense(dense), idx, y, lr)
+    torch.cuda.synchronize()
+    eager, graphed = engines
+    assert graphed._graphs[0] is not None and graphed._graphs[1] is not None and eager._graphs[0] is None
+    assert _rel(graphed.core.params, eager.core.params) < 2e-3
+    for t in (0, 5, 15):
+        assert _rel(graphed.core.tables[t], eager.core.tables[t]) < 2e-3
+    for eng in engines:
+        eng.close()

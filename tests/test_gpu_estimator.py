@@ -113,8 +113,12 @@ def test_dlrm_estimator_single_gpu(ray_cluster):
     state = torch.load(os.path.join(est.results.checkpoint.path, "model.pt"), weights_only=True)
     assert state["embeddings.25.weight"].shape == (sizes[25], 32) and "top.4.bias" in state
     trained.eval()
-    x = torch.tensor(np.stack([cols[f"d{i}"] for i in range(13)], 1)[:2048])
-    s = torch.tensor(np.stack([cols[f"c{t}"] for t in range(26)], 1)[:2048])
+    # checkpoint fidelity: the plain torch module restored from model.pt must score like the fused
+    # engine did on the same rows in its last evaluation epoch
+    x = torch.tensor(np.stack([cols[f"d{i}"] for i in range(13)], 1))
+    s = torch.tensor(np.stack([cols[f"c{t}"] for t in range(26)], 1))
     with torch.no_grad():
-        acc = ((trained(x, s)[:, 0] > 0).float() == torch.tensor(cols["label"][:2048])).float().mean().item()
-    assert acc > 0.52
+        acc = ((trained(x, s)[:, 0] > 0).float() == torch.tensor(cols["label"])).float().mean().item()
+    evals = [h for h in est.results.metrics_history if "eval_res" in h]
+    assert abs(acc - evals[-1]["eval_res"]["Accuracy"]) < 0.02, (acc, evals[-1]["eval_res"])
+    assert acc > 0.5
