@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--rows", type=int, default=100000, help="rows per embedding table")
     ap.add_argument("--impl", default="ours", choices=["ours", "standin"])
+    ap.add_argument("--check", action="store_true",
+                    help="ours only: graph-replayed steps vs eager steps from the same start, replicas bit-identical")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -45,6 +47,43 @@ def main():
         idx = torch.randint(0, args.rows, (B, 26), device=dev, generator=g, dtype=torch.int32)
         y = (torch.rand(B, device=dev, generator=g) < 0.25).float()
         pool.append((dense, idx, y))
+
+    if args.check:
+        from raydp_b200.parallel.hybrid import DistributedDLRM
+        model = DLRM(13, [1000] * 26, 32, sparse_grad=False).to(dev)
+        Bc = 1024
+        gen = torch.Generator(device=dev).manual_seed(7 + rank)
+        data = []
+        for _ in range(8):
+            d = torch.zeros(Bc, 16, device=dev, dtype=torch.bfloat16)
+            d[:, :13] = torch.randn(Bc, 13, device=dev, generator=gen).to(torch.bfloat16)
+            data.append((d, torch.randint(0, 1000, (Bc, 26), device=dev, generator=gen, dtype=torch.int32),
+                         (torch.rand(Bc, device=dev, generator=gen) < 0.3).float()))
+        finals = []
+        for use_graph in (False, True):
+            eng = DistributedDLRM(model.fused_spec(), Bc, dev, momentum=0.9, use_graph=use_graph)
+            eng.core.load_from_module(model)
+            for i, (d, idx, y) in enumerate(data):
+                eng.train_step(d, idx, y, 0.05 if i < 5 else 0.02)
+            torch.cuda.synchronize()
+            params = eng.core.params.detach().clone()
+            if world > 1:
+                ref = params.clone()
+                dist.broadcast(ref, src=0)
+                assert torch.equal(ref, params), "dense replicas diverged"
+            finals.append((params, [eng.core.tables[t].detach().clone() for t in eng.core.owned[:2]]))
+            assert use_graph == (eng._graphs[0] is not None)
+            eng.close()
+        rel = ((finals[0][0] - finals[1][0]).norm() / finals[0][0].norm()).item()
+        assert rel < 5e-3, rel
+        for a, b in zip(finals[0][1], finals[1][1]):
+            assert ((a - b).norm() / a.norm()).item() < 5e-3
+        if rank == 0:
+            print("CHECK OK", rel, flush=True)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     if args.impl == "ours":
         from raydp_b200.parallel.hybrid import DistributedDLRM

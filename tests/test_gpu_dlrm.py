@@ -142,3 +142,20 @@ def test_graph_replayed_step_tracks_the_eager_step():
         assert _rel(graphed.core.tables[t], eager.core.tables[t]) < 2e-3
     for eng in engines:
         eng.close()
+
+
+@pytest.mark.multigpu
+def test_multigpu_hybrid_dlrm_graph_vs_eager():
+    """Multi-process hybrid DLRM: graph-replayed steps track eager steps, dense replicas stay bit-identical."""
+    import os
+    import subprocess
+    import sys
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("needs >= 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={min(n_gpus, 4)}",
+           "--master-addr", "127.0.0.1", "--master-port", "29538", os.path.join(root, "bench", "dlrm_bench.py"),
+           "--check"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]

@@ -98,17 +98,17 @@ def test_dlrm_estimator_single_gpu(ray_cluster):
     model = DLRM(13, sizes, 32, sparse_grad=False)
     features = [f"d{i}" for i in range(13)] + [f"c{t}" for t in range(26)]
     est = TorchEstimator(num_workers=1, resources_per_worker={"GPU": 1}, model=model,
-                         optimizer=torch.optim.SGD(model.parameters(), lr=0.5), loss=nn.BCEWithLogitsLoss(),
+                         optimizer=torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9), loss=nn.BCEWithLogitsLoss(),
                          feature_columns=features, feature_types=[torch.float] * 13 + [torch.long] * 26,
-                         label_column="label", label_type=torch.float, batch_size=1024, num_epochs=24,
+                         label_column="label", label_type=torch.float, batch_size=1024, num_epochs=12,
                          shuffle=False, drop_last=True, metrics_name=["Accuracy"])
     est.fit(ds, ds)
     train = [h for h in est.results.metrics_history if "train_loss" in h]
     assert train[0]["engine"] == "fused-dlrm"
-    # plain SGD learns this model slowly (the PyTorch reference follows the same curve, see
-    # test_gpu_dlrm.py for the step-by-step numerics check)
-    assert train[-1]["train_loss"] < train[0]["train_loss"] - 0.003
-    assert train[-1]["train_res"]["Accuracy"] > 0.52
+    # SGD lr 0.05 + momentum 0.9: the plain PyTorch model goes 0.694 -> 0.56 in 8 epochs on this data
+    # (lr 0.5 without momentum only oscillates around 0.69, in PyTorch as well)
+    assert train[-1]["train_loss"] < train[0]["train_loss"] - 0.03
+    assert train[-1]["train_res"]["Accuracy"] > 0.58
     trained = est.get_model()
     state = torch.load(os.path.join(est.results.checkpoint.path, "model.pt"), weights_only=True)
     assert state["embeddings.25.weight"].shape == (sizes[25], 32) and "top.4.bias" in state
@@ -121,4 +121,4 @@ def test_dlrm_estimator_single_gpu(ray_cluster):
         acc = ((trained(x, s)[:, 0] > 0).float() == torch.tensor(cols["label"])).float().mean().item()
     evals = [h for h in est.results.metrics_history if "eval_res" in h]
     assert abs(acc - evals[-1]["eval_res"]["Accuracy"]) < 0.02, (acc, evals[-1]["eval_res"])
-    assert acc > 0.5
+    assert acc > 0.58
