@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--rows", type=int, default=100000, help="rows per embedding table")
     ap.add_argument("--impl", default="ours", choices=["ours", "standin"])
+    ap.add_argument("--breakdown", action="store_true",
+                    help="after timing, print per-kernel device time of 4 steps (torch profiler; not a bench number)")
     ap.add_argument("--check", action="store_true",
                     help="ours only: graph-replayed steps vs eager steps from the same start, replicas bit-identical")
     args = ap.parse_args()
@@ -137,6 +139,18 @@ def main():
                           "ms_per_step": ms / args.steps, "value": world * B * args.steps / (ms / 1e3),
                           "parallelism": "dense dp + table-wise embedding mp" if args.impl == "ours" else "ddp, replicated tables"}),
               flush=True)
+    if args.breakdown:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(4):
+                step(i)
+            torch.cuda.synchronize()
+        if rank == 0:
+            rows = sorted(prof.key_averages(), key=lambda k: -k.device_time_total)
+            total = sum(k.device_time_total for k in rows)
+            print(f"  4 steps: {total / 1e3:.3f} ms of kernel time in {sum(k.count for k in rows)} kernels", flush=True)
+            for k in rows[:22]:
+                print(f"  {k.device_time_total / 4:8.1f} us/step  x{k.count // 4:<3d} {k.key[:88]}", flush=True)
     if args.impl == "ours":
         eng.close()
     if world > 1:

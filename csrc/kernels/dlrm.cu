@@ -111,18 +111,29 @@ dot_interaction_fwd_kernel(const __nv_bfloat16* __restrict__ feats, __nv_bfloat1
   }
 }
 
-__global__ void __launch_bounds__(256)
+// dfeats[i, :] = sum_j dpair[i, j] * feats[j, :]  (+ the dense passthrough on row 0).
+// 8 warps x 4 feature rows each cover S <= 32 rows in one pass; lanes run over D.  A thread keeps its 4
+// row accumulators in registers, reads feats[j, d] once per j and the 4 dpair rows as warp-uniform
+// 128-bit broadcasts (dpair rows are padded to SP = 32 floats), i.e. 0.5 shared-memory loads per FMA
+// instead of the 2 of the element-per-thread formulation this replaced (which was LDS-bound).
+constexpr int kDotSP = 32;                 // padded pair-matrix row length
+// (4 blocks per SM: the per-sample chain load -> sync -> compute -> store is latency bound, so several
+//  samples must be in flight per SM; a fully unrolled j loop took 171 registers = 1 block per SM and was 2x slower)
+__global__ void __launch_bounds__(256, 4)
 dot_interaction_bwd_kernel(const __nv_bfloat16* __restrict__ feats, const __nv_bfloat16* __restrict__ dout,
                            __nv_bfloat16* __restrict__ dfeats, int B, int S, int D, int ld_out) {
-  extern __shared__ float sh[];            // feats [S][D + 1] | dpair [S][S] (symmetric, zero diagonal)
-  float* sf = sh;
-  float* sp = sh + S * (D + 1);
+  extern __shared__ __align__(16) float sh[];   // dpair [32][32] (symmetric, zero diagonal/padding) | feats [32][D + 1]
+  float* sp = sh;
+  float* sf = sh + kDotSP * kDotSP;
   const int n_pairs = S * (S - 1) / 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < kDotSP * (D + 1); i += blockDim.x) sf[i] = 0.f;     // rows >= S stay zero
   for (int b = blockIdx.x; b < B; b += gridDim.x) {
     const __nv_bfloat16* f = feats + size_t(b) * S * D;
     const __nv_bfloat16* go = dout + size_t(b) * ld_out;
+    __syncthreads();                                   // previous sample fully consumed
     for (int i = threadIdx.x; i < S * D; i += blockDim.x) sf[(i / D) * (D + 1) + (i % D)] = __bfloat162float(f[i]);
-    for (int i = threadIdx.x; i < S * S; i += blockDim.x) sp[i] = 0.f;
+    for (int i = threadIdx.x; i < kDotSP * kDotSP; i += blockDim.x) sp[i] = 0.f;
     __syncthreads();
     for (int q = threadIdx.x; q < n_pairs; q += blockDim.x) {
       int i = int((1.f + sqrtf(1.f + 8.f * float(q))) * 0.5f);
@@ -130,20 +141,35 @@ dot_interaction_bwd_kernel(const __nv_bfloat16* __restrict__ feats, const __nv_b
       while ((i + 1) * i / 2 <= q) ++i;
       const int j = q - i * (i - 1) / 2;
       const float g = __bfloat162float(go[D + q]);
-      sp[i * S + j] = g;
-      sp[j * S + i] = g;
+      sp[i * kDotSP + j] = g;
+      sp[j * kDotSP + i] = g;
     }
     __syncthreads();
     __nv_bfloat16* df = dfeats + size_t(b) * S * D;
-    for (int e = threadIdx.x; e < S * D; e += blockDim.x) {
-      const int i = e / D, d = e % D;
-      float v = (i == 0) ? __bfloat162float(go[d]) : 0.f;     // dense passthrough
-      const float* pr = sp + i * S;
-#pragma unroll 9
-      for (int j = 0; j < S; ++j) v = fmaf(pr[j], sf[j * (D + 1) + d], v);
-      df[e] = __float2bfloat16_rn(v);
+    const int i0 = warp * 4;                           // this warp's 4 feature rows
+    if (i0 < S) {
+      for (int d = lane; d < D; d += 32) {
+        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+#pragma unroll 2
+        for (int j4 = 0; j4 < kDotSP; j4 += 4) {
+          const float f0 = sf[(j4 + 0) * (D + 1) + d], f1 = sf[(j4 + 1) * (D + 1) + d];
+          const float f2 = sf[(j4 + 2) * (D + 1) + d], f3 = sf[(j4 + 3) * (D + 1) + d];
+          const float4 p0 = *reinterpret_cast<const float4*>(sp + (i0 + 0) * kDotSP + j4);
+          const float4 p1 = *reinterpret_cast<const float4*>(sp + (i0 + 1) * kDotSP + j4);
+          const float4 p2 = *reinterpret_cast<const float4*>(sp + (i0 + 2) * kDotSP + j4);
+          const float4 p3 = *reinterpret_cast<const float4*>(sp + (i0 + 3) * kDotSP + j4);
+          v0 = fmaf(p0.x, f0, fmaf(p0.y, f1, fmaf(p0.z, f2, fmaf(p0.w, f3, v0))));
+          v1 = fmaf(p1.x, f0, fmaf(p1.y, f1, fmaf(p1.z, f2, fmaf(p1.w, f3, v1))));
+          v2 = fmaf(p2.x, f0, fmaf(p2.y, f1, fmaf(p2.z, f2, fmaf(p2.w, f3, v2))));
+          v3 = fmaf(p3.x, f0, fmaf(p3.y, f1, fmaf(p3.z, f2, fmaf(p3.w, f3, v3))));
+        }
+        if (i0 == 0) v0 += __bfloat162float(go[d]);     // dense passthrough
+        const float vs[4] = {v0, v1, v2, v3};
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          if (i0 + r < S) df[(i0 + r) * D + d] = __float2bfloat16_rn(vs[r]);
+      }
     }
-    __syncthreads();
   }
 }
 
@@ -254,8 +280,8 @@ int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, i
 int rdp_dot_interaction_bwd(const void* feats, const void* dout, void* dfeats, int B, int S, int D, int ld_out,
                             void* stream) {
   RDP_REQUIRE(S <= kMaxS && D <= 128, "dot_interaction: bad shape S=%d D=%d", S, D);
-  int grid = B < num_sms() * 4 ? B : num_sms() * 4;
-  const size_t smem = (S * (D + 1) + S * S) * sizeof(float);
+  int grid = B < num_sms() * 4 ? B : num_sms() * 4;      // 4 resident blocks per SM (64 registers x 256 threads)
+  const size_t smem = (kDotSP * kDotSP + kDotSP * (D + 1)) * sizeof(float);
   dot_interaction_bwd_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(feats), static_cast<const __nv_bfloat16*>(dout),
       static_cast<__nv_bfloat16*>(dfeats), B, S, D, ld_out);

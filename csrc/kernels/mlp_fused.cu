@@ -102,6 +102,32 @@ __global__ void cast_weight_kernel(const float* __restrict__ w, int N, int K, __
   if (out_t != nullptr) out_t[size_t(k) * ldt + n] = v;
 }
 
+// fp32 [N, K] -> bf16 [N, ldo] and its transpose bf16 [K, ldt] through a 32 x 32 shared-memory tile:
+// both stores are coalesced (the element-per-thread kernel above writes the transpose with a stride)
+__global__ void __launch_bounds__(256) cast_weight_tiled_kernel(const float* __restrict__ w, int N, int K,
+                                                                __nv_bfloat16* __restrict__ out, int ldo,
+                                                                __nv_bfloat16* __restrict__ out_t, int ldt) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int n = n0 + ty + r * 8, k = k0 + tx;
+    float v = 0.f;
+    if (n < N && k < K) {
+      v = w[size_t(n) * K + k];
+      out[size_t(n) * ldo + k] = __float2bfloat16_rn(v);
+    }
+    tile[ty + r * 8][tx] = v;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int k = k0 + ty + r * 8, n = n0 + tx;
+    if (k < K && n < N) out_t[size_t(k) * ldt + n] = __float2bfloat16_rn(tile[tx][ty + r * 8]);
+  }
+}
+
 // contiguous fp32 -> bf16, 8 elements per thread (no transposed copy)
 __global__ void cast_bf16_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int64_t n8) {
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n8; i += int64_t(gridDim.x) * blockDim.x) {
@@ -554,6 +580,13 @@ int rdp_cast_weight(const float* w, int N, int K, void* out, int ldo, void* out_
     int grid = int((n8 + 255) / 256);
     if (grid > num_sms() * 16) grid = num_sms() * 16;
     cast_bf16_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(w, static_cast<__nv_bfloat16*>(out), n8);
+    RDP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
+  if (out_t != nullptr) {
+    dim3 grid((K + 31) / 32, (N + 31) / 32);
+    cast_weight_tiled_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        w, N, K, static_cast<__nv_bfloat16*>(out), ldo, static_cast<__nv_bfloat16*>(out_t), ldt);
     RDP_CHECK_CUDA(cudaGetLastError());
     return 0;
   }

@@ -184,3 +184,19 @@ def test_ingest_pack_matches_torch():
     assert torch.equal(idx_out[:, 0].long(), cols[2][5:].long() % 7)
     assert torch.equal(idx_out[:, 1].long(), cols[3][5:])
     assert int(idx_out[:, 2].min()) >= 0 and int(idx_out[:, 2].max()) < 1000
+
+
+def test_cast_weight_plain_and_transposed():
+    from raydp_b200 import ops
+    torch.manual_seed(4)
+    for N, K, ldo, ldt in ((100, 52, 56, 104), (1024, 384, 384, 1024), (33, 7, 8, 40)):
+        w = torch.randn(N, K, device="cuda")
+        out = torch.zeros(N, ldo, dtype=torch.bfloat16, device="cuda")[:, :K] if ldo != K else \
+            torch.zeros(N, K, dtype=torch.bfloat16, device="cuda")
+        out_t = torch.zeros(K, ldt, dtype=torch.bfloat16, device="cuda")[:, :N] if ldt != N else \
+            torch.zeros(K, N, dtype=torch.bfloat16, device="cuda")
+        ops.cast_weight(w, out, out_t)
+        assert torch.equal(out, w.to(torch.bfloat16)) and torch.equal(out_t, w.t().to(torch.bfloat16))
+        only = torch.zeros(N, K, dtype=torch.bfloat16, device="cuda")
+        ops.cast_weight(w, only)
+        assert torch.equal(only, w.to(torch.bfloat16))
