@@ -1,39 +1,38 @@
-// Large-GEMM path: CTA-pair (cta_group::2) tcgen05 kernels, 256 x 256 output tile per cluster.
+// Large-GEMM path: CTA-pair (cta_group::2) tcgen05 kernels.
 //
 // The 1-CTA kernels in gemm_tcgen05.cu move 32-48 KB of operands per 128 x {128,256} x 64 MMA
 // block; at BigMLP sizes (8192 x 16384 x 8192) that makes them L2->SM bandwidth bound at about half
-// of the tensor-core rate.  Here two CTAs of one cluster (one TPC) cooperate on one UMMA of
-// M = 256, N = 256: each CTA stages its own 128 rows of A and *half* of B (128 of the 256 columns),
-// the pair reads both halves, and each CTA's TMEM receives its 128 x 256 slice of the fp32
-// accumulator.  Per CTA that is 32 KB of shared-memory fill per 128 x 256 x 64 MACs -- half the
-// bytes per flop of the 1-CTA tile -- with a 6-deep TMA ring (192 KB) in front of the tensor cores.
+// of the tensor-core rate.  Here two CTAs of one cluster (one TPC) cooperate on UMMAs of
+// M = 256, N = 256: each CTA stages its own rows of A and *half* of B (128 of the 256 columns),
+// the pair reads both halves, and each CTA's TMEM receives its slice of the fp32 accumulator.
 //
 //   warp 0      TMA producer (both CTAs; completion bytes are signalled on the LEADER's barrier)
-//   warp 1      MMA issuer (leader CTA only) + TMEM allocation (both CTAs, cta_group::2)
-//   warps 2-5   epilogue: tcgen05.ld of the CTA's own accumulator slice, double-buffered in TMEM
-//               (2 x 256 columns) so it overlaps the next tile's main loop
+//   warp 1      MMA issuer (leader CTA) / tile scheduler (CTA 1, dynamic schedule); TMEM allocation
+//               in both CTAs (cta_group::2)
+//   warps 2..   epilogue: tcgen05.ld of the CTA's own accumulator slice (4 warps per 128-row half)
 //
-// Two operand layouts share the pipeline:
-//   kWgrad = false  out[M, N] (bf16) = act(A[M, K] . B[N, K]^T + bias)   K-major operands,
-//                   epilogue through swizzled smem staging + TMA stores
-//   kWgrad = true   out[Mw, Nw] (fp32) += G[rows, Mw]^T . X[rows, Nw]     MN-major operands,
-//                   epilogue red.global.add.v4.f32 (accumulates straight into weight.grad)
+// Template parameters of gemm_pair_kernel:
+//   kMode  0  out[M, N] (bf16) = act(A[M, K] . B[N, K]^T + bias)     K-major A and B (forward)
+//          1  out[Mw, Nw] (fp32) += G[rows, Mw]^T . X[rows, Nw]      MN-major A and B (wgrad),
+//             epilogue red.global.add.v4.f32 straight into weight.grad
+//          2  out[M, N] (bf16) = A[M, K] . B[K, N]                   K-major A, MN-major B (dgrad from
+//             the row-major weight, no transposed copy)
+//   kMH    1  cluster tile 256 x 256, 6-stage TMA ring, TMEM double-buffered (epilogue hidden)
+//          2  cluster tile 512 x 256, 4-stage ring, all 512 TMEM columns hold one tile; the epilogue
+//             drains TMEM into registers first so its stores overlap the next tile's MMAs
+//   kDynamic  tiles by cluster-launch-control work stealing instead of the static persistent loop
 //
 // Tiles are visited in groups of `group_m` row-blocks (column-major inside a group) so that the
-// 74 clusters in flight share a small set of A/B panels in the 126 MB L2.
+// clusters in flight share a small set of A/B panels in the 126 MB L2.
 #include "common.cuh"
 
 #include <stdlib.h>
 
 namespace rdp {
 
-constexpr int k2Threads = 192;
-constexpr int k2Stages = 6;
 constexpr int k2Tile = 256;                          // cluster tile edge (M and N)
 constexpr uint32_t k2HalfBytes = 128 * 64 * 2;       // one [128 x 64] bf16 operand block, 16 KB
-constexpr uint32_t k2StageBytes = 2 * k2HalfBytes;   // A block + B half per CTA
 constexpr uint32_t k2StoreBytes = 128 * 128;         // [128 rows x 64 cols] bf16 staging block
-constexpr int k2EpiWarps = 4;
 
 struct Gemm2Params {
   int M, N, K;                       // wgrad: M = Mw, N = Nw, K = batch rows
