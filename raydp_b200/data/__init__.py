@@ -395,6 +395,31 @@ class Dataset:
                                                      blocks[i].num_rows, batch_format), len(blocks))
         return from_arrow_refs(refs)
 
+    def map(self, fn: Callable[[Dict[str, Any]], Dict[str, Any]]) -> "Dataset":
+        """Row-wise ``fn(row_dict) -> row_dict`` (``ray.data.Dataset.map``)."""
+        def per_block(table: pa.Table, _fn=fn) -> pa.Table:
+            rows = [_fn(r) for r in table.to_pylist()]
+            return pa.Table.from_pylist(rows) if rows else table.slice(0, 0)
+        return self.map_batches(per_block)
+
+    def filter(self, fn: Callable[[Dict[str, Any]], bool]) -> "Dataset":
+        """Keep the rows for which ``fn(row_dict)`` is true."""
+        def per_block(table: pa.Table, _fn=fn) -> pa.Table:
+            keep = pa.array([bool(_fn(r)) for r in table.to_pylist()], type=pa.bool_())
+            return table.filter(keep)
+        return self.map_batches(per_block)
+
+    def add_column(self, name: str, fn: Callable) -> "Dataset":
+        """``fn(pandas.DataFrame) -> Series`` evaluated per block and appended as column ``name``."""
+        def per_block(table: pa.Table, _fn=fn, _name=name) -> pa.Table:
+            return table.append_column(_name, pa.array(_fn(table.to_pandas())))
+        return self.map_batches(per_block)
+
+    def sort(self, key: str, descending: bool = False) -> "Dataset":
+        """Global sort by one column (gathers on the driver; meant for small result sets)."""
+        table = self.to_arrow().sort_by([(key, "descending" if descending else "ascending")])
+        return from_arrow([table])
+
     def select_columns(self, cols: List[str]) -> "Dataset":
         return self.map_batches(lambda t, _c=tuple(cols): t.select(list(_c)))
 
@@ -414,6 +439,24 @@ class Dataset:
     def to_spark(self, spark, parallelism=None):
         from raydp_b200.spark.dataset import ray_dataset_to_spark_dataframe
         return ray_dataset_to_spark_dataframe(spark, self.schema(), self.to_arrow_refs())
+
+    def to_tf(self, feature_columns, label_columns, batch_size: int = 1, drop_last: bool = False,
+              feature_type_spec=None, label_type_spec=None):
+        """``tf.data.Dataset`` of ``(features, labels)`` batches (``ray.data.Dataset.to_tf`` as consumed by
+        reference ``tf/estimator.py:171-210``).  A single column name gives one tensor, a list gives a
+        dict of per-column tensors.  Needs TensorFlow."""
+        try:
+            import tensorflow as tf
+        except ImportError as exc:
+            raise ImportError("Dataset.to_tf needs TensorFlow, which is not installed") from exc
+        table = self.to_arrow()
+
+        def pick(cols):
+            if isinstance(cols, str):
+                return table.column(cols).to_numpy(zero_copy_only=False)
+            return {c: table.column(c).to_numpy(zero_copy_only=False) for c in cols}
+        ds = tf.data.Dataset.from_tensor_slices((pick(feature_columns), pick(label_columns)))
+        return ds.batch(batch_size, drop_remainder=drop_last)
 
     def write_parquet(self, path: str) -> None:
         import pyarrow.parquet as pq

@@ -81,3 +81,19 @@ def test_legacy_parallel_iterator_worker():
     w = ParallelIteratorWorkerWithLen(lambda: range(3), repeat=True, num_records=3)
     w.par_iter_init([lambda it: (v * 10 for v in it)])
     assert [w.par_iter_next() for _ in range(5)] == [0, 10, 20, 0, 10] and len(w) == 3
+
+
+def test_row_wise_map_filter_add_column_sort(ray_cluster):
+    import pyarrow as pa
+    from raydp_b200 import data as rdata
+    ds = rdata.from_arrow([pa.table({"a": list(range(0, 5))}), pa.table({"a": list(range(5, 10))})])
+    out = ds.map(lambda r: {"a": r["a"], "sq": r["a"] ** 2}).filter(lambda r: r["sq"] % 2 == 1)
+    assert [r["sq"] for r in out.take_all()] == [1, 9, 25, 49, 81]
+    plus = ds.add_column("b", lambda pdf: pdf["a"] * 10).sort("b", descending=True)
+    assert [r["b"] for r in plus.take(3)] == [90, 80, 70]
+    import pytest
+    try:
+        import tensorflow  # noqa: F401
+    except ImportError:
+        with pytest.raises(ImportError):
+            ds.to_tf("a", "a", batch_size=2)
