@@ -39,6 +39,12 @@ class _AliasFinder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
 if not any(isinstance(f, _AliasFinder) for f in sys.meta_path):
     sys.meta_path.insert(0, _AliasFinder())
 
+# Scripts written against the reference also ``import ray`` and ``from pyspark.sql...``: provide those
+# names (pointing at this framework's runtime / DataFrame engine) unless the real packages exist.
+from raydp_b200 import compat as _compat  # noqa: E402
+
+_compat.install()
+
 __all__ = ["init_spark", "stop_spark", "__version__"]
 
 

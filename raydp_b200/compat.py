@@ -1,0 +1,166 @@
+"""Import-name compatibility for scripts written against the reference's stack.
+
+Reference programs start with ``import ray`` / ``from pyspark.sql.functions import col`` (every file
+under ``examples/`` does).  Neither package exists here -- the runtime, the DataFrame engine, the
+dataset layer and the trainer are this framework's own -- so :func:`install` registers thin module
+objects named ``ray`` and ``pyspark`` whose attributes point at the equivalents:
+
+    ray.init / get / put / remote / get_actor / ...      -> raydp_b200.runtime
+    ray.util.placement_group, ray.util.state.list_actors -> raydp_b200.runtime
+    ray.data.from_spark / from_arrow_refs / Dataset      -> raydp_b200.data
+    ray.train.torch.TorchTrainer, ray.train.ScalingConfig, ray.air.session, ...  -> raydp_b200.train
+    ray.cluster_utils.Cluster                            -> raydp_b200.runtime.cluster_utils
+    pyspark.sql.{SparkSession,DataFrame,functions,types,Window}, pyspark.pandas   -> raydp_b200.sql
+
+A real installation always wins: a name is only registered when ``importlib`` cannot find the
+genuine package (``force=True`` overrides).  ``import raydp`` calls ``install()``; ``import raydp_b200``
+does not touch ``sys.modules``.
+"""
+from __future__ import annotations
+
+import importlib
+import importlib.machinery
+import importlib.util
+import sys
+import types
+from typing import Dict, List
+
+_INSTALLED: List[str] = []
+
+
+def _module(name: str, doc: str, **attrs) -> types.ModuleType:
+    mod = types.ModuleType(name, doc)
+    mod.__dict__.update(attrs)
+    mod.__raydp_b200_alias__ = True
+    # a spec keeps ``importlib.util.find_spec(name)`` (used by other libraries to probe for optional
+    # dependencies) from raising on a module that sits in sys.modules without one
+    mod.__spec__ = importlib.machinery.ModuleSpec(name, loader=None)
+    return mod
+
+
+def _register(tree: Dict[str, types.ModuleType]) -> None:
+    """``tree`` maps dotted names to modules; children become attributes of their parents."""
+    for name in sorted(tree):
+        sys.modules[name] = tree[name]
+        _INSTALLED.append(name)
+        parent, _, leaf = name.rpartition(".")
+        if parent and parent in tree:
+            setattr(tree[parent], leaf, tree[name])
+
+
+def _absent(name: str) -> bool:
+    if name in sys.modules:
+        return bool(getattr(sys.modules[name], "__raydp_b200_alias__", False))
+    try:
+        return importlib.util.find_spec(name) is None
+    except (ImportError, ValueError):
+        return True
+
+
+def _ray_tree() -> Dict[str, types.ModuleType]:
+    from raydp_b200 import data, runtime, train
+    from raydp_b200.runtime import cluster_utils, protocol
+    from raydp_b200.train import checkpoint, config, session, torch_utils, trainer
+
+    top = {k: getattr(runtime, k) for k in (
+        "init", "shutdown", "is_initialized", "get", "put", "wait", "remote", "get_actor", "kill", "nodes",
+        "cluster_resources", "available_resources", "get_runtime_context", "ObjectRef")}
+    ray = _module("ray", "alias of raydp_b200.runtime (see raydp_b200.compat)", __version__="2.50.0", **top)
+    ray.__path__ = []           # lets ``import ray.data`` style imports resolve through sys.modules
+
+    class _Client:              # ``ray.util.client.ray.is_connected()`` (reference context.py:219)
+        @staticmethod
+        def is_connected() -> bool:
+            return False
+
+    tree = {
+        "ray": ray,
+        "ray.actor": _module("ray.actor", "", exit_actor=runtime.exit_actor, ActorHandle=runtime.ActorHandle),
+        "ray.exceptions": _module("ray.exceptions", "", RayError=protocol.RuntimeErrorBase,
+                                  RayTaskError=protocol.TaskError, RayActorError=protocol.ActorDiedError,
+                                  GetTimeoutError=protocol.GetTimeoutError, ObjectLostError=protocol.ObjectLostError),
+        "ray.util": _module("ray.util", "", placement_group=runtime.placement_group,
+                            remove_placement_group=runtime.remove_placement_group,
+                            placement_group_table=runtime.placement_group_table,
+                            get_placement_group=runtime.get_placement_group,
+                            get_node_ip_address=runtime.get_node_ip_address),
+        "ray.util.placement_group": _module("ray.util.placement_group", "",
+                                            placement_group=runtime.placement_group,
+                                            remove_placement_group=runtime.remove_placement_group,
+                                            PlacementGroup=runtime.PlacementGroup),
+        "ray.util.scheduling_strategies": _module(
+            "ray.util.scheduling_strategies", "",
+            PlacementGroupSchedulingStrategy=runtime.PlacementGroupSchedulingStrategy),
+        "ray.util.state": _module("ray.util.state", "", list_actors=runtime.list_actors),
+        "ray.util.client": _module("ray.util.client", "", ray=_Client),
+        "ray.cluster_utils": _module("ray.cluster_utils", "", Cluster=cluster_utils.Cluster),
+        "ray.data": data,
+        "ray.train": _module("ray.train", "", ScalingConfig=config.ScalingConfig, RunConfig=config.RunConfig,
+                             FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig,
+                             Checkpoint=checkpoint.Checkpoint, get_dataset_shard=session.get_dataset_shard,
+                             report=session.report, get_context=session.get_context,
+                             get_checkpoint=session.get_checkpoint, Result=trainer.Result),
+        "ray.train.torch": _module("ray.train.torch", "", TorchTrainer=trainer.TorchTrainer,
+                                   TorchConfig=config.TorchConfig, TorchCheckpoint=checkpoint.TorchCheckpoint,
+                                   prepare_model=torch_utils.prepare_model, get_device=torch_utils.get_device),
+        "ray.air": _module("ray.air", "", session=session, Checkpoint=checkpoint.Checkpoint,
+                           ScalingConfig=config.ScalingConfig, RunConfig=config.RunConfig,
+                           FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig),
+        "ray.air.config": _module("ray.air.config", "", ScalingConfig=config.ScalingConfig,
+                                  RunConfig=config.RunConfig, FailureConfig=config.FailureConfig,
+                                  CheckpointConfig=config.CheckpointConfig),
+        "ray.air.session": session,
+    }
+    # ray.data / ray.air.session are real modules of this package: register under the alias names too
+    ray.data, ray.train = data, tree["ray.train"]
+    del train
+    return tree
+
+
+def _pyspark_tree() -> Dict[str, types.ModuleType]:
+    from raydp_b200 import sql
+    from raydp_b200.sql import column, dataframe, functions, pandas_api, session, types as sql_types, window
+
+    pyspark = _module("pyspark", "alias of raydp_b200.sql (see raydp_b200.compat)", __version__="3.5.0",
+                      SparkConf=session.SparkConf, SparkContext=session.SparkContext,
+                      StorageLevel=dataframe.StorageLevel, Row=sql_types.Row)
+    pyspark.__path__ = []
+    return {
+        "pyspark": pyspark,
+        "pyspark.sql": sql,
+        "pyspark.sql.functions": functions,
+        "pyspark.sql.types": sql_types,
+        "pyspark.sql.window": window,
+        "pyspark.sql.session": session,
+        "pyspark.sql.dataframe": dataframe,
+        "pyspark.sql.column": column,
+        "pyspark.pandas": pandas_api,
+        "pyspark.storagelevel": _module("pyspark.storagelevel", "", StorageLevel=dataframe.StorageLevel),
+    }
+
+
+def install(ray: bool = True, pyspark: bool = True, force: bool = False) -> List[str]:
+    """Register the ``ray`` / ``pyspark`` aliases that are missing; returns the top-level names added."""
+    added = []
+    if ray and (force or _absent("ray")) and not getattr(sys.modules.get("ray"), "__raydp_b200_alias__", False):
+        _register(_ray_tree())
+        added.append("ray")
+    if pyspark and (force or _absent("pyspark")) and \
+            not getattr(sys.modules.get("pyspark"), "__raydp_b200_alias__", False):
+        _register(_pyspark_tree())
+        added.append("pyspark")
+    return added
+
+
+def uninstall() -> None:
+    """Remove every alias :func:`install` registered."""
+    for name in _INSTALLED:
+        mod = sys.modules.get(name)
+        if mod is not None and (getattr(mod, "__raydp_b200_alias__", False) or
+                                getattr(mod, "__name__", "").startswith("raydp_b200")):
+            del sys.modules[name]
+    _INSTALLED.clear()
+
+
+def installed() -> List[str]:
+    return sorted(set(n.split(".")[0] for n in _INSTALLED))

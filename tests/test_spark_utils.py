@@ -76,3 +76,31 @@ def test_split_rows_evenly():
     assert [sum(stop - start for _, start, stop in p) for p in plan] == [8, 8, 8]
     seen = sorted((b, s) for p in plan for b, s, _ in p)
     assert seen[0] == (0, 0)
+
+
+def test_reference_import_names_resolve_to_this_framework():
+    """``import raydp`` provides ``ray`` / ``pyspark`` aliases when the real packages are absent, so
+    scripts written against the reference (``import ray``; ``from pyspark.sql.functions import col``)
+    import unchanged; a genuine installation is never shadowed."""
+    import importlib
+    import sys
+    import raydp  # noqa: F401
+    from raydp_b200 import compat, data as rdata, runtime
+    from raydp_b200.sql import functions as F
+    if "ray" in compat.installed():
+        import ray
+        from ray.train.torch import TorchTrainer
+        from ray.util.placement_group import placement_group
+        assert ray.init is runtime.init and ray.data is rdata and placement_group is runtime.placement_group
+        assert TorchTrainer.__module__.startswith("raydp_b200.train")
+        assert ray.util.client.ray.is_connected() is False
+    if "pyspark" in compat.installed():
+        from pyspark.sql.functions import col
+        from pyspark.sql import SparkSession
+        import pyspark.pandas as ps
+        assert col is F.col and SparkSession.__module__.startswith("raydp_b200.sql") and hasattr(ps, "range")
+    assert compat.install() == []                      # idempotent
+    real = [n for n in ("ray", "pyspark") if n not in compat.installed()]
+    for n in real:                                      # never shadow a genuine package
+        assert not getattr(importlib.import_module(n), "__raydp_b200_alias__", False)
+    assert all(getattr(sys.modules[n], "__raydp_b200_alias__", False) for n in compat.installed())
