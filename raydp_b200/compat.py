@@ -164,3 +164,24 @@ def uninstall() -> None:
 
 def installed() -> List[str]:
     return sorted(set(n.split(".")[0] for n in _INSTALLED))
+
+
+def _main(argv: List[str]) -> int:
+    """``python -m raydp_b200.compat script.py [args...]``: run a script written against the reference
+    (``import ray`` / ``import pyspark`` / ``import raydp`` in any order) with the aliases in place."""
+    import os
+    import runpy
+    if not argv:
+        print("usage: python -m raydp_b200.compat script.py [args...]", file=sys.stderr)
+        return 2
+    install()
+    import raydp  # noqa: F401  (registers the raydp.* alias finder)
+    script = os.path.abspath(argv[0])
+    sys.argv = [script] + list(argv[1:])
+    sys.path.insert(0, os.path.dirname(script))
+    runpy.run_path(script, run_name="__main__")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(_main(sys.argv[1:]))

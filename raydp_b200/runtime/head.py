@@ -289,7 +289,10 @@ class Head:
         try:
             while True:
                 req_id, op, kwargs = conn.recv()
-                self._pool.submit(run, req_id, op, kwargs)
+                try:
+                    self._pool.submit(run, req_id, op, kwargs)
+                except RuntimeError:          # the head is shutting down: late requests are dropped
+                    break
         except (EOFError, OSError):
             pass
         finally:

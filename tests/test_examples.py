@@ -30,3 +30,15 @@ def test_submit_py_files_example():
                 "--conf", "spark.executor.cores=1", "--conf", "spark.executor.memory=500M",
                 "examples/pyfiles_main.py"])
     assert "py-files OK" in out
+
+
+def test_reference_example_runs_unchanged_through_compat_runner():
+    """A script written against the reference (``import ray``, ``from pyspark.sql.functions import ...``,
+    ``raydp.init_spark`` with JVM-only options, ``ray.data.from_spark``) runs as is under
+    ``python -m raydp_b200.compat``."""
+    import pytest
+    script = "/root/reference/examples/data_process.py"
+    if not os.path.exists(script):
+        pytest.skip("reference examples not mounted")
+    proc_out = _run([sys.executable, "-m", "raydp_b200.compat", script])
+    assert "Traceback" not in proc_out
