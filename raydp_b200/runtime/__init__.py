@@ -123,7 +123,23 @@ def shutdown() -> None:
             _info = {}
 
 
-atexit.register(shutdown)
+def _register_exit_hooks() -> None:
+    """Shut the head down as early as possible at interpreter exit.  ``threading._shutdown`` runs
+    BEFORE ``atexit`` and first disables every ``ThreadPoolExecutor`` (concurrent.futures'
+    ``_python_exit``): from then on the head cannot schedule the handshake of a worker process that is
+    still starting, and its launch thread would sit in ``ready.wait(60)`` while the interpreter waits
+    for that thread.  Callbacks registered with ``threading._register_atexit`` run in reverse order of
+    registration, i.e. ours (registered after concurrent.futures was imported) runs first."""
+    import threading
+    import concurrent.futures.thread  # noqa: F401  (its own exit hook must be registered BEFORE ours)
+    try:
+        threading._register_atexit(shutdown)          # CPython >= 3.9
+    except Exception:  # noqa: BLE001
+        pass
+    atexit.register(shutdown)
+
+
+_register_exit_hooks()
 
 
 def _rpc(op: str, **kwargs):

@@ -576,7 +576,7 @@ class Head:
         call.holds = holds  # type: ignore[attr-defined]
 
         def launch():
-            if not worker.ready.wait(60.0) or worker.dead:
+            if not self._wait_ready(worker):
                 self._release(task.resources, holds)
                 self._task_failed(task, "task worker failed to start")
                 return
@@ -624,8 +624,16 @@ class Head:
         self._kick()
         return actor_id, actor.create_oid
 
+    def _wait_ready(self, worker: _Worker, timeout: float = 60.0) -> bool:
+        """Wait for a spawned worker's handshake, giving up at once when the head shuts down."""
+        deadline = time.time() + timeout
+        while not worker.ready.wait(0.25):
+            if self._shutdown or worker.dead or time.time() > deadline:
+                return False
+        return not (worker.dead or self._shutdown)
+
     def _try_start_actor(self, actor: _Actor) -> bool:
-        if actor.state == DEAD:
+        if actor.state == DEAD or self._shutdown:
             return True
         got = self._reserve(actor.resources, actor.pg, actor.bundle, prefer=None)
         if got is None:
@@ -641,7 +649,7 @@ class Head:
         actor.worker = worker
 
         def launch():
-            if not worker.ready.wait(60.0) or worker.dead:
+            if not self._wait_ready(worker):
                 return  # death handler takes over
             ctx = {"actor_id": actor.actor_id, "name": actor.name, "namespace": actor.namespace,
                    "was_restarted": actor.num_restarts > 0, "max_concurrency": actor.max_concurrency,
@@ -988,6 +996,8 @@ class Head:
                 pass
         for w in workers:
             _kill_proc(w.proc)
+            w.dead = True
+            w.ready.set()           # releases launch threads still waiting for the worker's handshake
         try:
             self._listener.close()
         except OSError:
