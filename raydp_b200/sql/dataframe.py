@@ -235,8 +235,26 @@ class DataFrame:
 
     def dropDuplicates(self, subset=None) -> "DataFrame":
         if subset:
-            raise NotImplementedError("dropDuplicates(subset) is not supported")
+            keys = [subset] if isinstance(subset, str) else list(subset)
+            return self.repartition(self.rdd.getNumPartitions(), *keys)._derive(("distinct_subset", tuple(keys)))
         return self.distinct()
+
+    drop_duplicates = dropDuplicates
+
+    def unionByName(self, other: "DataFrame", allowMissingColumns: bool = False) -> "DataFrame":
+        mine, theirs = self.columns, other.columns
+        if allowMissingColumns:
+            from raydp_b200.sql import functions as F
+            for c in mine:
+                if c not in theirs:
+                    other = other.withColumn(c, F.lit(None))
+            for c in theirs:
+                if c not in mine:
+                    self = self.withColumn(c, F.lit(None))     # noqa: PLW0642
+            mine = self.columns
+        elif set(mine) != set(theirs):
+            raise ValueError(f"unionByName: column sets differ: {mine} vs {theirs}")
+        return self.union(other.select(*mine))
 
     def limit(self, n: int) -> "DataFrame":
         table = self._collect_table(limit=n)

@@ -280,6 +280,13 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
                           use_threads=False)
     if kind == "distinct":
         return table.group_by(table.column_names, use_threads=False).aggregate([])
+    if kind == "distinct_subset":          # keep the first row of every key combination
+        if table.num_rows == 0:
+            return table
+        tagged = table.append_column("__row", pa.array(np.arange(table.num_rows, dtype=np.int64)))
+        first = tagged.group_by(list(op[1]), use_threads=False).aggregate([("__row", "min")])
+        rows = first.column("__row_min").combine_chunks()
+        return table.take(rows.take(pc.sort_indices(rows)))     # original order within the partition
     if kind == "cast_schema":
         return table.cast(op[1], safe=False)
     if kind == "posexplode":

@@ -221,3 +221,19 @@ def test_map_in_pandas_accepts_ddl_schema(spark_session):
 
     out = df.mapInPandas(add, "a int, b double, z long").collect()
     assert [r.z for r in out] == [10, 20]
+
+
+def test_drop_duplicates_subset_and_union_by_name(spark_session):
+    df = spark_session.createDataFrame([(1, "a", 10), (1, "b", 11), (2, "c", 12), (2, "d", 13), (3, "e", 14)],
+                                       ["k", "s", "v"])
+    out = df.dropDuplicates(["k"]).collect()
+    assert sorted(r.k for r in out) == [1, 2, 3] and {r.s for r in out} <= {"a", "b", "c", "d", "e"}
+    assert df.dropDuplicates().count() == 5
+    other = spark_session.createDataFrame([(99, "z")], ["v", "s"])
+    merged = df.unionByName(other, allowMissingColumns=True)
+    assert merged.count() == 6 and merged.columns == ["k", "s", "v"]
+    last = [r for r in merged.collect() if r.v == 99][0]
+    assert last.s == "z" and last.k is None
+    import pytest as _pytest
+    with _pytest.raises(ValueError):
+        df.unionByName(other)
