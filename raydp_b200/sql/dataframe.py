@@ -292,12 +292,32 @@ class DataFrame:
         return GroupedData(self, []).agg(*exprs)
 
     def join(self, other: "DataFrame", on=None, how: str = "inner") -> "DataFrame":
-        if on is None:
-            raise NotImplementedError("cross joins are not supported")
-        keys = [on] if isinstance(on, str) else [k if isinstance(k, str) else k._output_name() for k in on]
-        # broadcast-hash join: the right side is collected once and shipped with the plan
+        """Broadcast-hash join: the right side is collected once and shipped with the plan.  ``on`` is a
+        column name, a list of names, or an equality expression ``left.a == right.b`` (conjunctions
+        with ``&`` allowed).  Right / full outer joins first gather the left side into one partition
+        (unmatched right rows must be emitted exactly once)."""
+        how = how.lower()
+        if on is None or how == "cross":
+            return self.crossJoin(other)
+        if isinstance(on, Column):
+            pairs = _equi_join_pairs(on)
+            keys, right_keys = [p[0] for p in pairs], [p[1] for p in pairs]
+        else:
+            keys = [on] if isinstance(on, str) else [k if isinstance(k, str) else k._output_name() for k in on]
+            right_keys = keys
+        left = self
+        if how in ("right", "right_outer", "rightouter", "outer", "full", "full_outer", "fullouter"):
+            left = self.coalesce(1)
         right = other._collect_table()
-        return self._derive(("join", right, keys, how.lower(), keys))
+        how = {"rightouter": "right_outer", "fullouter": "full_outer"}.get(how, how)
+        return left._derive(("join", right, keys, how, right_keys))
+
+    def crossJoin(self, other: "DataFrame") -> "DataFrame":
+        from raydp_b200.sql import functions as F
+        key = "__cross_key"
+        joined = self.withColumn(key, F.lit(1))._derive(
+            ("join", other.withColumn(key, F.lit(1))._collect_table(), [key], "inner", [key]))
+        return joined.drop(key)
 
     def union(self, other: "DataFrame") -> "DataFrame":
         tables = self._run("collect") + other._run("collect")
@@ -476,6 +496,16 @@ class _NAFunctions:
 def _fmt(v, truncate: bool) -> str:
     s = "null" if v is None else str(v)
     return s[:17] + "..." if truncate and len(s) > 20 else s
+
+
+def _equi_join_pairs(cond: Column) -> List[Tuple[str, str]]:
+    """``(a == b) & (c == d)`` -> ``[(a, b), (c, d)]``; anything else is not an equi-join."""
+    if cond._kind == "binop" and cond._args[0] == "&":
+        return _equi_join_pairs(cond._args[1]) + _equi_join_pairs(cond._args[2])
+    if cond._kind == "binop" and cond._args[0] == "==" and all(
+            isinstance(a, Column) and a._kind == "col" for a in cond._args[1:3]):
+        return [(cond._args[1]._args[0], cond._args[2]._args[0])]
+    raise NotImplementedError("join conditions must be equalities between columns (optionally combined with &)")
 
 
 def _sort_keys(cols, ascending) -> List[Tuple[str, str]]:

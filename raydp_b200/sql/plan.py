@@ -222,7 +222,7 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
             names.append(expr._output_name())
         return pa.table(arrays, names=names) if arrays else table.select([])
     if kind == "drop":
-        keep = [c for c in table.column_names if c not in op[1]]
+        keep = [i for i, c in enumerate(table.column_names) if c not in op[1]]   # by index: names may repeat
         return table.select(keep)
     if kind == "rename":
         return table.rename_columns([op[2] if c == op[1] else c for c in table.column_names])
@@ -276,8 +276,14 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
                "outer": "full outer", "full": "full outer", "full_outer": "full outer",
                "left_semi": "left semi", "leftsemi": "left semi", "left_anti": "left anti",
                "leftanti": "left anti"}[how]
-        return table.join(right, keys=keys, right_keys=right_keys, join_type=how,
-                          use_threads=False)
+        out = table.join(right, keys=keys, right_keys=right_keys, join_type=how, use_threads=False)
+        if how in ("left semi", "left anti") or len(set(out.column_names)) != len(out.column_names):
+            return out
+        # Spark's layout: join keys, then the other left columns, then the other right columns
+        rest_left = [c for c in table.column_names if c not in keys]
+        rest_right = [c for c in right.column_names if c not in right_keys and c not in table.column_names]
+        wanted = [c for c in list(keys) + rest_left + rest_right if c in out.column_names]
+        return out.select(wanted) if wanted != out.column_names else out
     if kind == "distinct":
         return table.group_by(table.column_names, use_threads=False).aggregate([])
     if kind == "distinct_subset":          # keep the first row of every key combination

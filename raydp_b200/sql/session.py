@@ -195,10 +195,14 @@ class _Builder:
     def getOrCreate(self) -> "SparkSession":
         global _active_session
         with _active_lock:
-            if _active_session is not None and not _active_session._stopped:
+            wanted = self._opts.get("spark.master")
+            if _active_session is not None and not _active_session._stopped and (
+                    wanted is None or wanted == _active_session._conf.get("spark.master", wanted)):
                 for k, v in self._opts.items():
                     _active_session._conf.set(k, v)
                 return _active_session
+            # an explicit, different master (e.g. ``ray://<app master>`` from init_spark while a local[n]
+            # session is still around) gets its own session instead of silently reusing the old backend
             opts = dict(_builder_options)
             submitted = os.environ.get("RAYDP_SUBMIT_CONF")
             if submitted:                       # running under raydp-submit

@@ -237,3 +237,19 @@ def test_drop_duplicates_subset_and_union_by_name(spark_session):
     import pytest as _pytest
     with _pytest.raises(ValueError):
         df.unionByName(other)
+
+
+def test_join_variants(spark_session):
+    a = spark_session.createDataFrame([(1, "x"), (2, "y"), (3, "z")], ["k", "a"]).repartition(2)
+    b = spark_session.createDataFrame([(2, "B"), (3, "C"), (4, "D")], ["k", "b"])
+    key = lambda r: tuple("" if v is None else str(v) for v in r)  # noqa: E731
+    rows = lambda df: sorted((tuple(r) for r in df.collect()), key=key)  # noqa: E731
+    assert rows(a.join(b, "k", "right")) == sorted([(2, "y", "B"), (3, "z", "C"), (4, None, "D")], key=key)
+    assert len(rows(a.join(b, "k", "outer"))) == 4                      # unmatched rows exactly once each
+    assert rows(a.join(b, a.k == b.k)) == [(2, "y", "B"), (3, "z", "C")]
+    b2 = b.withColumnRenamed("k", "kk")
+    assert a.join(b2, a.k == b2.kk, "left_semi").count() == 2
+    assert a.crossJoin(b).count() == 9 and a.join(b, how="cross").count() == 9
+    import pytest as _pytest
+    with _pytest.raises(NotImplementedError):
+        a.join(b, a.k > b.k)
