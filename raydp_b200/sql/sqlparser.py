@@ -13,8 +13,10 @@ subset people actually type is parsed directly into the DataFrame API:
 
 Expressions: literals, column names, ``+ - * / %``, comparisons, ``AND / OR / NOT``, ``IS [NOT] NULL``,
 ``IN (...)``, ``BETWEEN a AND b``, ``CAST(x AS type)``, ``CASE WHEN ... THEN ... [ELSE ...] END`` and calls
-of anything in :mod:`raydp_b200.sql.functions` (aggregates included).  Joins, sub-queries and
-window clauses are not parsed; use the DataFrame API for those.
+of anything in :mod:`raydp_b200.sql.functions` (aggregates included).  ``FROM a [INNER|LEFT|RIGHT|FULL|
+CROSS|LEFT SEMI|LEFT ANTI] JOIN b ON a.k = b.k [AND ...] | USING (k)`` is an equi-join (column qualifiers are
+dropped: a join key named differently on the two sides keeps the left name).  Sub-queries and window
+clauses are not parsed; use the DataFrame API for those.
 """
 from __future__ import annotations
 
@@ -36,7 +38,7 @@ _TOKEN = re.compile(r"""
 _AGGREGATES = {"count", "sum", "avg", "mean", "min", "max", "first", "stddev", "variance", "countdistinct"}
 _KEYWORDS = {"select", "from", "where", "group", "by", "having", "order", "limit", "as", "and", "or", "not",
              "is", "null", "in", "between", "case", "when", "then", "else", "end", "cast", "distinct", "asc",
-             "desc", "true", "false", "like"}
+             "desc", "true", "false", "like", "join", "inner", "left", "right", "full", "cross", "on", "using"}
 
 
 class SqlError(ValueError):
@@ -441,8 +443,59 @@ def _parse_select(p: _Parser, session):
         one = session.range(1)
         return one.select(*[c for c in items if not isinstance(c, str)])
     df = session.catalog.lookup(_qualified_name(p))
-    if p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS:
-        p.name()                                    # table alias: columns are resolved by bare name
+    join_words = {"join", "inner", "left", "right", "full", "cross", "on", "using", "outer", "semi", "anti"}
+
+    def skip_alias():
+        if p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS | join_words:
+            p.name()                                # table alias: columns are resolved by bare name
+    skip_alias()
+    while True:                                     # [INNER | LEFT | RIGHT | FULL [OUTER] | CROSS | LEFT SEMI/ANTI] JOIN
+        how = None
+        if p.kw("join") or p.kw("inner", "join"):
+            how = "inner"
+        elif p.kw("cross", "join"):
+            how = "cross"
+        else:
+            for side in ("left", "right", "full"):
+                if p.at_kw(side):
+                    p.i += 1
+                    if p.kw("semi"):
+                        how = side + "_semi"
+                    elif p.kw("anti"):
+                        how = side + "_anti"
+                    else:
+                        p.kw("outer")
+                        how = side
+                    if not p.kw("join"):
+                        raise SqlError(f"expected JOIN after {side.upper()}")
+                    break
+        if how is None:
+            break
+        other = session.catalog.lookup(_qualified_name(p))
+        skip_alias()
+        if how == "cross":
+            df = df.crossJoin(other)
+        elif p.kw("using"):
+            p.expect_op("(")
+            names = [p.name()]
+            while p.op(","):
+                names.append(p.name())
+            p.expect_op(")")
+            df = df.join(other, names, how)
+        elif p.kw("on"):
+            from raydp_b200.sql.dataframe import _equi_join_pairs
+            pairs = [(a, b) if a in df.columns else (b, a) for a, b in _equi_join_pairs(p.expr())]
+            left_keys, right_keys = [a for a, _ in pairs], [b for _, b in pairs]
+            if left_keys == right_keys:
+                df = df.join(other, left_keys, how)
+            else:
+                renamed = other
+                for lk, rk in pairs:
+                    if lk != rk:
+                        renamed = renamed.withColumnRenamed(rk, lk)
+                df = df.join(renamed, left_keys, how)
+        else:
+            raise SqlError("JOIN needs ON <equalities> or USING (<columns>)")
     if p.kw("where"):
         df = df.filter(p.expr())
     keys: List[str] = []

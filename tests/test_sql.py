@@ -207,9 +207,14 @@ def test_sql_front_end_views_tables_and_expressions(spark_session, tmp_path):
     assert ("xxx", "db", False) in spark.catalog.listTables("db") and "db" in spark.catalog.listDatabases()
     spark.sql("drop table if exists db.xxx")
     assert not spark.catalog.tableExists("db.xxx")
+    # equi-joins in SQL text
+    spark.createDataFrame([(0, "zero"), (1, "one"), (7, "seven")], ["kk", "name"]).createOrReplaceTempView("names")
+    j = spark.sql("select id, name from t left join names n on t.k = n.kk where id < 3 order by id").collect()
+    assert [(r.id, r.name) for r in j] == [(0, "zero"), (1, "one"), (2, None)]
+    assert spark.sql("select count(*) as n from t join names on names.kk = t.k").collect()[0].n == 20
     import pytest as _pytest
     with _pytest.raises(ValueError):
-        spark.sql("select * from t join u on t.id = u.id")
+        spark.sql("select * from t where id in (select id from t)")
 
 
 def test_map_in_pandas_accepts_ddl_schema(spark_session):
