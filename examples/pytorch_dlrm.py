@@ -69,6 +69,40 @@ def preprocess(df, vocab: int):
     return df.withColumn(LABEL, col(LABEL).cast("float"))
 
 
+def preprocess_with_dictionaries(df, min_count: int = 2):
+    """The notebook's Criteo recipe (cells 6-7) on this DataFrame API: count every (column, value)
+    pair with ``posexplode(array(...))`` + ``groupBy``, rank values per column by frequency with a
+    ``row_number`` window (rare values below ``min_count`` fall out and become id 0 after ``fillna``),
+    join the dictionaries back column by column, log-transform the integer features and put the rows
+    in a random order with a partition-local sort.  Returns ``(frame, table sizes)``."""
+    from raydp.sql import Window
+    from raydp.sql.functions import array, desc, posexplode, rand, row_number
+    from raydp.sql.functions import count as count_rows
+
+    pairs = (df.select(posexplode(array(*SPARSE)))
+             .withColumnRenamed("pos", "column_id").withColumnRenamed("col", "value")
+             .filter(col("value").isNotNull())
+             .groupBy("column_id", "value").count()
+             .filter(col("count") >= min_count))
+    by_frequency = Window.partitionBy("column_id").orderBy(desc("count"))
+    ranked = pairs.withColumn("id", row_number().over(by_frequency)).drop("count").cache()   # ids start at 1
+    sizes = []
+    for j, name in enumerate(SPARSE):
+        dictionary = ranked.filter(col("column_id") == j).drop("column_id").withColumnRenamed("value", name)
+        sizes.append(dictionary.agg(count_rows("*").alias("n")).collect()[0].n + 1)     # + the "rare" id 0
+        df = df.join(dictionary, name, how="left").drop(name).withColumnRenamed("id", name)
+    df = df.fillna(0, SPARSE + DENSE)
+    for name in DENSE:
+        df = df.withColumn(name, log(col(name) + 3.0).cast("float"))
+    for name in SPARSE:
+        df = df.withColumn(name, col(name).cast("long"))
+    df = df.withColumn(LABEL, col(LABEL).cast("float"))
+    ordinal = "__ordinal"
+    df = df.withColumn(ordinal, (rand(7) * float(1 << 52)).cast("long"))
+    df = df.repartition(4, ordinal).sortWithinPartitions(ordinal).drop(ordinal)
+    return df.select(LABEL, *DENSE, *SPARSE), sizes
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=20000)
@@ -78,15 +112,22 @@ def main() -> None:
     ap.add_argument("--batch-size", type=int, default=128)
     ap.add_argument("--lr", type=float, default=0.01)
     ap.add_argument("--gpu", action="store_true")
+    ap.add_argument("--dictionary", action="store_true",
+                    help="frequency-ranked dictionary encoding (the notebook's recipe) instead of hashing")
     args = ap.parse_args()
 
     ray.init(address="local", num_cpus=4 + args.workers)
     spark = raydp.init_spark("DLRM on Criteo-shaped data", num_executors=2, executor_cores=1,
                              executor_memory="1G")
-    frame = preprocess(synthetic_criteo(spark, args.rows, partitions=4), args.vocab)
+    raw = synthetic_criteo(spark, args.rows, partitions=4)
+    if args.dictionary:
+        frame, table_sizes = preprocess_with_dictionaries(raw)
+        print("table sizes:", table_sizes)
+    else:
+        frame, table_sizes = preprocess(raw, args.vocab), [args.vocab] * 26
     train_df, test_df = random_split(frame, [0.9, 0.1], 0)
 
-    model = DLRM(num_dense=13, table_sizes=[args.vocab] * 26, embedding_dim=32,
+    model = DLRM(num_dense=13, table_sizes=table_sizes, embedding_dim=32,
                  sparse_grad=False)               # dense grads: DDP over NCCL cannot reduce sparse ones
     estimator = TorchEstimator(num_workers=args.workers, model=model,
                                optimizer=torch.optim.SGD(model.parameters(), lr=args.lr),

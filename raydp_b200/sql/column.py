@@ -346,10 +346,26 @@ def _call(fn: str, args: list, n: int, ctx: EvalContext):
             acc ^= acc >> np.uint64(29)
         return pa.array((acc & np.uint64(0x7FFFFFFF)).astype(np.int32))
     if fn == "array":
-        cols = [_np(_full(a, n)) for a in args]
-        stacked = np.stack(cols, axis=1)
-        return pa.FixedSizeListArray.from_arrays(pa.array(stacked.reshape(-1)), len(cols)).cast(
-            pa.list_(pa.from_numpy_dtype(stacked.dtype)))
+        # element j of row i = args[j][i]; done in Arrow so strings and nulls survive (numpy stacking
+        # would turn them into objects)
+        parts = []
+        for a in args:
+            v = _full(a, n)
+            v = v.combine_chunks() if isinstance(v, pa.ChunkedArray) else (
+                v if isinstance(v, pa.Array) else pa.array(v))
+            parts.append(v)
+        common = parts[0].type
+        for v in parts[1:]:
+            if v.type != common:
+                common = pa.float64() if (pa.types.is_floating(common) or pa.types.is_floating(v.type)) else (
+                    pa.int64() if pa.types.is_integer(common) and pa.types.is_integer(v.type) else pa.string())
+        parts = [v.cast(common) for v in parts]
+        k = len(parts)
+        flat = pa.concat_arrays(parts)                                   # column-major: [col0 | col1 | ...]
+        order = (np.arange(n, dtype=np.int64)[:, None] + np.arange(k, dtype=np.int64)[None, :] * n).reshape(-1)
+        values = flat.take(pa.array(order))                              # row-major
+        offsets = pa.array(np.arange(0, (n + 1) * k, k, dtype=np.int32))
+        return pa.ListArray.from_arrays(offsets, values)
     raise NotImplementedError(f"SQL function {fn!r} is not supported by the built-in engine")
 
 

@@ -304,8 +304,11 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
         parent = pc.list_parent_indices(arr)
         offsets = np.asarray(arr.offsets)
         pos = np.arange(len(flat), dtype=np.int64) - offsets[:-1][np.asarray(parent)]
+        pos_col = pa.array(pos.astype(np.int32))
+        if not keep:                       # select(posexplode(...)) alone: a zero-column table has no length
+            return pa.table({"pos": pos_col, "col": flat})
         base = table.select(keep).take(parent)
-        return base.append_column("pos", pa.array(pos.astype(np.int32))).append_column("col", flat)
+        return base.append_column("pos", pos_col).append_column("col", flat)
     raise NotImplementedError(f"operator {kind!r}")
 
 

@@ -258,3 +258,21 @@ def test_join_variants(spark_session):
     import pytest as _pytest
     with _pytest.raises(NotImplementedError):
         a.join(b, a.k > b.k)
+
+
+def test_frequency_dictionary_recipe(spark_session):
+    """The DLRM notebook's categorical encoding (cells 6-7): posexplode(array(string columns)) alone in a
+    select, groupBy/count, row_number window by descending count, join back, fillna."""
+    df = spark_session.createDataFrame(
+        [("a", "x"), ("a", "y"), ("b", "x"), ("a", None), ("c", "x")], ["c0", "c1"])
+    pairs = (df.select(F.posexplode(F.array("c0", "c1")))
+             .withColumnRenamed("pos", "column_id").withColumnRenamed("col", "value")
+             .filter(col("value").isNotNull()).groupBy("column_id", "value").count())
+    counts = {(r.column_id, r.value): r["count"] for r in pairs.collect()}
+    assert counts == {(0, "a"): 3, (0, "b"): 1, (0, "c"): 1, (1, "x"): 3, (1, "y"): 1}
+    ranked = pairs.withColumn("id", F.row_number().over(Window.partitionBy("column_id").orderBy(F.desc("count"))))
+    top = {(r.column_id, r.value): r.id for r in ranked.collect()}
+    assert top[(0, "a")] == 1 and top[(1, "x")] == 1 and top[(1, "y")] == 2
+    d0 = ranked.filter(col("column_id") == 0).select("value", "id").withColumnRenamed("value", "c0")
+    enc = df.join(d0.filter(col("id") <= 1), "c0", "left").drop("c0").withColumnRenamed("id", "c0").fillna(0, ["c0"])
+    assert sorted(r.c0 for r in enc.collect()) == [0, 0, 1, 1, 1]
