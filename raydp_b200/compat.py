@@ -57,6 +57,11 @@ def _absent(name: str) -> bool:
         return True
 
 
+def _global_gc() -> None:
+    import gc
+    gc.collect()
+
+
 def _ray_tree() -> Dict[str, types.ModuleType]:
     from raydp_b200 import data, runtime, train
     from raydp_b200.runtime import cluster_utils, protocol
@@ -94,6 +99,11 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
         "ray.util.state": _module("ray.util.state", "", list_actors=runtime.list_actors),
         "ray.util.client": _module("ray.util.client", "", ray=_Client),
         "ray.cluster_utils": _module("ray.cluster_utils", "", Cluster=cluster_utils.Cluster),
+        # a few private hooks that test code written against Ray pokes at
+        "ray._private": _module("ray._private", ""),
+        "ray._private.client_mode_hook": _module("ray._private.client_mode_hook", "",
+                                                 client_mode_wrap=lambda fn: fn),
+        "ray._private.internal_api": _module("ray._private.internal_api", "", global_gc=_global_gc),
         "ray.data": data,
         "ray.train": _module("ray.train", "", ScalingConfig=config.ScalingConfig, RunConfig=config.RunConfig,
                              FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig,

@@ -65,7 +65,9 @@ def init(address: Optional[str] = None, num_cpus: Optional[int] = None,
     global _head, _client, _info
     with _state_lock:
         if _client is not None:
-            if ignore_reinit_error or address == "auto":
+            # "connecting" to the runtime this process already hosts (``Cluster(...)`` followed by
+            # ``init(address=cluster.address)``) is a no-op
+            if ignore_reinit_error or address == "auto" or (address and address == _info.get("address")):
                 return _info
             raise RuntimeError("Maybe you called runtime.init twice by accident? "
                                "pass ignore_reinit_error=True to allow it")
@@ -314,7 +316,7 @@ class _ActorMethod:
 
 class ActorHandle:
     def __init__(self, actor_id: str, class_name: str = "", create_oid: Optional[str] = None):
-        self._actor_id = actor_id
+        self._actor_id = _Id(actor_id)
         self._class_name = class_name
         self._create_oid = create_oid
 
@@ -409,8 +411,27 @@ def exit_actor() -> None:
     raise _ActorExit()
 
 
-def list_actors(filters: Optional[List[Tuple[str, str, Any]]] = None) -> List[dict]:
-    return _rpc("list_actors", filters=filters)
+class _Id(str):
+    """Identifier string that also answers ``.hex()`` like the binary ids of the reference's runtime."""
+
+    def hex(self) -> str:
+        return str(self)
+
+
+class ActorState(dict):
+    """One ``list_actors`` record: a dict whose keys also read as attributes (``state.required_resources``)."""
+
+    def __getattr__(self, name: str):
+        try:
+            return self[name]
+        except KeyError as exc:
+            raise AttributeError(name) from exc
+
+
+def list_actors(filters: Optional[List[Tuple[str, str, Any]]] = None, detail: bool = False,
+                **_ignored) -> List[ActorState]:
+    filters = [(k, op, str(v) if k == "actor_id" else v) for k, op, v in (filters or [])]
+    return [ActorState(r) for r in _rpc("list_actors", filters=filters)]
 
 
 # --------------------------------------------------------------------------- cluster info

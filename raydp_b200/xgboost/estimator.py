@@ -148,7 +148,11 @@ class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
             booster.load_model(os.path.join(path, "model.json"))
             return booster
         with open(os.path.join(path, "model.pkl"), "rb") as fh:
-            return pickle.load(fh)
+            model = pickle.load(fh)
+        # code written for xgboost.Booster calls inplace_predict(ndarray); give the fallback model that name
+        if not hasattr(model, "inplace_predict"):
+            model.inplace_predict = model.predict
+        return model
 
     @property
     def results(self):
