@@ -45,7 +45,10 @@ def _register(tree: Dict[str, types.ModuleType]) -> None:
         _INSTALLED.append(name)
         parent, _, leaf = name.rpartition(".")
         if parent and parent in tree:
-            setattr(tree[parent], leaf, tree[name])
+            # ``ray.util.placement_group`` is a function AND the name of a sub-module: keep the function
+            existing = getattr(tree[parent], leaf, None)
+            if existing is None or isinstance(existing, types.ModuleType):
+                setattr(tree[parent], leaf, tree[name])
 
 
 def _absent(name: str) -> bool:

@@ -230,7 +230,9 @@ class MPIJob:
             return
         if not runtime.is_initialized():
             runtime.init()
-        self.job_id = f"{self.job_name}-{_proto.new_id()[:8]}"
+        # the job id the ranks see IS the job name (reference mpi_job.py:260,281); a restart gets a new
+        # driver port, so stale ranks of an earlier start cannot register with this one
+        self.job_id = self.job_name
         self.failed = False
         self.registered = 0
         try:
@@ -267,6 +269,12 @@ class MPIJob:
         return fr.results
 
     def get_rank_addresses(self) -> List[str]:
+        """IP address of every rank's node, by rank (reference ``mpi_job.py:340-342``)."""
+        assert self.started
+        return [addr.rsplit(":", 1)[0] for addr in self.rank_addresses]
+
+    def get_rank_endpoints(self) -> List[str]:
+        """``ip:port`` of every rank's own RPC service, by rank."""
         assert self.started
         return list(self.rank_addresses)
 

@@ -34,7 +34,9 @@ def test_mpi_context_manager_addresses_env_and_errors(ray_cluster):
 
     with create_mpi_job("ctx", 2, 1, 2, mpi_script_prepare_fn=prepare, timeout=5, mpi_type="intel_mpi") as job:
         addrs = job.get_rank_addresses()
-        assert len(addrs) == 2 and all(":" in a for a in addrs) and addrs[0] != addrs[1]
+        assert addrs == [rt.get_node_ip_address()] * 2                  # node IPs, like the reference
+        ends = job.get_rank_endpoints()
+        assert len(ends) == 2 and all(":" in a for a in ends) and ends[0] != ends[1]
 
         def read_env(ctx):
             import os
