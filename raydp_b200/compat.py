@@ -60,6 +60,17 @@ def _absent(name: str) -> bool:
         return True
 
 
+class JobConfig:
+    """Stand-in for ``ray.job_config.JobConfig``: settings are recorded, ``code_search_path`` entries are
+    put on ``sys.path`` (workers inherit the driver's path)."""
+
+    def __init__(self, **settings):
+        self.settings = settings
+        for path in settings.get("code_search_path") or []:
+            if path not in sys.path:
+                sys.path.append(path)
+
+
 def _global_gc() -> None:
     import gc
     gc.collect()
@@ -95,6 +106,8 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
         "ray.util.placement_group": _module("ray.util.placement_group", "",
                                             placement_group=runtime.placement_group,
                                             remove_placement_group=runtime.remove_placement_group,
+                                            placement_group_table=runtime.placement_group_table,
+                                            get_placement_group=runtime.get_placement_group,
                                             PlacementGroup=runtime.PlacementGroup),
         "ray.util.scheduling_strategies": _module(
             "ray.util.scheduling_strategies", "",
@@ -103,6 +116,7 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
         "ray.util.client": _module("ray.util.client", "", ray=_Client),
         "ray.cluster_utils": _module("ray.cluster_utils", "", Cluster=cluster_utils.Cluster),
         # a few private hooks that test code written against Ray pokes at
+        "ray.job_config": _module("ray.job_config", "", JobConfig=JobConfig),
         "ray._private": _module("ray._private", ""),
         "ray._private.client_mode_hook": _module("ray._private.client_mode_hook", "",
                                                  client_mode_wrap=lambda fn: fn),

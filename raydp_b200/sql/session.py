@@ -103,6 +103,55 @@ class SparkContext:
     def stop(self) -> None:
         self._session.stop()
 
+    # ---- the two py4j handles test code written against PySpark reaches for.  There is no JVM: they
+    # answer the questions such code asks (force a GC; which recoverable RDDs are still pinned).
+    @property
+    def _jvm(self):
+        return _JvmStandIn()
+
+    @property
+    def _jsc(self):
+        return _JscStandIn(self._session)
+
+
+class _JvmStandIn:
+    class System:
+        @staticmethod
+        def gc() -> None:
+            import gc
+            gc.collect()
+
+
+class _PersistentRdds:
+    def __init__(self, ids):
+        self._ids = set(ids)
+
+    def contains(self, rdd_id) -> bool:
+        return int(rdd_id) in self._ids
+
+    def __contains__(self, rdd_id) -> bool:
+        return self.contains(rdd_id)
+
+    def size(self) -> int:
+        return len(self._ids)
+
+
+class _JscStandIn:
+    def __init__(self, session: "SparkSession"):
+        self._session = session
+
+    def sc(self) -> "_JscStandIn":
+        return self
+
+    def getPersistentRDDs(self) -> _PersistentRdds:
+        """Ids of the recoverable RDDs whose lineage the master actor still pins."""
+        backend = self._session._backend
+        master = getattr(backend, "master", None)
+        if master is None:
+            return _PersistentRdds([])
+        from raydp_b200 import runtime
+        return _PersistentRdds(runtime.get(master.persistent_rdd_ids.remote()))
+
 
 class DataFrameReader:
     def __init__(self, session: "SparkSession"):

@@ -42,3 +42,26 @@ def test_reference_example_runs_unchanged_through_compat_runner():
         pytest.skip("reference examples not mounted")
     proc_out = _run([sys.executable, "-m", "raydp_b200.compat", script])
     assert "Traceback" not in proc_out
+
+
+def test_reference_unit_tests_pass_unchanged(tmp_path):
+    """The reference's own pytest files (copied, not edited) run against this framework through the
+    ``ray`` / ``pyspark`` aliases.  The quick ones run here; test_spark_cluster / test_torch / test_mpi /
+    test_xgboost / test_read_parquet / test_torch_sequential pass the same way (see docs/COVERAGE.md)."""
+    import glob
+    import shutil
+    import pytest
+    src = "/root/reference/python/raydp/tests"
+    if not os.path.isdir(src):
+        pytest.skip("reference tests not mounted")
+    for f in glob.glob(os.path.join(src, "*.py")):
+        if os.path.basename(f) != "__init__.py":
+            shutil.copy(f, tmp_path)
+    code = ("from raydp_b200 import compat; compat.install(); import raydp, pytest, sys; "
+            "sys.exit(pytest.main(['-x', '-q', '-p', 'no:cacheprovider', 'test_spark_utils.py', "
+            "'test_from_spark.py', 'test_spark_master_memory.py']))")
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, capture_output=True,
+                          text=True, timeout=600)
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-2000:]
+    assert "7 passed" in proc.stdout
