@@ -76,6 +76,49 @@ def _global_gc() -> None:
     gc.collect()
 
 
+class _NodeView:
+    """``ray.worker.global_worker.node``: what the reference's submit recipe reads to write ``ray.conf``
+    (reference doc/spark_on_ray.md, "spark-submit" section)."""
+
+    @staticmethod
+    def _info() -> dict:
+        from raydp_b200 import runtime
+        if not runtime.is_initialized():
+            raise RuntimeError("the runtime is not initialised: call ray.init() first")
+        return runtime._info
+
+    @property
+    def node_ip_address(self) -> str:
+        return self._info()["node_ip"]
+
+    @property
+    def address(self) -> str:
+        return self._info()["address"]
+
+    @property
+    def unique_id(self) -> str:
+        return self._info()["node_id"]
+
+    def get_session_dir_path(self) -> str:
+        return self._info()["dir"]
+
+    def get_logs_dir_path(self) -> str:
+        return self._info()["log_dir"]
+
+
+class _GlobalWorker:
+    node = _NodeView()
+
+    @property
+    def connected(self) -> bool:
+        from raydp_b200 import runtime
+        return runtime.is_initialized()
+
+    @property
+    def namespace(self):
+        return _NodeView._info().get("namespace")
+
+
 def _ray_tree() -> Dict[str, types.ModuleType]:
     from raydp_b200 import data, runtime, train
     from raydp_b200.runtime import cluster_utils, protocol
@@ -118,6 +161,8 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
         # a few private hooks that test code written against Ray pokes at
         "ray.job_config": _module("ray.job_config", "", JobConfig=JobConfig),
         "ray._private": _module("ray._private", ""),
+        "ray.worker": _module("ray.worker", "", global_worker=_GlobalWorker()),
+        "ray._private.worker": _module("ray._private.worker", "", global_worker=_GlobalWorker()),
         "ray._private.client_mode_hook": _module("ray._private.client_mode_hook", "",
                                                  client_mode_wrap=lambda fn: fn),
         "ray._private.internal_api": _module("ray._private.internal_api", "", global_gc=_global_gc),

@@ -57,11 +57,15 @@ class RuntimeConfig:
     def set(self, key: str, value) -> None:
         self._conf.set(key, value)
 
-    def get(self, key: str, default: Optional[str] = None) -> Optional[str]:
-        value = self._conf.get(key, default)
-        if value is None and default is None and not self._conf.contains(key):
+    _UNSET = object()
+
+    def get(self, key: str, default=_UNSET) -> Optional[str]:
+        """Like ``spark.conf.get``: a missing key raises unless a default (``None`` included) is given."""
+        if self._conf.contains(key):
+            return self._conf.get(key)
+        if default is RuntimeConfig._UNSET:
             raise KeyError(f"[SQL_CONF_NOT_FOUND] The SQL config \"{key}\" cannot be found.")
-        return value
+        return default
 
     def unset(self, key: str) -> None:
         self._conf._values.pop(key, None)

@@ -65,3 +65,55 @@ def test_reference_unit_tests_pass_unchanged(tmp_path):
                           text=True, timeout=600)
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-2000:]
     assert "7 passed" in proc.stdout
+
+
+_DOC_SNIPPETS = '''
+import json
+import ray
+import raydp
+ray.init(num_cpus=4, resources={"spark_master": 1, "spark_executor": 2})
+# doc/spark_on_ray.md, spark-submit recipe: the node facts that go into ray.conf
+node = ray.worker.global_worker.node
+options = {"ray": {"run-mode": "CLUSTER", "node-ip": node.node_ip_address, "address": node.address,
+                   "session-dir": node.get_session_dir_path()}}
+json.dumps(options)
+# doc/spark_on_ray.md: actor resources for master and executors, oversubscription, shuffle service, hive
+spark = raydp.init_spark(app_name="RayDP Oversubscribe Example", num_executors=1, executor_cores=3,
+                         executor_memory=1 * 1024 * 1024 * 1024,
+                         configs={"spark.ray.raydp_spark_executor.actor.resource.cpu": 1,
+                                  "spark.ray.raydp_spark_master.actor.resource.CPU": 0,
+                                  "spark.ray.raydp_spark_master.actor.resource.spark_master": 1,
+                                  "spark.ray.raydp_spark_executor.actor.resource.spark_executor": 1,
+                                  "spark.shuffle.service.enabled": "true",
+                                  "raydp.executor.extraClassPath": "/your/extra/jar/path:/another/path"},
+                         enable_hive=True)
+free = ray.available_resources()
+assert free["CPU"] == 3.0 and free["spark_executor"] == 1.0 and "spark_master" not in free, free
+assert spark.conf.get("spark.sql.warehouse.dir", None) is None
+spark.sql("create database if not exists db")
+spark.range(10).write.saveAsTable("db.xxx")
+assert spark.sql("select * from db.xxx").count() == 10
+# README.md: word count, Spark <-> dataset conversion, recoverable conversion
+df = spark.createDataFrame([("look",), ("spark",), ("tutorial",), ("spark",), ("look",), ("python",)], ["word"])
+counts = {r["word"]: r["count"] for r in df.groupBy("word").count().collect()}
+assert counts == {"look": 2, "spark": 2, "tutorial": 1, "python": 1}, counts
+ds1 = ray.data.from_spark(spark.range(0, 1000))
+ds2 = ray.data.from_items([{"id": i} for i in range(1000)])
+assert ds1.count() == 1000 and ds2.to_spark(spark).count() == 1000
+assert raydp.spark.from_spark_recoverable(spark.range(100000)).count() == 100000
+raydp.stop_spark()
+ray.shutdown()
+print("doc snippets OK")
+'''
+
+
+def test_reference_doc_snippets_run_through_compat(tmp_path):
+    """The code blocks of the reference's README.md and doc/spark_on_ray.md (custom actor resources,
+    oversubscription, shuffle service, hive tables, ``ray.worker.global_worker.node`` for ray.conf)."""
+    script = tmp_path / "snippets.py"
+    script.write_text(_DOC_SNIPPETS)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.run([sys.executable, "-m", "raydp_b200.compat", str(script)], cwd=str(tmp_path), env=env,
+                          capture_output=True, text=True, timeout=420)
+    assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
+    assert "doc snippets OK" in proc.stdout
