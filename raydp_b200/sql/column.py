@@ -49,8 +49,9 @@ class Column:
         self._name = name
 
     # ------------------------------------------------------------------ naming
-    def alias(self, name: str) -> "Column":
-        return Column(self._kind, self._args, name)
+    def alias(self, *names: str, **_metadata) -> "Column":
+        # generators (posexplode, map explode) take one alias per produced column
+        return Column(self._kind, self._args, names[0] if len(names) == 1 else tuple(names))
 
     name = alias
 
@@ -126,6 +127,80 @@ class Column:
     def asc(self) -> "Column":
         return Column("sort", (self, "ascending"))
 
+    # Arrow sorts nulls last in either direction; the placement is kept as a third field for the sorters
+    def asc_nulls_first(self) -> "Column":
+        return Column("sort", (self, "ascending", "at_start"))
+
+    def asc_nulls_last(self) -> "Column":
+        return Column("sort", (self, "ascending", "at_end"))
+
+    def desc_nulls_first(self) -> "Column":
+        return Column("sort", (self, "descending", "at_start"))
+
+    def desc_nulls_last(self) -> "Column":
+        return Column("sort", (self, "descending", "at_end"))
+
+    def _fn(self, fn: str, *params) -> "Column":
+        return Column("call", (fn, (self,) + tuple(params)))
+
+    def bitwiseAND(self, other) -> "Column":
+        return self._fn("bitwise_and", as_column_or_lit(other))
+
+    def bitwiseOR(self, other) -> "Column":
+        return self._fn("bitwise_or", as_column_or_lit(other))
+
+    def bitwiseXOR(self, other) -> "Column":
+        return self._fn("bitwise_xor", as_column_or_lit(other))
+
+    def contains(self, other) -> "Column":
+        return self._fn("contains", as_column_or_lit(other))
+
+    def startswith(self, other) -> "Column":
+        return self._fn("startswith", as_column_or_lit(other))
+
+    def endswith(self, other) -> "Column":
+        return self._fn("endswith", as_column_or_lit(other))
+
+    def like(self, pattern: str) -> "Column":
+        return self._fn("like", pattern)
+
+    def ilike(self, pattern: str) -> "Column":
+        return self._fn("ilike", pattern)
+
+    def rlike(self, pattern: str) -> "Column":
+        return self._fn("rlike", pattern)
+
+    def substr(self, startPos, length) -> "Column":
+        return self._fn("substring", startPos, length)
+
+    def eqNullSafe(self, other) -> "Column":
+        return self._fn("eq_null_safe", as_column_or_lit(other))
+
+    def getItem(self, key) -> "Column":
+        return Column("call", ("get_item", (self, as_column_or_lit(key))), name=f"{self._output_name()}[{key}]")
+
+    def getField(self, name: str) -> "Column":
+        return Column("call", ("get_field", (self, name)), name=f"{self._output_name()}.{name}")
+
+    def __getitem__(self, key) -> "Column":
+        if isinstance(key, slice):
+            return self.substr(key.start, key.stop)
+        return self.getItem(key)
+
+    def __iter__(self):
+        raise TypeError("Column is not iterable")
+
+    def withField(self, fieldName: str, col: "Column") -> "Column":
+        return Column("call", ("with_field", (self, fieldName, col)))
+
+    def dropFields(self, *fieldNames: str) -> "Column":
+        return Column("call", ("drop_fields", (self, tuple(fieldNames))))
+
+    def __rmod__(self, o): return self._bin("%", o, True)
+    def __rpow__(self, o): return self._bin("**", o, True)
+    def __rand__(self, o): return self._bin("&", o, True)
+    def __ror__(self, o): return self._bin("|", o, True)
+
     def over(self, window) -> "Column":
         return Column("window", (self, window), self._name)
 
@@ -162,8 +237,7 @@ class Column:
         if k == "binop":
             return _binop(a[0], a[1].evaluate(table, ctx), a[2].evaluate(table, ctx))
         if k == "cast":
-            value = a[0].evaluate(table, ctx)
-            return pc.cast(value, a[1].arrow, safe=False)
+            return _cast(a[0].evaluate(table, ctx), a[1].arrow, n)
         if k == "isin":
             return pc.is_in(a[0].evaluate(table, ctx), value_set=pa.array(list(a[1])))
         if k == "call":
@@ -184,6 +258,11 @@ class Column:
             return pa.array(np.asarray(func(*nps)), type=rtype.arrow)
         if k == "sort":
             return a[0].evaluate(table, ctx)
+        if k == "hof":
+            from raydp_b200.sql.fnlib import eval_higher_order
+            name, array_cols, body, variables, extra = a
+            return eval_higher_order(name, [c.evaluate(table, ctx) for c in array_cols], body, list(variables),
+                                     dict(extra), table, ctx)
         if k == "when":
             branches, otherwise = a
             result = otherwise.evaluate(table, ctx) if otherwise is not None else pa.scalar(None)
@@ -206,6 +285,41 @@ class Column:
     def otherwise(self, value) -> "Column":
         value = value if isinstance(value, Column) else Column("lit", (value,))
         return Column("when", (self._args[0], value))
+
+
+def _cast(value, target: pa.DataType, n: int):
+    """Spark SQL cast rules where they differ from Arrow's: timestamps convert to and from numbers as
+    SECONDS since the epoch, strings become dates / timestamps leniently, booleans print lower-case."""
+    src = value.type
+    if pa.types.is_timestamp(src) and (pa.types.is_integer(target) or pa.types.is_floating(target)):
+        micros = pc.cast(pc.cast(value, pa.timestamp("us")), pa.int64())
+        if pa.types.is_integer(target):
+            secs = pc.floor(pc.divide(pc.cast(micros, pa.float64()), 1e6))
+            return pc.cast(secs, target, safe=False)
+        return pc.cast(pc.divide(pc.cast(micros, pa.float64()), 1e6), target)
+    if pa.types.is_timestamp(target) and (pa.types.is_integer(src) or pa.types.is_floating(src)):
+        micros = pc.cast(pc.multiply(pc.cast(value, pa.float64()), 1e6), pa.int64(), safe=False)
+        return pc.cast(micros, target)
+    if (pa.types.is_string(src) or pa.types.is_large_string(src)) and \
+            (pa.types.is_timestamp(target) or pa.types.is_date(target)):
+        from raydp_b200.sql.fnlib import _as_date, _as_ts
+        arr = _full(value, n)
+        return _as_date(arr, n, None) if pa.types.is_date(target) else pc.cast(_as_ts(arr, n, EvalContext()), target)
+    if pa.types.is_string(target) and pa.types.is_timestamp(src):
+        from raydp_b200.sql.fnlib import _strftime
+        return _strftime(_full(value, n), "%Y-%m-%d %H:%M:%S")
+    if (pa.types.is_string(src) or pa.types.is_large_string(src)) and \
+            (pa.types.is_integer(target) or pa.types.is_floating(target)):
+        # unparsable text becomes null instead of failing the query
+        arr = _full(value, n)
+        arr = arr.combine_chunks() if isinstance(arr, pa.ChunkedArray) else arr
+        trimmed = pc.utf8_trim_whitespace(arr)
+        numeric = pc.match_substring_regex(trimmed, r"^[+-]?(\d+\.?\d*([eE][+-]?\d+)?|\.\d+([eE][+-]?\d+)?|NaN|Infinity|-Infinity)$")
+        cleaned = pc.if_else(pc.fill_null(numeric, False), trimmed, pa.nulls(len(arr), pa.string()))
+        as_float = pc.cast(cleaned, pa.float64())
+        return pc.cast(pc.trunc(as_float), target, safe=False) if pa.types.is_integer(target) else \
+            pc.cast(as_float, target)
+    return pc.cast(value, target, safe=False)
 
 
 def _full(value, n: int):
@@ -269,7 +383,12 @@ def parse_timestamp_strings(value):
     cleaned = pc.replace_substring_regex(value, r"\s*(UTC|Z)$", "")
     cleaned = pc.replace_substring_regex(cleaned, r"T", " ")
     cleaned = pc.replace_substring_regex(cleaned, r"\.\d+$", "")
-    return pc.strptime(cleaned, format="%Y-%m-%d %H:%M:%S", unit="us", error_is_null=True)
+    full = pc.strptime(cleaned, format="%Y-%m-%d %H:%M:%S", unit="us", error_is_null=True)
+    if full.null_count == 0:
+        return full
+    day = pc.strptime(pc.utf8_trim_whitespace(cleaned), format="%Y-%m-%d", unit="us", error_is_null=True)
+    minute = pc.strptime(cleaned, format="%Y-%m-%d %H:%M", unit="us", error_is_null=True)
+    return pc.coalesce(full, day, minute)
 
 
 def _call(fn: str, args: list, n: int, ctx: EvalContext):
@@ -291,7 +410,8 @@ def _call(fn: str, args: list, n: int, ctx: EvalContext):
     if fn in ("log1p", "exp", "sqrt", "floor", "ceil", "sin", "cos", "log2", "log10"):
         return getattr(pc, fn)(pc.cast(x, pa.float64()))
     if fn == "round":
-        return pc.round(x, ndigits=args[1] if len(args) > 1 else 0)
+        # Spark rounds HALF_UP (2.5 -> 3, -2.5 -> -3); bround() is the half-even one
+        return pc.round(x, ndigits=args[1] if len(args) > 1 else 0, round_mode="half_towards_infinity")
     if fn == "pow":
         return pc.power(pc.cast(x, pa.float64()), args[1])
     if fn == "rand":
@@ -366,6 +486,10 @@ def _call(fn: str, args: list, n: int, ctx: EvalContext):
         values = flat.take(pa.array(order))                              # row-major
         offsets = pa.array(np.arange(0, (n + 1) * k, k, dtype=np.int32))
         return pa.ListArray.from_arrays(offsets, values)
+    from raydp_b200.sql.fnlib import SCALAR
+    impl = SCALAR.get(fn)
+    if impl is not None:
+        return impl(args, n, ctx)
     raise NotImplementedError(f"SQL function {fn!r} is not supported by the built-in engine")
 
 
@@ -374,6 +498,11 @@ def hash_str(s) -> int:
     for ch in str(s).encode():
         h = ((h ^ ch) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
     return h
+
+
+def as_column_or_lit(value) -> Column:
+    """A Column stays; anything else (strings included) becomes a literal."""
+    return value if isinstance(value, Column) else Column("lit", (value,))
 
 
 def as_column(value) -> Column:

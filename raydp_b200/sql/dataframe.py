@@ -18,6 +18,7 @@ import pyarrow.compute as pc
 
 from raydp_b200.sql import types as T
 from raydp_b200.sql.column import Column, as_column
+from raydp_b200.sql.dataframe_ext import DataFrameExtras
 from raydp_b200.sql.plan import LocalSource, Plan, RefSource
 
 
@@ -36,7 +37,7 @@ for _n in ("MEMORY_ONLY", "MEMORY_AND_DISK", "DISK_ONLY", "MEMORY_ONLY_2", "MEMO
     setattr(StorageLevel, _n, StorageLevel(_n))
 
 
-class DataFrame:
+class DataFrame(DataFrameExtras):
     def __init__(self, session, plan: Plan):
         self._session = session
         self._plan = plan
@@ -125,10 +126,16 @@ class DataFrame:
     def withColumn(self, name: str, col: Column) -> "DataFrame":
         if not isinstance(col, Column):
             raise TypeError("col should be Column")
-        if col._kind in ("window",):
-            return self._with_window_column(name, col)
+        from raydp_b200.sql import windowing
+        if windowing.has_window(col):
+            found: list = []
+            rewritten = windowing.extract_windows(col, "__win_", found)
+            if rewritten._kind == "col" and len(found) == 1:          # the window expression IS the column
+                return self._with_windows([(name, found[0][1])])
+            return self._with_windows(found)._derive(("with_column", name, rewritten)).drop(*[t for t, _ in found])
         if col._kind in ("posexplode", "explode"):
-            raise NotImplementedError("use select(..., posexplode(...)) for generators")
+            others = [Column("col", (c,)) for c in self.columns if c != name]
+            return self.select(*others, col.alias(name) if col._kind == "explode" else col)
         return self._derive(("with_column", name, col))
 
     def withColumns(self, cols: Dict[str, Column]) -> "DataFrame":
@@ -157,16 +164,41 @@ class DataFrame:
         if len(cols) == 1 and isinstance(cols[0], (list, tuple)):
             cols = tuple(cols[0])
         exprs = [as_column(c) for c in cols]
-        gens = [e for e in exprs if e._kind in ("posexplode", "explode")]
+        exprs = self._expand_star(exprs)
+        gens = [i for i, e in enumerate(exprs) if e._kind in ("posexplode", "explode")]
+        if len(gens) > 1:
+            raise ValueError("only one generator (explode / posexplode) is allowed per select")
+        from raydp_b200.sql import windowing
+        if any(windowing.has_window(e) for e in exprs):
+            found: list = []
+            rewritten = [windowing.extract_windows(e, "__win_", found) for e in exprs]
+            rewritten = [r.alias(e._output_name()) if r._name is None and windowing.has_window(e) else r
+                         for r, e in zip(rewritten, exprs)]
+            return self._with_windows(found).select(*rewritten)
         if gens:
-            keep = [e._args[0] for e in exprs if e._kind == "col"]
-            df = self._derive(("posexplode", gens[0]._args[0], keep))
-            if gens[0]._kind == "explode":
-                df = df.drop("pos")
-            return df
-        if any(e._kind == "agg" for e in exprs):
+            return self._derive(("generate", exprs, gens[0]))
+        if any(_contains_agg(e) for e in exprs):
             return self.agg(*exprs)
         return self._derive(("select", exprs))
+
+    def _expand_star(self, exprs: List[Column]) -> List[Column]:
+        out: List[Column] = []
+        for e in exprs:
+            if e._kind == "col" and e._args[0] == "*":
+                out.extend(Column("col", (c,)) for c in self.columns)
+            elif e._kind == "col" and e._args[0].endswith(".*"):
+                # struct expansion: select("s.*")
+                base = e._args[0][:-2]
+                field_type = self._arrow_schema().field(base).type
+                out.extend(Column("col", (base,)).getField(f.name).alias(f.name) for f in field_type)
+            else:
+                out.append(e)
+        return out
+
+    def _with_windows(self, requests) -> "DataFrame":
+        from raydp_b200.sql import windowing
+        table = windowing.evaluate_windows(self._collect_table(), list(requests))
+        return self._session._from_tables(_split_table(table, max(1, self.rdd.getNumPartitions())))
 
     def selectExpr(self, *exprs) -> "DataFrame":
         from raydp_b200.sql.sqlparser import parse_expression
@@ -202,7 +234,11 @@ class DataFrame:
         return self._derive(("dropna", list(subset) if subset else None))
 
     def sortWithinPartitions(self, *cols, ascending: Union[bool, List[bool]] = True) -> "DataFrame":
-        return self._derive(("sort_within", _sort_keys(cols, ascending)))
+        from raydp_b200.sql.windowing import sort_spec
+        if len(cols) == 1 and isinstance(cols[0], (list, tuple)):
+            cols = tuple(cols[0])
+        asc = ascending if isinstance(ascending, (list, tuple)) else [ascending] * len(cols)
+        return self._derive(("sort_within", [sort_spec(c, bool(a)) for c, a in zip(cols, asc)]))
 
     def sample(self, withReplacement=None, fraction=None, seed=None) -> "DataFrame":
         if isinstance(withReplacement, float) and fraction is None:
@@ -284,7 +320,15 @@ class DataFrame:
     def groupBy(self, *cols) -> "GroupedData":
         if len(cols) == 1 and isinstance(cols[0], (list, tuple)):
             cols = tuple(cols[0])
-        return GroupedData(self, [c if isinstance(c, str) else c._output_name() for c in cols])
+        df, keys = self, []
+        for c in cols:
+            if isinstance(c, str) or c._kind == "col":
+                keys.append(c if isinstance(c, str) else c._args[0])
+            else:                                   # groupBy(F.year("ts"), (col("a") % 2).alias("odd"))
+                name = c._output_name()
+                df = df.withColumn(name, c)
+                keys.append(name)
+        return GroupedData(df, keys)
 
     groupby = groupBy
 
@@ -328,36 +372,12 @@ class DataFrame:
     unionAll = union
 
     def orderBy(self, *cols, ascending: Union[bool, List[bool]] = True) -> "DataFrame":
-        table = self._collect_table().sort_by(_sort_keys(cols, ascending))
+        from raydp_b200.sql.windowing import sort_table
+        table = sort_table(self._collect_table(), cols, ascending)
         n = max(1, self.rdd.getNumPartitions())
         return self._session._from_tables(_split_table(table, n))
 
     sort = orderBy
-
-    def _with_window_column(self, name: str, col: Column) -> "DataFrame":
-        fn, spec = col._args
-        if fn._kind != "rank_fn" or fn._args[0] != "row_number":
-            raise NotImplementedError("only row_number() window functions are supported")
-        part_keys = [c._output_name() for c in spec._partition_by]
-        table = self._collect_table()
-        order = [(c._args[0]._output_name() if c._kind == "sort" else c._output_name(),
-                  c._args[1] if c._kind == "sort" else "ascending") for c in spec._order_by]
-        idx = pc.sort_indices(table, sort_keys=[(k, "ascending") for k in part_keys] + order)
-        sorted_t = table.take(idx)
-        n = sorted_t.num_rows
-        if part_keys and n:
-            change = np.zeros(n, dtype=bool)
-            change[0] = True
-            for k in part_keys:
-                v = sorted_t.column(k).combine_chunks()
-                neq = pc.not_equal(v.slice(1), v.slice(0, n - 1)).to_numpy(zero_copy_only=False)
-                change[1:] |= neq.astype(bool)
-            starts = np.maximum.accumulate(np.where(change, np.arange(n), 0))
-            rn = np.arange(n) - starts + 1
-        else:
-            rn = np.arange(1, n + 1)
-        sorted_t = sorted_t.append_column(name, pa.array(rn.astype(np.int32)))
-        return self._session._from_tables(_split_table(sorted_t, max(1, self.rdd.getNumPartitions())))
 
     # ------------------------------------------------------------------ persistence
     def cache(self) -> "DataFrame":
@@ -533,6 +553,18 @@ def _split_table(table: pa.Table, n: int) -> List[pa.Table]:
     return out
 
 
+def _contains_agg(e) -> bool:
+    if isinstance(e, Column):
+        if e._kind == "agg":
+            return True
+        if e._kind == "window":
+            return False
+        return any(_contains_agg(a) for a in e._args)
+    if isinstance(e, (tuple, list)):
+        return any(_contains_agg(a) for a in e)
+    return False
+
+
 class GroupedData:
     def __init__(self, df: DataFrame, keys: List[str]):
         self._df = df
@@ -559,13 +591,25 @@ class GroupedData:
         if len(exprs) == 1 and isinstance(exprs[0], dict):
             exprs = tuple(Column("agg", ({"avg": "mean"}.get(fn, fn), None if c == "*" else as_column(c)),
                                  f"{fn}({c})") for c, fn in exprs[0].items())
+        if len(exprs) == 1 and isinstance(exprs[0], (list, tuple)):
+            exprs = tuple(exprs[0])
+        # an output may be an expression OVER aggregates (sum(a) / count(b), round(avg(x), 2)): the aggregate
+        # nodes are computed first, the surrounding expression is applied to the aggregated table
+        leaves: List[Column] = []
+        outputs: List[Tuple[str, Column]] = []
+        for e in exprs:
+            if not isinstance(e, Column):
+                raise TypeError("agg() expects aggregate expressions such as count('*')")
+            rewritten = _extract_aggregates(e, leaves)
+            if not leaves:
+                raise TypeError("agg() expects aggregate expressions such as count('*')")
+            outputs.append((e._name or _agg_default_name(e), rewritten))
         df = self._df
         aggs: List[Tuple[str, Optional[str]]] = []
-        names: List[str] = []
-        for i, e in enumerate(exprs):
-            if e._kind != "agg":
-                raise TypeError("agg() expects aggregate expressions such as count('*')")
-            fn, target = e._args
+        params: List[tuple] = []
+        in_types: List[Optional[pa.DataType]] = []
+        for i, leaf in enumerate(leaves):
+            fn, target = leaf._args[0], leaf._args[1]
             if target is None:
                 col_name = None
             elif target._kind == "col":
@@ -573,23 +617,233 @@ class GroupedData:
             else:
                 col_name = f"__agg_in_{i}"
                 df = df.withColumn(col_name, target)
+            if fn == "count_distinct" and target is not None and target._kind == "call" and target._args[0] == "struct":
+                fn = "count_distinct_rows"            # structs have no hash kernel: gathered instead
             aggs.append((fn, col_name))
-            default = f"{ {'mean': 'avg'}.get(fn, fn) }({'1' if target is None else target._output_name()})"
-            names.append(e._name or default.replace(" ", ""))
-        partials = df._run("agg_partial", {"keys": self._keys, "aggs": aggs})
+            params.append(tuple(leaf._args[2:]))
+        schema = df._arrow_schema()
+        in_types = [None if c is None else schema.field(c).type for _, c in aggs]
+        names = [f"__agg_out_{i}" for i in range(len(leaves))]
+        partials = df._run("agg_partial", {"keys": self._keys, "aggs": list(dict.fromkeys(aggs))})
         merged = pa.concat_tables(partials, promote_options="default")
-        result = _final_agg(merged, self._keys, aggs, names)
-        return df._session._from_tables([result])
+        result = _final_agg(merged, self._keys, aggs, names, params, in_types)
+        out_cols = [result.column(k) for k in self._keys]
+        out_names = list(self._keys)
+        for name, expr in outputs:
+            out_cols.append(expr.evaluate_array(result))
+            out_names.append(name)
+        return df._session._from_tables([pa.table(out_cols, names=out_names)])
+
+    def pivot(self, pivot_col: str, values: Optional[Sequence[Any]] = None) -> "PivotedData":
+        return PivotedData(self, pivot_col, values)
+
+    def applyInPandas(self, func, schema) -> DataFrame:
+        """Each group as one pandas DataFrame through ``func``; ``schema`` (DDL string or StructType) types
+        the output."""
+        import pandas as pd
+        struct = T.parse_ddl(schema) if isinstance(schema, str) else schema
+        arrow_schema = pa.schema([(f.name, f.dataType.arrow) for f in struct.fields])
+        table = self._df._collect_table()
+        pdf = table.to_pandas()
+        pieces = []
+        if self._keys:
+            for _, group in pdf.groupby(self._keys, sort=True, dropna=False):
+                pieces.append(func(group.reset_index(drop=True)))
+        else:
+            pieces.append(func(pdf))
+        pieces = [p for p in pieces if p is not None and len(p)]
+        if not pieces:
+            return self._df._session._from_tables([arrow_schema.empty_table()])
+        out = pd.concat(pieces, ignore_index=True)
+        result = pa.Table.from_pandas(out[[f.name for f in struct.fields]], schema=arrow_schema, preserve_index=False)
+        return self._df._session._from_tables(_split_table(result, max(1, self._df.rdd.getNumPartitions())))
+
+    apply = applyInPandas
+
+    def cogroup(self, other: "GroupedData") -> "CoGroupedData":
+        return CoGroupedData(self, other)
 
 
-def _final_agg(merged: pa.Table, keys: List[str], aggs, names) -> pa.Table:
+class GroupingSets:
+    """``rollup`` / ``cube``: the aggregation runs once per grouping set; keys outside a set are null."""
+
+    def __init__(self, df: DataFrame, keys: List[str], sets: List[List[str]]):
+        self._df, self._keys, self._sets = df, keys, sets
+
+    def agg(self, *exprs) -> DataFrame:
+        schema = self._df._arrow_schema()
+        pieces = []
+        for subset in self._sets:
+            part = GroupedData(self._df, list(subset)).agg(*exprs)._collect_table()
+            cols, names = [], []
+            for k in self._keys:
+                names.append(k)
+                cols.append(part.column(k) if k in subset else pa.nulls(part.num_rows, schema.field(k).type))
+            for nme in part.column_names:
+                if nme not in subset:
+                    names.append(nme)
+                    cols.append(part.column(nme))
+            pieces.append(pa.table(cols, names=names))
+        return self._df._session._from_tables([pa.concat_tables(pieces, promote_options="default")])
+
+    def count(self): return self.agg(Column("agg", ("count", None), "count"))
+    def sum(self, *cols): return self.agg(*[Column("agg", ("sum", as_column(c)), f"sum({c})") for c in cols])
+    def avg(self, *cols): return self.agg(*[Column("agg", ("mean", as_column(c)), f"avg({c})") for c in cols])
+    mean = avg
+    def min(self, *cols): return self.agg(*[Column("agg", ("min", as_column(c)), f"min({c})") for c in cols])
+    def max(self, *cols): return self.agg(*[Column("agg", ("max", as_column(c)), f"max({c})") for c in cols])
+
+
+class CoGroupedData:
+    def __init__(self, left: GroupedData, right: GroupedData):
+        self._left, self._right = left, right
+
+    def applyInPandas(self, func, schema) -> DataFrame:
+        import pandas as pd
+        struct = T.parse_ddl(schema) if isinstance(schema, str) else schema
+        arrow_schema = pa.schema([(f.name, f.dataType.arrow) for f in struct.fields])
+        lp, rp = self._left._df.toPandas(), self._right._df.toPandas()
+        lg = {k: g for k, g in lp.groupby(self._left._keys, sort=True, dropna=False)}
+        rg = {k: g for k, g in rp.groupby(self._right._keys, sort=True, dropna=False)}
+        pieces = []
+        for key in sorted(set(lg) | set(rg), key=repr):
+            a = lg.get(key, lp.iloc[0:0]).reset_index(drop=True)
+            b = rg.get(key, rp.iloc[0:0]).reset_index(drop=True)
+            pieces.append(func(a, b))
+        pieces = [p for p in pieces if p is not None and len(p)]
+        session = self._left._df._session
+        if not pieces:
+            return session._from_tables([arrow_schema.empty_table()])
+        out = pd.concat(pieces, ignore_index=True)
+        return session._from_tables([pa.Table.from_pandas(out[[f.name for f in struct.fields]], schema=arrow_schema,
+                                                          preserve_index=False)])
+
+
+class PivotedData:
+    """``groupBy(keys).pivot(col[, values]).agg(...)``: one output column per pivot value (and per
+    aggregate when several are given)."""
+
+    def __init__(self, grouped: GroupedData, pivot_col: str, values):
+        self._grouped, self._pivot_col, self._values = grouped, pivot_col, values
+
+    def agg(self, *exprs) -> DataFrame:
+        g, pcol = self._grouped, self._pivot_col
+        values = self._values
+        if values is None:
+            found = g._df.select(pcol).distinct()._collect_table().column(0).to_pylist()
+            values = sorted((v for v in found if v is not None), key=lambda v: (str(type(v)), v))
+        base = GroupedData(g._df, g._keys + [pcol]).agg(*[e.alias(f"__pv_{i}") for i, e in enumerate(exprs)])
+        table = base._collect_table()
+        from raydp_b200.sql.windowing import sort_table
+        if g._keys:
+            table = sort_table(table, g._keys)
+        key_rows = list(zip(*[table.column(k).to_pylist() for k in g._keys])) if g._keys else [()] * table.num_rows
+        pivots = table.column(pcol).to_pylist()
+        groups: Dict[tuple, int] = {}
+        for kr in key_rows:
+            groups.setdefault(kr, len(groups))
+        if not g._keys:
+            groups.setdefault((), 0)
+        labels, cells, types = [], {}, {}
+        for v in values:
+            for i, e in enumerate(exprs):
+                label = str(v) if len(exprs) == 1 else f"{v}_{e._name or _agg_default_name(e)}"
+                labels.append(label)
+                cells[label] = [None] * len(groups)
+                types[label] = table.schema.field(f"__pv_{i}").type
+        measures = [table.column(f"__pv_{i}").to_pylist() for i in range(len(exprs))]
+        wanted = {_hashable(v) for v in values}
+        for row, (kr, pv) in enumerate(zip(key_rows, pivots)):
+            if _hashable(pv) not in wanted:
+                continue
+            for i, e in enumerate(exprs):
+                label = str(pv) if len(exprs) == 1 else f"{pv}_{e._name or _agg_default_name(e)}"
+                cells[label][groups[kr]] = measures[i][row]
+        ordered = list(groups)
+        cols = [pa.array([kr[j] for kr in ordered], type=table.schema.field(k).type) for j, k in enumerate(g._keys)]
+        cols += [pa.array(cells[lb], type=types[lb]) for lb in labels]
+        return g._df._session._from_tables([pa.table(cols, names=g._keys + labels)])
+
+    def count(self): return self.agg(Column("agg", ("count", None), "count"))
+    def sum(self, *cols): return self.agg(*[Column("agg", ("sum", as_column(c)), f"sum({c})") for c in cols])
+    def avg(self, *cols): return self.agg(*[Column("agg", ("mean", as_column(c)), f"avg({c})") for c in cols])
+    mean = avg
+    def min(self, *cols): return self.agg(*[Column("agg", ("min", as_column(c)), f"min({c})") for c in cols])
+    def max(self, *cols): return self.agg(*[Column("agg", ("max", as_column(c)), f"max({c})") for c in cols])
+
+
+_AGG_DISPLAY = {"mean": "avg", "count_distinct": "count", "stddev": "stddev", "variance": "variance"}
+
+
+def _agg_default_name(e: Column) -> str:
+    if e._kind == "agg":
+        fn, target = e._args[0], e._args[1]
+        inner = "1" if target is None else target._output_name()
+        if fn == "count_distinct":
+            return f"count(DISTINCT {inner})".replace("DISTINCT ", "DISTINCT ")
+        return f"{_AGG_DISPLAY.get(fn, fn)}({inner})".replace(" ", "")
+    if e._kind == "binop":
+        return f"({_agg_default_name(e._args[1])} {e._args[0]} {_agg_default_name(e._args[2])})"
+    if e._kind == "call":
+        inner = ", ".join(_agg_default_name(a) if isinstance(a, Column) else str(a) for a in e._args[1])
+        return f"{e._args[0]}({inner})"
+    return e._output_name()
+
+
+def _extract_aggregates(expr: Column, leaves: List[Column]) -> Column:
+    """Replace aggregate nodes inside ``expr`` by references to ``__agg_out_<i>`` columns."""
+    if not isinstance(expr, Column):
+        return expr
+    if expr._kind == "agg":
+        leaves.append(expr)
+        return Column("col", (f"__agg_out_{len(leaves) - 1}",))
+    if expr._kind in ("col", "lit"):
+        return expr
+
+    def walk(node):
+        if isinstance(node, Column):
+            return _extract_aggregates(node, leaves)
+        if isinstance(node, tuple):
+            return tuple(walk(x) for x in node)
+        if isinstance(node, list):
+            return [walk(x) for x in node]
+        return node
+    return Column(expr._kind, tuple(walk(a) for a in expr._args), expr._name)
+
+
+def _final_agg(merged: pa.Table, keys: List[str], aggs, names, params=None, in_types=None) -> pa.Table:
     """Second aggregation stage: merge per-partition partial states."""
+    from raydp_b200.sql.aggregates import MERGEABLE, reduce_groups
+    params = params or [()] * len(aggs)
+    in_types = in_types or [None] * len(aggs)
+
     def grouped(specs):
         if keys:
             return merged.group_by(keys, use_threads=False).aggregate(specs)
-        return pa.TableGroupBy(merged, [], use_threads=False).aggregate(specs)
+        if merged.num_rows == 0:
+            return pa.TableGroupBy(merged, [], use_threads=False).aggregate(specs)
+        keyed = merged.append_column("__all", pa.array(np.zeros(merged.num_rows, dtype=np.int8)))
+        return keyed.group_by(["__all"], use_threads=False).aggregate(specs).drop_columns(["__all"])
 
+    if not keys and merged.num_rows == 0:
+        # a global aggregate over no rows still answers with one row: counts are 0, collections empty
+        from raydp_b200.sql.aggregates import result_type
+        cols = []
+        for (fn, col), in_type in zip(aggs, in_types):
+            in_type = in_type if in_type is not None else pa.null()
+            if fn in ("count", "count_distinct", "count_distinct_rows", "approx_count_distinct", "count_if"):
+                cols.append(pa.array([0], type=pa.int64()))
+            elif fn in ("collect_list", "collect_set"):
+                cols.append(pa.array([[]], type=pa.list_(in_type)))
+            elif fn in ("sum", "min", "max", "first"):
+                cols.append(pa.nulls(1, in_type))
+            elif fn in MERGEABLE:
+                cols.append(pa.nulls(1, pa.float64()))
+            else:
+                cols.append(pa.nulls(1, result_type(fn, in_type) or pa.float64()))
+        return pa.table(cols, names=list(names))
     merge_specs = []
+    gathered: List[str] = []
     for fn, col in aggs:
         if fn == "count":
             merge_specs.append(("count_all" if col is None else f"{col}_count", "sum"))
@@ -604,11 +858,20 @@ def _final_agg(merged: pa.Table, keys: List[str], aggs, names) -> pa.Table:
         elif fn == "first":
             merge_specs.append((f"{col}_first", "first"))
         elif fn == "count_distinct":
-            merge_specs.append((f"{col}_distinct", "list"))
+            if f"{col}_distinct" not in gathered:
+                gathered.append(f"{col}_distinct")
+        elif f"{col}_list" not in gathered:
+            gathered.append(f"{col}_list")
+    if gathered:
+        merged = merged.append_column("__rowidx", pa.array(np.arange(merged.num_rows, dtype=np.int64)))
+        merge_specs.append(("__rowidx", "list"))
     uniq = list(dict.fromkeys(merge_specs))
     g = grouped(uniq)
+    if gathered:
+        from raydp_b200.sql.executor import gather_by_index
+        g = gather_by_index(g, "__rowidx_list", merged, gathered)       # -> <col>_list_list: list<list<T>>
     out_cols, out_names = [g.column(k) for k in keys], list(keys)
-    for (fn, col), name in zip(aggs, names):
+    for (fn, col), name, prm, in_type in zip(aggs, names, params, in_types):
         if fn == "count":
             src = "count_all_sum" if col is None else f"{col}_count_sum"
             out_cols.append(pc.cast(g.column(src), pa.int64()))
@@ -629,10 +892,26 @@ def _final_agg(merged: pa.Table, keys: List[str], aggs, names) -> pa.Table:
             out_cols.append(g.column(f"{col}_first_first"))
         elif fn == "count_distinct":
             lists = g.column(f"{col}_distinct_list").to_pylist()
-            out_cols.append(pa.array([len({v for sub in row for v in sub if v is not None})
+            out_cols.append(pa.array([len({_hashable(v) for sub in row for v in sub if v is not None})
                                       for row in lists], type=pa.int64()))
+        else:
+            assert fn not in MERGEABLE or fn == "count_distinct_rows"
+            nested = g.column(f"{col}_list_list").combine_chunks()      # one inner list per partition
+            inner = pc.list_flatten(nested)                             # list<T>, all partial lists in group order
+            group_offsets = inner.offsets.take(nested.offsets) if len(inner) else \
+                pa.array(np.zeros(len(nested) + 1, dtype=np.int32))
+            flat = pa.ListArray.from_arrays(group_offsets, pc.list_flatten(inner))
+            out_cols.append(reduce_groups(fn, flat, prm, flat.type.value_type))
         out_names.append(name)
     return pa.table(out_cols, names=out_names)
+
+
+def _hashable(v):
+    if isinstance(v, dict):
+        return tuple((k, _hashable(x)) for k, x in v.items())
+    if isinstance(v, list):
+        return tuple(_hashable(x) for x in v)
+    return v
 
 
 class DataFrameWriter:

@@ -25,8 +25,12 @@ EXECUTOR_NAME_PREFIX = "raydp-executor-"
 
 
 def _partial_agg(table: pa.Table, keys: List[str], aggs: List[Tuple[str, Optional[str]]]) -> pa.Table:
-    """First stage of a two-stage aggregation; emits mergeable partial states."""
+    """First stage of a two-stage aggregation; emits mergeable partial states.  Aggregates without a
+    compact state (``sql/aggregates.py``) get their group's values gathered into a ``<col>_list`` column:
+    the group-by collects ROW INDICES (a list of int64 works for every value type, structs included) and
+    the values are taken by index afterwards."""
     specs = []
+    gathered: List[str] = []
     for fn, col in aggs:
         if fn == "count":
             specs.append(([], "count_all") if col is None else (col, "count"))
@@ -44,8 +48,11 @@ def _partial_agg(table: pa.Table, keys: List[str], aggs: List[Tuple[str, Optiona
             specs.append((col, "distinct"))
         elif fn == "first":
             specs.append((col, "first"))
-        else:
-            raise NotImplementedError(f"aggregate {fn}")
+        elif col not in gathered:
+            gathered.append(col)
+    if gathered:
+        table = table.append_column("__rowidx", pa.array(np.arange(table.num_rows, dtype=np.int64)))
+        specs.append(("__rowidx", "list"))
     seen, uniq = set(), []
     for s in specs:
         k = (tuple(s[0]) if isinstance(s[0], list) else s[0], s[1])
@@ -53,8 +60,32 @@ def _partial_agg(table: pa.Table, keys: List[str], aggs: List[Tuple[str, Optiona
             seen.add(k)
             uniq.append(s)
     if keys:
-        return table.group_by(keys, use_threads=False).aggregate(uniq)
-    return pa.TableGroupBy(table, [], use_threads=False).aggregate(uniq)
+        out = table.group_by(keys, use_threads=False).aggregate(uniq)
+    elif table.num_rows == 0 and not gathered:
+        out = pa.TableGroupBy(table, [], use_threads=False).aggregate(uniq)
+    else:
+        # a global aggregate is a group-by over one constant key (the scalar path lacks list / distinct)
+        keyed = table.append_column("__all", pa.array(np.zeros(table.num_rows, dtype=np.int8)))
+        out = keyed.group_by(["__all"], use_threads=False).aggregate(uniq).drop_columns(["__all"])
+    if gathered:
+        out = gather_by_index(out, "__rowidx_list", table, gathered)
+    return out
+
+
+def gather_by_index(grouped: pa.Table, index_col: str, source: pa.Table, cols: List[str]) -> pa.Table:
+    """Replace ``index_col`` (list<int64> of row numbers of ``source``) by one ``<col>_list`` column per
+    entry of ``cols`` holding the rows' values."""
+    idx = grouped.column(index_col).combine_chunks()
+    position = grouped.column_names.index(index_col)
+    grouped = grouped.remove_column(position)
+    flat = pc.list_flatten(idx)
+    offsets = idx.offsets
+    if len(idx) and offsets[0].as_py() != 0:
+        offsets = pc.subtract(offsets, offsets[0])
+    for col in cols:
+        values = source.column(col).combine_chunks().take(flat)
+        grouped = grouped.append_column(f"{col}_list", pa.ListArray.from_arrays(offsets, values))
+    return grouped
 
 
 def execute_action(plan: Plan, idx: int, action: str, args: Dict[str, Any], blocks: Dict) -> Any:

@@ -247,7 +247,8 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
             mask = valid if mask is None else pc.and_(mask, valid)
         return table.filter(mask) if mask is not None else table
     if kind == "sort_within":
-        return table.sort_by(op[1])
+        from raydp_b200.sql.windowing import sort_indices
+        return table.take(sort_indices(table, op[1], ctx))
     if kind == "split":  # randomSplit piece: uniform draw in [lo, hi)
         _, lo, hi, seed = op
         rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index, 7])
@@ -295,20 +296,51 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
         return table.take(rows.take(pc.sort_indices(rows)))     # original order within the partition
     if kind == "cast_schema":
         return table.cast(op[1], safe=False)
-    if kind == "posexplode":
-        _, expr, keep = op
-        arr = _full(expr.evaluate(table, ctx), n)
+    if kind == "generate":
+        # select(<exprs...>, explode|posexplode[_outer](<array or map>), <exprs...>)
+        _, exprs, gi = op
+        gen = exprs[gi]
+        outer = len(gen._args) > 1 and bool(gen._args[1])
+        arr = _full(gen._args[0].evaluate(table, ctx), n)
         if isinstance(arr, pa.ChunkedArray):
             arr = arr.combine_chunks()
-        flat = pc.list_flatten(arr)
-        parent = pc.list_parent_indices(arr)
-        offsets = np.asarray(arr.offsets)
-        pos = np.arange(len(flat), dtype=np.int64) - offsets[:-1][np.asarray(parent)]
-        pos_col = pa.array(pos.astype(np.int32))
-        if not keep:                       # select(posexplode(...)) alone: a zero-column table has no length
-            return pa.table({"pos": pos_col, "col": flat})
-        base = table.select(keep).take(parent)
-        return base.append_column("pos", pos_col).append_column("col", flat)
+        is_map = pa.types.is_map(arr.type)
+        lengths = np.asarray(pc.fill_null(pc.list_value_length(arr), 0)).astype(np.int64) if not is_map else \
+            np.array([0 if v is None else len(v) for v in arr.to_pylist()], dtype=np.int64)
+        out_len = np.where(lengths == 0, 1, lengths) if outer else lengths
+        parent = np.repeat(np.arange(n, dtype=np.int64), out_len)
+        starts_out = np.concatenate([[0], np.cumsum(out_len)[:-1]]) if n else np.zeros(0, dtype=np.int64)
+        starts_in = np.concatenate([[0], np.cumsum(lengths)[:-1]]) if n else np.zeros(0, dtype=np.int64)
+        pos = np.arange(len(parent), dtype=np.int64) - starts_out[parent]
+        hollow = lengths[parent] == 0                      # rows produced only because of *_outer
+        src = pa.array(np.where(hollow, 0, starts_in[parent] + pos), mask=hollow)
+        if is_map:
+            flat_k, flat_v = arr.keys[arr.offsets[0].as_py():], arr.items[arr.offsets[0].as_py():]
+            produced = [("key", flat_k.take(src) if len(flat_k) else pa.nulls(len(parent), flat_k.type)),
+                        ("value", flat_v.take(src) if len(flat_v) else pa.nulls(len(parent), flat_v.type))]
+        else:
+            flat = pc.list_flatten(arr)
+            produced = [("col", flat.take(src) if len(flat) else pa.nulls(len(parent), flat.type))]
+        if gen._kind == "posexplode":
+            produced.insert(0, ("pos", pa.array(pos.astype(np.int32), mask=hollow)))
+        alias = gen._name
+        if alias is not None:
+            names = list(alias) if isinstance(alias, (tuple, list)) else [alias]
+            if len(names) != len(produced):
+                raise ValueError(f"the generator produces {len(produced)} columns but {len(names)} aliases were given")
+            produced = [(nm, v) for nm, (_, v) in zip(names, produced)]
+        cols, names = [], []
+        parent_idx = pa.array(parent)
+        for i, e in enumerate(exprs):
+            if i == gi:
+                for nm, v in produced:
+                    names.append(nm)
+                    cols.append(v)
+                continue
+            value = _full(e.evaluate(table, ctx), n)
+            names.append(e._output_name())
+            cols.append(value.take(parent_idx))
+        return pa.table(cols, names=names)
     raise NotImplementedError(f"operator {kind!r}")
 
 

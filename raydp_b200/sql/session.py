@@ -346,8 +346,7 @@ class SparkSession:
         elif isinstance(schema, (list, tuple)):
             names = list(schema)
         elif isinstance(schema, str):
-            fields = [p.strip().split() for p in schema.replace(":", " ").split(",")]
-            st = T.StructType([T.StructField(n, T.parse_type(t)) for n, t in fields])
+            st = T.parse_ddl(schema)
             arrow_schema, names = st.to_arrow_schema(), st.names
         if isinstance(data, RDD):
             parts = data._collect_partitions()

@@ -21,7 +21,7 @@ clauses are not parsed; use the DataFrame API for those.
 from __future__ import annotations
 
 import re
-from typing import Any, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Tuple
 
 from raydp_b200.sql import functions as F
 from raydp_b200.sql.column import Column
@@ -309,6 +309,40 @@ def _is_aggregate(col: Column) -> bool:
     return False
 
 
+def _signature(node) -> str:
+    """Structural fingerprint of an expression (``Column.__eq__`` builds an expression, it does not compare)."""
+    if isinstance(node, Column):
+        return f"{node._kind}({', '.join(_signature(a) for a in node._args)})"
+    if isinstance(node, (tuple, list)):
+        return "[" + ", ".join(_signature(a) for a in node) + "]"
+    return repr(node)
+
+
+def _replace_aggregates(expr: Column, registry: Dict[str, str], hidden: List[Column]) -> Column:
+    """Aggregates inside HAVING / ORDER BY become references to aggregate output columns; an aggregate the
+    SELECT list does not compute is added as a hidden output."""
+    if not isinstance(expr, Column):
+        return expr
+    if expr._kind == "agg":
+        sig = _signature(expr)
+        if sig not in registry:
+            registry[sig] = f"__hidden_agg_{len(hidden)}"
+            hidden.append(expr.alias(registry[sig]))
+        return F.col(registry[sig])
+    if expr._kind in ("col", "lit"):
+        return expr
+
+    def walk(node):
+        if isinstance(node, Column):
+            return _replace_aggregates(node, registry, hidden)
+        if isinstance(node, tuple):
+            return tuple(walk(x) for x in node)
+        if isinstance(node, list):
+            return [walk(x) for x in node]
+        return node
+    return Column(expr._kind, tuple(walk(a) for a in expr._args), expr._name)
+
+
 def parse_expression(text: str) -> Column:
     """One SQL expression (optionally ``... AS alias``) -> :class:`Column`."""
     p = _Parser(tokenize(text))
@@ -498,11 +532,12 @@ def _parse_select(p: _Parser, session):
             raise SqlError("JOIN needs ON <equalities> or USING (<columns>)")
     if p.kw("where"):
         df = df.filter(p.expr())
-    keys: List[str] = []
+    key_exprs: List[Column] = []
     if p.kw("group", "by"):
-        keys.append(p.expr()._output_name())
+        key_exprs.append(p.expr())
         while p.op(","):
-            keys.append(p.expr()._output_name())
+            key_exprs.append(p.expr())
+    keys: List[str] = [e._output_name() for e in key_exprs]
     having = p.expr() if p.kw("having") else None
     order: List[Tuple[Column, bool]] = []
     if p.kw("order", "by"):
@@ -523,26 +558,50 @@ def _parse_select(p: _Parser, session):
     cols = [c for c in items if not isinstance(c, str)]
     grouped = bool(keys) or any(_is_aggregate(c) for c in cols)
     if grouped:
-        aggs = [c for c in cols if _is_aggregate(c)]
-        for c in aggs:
-            if c._kind != "agg":
-                raise SqlError("aggregates inside larger expressions are not supported; "
-                               "select the aggregate with an alias and compute on the result")
-        plain = [c._output_name() for c in cols if not _is_aggregate(c)]
-        missing = [n for n in plain if n not in keys]
-        if missing:
-            raise SqlError(f"columns {missing} must appear in GROUP BY")
-        out = df.groupBy(*keys).agg(*aggs) if aggs else df.select(*keys).distinct()
+        from raydp_b200.sql.dataframe import _agg_default_name
+        # GROUP BY 1, 2 (ordinals) and GROUP BY <select alias>
+        for i, e in enumerate(key_exprs):
+            if e._kind == "lit" and isinstance(e._args[0], int) and 1 <= e._args[0] <= len(cols):
+                key_exprs[i] = cols[e._args[0] - 1]
+            elif e._kind == "col" and e._args[0] not in df.columns:
+                match = [c for c in cols if c._name == e._args[0]]
+                if match:
+                    key_exprs[i] = match[0]
+        keys = [e._output_name() for e in key_exprs]
+        agg_items: List[Column] = []
+        registry: Dict[str, str] = {}
+        post: List[Column] = []
+        for c in cols:
+            if _is_aggregate(c):
+                name = c._name or _agg_default_name(c)
+                agg_items.append(c.alias(name))
+                if c._kind == "agg":
+                    registry[_signature(c)] = name
+                post.append(F.col(name))
+            elif c._output_name() in keys:
+                post.append(F.col(c._output_name()))
+            else:
+                post.append(c)                      # an expression over the grouping keys: applied afterwards
+        hidden: List[Column] = []
+        if having is not None:
+            having = _replace_aggregates(having, registry, hidden)
+        order = [(_replace_aggregates(e, registry, hidden), a) for e, a in order]
+        if agg_items or hidden:
+            out = df.groupBy(*key_exprs).agg(*(agg_items + hidden))
+        else:
+            out = df.groupBy(*key_exprs).agg(F.count("*").alias("__n")).drop("__n")
         if having is not None:
             out = out.filter(having)
-        names = [c._output_name() if not _is_aggregate(c) else None for c in cols]
-        agg_names = [n for n in out.columns if n not in keys]
-        final = []
-        it = iter(agg_names)
-        for n in names:
-            final.append(n if n is not None else next(it))
-        if final and final != out.columns:
-            out = out.select(*final)
+        out_names = [c._output_name() for c in post]
+        if order and not all(e._kind == "col" and e._output_name() in out_names for e, _ in order):
+            key_names = [f"__ok{i}" for i in range(len(order))]
+            for n, (e, _) in zip(key_names, order):
+                alias_hit = [c for c in post if c._name == e._output_name()] if e._kind == "col" and \
+                    e._args[0] not in out.columns else []
+                out = out.withColumn(n, alias_hit[0] if alias_hit else e)
+            out = out.orderBy(*key_names, ascending=[a for _, a in order])
+            order = []
+        out = out.select(*post)
     else:
         out = df
         proj: List[Any] = []

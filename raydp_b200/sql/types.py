@@ -65,6 +65,43 @@ class ArrayType(DataType):
         return f"array<{self.elementType.simpleString()}>"
 
 
+class MapType(DataType):
+    name = "map"
+
+    def __init__(self, keyType: DataType, valueType: DataType, valueContainsNull: bool = True):
+        self.keyType = keyType
+        self.valueType = valueType
+        self.valueContainsNull = valueContainsNull
+
+    @property
+    def arrow(self):  # type: ignore[override]
+        return pa.map_(self.keyType.arrow, self.valueType.arrow)
+
+    def simpleString(self):
+        return f"map<{self.keyType.simpleString()},{self.valueType.simpleString()}>"
+
+    def __repr__(self):
+        return f"MapType({self.keyType!r}, {self.valueType!r}, {self.valueContainsNull})"
+
+
+class DecimalType(DataType):
+    name = "decimal"
+
+    def __init__(self, precision: int = 10, scale: int = 0):
+        self.precision = precision
+        self.scale = scale
+
+    @property
+    def arrow(self):  # type: ignore[override]
+        return pa.decimal128(self.precision, self.scale)
+
+    def simpleString(self):
+        return f"decimal({self.precision},{self.scale})"
+
+    def __repr__(self):
+        return f"DecimalType({self.precision},{self.scale})"
+
+
 class StructField:
     def __init__(self, name: str, dataType: DataType, nullable: bool = True, metadata=None):
         self.name = name
@@ -145,24 +182,66 @@ def parse_type(spec: Union[str, DataType, pa.DataType]) -> DataType:
         return spec
     if isinstance(spec, pa.DataType):
         return from_arrow_type(spec)
-    key = str(spec).strip().lower()
+    text = str(spec).strip()
+    key = text.lower()
     if key in _BY_NAME:
         return _BY_NAME[key]()
+    if key.startswith("array<") and key.endswith(">"):
+        return ArrayType(parse_type(text[6:-1]))
+    if key.startswith("map<") and key.endswith(">"):
+        parts = _split_top_level(text[4:-1])
+        if len(parts) != 2:
+            raise ValueError(f"unsupported data type string: {spec!r}")
+        return MapType(parse_type(parts[0]), parse_type(parts[1]))
+    if key.startswith("struct<") and key.endswith(">"):
+        return parse_ddl(text[7:-1])
+    if key.startswith(("decimal", "numeric", "dec")):
+        inside = key[key.index("(") + 1:key.rindex(")")] if "(" in key else "10,0"
+        nums = [int(x) for x in inside.split(",")]
+        return DecimalType(nums[0], nums[1] if len(nums) > 1 else 0)
+    if key.startswith(("varchar", "char")):
+        return StringType()
     raise ValueError(f"unsupported data type string: {spec!r}")
+
+
+def _split_top_level(text: str, sep: str = ",") -> List[str]:
+    """Split on ``sep`` outside ``<...>`` / ``(...)`` nesting."""
+    out, depth, cur = [], 0, []
+    for ch in text:
+        if ch in "<(":
+            depth += 1
+        elif ch in ">)":
+            depth -= 1
+        if ch == sep and depth == 0:
+            out.append("".join(cur))
+            cur = []
+        else:
+            cur.append(ch)
+    if "".join(cur).strip():
+        out.append("".join(cur))
+    return out
 
 
 def parse_ddl(ddl: str) -> "StructType":
     """``"a int, b double"`` / ``"a: int, b: string"`` -> StructType (the DDL strings pyspark accepts for
     ``mapInPandas``, ``createDataFrame(schema=...)`` and ``read.schema(...)``)."""
     fields = []
-    for part in ddl.split(","):
+    for part in _split_top_level(ddl):
         part = part.strip()
         if not part:
             continue
-        name, _, tname = part.replace(":", " ", 1).partition(" ")
-        if not tname.strip():
+        head = part.split("<", 1)[0]
+        if ":" in head:                             # "name: type" (struct<...> notation)
+            name, _, tname = part.partition(":")
+        else:
+            name, _, tname = part.partition(" ")
+        tname = tname.strip()
+        nullable = True
+        if tname.lower().endswith(" not null"):
+            tname, nullable = tname[:-9].strip(), False
+        if not tname:
             raise ValueError(f"cannot parse schema field {part!r}; expected '<name> <type>'")
-        fields.append(StructField(name.strip().strip("`"), parse_type(tname.strip())))
+        fields.append(StructField(name.strip().strip("`"), parse_type(tname), nullable))
     return StructType(fields)
 
 
@@ -193,6 +272,12 @@ def from_arrow_type(t: pa.DataType) -> DataType:
         return ArrayType(from_arrow_type(t.value_type))
     if pa.types.is_struct(t):
         return StructType([StructField(f.name, from_arrow_type(f.type)) for f in t])
+    if pa.types.is_map(t):
+        return MapType(from_arrow_type(t.key_type), from_arrow_type(t.item_type))
+    if pa.types.is_decimal(t):
+        return DecimalType(t.precision, t.scale)
+    if pa.types.is_fixed_size_list(t):
+        return ArrayType(from_arrow_type(t.value_type))
     if pa.types.is_null(t):
         return NullType()
     if pa.types.is_dictionary(t):
