@@ -230,6 +230,16 @@ class Column:
         n = table.num_rows
         if k == "col":
             if a[0] not in table.column_names:
+                # "alias.column" (the bare column unless a join kept the alias-qualified copy) or "struct.field"
+                if "." in a[0]:
+                    head, rest = a[0].split(".", 1)
+                    if head in table.column_names and pa.types.is_struct(table.schema.field(head).type):
+                        value = table.column(head)
+                        for part in rest.split("."):
+                            value = pc.struct_field(value, part)
+                        return value
+                    if rest in table.column_names:
+                        return table.column(rest)
                 raise KeyError(f"cannot resolve column '{a[0]}' given input columns {table.column_names}")
             return table.column(a[0])
         if k == "lit":
@@ -411,15 +421,19 @@ def _call(fn: str, args: list, n: int, ctx: EvalContext):
         return getattr(pc, fn)(pc.cast(x, pa.float64()))
     if fn == "round":
         # Spark rounds HALF_UP (2.5 -> 3, -2.5 -> -3); bround() is the half-even one
-        return pc.round(x, ndigits=args[1] if len(args) > 1 else 0, round_mode="half_towards_infinity")
+        digits = args[1] if len(args) > 1 else 0
+        digits = digits.as_py() if isinstance(digits, pa.Scalar) else digits
+        return pc.round(x, ndigits=int(digits or 0), round_mode="half_towards_infinity")
     if fn == "pow":
         return pc.power(pc.cast(x, pa.float64()), args[1])
     if fn == "rand":
         seed = args[0] if args and args[0] is not None else 0x5eed
+        seed = seed.as_py() if isinstance(seed, pa.Scalar) else seed
         rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index])
         return pa.array(rng.random(n))
     if fn == "randn":
         seed = args[0] if args and args[0] is not None else 0x5eed
+        seed = seed.as_py() if isinstance(seed, pa.Scalar) else seed
         rng = np.random.default_rng([int(seed) & 0x7FFFFFFF, ctx.partition_index, 1])
         return pa.array(rng.standard_normal(n))
     if fn == "monotonically_increasing_id":

@@ -119,6 +119,15 @@ def asc(c) -> Column:
 
 
 # aggregate expressions (used with DataFrame.agg / GroupedData.agg)
+def _plain(v):
+    """Parameters that must be constants: unwrap ``lit(...)``."""
+    if isinstance(v, Column):
+        if v._kind != "lit":
+            raise TypeError("this parameter must be a literal")
+        return v._args[0]
+    return v
+
+
 def _agg(fn: str, c) -> Column:
     target = None if (isinstance(c, str) and c == "*") else as_column(c)
     return Column("agg", (fn, target))
@@ -133,7 +142,8 @@ def max(c): return _agg("max", c)  # noqa: A001
 def stddev(c): return _agg("stddev", c)
 def variance(c): return _agg("variance", c)
 def countDistinct(c, *cols): return count_distinct(c, *cols)
-def first(c): return _agg("first", c)
+def first(c, ignorenulls: bool = False):
+    return Column("agg", ("first_value", as_column(c), True)) if _plain(ignorenulls) else _agg("first", c)
 
 
 def row_number() -> Column:
@@ -318,9 +328,9 @@ def _duration_micros(text: str) -> int:
 
 def window(timeColumn, windowDuration: str, slideDuration: Optional[str] = None, startTime: Optional[str] = None):
     """Tumbling time window: a struct ``{start, end}`` (sliding windows are not supported)."""
-    if slideDuration is not None and slideDuration != windowDuration:
+    if slideDuration is not None and _plain(slideDuration) != _plain(windowDuration):
         raise NotImplementedError("sliding windows are not supported by the built-in engine")
-    width = _duration_micros(windowDuration)
+    width = _duration_micros(_plain(windowDuration))
     start = Column("call", ("window_start", (as_column(timeColumn), width, 0)))
     end = Column("call", ("window_start", (as_column(timeColumn), width, width)))
     return struct(start.alias("start"), end.alias("end")).alias("window")
@@ -381,6 +391,7 @@ def json_tuple(c, *fields):
 
 
 def from_json(c, schema, options=None):
+    schema = _plain(schema)
     if isinstance(schema, str):
         try:
             schema = T.parse_type(schema)
@@ -477,11 +488,11 @@ def _agg2(fn: str, a, b) -> Column:
 def collect_list(c): return _agg_p("collect_list", c)
 array_agg = collect_list
 def collect_set(c): return _agg_p("collect_set", c)
-def last(c, ignorenulls: bool = False): return _agg_p("last", c, ignorenulls)
-def any_value(c, ignoreNulls: bool = False): return _agg_p("any_value", c, ignoreNulls)
-def first_value(c, ignoreNulls: bool = False): return _agg_p("first_value", c, ignoreNulls)
-def last_value(c, ignoreNulls: bool = False): return _agg_p("last_value", c, ignoreNulls)
-def nth_value(c, offset: int, ignoreNulls: bool = False): return _agg_p("nth_value", c, offset)
+def last(c, ignorenulls: bool = False): return _agg_p("last", c, bool(_plain(ignorenulls)))
+def any_value(c, ignoreNulls: bool = False): return _agg_p("any_value", c, bool(_plain(ignoreNulls)))
+def first_value(c, ignoreNulls: bool = False): return _agg_p("first_value", c, bool(_plain(ignoreNulls)))
+def last_value(c, ignoreNulls: bool = False): return _agg_p("last_value", c, bool(_plain(ignoreNulls)))
+def nth_value(c, offset: int, ignoreNulls: bool = False): return _agg_p("nth_value", c, int(_plain(offset)))
 def approx_count_distinct(c, rsd: Optional[float] = None): return _agg_p("approx_count_distinct", c)
 approxCountDistinct = approx_count_distinct
 def sum_distinct(c): return _agg_p("sum_distinct", c)
@@ -531,9 +542,9 @@ def rank() -> Column: return Column("rank_fn", ("rank",))
 def dense_rank() -> Column: return Column("rank_fn", ("dense_rank",))
 def percent_rank() -> Column: return Column("rank_fn", ("percent_rank",))
 def cume_dist() -> Column: return Column("rank_fn", ("cume_dist",))
-def ntile(n: int) -> Column: return Column("rank_fn", ("ntile", int(n)))
-def lag(c, offset: int = 1, default=None) -> Column: return Column("rank_fn", ("lag", as_column(c), offset, default))
-def lead(c, offset: int = 1, default=None) -> Column: return Column("rank_fn", ("lead", as_column(c), offset, default))
+def ntile(n: int) -> Column: return Column("rank_fn", ("ntile", int(_plain(n))))
+def lag(c, offset: int = 1, default=None) -> Column: return Column("rank_fn", ("lag", as_column(c), int(_plain(offset)), default))
+def lead(c, offset: int = 1, default=None) -> Column: return Column("rank_fn", ("lead", as_column(c), int(_plain(offset)), default))
 
 
 class UserDefinedFunction:

@@ -32,13 +32,15 @@ _TOKEN = re.compile(r"""
     | (?P<str>'(?:[^']|'')*'|"(?:[^"]|"")*")
     | (?P<bq>`[^`]+`)
     | (?P<id>[A-Za-z_][A-Za-z_0-9]*)
-    | (?P<op><=|>=|<>|!=|==|[-+*/%(),.<>=])
+    | (?P<op><=>|<=|>=|<>|!=|==|\|\||[-+*/%(),.<>=\[\]])
     )""", re.X)
 
 _AGGREGATES = {"count", "sum", "avg", "mean", "min", "max", "first", "stddev", "variance", "countdistinct"}
 _KEYWORDS = {"select", "from", "where", "group", "by", "having", "order", "limit", "as", "and", "or", "not",
              "is", "null", "in", "between", "case", "when", "then", "else", "end", "cast", "distinct", "asc",
-             "desc", "true", "false", "like", "join", "inner", "left", "right", "full", "cross", "on", "using"}
+             "desc", "true", "false", "like", "join", "inner", "left", "right", "full", "cross", "on", "using",
+             "union", "intersect", "except", "minus", "over", "rlike", "ilike", "regexp", "exists", "with",
+             "partition", "rows", "range", "window", "outer", "semi", "anti", "natural", "lateral"}
 
 
 class SqlError(ValueError):
@@ -47,6 +49,7 @@ class SqlError(ValueError):
 
 def tokenize(text: str) -> List[Tuple[str, str]]:
     out, pos = [], 0
+    text = re.sub(r"--[^\n]*", " ", text)            # line comments
     text = text.strip().rstrip(";")
     while pos < len(text):
         m = _TOKEN.match(text, pos)
@@ -67,9 +70,19 @@ def tokenize(text: str) -> List[Tuple[str, str]]:
 
 
 class _Parser:
-    def __init__(self, tokens: List[Tuple[str, str]]):
+    def __init__(self, tokens: List[Tuple[str, str]], session=None, ctes: Optional[Dict[str, Any]] = None):
         self.t = tokens
         self.i = 0
+        self.session = session
+        self.ctes: Dict[str, Any] = dict(ctes or {})
+
+    def _subquery(self):
+        """``( SELECT ... )`` with the opening parenthesis already consumed; consumes the closing one."""
+        if self.session is None:
+            raise SqlError("sub-queries need a session: use spark.sql(...)")
+        df = _parse_query(self, self.session)
+        self.expect_op(")")
+        return df
 
     # ---- token helpers
     def peek(self, k: int = 0) -> Tuple[str, str]:
@@ -134,11 +147,26 @@ class _Parser:
                 left = left.isNotNull()
             elif self.kw("is", "null"):
                 left = left.isNull()
+            elif self.kw("is", "not", "distinct", "from"):
+                left = left.eqNullSafe(self.additive())
+            elif self.kw("is", "distinct", "from"):
+                left = ~left.eqNullSafe(self.additive())
+            elif self.kw("is", "not", "true") or self.kw("is", "false"):
+                left = F.coalesce(left, F.lit(False)) == F.lit(False)
+            elif self.kw("is", "true") or self.kw("is", "not", "false"):
+                left = F.coalesce(left, F.lit(False)) == F.lit(True)
             elif self.at_kw("not") and self.peek(1)[1].lower() in ("in", "between"):
                 self.i += 1
                 left = ~self._in_or_between(left)
             elif self.at_kw("in") or self.at_kw("between"):
                 left = self._in_or_between(left)
+            elif self.at_kw("not") and self.peek(1)[1].lower() in ("like", "rlike", "ilike", "regexp"):
+                self.i += 1
+                left = ~self._like(left)
+            elif self.at_kw("like") or self.at_kw("rlike") or self.at_kw("ilike") or self.at_kw("regexp"):
+                left = self._like(left)
+            elif self.op("<=>"):
+                left = left.eqNullSafe(self.additive())
             else:
                 kind, v = self.peek()
                 if kind == "op" and v in ("=", "==", "<>", "!=", "<", "<=", ">", ">="):
@@ -149,9 +177,22 @@ class _Parser:
                 else:
                     return left
 
+    def _like(self, left: Column) -> Column:
+        word = self.name().lower()
+        pattern = self.additive()
+        if pattern._kind != "lit":
+            raise SqlError(f"{word.upper()} needs a literal pattern")
+        text = pattern._args[0]
+        if self.kw("escape"):
+            self.i += 1
+        return {"like": left.like, "ilike": left.ilike, "rlike": left.rlike, "regexp": left.rlike}[word](text)
+
     def _in_or_between(self, left: Column) -> Column:
         if self.kw("in"):
             self.expect_op("(")
+            if self.at_kw("select") or self.at_kw("with"):
+                sub = self._subquery()
+                return left.isin(*[r[0] for r in sub.collect() if r[0] is not None])
             values = [self._literal_value()]
             while self.op(","):
                 values.append(self._literal_value())
@@ -184,6 +225,8 @@ class _Parser:
                 left = left + self.multiplicative()
             elif self.op("-"):
                 left = left - self.multiplicative()
+            elif self.op("||"):
+                left = F.concat(left, self.multiplicative())
             else:
                 return left
 
@@ -216,9 +259,15 @@ class _Parser:
             return F.lit(v)
         if kind == "op" and v == "(":
             self.i += 1
+            if self.at_kw("select") or self.at_kw("with"):
+                sub = self._subquery()                       # scalar sub-query (uncorrelated): first cell
+                rows = sub.limit(2).collect()
+                if len(rows) > 1:
+                    raise SqlError("a scalar sub-query returned more than one row")
+                return F.lit(rows[0][0] if rows else None)
             inner = self.expr()
             self.expect_op(")")
-            return inner
+            return self._postfix(inner)
         if kind == "qid":
             self.i += 1
             return F.col(v)
@@ -233,22 +282,64 @@ class _Parser:
             return F.lit(None)
         if low == "case":
             return self._case()
+        if low == "exists" and self.peek(1) == ("op", "("):
+            self.i += 2
+            return F.lit(self._subquery().limit(1).count() > 0)
+        if low in ("date", "timestamp") and self.peek(1)[0] == "str":
+            self.i += 2
+            text = self.t[self.i - 1][1]
+            return F.to_date(F.lit(text)) if low == "date" else F.to_timestamp(F.lit(text))
+        if low == "interval":
+            raise SqlError("INTERVAL literals are not supported; use date_add / add_months")
         if low == "cast" and self.peek(1) == ("op", "("):
             self.i += 2
             inner = self.expr()
             if not self.kw("as"):
                 raise SqlError("CAST needs AS <type>")
-            type_name = self.name()
+            type_name = self._type_text()
             self.expect_op(")")
-            return inner.cast(type_name.lower())
+            return self._postfix(inner.cast(type_name.lower()))
         if self.peek(1) == ("op", "("):
-            return self._call()
+            return self._postfix(self._call())
         self.i += 1
-        # qualified name  view.column -> column
-        while self.peek() == ("op", ".") and self.peek(1)[0] in ("id", "qid"):
+        # qualified name: alias.column (resolved at evaluation: "<alias>.<column>" if the join kept it
+        # apart, else the bare column) or struct_column.field
+        while self.peek() == ("op", ".") and (self.peek(1)[0] in ("id", "qid") or self.peek(1) == ("op", "*")):
             self.i += 1
-            v = self.name()
-        return F.col(v)
+            if self.op("*"):
+                return F.col(v + ".*")
+            v = v + "." + self.name()
+        return self._postfix(F.col(v))
+
+    def _postfix(self, col: Column) -> Column:
+        """``expr[index]`` / ``expr['key']`` and ``expr.field`` after a call or parenthesis."""
+        while True:
+            if self.op("["):
+                key = self.expr()
+                self.expect_op("]")
+                col = col.getItem(key._args[0] if key._kind == "lit" else key)
+            elif col._kind != "col" and self.peek() == ("op", ".") and self.peek(1)[0] in ("id", "qid"):
+                self.i += 1
+                col = col.getField(self.name())
+            else:
+                return col
+
+    def _type_text(self) -> str:
+        """The type after ``CAST(x AS``: everything up to the parenthesis that closes the CAST."""
+        parts, depth = [], 0
+        while True:
+            kind, v = self.peek()
+            if kind == "eof":
+                raise SqlError("unterminated CAST")
+            if kind == "op" and v in ("(", "<"):
+                depth += 1
+            elif kind == "op" and v in (")", ">"):
+                if depth == 0 and v == ")":
+                    break
+                depth -= 1
+            parts.append(v)
+            self.i += 1
+        return "".join(parts)
 
     def _case(self) -> Column:
         self.kw("case")
@@ -293,14 +384,85 @@ class _Parser:
                     fn = getattr(F, cand)
                     break
         if fn is None or not callable(fn):
-            raise SqlError(f"unknown SQL function {fn_name!r}")
-        return fn(*args)
+            udf = getattr(self.session, "_registered_udfs", {}).get(fn_name) if self.session is not None else None
+            if udf is None:
+                raise SqlError(f"unknown SQL function {fn_name!r}")
+            fn = udf
+        out = fn(*args)
+        if self.kw("over"):
+            out = out.over(self._window_spec())
+        return out
+
+    def _window_spec(self):
+        from raydp_b200.sql.window import Window, WindowSpec
+        if not self.op("("):
+            name = self.name()                              # OVER w  (WINDOW w AS (...))
+            spec = getattr(self, "named_windows", {}).get(name.lower())
+            if spec is None:
+                raise SqlError(f"unknown window {name!r}")
+            return spec
+        spec = WindowSpec()
+        if self.kw("partition", "by") or self.kw("distribute", "by"):
+            parts = [self.expr()]
+            while self.op(","):
+                parts.append(self.expr())
+            spec = spec.partitionBy(*parts)
+        if self.kw("order", "by") or self.kw("sort", "by"):
+            spec = spec.orderBy(*self._order_items())
+        for kind in ("rows", "range"):
+            if self.kw(kind):
+                def bound() -> int:
+                    if self.kw("unbounded", "preceding"):
+                        return Window.unboundedPreceding
+                    if self.kw("unbounded", "following"):
+                        return Window.unboundedFollowing
+                    if self.kw("current", "row"):
+                        return 0
+                    n = int(self._literal_value())
+                    if self.kw("preceding"):
+                        return -n
+                    if self.kw("following"):
+                        return n
+                    raise SqlError("frame bound needs PRECEDING or FOLLOWING")
+                if self.kw("between"):
+                    lo = bound()
+                    if not self.kw("and"):
+                        raise SqlError("frame BETWEEN needs AND")
+                    hi = bound()
+                else:
+                    lo, hi = bound(), 0
+                spec = spec.rowsBetween(lo, hi) if kind == "rows" else spec.rangeBetween(lo, hi)
+        self.expect_op(")")
+        return spec
+
+    def _order_items(self) -> List[Column]:
+        out = []
+        while True:
+            e = self.expr()
+            direction = "ascending"
+            if self.kw("desc"):
+                direction = "descending"
+            else:
+                self.kw("asc")
+            placement = None
+            if self.kw("nulls", "first"):
+                placement = "at_start"
+            elif self.kw("nulls", "last"):
+                placement = "at_end"
+            if placement is None:
+                out.append(e.desc() if direction == "descending" else e.asc())
+            else:
+                out.append(Column("sort", (e, direction, placement)))
+            if not self.op(","):
+                return out
 
 
 def _is_aggregate(col: Column) -> bool:
     """True if the expression tree contains an aggregate call."""
     if getattr(col, "_kind", None) == "agg":
         return True
+    if getattr(col, "_kind", None) == "window":      # sum(x) OVER (...) is not a grouping aggregate
+        return False
     for a in getattr(col, "_args", ()) or ():
         if isinstance(a, Column) and _is_aggregate(a):
             return True
@@ -455,10 +617,104 @@ def _qualified_name(p: _Parser) -> str:
     return name
 
 
+_JOIN_WORDS = {"join", "inner", "left", "right", "full", "cross", "on", "using", "outer", "semi", "anti", "natural"}
+_CLAUSE_WORDS = {"where", "group", "having", "order", "limit", "union", "intersect", "except", "minus", "window",
+                 "offset"}
+
+
 def _parse_select(p: _Parser, session):
+    """Kept name of the statement entry point: a full query (WITH / set operations / ORDER BY / LIMIT)."""
+    p.session = session
+    return _parse_query(p, session)
+
+
+def _parse_query(p: _Parser, session):
+    """``[WITH name AS (query), ...] core {UNION [ALL] | INTERSECT | EXCEPT core} [ORDER BY ...] [LIMIT n]``"""
+    p.session = session
+    saved_ctes = dict(p.ctes)
+    if p.kw("with"):
+        while True:
+            name = p.name()
+            p.kw("as")
+            p.expect_op("(")
+            p.ctes[name.lower()] = p._subquery()
+            if not p.op(","):
+                break
+    df = _parse_term(p, session)
+    combined = False
+    while True:
+        if p.kw("union"):
+            keep_all = p.kw("all")
+            p.kw("distinct")
+            right = _parse_term(p, session, tail=False)
+            df = df.union(right) if keep_all else df.union(right).distinct()
+        elif p.kw("intersect"):
+            keep_all = p.kw("all")
+            right = _parse_term(p, session, tail=False)
+            df = df.intersectAll(right) if keep_all else df.intersect(right)
+        elif p.kw("except") or p.kw("minus"):
+            keep_all = p.kw("all")
+            right = _parse_term(p, session, tail=False)
+            df = df.exceptAll(right) if keep_all else df.subtract(right)
+        else:
+            break
+        combined = True
+    if combined:                                    # the tail belongs to the combined result
+        if p.kw("order", "by"):
+            df = df.orderBy(*p._order_items())
+        if p.kw("limit"):
+            df = df.limit(int(p._literal_value()))
+    p.ctes = saved_ctes
+    return df
+
+
+def _parse_term(p: _Parser, session, tail: bool = True):
+    if p.peek() == ("op", "(") and p.peek(1)[0] == "id" and p.peek(1)[1].lower() in ("select", "with"):
+        p.i += 1
+        return p._subquery()
+    return _parse_core(p, session, tail)
+
+
+def _table_ref(p: _Parser, session) -> Tuple[Any, Optional[str]]:
+    """``name [AS alias]`` or ``( query ) [AS] alias`` -> (DataFrame, alias)."""
+    if p.op("("):
+        df = p._subquery()
+        default_alias = None
+    else:
+        name = _qualified_name(p)
+        df = p.ctes.get(name.lower())
+        if df is None:
+            df = session.catalog.lookup(name)
+        default_alias = name.split(".")[-1]
+    alias = default_alias
+    if p.kw("as"):
+        alias = p.name()
+    elif p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS | _JOIN_WORDS | _CLAUSE_WORDS:
+        alias = p.name()
+    return df, alias
+
+
+def _side_of(name: str, left_aliases: set, right_alias: Optional[str], left_cols, right_cols) -> Tuple[str, str]:
+    """``alias.col`` / ``col`` of an ON equality -> (``"l"`` | ``"r"``, bare column name)."""
+    if "." in name:
+        qual, bare = name.rsplit(".", 1)
+        if qual == right_alias and bare in right_cols:
+            return "r", bare
+        if qual in left_aliases and (bare in left_cols or f"{qual}.{bare}" in left_cols):
+            return "l", bare if bare in left_cols else f"{qual}.{bare}"
+        name = bare
+    if name in left_cols and name not in right_cols:
+        return "l", name
+    if name in right_cols and name not in left_cols:
+        return "r", name
+    return ("l", name) if name in left_cols else ("r", name)
+
+
+def _parse_core(p: _Parser, session, tail: bool = True):
     if not p.kw("select"):
         raise SqlError("expected SELECT")
     distinct = p.kw("distinct")
+    p.kw("all")
     items: List[Any] = []          # "*" or Column
     while True:
         if p.op("*"):
@@ -467,8 +723,10 @@ def _parse_select(p: _Parser, session):
             col = p.expr()
             if p.kw("as"):
                 col = col.alias(p.name())
-            elif p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS:
+            elif p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS | _CLAUSE_WORDS:
                 col = col.alias(p.name())
+            elif col._kind == "col" and "." in col._args[0] and not col._args[0].endswith(".*") and col._name is None:
+                col = col.alias(col._args[0].rsplit(".", 1)[1])        # a.k shows up as k
             items.append(col)
         if not p.op(","):
             break
@@ -476,19 +734,17 @@ def _parse_select(p: _Parser, session):
         # SELECT <constant expressions>: one row
         one = session.range(1)
         return one.select(*[c for c in items if not isinstance(c, str)])
-    df = session.catalog.lookup(_qualified_name(p))
-    join_words = {"join", "inner", "left", "right", "full", "cross", "on", "using", "outer", "semi", "anti"}
-
-    def skip_alias():
-        if p.peek()[0] in ("id", "qid") and p.peek()[1].lower() not in _KEYWORDS | join_words:
-            p.name()                                # table alias: columns are resolved by bare name
-    skip_alias()
+    df, alias = _table_ref(p, session)
+    left_aliases = {alias} if alias else set()
     while True:                                     # [INNER | LEFT | RIGHT | FULL [OUTER] | CROSS | LEFT SEMI/ANTI] JOIN
         how = None
+        natural = p.kw("natural")
         if p.kw("join") or p.kw("inner", "join"):
             how = "inner"
         elif p.kw("cross", "join"):
             how = "cross"
+        elif p.op(","):
+            how = "cross"                           # FROM a, b
         else:
             for side in ("left", "right", "full"):
                 if p.at_kw(side):
@@ -505,31 +761,51 @@ def _parse_select(p: _Parser, session):
                     break
         if how is None:
             break
-        other = session.catalog.lookup(_qualified_name(p))
-        skip_alias()
-        if how == "cross":
-            df = df.crossJoin(other)
+        other, other_alias = _table_ref(p, session)
+        # columns both sides have (other than the join keys, known below) stay reachable as <alias>.<column>
+        pairs: List[Tuple[str, str]] = []
+        using: Optional[List[str]] = None
+        if natural:
+            using = [c for c in df.columns if c in other.columns]
+        elif how == "cross":
+            using = None
         elif p.kw("using"):
             p.expect_op("(")
-            names = [p.name()]
+            using = [p.name()]
             while p.op(","):
-                names.append(p.name())
+                using.append(p.name())
             p.expect_op(")")
-            df = df.join(other, names, how)
         elif p.kw("on"):
             from raydp_b200.sql.dataframe import _equi_join_pairs
-            pairs = [(a, b) if a in df.columns else (b, a) for a, b in _equi_join_pairs(p.expr())]
-            left_keys, right_keys = [a for a, _ in pairs], [b for _, b in pairs]
-            if left_keys == right_keys:
-                df = df.join(other, left_keys, how)
-            else:
-                renamed = other
-                for lk, rk in pairs:
-                    if lk != rk:
-                        renamed = renamed.withColumnRenamed(rk, lk)
-                df = df.join(renamed, left_keys, how)
+            for a, b in _equi_join_pairs(p.expr()):
+                side_a, name_a = _side_of(a, left_aliases, other_alias, df.columns, other.columns)
+                side_b, name_b = _side_of(b, left_aliases, other_alias, df.columns, other.columns)
+                if side_a == side_b:
+                    raise SqlError(f"join condition {a} = {b} does not relate the two sides")
+                pairs.append((name_a, name_b) if side_a == "l" else (name_b, name_a))
         else:
             raise SqlError("JOIN needs ON <equalities> or USING (<columns>)")
+        key_right = set(using or []) | {r for _, r in pairs}
+        clashes = [c for c in other.columns if c in df.columns and c not in key_right]
+        if clashes and how not in ("left_semi", "left_anti"):
+            tag = other_alias or "right"
+            for c in clashes:
+                other = other.withColumnRenamed(c, f"{tag}.{c}")
+        if how == "cross":
+            df = df.crossJoin(other)
+        elif using is not None:
+            df = df.join(other, using, how)
+        else:
+            left_keys, right_keys = [l for l, _ in pairs], [r for _, r in pairs]
+            renamed = other
+            for lk, rk in pairs:
+                if lk != rk:
+                    if lk in renamed.columns:       # the left key's name is taken on the right by another column
+                        renamed = renamed.withColumnRenamed(lk, f"{other_alias or 'right'}.{lk}")
+                    renamed = renamed.withColumnRenamed(rk, lk)
+            df = df.join(renamed, left_keys, how)
+        if other_alias:
+            left_aliases.add(other_alias)
     if p.kw("where"):
         df = df.filter(p.expr())
     key_exprs: List[Column] = []
@@ -539,27 +815,31 @@ def _parse_select(p: _Parser, session):
             key_exprs.append(p.expr())
     keys: List[str] = [e._output_name() for e in key_exprs]
     having = p.expr() if p.kw("having") else None
-    order: List[Tuple[Column, bool]] = []
-    if p.kw("order", "by"):
-        while True:
-            e = p.expr()
-            asc = True
-            if p.kw("desc"):
-                asc = False
-            else:
-                p.kw("asc")
-            order.append((e, asc))
-            if not p.op(","):
-                break
+    order: List[Column] = []
     limit = None
-    if p.kw("limit"):
-        limit = int(p._literal_value())
+    if tail:
+        if p.kw("order", "by") or p.kw("sort", "by"):
+            order = p._order_items()
+        if p.kw("limit"):
+            limit = int(p._literal_value())
+
+    def order_parts(item: Column) -> Tuple[Column, str, Optional[str]]:
+        return item._args[0], item._args[1], (item._args[2] if len(item._args) > 2 else None)
+
+    def rebuild(expr: Column, direction: str, placement: Optional[str]) -> Column:
+        return Column("sort", (expr, direction) + ((placement,) if placement else ()))
 
     cols = [c for c in items if not isinstance(c, str)]
-    grouped = bool(keys) or any(_is_aggregate(c) for c in cols)
+    # ORDER BY 1, 2: ordinals of the select list
+    for i, item in enumerate(order):
+        e, direction, placement = order_parts(item)
+        if e._kind == "lit" and isinstance(e._args[0], int) and 1 <= e._args[0] <= len(cols):
+            order[i] = rebuild(F.col(cols[e._args[0] - 1]._output_name()), direction, placement)
+    grouped = bool(keys) or any(_is_aggregate(c) for c in cols) or (having is not None and _is_aggregate(having))
     if grouped:
         from raydp_b200.sql.dataframe import _agg_default_name
-        # GROUP BY 1, 2 (ordinals) and GROUP BY <select alias>
+        select_sigs = {_signature(Column(c._kind, c._args)): c for c in cols if not _is_aggregate(c)}
+        # GROUP BY 1, 2 (ordinals), GROUP BY <select alias>, GROUP BY <expression that a select item repeats>
         for i, e in enumerate(key_exprs):
             if e._kind == "lit" and isinstance(e._args[0], int) and 1 <= e._args[0] <= len(cols):
                 key_exprs[i] = cols[e._args[0] - 1]
@@ -567,25 +847,33 @@ def _parse_select(p: _Parser, session):
                 match = [c for c in cols if c._name == e._args[0]]
                 if match:
                     key_exprs[i] = match[0]
+            elif e._name is None and _signature(e) in select_sigs:
+                key_exprs[i] = select_sigs[_signature(e)]
         keys = [e._output_name() for e in key_exprs]
+        key_sigs = {_signature(Column(e._kind, e._args)): e._output_name() for e in key_exprs}
         agg_items: List[Column] = []
         registry: Dict[str, str] = {}
         post: List[Column] = []
         for c in cols:
+            bare_sig = _signature(Column(c._kind, c._args))
             if _is_aggregate(c):
                 name = c._name or _agg_default_name(c)
                 agg_items.append(c.alias(name))
                 if c._kind == "agg":
-                    registry[_signature(c)] = name
+                    registry[_signature(Column(c._kind, c._args))] = name
                 post.append(F.col(name))
             elif c._output_name() in keys:
                 post.append(F.col(c._output_name()))
+            elif bare_sig in key_sigs:
+                post.append(F.col(key_sigs[bare_sig]).alias(c._output_name()))
             else:
                 post.append(c)                      # an expression over the grouping keys: applied afterwards
+        if any(isinstance(c, str) for c in items):
+            raise SqlError("SELECT * cannot be combined with GROUP BY")
         hidden: List[Column] = []
         if having is not None:
             having = _replace_aggregates(having, registry, hidden)
-        order = [(_replace_aggregates(e, registry, hidden), a) for e, a in order]
+        order = [rebuild(_replace_aggregates(order_parts(o)[0], registry, hidden), *order_parts(o)[1:]) for o in order]
         if agg_items or hidden:
             out = df.groupBy(*key_exprs).agg(*(agg_items + hidden))
         else:
@@ -593,13 +881,15 @@ def _parse_select(p: _Parser, session):
         if having is not None:
             out = out.filter(having)
         out_names = [c._output_name() for c in post]
-        if order and not all(e._kind == "col" and e._output_name() in out_names for e, _ in order):
-            key_names = [f"__ok{i}" for i in range(len(order))]
-            for n, (e, _) in zip(key_names, order):
+        if order and not all(order_parts(o)[0]._kind == "col" and order_parts(o)[0]._output_name() in out_names
+                             for o in order):
+            resolved = []
+            for o in order:
+                e, direction, placement = order_parts(o)
                 alias_hit = [c for c in post if c._name == e._output_name()] if e._kind == "col" and \
                     e._args[0] not in out.columns else []
-                out = out.withColumn(n, alias_hit[0] if alias_hit else e)
-            out = out.orderBy(*key_names, ascending=[a for _, a in order])
+                resolved.append(rebuild(alias_hit[0] if alias_hit else e, direction, placement))
+            out = out.orderBy(*resolved)
             order = []
         out = out.select(*post)
     else:
@@ -610,11 +900,9 @@ def _parse_select(p: _Parser, session):
         out_names = [c if isinstance(c, str) else c._output_name() for c in proj]
         # ORDER BY on output names (aliases) sorts after the projection; anything else is evaluated on
         # the input first (the global sort's order survives the narrow projection that follows)
-        if order and not all(e._kind == "col" and e._output_name() in out_names for e, _ in order):
-            key_names = [f"__ok{i}" for i in range(len(order))]
-            for n, (e, _) in zip(key_names, order):
-                out = out.withColumn(n, e)
-            out = out.orderBy(*key_names, ascending=[a for _, a in order])
+        if order and not all(order_parts(o)[0]._kind == "col" and order_parts(o)[0]._output_name() in out_names
+                             for o in order):
+            out = out.orderBy(*order)
             order = []
         star_only = len(items) == 1 and isinstance(items[0], str)
         if not star_only or out.columns != df.columns:
@@ -622,7 +910,7 @@ def _parse_select(p: _Parser, session):
     if distinct:
         out = out.distinct()
     if order:
-        out = out.orderBy(*[e._output_name() for e, _ in order], ascending=[a for _, a in order])
+        out = out.orderBy(*order)
     if limit is not None:
         out = out.limit(limit)
     return out
@@ -630,9 +918,9 @@ def _parse_select(p: _Parser, session):
 
 def run_sql(session, query: str):
     """Execute one statement; always returns a DataFrame (empty for DDL)."""
-    p = _Parser(tokenize(query))
+    p = _Parser(tokenize(query), session)
     cat = session.catalog
-    if p.at_kw("select"):
+    if p.at_kw("select") or p.at_kw("with") or p.peek() == ("op", "("):
         out = _parse_select(p, session)
     elif p.kw("show", "tables"):
         db = None

@@ -212,9 +212,11 @@ def test_sql_front_end_views_tables_and_expressions(spark_session, tmp_path):
     j = spark.sql("select id, name from t left join names n on t.k = n.kk where id < 3 order by id").collect()
     assert [(r.id, r.name) for r in j] == [(0, "zero"), (1, "one"), (2, None)]
     assert spark.sql("select count(*) as n from t join names on names.kk = t.k").collect()[0].n == 20
+    # uncorrelated sub-queries are evaluated first
+    assert spark.sql("select * from t where id in (select id from t where id < 4)").count() == 4
     import pytest as _pytest
     with _pytest.raises(ValueError):
-        spark.sql("select * from t where id in (select id from t)")
+        spark.sql("select * from t where id > interval 1 day")
 
 
 def test_map_in_pandas_accepts_ddl_schema(spark_session):

@@ -273,3 +273,70 @@ def test_sql_uses_the_same_functions(spark, people):
     assert spark.sql("SELECT date_add('2020-02-27', 3) AS d, substring('Spark SQL', 5, 1) AS s, "
                      "array_contains(array(1, 2), 2) AS a").collect()[0].asDict() == \
         {"d": dt.date(2020, 3, 1), "s": "k", "a": True}
+
+
+@pytest.fixture(scope="module")
+def sales(spark):
+    df = spark.createDataFrame(
+        [("a", 1, 10.0, "2020-01-05"), ("a", 2, 20.0, "2020-02-01"), ("a", 2, None, "2021-01-01"),
+         ("b", 5, 1.0, "2020-01-09"), ("b", 3, 2.0, "2020-03-01"), (None, 9, 9.0, None)], ["k", "v", "x", "d"])
+    df.createOrReplaceTempView("sales")
+    return df
+
+
+def q(spark, text):
+    return [tuple(r) for r in spark.sql(text).collect()]
+
+
+def test_sql_grouping_having_order(spark, sales):
+    assert q(spark, "SELECT k, count(*) AS n FROM sales GROUP BY k HAVING count(*) > 1 ORDER BY sum(v) DESC") == \
+        [("b", 2), ("a", 3)]
+    assert q(spark, "SELECT year(d) AS y, sum(v) FROM sales GROUP BY year(d) ORDER BY y") == \
+        [(None, 9), (2020, 11), (2021, 2)]
+    assert q(spark, "SELECT k, sum(v) / count(*) AS m, round(avg(x), 1) FROM sales GROUP BY 1 ORDER BY 1 NULLS LAST") == \
+        [("a", 5 / 3, 15.0), ("b", 4.0, 1.5), (None, 9.0, 9.0)]
+    assert q(spark, "SELECT k, first(x, true), last(v) FROM sales WHERE k IS NOT NULL GROUP BY k ORDER BY k") == \
+        [("a", 10.0, 2), ("b", 1.0, 3)]
+    assert q(spark, "SELECT k, v FROM sales ORDER BY 2 DESC NULLS LAST LIMIT 2") == [(None, 9), ("b", 5)]
+
+
+def test_sql_predicates_and_operators(spark, sales):
+    assert q(spark, "SELECT v FROM sales WHERE k IN ('a') AND v BETWEEN 1 AND 2 AND d LIKE '2020%' AND x IS NOT NULL") == \
+        [(1,), (2,)]
+    assert q(spark, "SELECT cast(v AS string) || '_' || k AS s FROM sales WHERE v NOT IN (2, 9) AND d NOT LIKE '%-03-%'") == \
+        [("1_a",), ("5_b",)]
+    assert q(spark, "SELECT split(d, '-')[0] AS y, DATE '2020-01-01' AS dd FROM sales LIMIT 1") == \
+        [("2020", dt.date(2020, 1, 1))]
+    assert q(spark, "SELECT count(*) FROM sales WHERE k <=> NULL OR d RLIKE '^2021'") == [(2,)]
+    assert q(spark, "SELECT CASE WHEN v > 2 THEN 'hi' ELSE 'lo' END AS c, count(*) FROM sales GROUP BY 1 ORDER BY 1") == \
+        [("hi", 3), ("lo", 3)]
+
+
+def test_sql_subqueries_ctes_set_operations(spark, sales):
+    assert q(spark, "SELECT k, v FROM (SELECT k, v FROM sales WHERE v > 1) sub WHERE k = 'a'") == [("a", 2), ("a", 2)]
+    assert q(spark, "WITH big AS (SELECT * FROM sales WHERE v > 2), n AS (SELECT count(*) AS c FROM big) SELECT c FROM n") == [(3,)]
+    assert q(spark, "SELECT k, v FROM sales WHERE v = (SELECT max(v) FROM sales)") == [(None, 9)]
+    assert q(spark, "SELECT k, v FROM sales WHERE k IN (SELECT k FROM sales WHERE v > 4)") == [("b", 5), ("b", 3)]
+    assert q(spark, "SELECT k FROM sales UNION SELECT k FROM sales ORDER BY k") == [(None,), ("a",), ("b",)]
+    assert len(q(spark, "SELECT k FROM sales UNION ALL SELECT k FROM sales")) == 12
+    assert q(spark, "SELECT k FROM sales EXCEPT SELECT k FROM sales WHERE v > 2") == [("a",)]
+    assert q(spark, "SELECT k FROM sales INTERSECT SELECT k FROM sales WHERE v = 5") == [("b",)]
+    assert q(spark, "SELECT EXISTS (SELECT 1 FROM sales WHERE v > 100) AS e") == [(False,)]
+
+
+def test_sql_joins_with_aliases(spark, sales):
+    assert sorted(q(spark, "SELECT a.k, b.v FROM sales a JOIN sales b ON a.k = b.k WHERE a.v < b.v")) == \
+        [("a", 2), ("a", 2), ("b", 5)]
+    assert q(spark, "SELECT s.k, u.n FROM sales s LEFT JOIN (SELECT k, count(*) AS n FROM sales GROUP BY k) u "
+                    "ON s.k = u.k WHERE v = 1") == [("a", 3)]
+    assert q(spark, "SELECT count(*) FROM sales a, sales b") == [(36,)]
+
+
+def test_sql_window_clauses(spark, sales):
+    rows = q(spark, "SELECT k, v, row_number() OVER (PARTITION BY k ORDER BY v DESC) AS rn, "
+                    "sum(v) OVER (PARTITION BY k) AS tot, lag(v, 1) OVER (PARTITION BY k ORDER BY v DESC) AS p, "
+                    "sum(v) OVER (PARTITION BY k ORDER BY v DESC ROWS BETWEEN UNBOUNDED PRECEDING AND CURRENT ROW) AS r "
+                    "FROM sales WHERE k = 'a'")
+    assert rows == [("a", 2, 1, 5, None, 2), ("a", 2, 2, 5, 2, 4), ("a", 1, 3, 5, 2, 5)]
+    assert q(spark, "SELECT k, v FROM (SELECT k, v, rank() OVER (PARTITION BY k ORDER BY v DESC) AS r FROM sales) "
+                    "WHERE r = 1 AND k = 'b'") == [("b", 5)]
