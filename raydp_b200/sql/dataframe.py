@@ -949,17 +949,50 @@ class DataFrameWriter:
         os.makedirs(path, exist_ok=True)
         return path
 
-    def parquet(self, path: str, mode: Optional[str] = None, compression: Optional[str] = None) -> None:
+    def partitionBy(self, *cols) -> "DataFrameWriter":
+        cols = cols[0] if len(cols) == 1 and isinstance(cols[0], (list, tuple)) else cols
+        self._partition_by = list(cols)
+        return self
+
+    def bucketBy(self, numBuckets: int, col, *cols) -> "DataFrameWriter":
+        return self                                   # layout hint only
+
+    def sortBy(self, col, *cols) -> "DataFrameWriter":
+        return self
+
+    def options(self, **opts) -> "DataFrameWriter":
+        for k, v in opts.items():
+            self.option(k, v)
+        return self
+
+    def _write(self, fmt: str, path: str, mode: Optional[str], **extra) -> None:
         import os
         if mode:
             self.mode(mode)
         target = self._prepare(path)
         if target is None:
             return
-        compression = compression or self._options.get("compression")
-        self._df._run("write_parquet", {"path": target, "compression": compression,
-                                        "job": uuid.uuid4().hex[:8]})
+        args = {"path": target, "format": fmt, "job": uuid.uuid4().hex[:8],
+                "partition_by": getattr(self, "_partition_by", None)}
+        args.update({k: v for k, v in extra.items() if v is not None})
+        self._df._run("write_files", args)
         open(os.path.join(target, "_SUCCESS"), "w").close()
+
+    def parquet(self, path: str, mode: Optional[str] = None, partitionBy=None, compression: Optional[str] = None) -> None:
+        if partitionBy is not None:
+            self.partitionBy(partitionBy)
+        self._write("parquet", path, mode, compression=compression or self._options.get("compression"))
+
+    def orc(self, path: str, mode: Optional[str] = None, partitionBy=None, compression: Optional[str] = None) -> None:
+        if partitionBy is not None:
+            self.partitionBy(partitionBy)
+        self._write("orc", path, mode)
+
+    def json(self, path: str, mode: Optional[str] = None, **_kw) -> None:
+        self._write("json", path, mode)
+
+    def text(self, path: str, compression=None, lineSep=None) -> None:
+        self._write("text", path, None)
 
     def saveAsTable(self, name: str, format: Optional[str] = None, mode: Optional[str] = None, **_kw) -> None:  # noqa: A002
         """Persist as a parquet table under the warehouse directory (see ``sqlparser.Catalog``)."""
@@ -968,18 +1001,24 @@ class DataFrameWriter:
     def insertInto(self, name: str, overwrite: bool = False) -> None:
         self._df._session.catalog.save_table(self._df, name, "overwrite" if overwrite else "append")
 
-    def csv(self, path: str, mode: Optional[str] = None, header=None, **_kw) -> None:
-        import os
-        if mode:
-            self.mode(mode)
-        target = self._prepare(path)
-        if target is None:
-            return
+    def csv(self, path: str, mode: Optional[str] = None, header=None, sep=None, **_kw) -> None:
         hdr = header if header is not None else self._options.get("header", False)
         hdr = str(hdr).lower() == "true" if not isinstance(hdr, bool) else hdr
-        self._df._run("write_csv", {"path": target, "header": hdr, "job": uuid.uuid4().hex[:8]})
-        open(os.path.join(target, "_SUCCESS"), "w").close()
+        self._write("csv", path, mode, header=hdr, sep=sep or self._options.get("sep") or self._options.get("delimiter"))
 
-    def save(self, path: str) -> None:
-        fmt = self._options.get("__format", "parquet")
+    def save(self, path: Optional[str] = None, format: Optional[str] = None, mode: Optional[str] = None,  # noqa: A002
+             partitionBy=None, **options) -> None:
+        if format:
+            self.format(format)
+        if mode:
+            self.mode(mode)
+        if partitionBy is not None:
+            self.partitionBy(partitionBy)
+        self.options(**options)
+        path = path or self._options.get("path")
+        if path is None:
+            raise ValueError("save() needs a path")
+        fmt = str(self._options.get("__format", "parquet")).lower()
+        if fmt not in ("parquet", "orc", "csv", "json", "text"):
+            raise NotImplementedError(f"data source format {fmt!r} is not supported")
         getattr(self, fmt)(path)

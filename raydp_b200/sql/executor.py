@@ -88,6 +88,66 @@ def gather_by_index(grouped: pa.Table, index_col: str, source: pa.Table, cols: L
     return grouped
 
 
+def _write_one(table: pa.Table, directory: str, idx: int, args: Dict[str, Any]) -> None:
+    fmt = args["format"]
+    os.makedirs(directory, exist_ok=True)
+    stem = os.path.join(directory, f"part-{idx:05d}-{args['job']}")
+    if fmt == "parquet":
+        import pyarrow.parquet as pq
+        compression = args.get("compression") or "snappy"
+        pq.write_table(table, stem + ".parquet",
+                       compression=None if compression in ("none", "uncompressed") else compression)
+    elif fmt == "orc":
+        import pyarrow.orc as orc
+        orc.write_table(table, stem + ".orc")
+    elif fmt == "csv":
+        import pyarrow.csv as pacsv
+        pacsv.write_csv(table, stem + ".csv", pacsv.WriteOptions(include_header=bool(args.get("header", False)),
+                                                                 delimiter=args.get("sep", ",")))
+    elif fmt == "json":
+        import json as _json
+        from raydp_b200.sql.fnlib import _jsonable
+        names = table.column_names
+        cols = [c.to_pylist() for c in table.columns]
+        with open(stem + ".json", "w", encoding="utf-8") as fh:
+            for row in zip(*cols):
+                fh.write(_json.dumps({k: _jsonable(v) for k, v in zip(names, row) if v is not None},
+                                     separators=(",", ":")) + "\n")
+    elif fmt == "text":
+        if table.num_columns != 1 or not pa.types.is_string(table.schema.field(0).type):
+            raise ValueError("Text data source supports only a single string column")
+        with open(stem + ".txt", "w", encoding="utf-8") as fh:
+            for line in table.column(0).to_pylist():
+                fh.write(("" if line is None else line) + "\n")
+    else:
+        raise NotImplementedError(f"data source format {fmt!r} is not supported")
+
+
+def write_partition(table: pa.Table, idx: int, args: Dict[str, Any]) -> int:
+    """Write one partition under ``args["path"]``; with ``partition_by`` the rows go to
+    ``key=value/...`` sub-directories and the partition columns are left out of the files."""
+    keys: List[str] = list(args.get("partition_by") or [])
+    if not keys:
+        if table.num_rows or idx == 0:
+            _write_one(table, args["path"], idx, args)
+        return table.num_rows
+    if table.num_rows == 0:
+        return 0
+    groups = table.group_by(keys, use_threads=False).aggregate([])
+    key_cols = [table.column(k).combine_chunks() for k in keys]
+    for g in range(groups.num_rows):
+        mask = None
+        parts = []
+        for k, col in zip(keys, key_cols):
+            v = groups.column(k)[g]
+            hit = pc.is_null(col) if not v.is_valid else pc.fill_null(pc.equal(col, v), False)
+            mask = hit if mask is None else pc.and_(mask, hit)
+            parts.append(f"{k}={'__HIVE_DEFAULT_PARTITION__' if not v.is_valid else v.as_py()}")
+        piece = table.filter(mask).drop_columns(keys)
+        _write_one(piece, os.path.join(args["path"], *parts), idx, args)
+    return table.num_rows
+
+
 def execute_action(plan: Plan, idx: int, action: str, args: Dict[str, Any], blocks: Dict) -> Any:
     """Run one partition task.  Shared by executor actors and the in-process local backend."""
     if action == "load_block":
@@ -123,6 +183,8 @@ def execute_action(plan: Plan, idx: int, action: str, args: Dict[str, Any], bloc
         out = os.path.join(args["path"], f"part-{idx:05d}-{args['job']}.csv")
         pacsv.write_csv(table, out, pacsv.WriteOptions(include_header=args.get("header", False)))
         return table.num_rows
+    if action == "write_files":
+        return write_partition(table, idx, args)
     if action == "shuffle_map":
         from raydp_b200 import runtime
         n_out = args["n_out"]

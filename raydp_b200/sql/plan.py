@@ -163,11 +163,127 @@ class ParquetSource(Source):
 
     def load(self, idx: int) -> pa.Table:
         import pyarrow.parquet as pq
-        return pq.read_table(self.files[idx], columns=self.columns)
+        # the file alone: read_table() would also turn key=value directory names into columns
+        return pq.ParquetFile(self.files[idx]).read(columns=self.columns)
 
     def schema(self) -> pa.Schema:
         import pyarrow.parquet as pq
         return pq.read_schema(self.files[0])
+
+
+def partition_values(path: str, root: Optional[str] = None) -> List[Tuple[str, str]]:
+    """Hive-style partition directories in a file path: ``.../year=2020/month=1/part-0.parquet``."""
+    rel = os.path.relpath(path, root) if root else path
+    out = []
+    for part in os.path.dirname(rel).split(os.sep):
+        if "=" in part and not part.startswith(("_", ".")):
+            k, _, v = part.partition("=")
+            out.append((k, v))
+    return out
+
+
+def _typed_partition_column(values: List[Optional[str]]) -> pa.Array:
+    """Partition values are text in the path; ints and floats are recognised like Spark's inference does."""
+    live = [v for v in values if v is not None]
+    for caster, arrow_type in ((int, pa.int32()), (float, pa.float64())):
+        try:
+            converted = [None if v is None else caster(v) for v in values]
+            if arrow_type == pa.int32() and any(abs(x) >= 2 ** 31 for x in converted if x is not None):
+                arrow_type = pa.int64()
+            if live:
+                return pa.array(converted, type=arrow_type)
+        except ValueError:
+            continue
+    return pa.array(values, type=pa.string())
+
+
+class FileSource(Source):
+    """One partition per file for the line / columnar formats: ``parquet``, ``orc``, ``json`` (one object
+    per line), ``text``.  Columns encoded in the directory names (``key=value``) are appended."""
+
+    def __init__(self, files: List[str], fmt: str, root: Optional[str] = None,
+                 schema: Optional[T.StructType] = None, options: Optional[Dict[str, str]] = None):
+        self.files, self.fmt, self.root = files, fmt, root
+        self.user_schema = schema
+        self.options = dict(options or {})
+        self.num_partitions = max(1, len(files))
+        self._cached_schema: Optional[pa.Schema] = None
+        keys: List[str] = []
+        for f in files:
+            for k, _ in partition_values(f, root):
+                if k not in keys:
+                    keys.append(k)
+        self.partition_keys = keys
+        self._partition_types: Dict[str, pa.DataType] = {}
+        for k in keys:
+            vals = [dict(partition_values(f, root)).get(k) for f in files]
+            vals = [None if v == "__HIVE_DEFAULT_PARTITION__" else v for v in vals]
+            self._partition_types[k] = _typed_partition_column(vals).type
+
+    def _read(self, path: str) -> pa.Table:
+        if self.fmt == "parquet":
+            import pyarrow.parquet as pq
+            return pq.ParquetFile(path).read()       # the file alone: partition columns are added below
+        if self.fmt == "orc":
+            import pyarrow.orc as orc
+            return orc.read_table(path)
+        if self.fmt == "json":
+            import pyarrow.json as pajson
+            explicit = None
+            if self.user_schema is not None:
+                explicit = pa.schema([(f.name, f.dataType.arrow) for f in self.user_schema
+                                      if f.name not in self.partition_keys])
+            if os.path.getsize(path) == 0:
+                return (explicit or pa.schema([])).empty_table()
+            table = pajson.read_json(path, parse_options=pajson.ParseOptions(
+                explicit_schema=explicit, unexpected_field_behavior="ignore" if explicit is not None else "infer"))
+            return _infer_timestamps(table) if explicit is None else table
+        if self.fmt == "text":
+            with open(path, "r", encoding="utf-8") as fh:
+                if str(self.options.get("wholetext", "false")).lower() == "true":
+                    lines = [fh.read()]
+                else:
+                    lines = fh.read().splitlines()
+            return pa.table({"value": pa.array(lines, type=pa.string())})
+        raise NotImplementedError(f"data source format {self.fmt!r} is not supported")
+
+    def load(self, idx: int) -> pa.Table:
+        if not self.files:
+            return self.schema().empty_table()
+        path = self.files[idx]
+        table = self._read(path)
+        if self.fmt == "json" and self.user_schema is None and len(self.files) > 1:
+            # objects omit null fields, so files can disagree on the columns: align to the union
+            if getattr(self, "_json_schema", None) is None:
+                self._json_schema = pa.unify_schemas([self._read(f).schema for f in self.files],
+                                                     promote_options="permissive")
+            cols = [table.column(f.name).cast(f.type) if f.name in table.column_names
+                    else pa.nulls(table.num_rows, f.type) for f in self._json_schema]
+            table = pa.table(cols, names=self._json_schema.names)
+        if self.user_schema is not None and self.fmt != "json":
+            wanted = [f for f in self.user_schema if f.name not in self.partition_keys]
+            table = table.select([f.name for f in wanted]).cast(
+                pa.schema([(f.name, f.dataType.arrow) for f in wanted]), safe=False)
+        found = dict(partition_values(path, self.root))
+        for k in self.partition_keys:
+            v = found.get(k)
+            v = None if v == "__HIVE_DEFAULT_PARTITION__" else v
+            t = self._partition_types[k]
+            value = None if v is None else (int(v) if pa.types.is_integer(t) else float(v) if pa.types.is_floating(t) else v)
+            column = pa.array([value] * table.num_rows, type=t)
+            if k in table.column_names:
+                table = table.set_column(table.column_names.index(k), k, column)
+            else:
+                table = table.append_column(k, column)
+        return table
+
+    def schema(self) -> pa.Schema:
+        if self._cached_schema is None:
+            if not self.files:
+                self._cached_schema = self.user_schema.to_arrow_schema() if self.user_schema is not None else pa.schema([])
+            else:
+                self._cached_schema = self.load(0).schema
+        return self._cached_schema
 
 
 class FuncSource(Source):

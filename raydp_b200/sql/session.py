@@ -107,6 +107,102 @@ class SparkContext:
     def stop(self) -> None:
         self._session.stop()
 
+    @property
+    def version(self) -> str:
+        return self._session.version
+
+    @property
+    def defaultMinPartitions(self) -> int:
+        return min(self.defaultParallelism, 2)
+
+    @classmethod
+    def getOrCreate(cls, conf: Optional[SparkConf] = None) -> "SparkContext":
+        builder = SparkSession.builder
+        if conf is not None:
+            builder = builder.config(conf=conf)
+        return builder.getOrCreate().sparkContext
+
+    def range(self, start: int, end: Optional[int] = None, step: int = 1, numSlices: Optional[int] = None):  # noqa: A003
+        if end is None:
+            start, end = 0, start
+        return self.parallelize(range(start, end, step), numSlices)
+
+    def emptyRDD(self):
+        from raydp_b200.sql.rdd import RDD
+        return RDD(self._session, [[]])
+
+    def union(self, rdds):
+        from raydp_b200.sql.rdd import RDD
+        return RDD(self._session, [p for r in rdds for p in r._collect_partitions()])
+
+    def textFile(self, name: str, minPartitions: Optional[int] = None, use_unicode: bool = True):
+        """One element per line; a directory or glob reads every file (one partition per file)."""
+        from raydp_b200.sql.plan import list_data_files
+        from raydp_b200.sql.rdd import RDD
+        parts = []
+        for path in list_data_files(name, ()):
+            with open(path, "r", encoding="utf-8") as fh:
+                parts.append(fh.read().splitlines())
+        return RDD(self._session, parts or [[]])
+
+    def wholeTextFiles(self, path: str, minPartitions: Optional[int] = None, use_unicode: bool = True):
+        from raydp_b200.sql.plan import list_data_files
+        from raydp_b200.sql.rdd import RDD
+        parts = []
+        for f in list_data_files(path, ()):
+            with open(f, "r", encoding="utf-8") as fh:
+                parts.append([("file:" + f, fh.read())])
+        return RDD(self._session, parts or [[]])
+
+    def pickleFile(self, name: str, minPartitions: Optional[int] = None):
+        import pickle
+        from raydp_b200.sql.plan import list_data_files
+        from raydp_b200.sql.rdd import RDD
+        parts = []
+        for f in list_data_files(name, ()):
+            with open(f, "rb") as fh:
+                parts.append(pickle.load(fh))
+        return RDD(self._session, parts or [[]])
+
+    def broadcast(self, value) -> "Broadcast":
+        return Broadcast(value)
+
+    def accumulator(self, value, accum_param=None) -> "Accumulator":
+        return Accumulator(value)
+
+    def addPyFile(self, path: str) -> None:
+        import sys as _sys
+        target = os.path.dirname(os.path.abspath(path)) if path.endswith(".py") else os.path.abspath(path)
+        if target not in _sys.path:
+            _sys.path.insert(0, target)
+
+    def addFile(self, path: str, recursive: bool = False) -> None:
+        self._session._conf.set("spark.files", ",".join(filter(None, [self._session._conf.get("spark.files"), path])))
+
+    def setJobGroup(self, groupId: str, description: str, interruptOnCancel: bool = False) -> None:
+        self._session._conf.set("spark.jobGroup.id", groupId)
+
+    def setJobDescription(self, value: str) -> None:
+        self._session._conf.set("spark.job.description", value)
+
+    def setLocalProperty(self, key: str, value: str) -> None:
+        self._session._conf.set(key, value)
+
+    def getLocalProperty(self, key: str) -> Optional[str]:
+        return self._session._conf.get(key)
+
+    def setCheckpointDir(self, dirName: str) -> None:
+        self._session._conf.set("spark.checkpoint.dir", dirName)
+
+    def cancelAllJobs(self) -> None:
+        pass
+
+    def cancelJobGroup(self, groupId: str) -> None:
+        pass
+
+    def statusTracker(self):
+        return None
+
     # ---- the two py4j handles test code written against PySpark reaches for.  There is no JVM: they
     # answer the questions such code asks (force a GC; which recoverable RDDs are still pinned).
     @property
@@ -116,6 +212,62 @@ class SparkContext:
     @property
     def _jsc(self):
         return _JscStandIn(self._session)
+
+
+class Broadcast:
+    """``sc.broadcast(v)``: closures capture the wrapper and read ``.value`` on the executors (the value
+    travels with the pickled closure; there is no separate torrent distribution to manage)."""
+
+    def __init__(self, value):
+        self._value = value
+
+    @property
+    def value(self):
+        return self._value
+
+    def unpersist(self, blocking: bool = False) -> None:
+        pass
+
+    def destroy(self, blocking: bool = False) -> None:
+        self._value = None
+
+
+class Accumulator:
+    """Driver-side accumulator: ``+=`` / ``add`` from driver code (and from executors that run in this
+    process); updates made in remote executor processes are not shipped back."""
+
+    def __init__(self, value):
+        self.value = value
+
+    def add(self, term) -> None:
+        self.value += term
+
+    def __iadd__(self, term):
+        self.add(term)
+        return self
+
+    def __repr__(self):
+        return str(self.value)
+
+
+class UDFRegistration:
+    """``spark.udf.register(name, f, returnType)``: the function becomes callable from SQL text."""
+
+    def __init__(self, session: "SparkSession"):
+        self._session = session
+
+    def register(self, name: str, f, returnType=None):
+        from raydp_b200.sql import functions as F
+        if isinstance(f, F.UserDefinedFunction):
+            udf = f if returnType is None else F.UserDefinedFunction(f.func, returnType, f.vectorized)
+        else:
+            udf = F.UserDefinedFunction(f, returnType if returnType is not None else T.StringType())
+        self._session._registered_udfs[name] = udf
+        self._session._registered_udfs[name.lower()] = udf
+        return udf
+
+    def registerJavaFunction(self, name: str, javaClassName: str, returnType=None) -> None:
+        raise NotImplementedError("there is no JVM in raydp_b200; register a Python function instead")
 
 
 class _JvmStandIn:
@@ -183,15 +335,41 @@ class DataFrameReader:
         self._schema = schema
         return self
 
-    def load(self, path: Optional[str] = None, format: Optional[str] = None, **opts) -> DataFrame:  # noqa: A002
+    def load(self, path: Optional[str] = None, format: Optional[str] = None, schema=None, **opts) -> DataFrame:  # noqa: A002
         if format:
             self.format(format)
+        if schema is not None:
+            self.schema(schema)
         self.options(**opts)
-        if self._format == "csv":
-            return self.csv(path)
-        if self._format == "parquet":
-            return self.parquet(path)
+        path = path or self._options.get("path")
+        if self._format in ("csv", "parquet", "orc", "json", "text"):
+            paths = [path] if isinstance(path, str) else list(path)
+            return getattr(self, self._format)(*paths) if self._format != "csv" else self.csv(paths)
         raise NotImplementedError(f"data source format {self._format!r} is not supported")
+
+    def _files(self, fmt: str, paths, suffixes) -> DataFrame:
+        import os
+        from raydp_b200.sql.plan import FileSource, strip_scheme
+        flat = [q for p in paths for q in (p if isinstance(p, (list, tuple)) else [p])]
+        files = [f for p in flat for f in list_data_files(p, suffixes)]
+        root = strip_scheme(flat[0]) if len(flat) == 1 and os.path.isdir(strip_scheme(flat[0])) else None
+        base = self._options.get("basepath")
+        return DataFrame(self._session, Plan(FileSource(files, fmt, strip_scheme(base) if base else root,
+                                                        self._schema, self._options)))
+
+    def json(self, *paths, schema=None, **opts) -> DataFrame:
+        if schema is not None:
+            self.schema(schema)
+        self.options(**opts)
+        return self._files("json", paths, ())
+
+    def orc(self, *paths, **opts) -> DataFrame:
+        self.options(**opts)
+        return self._files("orc", paths, (".orc",))
+
+    def text(self, *paths, wholetext: bool = False, **opts) -> DataFrame:
+        self.option("wholetext", wholetext)
+        return self._files("text", paths, ())
 
     def _flag(self, key: str, default: bool = False) -> bool:
         return str(self._options.get(key.lower(), default)).lower() == "true"
@@ -212,8 +390,15 @@ class DataFrameReader:
         src = CsvSource(files, self._flag("header"), self._flag("inferschema"), delim, self._schema)
         return DataFrame(self._session, Plan(src))
 
-    def parquet(self, *paths: str) -> DataFrame:
-        files = [f for p in paths for f in list_data_files(p, (".parquet",))]
+    def parquet(self, *paths: str, **opts) -> DataFrame:
+        import os
+        from raydp_b200.sql.plan import partition_values, strip_scheme
+        self.options(**opts)
+        flat = [q for p in paths for q in (p if isinstance(p, (list, tuple)) else [p])]
+        files = [f for p in flat for f in list_data_files(p, (".parquet",))]
+        root = strip_scheme(flat[0]) if len(flat) == 1 and os.path.isdir(strip_scheme(flat[0])) else None
+        if self._schema is not None or any(partition_values(f, root) for f in files):
+            return self._files("parquet", paths, (".parquet",))      # partition columns come from the paths
         return DataFrame(self._session, Plan(ParquetSource(files)))
 
     def table(self, name: str):
@@ -309,11 +494,28 @@ class SparkSession:
         self.sparkContext = SparkContext(self)
         self.conf = RuntimeConfig(self._conf)
         self.version = "3.5.0-raydp-b200"
+        self._registered_udfs: Dict[str, Any] = {}
+        self.udf = UDFRegistration(self)
 
     # ------------------------------------------------------------------ factories
     @classmethod
     def getActiveSession(cls) -> Optional["SparkSession"]:
         return _active_session if _active_session is not None and not _active_session._stopped else None
+
+    @classmethod
+    def active(cls) -> "SparkSession":
+        session = cls.getActiveSession()
+        if session is None:
+            raise RuntimeError("No active or default Spark session found")
+        return session
+
+    @property
+    def streams(self):
+        raise NotImplementedError("structured streaming is not part of the built-in engine")
+
+    @property
+    def readStream(self):
+        raise NotImplementedError("structured streaming is not part of the built-in engine")
 
     @property
     def _jvm(self):

@@ -307,8 +307,37 @@ class Row(tuple):
         row.__fields__ = list(fields)
         return row
 
-    def asDict(self) -> dict:
-        return dict(zip(self.__fields__ or [], self))
+    def asDict(self, recursive: bool = False) -> dict:
+        if not recursive:
+            return dict(zip(self.__fields__ or [], self))
+
+        def conv(v):
+            if isinstance(v, Row):
+                return v.asDict(True)
+            if isinstance(v, list):
+                return [conv(x) for x in v]
+            if isinstance(v, dict):
+                return {k: conv(x) for k, x in v.items()}
+            return v
+        return {k: conv(v) for k, v in zip(self.__fields__ or [], self)}
+
+    def __call__(self, *values) -> "Row":
+        """``Person = Row("name", "age"); Person("Alice", 11)``: a Row of names is a row factory."""
+        if self.__fields__ is not None:
+            raise TypeError("only a Row created from field names can be called")
+        if len(values) > len(self):
+            raise ValueError(f"Can not create Row with fields {tuple(self)}, expected {len(self)} values but got {values}")
+        return Row._make([str(f) for f in self], values)
+
+    def __contains__(self, item) -> bool:
+        if self.__fields__ is not None:
+            return item in self.__fields__
+        return tuple.__contains__(self, item)
+
+    def __reduce__(self):
+        if self.__fields__ is None:
+            return (Row, tuple(self))
+        return (Row._make, (list(self.__fields__), tuple(self)))
 
     def __getattr__(self, item):
         fields = self.__dict__.get("__fields__")

@@ -14,10 +14,8 @@ from raydp_b200.sql.window import Window
 
 
 @pytest.fixture(scope="module")
-def spark():
-    session = SparkSession.builder.master("local[2]").appName("fn-surface").getOrCreate()
-    yield session
-    session.stop()
+def spark(spark_session):
+    return spark_session
 
 
 @pytest.fixture(scope="module")

@@ -1,0 +1,110 @@
+"""Data sources (parquet / orc / json / csv / text, ``partitionBy`` + partition discovery), the RDD surface,
+SparkContext helpers and ``spark.udf.register``."""
+import os
+
+import pytest
+
+from raydp_b200.sql import functions as F
+from raydp_b200.sql.session import SparkSession
+from raydp_b200.sql.types import Row
+
+
+@pytest.fixture(scope="module")
+def spark(spark_session):
+    return spark_session
+
+
+@pytest.fixture(scope="module")
+def df(spark):
+    return spark.createDataFrame([("a", 1, 10.0), ("a", 2, 20.0), ("b", 5, None), (None, 9, 9.0)], ["k", "v", "x"])
+
+
+def rows(frame, key="v"):
+    return sorted((tuple(r) for r in frame.collect()), key=repr)
+
+
+def test_partitioned_parquet_round_trip(spark, df, tmp_path):
+    target = str(tmp_path / "p")
+    df.write.partitionBy("k").parquet(target)
+    assert sorted(os.listdir(target)) == ["_SUCCESS", "k=__HIVE_DEFAULT_PARTITION__", "k=a", "k=b"]
+    back = spark.read.parquet(target)
+    assert back.columns == ["v", "x", "k"]                       # partition columns come last, as in Spark
+    assert rows(back) == rows(df.select("v", "x", "k"))
+    assert rows(spark.read.parquet(os.path.join(target, "k=a"))) == [(1, 10.0), (2, 20.0)]
+    assert back.filter("k = 'b'").count() == 1
+    with pytest.raises(FileExistsError):
+        df.write.parquet(target)
+    df.write.mode("append").partitionBy("k").parquet(target)
+    assert spark.read.parquet(target).count() == 8
+
+
+def test_json_text_orc_csv_round_trips(spark, df, tmp_path):
+    df.write.json(str(tmp_path / "j"))
+    first = sorted(f for f in os.listdir(tmp_path / "j") if f.endswith(".json"))[0]
+    assert open(tmp_path / "j" / first).read().splitlines()[0] == '{"k":"a","v":1,"x":10.0}'
+    assert rows(spark.read.json(str(tmp_path / "j")).select("k", "v", "x")) == rows(df)
+    typed = spark.read.schema("v int, k string").json(str(tmp_path / "j"))
+    assert typed.dtypes == [("v", "int"), ("k", "string")] and typed.count() == 4
+    df.select("k").fillna("?").write.text(str(tmp_path / "t"))
+    assert sorted(r.value for r in spark.read.text(str(tmp_path / "t")).collect()) == ["?", "a", "a", "b"]
+    df.write.format("orc").mode("overwrite").save(str(tmp_path / "o"))
+    assert rows(spark.read.format("orc").load(str(tmp_path / "o"))) == rows(df)
+    df.write.option("header", True).csv(str(tmp_path / "c"))
+    back = spark.read.option("header", True).option("inferSchema", True).csv(str(tmp_path / "c"))
+    assert back.columns == ["k", "v", "x"] and back.count() == 4
+    df.write.partitionBy("k", "v").format("json").save(str(tmp_path / "pj"))
+    nested = spark.read.json(str(tmp_path / "pj"))
+    assert set(nested.columns) == {"x", "k", "v"} and rows(nested.select("k", "v", "x")) == rows(df)
+    assert dict(nested.dtypes)["v"] == "int"                       # inferred from the directory names
+
+
+def test_rdd_surface(spark):
+    sc = spark.sparkContext
+    r = sc.parallelize(range(10), 3)
+    assert r.map(lambda x: x * 2).filter(lambda x: x % 3 == 0).collect() == [0, 6, 12, 18]
+    assert (r.reduce(lambda a, b: a + b), r.sum(), r.max(), r.min(), r.mean(), r.count()) == (45, 45, 9, 0, 4.5, 10)
+    assert r.take(3) == [0, 1, 2] and r.first() == 0 and r.top(2) == [9, 8] and r.takeOrdered(2, key=lambda x: -x) == [9, 8]
+    assert r.glom().collect() == [[0, 1, 2, 3], [4, 5, 6], [7, 8, 9]]
+    assert r.aggregate((0, 0), lambda a, x: (a[0] + x, a[1] + 1), lambda a, b: (a[0] + b[0], a[1] + b[1])) == (45, 10)
+    assert r.fold(0, lambda a, b: a + b) == 45 and r.zipWithIndex().take(2) == [(0, 0), (1, 1)]
+    assert r.union(r).distinct().count() == 10 and r.subtract(sc.parallelize([0, 1])).count() == 8
+    assert r.sortBy(lambda x: -x).take(2) == [9, 8] and r.keyBy(lambda x: x % 2).countByKey() == {0: 5, 1: 5}
+    kv = sc.parallelize([("a", 1), ("b", 2), ("a", 3)])
+    assert sorted(kv.reduceByKey(lambda a, b: a + b).collect()) == [("a", 4), ("b", 2)]
+    assert sorted(kv.groupByKey().mapValues(list).collect()) == [("a", [1, 3]), ("b", [2])]
+    assert kv.join(sc.parallelize([("a", "x")])).collect() == [("a", (1, "x")), ("a", (3, "x"))]
+    assert sorted(kv.leftOuterJoin(sc.parallelize([("a", "x")])).collect())[-1] == ("b", (2, None))
+    assert kv.collectAsMap() == {"a": 3, "b": 2} and kv.keys().collect() == ["a", "b", "a"]
+    assert sorted(kv.combineByKey(lambda v: [v], lambda c, v: c + [v], lambda a, b: a + b).collect()) == \
+        [("a", [1, 3]), ("b", [2])]
+    frame = spark.createDataFrame(kv.map(lambda t: Row(k=t[0], v=t[1])))
+    assert frame.columns == ["k", "v"] and frame.count() == 3
+    ids = spark.range(5).rdd
+    assert ids.map(lambda row: row.id * 2).collect() == [0, 2, 4, 6, 8] and ids.first() == Row(id=0)
+    assert ids.zipWithIndex().take(1) == [(Row(id=0), 0)]
+
+
+def test_spark_context_helpers_and_udf_registration(spark, tmp_path):
+    sc = spark.sparkContext
+    sc.parallelize(["a b", "c"], 2).saveAsTextFile(str(tmp_path / "t"))
+    assert sc.textFile(str(tmp_path / "t")).flatMap(str.split).collect() == ["a", "b", "c"]
+    assert sc.range(3).collect() == [0, 1, 2] and sc.emptyRDD().isEmpty() and sc.version == spark.version
+    lookup = sc.broadcast({0: "zero"})
+    assert spark.range(2).rdd.map(lambda r: lookup.value.get(r.id)).collect() == ["zero", None]
+    acc = sc.accumulator(0)
+    acc += 5
+    acc.add(2)
+    assert acc.value == 7
+    spark.udf.register("plus_one", lambda x: x + 1, "int")
+    spark.range(3).createOrReplaceTempView("r_udf")
+    assert [r.p for r in spark.sql("select plus_one(id) as p from r_udf").collect()] == [1, 2, 3]
+    assert SparkSession.active() is spark
+
+
+def test_rows_and_nested_schemas(spark):
+    person = Row("name", "age")
+    assert person("Al", 3) == Row(name="Al", age=3) and person("Al", 3).asDict() == {"name": "Al", "age": 3}
+    assert Row(a=1, b=Row(c=2)).asDict(True) == {"a": 1, "b": {"c": 2}} and "a" in Row(a=1)
+    nested = spark.createDataFrame([(1, [1, 2], {"k": 1.5})], "id int, xs array<int>, m map<string,double>")
+    assert nested.dtypes == [("id", "int"), ("xs", "array<int>"), ("m", "map<string,double>")]
+    assert nested.select(F.col("m")["k"].alias("v"), F.size("xs").alias("n")).collect()[0] == Row(v=1.5, n=2)
