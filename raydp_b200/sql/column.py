@@ -265,7 +265,7 @@ class Column:
             arrays = [c.evaluate(table, ctx) for c in arg_cols]
             nps = [np.asarray(_to_array(x, n)) if _is_arrayish(x) else np.full(n, x.as_py())
                    for x in arrays]
-            return pa.array(np.asarray(func(*nps)), type=rtype.arrow)
+            return pa.array(np.asarray(func(*nps)), type=rtype.arrow, from_pandas=True)
         if k == "sort":
             return a[0].evaluate(table, ctx)
         if k == "hof":

@@ -343,8 +343,16 @@ class DataFrame(DataFrameExtras):
         how = how.lower()
         if on is None or how == "cross":
             return self.crossJoin(other)
+        if isinstance(on, (list, tuple)) and on and all(isinstance(c, Column) and c._kind != "col" for c in on):
+            combined = on[0]
+            for c in on[1:]:
+                combined = combined & c
+            on = combined
         if isinstance(on, Column):
-            pairs = _equi_join_pairs(on)
+            try:
+                pairs = _equi_join_pairs(on)
+            except NotImplementedError:
+                return self._theta_join(other, on, how)
             keys, right_keys = [p[0] for p in pairs], [p[1] for p in pairs]
         else:
             keys = [on] if isinstance(on, str) else [k if isinstance(k, str) else k._output_name() for k in on]
@@ -355,6 +363,33 @@ class DataFrame(DataFrameExtras):
         right = other._collect_table()
         how = {"rightouter": "right_outer", "fullouter": "full_outer"}.get(how, how)
         return left._derive(("join", right, keys, how, right_keys))
+
+    def _theta_join(self, other: "DataFrame", condition: Column, how: str) -> "DataFrame":
+        """A join on an arbitrary predicate (``a.x > b.y``, ranges, mixed conditions): the pairs are formed
+        by a cross join and filtered; outer variants add back the rows that found no partner."""
+        from raydp_b200.sql import functions as F
+        how = {"leftouter": "left", "left_outer": "left", "leftsemi": "left_semi", "leftanti": "left_anti",
+               "semi": "left_semi", "anti": "left_anti"}.get(how, how)
+        if how not in ("inner", "left", "left_semi", "left_anti"):
+            raise NotImplementedError(f"{how} joins need equality conditions; a non-equality predicate is supported "
+                                      "for inner, left, left_semi and left_anti joins")
+        clash = [c for c in other.columns if c in self.columns]
+        if clash:
+            raise ValueError(f"both sides of a non-equality join have columns {clash}: rename one side first")
+        tagged = self.withColumn("__lid", F.monotonically_increasing_id())
+        matched = tagged.crossJoin(other).filter(condition)
+        if how == "inner":
+            return matched.drop("__lid")
+        hit_ids = [r[0] for r in matched.select("__lid").distinct().collect()]
+        if how == "left_semi":
+            return tagged.filter(F.col("__lid").isin(hit_ids)).drop("__lid")
+        lonely = tagged.filter(~F.col("__lid").isin(hit_ids)) if hit_ids else tagged
+        if how == "left_anti":
+            return lonely.drop("__lid")
+        right_schema = other._arrow_schema()
+        for f in right_schema:
+            lonely = lonely.withColumn(f.name, F.lit(None).cast(T.from_arrow_type(f.type)))
+        return matched.union(lonely.select(*matched.columns)).drop("__lid")
 
     def crossJoin(self, other: "DataFrame") -> "DataFrame":
         from raydp_b200.sql import functions as F
@@ -453,7 +488,21 @@ class DataFrame(DataFrameExtras):
         more = table.num_rows > n
         table = table.slice(0, n)
         names = table.column_names
-        cells = [[_fmt(v, truncate) for v in c.to_pylist()] for c in table.columns]
+        if isinstance(truncate, int) and not isinstance(truncate, bool) and truncate > 0:
+            limit_chars = truncate
+            cells = [[(lambda t: t[:limit_chars - 3] + "..." if len(t) > limit_chars > 3 else t[:limit_chars])(
+                _fmt(v, False)) for v in c.to_pylist()] for c in table.columns]
+        else:
+            cells = [[_fmt(v, bool(truncate)) for v in c.to_pylist()] for c in table.columns]
+        if vertical:
+            width = max([len(nm) for nm in names] + [1])
+            for i in range(table.num_rows):
+                print(f"-RECORD {i}" + "-" * 20)
+                for nm, col in zip(names, cells):
+                    print(f" {nm.ljust(width)} | {col[i]}")
+            if more:
+                print(f"only showing top {n} row{'s' if n != 1 else ''}")
+            return
         widths = [max([len(nm)] + [len(v) for v in col]) for nm, col in zip(names, cells)]
         line = "+" + "+".join("-" * w for w in widths) + "+"
         print(line)

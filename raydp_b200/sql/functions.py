@@ -572,7 +572,35 @@ def vectorized_udf(returnType=T.DoubleType()):
     return lambda fn: UserDefinedFunction(fn, returnType, vectorized=True)
 
 
-pandas_udf = vectorized_udf
+class PandasUDFType:
+    SCALAR, SCALAR_ITER, GROUPED_MAP, GROUPED_AGG = 200, 204, 201, 202
+
+
+def pandas_udf(f=None, returnType=None, functionType=None):
+    """``@pandas_udf("double")``, ``@pandas_udf(returnType=...)`` and ``pandas_udf(fn, "double")``: the
+    function gets one ``pandas.Series`` per argument column (a whole partition at a time) and returns a
+    Series / array of the same length."""
+    if callable(f) and not isinstance(f, T.DataType):
+        return UserDefinedFunction(_series_adapter(f), returnType if returnType is not None else T.DoubleType(),
+                                   vectorized=True)
+    rtype = f if f is not None else returnType
+    return lambda fn: UserDefinedFunction(_series_adapter(fn), rtype if rtype is not None else T.DoubleType(),
+                                          vectorized=True)
+
+
+def _series_adapter(fn: Callable) -> Callable:
+    def call(*arrays):
+        import numpy as np
+        import pandas as pd
+        out = fn(*[pd.Series(a) for a in arrays])
+        if isinstance(out, pd.Series):
+            if out.dtype == object or str(out.dtype) in ("string", "str"):
+                return np.array([None if v is None or v is pd.NA or (isinstance(v, float) and v != v) else v
+                                 for v in out], dtype=object)
+            return out.to_numpy()
+        return np.asarray(out)
+    call.__name__ = getattr(fn, "__name__", "pandas_udf")
+    return call
 
 
 def expr(text: str) -> Column:

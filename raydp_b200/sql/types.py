@@ -31,6 +31,17 @@ class DataType:
     def __repr__(self):
         return f"{type(self).__name__}()"
 
+    def jsonValue(self):
+        return self.simpleString() if type(self).__name__ not in _JSON_NAMES else _JSON_NAMES[type(self).__name__]
+
+    def json(self) -> str:
+        import json as _json
+        return _json.dumps(self.jsonValue(), separators=(",", ":"), sort_keys=True)
+
+
+_JSON_NAMES = {"LongType": "long", "IntegerType": "integer", "ShortType": "short", "ByteType": "byte",
+               "NullType": "void"}
+
 
 def _simple(cls_name: str, arrow_type: pa.DataType, simple: str):
     return type(cls_name, (DataType,), {"arrow": arrow_type, "name": simple})
@@ -64,6 +75,9 @@ class ArrayType(DataType):
     def simpleString(self):
         return f"array<{self.elementType.simpleString()}>"
 
+    def jsonValue(self):
+        return {"type": "array", "elementType": self.elementType.jsonValue(), "containsNull": self.containsNull}
+
 
 class MapType(DataType):
     name = "map"
@@ -79,6 +93,10 @@ class MapType(DataType):
 
     def simpleString(self):
         return f"map<{self.keyType.simpleString()},{self.valueType.simpleString()}>"
+
+    def jsonValue(self):
+        return {"type": "map", "keyType": self.keyType.jsonValue(), "valueType": self.valueType.jsonValue(),
+                "valueContainsNull": self.valueContainsNull}
 
     def __repr__(self):
         return f"MapType({self.keyType!r}, {self.valueType!r}, {self.valueContainsNull})"
@@ -128,8 +146,19 @@ class StructType(DataType):
         if isinstance(field, StructField):
             self.fields.append(field)
         else:
-            self.fields.append(StructField(field, data_type or StringType(), nullable))
+            self.fields.append(StructField(field, parse_type(data_type) if data_type is not None else StringType(),
+                                           nullable))
         return self
+
+    def jsonValue(self):
+        return {"type": "struct", "fields": [
+            {"name": f.name, "type": f.dataType.jsonValue(), "nullable": f.nullable, "metadata": f.metadata}
+            for f in self.fields]}
+
+    @classmethod
+    def fromJson(cls, json: dict) -> "StructType":  # noqa: A002
+        return cls([StructField(f["name"], _type_from_json(f["type"]), f.get("nullable", True), f.get("metadata"))
+                    for f in json["fields"]])
 
     @property
     def names(self) -> List[str]:
@@ -172,8 +201,22 @@ _BY_NAME = {
     "smallint": ShortType, "short": ShortType, "int": IntegerType, "integer": IntegerType,
     "bigint": LongType, "long": LongType, "float": FloatType, "double": DoubleType,
     "string": StringType, "str": StringType, "binary": BinaryType, "date": DateType,
-    "timestamp": TimestampType,
+    "timestamp": TimestampType, "void": NullType, "null": NullType, "timestamp_ntz": TimestampType,
 }
+
+
+def _type_from_json(value) -> DataType:
+    if isinstance(value, dict):
+        kind = value.get("type")
+        if kind == "struct":
+            return StructType.fromJson(value)
+        if kind == "array":
+            return ArrayType(_type_from_json(value["elementType"]), value.get("containsNull", True))
+        if kind == "map":
+            return MapType(_type_from_json(value["keyType"]), _type_from_json(value["valueType"]),
+                           value.get("valueContainsNull", True))
+        raise ValueError(f"unsupported type json: {value!r}")
+    return parse_type(value)
 
 
 def parse_type(spec: Union[str, DataType, pa.DataType]) -> DataType:

@@ -266,3 +266,27 @@ def test_spark_defaults_conf_is_loaded_with_user_precedence(ray_cluster, tmp_pat
         assert conf.get("not.spark.key", "absent") == "absent"
     finally:
         raydp.stop_spark()
+
+
+def test_wider_sql_surface_runs_on_executors(spark_on_ray_2_executors, tmp_path):
+    """Gathered aggregates, higher-order functions, windows, partitioned writes and SQL text through the
+    executor actors (expressions are pickled to the executors; the function library is imported there)."""
+    from raydp_b200.sql import functions as F
+    from raydp_b200.sql.window import Window
+    spark = spark_on_ray_2_executors
+    df = spark.createDataFrame([("a", 1, [1, 2]), ("a", 2, [3]), ("b", 5, []), (None, 9, None)],
+                               ["k", "v", "xs"]).repartition(2)
+    agg = df.groupBy("k").agg(F.collect_list("v").alias("l"), F.percentile_approx("v", 0.5).alias("p"),
+                              F.max_by("v", "v").alias("m")).orderBy("k").collect()
+    assert [(r.k, sorted(r.l), r.p, r.m) for r in agg] == [(None, [9], 9, 9), ("a", [1, 2], 1, 2), ("b", [5], 5, 5)]
+    hof = df.select("k", "v", F.transform("xs", lambda x: x * F.col("v")).alias("t"),
+                    F.concat_ws("-", "k", F.lit("z")).alias("c")).orderBy("v").collect()
+    assert [(r.t, r.c) for r in hof] == [([1, 2], "a-z"), ([6], "a-z"), ([], "b-z"), (None, "z")]
+    ranked = df.withColumn("r", F.rank().over(Window.partitionBy("k").orderBy(F.desc("v")))).orderBy("k", "r").collect()
+    assert [(r.k, r.v, r.r) for r in ranked] == [(None, 9, 1), ("a", 2, 1), ("a", 1, 2), ("b", 5, 1)]
+    df.select("k", "v").write.partitionBy("k").json(str(tmp_path / "o"))
+    back = sorted((tuple(r) for r in spark.read.json(str(tmp_path / "o")).collect()), key=repr)
+    assert back == [(1, "a"), (2, "a"), (5, "b"), (9, None)]
+    df.createOrReplaceTempView("wide_t")
+    rows = spark.sql("select k, sum(v) s from wide_t group by k having sum(v) > 2 order by s desc").collect()
+    assert [(r.k, r.s) for r in rows] == [(None, 9), ("b", 5), ("a", 3)]

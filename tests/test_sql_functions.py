@@ -338,3 +338,25 @@ def test_sql_window_clauses(spark, sales):
     assert rows == [("a", 2, 1, 5, None, 2), ("a", 2, 2, 5, 2, 4), ("a", 1, 3, 5, 2, 5)]
     assert q(spark, "SELECT k, v FROM (SELECT k, v, rank() OVER (PARTITION BY k ORDER BY v DESC) AS r FROM sales) "
                     "WHERE r = 1 AND k = 'b'") == [("b", 5)]
+
+
+def test_theta_joins_pandas_udfs_schema_json(spark, people):
+    from raydp_b200.sql import types as T
+    other = spark.createDataFrame([("a", "A"), ("c", "C")], ["kk", "name"])
+    assert [tuple(r) for r in people.join(other, F.col("k") > F.col("kk")).collect()] == \
+        [("b", 5, 1.0, "a", "A"), ("b", 3, 2.0, "a", "A")]
+    left = people.join(other, (F.col("k") > F.col("kk")) & (F.col("v") > 3), "left")
+    assert left.count() == 6 and left.filter("name is not null").count() == 1
+    assert people.join(other, F.col("k") > F.col("kk"), "left_anti").count() == 4
+    assert people.join(other, F.col("k") > F.col("kk"), "left_semi").count() == 2
+    up = people.select(F.pandas_udf(lambda s: s.str.upper(), "string")("k").alias("u")).collect()
+    assert [r.u for r in up] == ["A", "A", "A", "B", "B", None]
+
+    @F.pandas_udf("double")
+    def times(a, b):
+        return a * b.fillna(0)
+    assert [r.p for r in people.select(times("v", "x").alias("p")).collect()] == [10.0, 40.0, 0.0, 5.0, 6.0, 81.0]
+    schema = people.schema
+    assert T.StructType.fromJson(schema.jsonValue()) == schema and '"name":"k"' in schema.json()
+    assert T.StructType().add("a", T.IntegerType()).add("b", "array<string>").simpleString() == \
+        "struct<a:int,b:array<string>>"
