@@ -167,6 +167,9 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
                                                  client_mode_wrap=lambda fn: fn),
         "ray._private.internal_api": _module("ray._private.internal_api", "", global_gc=_global_gc),
         "ray.data": data,
+        "ray.data.aggregate": _module("ray.data.aggregate", "", **{k: getattr(data, k) for k in (
+            "AggregateFn", "Count", "Sum", "Min", "Max", "Mean", "Std", "AbsMax", "Unique", "Quantile")}),
+        "ray.data.context": _module("ray.data.context", "", DataContext=data.DataContext),
         "ray.train": _module("ray.train", "", ScalingConfig=config.ScalingConfig, RunConfig=config.RunConfig,
                              FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig,
                              Checkpoint=checkpoint.Checkpoint, get_dataset_shard=session.get_dataset_shard,

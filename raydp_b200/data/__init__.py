@@ -544,3 +544,124 @@ def read_csv(path: Union[str, List[str]], **_kw) -> Dataset:
     files = [f for p in paths for f in list_data_files(p, ())]
     refs = _in_waves(lambda i: _read_csv_file.remote(files[i]), len(files))
     return from_arrow_refs(refs)
+
+
+def read_json(path: Union[str, List[str]], **_kw) -> Dataset:
+    """JSON-lines files, one block per file."""
+    import pyarrow.json as pajson
+    from raydp_b200.sql.plan import list_data_files
+    paths = [path] if isinstance(path, str) else list(path)
+    files = [f for p in paths for f in list_data_files(p, ())]
+    ds = from_arrow([pajson.read_json(f) for f in files])
+    ds._input_files = files
+    return ds
+
+
+def read_text(path: Union[str, List[str]], encoding: str = "utf-8", drop_empty_lines: bool = True, **_kw) -> Dataset:
+    from raydp_b200.sql.plan import list_data_files
+    paths = [path] if isinstance(path, str) else list(path)
+    files = [f for p in paths for f in list_data_files(p, ())]
+    tables = []
+    for f in files:
+        with open(f, "r", encoding=encoding) as fh:
+            lines = fh.read().splitlines()
+        tables.append(pa.table({"text": pa.array([ln for ln in lines if ln or not drop_empty_lines], pa.string())}))
+    ds = from_arrow(tables)
+    ds._input_files = files
+    return ds
+
+
+def read_numpy(path: Union[str, List[str]], **_kw) -> Dataset:
+    from raydp_b200.sql.plan import list_data_files
+    paths = [path] if isinstance(path, str) else list(path)
+    files = [f for p in paths for f in list_data_files(p, (".npy",))]
+    tables = []
+    for f in files:
+        arr = np.load(f)
+        tables.append(pa.table({"data": list(arr) if arr.ndim > 1 else arr}))
+    ds = from_arrow(tables)
+    ds._input_files = files
+    return ds
+
+
+def read_binary_files(path: Union[str, List[str]], include_paths: bool = False, **_kw) -> Dataset:
+    from raydp_b200.sql.plan import list_data_files
+    paths = [path] if isinstance(path, str) else list(path)
+    files = [f for p in paths for f in list_data_files(p, ())]
+    tables = []
+    for f in files:
+        with open(f, "rb") as fh:
+            cols = {"bytes": pa.array([fh.read()], pa.binary())}
+        if include_paths:
+            cols["path"] = pa.array([f])
+        tables.append(pa.table(cols))
+    ds = from_arrow(tables)
+    ds._input_files = files
+    return ds
+
+
+def read_images(path: Union[str, List[str]], **_kw) -> Dataset:
+    try:
+        from PIL import Image
+    except ImportError as exc:
+        raise ImportError("read_images needs Pillow, which is not installed") from exc
+    from raydp_b200.sql.plan import list_data_files
+    paths = [path] if isinstance(path, str) else list(path)
+    files = [f for p in paths for f in list_data_files(p, ())]
+    return from_items([{"image": np.asarray(Image.open(f)).tolist(), "path": f} for f in files])
+
+
+def range_tensor(n: int, shape=(1,), parallelism: int = 4) -> Dataset:
+    shape = tuple(shape)
+    parallelism = max(1, min(parallelism, max(1, n)))
+    bounds = np.linspace(0, n, parallelism + 1).astype(np.int64)
+    tables = []
+    for i in builtins_range(parallelism):
+        ids = np.arange(bounds[i], bounds[i + 1], dtype=np.int64)
+        data = np.broadcast_to(ids.reshape((-1,) + (1,) * len(shape)), (len(ids),) + shape)
+        tables.append(pa.table({"data": [row.tolist() for row in data]}))
+    return from_arrow(tables)
+
+
+def from_torch(dataset) -> Dataset:
+    """A map-style ``torch.utils.data.Dataset`` -> one ``item`` column."""
+    return from_items([_plain_item(dataset[i]) for i in builtins_range(len(dataset))])
+
+
+def _plain_item(value):
+    if hasattr(value, "tolist"):
+        return value.tolist()
+    if isinstance(value, (tuple, list)):
+        return [_plain_item(v) for v in value]
+    if isinstance(value, dict):
+        return {k: _plain_item(v) for k, v in value.items()}
+    return value
+
+
+def from_huggingface(dataset) -> Dataset:
+    """A ``datasets.Dataset`` (Arrow-backed) -> Dataset, without copying through Python objects."""
+    table = getattr(getattr(dataset, "data", None), "table", None)
+    if isinstance(table, pa.Table):
+        return from_arrow([table.combine_chunks()])
+    return from_pandas(dataset.to_pandas())
+
+
+def from_pandas_refs(refs) -> Dataset:
+    refs = [refs] if not isinstance(refs, (list, tuple)) else list(refs)
+    return from_pandas([runtime.get(r) for r in refs])
+
+
+def from_numpy_refs(refs, column: str = "data") -> Dataset:
+    refs = [refs] if not isinstance(refs, (list, tuple)) else list(refs)
+    return from_arrow([pa.table({column: list(a) if a.ndim > 1 else a}) for a in (runtime.get(r) for r in refs)])
+
+
+def from_blocks(blocks: List[pa.Table]) -> Dataset:
+    return from_arrow(list(blocks))
+
+
+from raydp_b200.data import extras as _extras  # noqa: E402
+from raydp_b200.data.extras import (AbsMax, AggregateFn, Count, DataContext, DataIterator, GroupedData, Max,  # noqa: E402,F401
+                                    Mean, Min, Quantile, Std, Sum, Unique)
+
+_extras._install(Dataset)

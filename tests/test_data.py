@@ -97,3 +97,36 @@ def test_row_wise_map_filter_add_column_sort(ray_cluster):
     except ImportError:
         with pytest.raises(ImportError):
             ds.to_tf("a", "a", batch_size=2)
+
+
+def test_aggregations_groupby_zip_join_and_io(ray_cluster, tmp_path):
+    """The wider ray.data surface: global / grouped aggregates, custom AggregateFn, map_groups, zip, join,
+    sampling, extra readers and writers."""
+    from raydp_b200 import data
+    ds = data.from_items([{"k": "a" if i % 2 else "b", "v": i, "x": float(i) * 0.5} for i in range(10)], parallelism=3)
+    assert (ds.sum("v"), ds.min("v"), ds.max("x"), ds.mean("v")) == (45, 0, 4.5, 4.5)
+    assert abs(ds.std("v") - 3.0276503540974917) < 1e-12 and sorted(ds.unique("k")) == ["a", "b"]
+    assert ds.groupby("k").count().take_all() == [{"k": "a", "count()": 5}, {"k": "b", "count()": 5}]
+    assert ds.groupby("k").sum("v").take_all() == [{"k": "a", "sum(v)": 25}, {"k": "b", "sum(v)": 20}]
+    assert ds.groupby("k").mean(["v", "x"]).take_all()[0] == {"k": "a", "mean(v)": 5.0, "mean(x)": 2.5}
+    assert ds.aggregate(data.Count(), data.Sum("v"), data.Quantile("v", q=0.5), data.AbsMax("x")) == \
+        {"count()": 10, "sum(v)": 45, "quantile(v)": 4.5, "absmax(x)": 4.5}
+    total = data.AggregateFn(init=lambda k: 0, accumulate_row=lambda a, r: a + r["v"], merge=lambda a, b: a + b,
+                             name="tot")
+    assert ds.groupby("k").aggregate(data.Max("v"), total).take_all() == \
+        [{"k": "a", "max(v)": 9, "tot": 25}, {"k": "b", "max(v)": 8, "tot": 20}]
+    shifted = ds.groupby("k").map_groups(lambda p: p.assign(v=p.v - p.v.min())).take_all()
+    assert [r["v"] for r in shifted if r["k"] == "a"] == [0, 2, 4, 6, 8]
+    assert ds.flat_map(lambda r: [r, r]).count() == 20 and ds.rename_columns({"v": "w"}).columns() == ["k", "w", "x"]
+    assert list(ds.take_batch(2)["v"]) == [0, 1]
+    assert ds.zip(ds.select_columns(["v"])).columns() == ["k", "v", "x", "v_1"]
+    assert ds.join(data.from_items([{"k": "a", "n": 1}]), "inner", on="k").count() == 5
+    assert 0 < ds.random_sample(0.5, seed=1).count() < 10 and ds.repeat(2).count() == 20
+    shards = ds.streaming_split(2)
+    assert sum(s.count() for s in shards) == 10 and sum(len(b["v"]) for b in shards[0].iter_batches(batch_format="numpy")) > 0
+    ds.write_json(str(tmp_path / "j"))
+    ds.write_csv(str(tmp_path / "c"))
+    assert data.read_json(str(tmp_path / "j")).sum("v") == 45 and data.read_csv(str(tmp_path / "c")).count() == 10
+    assert data.read_text(str(tmp_path / "c")).count() == 13          # 3 blocks: 3 headers + 10 rows
+    assert data.range_tensor(4, shape=(2, 2)).take(1) == [{"data": [[0, 0], [0, 0]]}]
+    assert data.DataContext.get_current() is data.DataContext.get_current()
