@@ -259,7 +259,14 @@ class Column:
             cols = [(_to_array(x, n) if _is_arrayish(x) else None, x) for x in arrays]
             pylists = [c.to_pylist() if c is not None else [s.as_py()] * n for c, s in cols]
             out = [func(*row) for row in zip(*pylists)] if pylists else [func() for _ in range(n)]
-            return pa.array(out, type=rtype.arrow)
+            try:
+                return pa.array(out, type=rtype.arrow)
+            except (pa.ArrowTypeError, pa.ArrowInvalid):
+                # the function returned something other than the declared type: text is rendered, anything
+                # else goes through a cast of what Arrow infers
+                if pa.types.is_string(rtype.arrow):
+                    return pa.array([None if v is None else str(v) for v in out], type=pa.string())
+                return pc.cast(pa.array(out), rtype.arrow, safe=False)
         if k == "vudf":  # vectorised: func(numpy arrays...) -> numpy array
             func, rtype, arg_cols = a
             arrays = [c.evaluate(table, ctx) for c in arg_cols]

@@ -108,3 +108,36 @@ def test_rows_and_nested_schemas(spark):
     nested = spark.createDataFrame([(1, [1, 2], {"k": 1.5})], "id int, xs array<int>, m map<string,double>")
     assert nested.dtypes == [("id", "int"), ("xs", "array<int>"), ("m", "map<string,double>")]
     assert nested.select(F.col("m")["k"].alias("v"), F.size("xs").alias("n")).collect()[0] == Row(v=1.5, n=2)
+
+
+def test_pandas_on_spark_surface(spark):
+    """``pyspark.pandas`` stand-in: lazy column expressions, reductions, accessors, groupby, merge."""
+    from raydp_b200.sql import pandas_api as ps
+    df = ps.DataFrame({"k": ["a", "a", "b", None], "v": [1, 2, 5, 9], "x": [10.0, 20.0, None, 9.0],
+                       "t": ["2020-01-05 10:00:00"] * 4})
+    df["y"] = df["v"] * 2 + 1
+    assert df.shape == (4, 5) and df.dtypes.to_dict()["y"] == "bigint"
+    assert df[df.v > 1][["k", "v"]].to_pandas()["v"].tolist() == [2, 5, 9]
+    assert (df.v.sum(), df.v.mean(), df.x.max(), df.k.nunique()) == (17, 4.25, 20.0, 2)
+    assert df.k.str.upper().to_pandas().tolist()[:3] == ["A", "A", "B"]
+    assert df.t.astype("datetime64[ns]").dt.year.to_pandas().tolist() == [2020] * 4
+    assert ps.to_datetime(df.t).dt.dayofweek.head(1).tolist() == [6]                       # a Sunday
+    by_k = df.groupby("k").sum().to_pandas()
+    assert by_k[by_k.k == "a"][["v", "x", "y"]].values.tolist() == [[3, 30.0, 8]]
+    assert df.groupby("k")["v"].agg(["min", "max"]).to_pandas().values.tolist()[1:] == [["a", 1, 2], ["b", 5, 5]]
+    assert df.groupby("k").agg(total=("v", "sum")).to_pandas()["total"].tolist() == [9, 3, 5]
+    assert df.sort_values("v", ascending=False).head(1)["v"].tolist() == [9]
+    assert df.fillna(0).x.sum() == 39.0 and df.dropna().shape == (2, 5) and "t" not in df.drop(columns=["t"]).columns
+    other = ps.DataFrame({"k": ["a", "c"], "name": ["A", "C"], "v": [7, 8]})
+    merged = df.merge(other, on="k", how="left")
+    assert merged.columns == ["k", "v_x", "x", "t", "y", "name", "v_y"] and len(df.merge(other, on="k")) == 2
+    assert df.v.map({1: "one"}).to_pandas().tolist()[0] == "one"
+    assert df.x.fillna(-1).clip(0, 15).to_pandas().tolist() == [10.0, 15.0, 0.0, 9.0]
+    assert df.assign(z=lambda d: d.v + d.y).z.sum() == 55 and df.describe().loc["mean", "v"] == 4.25
+    assert ps.get_dummies(df[["k", "v"]]).columns == ["v", "k_a", "k_b"]
+    assert ps.concat([df[["k"]], df[["k"]]]).shape == (8, 1) and df.loc[df.v > 2, ["k"]].shape == (2, 1)
+
+    def row_total(r) -> float:
+        return float(r["v"]) + float(r["y"])
+    assert df.apply(row_total, axis=1).to_pandas().tolist() == [4.0, 7.0, 16.0, 28.0]
+    assert ps.range(10).to_spark().count() == 10 and isinstance(df.to_spark(), type(spark.range(1)))
