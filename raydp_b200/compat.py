@@ -120,7 +120,8 @@ class _GlobalWorker:
 
 
 def _ray_tree() -> Dict[str, types.ModuleType]:
-    from raydp_b200 import data, runtime, train
+    from raydp_b200 import data, runtime, train, tune
+    from raydp_b200.train import legacy
     from raydp_b200.runtime import cluster_utils, protocol
     from raydp_b200.train import checkpoint, config, session, torch_utils, trainer
 
@@ -174,7 +175,11 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
                              FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig,
                              Checkpoint=checkpoint.Checkpoint, get_dataset_shard=session.get_dataset_shard,
                              report=session.report, get_context=session.get_context,
-                             get_checkpoint=session.get_checkpoint, Result=trainer.Result),
+                             get_checkpoint=session.get_checkpoint, Result=trainer.Result,
+                             Trainer=legacy.Trainer, TrainingCallback=legacy.TrainingCallback,
+                             world_rank=lambda: session.get_context().get_world_rank(),
+                             local_rank=lambda: session.get_context().get_local_rank(),
+                             world_size=lambda: session.get_context().get_world_size()),
         "ray.train.torch": _module("ray.train.torch", "", TorchTrainer=trainer.TorchTrainer,
                                    TorchConfig=config.TorchConfig, TorchCheckpoint=checkpoint.TorchCheckpoint,
                                    prepare_model=torch_utils.prepare_model, get_device=torch_utils.get_device),
@@ -185,7 +190,16 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
                                   RunConfig=config.RunConfig, FailureConfig=config.FailureConfig,
                                   CheckpointConfig=config.CheckpointConfig),
         "ray.air.session": session,
+        "ray.tune": tune,
+        "ray.tune.search": _module("ray.tune.search", ""),
+        "ray.tune.search.sample": _module("ray.tune.search.sample", "", Domain=tune.Domain),
+        "ray.data.dataset": _module("ray.data.dataset", "", Dataset=data.Dataset),
+        "ray.types": _module("ray.types", "", ObjectRef=runtime.ObjectRef),
+        "ray.cloudpickle": __import__("cloudpickle"),
+        "ray.runtime_context": _module("ray.runtime_context", "", get_runtime_context=runtime.get_runtime_context),
     }
+    tree["ray.train"].torch = tree["ray.train.torch"]
+    ray.tune, ray.cloudpickle = tune, tree["ray.cloudpickle"]
     # ray.data / ray.air.session are real modules of this package: register under the alias names too
     ray.data, ray.train = data, tree["ray.train"]
     del train
@@ -224,6 +238,9 @@ def install(ray: bool = True, pyspark: bool = True, force: bool = False) -> List
             not getattr(sys.modules.get("pyspark"), "__raydp_b200_alias__", False):
         _register(_pyspark_tree())
         added.append("pyspark")
+    if _INSTALLED:
+        import os
+        os.environ["RAYDP_B200_COMPAT_ALIASES"] = "1"      # worker processes install the same aliases
     return added
 
 

@@ -27,6 +27,14 @@ def _resolve_args(args, kwargs):
 
 
 def main() -> None:
+    if os.environ.get("RAYDP_B200_COMPAT_ALIASES") == "1":
+        # the driver runs with the ``ray`` / ``pyspark`` import aliases: closures it ships refer to
+        # modules by those names
+        try:
+            from raydp_b200 import compat
+            compat.install()
+        except Exception:  # noqa: BLE001
+            traceback.print_exc()
     head = os.environ[P.ENV_HEAD]
     auth = bytes.fromhex(os.environ[P.ENV_AUTH])
     worker_id = os.environ[P.ENV_WORKER]

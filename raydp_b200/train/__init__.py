@@ -6,3 +6,4 @@ from raydp_b200.train.session import (get_checkpoint, get_context, get_dataset_s
                                       report)
 from raydp_b200.train.torch_utils import get_device, prepare_model  # noqa: F401
 from raydp_b200.train.trainer import Result, TorchTrainer, TrainingFailedError  # noqa: F401
+from raydp_b200.train.legacy import Trainer, TrainingCallback  # noqa: F401,E402

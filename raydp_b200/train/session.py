@@ -86,8 +86,12 @@ def get_dataset_shard(name: Optional[str] = None):
     return shards.get(name)
 
 
-def report(metrics: Dict[str, Any], checkpoint=None) -> None:
-    get_session().report(metrics, checkpoint)
+def report(metrics: Optional[Dict[str, Any]] = None, checkpoint=None, **kwargs) -> None:
+    """``report({"loss": x}, checkpoint=...)``; the keyword form ``report(loss=x)`` of the older API is
+    accepted too."""
+    merged = dict(metrics or {})
+    merged.update(kwargs)
+    get_session().report(merged, checkpoint)
 
 
 def get_checkpoint():

@@ -227,6 +227,7 @@ class TorchTrainer:
                 all_reports = runtime.get(refs)
             except runtime.TaskError as exc:
                 raise TrainingFailedError(str(exc)) from exc
+            self._all_reports = all_reports                 # every rank's reports (legacy Trainer.run)
             return all_reports[0]
         finally:
             for w in workers:

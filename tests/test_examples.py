@@ -44,6 +44,23 @@ def test_reference_example_runs_unchanged_through_compat_runner():
     assert "Traceback" not in proc_out
 
 
+def test_reference_raytrain_example_runs_unchanged(tmp_path):
+    """``examples/raytrain_nyctaxi.py`` of the reference: first-generation ``ray.train.Trainer`` /
+    ``TrainingCallback``, ``from ray import tune``, ``get_dataset_shard(...).to_torch(...)``."""
+    import glob
+    import shutil
+    import pytest
+    src = "/root/reference/examples"
+    if not os.path.isdir(src):
+        pytest.skip("reference examples not mounted")
+    for f in glob.glob(os.path.join(src, "*.py")) + glob.glob(os.path.join(src, "*.csv")):
+        shutil.copy(f, tmp_path)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.run([sys.executable, "-m", "raydp_b200.compat", "raytrain_nyctaxi.py"], cwd=str(tmp_path),
+                          env=env, capture_output=True, text=True, timeout=600)
+    assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
+
+
 def test_reference_unit_tests_pass_unchanged(tmp_path):
     """The reference's own pytest files (copied, not edited) run against this framework through the
     ``ray`` / ``pyspark`` aliases.  The quick ones run here; test_spark_cluster / test_torch / test_mpi /

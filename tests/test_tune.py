@@ -1,0 +1,68 @@
+"""Hyper-parameter search (the ``ray.tune`` slice) and the first-generation ``Trainer`` API."""
+import pytest
+
+from raydp_b200 import tune
+from raydp_b200.train import Trainer, TrainingCallback
+from raydp_b200.train import session
+
+
+def _trainable(config):
+    for i in range(3):
+        tune.report(loss=(config["lr"] - 0.01) ** 2 + 1.0 / (i + 1), it=i)
+
+
+def test_search_space_expansion():
+    space = {"a": tune.grid_search([1, 2]), "b": {"c": tune.grid_search(["x", "y"]), "d": tune.uniform(0, 1)}, "e": 5}
+    configs = tune.generate_configs(space, num_samples=2, seed=0)
+    assert len(configs) == 8 and {(c["a"], c["b"]["c"]) for c in configs} == {(1, "x"), (1, "y"), (2, "x"), (2, "y")}
+    assert all(0 <= c["b"]["d"] <= 1 and c["e"] == 5 for c in configs)
+    assert len({c["b"]["d"] for c in configs}) == 8                      # every trial draws its own sample
+    assert tune.generate_configs(space, seed=0) == tune.generate_configs(space, seed=0)
+    draws = tune.generate_configs({"n": tune.randint(0, 3), "c": tune.choice(["p", "q"]), "l": tune.loguniform(1e-4, 1e-1)},
+                                  num_samples=20, seed=1)
+    assert all(d["n"] in (0, 1, 2) and d["c"] in ("p", "q") and 1e-4 <= d["l"] <= 1e-1 for d in draws)
+
+
+def test_run_in_process_and_best_config():
+    analysis = tune.run(_trainable, config={"lr": tune.grid_search([0.005, 0.01, 0.05])}, metric="loss", mode="min")
+    assert analysis.get_best_config() == {"lr": 0.01} and abs(analysis.best_result["loss"] - 1 / 3) < 1e-12
+    assert analysis.get_best_config("loss", "max") == {"lr": 0.05}
+    frame = analysis.dataframe()
+    assert frame.shape[0] == 3 and "config/lr" in frame.columns and list(frame["it"]) == [2, 2, 2]
+    with pytest.raises(tune.TuneError):
+        tune.run(lambda config: 1 / 0, config={})
+
+
+def test_tuner_runs_trials_as_runtime_tasks(ray_cluster):
+    grid = tune.Tuner(_trainable, param_space={"lr": tune.grid_search([0.01, 0.1])},
+                      tune_config=tune.TuneConfig(metric="loss", mode="min")).fit()
+    best = grid.get_best_result()
+    assert len(grid) == 2 and best.config == {"lr": 0.01} and abs(best.metrics["loss"] - 1 / 3) < 1e-12
+    assert grid.num_errors == 0 and len(best.metrics_history) == 3
+    failed = tune.Tuner(lambda config: 1 / 0, param_space={}).fit()
+    assert failed.num_errors == 1 and "ZeroDivisionError" in str(failed.errors[0])
+
+
+def test_legacy_trainer_run_callbacks_and_tune_trainable(ray_cluster):
+    seen = []
+
+    class Collect(TrainingCallback):
+        def handle_result(self, results, **info):
+            seen.append(results)
+
+    def train_func(config):
+        rank = session.get_context().get_world_rank()
+        session.report(loss=config["x"] * (rank + 1))
+        return rank
+
+    trainer = Trainer(backend="torch", num_workers=2)
+    with pytest.raises(RuntimeError):
+        trainer.run(train_func, config={"x": 1.0})
+    trainer.start()
+    assert trainer.run(train_func, config={"x": 2.0}, callbacks=[Collect()]) == [0, 1]
+    assert seen == [[{"loss": 2.0}, {"loss": 4.0}]]
+    trainable = trainer.to_tune_trainable(train_func)
+    trainer.shutdown()
+    analysis = tune.run(trainable, config={"x": tune.grid_search([3.0, 1.0])}, metric="loss", mode="min",
+                        max_concurrent_trials=1)
+    assert analysis.get_best_config() == {"x": 1.0}
