@@ -35,6 +35,7 @@ def _module(name: str, doc: str, **attrs) -> types.ModuleType:
     # a spec keeps ``importlib.util.find_spec(name)`` (used by other libraries to probe for optional
     # dependencies) from raising on a module that sits in sys.modules without one
     mod.__spec__ = importlib.machinery.ModuleSpec(name, loader=None)
+    mod.__path__ = []           # lets ``import <alias>.<child>`` resolve children registered in sys.modules
     return mod
 
 
@@ -69,6 +70,13 @@ class JobConfig:
         for path in settings.get("code_search_path") or []:
             if path not in sys.path:
                 sys.path.append(path)
+
+
+def _passthrough_decorator(*args, **kwargs):
+    """``@PublicAPI`` / ``@PublicAPI(stability="beta")``: annotations only."""
+    if len(args) == 1 and callable(args[0]) and not kwargs:
+        return args[0]
+    return lambda obj: obj
 
 
 def _global_gc() -> None:
@@ -122,6 +130,9 @@ class _GlobalWorker:
 def _ray_tree() -> Dict[str, types.ModuleType]:
     from raydp_b200 import data, runtime, train, tune
     from raydp_b200.train import legacy
+    from raydp_b200.runtime import util as rt_util
+    from raydp_b200.spark.parallel_iterator_worker import ParallelIteratorWorkerWithLen
+    from raydp_b200.torch.torch_ml_dataset import TorchMLDataset
     from raydp_b200.runtime import cluster_utils, protocol
     from raydp_b200.train import checkpoint, config, session, torch_utils, trainer
 
@@ -190,6 +201,12 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
                                   RunConfig=config.RunConfig, FailureConfig=config.FailureConfig,
                                   CheckpointConfig=config.CheckpointConfig),
         "ray.air.session": session,
+        "ray.util.actor_pool": _module("ray.util.actor_pool", "", ActorPool=rt_util.ActorPool),
+        "ray.util.queue": _module("ray.util.queue", "", Queue=rt_util.Queue, Empty=rt_util.Empty, Full=rt_util.Full),
+        "ray.util.iter": _module("ray.util.iter", "", ParallelIteratorWorker=ParallelIteratorWorkerWithLen),
+        "ray.util.data": _module("ray.util.data", "", MLDataset=TorchMLDataset),
+        "ray.util.annotations": _module("ray.util.annotations", "", PublicAPI=_passthrough_decorator,
+                                        DeveloperAPI=_passthrough_decorator, Deprecated=_passthrough_decorator),
         "ray.tune": tune,
         "ray.tune.search": _module("ray.tune.search", ""),
         "ray.tune.search.sample": _module("ray.tune.search.sample", "", Domain=tune.Domain),

@@ -123,3 +123,41 @@ def test_custom_resource_node_affinity_and_node_loss():
         assert rt.get(c.inc.remote(), timeout=60) == 1      # actor restarted elsewhere
     finally:
         cluster.shutdown()
+
+
+def test_actor_pool_and_queue(ray_cluster):
+    """``ActorPool`` keeps submission order in ``map`` and hands queued work to freed actors; ``Queue`` is
+    shared state in an actor, usable from tasks."""
+    from raydp_b200 import runtime
+    from raydp_b200.runtime.util import ActorPool, Empty, Full, Queue
+
+    @runtime.remote
+    class Doubler:
+        def f(self, v):
+            import time
+            time.sleep(0.01 * (5 - v))
+            return v * 2
+
+    pool = ActorPool([Doubler.remote(), Doubler.remote()])
+    assert list(pool.map(lambda a, v: a.f.remote(v), range(5))) == [0, 2, 4, 6, 8]
+    assert sorted(pool.map_unordered(lambda a, v: a.f.remote(v), range(5))) == [0, 2, 4, 6, 8]
+    assert not pool.has_next() and pool.has_free()
+
+    q = Queue(maxsize=2)
+    q.put(1)
+    q.put(2)
+    with pytest.raises(Full):
+        q.put(3, block=False)
+    assert (q.get(), q.size(), q.get(), q.empty()) == (1, 1, 2, True)
+    with pytest.raises(Empty):
+        q.get(timeout=0.05)
+
+    @runtime.remote
+    def producer(queue):
+        for i in range(3):
+            queue.put(i)
+
+    shared = Queue()
+    runtime.get(producer.remote(shared))
+    assert [shared.get() for _ in range(3)] == [0, 1, 2]
+    shared.shutdown()
