@@ -258,8 +258,9 @@ def test_join_variants(spark_session):
     assert a.join(b2, a.k == b2.kk, "left_semi").count() == 2
     assert a.crossJoin(b).count() == 9 and a.join(b, how="cross").count() == 9
     import pytest as _pytest
-    with _pytest.raises(NotImplementedError):
+    with _pytest.raises(ValueError):                                  # same-named columns cannot be told apart
         a.join(b, a.k > b.k)
+    assert rows(a.join(b2, a.k > b2.kk).select("k", "kk")) == [(3, 2)]   # a non-equality predicate
 
 
 def test_frequency_dictionary_recipe(spark_session):
