@@ -242,6 +242,36 @@ def _pyspark_tree() -> Dict[str, types.ModuleType]:
         "pyspark.sql.column": column,
         "pyspark.pandas": pandas_api,
         "pyspark.storagelevel": _module("pyspark.storagelevel", "", StorageLevel=dataframe.StorageLevel),
+        **_pyspark_ml_tree(),
+    }
+
+
+def _pyspark_ml_tree() -> Dict[str, types.ModuleType]:
+    from raydp_b200.sql import ml
+    from raydp_b200.sql.ml import base, feature, linalg, models
+
+    def pick(mod, *names):
+        return {n: getattr(mod, n) for n in names}
+    return {
+        "pyspark.ml": _module("pyspark.ml", "alias of raydp_b200.sql.ml", **pick(
+            base, "Pipeline", "PipelineModel", "Transformer", "Estimator", "Model")),
+        "pyspark.ml.feature": feature,
+        "pyspark.ml.linalg": linalg,
+        "pyspark.ml.pipeline": _module("pyspark.ml.pipeline", "", **pick(base, "Pipeline", "PipelineModel")),
+        "pyspark.ml.regression": _module("pyspark.ml.regression", "", **pick(
+            models, "LinearRegression", "LinearRegressionModel")),
+        "pyspark.ml.classification": _module("pyspark.ml.classification", "", **pick(
+            models, "LogisticRegression", "LogisticRegressionModel")),
+        "pyspark.ml.clustering": _module("pyspark.ml.clustering", "", **pick(models, "KMeans", "KMeansModel")),
+        "pyspark.ml.evaluation": _module("pyspark.ml.evaluation", "", **pick(
+            models, "Evaluator", "RegressionEvaluator", "BinaryClassificationEvaluator",
+            "MulticlassClassificationEvaluator")),
+        "pyspark.ml.tuning": _module("pyspark.ml.tuning", "", **pick(
+            models, "ParamGridBuilder", "CrossValidator", "CrossValidatorModel", "TrainValidationSplit",
+            "TrainValidationSplitModel")),
+        # vectors are array<double> columns already
+        "pyspark.ml.functions": _module("pyspark.ml.functions", "", vector_to_array=lambda col, dtype="float64": col,
+                                        array_to_vector=lambda col: col),
     }
 
 

@@ -69,6 +69,8 @@ class Column:
             return f"({self._args[1]._output_name()} {self._args[0]} {self._args[2]._output_name()})"
         if self._kind == "udf":
             return f"{self._args[0].__name__}(...)"
+        if self._kind == "arrowfn":
+            return f"{getattr(self._args[0], '__name__', 'fn')}(...)"
         return self._kind
 
     # ------------------------------------------------------------------ operators
@@ -275,6 +277,11 @@ class Column:
             return pa.array(np.asarray(func(*nps)), type=rtype.arrow, from_pandas=True)
         if k == "sort":
             return a[0].evaluate(table, ctx)
+        if k == "arrowfn":      # func(*arrow arrays) -> arrow array: whole-partition kernels (sql/ml stages)
+            func, arg_cols = a
+            arrays = [_full(c.evaluate(table, ctx), n) for c in arg_cols]
+            arrays = [x.combine_chunks() if isinstance(x, pa.ChunkedArray) else x for x in arrays]
+            return func(*arrays)
         if k == "hof":
             from raydp_b200.sql.fnlib import eval_higher_order
             name, array_cols, body, variables, extra = a
