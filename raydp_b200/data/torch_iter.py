@@ -27,6 +27,29 @@ def _column_numpy(table: pa.Table, name: str) -> np.ndarray:
     return arr.to_numpy(zero_copy_only=False)
 
 
+def _is_vector(table: pa.Table, name: str) -> bool:
+    t = table.schema.field(name).type
+    return pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_fixed_size_list(t)
+
+
+def _column_matrix(table: pa.Table, name: str) -> np.ndarray:
+    """A fixed-width ``array<number>`` column (what ``VectorAssembler`` produces) as an ``[n, width]`` array."""
+    import pyarrow.compute as pc
+    col = table.column(name)
+    arr = col.combine_chunks() if isinstance(col, pa.ChunkedArray) else col
+    n = len(arr)
+    if n == 0:
+        return np.zeros((0, 0))
+    lengths = pc.list_value_length(arr)
+    width = pc.max(lengths).as_py() or 0
+    if arr.null_count or pc.min(lengths).as_py() != width:
+        raise ValueError(f"feature column {name!r} must hold vectors of one length without nulls")
+    flat = pc.list_flatten(arr)
+    if flat.null_count:
+        flat = flat.fill_null(0)
+    return flat.to_numpy(zero_copy_only=False).reshape(n, width)
+
+
 def _np_dtype(torch_dtype):
     import torch
     if torch_dtype is None:
@@ -41,9 +64,16 @@ def block_to_arrays(table: pa.Table, feature_columns: Sequence[str], feature_dty
                     label_column: Optional[str], label_dtype):
     """One Arrow block -> ``([n, F] features, [n, 1] label)`` numpy arrays."""
     f_np = _np_dtype(feature_dtype) or np.float32
-    feats = np.empty((table.num_rows, len(feature_columns)), dtype=f_np)
-    for j, name in enumerate(feature_columns):
-        feats[:, j] = _column_numpy(table, name)
+    if any(_is_vector(table, name) for name in feature_columns):
+        # vector columns contribute their width: [scalar | vector(k) | ...] -> [n, 1 + k + ...]
+        parts = [_column_matrix(table, name) if _is_vector(table, name) else _column_numpy(table, name).reshape(-1, 1)
+                 for name in feature_columns]
+        feats = np.concatenate([p.astype(f_np, copy=False) for p in parts], axis=1) if table.num_rows else \
+            np.empty((0, len(feature_columns)), dtype=f_np)
+    else:
+        feats = np.empty((table.num_rows, len(feature_columns)), dtype=f_np)
+        for j, name in enumerate(feature_columns):
+            feats[:, j] = _column_numpy(table, name)
     label = None
     if label_column is not None:
         l_np = _np_dtype(label_dtype) or np.float32
@@ -81,8 +111,10 @@ class TorchBatchIterable:
         if self._multi:
             feats = []
             for name, dt in zip(self._features, self._feature_dtypes):
-                arr = _column_numpy(table, name)
-                t = torch.as_tensor(np.ascontiguousarray(arr)).reshape(-1, 1)
+                if _is_vector(table, name):
+                    t = torch.as_tensor(np.ascontiguousarray(_column_matrix(table, name)))
+                else:
+                    t = torch.as_tensor(np.ascontiguousarray(_column_numpy(table, name))).reshape(-1, 1)
                 feats.append(t.to(dt) if dt is not None else t)
             label = None
             if self._label is not None:

@@ -59,6 +59,9 @@ class _ColumnSpan:
     __slots__ = ("address", "rows", "code", "width", "keep")
 
     def __init__(self, arr: pa.Array):
+        if arr.type not in _ARROW_CODES:
+            raise TypeError(f"the GPU ingest path reads fixed-width numeric columns, not {arr.type}: expand vector "
+                            "columns into scalar columns (F.col('features')[i]) or use a model without fused_spec()")
         code, width = _ARROW_CODES[arr.type]
         buf = arr.buffers()[1]
         self.address = buf.address + arr.offset * width

@@ -98,3 +98,19 @@ def test_pyspark_ml_import_names():
     proc = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True,
                           env=dict(os.environ, PYTHONPATH=root + os.pathsep + os.environ.get("PYTHONPATH", "")))
     assert proc.returncode == 0 and "ok" in proc.stdout, proc.stderr[-1500:]
+
+
+def test_assembled_vector_column_feeds_the_torch_bridge(ray_cluster):
+    """``VectorAssembler`` output (``array<double>``) is a valid feature column of ``Dataset.to_torch``: it
+    contributes its width to the feature matrix."""
+    import torch
+    from raydp_b200 import data
+    ds = data.from_items([{"f": [float(i), float(2 * i)], "s": float(i) + 0.5, "y": float(i)} for i in range(6)])
+    batches = list(ds.to_torch(label_column="y", feature_columns=["s", "f"], feature_column_dtypes=torch.float,
+                               label_column_dtype=torch.float, batch_size=4))
+    feats, label = batches[0]
+    assert feats.shape == (4, 3) and feats[1].tolist() == [1.5, 1.0, 2.0] and label.shape == (4, 1)
+    per_col = list(ds.to_torch(label_column="y", feature_columns=["s", "f"],
+                               feature_column_dtypes=[torch.float, torch.float], label_column_dtype=torch.float,
+                               batch_size=6))[0][0]
+    assert per_col[0].shape == (6, 1) and per_col[1].shape == (6, 2)
