@@ -181,6 +181,9 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
         "ray.data": data,
         "ray.data.aggregate": _module("ray.data.aggregate", "", **{k: getattr(data, k) for k in (
             "AggregateFn", "Count", "Sum", "Min", "Max", "Mean", "Std", "AbsMax", "Unique", "Quantile")}),
+        "ray.data.preprocessors": __import__("raydp_b200.data.preprocessors", fromlist=["x"]),
+        "ray.data.preprocessor": _module("ray.data.preprocessor", "", Preprocessor=__import__(
+            "raydp_b200.data.preprocessors", fromlist=["x"]).Preprocessor),
         "ray.data.context": _module("ray.data.context", "", DataContext=data.DataContext),
         "ray.train": _module("ray.train", "", ScalingConfig=config.ScalingConfig, RunConfig=config.RunConfig,
                              FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig,

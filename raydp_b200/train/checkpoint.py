@@ -36,6 +36,49 @@ class Checkpoint:
     def as_directory(self):
         yield self.path
 
+    # dict checkpoints of the AIR generation: one pickled mapping inside the directory
+    _DICT_FILE = "dict_checkpoint.pkl"
+
+    @classmethod
+    def from_dict(cls, data: Dict[str, Any]) -> "Checkpoint":
+        import cloudpickle
+        path = tempfile.mkdtemp(prefix="raydp_b200_ckpt_")
+        with open(os.path.join(path, cls._DICT_FILE), "wb") as fh:
+            cloudpickle.dump(dict(data), fh)
+        return cls(path)
+
+    def to_dict(self) -> Dict[str, Any]:
+        import pickle
+        target = os.path.join(self.path, self._DICT_FILE)
+        if os.path.exists(target):
+            with open(target, "rb") as fh:
+                return pickle.load(fh)
+        out: Dict[str, Any] = {}
+        for name in sorted(os.listdir(self.path)):          # a directory checkpoint: file name -> bytes
+            full = os.path.join(self.path, name)
+            if os.path.isfile(full):
+                with open(full, "rb") as fh:
+                    out[name] = fh.read()
+        return out
+
+    def get_metadata(self) -> Dict[str, Any]:
+        import json
+        meta = os.path.join(self.path, ".metadata.json")
+        if not os.path.exists(meta):
+            return {}
+        with open(meta, "r", encoding="utf-8") as fh:
+            return json.load(fh)
+
+    def set_metadata(self, metadata: Dict[str, Any]) -> None:
+        import json
+        with open(os.path.join(self.path, ".metadata.json"), "w", encoding="utf-8") as fh:
+            json.dump(metadata, fh)
+
+    def update_metadata(self, metadata: Dict[str, Any]) -> None:
+        merged = self.get_metadata()
+        merged.update(metadata)
+        self.set_metadata(merged)
+
     def _persist(self, storage_dir: str) -> "Checkpoint":
         os.makedirs(storage_dir, exist_ok=True)
         dest = os.path.join(storage_dir, f"checkpoint_{uuid.uuid4().hex[:8]}")

@@ -130,3 +130,29 @@ def test_aggregations_groupby_zip_join_and_io(ray_cluster, tmp_path):
     assert data.read_text(str(tmp_path / "c")).count() == 13          # 3 blocks: 3 headers + 10 rows
     assert data.range_tensor(4, shape=(2, 2)).take(1) == [{"data": [[0, 0], [0, 0]]}]
     assert data.DataContext.get_current() is data.DataContext.get_current()
+
+
+def test_preprocessors(ray_cluster):
+    import pandas as pd
+    from raydp_b200 import data
+    from raydp_b200.data.preprocessors import (Chain, Concatenator, LabelEncoder, MinMaxScaler, OneHotEncoder,
+                                               OrdinalEncoder, PreprocessorNotFittedException, SimpleImputer,
+                                               StandardScaler)
+    ds = data.from_items([{"k": "a" if i % 2 else "b", "v": float(i), "x": None if i == 3 else float(i) * 2,
+                           "y": "p" if i < 5 else "n"} for i in range(10)], parallelism=3)
+    scaled = StandardScaler(["v"]).fit_transform(ds).to_pandas()["v"]
+    assert abs(scaled.mean()) < 1e-12 and abs(scaled.std(ddof=0) - 1.0) < 1e-12
+    assert MinMaxScaler(["v"]).fit_transform(ds).max("v") == 1.0
+    assert abs(SimpleImputer(["x"]).fit_transform(ds).take(4)[3]["x"] - 28.0 / 3) < 1e-12
+    assert SimpleImputer(["x"], "constant", fill_value=-1.0).transform(ds).take(4)[3]["x"] == -1.0
+    chain = Chain(SimpleImputer(["x"]), OneHotEncoder(["k"]), LabelEncoder("y"), MinMaxScaler(["v", "x"]),
+                  Concatenator(output_column_name="features", exclude=["y"]))
+    out = chain.fit_transform(ds)
+    assert out.columns() == ["y", "features"] and out.take(1) == [{"y": 1, "features": [0.0, 0.0, 0.0, 1.0]}]
+    served = chain.transform_batch(pd.DataFrame({"k": ["a"], "v": [9.0], "x": [None], "y": ["n"]}))
+    assert served["y"].tolist() == [0] and served["features"][0].tolist()[0] == 1.0
+    assert [r["k"] for r in OrdinalEncoder(["k"]).fit_transform(ds).take(2)] == [1, 0]
+    enc = LabelEncoder("y").fit(ds)
+    assert enc.inverse_transform(enc.transform(ds)).take(1)[0]["y"] == "p"
+    with pytest.raises(PreprocessorNotFittedException):
+        StandardScaler(["v"]).transform(ds)
