@@ -245,6 +245,13 @@ class Column:
                 raise KeyError(f"cannot resolve column '{a[0]}' given input columns {table.column_names}")
             return table.column(a[0])
         if k == "lit":
+            if isinstance(a[0], (list, tuple)):
+                one = pa.array([list(a[0])])
+                return pa.array([list(a[0])] * n, type=one.type)
+            if isinstance(a[0], dict):
+                arr = pa.array([list(a[0].items())] * n)
+                return pa.MapArray.from_arrays(arr.offsets, pc.struct_field(arr.values, 0), pc.struct_field(arr.values, 1)) \
+                    if n else pa.array([], type=pa.map_(pa.string(), pa.string()))
             return pa.scalar(a[0])
         if k == "binop":
             return _binop(a[0], a[1].evaluate(table, ctx), a[2].evaluate(table, ctx))
@@ -329,6 +336,12 @@ def _cast(value, target: pa.DataType, n: int):
         from raydp_b200.sql.fnlib import _as_date, _as_ts
         arr = _full(value, n)
         return _as_date(arr, n, None) if pa.types.is_date(target) else pc.cast(_as_ts(arr, n, EvalContext()), target)
+    if pa.types.is_string(target) and pa.types.is_floating(src):
+        arr = _full(value, n)
+        arr = arr.combine_chunks() if isinstance(arr, pa.ChunkedArray) else arr
+        return pa.array([None if v is None else _float_text(v) for v in arr.to_pylist()], type=pa.string())
+    if pa.types.is_string(target) and pa.types.is_boolean(src):
+        return pc.if_else(value, "true", "false")
     if pa.types.is_string(target) and pa.types.is_timestamp(src):
         from raydp_b200.sql.fnlib import _strftime
         return _strftime(_full(value, n), "%Y-%m-%d %H:%M:%S")
@@ -344,6 +357,19 @@ def _cast(value, target: pa.DataType, n: int):
         return pc.cast(pc.trunc(as_float), target, safe=False) if pa.types.is_integer(target) else \
             pc.cast(as_float, target)
     return pc.cast(value, target, safe=False)
+
+
+def _float_text(v: float) -> str:
+    if v != v:
+        return "NaN"
+    if v in (float("inf"), float("-inf")):
+        return "Infinity" if v > 0 else "-Infinity"
+    text = repr(float(v))
+    if "e" in text:                                   # 1e+20 -> 1.0E20
+        mantissa, exp = text.split("e")
+        mantissa = mantissa if "." in mantissa else mantissa + ".0"
+        return f"{mantissa}E{int(exp)}"
+    return text
 
 
 def _full(value, n: int):
@@ -362,16 +388,62 @@ _CMP = {"<": "less", "<=": "less_equal", ">": "greater", ">=": "greater_equal",
         "==": "equal", "!=": "not_equal"}
 
 
+def _coerce_pair(left, right):
+    """Spark's implicit casts for a comparison: text against a date / timestamp is parsed, text against a
+    number becomes a double."""
+    lt, rt = left.type, right.type
+    is_text = lambda t: pa.types.is_string(t) or pa.types.is_large_string(t)  # noqa: E731
+    is_time = lambda t: pa.types.is_date(t) or pa.types.is_timestamp(t)  # noqa: E731
+    is_num = lambda t: pa.types.is_integer(t) or pa.types.is_floating(t) or pa.types.is_decimal(t)  # noqa: E731
+    if is_text(lt) and is_time(rt):
+        return _cast(left, rt, len(left) if _is_arrayish(left) else 1), right
+    if is_time(lt) and is_text(rt):
+        return left, _cast(right, lt, len(right) if _is_arrayish(right) else 1)
+    if pa.types.is_date(lt) and pa.types.is_timestamp(rt):
+        return pc.cast(left, rt), right
+    if pa.types.is_timestamp(lt) and pa.types.is_date(rt):
+        return left, pc.cast(right, lt)
+    if is_text(lt) and is_num(rt):
+        return _cast(left, pa.float64(), len(left) if _is_arrayish(left) else 1), pc.cast(right, pa.float64())
+    if is_num(lt) and is_text(rt):
+        return pc.cast(left, pa.float64()), _cast(right, pa.float64(), len(right) if _is_arrayish(right) else 1)
+    return left, right
+
+
+def _scalar_array(value):
+    """pa.Scalar -> one-element array (the cast helpers work on arrays)."""
+    return pa.array([value.as_py()], type=value.type) if isinstance(value, pa.Scalar) else value
+
+
 def _binop(op: str, left, right):
     if op in _ARITH:
         return getattr(pc, _ARITH[op])(left, right)
     if op == "/":
-        # Spark's `/` is always floating-point division
-        return pc.divide(pc.cast(left, pa.float64()), pc.cast(right, pa.float64()))
+        # Spark's `/` is always floating-point division; x / 0 is NULL, not infinity
+        num, den = pc.cast(left, pa.float64()), pc.cast(right, pa.float64())
+        zero = pc.equal(den, 0.0)
+        if isinstance(den, pa.Scalar):
+            if den.is_valid and den.as_py() == 0.0:
+                return pc.multiply(num, pa.scalar(None, pa.float64()))
+            return pc.divide(num, den)
+        return pc.divide(num, pc.if_else(pc.fill_null(zero, False), pa.scalar(None, pa.float64()), den))
     if op == "%":
         l_np, r_np = _np(left), _np(right)
-        return pa.array(np.fmod(l_np, r_np))
+        with np.errstate(all="ignore"):
+            out = np.fmod(l_np, r_np)
+        if not isinstance(out, np.ndarray):
+            return pa.scalar(None if r_np == 0 else out)
+        mask = np.broadcast_to(np.asarray(r_np) == 0, out.shape)       # x % 0 is NULL
+        for side in (left, right):
+            if _is_arrayish(side) and side.null_count:
+                mask = mask | np.asarray(pc.is_null(side))
+        return pa.array(out, mask=mask) if mask.any() else pa.array(out)
     if op in _CMP:
+        if left.type != right.type:
+            scalar_l, scalar_r = isinstance(left, pa.Scalar), isinstance(right, pa.Scalar)
+            a, b = _coerce_pair(_scalar_array(left), _scalar_array(right))
+            left = a[0] if scalar_l and _is_arrayish(a) else a
+            right = b[0] if scalar_r and _is_arrayish(b) else b
         return getattr(pc, _CMP[op])(left, right)
     if op == "&":
         return pc.and_kleene(left, right)

@@ -401,6 +401,21 @@ class DataFrame(DataFrameExtras):
     def union(self, other: "DataFrame") -> "DataFrame":
         tables = self._run("collect") + other._run("collect")
         schema = self._arrow_schema()
+        theirs = other._arrow_schema()
+        if len(theirs) != len(schema):
+            raise ValueError(f"Union can only be performed on tables with the same number of columns, but the first "
+                             f"table has {len(schema)} columns and the second table has {len(theirs)} columns")
+        fields = []
+        for mine, yours in zip(schema, theirs):              # positional; numeric columns widen like Spark's
+            t = mine.type
+            if mine.type != yours.type:
+                try:
+                    t = pa.unify_schemas([pa.schema([pa.field("c", mine.type)]), pa.schema([pa.field("c", yours.type)])],
+                                         promote_options="permissive").field("c").type
+                except (pa.ArrowInvalid, pa.ArrowTypeError):
+                    t = mine.type
+            fields.append(pa.field(mine.name, t))
+        schema = pa.schema(fields)
         tables = [t.rename_columns(schema.names).cast(schema, safe=False) for t in tables]
         return self._session._from_tables(tables)
 
@@ -462,16 +477,10 @@ class DataFrame(DataFrameExtras):
         return self._collect_table().to_pandas()
 
     def collect(self) -> List[T.Row]:
-        table = self._collect_table()
-        names = table.column_names
-        cols = [c.to_pylist() for c in table.columns]
-        return [T.Row._make(names, vals) for vals in zip(*cols)] if cols else []
+        return T.table_to_rows(self._collect_table())
 
     def take(self, num: int) -> List[T.Row]:
-        table = self._collect_table(limit=num).slice(0, num)
-        names = table.column_names
-        cols = [c.to_pylist() for c in table.columns]
-        return [T.Row._make(names, vals) for vals in zip(*cols)] if cols else []
+        return T.table_to_rows(self._collect_table(limit=num).slice(0, num))
 
     def head(self, n: Optional[int] = None):
         rows = self.take(1 if n is None else n)
@@ -516,9 +525,7 @@ class DataFrame(DataFrameExtras):
 
     def foreachPartition(self, f) -> None:
         def run(table, _f=f):
-            names = table.column_names
-            cols = [c.to_pylist() for c in table.columns]
-            _f(iter([T.Row._make(names, vals) for vals in zip(*cols)]))
+            _f(iter(T.table_to_rows(table)))
             return None
         self._run("py_partition", {"fn": run})
 
@@ -555,6 +562,9 @@ class _NAFunctions:
     def __init__(self, df: DataFrame):
         self._df = df
 
+    def replace(self, to_replace, value=None, subset=None):
+        return self._df.replace(to_replace, value, subset)
+
     def fill(self, value, subset=None):
         return self._df.fillna(value, subset)
 
@@ -562,8 +572,22 @@ class _NAFunctions:
         return self._df.dropna(how, thresh, subset)
 
 
+def _show_text(v) -> str:
+    if v is None:
+        return "null"
+    if isinstance(v, bool):
+        return "true" if v else "false"
+    if isinstance(v, dict):                             # a struct (maps come out of Arrow as lists of pairs)
+        return "{" + ", ".join(_show_text(x) for x in v.values()) + "}"
+    if isinstance(v, list) and v and all(isinstance(x, tuple) and len(x) == 2 for x in v):
+        return "{" + ", ".join(f"{_show_text(k)} -> {_show_text(x)}" for k, x in v) + "}"
+    if isinstance(v, (list, tuple)):
+        return "[" + ", ".join(_show_text(x) for x in v) + "]"
+    return str(v)
+
+
 def _fmt(v, truncate: bool) -> str:
-    s = "null" if v is None else str(v)
+    s = _show_text(v)
     return s[:17] + "..." if truncate and len(s) > 20 else s
 
 

@@ -148,6 +148,22 @@ def write_partition(table: pa.Table, idx: int, args: Dict[str, Any]) -> int:
     return table.num_rows
 
 
+def _stable_hashes(col: pa.Array) -> np.ndarray:
+    """Per-value 64-bit hashes that agree ACROSS PROCESSES (Python's ``hash(str)`` is salted per process, which
+    would send equal keys to different shuffle partitions on different executors)."""
+    import hashlib
+
+    def digest(value) -> int:
+        return int.from_bytes(hashlib.blake2b(repr(value).encode(), digest_size=8).digest(), "little")
+    try:
+        uniq = pc.unique(col)
+        codes = pc.index_in(col, value_set=uniq).to_numpy(zero_copy_only=False)
+        table = np.array([digest(v) for v in uniq.to_pylist()] + [0], dtype=np.uint64)
+        return table[np.where(np.isnan(codes.astype(np.float64)), len(table) - 1, codes).astype(np.int64)]
+    except (pa.ArrowNotImplementedError, pa.ArrowInvalid):        # nested types: hash row by row
+        return np.array([digest(v) for v in col.to_pylist()], dtype=np.uint64)
+
+
 def execute_action(plan: Plan, idx: int, action: str, args: Dict[str, Any], blocks: Dict) -> Any:
     """Run one partition task.  Shared by executor actors and the in-process local backend."""
     if action == "load_block":
@@ -196,7 +212,7 @@ def execute_action(plan: Plan, idx: int, action: str, args: Dict[str, Any], bloc
                 if pa.types.is_integer(col.type) or pa.types.is_floating(col.type):
                     v = np.nan_to_num(col.to_numpy(zero_copy_only=False)).astype(np.int64).view(np.uint64)
                 else:
-                    v = np.array([hash(x) & 0xFFFFFFFFFFFF for x in col.to_pylist()], dtype=np.uint64)
+                    v = _stable_hashes(col)
                 h = (h ^ v) * np.uint64(0x9E3779B97F4A7C15)
             dest = (h % np.uint64(n_out)).astype(np.int64)
         else:

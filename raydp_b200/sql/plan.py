@@ -402,7 +402,18 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
         wanted = [c for c in list(keys) + rest_left + rest_right if c in out.column_names]
         return out.select(wanted) if wanted != out.column_names else out
     if kind == "distinct":
-        return table.group_by(table.column_names, use_threads=False).aggregate([])
+        try:
+            return table.group_by(table.column_names, use_threads=False).aggregate([])
+        except (pa.ArrowNotImplementedError, pa.ArrowInvalid):
+            # nested columns (arrays, structs, maps) are not hashable by Arrow's group-by: compare by value
+            seen, keep = set(), []
+            cols = [c.to_pylist() for c in table.columns]
+            for i, row in enumerate(zip(*cols)):
+                key = repr(row)
+                if key not in seen:
+                    seen.add(key)
+                    keep.append(i)
+            return table.take(pa.array(keep, type=pa.int64()))
     if kind == "distinct_subset":          # keep the first row of every key combination
         if table.num_rows == 0:
             return table

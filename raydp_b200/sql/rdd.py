@@ -79,9 +79,7 @@ class DataFrameRDD:
         tables = self._df._run("collect")
         parts = []
         for t in tables:
-            names = t.column_names
-            cols = [c.to_pylist() for c in t.columns]
-            parts.append([T.Row._make(names, vals) for vals in zip(*cols)] if cols else [])
+            parts.append(T.table_to_rows(t))
         return RDD(self._df._session, parts)
 
     def mapPartitions(self, f, preservesPartitioning: bool = False) -> RDD:

@@ -397,3 +397,37 @@ class Row(tuple):
         if self.__fields__:
             return "Row(" + ", ".join(f"{k}={v!r}" for k, v in zip(self.__fields__, self)) + ")"
         return "Row" + tuple.__repr__(self)
+
+
+def _python_value(value, t: pa.DataType):
+    """Arrow's ``to_pylist`` shapes -> what PySpark hands back: structs as Row, maps as dict (recursively)."""
+    if value is None:
+        return None
+    if pa.types.is_struct(t):
+        return Row._make([f.name for f in t], [_python_value(value.get(f.name), f.type) for f in t])
+    if pa.types.is_map(t):
+        return {_python_value(k, t.key_type): _python_value(v, t.item_type) for k, v in value}
+    if pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_fixed_size_list(t):
+        inner = t.value_type
+        if _is_nested(inner):
+            return [_python_value(v, inner) for v in value]
+    return value
+
+
+def _is_nested(t: pa.DataType) -> bool:
+    return pa.types.is_struct(t) or pa.types.is_map(t) or pa.types.is_list(t) or pa.types.is_large_list(t) or \
+        pa.types.is_fixed_size_list(t)
+
+
+def table_to_rows(table: pa.Table) -> List["Row"]:
+    names = table.column_names
+    if not names:
+        return []
+    cols = []
+    for field, col in zip(table.schema, table.columns):
+        values = col.to_pylist()
+        if _is_nested(field.type) and not (
+                (pa.types.is_list(field.type) or pa.types.is_large_list(field.type)) and not _is_nested(field.type.value_type)):
+            values = [_python_value(v, field.type) for v in values]
+        cols.append(values)
+    return [Row._make(names, vals) for vals in zip(*cols)]

@@ -290,3 +290,22 @@ def test_wider_sql_surface_runs_on_executors(spark_on_ray_2_executors, tmp_path)
     df.createOrReplaceTempView("wide_t")
     rows = spark.sql("select k, sum(v) s from wide_t group by k having sum(v) > 2 order by s desc").collect()
     assert [(r.k, r.s) for r in rows] == [(None, 9), ("b", 5), ("a", 3)]
+
+
+def test_shuffle_keys_hash_the_same_on_every_executor(spark_on_ray_2_executors):
+    """String keys must land in the same shuffle partition whichever executor process hashes them
+    (``hash(str)`` is salted per process): distinct / dropDuplicates / groupBy after repartition rely on it."""
+    import subprocess
+    import sys
+    spark = spark_on_ray_2_executors
+    words = [f"w{i % 7}" for i in range(200)]
+    df = spark.createDataFrame([(w, i) for i, w in enumerate(words)], ["w", "i"]).repartition(4)
+    assert df.select("w").distinct().count() == 7
+    assert df.dropDuplicates(["w"]).count() == 7
+    parts = df.repartition(3, "w").rdd.mapPartitions(lambda rows: [sorted({r.w for r in rows})]).collect()
+    assert sorted(w for p in parts for w in p) == sorted(set(words))          # no key in two partitions
+    code = ("import pyarrow as pa; from raydp_b200.sql.executor import _stable_hashes; "
+            "print(_stable_hashes(pa.array(['a', 'b', None, 'a'])).tolist())")
+    outs = {subprocess.run([sys.executable, "-c", code], capture_output=True, text=True,
+                           env=dict(__import__('os').environ, PYTHONHASHSEED=seed)).stdout for seed in ("1", "2")}
+    assert len(outs) == 1 and "[" in outs.pop()

@@ -123,8 +123,8 @@ def test_array_map_struct_json_functions(spark):
     assert row["amax"] == 3 and row["amin"] == 1 and row["sa"] == [3, 2, 1, 1, None] and row["as_"] == [1, 1, 2, 3, None]
     assert row["ea"] == 1 and row["gi"] == 3 and row["sl"] == [1, None] and row["ap"] == 2 and row["ar"] == [3, None, 2]
     assert row["au"] == [3, 1, None, 2, 7] and row["ai"] == [1, 2] and row["ae"] == [3, None, 2] and row["rp"] == ["z", "z"]
-    assert row["sq"] == [1, 4, 7] and row["fl"] == ["a", "b", "a", "b"] and row["az"][1] == {"0": "b", "1": "b"}
-    assert row["gj"] == "2" and row["tj"] == '{"ys":["a","b"],"n":1}' and row["fj"] == {"c": "x", "a": {"b": [1, 2]}}
+    assert row["sq"] == [1, 4, 7] and row["fl"] == ["a", "b", "a", "b"] and row["az"][1].asDict() == {"0": "b", "1": "b"}
+    assert row["gj"] == "2" and row["tj"] == '{"ys":["a","b"],"n":1}' and row["fj"].asDict(True) == {"c": "x", "a": {"b": [1, 2]}}
     assert dict(row["m"]) == {"k": 1} and row["cp"] == [3, 1, 2, 1] and row["app"] == ["a", "b", "c"]
     maps = df.select(F.create_map(F.lit("k"), F.size("xs"), F.lit("j"), F.lit(0)).alias("m")) \
         .select(F.map_keys("m").alias("k"), F.map_values("m").alias("v"), F.col("m")["k"].alias("at"),
@@ -135,7 +135,7 @@ def test_array_map_struct_json_functions(spark):
     st = df.select(F.struct(F.size("xs").alias("n"), F.col("ys")).alias("s")) \
         .select(F.col("s").getField("n").alias("n"), F.col("s")["ys"].alias("ys"), F.col("s").withField("z", F.lit(1)).alias("w"),
                 F.col("s").dropFields("ys").alias("d"), "s.*").collect()[0]
-    assert st[0] == 5 and st[1] == ["a", "b"] and st["w"] == {"n": 5, "ys": ["a", "b"], "z": 1} and st["d"] == {"n": 5}
+    assert st[0] == 5 and st[1] == ["a", "b"] and st["w"].asDict() == {"n": 5, "ys": ["a", "b"], "z": 1} and st["d"].asDict() == {"n": 5} and st["w"].z == 1
     assert st[4] == 5 and st[5] == ["a", "b"]
 
 
