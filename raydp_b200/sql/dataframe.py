@@ -323,7 +323,10 @@ class DataFrame(DataFrameExtras):
         df, keys = self, []
         for c in cols:
             if isinstance(c, str) or c._kind == "col":
-                keys.append(c if isinstance(c, str) else c._args[0])
+                name = c if isinstance(c, str) else c._args[0]
+                if name not in df.columns and "." in name and name.split(".", 1)[1] in df.columns:
+                    name = name.split(".", 1)[1]            # alias.column of a SQL query
+                keys.append(name)
             else:                                   # groupBy(F.year("ts"), (col("a") % 2).alias("odd"))
                 name = c._output_name()
                 df = df.withColumn(name, c)

@@ -393,7 +393,7 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
                "outer": "full outer", "full": "full outer", "full_outer": "full outer",
                "left_semi": "left semi", "leftsemi": "left semi", "left_anti": "left anti",
                "leftanti": "left anti"}[how]
-        out = table.join(right, keys=keys, right_keys=right_keys, join_type=how, use_threads=False)
+        out = _join_tables(table, right, list(keys), list(right_keys), how)
         if how in ("left semi", "left anti") or len(set(out.column_names)) != len(out.column_names):
             return out
         # Spark's layout: join keys, then the other left columns, then the other right columns
@@ -469,6 +469,44 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
             cols.append(value.take(parent_idx))
         return pa.table(cols, names=names)
     raise NotImplementedError(f"operator {kind!r}")
+
+
+def _nested(t: pa.DataType) -> bool:
+    return pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_struct(t) or pa.types.is_map(t) or \
+        pa.types.is_fixed_size_list(t)
+
+
+def _join_tables(left: pa.Table, right: pa.Table, keys: List[str], right_keys: List[str], how: str) -> pa.Table:
+    """Hash join.  Arrow's join kernel carries only flat payload columns, so when a side has arrays / structs /
+    maps the join runs on (keys, row number) and the payload is gathered by row number afterwards."""
+    payload_nested = any(_nested(f.type) for f in left.schema if f.name not in keys) or \
+        any(_nested(f.type) for f in right.schema if f.name not in right_keys)
+    if not payload_nested:
+        return left.join(right, keys=keys, right_keys=right_keys, join_type=how, use_threads=False)
+    slim_l = left.select(keys).append_column("__li", pa.array(np.arange(left.num_rows, dtype=np.int64)))
+    slim_r = right.select(right_keys).append_column("__ri", pa.array(np.arange(right.num_rows, dtype=np.int64)))
+    joined = slim_l.join(slim_r, keys=keys, right_keys=right_keys, join_type=how, use_threads=False)
+    cols, names = [], []
+
+    def gather(source: pa.Table, index_name: str, skip: List[str]) -> None:
+        if index_name not in joined.column_names:
+            return
+        idx = joined.column(index_name).combine_chunks()
+        for f in source.schema:
+            if f.name in skip:
+                continue
+            names.append(f.name)
+            cols.append(source.column(f.name).combine_chunks().take(idx))       # null index -> null value
+    for k in keys:
+        names.append(k)
+        cols.append(joined.column(k))
+    if how in ("right semi", "right anti"):
+        gather(right, "__ri", right_keys)
+    else:
+        gather(left, "__li", keys)
+        if how not in ("left semi", "left anti"):
+            gather(right, "__ri", right_keys)
+    return pa.table(cols, names=names)
 
 
 def _compatible(value, arrow_type: pa.DataType) -> bool:

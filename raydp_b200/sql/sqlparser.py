@@ -850,6 +850,8 @@ def _parse_core(p: _Parser, session, tail: bool = True):
             elif e._name is None and _signature(e) in select_sigs:
                 key_exprs[i] = select_sigs[_signature(e)]
         keys = [e._output_name() for e in key_exprs]
+        keys = [k.split(".", 1)[1] if k not in df.columns and "." in k and k.split(".", 1)[1] in df.columns else k
+                for k in keys]
         key_sigs = {_signature(Column(e._kind, e._args)): e._output_name() for e in key_exprs}
         agg_items: List[Column] = []
         registry: Dict[str, str] = {}

@@ -309,3 +309,56 @@ def test_shuffle_keys_hash_the_same_on_every_executor(spark_on_ray_2_executors):
     outs = {subprocess.run([sys.executable, "-c", code], capture_output=True, text=True,
                            env=dict(__import__('os').environ, PYTHONHASHSEED=seed)).stdout for seed in ("1", "2")}
     assert len(outs) == 1 and "[" in outs.pop()
+
+
+def _backend_queries(spark):
+    import numpy as np
+    from raydp_b200.sql import functions as F
+    from raydp_b200.sql.window import Window
+    rng = np.random.default_rng(0)
+    rows = [(f"k{int(rng.integers(0, 9))}", int(rng.integers(0, 50)), float(rng.normal()),
+             None if i % 11 == 0 else f"2020-0{1 + i % 9}-1{i % 9}", [int(i % 3), int(i % 5)]) for i in range(500)]
+    df = spark.createDataFrame(rows, ["k", "v", "x", "d", "a"]).repartition(5)
+    other = spark.createDataFrame([(f"k{i}", i * 10) for i in range(0, 12, 2)], ["k", "w"])
+    df.createOrReplaceTempView("t_diff")
+    other.createOrReplaceTempView("o_diff")
+    out = {
+        "group": df.groupBy("k").agg(F.sum("v"), F.avg("x"), F.countDistinct("v"), F.collect_set("v"),
+                                     F.percentile_approx("x", 0.5), F.stddev("x"), F.max_by("v", "x")),
+        "distinct": df.select("k", "d").distinct(),
+        "dropdup": df.dropDuplicates(["k"]).select("k"),
+        "join_left_nested_payload": df.join(other, "k", "left").groupBy("w").count(),
+        "join_full": df.select("k").distinct().join(other, "k", "full"),
+        "window": df.withColumn("r", F.dense_rank().over(Window.partitionBy("k").orderBy(F.desc("v"))))
+                    .filter("r <= 2").select("k", "v", "r").distinct(),
+        "sql": spark.sql("select t.k, count(*) c, sum(w) sw from t_diff t join o_diff o on t.k = o.k "
+                         "where v > 10 group by t.k having count(*) > 3"),
+        "explode": df.select("k", F.explode("a").alias("e")).groupBy("k", "e").count(),
+        "dates": df.groupBy(F.month(F.to_date("d")).alias("m")).agg(F.count("*").alias("n"), F.min("d")),
+        "pivot": df.groupBy("k").pivot("v", [1, 2, 3]).agg(F.count("*")),
+        "setops": df.select("k").subtract(other.select("k")),
+        "rollup": df.rollup("k").agg(F.sum("v").alias("s")),
+        "repartition_by_key": df.repartition(3, "k").groupBy(F.spark_partition_id().alias("p"))
+                                .agg(F.countDistinct("k").alias("nk")).agg(F.sum("nk")),
+        "top": df.orderBy("v", "x").limit(7).select("v", "x"),
+    }
+
+    def norm(frame):
+        def key(v):
+            if isinstance(v, float):
+                return round(v, 9)
+            if isinstance(v, list):
+                return tuple(sorted(v, key=repr))
+            return v
+        return sorted((tuple(key(v) for v in r) for r in frame.collect()), key=repr)
+    return {name: norm(frame) for name, frame in out.items()}
+
+
+def test_local_and_cluster_backends_agree(spark_session, spark_on_ray_2_executors):
+    """The same queries through the in-process backend and through two executor actors: aggregation,
+    distinct, joins (nested payload columns included), windows, SQL, generators, pivots, set operations."""
+    local = _backend_queries(spark_session)
+    cluster = _backend_queries(spark_on_ray_2_executors)
+    for name in local:
+        assert local[name] == cluster[name], name
+    assert local["repartition_by_key"] == [(9,)] and len(local["group"]) == 9 and len(local["sql"]) > 0
