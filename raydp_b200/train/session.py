@@ -95,4 +95,13 @@ def report(metrics: Optional[Dict[str, Any]] = None, checkpoint=None, **kwargs) 
 
 
 def get_checkpoint():
-    return None
+    """The checkpoint to resume from, or ``None``: ``TorchTrainer(resume_from_checkpoint=...)`` on the first
+    attempt, the last checkpoint reported before a failure on a retry (``FailureConfig.max_failures``)."""
+    import os
+    from raydp_b200.train.checkpoint import Checkpoint
+    marker = os.path.join(get_session().storage_dir, ".resume_from")
+    if not os.path.exists(marker):
+        return None
+    with open(marker, "r", encoding="utf-8") as fh:
+        path = fh.read().strip()
+    return Checkpoint(path) if path and os.path.isdir(path) else None

@@ -135,6 +135,7 @@ class TorchTrainer:
         self._run = run_config or RunConfig()
         self._torch = torch_config or TorchConfig()
         self._datasets = {k: v for k, v in (datasets or {}).items() if v is not None}
+        self._resume = resume_from_checkpoint
 
     # ------------------------------------------------------------------ shards
     def _shards_for(self, world: int) -> List[Dict[str, Any]]:
@@ -159,6 +160,7 @@ class TorchTrainer:
         max_failures = self._run.failure_config.max_failures
         attempt, last_error = 0, None
         while True:
+            self._publish_resume_point(storage, attempt, self._resume)
             try:
                 spmd = _spmd_world()
                 if spmd is not None and spmd == self._scaling.num_workers:
@@ -172,6 +174,26 @@ class TorchTrainer:
                 if max_failures >= 0 and attempt > max_failures:
                     raise TrainingFailedError(
                         f"training failed after {attempt} attempt(s): {exc}") from exc
+
+    @staticmethod
+    def _publish_resume_point(storage: str, attempt: int, initial=None) -> None:
+        """What ``train.get_checkpoint()`` answers inside the workers: the checkpoint given to the trainer
+        on the first attempt, the newest checkpoint the failed attempt reported afterwards (so a training
+        loop that reports checkpoints resumes mid-run instead of starting over)."""
+        marker = os.path.join(storage, ".resume_from")
+        path = None
+        if attempt > 0:
+            found = [os.path.join(storage, d) for d in os.listdir(storage) if d.startswith("checkpoint_")]
+            if found:
+                path = max(found, key=os.path.getmtime)
+        if path is None and initial is not None:
+            path = initial.path
+        if path is None:
+            if attempt == 0 and os.path.exists(marker):
+                os.remove(marker)
+            return
+        with open(marker, "w", encoding="utf-8") as fh:
+            fh.write(path)
 
     def _result(self, reports: List[Dict[str, Any]], storage: str) -> Result:
         history = [r["metrics"] for r in reports if r["metrics"]]

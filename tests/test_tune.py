@@ -66,3 +66,35 @@ def test_legacy_trainer_run_callbacks_and_tune_trainable(ray_cluster):
     analysis = tune.run(trainable, config={"x": tune.grid_search([3.0, 1.0])}, metric="loss", mode="min",
                         max_concurrent_trials=1)
     assert analysis.get_best_config() == {"x": 1.0}
+
+
+def test_trainer_resumes_from_last_reported_checkpoint(ray_cluster, tmp_path):
+    """A worker failure mid-run restarts the group (``FailureConfig``); ``train.get_checkpoint()`` then
+    returns the newest checkpoint reported before the failure, so the loop continues instead of restarting.
+    ``resume_from_checkpoint`` seeds the first attempt the same way."""
+    import os
+    from raydp_b200.train import (Checkpoint, FailureConfig, RunConfig, ScalingConfig, TorchTrainer, get_checkpoint,
+                                  report)
+    flag = str(tmp_path / "crashed_once")
+
+    def loop(config):
+        start = 0
+        ckpt = get_checkpoint()
+        if ckpt is not None:
+            start = ckpt.to_dict()["epoch"] + 1
+        for epoch in range(start, 4):
+            if epoch == 2 and not os.path.exists(config["flag"]):
+                open(config["flag"], "w").close()
+                raise RuntimeError("injected failure")
+            report({"epoch": epoch, "started_at": start}, checkpoint=Checkpoint.from_dict({"epoch": epoch}))
+
+    trainer = TorchTrainer(loop, train_loop_config={"flag": flag}, scaling_config=ScalingConfig(num_workers=1),
+                           run_config=RunConfig(storage_path=str(tmp_path), name="resume",
+                                                failure_config=FailureConfig(max_failures=1)))
+    result = trainer.fit()
+    assert result.metrics["epoch"] == 3 and result.metrics["started_at"] == 2          # resumed after epoch 1
+    assert [m["epoch"] for m in result.metrics_history] == [2, 3]
+    again = TorchTrainer(loop, train_loop_config={"flag": flag}, scaling_config=ScalingConfig(num_workers=1),
+                         run_config=RunConfig(storage_path=str(tmp_path), name="seeded"),
+                         resume_from_checkpoint=Checkpoint.from_dict({"epoch": 2})).fit()
+    assert [m["epoch"] for m in again.metrics_history] == [3] and again.checkpoint.to_dict() == {"epoch": 3}
