@@ -684,8 +684,14 @@ class GroupedData:
         aggs: List[Tuple[str, Optional[str]]] = []
         params: List[tuple] = []
         in_types: List[Optional[pa.DataType]] = []
+        base_schema = df._arrow_schema()
+        numeric_only = {"sum", "mean", "stddev", "variance", "stddev_pop", "var_pop", "skewness", "kurtosis", "median",
+                        "product", "sum_distinct", "percentile"}
         for i, leaf in enumerate(leaves):
             fn, target = leaf._args[0], leaf._args[1]
+            if target is not None and target._kind == "col" and fn in numeric_only and \
+                    target._args[0] in base_schema.names and pa.types.is_string(base_schema.field(target._args[0]).type):
+                target = target.cast("double")          # Spark's implicit cast: unparsable text counts as NULL
             if target is None:
                 col_name = None
             elif target._kind == "col":

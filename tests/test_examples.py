@@ -61,6 +61,29 @@ def test_reference_raytrain_example_runs_unchanged(tmp_path):
     assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
 
 
+def test_reference_tutorial_notebook_code_runs(tmp_path):
+    """The code cells of ``tutorials/pytorch_example.ipynb`` (shell cells dropped, the dataset path pointed
+    at the file in the reference tree): rollup, describe, ``avg`` over a text column with ``N/A`` entries,
+    ``@udf`` cleaning, ``random_split``, ``TorchEstimator`` with per-column dtypes and torchmetrics."""
+    import json
+    import pytest
+    nb = "/root/reference/tutorials/pytorch_example.ipynb"
+    data = "/root/reference/tutorials/dataset/healthcare-dataset-stroke-data.csv"
+    if not (os.path.exists(nb) and os.path.exists(data)):
+        pytest.skip("reference tutorials not mounted")
+    cells = json.load(open(nb))["cells"]
+    code = "\n\n".join("".join(c["source"]) for c in cells if c["cell_type"] == "code")
+    code = "\n".join(line for line in code.splitlines() if not line.startswith("!"))
+    code = code.replace("/content/healthcare-dataset-stroke-data.csv", data)
+    script = tmp_path / "pytorch_example.py"
+    script.write_text(code)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.run([sys.executable, "-m", "raydp_b200.compat", str(script)], cwd=str(tmp_path), env=env,
+                          capture_output=True, text=True, timeout=600)
+    assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
+    assert "|  null| 5110|" in proc.stdout                        # the rollup totals of the 5110-row dataset
+
+
 def test_reference_unit_tests_pass_unchanged(tmp_path):
     """The reference's own pytest files (copied, not edited) run against this framework through the
     ``ray`` / ``pyspark`` aliases.  The quick ones run here; test_spark_cluster / test_torch / test_mpi /
