@@ -190,10 +190,93 @@ def result_type(fn: str, input_type: pa.DataType) -> Optional[pa.DataType]:
     return pa.float64()
 
 
+def _reduce_groups_numeric(fn: str, lists: pa.Array, params: tuple) -> Optional[pa.Array]:
+    """Segmented numpy versions of the numeric reducers (one pass over all groups instead of a Python loop
+    per group): moments through ``bincount``, order statistics through one (group, value) sort."""
+    vtype = lists.type.value_type
+    if not (pa.types.is_integer(vtype) or pa.types.is_floating(vtype)) or lists.null_count:
+        return None
+    if fn not in ("median", "percentile_approx", "stddev_pop", "var_pop", "stddev_samp", "var_samp", "skewness",
+                  "kurtosis", "count_distinct", "approx_count_distinct", "sum_distinct", "product"):
+        return None
+    if fn == "percentile_approx" and isinstance(params[0], (list, tuple)):
+        return None
+    g = len(lists)
+    lengths = np.asarray(pc.list_value_length(lists)).astype(np.int64)
+    group = np.repeat(np.arange(g, dtype=np.int64), lengths)
+    flat = pc.list_flatten(lists)
+    keep = np.asarray(pc.is_valid(flat))
+    if pa.types.is_floating(vtype):
+        keep &= ~np.asarray(pc.fill_null(pc.is_nan(flat), False)) if fn in ("median", "percentile_approx") else True
+    raw = flat.to_numpy(zero_copy_only=False)
+    group, vals = group[keep], raw[keep]
+    x = vals.astype(np.float64)
+    n = np.bincount(group, minlength=g).astype(np.float64)
+    empty = n == 0
+    if fn in ("median", "percentile_approx"):
+        order = np.lexsort((x, group))
+        sorted_vals, starts = vals[order], np.concatenate([[0], np.cumsum(n)[:-1]]).astype(np.int64)
+        cnt = n.astype(np.int64)
+        if fn == "median":
+            lo = starts + np.maximum(cnt - 1, 0) // 2
+            hi = starts + cnt // 2
+            safe_lo, safe_hi = np.minimum(lo, max(len(x) - 1, 0)), np.minimum(hi, max(len(x) - 1, 0))
+            out = (sorted_vals[safe_lo].astype(np.float64) + sorted_vals[safe_hi].astype(np.float64)) / 2.0 if len(x) else \
+                np.zeros(g)
+            return pa.array(out, mask=empty)
+        q = float(params[0])
+        k = np.maximum(np.ceil(q * cnt).astype(np.int64) - 1, 0)
+        idx = np.minimum(starts + k, max(len(x) - 1, 0))
+        out = sorted_vals[idx] if len(x) else np.zeros(g, dtype=vals.dtype)
+        return pa.array(out, mask=empty)
+    if fn in ("count_distinct", "approx_count_distinct", "sum_distinct"):
+        pairs = np.unique(np.stack([group.astype(np.float64), x], axis=1), axis=0) if len(x) else np.zeros((0, 2))
+        gid = pairs[:, 0].astype(np.int64)
+        if fn == "sum_distinct":
+            total = np.bincount(gid, weights=pairs[:, 1], minlength=g)
+            if pa.types.is_integer(vtype):
+                return pa.array(total.astype(np.int64), mask=empty)
+            return pa.array(total, mask=empty)
+        return pa.array(np.bincount(gid, minlength=g).astype(np.int64))
+    if fn == "product":
+        out = np.ones(g)
+        np.multiply.at(out, group, x)
+        return pa.array(out, mask=empty)
+    safe_n = np.maximum(n, 1.0)
+    mean = np.bincount(group, weights=x, minlength=g) / safe_n
+    d = x - mean[group]
+    m2 = np.bincount(group, weights=d * d, minlength=g)
+    if fn in ("stddev_pop", "var_pop", "stddev_samp", "var_samp"):
+        ddof = 0.0 if fn.endswith("_pop") else 1.0
+        bad = (n - ddof) <= 0
+        var = m2 / np.where(bad, 1.0, n - ddof)
+        return pa.array(np.sqrt(var) if fn.startswith("stddev") else var, mask=bad)
+    m2 = m2 / safe_n
+    if fn == "skewness":
+        m3 = np.bincount(group, weights=d ** 3, minlength=g) / safe_n
+        bad = empty | (m2 <= 0)
+        return pa.array(m3 / np.where(bad, 1.0, m2) ** 1.5, mask=bad)
+    m4 = np.bincount(group, weights=d ** 4, minlength=g) / safe_n
+    bad = empty | (m2 <= 0)
+    return pa.array(m4 / np.where(bad, 1.0, m2 * m2) - 3.0, mask=bad)
+
+
 def reduce_groups(fn: str, lists: pa.ChunkedArray, params: tuple, input_type: pa.DataType) -> pa.Array:
     """Final stage of a gathered aggregate: one list of values per group -> one value per group."""
     if isinstance(lists, pa.ChunkedArray):
         lists = lists.combine_chunks()
+    if fn == "collect_list" and lists.null_count == 0 and lists.values.null_count == 0:
+        return lists                                    # already one list per group, nothing to drop
+    if fn in ("first_value", "any_value", "first", "last", "last_value") and not (params and params[-1]) \
+            and len(lists) and lists.null_count == 0:
+        lengths = pc.list_value_length(lists)
+        if pc.min(lengths).as_py() > 0:                 # vectorised: first / last element of every group
+            offsets = np.asarray(lists.offsets)
+            pick = offsets[:-1] if fn in ("first_value", "any_value", "first") else offsets[1:] - 1
+            return lists.values.take(pa.array(pick))
+    fast = _reduce_groups_numeric(fn, lists, params)
+    if fast is not None:
+        return fast
     out: List[Any] = []
     for i in range(len(lists)):
         cell = lists[i]

@@ -480,6 +480,8 @@ class SparkSession:
         self._stopped = False
         self._tracked_refs: List[Any] = []
         self._conf.set("spark.app.id", self._app_id)
+        self._conf.set("spark.app.name", self._app_name)
+        self._conf.set("spark.master", self._master)
         self._conf.set("spark.sql.session.timeZone", options.get("spark.sql.session.timeZone", "UTC"))
         if self._master.startswith("local"):
             spec = self._master[len("local"):].strip("[]")
