@@ -225,6 +225,21 @@ class _Frame:
             var = np.maximum(var, 0.0)
             out = np.sqrt(var) if fn.startswith("stddev") else var
             return pa.array(out, mask=denom <= 0)
+        if fn in ("min", "max") and numeric and not pa.types.is_boolean(values.type) and n and \
+                np.array_equal(lo, self.seg_start):
+            # frames that start at the partition start (running and whole-partition frames): a per-partition
+            # cumulative min / max, read at each row's frame end
+            import pandas as pd
+            x = np.asarray(pc.cast(values, pa.float64()).to_numpy(zero_copy_only=False), dtype=np.float64)
+            x = np.where(valid, x, np.inf if fn == "min" else -np.inf)
+            seg_id = np.cumsum(self.part_change) - 1
+            grouped = pd.Series(x).groupby(seg_id)
+            acc = (grouped.cummin() if fn == "min" else grouped.cummax()).to_numpy()
+            cnt_prefix = np.concatenate([[0], np.cumsum(valid)])
+            none = (cnt_prefix[hi_c + 1] - cnt_prefix[lo_c] == 0) | empty
+            out_vals = acc[hi_c]
+            result = pa.array(np.where(none, 0.0, out_vals), mask=none)
+            return pc.cast(result, values.type) if pa.types.is_integer(values.type) else result
         # everything else: evaluate the frame slice; frames shared by a whole group are computed once
         from raydp_b200.sql.aggregates import reduce_values
         out: List[Any] = [None] * n
