@@ -1378,3 +1378,29 @@ def _drop_fields(args, n, ctx):
     a, drop = _arr(args[0], n), set(args[1])
     names = [f.name for f in a.type if f.name not in drop]
     return pa.StructArray.from_arrays([pc.struct_field(a, nm) for nm in names], names=names, mask=pc.is_null(a))
+
+
+@scalar("add_interval")
+def _add_interval(args, n, ctx):
+    """``date_or_timestamp + INTERVAL``: months move the calendar month (clamped to its last day), days and
+    the sub-day part are exact.  A date stays a date unless the interval has a time part."""
+    months, days, micros = int(_py(args[1])), int(_py(args[2])), int(_py(args[3]))
+    a = _arr(args[0], n)
+    as_date = pa.types.is_date(a.type)
+    if as_date and micros == 0:
+        out = a
+        if months:
+            out = _map_rows(_add_months_py, n, out, pa.scalar(months), type=pa.date32())
+        if days:
+            out = pc.cast(pc.add(pc.cast(out, pa.int32()), pa.scalar(days, pa.int32())), pa.date32())
+        return out
+    ts = _as_ts(a, n, ctx)
+    if months:
+        def shift(t):
+            d = _add_months_py(t.date(), months)
+            return t.replace(year=d.year, month=d.month, day=d.day)
+        ts = _map_rows(shift, n, ts, type=pa.timestamp("us"))
+    delta = days * 86400 * 10 ** 6 + micros
+    if delta:
+        ts = pc.cast(pc.add(pc.cast(ts, pa.int64()), delta), pa.timestamp("us"))
+    return ts

@@ -222,9 +222,16 @@ class _Parser:
         left = self.multiplicative()
         while True:
             if self.op("+"):
-                left = left + self.multiplicative()
+                right = self.multiplicative()
+                if right._kind == "interval":
+                    left = self._shift(left, right, 1)
+                elif left._kind == "interval":
+                    left = self._shift(right, left, 1)
+                else:
+                    left = left + right
             elif self.op("-"):
-                left = left - self.multiplicative()
+                right = self.multiplicative()
+                left = self._shift(left, right, -1) if right._kind == "interval" else left - right
             elif self.op("||"):
                 left = F.concat(left, self.multiplicative())
             else:
@@ -290,7 +297,8 @@ class _Parser:
             text = self.t[self.i - 1][1]
             return F.to_date(F.lit(text)) if low == "date" else F.to_timestamp(F.lit(text))
         if low == "interval":
-            raise SqlError("INTERVAL literals are not supported; use date_add / add_months")
+            self.i += 1
+            return self._interval()
         if low == "cast" and self.peek(1) == ("op", "("):
             self.i += 2
             inner = self.expr()
@@ -310,6 +318,57 @@ class _Parser:
                 return F.col(v + ".*")
             v = v + "." + self.name()
         return self._postfix(F.col(v))
+
+    _INTERVAL_UNITS = {"year": (12, 0, 0), "month": (1, 0, 0), "week": (0, 7, 0), "day": (0, 1, 0),
+                       "hour": (0, 0, 3600 * 10 ** 6), "minute": (0, 0, 60 * 10 ** 6), "second": (0, 0, 10 ** 6),
+                       "millisecond": (0, 0, 1000), "microsecond": (0, 0, 1)}
+
+    def _interval(self) -> Column:
+        """``INTERVAL 3 DAY``, ``INTERVAL '3' DAY``, ``INTERVAL '1 day 2 hours'``, ``INTERVAL 1 YEAR 2 MONTHS``."""
+        months = days = micros = 0
+
+        def add(qty: float, unit: str) -> None:
+            nonlocal months, days, micros
+            key = unit.lower().rstrip("s")
+            if key not in self._INTERVAL_UNITS:
+                raise SqlError(f"unknown interval unit {unit!r}")
+            m, d, u = self._INTERVAL_UNITS[key]
+            months += int(qty * m)
+            days += int(qty * d)
+            micros += int(qty * u)
+        seen = False
+        while True:
+            kind, v = self.peek()
+            sign = 1
+            if kind == "op" and v == "-":
+                self.i += 1
+                sign, (kind, v) = -1, self.peek()
+            if kind == "num":
+                self.i += 1
+                add(sign * float(v), self.name())
+            elif kind == "str":
+                self.i += 1
+                parts = v.split()
+                if len(parts) == 1:
+                    add(sign * float(parts[0]), self.name())
+                else:
+                    for qty, unit in zip(parts[0::2], parts[1::2]):
+                        add(sign * float(qty), unit)
+            else:
+                break
+            seen = True
+            nxt = self.peek()
+            if not (nxt[0] in ("num", "str") or nxt == ("op", "-") and self.peek(1)[0] == "num" and
+                    self.peek(2)[0] == "id" and self.peek(2)[1].lower().rstrip("s") in self._INTERVAL_UNITS):
+                break
+        if not seen:
+            raise SqlError("INTERVAL needs a quantity and a unit")
+        return Column("interval", (months, days, micros))
+
+    @staticmethod
+    def _shift(value: Column, interval: Column, sign: int) -> Column:
+        months, days, micros = (sign * x for x in interval._args)
+        return Column("call", ("add_interval", (value, months, days, micros)))
 
     def _postfix(self, col: Column) -> Column:
         """``expr[index]`` / ``expr['key']`` and ``expr.field`` after a call or parenthesis."""

@@ -216,7 +216,7 @@ def test_sql_front_end_views_tables_and_expressions(spark_session, tmp_path):
     assert spark.sql("select * from t where id in (select id from t where id < 4)").count() == 4
     import pytest as _pytest
     with _pytest.raises(ValueError):
-        spark.sql("select * from t where id > interval 1 day")
+        spark.sql("select * from t where id > interval 1 fortnight")
 
 
 def test_map_in_pandas_accepts_ddl_schema(spark_session):

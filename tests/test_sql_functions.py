@@ -360,3 +360,14 @@ def test_theta_joins_pandas_udfs_schema_json(spark, people):
     assert T.StructType.fromJson(schema.jsonValue()) == schema and '"name":"k"' in schema.json()
     assert T.StructType().add("a", T.IntegerType()).add("b", "array<string>").simpleString() == \
         "struct<a:int,b:array<string>>"
+
+
+def test_sql_interval_arithmetic(spark):
+    spark.createDataFrame([("2020-01-31", "2020-01-31 10:00:00")], ["d", "t"]).createOrReplaceTempView("iv")
+    row = spark.sql("select to_date(d) + interval 1 month as a, to_date(d) - interval '3' day as b, "
+                    "to_timestamp(t) + interval 2 hours as c, to_timestamp(t) + interval '1 day 30 minutes' as e, "
+                    "date '2020-03-01' - interval 1 year 1 month as f, to_date(d) + interval 1 hour as g from iv").collect()[0]
+    assert row.a == dt.date(2020, 2, 29) and row.b == dt.date(2020, 1, 28) and row.c == dt.datetime(2020, 1, 31, 12, 0)
+    assert row.e == dt.datetime(2020, 2, 1, 10, 30) and row.f == dt.date(2019, 2, 1)
+    assert row.g == dt.datetime(2020, 1, 31, 1, 0)                       # a time part turns the date into a timestamp
+    assert spark.sql("select count(*) from iv where to_date(d) >= date '2020-02-01' - interval 7 days").collect()[0][0] == 1
