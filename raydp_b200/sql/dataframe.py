@@ -669,6 +669,30 @@ class GroupedData:
                                  f"{fn}({c})") for c, fn in exprs[0].items())
         if len(exprs) == 1 and isinstance(exprs[0], (list, tuple)):
             exprs = tuple(exprs[0])
+        # struct keys (F.window(...) is one) are grouped by their fields and put back together afterwards:
+        # Arrow's group-by hashes flat columns only
+        key_schema = self._df._arrow_schema()
+        struct_keys = {k: [f.name for f in key_schema.field(k).type] for k in self._keys
+                       if pa.types.is_struct(key_schema.field(k).type)}
+        if struct_keys:
+            from raydp_b200.sql import functions as F
+            flat_df, flat_keys = self._df, []
+            for k in self._keys:
+                if k in struct_keys:
+                    for f in struct_keys[k]:
+                        flat_df = flat_df.withColumn(f"__sk_{k}_{f}", Column("col", (k,)).getField(f))
+                        flat_keys.append(f"__sk_{k}_{f}")
+                else:
+                    flat_keys.append(k)
+            grouped = GroupedData(flat_df, flat_keys).agg(*exprs)
+            rebuilt = []
+            for k in self._keys:
+                if k in struct_keys:
+                    rebuilt.append(F.struct(*[Column("col", (f"__sk_{k}_{f}",)).alias(f) for f in struct_keys[k]]).alias(k))
+                else:
+                    rebuilt.append(Column("col", (k,)))
+            rest = [Column("col", (c,)) for c in grouped.columns if c not in flat_keys]
+            return grouped.select(*rebuilt, *rest)
         # an output may be an expression OVER aggregates (sum(a) / count(b), round(avg(x), 2)): the aggregate
         # nodes are computed first, the surrounding expression is applied to the aggregated table
         leaves: List[Column] = []

@@ -1404,3 +1404,24 @@ def _add_interval(args, n, ctx):
     if delta:
         ts = pc.cast(pc.add(pc.cast(ts, pa.int64()), delta), pa.timestamp("us"))
     return ts
+
+
+@scalar("sliding_windows")
+def _sliding_windows(args, n, ctx):
+    """Every window ``[start, start + width)`` on the ``slide`` grid that contains the timestamp, as
+    ``array<struct<start, end>>`` (earliest first); ``F.window`` explodes it."""
+    width, slide = int(_py(args[1])), int(_py(args[2]))
+    offset = int(_py(args[3])) if len(args) > 3 else 0
+    micros = pc.cast(_as_ts(args[0], n, ctx), pa.int64()).to_numpy(zero_copy_only=False)
+    mask = np.asarray(pc.is_null(_arr(args[0], n)))
+    t = np.where(mask, 0, micros).astype(np.int64)
+    last = ((t - offset) // slide) * slide + offset                    # latest window start <= t
+    per_row = -(-width // slide)                                          # ceil(width / slide) candidates
+    starts = last[:, None] - np.arange(per_row - 1, -1, -1, dtype=np.int64)[None, :] * slide
+    inside = (starts + width > t[:, None]) & ~mask[:, None]
+    lengths = inside.sum(axis=1)
+    flat = starts[inside]
+    offsets = np.concatenate([[0], np.cumsum(lengths)]).astype(np.int32)
+    structs = pa.StructArray.from_arrays([pc.cast(pa.array(flat), pa.timestamp("us")),
+                                          pc.cast(pa.array(flat + width), pa.timestamp("us"))], names=["start", "end"])
+    return pa.ListArray.from_arrays(pa.array(offsets), structs, mask=pa.array(mask))

@@ -327,13 +327,16 @@ def _duration_micros(text: str) -> int:
 
 
 def window(timeColumn, windowDuration: str, slideDuration: Optional[str] = None, startTime: Optional[str] = None):
-    """Tumbling time window: a struct ``{start, end}`` (sliding windows are not supported)."""
-    if slideDuration is not None and _plain(slideDuration) != _plain(windowDuration):
-        raise NotImplementedError("sliding windows are not supported by the built-in engine")
+    """Time windows: a struct ``{start, end}`` per row for tumbling windows; with a ``slideDuration`` every
+    window containing the timestamp (the row is repeated once per window, like Spark's Expand)."""
     width = _duration_micros(_plain(windowDuration))
-    start = Column("call", ("window_start", (as_column(timeColumn), width, 0)))
-    end = Column("call", ("window_start", (as_column(timeColumn), width, width)))
-    return struct(start.alias("start"), end.alias("end")).alias("window")
+    offset = _duration_micros(_plain(startTime)) if startTime else 0
+    slide = _duration_micros(_plain(slideDuration)) if slideDuration is not None else width
+    if slide > width:
+        raise ValueError("The slide duration must be less than or equal to the window duration")
+    # rows without a timestamp belong to no window and drop out, as in Spark
+    windows = Column("call", ("sliding_windows", (as_column(timeColumn), width, slide, offset)))
+    return Column("explode", (windows,), "window")
 
 
 # arrays / maps / structs / json ---------------------------------------------------------------------------

@@ -371,3 +371,14 @@ def test_sql_interval_arithmetic(spark):
     assert row.e == dt.datetime(2020, 2, 1, 10, 30) and row.f == dt.date(2019, 2, 1)
     assert row.g == dt.datetime(2020, 1, 31, 1, 0)                       # a time part turns the date into a timestamp
     assert spark.sql("select count(*) from iv where to_date(d) >= date '2020-02-01' - interval 7 days").collect()[0][0] == 1
+
+
+def test_time_windows_tumbling_and_sliding(spark):
+    df = spark.createDataFrame([("2020-01-01 10:07:00", 1), ("2020-01-01 10:12:00", 2), (None, 3)], ["t", "v"])
+    slid = df.groupBy(F.window("t", "10 minutes", "5 minutes")).agg(F.sum("v").alias("s")).orderBy("window").collect()
+    assert [(r.window.start.minute, r.window.end.minute, r.s) for r in slid] == [(0, 10, 1), (5, 15, 3), (10, 20, 2)]
+    tumbling = df.groupBy(F.window("t", "10 minutes")).agg(F.sum("v").alias("s")).orderBy("window").collect()
+    assert [(r.window.start.minute, r.s) for r in tumbling] == [(0, 1), (10, 2)]          # the null timestamp drops out
+    assert df.select("v", F.window("t", "10 minutes", "5 minutes")).count() == 4
+    by_struct = df.select(F.struct("v", (F.col("v") % 2).alias("odd")).alias("s")).groupBy("s").count().collect()
+    assert sorted((r.s.v, r.s.odd, r["count"]) for r in by_struct) == [(1, 1, 1), (2, 0, 1), (3, 1, 1)]
