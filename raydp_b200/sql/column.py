@@ -480,7 +480,7 @@ def parse_timestamp_strings(value):
     cleaned = pc.replace_substring_regex(cleaned, r"T", " ")
     cleaned = pc.replace_substring_regex(cleaned, r"\.\d+$", "")
     full = pc.strptime(cleaned, format="%Y-%m-%d %H:%M:%S", unit="us", error_is_null=True)
-    if full.null_count == 0:
+    if (full.is_valid if isinstance(full, pa.Scalar) else full.null_count == 0):
         return full
     day = pc.strptime(pc.utf8_trim_whitespace(cleaned), format="%Y-%m-%d", unit="us", error_is_null=True)
     minute = pc.strptime(cleaned, format="%Y-%m-%d %H:%M", unit="us", error_is_null=True)
@@ -503,7 +503,9 @@ def _call(fn: str, args: list, n: int, ctx: EvalContext):
         if len(args) == 2:  # log(base, x)
             return pc.divide(pc.ln(pc.cast(args[1], pa.float64())), pc.ln(pc.cast(x, pa.float64())))
         return pc.ln(pc.cast(x, pa.float64()))
-    if fn in ("log1p", "exp", "sqrt", "floor", "ceil", "sin", "cos", "log2", "log10"):
+    if fn in ("floor", "ceil"):                         # Spark: floor / ceil of a number is a bigint
+        return pc.cast(getattr(pc, fn)(pc.cast(x, pa.float64())), pa.int64(), safe=False)
+    if fn in ("log1p", "exp", "sqrt", "sin", "cos", "log2", "log10"):
         return getattr(pc, fn)(pc.cast(x, pa.float64()))
     if fn == "round":
         # Spark rounds HALF_UP (2.5 -> 3, -2.5 -> -3); bround() is the half-even one

@@ -133,7 +133,7 @@ class DataFrame(DataFrameExtras):
             if rewritten._kind == "col" and len(found) == 1:          # the window expression IS the column
                 return self._with_windows([(name, found[0][1])])
             return self._with_windows(found)._derive(("with_column", name, rewritten)).drop(*[t for t, _ in found])
-        if col._kind in ("posexplode", "explode"):
+        if col._kind in ("posexplode", "explode", "inline"):
             others = [Column("col", (c,)) for c in self.columns if c != name]
             return self.select(*others, col.alias(name) if col._kind == "explode" else col)
         return self._derive(("with_column", name, col))
@@ -165,7 +165,7 @@ class DataFrame(DataFrameExtras):
             cols = tuple(cols[0])
         exprs = [as_column(c) for c in cols]
         exprs = self._expand_star(exprs)
-        gens = [i for i, e in enumerate(exprs) if e._kind in ("posexplode", "explode")]
+        gens = [i for i, e in enumerate(exprs) if e._kind in ("posexplode", "explode", "inline")]
         if len(gens) > 1:
             raise ValueError("only one generator (explode / posexplode) is allowed per select")
         from raydp_b200.sql import windowing

@@ -1425,3 +1425,276 @@ def _sliding_windows(args, n, ctx):
     structs = pa.StructArray.from_arrays([pc.cast(pa.array(flat), pa.timestamp("us")),
                                           pc.cast(pa.array(flat + width), pa.timestamp("us"))], names=["start", "end"])
     return pa.ListArray.from_arrays(pa.array(offsets), structs, mask=pa.array(mask))
+
+
+# ------------------------------------------------------------------------------------------ second batch
+@scalar("cot")
+def _cot(args, n, ctx):
+    return pc.divide(1.0, pc.tan(_f64(args[0])))
+
+
+@scalar("csc")
+def _csc(args, n, ctx):
+    return pc.divide(1.0, pc.sin(_f64(args[0])))
+
+
+@scalar("sec")
+def _sec(args, n, ctx):
+    return pc.divide(1.0, pc.cos(_f64(args[0])))
+
+
+@scalar("bit_count")
+def _bit_count(args, n, ctx):
+    return _map_rows(lambda v: bin(int(v) & 0xFFFFFFFFFFFFFFFF).count("1"), n, args[0], type=pa.int32())
+
+
+@scalar("getbit", "bit_get")
+def _getbit(args, n, ctx):
+    return _map_rows(lambda v, p: (int(v) >> int(p)) & 1, n, args[0], args[1], type=pa.int8())
+
+
+@scalar("shiftrightunsigned")
+def _shiftrightunsigned(args, n, ctx):
+    k = int(_py(args[1]))
+    return _map_rows(lambda v: (int(v) & 0xFFFFFFFFFFFFFFFF) >> k, n, args[0], type=pa.int64())
+
+
+@scalar("char", "chr")
+def _char(args, n, ctx):
+    return _map_rows(lambda v: chr(int(v) % 256), n, args[0], type=pa.string())
+
+
+@scalar("elt")
+def _elt(args, n, ctx):
+    cols = [_rows(a, n) for a in args]
+    out = []
+    for row in zip(*cols):
+        i = row[0]
+        out.append(row[i] if i is not None and 1 <= i < len(row) else None)
+    return pa.array(out)
+
+
+@scalar("find_in_set")
+def _find_in_set(args, n, ctx):
+    return _map_rows(lambda s, lst: (lst.split(",").index(s) + 1) if s in lst.split(",") and "," not in s else 0, n,
+                     args[0], args[1], type=pa.int32())
+
+
+@scalar("position")
+def _position(args, n, ctx):
+    start = int(_py(args[2])) if len(args) > 2 else 1
+    return _map_rows(lambda sub, s: s.find(sub, max(start - 1, 0)) + 1, n, args[0], args[1], type=pa.int32())
+
+
+@scalar("replace")
+def _replace_fn(args, n, ctx):
+    repl = _py(args[2]) if len(args) > 2 else ""
+    return pc.replace_substring(_string(args[0], n), pattern=_py(args[1]), replacement=repl)
+
+
+@scalar("mask")
+def _mask(args, n, ctx):
+    up, low, dig, other = [(_py(args[i]) if len(args) > i else d) for i, d in ((1, "X"), (2, "x"), (3, "n"), (4, None))]
+
+    def one(s):
+        out = []
+        for ch in s:
+            if ch.isupper():
+                out.append(up if up is not None else ch)
+            elif ch.islower():
+                out.append(low if low is not None else ch)
+            elif ch.isdigit():
+                out.append(dig if dig is not None else ch)
+            else:
+                out.append(other if other is not None else ch)
+        return "".join(out)
+    return _map_rows(one, n, args[0], type=pa.string())
+
+
+@scalar("regexp_extract_all")
+def _regexp_extract_all(args, n, ctx):
+    rx, idx = re.compile(_py(args[1])), (int(_py(args[2])) if len(args) > 2 else 1)
+    return _map_rows(lambda s: [m.group(idx) if rx.groups >= idx else m.group(0) for m in rx.finditer(s)], n, args[0],
+                     type=pa.list_(pa.string()))
+
+
+@scalar("regexp_instr")
+def _regexp_instr(args, n, ctx):
+    rx = re.compile(_py(args[1]))
+
+    def one(s):
+        m = rx.search(s)
+        return 0 if m is None else m.start() + 1
+    return _map_rows(one, n, args[0], type=pa.int32())
+
+
+@scalar("str_to_map")
+def _str_to_map(args, n, ctx):
+    pair_delim = _py(args[1]) if len(args) > 1 else ","
+    kv_delim = _py(args[2]) if len(args) > 2 else ":"
+
+    def one(s):
+        out = []
+        for part in s.split(pair_delim):
+            k, sep, v = part.partition(kv_delim)
+            out.append((k, v if sep else None))
+        return out
+    return _map_rows(one, n, args[0], type=pa.map_(pa.string(), pa.string()))
+
+
+@scalar("json_array_length")
+def _json_array_length(args, n, ctx):
+    def one(s):
+        try:
+            v = json.loads(s)
+        except ValueError:
+            return None
+        return len(v) if isinstance(v, list) else None
+    return _map_rows(one, n, args[0], type=pa.int32())
+
+
+@scalar("json_object_keys")
+def _json_object_keys(args, n, ctx):
+    def one(s):
+        try:
+            v = json.loads(s)
+        except ValueError:
+            return None
+        return list(v) if isinstance(v, dict) else None
+    return _map_rows(one, n, args[0], type=pa.list_(pa.string()))
+
+
+@scalar("to_csv")
+def _to_csv(args, n, ctx):
+    return _map_rows(lambda row: ",".join("" if v is None else str(v) for v in row.values()), n, args[0],
+                     type=pa.string())
+
+
+@scalar("uuid")
+def _uuid(args, n, ctx):
+    import uuid as _uuid_mod
+    return pa.array([str(_uuid_mod.uuid4()) for _ in range(n)], type=pa.string())
+
+
+@scalar("raise_error")
+def _raise_error(args, n, ctx):
+    if n:
+        raise RuntimeError(str(_py(args[0]) if not _arrayish(args[0]) else _rows(args[0], n)[0]))
+    return pa.nulls(0)
+
+
+@scalar("width_bucket")
+def _width_bucket(args, n, ctx):
+    def one(v, lo, hi, k):
+        if k <= 0 or lo == hi:
+            return None
+        if lo < hi:
+            return 0 if v < lo else (k + 1 if v >= hi else int((v - lo) / (hi - lo) * k) + 1)
+        return 0 if v > lo else (k + 1 if v <= hi else int((lo - v) / (lo - hi) * k) + 1)
+    return _map_rows(one, n, args[0], args[1], args[2], args[3], type=pa.int64())
+
+
+@scalar("date_from_unix_date")
+def _date_from_unix_date(args, n, ctx):
+    return pc.cast(pc.cast(_arr(args[0], n), pa.int32()), pa.date32())
+
+
+@scalar("unix_date")
+def _unix_date(args, n, ctx):
+    return pc.cast(_as_date(args[0], n, ctx), pa.int32())
+
+
+def _unix_scaled(divisor: int):
+    def impl(args, n, ctx):
+        micros = pc.cast(_as_ts(args[0], n, ctx), pa.int64())
+        return micros if divisor == 1 else pc.cast(pc.floor(pc.divide(pc.cast(micros, pa.float64()), float(divisor))),
+                                                   pa.int64())
+    return impl
+
+
+SCALAR["unix_micros"] = _unix_scaled(1)
+SCALAR["unix_millis"] = _unix_scaled(1000)
+SCALAR["unix_seconds"] = _unix_scaled(10 ** 6)
+
+
+@scalar("timestamp_millis")
+def _timestamp_millis(args, n, ctx):
+    return pc.cast(pc.multiply(pc.cast(_arr(args[0], n), pa.int64()), 1000), pa.timestamp("us"))
+
+
+@scalar("timestamp_micros")
+def _timestamp_micros(args, n, ctx):
+    return pc.cast(pc.cast(_arr(args[0], n), pa.int64()), pa.timestamp("us"))
+
+
+@scalar("make_timestamp")
+def _make_timestamp(args, n, ctx):
+    def one(y, mo, d, h, mi, s):
+        try:
+            whole = int(s)
+            return _dt.datetime(y, mo, d, h, mi, whole, int(round((s - whole) * 10 ** 6)))
+        except ValueError:
+            return None
+    return _map_rows(one, n, *args[:6], type=pa.timestamp("us"))
+
+
+@scalar("weekday")
+def _weekday(args, n, ctx):          # Monday = 0
+    return pc.cast(pc.day_of_week(_as_ts(args[0], n, ctx), count_from_zero=True, week_start=1), pa.int32())
+
+
+@scalar("date_part")
+def _date_part(args, n, ctx):
+    field = str(_py(args[0])).lower()
+    ts = _as_ts(args[1], n, ctx)
+    table = {"year": pc.year, "yr": pc.year, "years": pc.year, "month": pc.month, "mon": pc.month, "day": pc.day,
+             "d": pc.day, "hour": pc.hour, "h": pc.hour, "minute": pc.minute, "min": pc.minute, "quarter": pc.quarter,
+             "qtr": pc.quarter, "week": pc.iso_week, "w": pc.iso_week, "doy": pc.day_of_year, "dayofyear": pc.day_of_year}
+    if field in table:
+        return pc.cast(table[field](ts), pa.int32())
+    if field in ("second", "sec", "s", "seconds"):
+        return pc.add(pc.cast(pc.second(ts), pa.float64()), pc.divide(pc.cast(pc.microsecond(ts), pa.float64()), 1e6))
+    if field in ("dow", "dayofweek"):
+        return pc.cast(pc.day_of_week(ts, count_from_zero=False, week_start=7), pa.int32())
+    raise ValueError(f"date_part: unknown field {field!r}")
+
+
+@scalar("convert_timezone")
+def _convert_timezone(args, n, ctx):        # convert_timezone(source_tz, target_tz, ts)
+    src, dst, ts = _py(args[0]), _py(args[1]), _as_ts(args[2], n, ctx)
+    instant = pc.assume_timezone(ts, src, ambiguous="earliest", nonexistent="earliest")
+    return pc.local_timestamp(pc.cast(instant, pa.timestamp("us", dst)))
+
+
+@scalar("to_number")
+def _to_number(args, n, ctx):
+    def one(s):
+        cleaned = re.sub(r"[,$\s]", "", s)
+        try:
+            return float(cleaned)
+        except ValueError:
+            return None
+    return _map_rows(one, n, args[0], type=pa.float64())
+
+
+def _try_arith(name: str):
+    def impl(args, n, ctx):
+        a, b = _arr(args[0], n), _arr(args[1], n)
+        if name == "divide":
+            fa, fb = _f64(a), _f64(b)
+            safe = pc.if_else(pc.fill_null(pc.equal(fb, 0.0), False), pa.nulls(n, pa.float64()), fb)
+            return pc.divide(fa, safe)
+        try:
+            return getattr(pc, name + "_checked")(a, b)
+        except pa.ArrowInvalid:                                            # overflow somewhere: row by row
+            op = {"add": lambda x, y: x + y, "subtract": lambda x, y: x - y, "multiply": lambda x, y: x * y}[name]
+
+            def one(x, y):
+                v = op(x, y)
+                return v if isinstance(v, float) or -2 ** 63 <= v < 2 ** 63 else None
+            return _map_rows(one, n, a, b)
+    return impl
+
+
+for _name in ("add", "subtract", "multiply", "divide"):
+    SCALAR["try_" + _name] = _try_arith(_name)

@@ -540,6 +540,74 @@ def count_distinct(c, *cols):
     return _agg("count_distinct", c)
 
 
+# second batch of scalar names ----------------------------------------------------------------------------
+for _n in ("cot", "csc", "sec", "bit_count", "char", "json_array_length", "json_object_keys", "to_csv", "unix_date",
+           "unix_micros", "unix_millis", "unix_seconds", "timestamp_millis", "timestamp_micros", "date_from_unix_date",
+           "weekday", "to_number"):
+    globals()[_n] = _unary(_n)
+del _n
+ceiling, ln, power, lcase, ucase, negative, negate, day = ceil, log, pow, lower, upper, (lambda c: -as_column(c)), \
+    (lambda c: -as_column(c)), dayofmonth
+positive = lambda c: as_column(c)  # noqa: E731
+btrim = trim
+try_to_number = to_number  # noqa: F821
+to_unix_timestamp = unix_timestamp
+
+
+def pi(): return lit(3.141592653589793)
+def e(): return lit(2.718281828459045)
+def uuid(): return Column("call", ("uuid", ()))
+def current_database(): return lit("default")
+current_schema = current_database
+def current_catalog(): return lit("spark_catalog")
+def current_user(): return lit(__import__("getpass").getuser())
+def current_timezone(): return lit("UTC")
+def input_file_name(): return lit("")
+def getbit(c, pos): return _fn("getbit", c, _lit_or_col(pos))
+bit_get = getbit
+def shiftrightunsigned(c, numBits: int): return Column("call", ("shiftrightunsigned", (as_column(c), _plain(numBits))))
+def elt(*cols): return _fn("elt", *[_lit_or_col(c) if not isinstance(c, str) else as_column(c) for c in cols])
+def find_in_set(s, str_array): return _fn("find_in_set", s, str_array)
+def position(substr, s, start=None): return Column("call", ("position", (_lit_or_col(substr), as_column(s)) + ((_plain(start),) if start is not None else ())))  # noqa: A002
+def replace(src, search, replace=None): return Column("call", ("replace", (as_column(src), _plain(search)) + ((_plain(replace),) if replace is not None else ())))
+def mask(c, upperChar="X", lowerChar="x", digitChar="n", otherChar=None): return Column("call", ("mask", (as_column(c), _plain(upperChar), _plain(lowerChar), _plain(digitChar), _plain(otherChar))))
+def regexp_extract_all(c, regexp, idx=1): return Column("call", ("regexp_extract_all", (as_column(c), _plain(regexp), _plain(idx))))
+def regexp_instr(c, regexp, idx=None): return Column("call", ("regexp_instr", (as_column(c), _plain(regexp))))
+def str_to_map(text, pairDelim=",", keyValueDelim=":"): return Column("call", ("str_to_map", (as_column(text), _plain(pairDelim), _plain(keyValueDelim))))
+def raise_error(errMsg): return Column("call", ("raise_error", (_lit_or_col(errMsg),)))
+def width_bucket(v, min, max, numBucket): return _fn("width_bucket", v, _lit_or_col(min), _lit_or_col(max), _lit_or_col(numBucket))  # noqa: A002
+def make_timestamp(years, months, days, hours, mins, secs, timezone=None): return _fn("make_timestamp", years, months, days, hours, mins, secs)
+def date_part(field, source): return Column("call", ("date_part", (_plain(field), as_column(source))))
+datepart = extract = date_part
+def convert_timezone(sourceTz, targetTz, sourceTs): return Column("call", ("convert_timezone", (_plain(sourceTz), _plain(targetTz), as_column(sourceTs))))
+def to_char(c, format): return date_format(c, _plain(format))  # noqa: A002
+def try_add(a, b): return _fn("try_add", a, b)
+def try_subtract(a, b): return _fn("try_subtract", a, b)
+def try_multiply(a, b): return _fn("try_multiply", a, b)
+def try_divide(a, b): return _fn("try_divide", a, b)
+def try_sum(c): return sum(c)
+def call_udf(udfName: str, *cols):
+    from raydp_b200.sql.session import SparkSession
+    return SparkSession.active()._registered_udfs[udfName](*cols)
+
+
+def stack(n, *cols):
+    """``stack(n, v1, ..., vk)``: ``n`` rows of ``k / n`` columns each (a generator, like ``explode``)."""
+    rows = int(_plain(n))
+    values = [_lit_or_col(c) if not isinstance(c, str) else as_column(c) for c in cols]
+    width = -(-len(values) // rows)
+    structs = []
+    for r in range(rows):
+        chunk = values[r * width:(r + 1) * width]
+        chunk = chunk + [lit(None)] * (width - len(chunk))
+        structs.append(struct(*[c.alias(f"col{i}") for i, c in enumerate(chunk)]))
+    return Column("inline", (array(*structs),))
+
+
+def inline(c): return Column("inline", (as_column(c),))
+def inline_outer(c): return Column("inline", (as_column(c), True))
+
+
 # window functions -----------------------------------------------------------------------------------------
 def rank() -> Column: return Column("rank_fn", ("rank",))
 def dense_rank() -> Column: return Column("rank_fn", ("dense_rank",))

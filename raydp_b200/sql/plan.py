@@ -445,6 +445,10 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
             flat_k, flat_v = arr.keys[arr.offsets[0].as_py():], arr.items[arr.offsets[0].as_py():]
             produced = [("key", flat_k.take(src) if len(flat_k) else pa.nulls(len(parent), flat_k.type)),
                         ("value", flat_v.take(src) if len(flat_v) else pa.nulls(len(parent), flat_v.type))]
+        elif gen._kind == "inline":              # array<struct<...>> -> one column per struct field
+            flat = pc.list_flatten(arr)
+            taken = flat.take(src) if len(flat) else pa.nulls(len(parent), flat.type)
+            produced = [(f.name, pc.struct_field(taken, f.name)) for f in flat.type]
         else:
             flat = pc.list_flatten(arr)
             produced = [("col", flat.take(src) if len(flat) else pa.nulls(len(parent), flat.type))]

@@ -382,3 +382,29 @@ def test_time_windows_tumbling_and_sliding(spark):
     assert df.select("v", F.window("t", "10 minutes", "5 minutes")).count() == 4
     by_struct = df.select(F.struct("v", (F.col("v") % 2).alias("odd")).alias("s")).groupBy("s").count().collect()
     assert sorted((r.s.v, r.s.odd, r["count"]) for r in by_struct) == [(1, 1, 1), (2, 0, 1), (3, 1, 1)]
+
+
+def test_second_batch_of_functions_and_generators(spark):
+    df = spark.createDataFrame([("Ab1-x", 5, "a:1,b:2", "[1,2,3]", "2020-03-04 05:06:07")], ["s", "v", "m", "j", "t"])
+    r = df.select(
+        F.mask("s").alias("mk"), F.bit_count("v").alias("bc"), F.getbit("v", 2).alias("gb"), F.str_to_map("m").alias("sm"),
+        F.json_array_length("j").alias("jl"), F.regexp_extract_all(F.lit("a1b22c333"), r"(\d+)", 1).alias("ra"),
+        F.regexp_instr("s", r"\d").alias("ri"), F.replace("s", "b", "Z").alias("rp"), F.position(F.lit("1"), "s").alias("ps"),
+        F.elt(F.lit(2), F.lit("x"), F.lit("y")).alias("el"), F.find_in_set(F.lit("b"), F.lit("a,b,c")).alias("fs"),
+        F.width_bucket("v", 0, 10, 5).alias("wb"), F.weekday("t").alias("wd"), F.date_part("hour", "t").alias("dp"),
+        F.unix_seconds(F.to_timestamp("t")).alias("us"), F.timestamp_millis(F.lit(1000)).alias("tm"),
+        F.make_timestamp(F.lit(2020), F.lit(1), F.lit(2), F.lit(3), F.lit(4), F.lit(5.5)).alias("mt"),
+        F.try_divide("v", F.lit(0)).alias("td"), F.try_add("v", F.lit(1)).alias("ta"), F.ceiling(F.lit(1.2)).alias("ce"),
+        F.floor(F.lit(-1.2)).alias("fl"), F.ln(F.e()).alias("ln"), F.convert_timezone("UTC", "Asia/Tokyo", "t").alias("cz"),
+        F.to_number(F.lit("$1,234.5")).alias("tn"), F.char(F.lit(65)).alias("ch")).first()
+    assert (r.mk, r.bc, r.gb, r.sm, r.jl, r.ra) == ("Xxn-x", 2, 1, {"a": "1", "b": "2"}, 3, ["1", "22", "333"])
+    assert (r.ri, r.rp, r.ps, r.el, r.fs, r.wb, r.wd, r.dp) == (3, "AZ1-x", 3, "y", 2, 3, 2, 5)
+    assert r.us == 1583298367 and r.tm == dt.datetime(1970, 1, 1, 0, 0, 1) and r.mt == dt.datetime(2020, 1, 2, 3, 4, 5, 500000)
+    assert r.td is None and r.ta == 6 and r.ce == 2 and isinstance(r.ce, int) and r.fl == -2 and r.ln == 1.0
+    assert r.cz == dt.datetime(2020, 3, 4, 14, 6, 7) and r.tn == 1234.5 and r.ch == "A"
+    stacked = df.select("v", F.stack(2, F.lit("a"), F.lit(1), F.lit("b"), F.lit(2))).collect()
+    assert [tuple(x) for x in stacked] == [(5, "a", 1), (5, "b", 2)]
+    assert [tuple(x) for x in df.select(F.inline(F.array(F.struct(F.lit(1).alias("x"), F.lit("p").alias("y"))))).collect()] == \
+        [(1, "p")]
+    assert tuple(spark.sql("select extract('year', to_timestamp('2020-03-04 05:06:07')) y, ceiling(1.5) c, power(2, 3) p, "
+                           "ucase('a') u").collect()[0]) == (2020, 2, 8.0, "A")
