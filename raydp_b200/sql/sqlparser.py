@@ -652,6 +652,100 @@ class Catalog:
             return self._session.read.parquet(path)
         raise SqlError(f"Table or view not found: {name}")
 
+    # ---- the rest of ``spark.catalog``
+    def databaseExists(self, dbName: str) -> bool:
+        return dbName in self.listDatabases()
+
+    def getDatabase(self, dbName: str):
+        import collections
+        import os
+        if not self.databaseExists(dbName):
+            raise SqlError(f"Database '{dbName}' not found")
+        Database = collections.namedtuple("Database", "name catalog description locationUri")
+        path = self.warehouse() if dbName == "default" else os.path.join(self.warehouse(), dbName + ".db")
+        return Database(dbName, "spark_catalog", "", "file:" + path)
+
+    def getTable(self, tableName: str):
+        import collections
+        if not self.tableExists(tableName):
+            raise SqlError(f"Table or view not found: {tableName}")
+        Table = collections.namedtuple("Table", "name catalog namespace description tableType isTemporary")
+        temp = tableName in self._views
+        db = None if temp else (tableName.split(".")[0] if "." in tableName else self._current_db)
+        return Table(tableName.split(".")[-1], None if temp else "spark_catalog", None if temp else [db], None,
+                     "TEMPORARY" if temp else "MANAGED", temp)
+
+    def listColumns(self, tableName: str, dbName: Optional[str] = None):
+        import collections
+        Col = collections.namedtuple("Column", "name description dataType nullable isPartition isBucket")
+        df = self.lookup(f"{dbName}.{tableName}" if dbName else tableName)
+        return [Col(f.name, None, f.dataType.simpleString(), f.nullable, False, False) for f in df.schema.fields]
+
+    def listFunctions(self, dbName: Optional[str] = None, pattern: Optional[str] = None):
+        import collections
+        import fnmatch
+        Fn = collections.namedtuple("Function", "name catalog namespace description className isTemporary")
+        names = sorted(n for n in dir(F) if not n.startswith("_") and callable(getattr(F, n)))
+        names += sorted(set(getattr(self._session, "_registered_udfs", {})))
+        if pattern:
+            names = [n for n in names if fnmatch.fnmatch(n, pattern)]
+        return [Fn(n, None, None, None, "", n in getattr(self._session, "_registered_udfs", {})) for n in names]
+
+    def functionExists(self, functionName: str, dbName: Optional[str] = None) -> bool:
+        return any(f.name.lower() == functionName.lower() for f in self.listFunctions())
+
+    def dropGlobalTempView(self, name: str) -> bool:
+        gone = self._views.pop(f"global_temp.{name}", None) is not None
+        return (self._views.pop(name, None) is not None) or gone
+
+    def cacheTable(self, tableName: str, storageLevel=None) -> None:
+        self.lookup(tableName).cache()
+
+    def uncacheTable(self, tableName: str) -> None:
+        self.lookup(tableName).unpersist()
+
+    def isCached(self, tableName: str) -> bool:
+        return bool(getattr(self.lookup(tableName), "is_cached", False))
+
+    def clearCache(self) -> None:
+        for df in self._views.values():
+            df.unpersist()
+
+    def refreshTable(self, tableName: str) -> None:
+        pass                                            # tables are read from their files on every lookup
+
+    def refreshByPath(self, path: str) -> None:
+        pass
+
+    def recoverPartitions(self, tableName: str) -> None:
+        pass
+
+    def currentCatalog(self) -> str:
+        return "spark_catalog"
+
+    def listCatalogs(self, pattern: Optional[str] = None):
+        import collections
+        return [collections.namedtuple("CatalogMetadata", "name description")("spark_catalog", None)]
+
+    def createTable(self, tableName: str, path: Optional[str] = None, source: Optional[str] = None, schema=None,
+                    description: Optional[str] = None, **options):
+        """An external table over files at ``path`` (registered as a view of the reader), or an empty managed
+        table with ``schema``."""
+        if path is not None:
+            reader = self._session.read.format(source or "parquet").options(**options)
+            if schema is not None:
+                reader = reader.schema(schema)
+            df = reader.load(path)
+            self._views[tableName] = df
+            return df
+        if schema is None:
+            raise SqlError("createTable needs a path or a schema")
+        empty = self._session.createDataFrame([], schema)
+        self.save_table(empty, tableName, "errorifexists")
+        return self.lookup(tableName)
+
+    createExternalTable = createTable
+
     def save_table(self, df, name: str, mode: str = "errorifexists") -> None:
         df.write.mode(mode).parquet(self._table_dir(name))
 

@@ -141,3 +141,22 @@ def test_pandas_on_spark_surface(spark):
         return float(r["v"]) + float(r["y"])
     assert df.apply(row_total, axis=1).to_pandas().tolist() == [4.0, 7.0, 16.0, 28.0]
     assert ps.range(10).to_spark().count() == 10 and isinstance(df.to_spark(), type(spark.range(1)))
+
+
+def test_catalog_api(spark, tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)                                   # the default warehouse is ./spark-warehouse
+    spark.range(3).createOrReplaceTempView("cat_v")
+    cat = spark.catalog
+    cols = cat.listColumns("cat_v")
+    assert [(c.name, c.dataType) for c in cols] == [("id", "bigint")] and cat.getTable("cat_v").isTemporary
+    assert cat.functionExists("concat_ws") and len(cat.listFunctions(pattern="array_*")) >= 15
+    assert cat.databaseExists("default") and cat.getDatabase("default").name == "default"
+    spark.range(5).write.parquet(str(tmp_path / "ext"))
+    assert cat.createTable("cat_ext", path=str(tmp_path / "ext")).count() == 5
+    assert spark.sql("select count(*) from cat_ext").collect()[0][0] == 5
+    assert cat.createTable("cat_managed", schema="a int, b string").columns == ["a", "b"] and cat.tableExists("cat_managed")
+    cat.cacheTable("cat_v")
+    assert cat.isCached("cat_v")
+    cat.clearCache()
+    spark.sql("drop table cat_managed")
+    assert cat.dropTempView("cat_v") and not cat.tableExists("cat_v")
