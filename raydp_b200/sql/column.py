@@ -67,6 +67,10 @@ class Column:
             return f"{self._args[0]}({inner})"
         if self._kind == "binop":
             return f"({self._args[1]._output_name()} {self._args[0]} {self._args[2]._output_name()})"
+        if self._kind in ("cast", "sort"):
+            inner = self._args[0]._output_name()
+            return inner if self._kind == "sort" or self._args[0]._kind == "col" else \
+                f"CAST({inner} AS {self._args[1].simpleString().upper()})"
         if self._kind == "udf":
             return f"{self._args[0].__name__}(...)"
         if self._kind == "arrowfn":
@@ -570,6 +574,8 @@ def _call(fn: str, args: list, n: int, ctx: EvalContext):
     if fn == "array":
         # element j of row i = args[j][i]; done in Arrow so strings and nulls survive (numpy stacking
         # would turn them into objects)
+        if not args:                                     # array(): an empty array per row
+            return pa.array([[]] * n, type=pa.list_(pa.null()))
         parts = []
         for a in args:
             v = _full(a, n)

@@ -747,7 +747,13 @@ class Catalog:
     createExternalTable = createTable
 
     def save_table(self, df, name: str, mode: str = "errorifexists") -> None:
-        df.write.mode(mode).parquet(self._table_dir(name))
+        import os
+        target = self._table_dir(name)
+        if mode == "overwrite" and os.path.isdir(target):
+            # the new contents may be computed FROM the table (INSERT OVERWRITE t SELECT ... FROM t, TRUNCATE):
+            # evaluate them before the old files go away
+            df = df._session._from_tables(df._run("collect") or [df._arrow_schema().empty_table()])
+        df.write.mode(mode).parquet(target)
 
     def drop_table(self, name: str, if_exists: bool = False) -> None:
         import os
@@ -1097,21 +1103,136 @@ def run_sql(session, query: str):
         if_exists = p.kw("if", "exists")
         cat.drop_table(_qualified_name(p), if_exists)
         return session.createDataFrame([(0,)], ["ok"]).limit(0)
-    elif p.kw("create", "table") or p.kw("create", "or", "replace", "table"):
-        p.kw("if", "not", "exists")
+    elif p.kw("create", "table") or p.kw("create", "or", "replace", "table") or p.kw("create", "external", "table"):
+        if_not_exists = p.kw("if", "not", "exists")
         name = _qualified_name(p)
+        schema = None
+        if p.peek() == ("op", "("):                          # CREATE TABLE t (a int, b string)
+            p.i += 1
+            depth, parts = 0, []
+            while not (p.peek() == ("op", ")") and depth == 0):
+                kind, v = p.peek()
+                if kind == "eof":
+                    raise SqlError("unterminated column list")
+                depth += (v in ("(", "<")) - (v in (")", ">")) if kind == "op" else 0
+                parts.append("," if (kind, v) == ("op", ",") else v)
+                p.i += 1
+            p.i += 1
+            from raydp_b200.sql.types import parse_ddl
+            schema = parse_ddl(" ".join(parts).replace(" ,", ",").replace("< ", "<").replace(" >", ">")
+                               .replace(" <", "<").replace("( ", "(").replace(" )", ")").replace(" (", "("))
         if p.kw("using"):
             p.name()
-        if not p.kw("as"):
-            raise SqlError("only CREATE TABLE ... AS SELECT is supported")
-        cat.save_table(_parse_select(p, session), name, "overwrite")
+        while p.kw("partitioned", "by") or p.kw("location") or p.kw("comment") or p.kw("tblproperties"):
+            if p.peek()[0] == "str":
+                p.i += 1
+            elif p.op("("):
+                while not p.op(")"):
+                    p.i += 1
+        if p.kw("as"):
+            cat.save_table(_parse_select(p, session), name, "overwrite")
+        elif schema is not None:
+            if not (if_not_exists and cat.tableExists(name)):
+                cat.save_table(session.createDataFrame([], schema), name, "errorifexists")
+        else:
+            raise SqlError("CREATE TABLE needs a column list or AS SELECT")
         return session.createDataFrame([(0,)], ["ok"]).limit(0)
-    elif p.kw("insert", "into") or p.kw("insert", "overwrite", "table"):
+    elif p.kw("create", "view") or p.kw("create", "or", "replace", "view") or p.kw("create", "temp", "view") or \
+            p.kw("create", "temporary", "view") or p.kw("create", "or", "replace", "temp", "view") or \
+            p.kw("create", "or", "replace", "temporary", "view") or p.kw("create", "global", "temp", "view") or \
+            p.kw("create", "or", "replace", "global", "temp", "view"):
+        p.kw("if", "not", "exists")
+        name = _qualified_name(p)
+        if not p.kw("as"):
+            raise SqlError("CREATE VIEW needs AS SELECT")
+        cat.register_view(name, _parse_select(p, session))
+        return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("insert", "into") or p.kw("insert", "overwrite", "table") or p.kw("insert", "overwrite"):
         overwrite = p.t[1][1].lower() == "overwrite"
         p.kw("table")
         name = _qualified_name(p)
-        cat.save_table(_parse_select(p, session), name, "overwrite" if overwrite else "append")
+        if p.kw("values"):
+            target = cat.lookup(name)
+            rows = []
+            while True:
+                p.expect_op("(")
+                row = [p.expr()]
+                while p.op(","):
+                    row.append(p.expr())
+                p.expect_op(")")
+                rows.append(tuple(session.range(1).select(*[c.alias(f"c{i}") for i, c in enumerate(row)]).collect()[0]))
+                if not p.op(","):
+                    break
+            data = session.createDataFrame(rows, target.schema)
+        else:
+            data = _parse_select(p, session)
+            if cat.tableExists(name):                    # columns are matched by position, typed by the table
+                target = cat.lookup(name)
+                if len(target.columns) != len(data.columns):
+                    raise SqlError(f"INSERT INTO {name}: the table has {len(target.columns)} columns, the query "
+                                   f"returns {len(data.columns)}")
+                data = data.toDF(*target.columns)
+                data = data.select(*[F.col(f.name).cast(f.dataType) for f in target.schema.fields])
+        cat.save_table(data, name, "overwrite" if overwrite else "append")
         return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("truncate", "table"):
+        name = _qualified_name(p)
+        cat.save_table(cat.lookup(name).limit(0), name, "overwrite")
+        return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("describe") or p.kw("desc"):
+        p.kw("table")
+        p.kw("extended")
+        df = cat.lookup(_qualified_name(p))
+        return session.createDataFrame([(f.name, f.dataType.simpleString(), None) for f in df.schema.fields],
+                                       "col_name string, data_type string, comment string")
+    elif p.kw("show", "columns"):
+        if not (p.kw("in") or p.kw("from")):
+            raise SqlError("SHOW COLUMNS needs IN <table>")
+        df = cat.lookup(_qualified_name(p))
+        return session.createDataFrame([(c,) for c in df.columns], ["col_name"])
+    elif p.kw("show", "functions"):
+        return session.createDataFrame([(f.name,) for f in cat.listFunctions()], ["function"])
+    elif p.kw("show", "views"):
+        return session.createDataFrame([("", v, True) for v in sorted(cat._views)] or [("", "", True)],
+                                       ["namespace", "viewName", "isTemporary"]).limit(len(cat._views))
+    elif p.kw("cache", "table") or p.kw("cache", "lazy", "table"):
+        cat.cacheTable(_qualified_name(p))
+        return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("uncache", "table"):
+        p.kw("if", "exists")
+        cat.uncacheTable(_qualified_name(p))
+        return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("clear", "cache"):
+        cat.clearCache()
+        return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("refresh"):
+        p.kw("table")
+        return session.createDataFrame([(0,)], ["ok"]).limit(0)
+    elif p.kw("set"):
+        text = query.strip().rstrip(";")[3:].strip()
+        if not text:
+            return session.createDataFrame(session._conf.getAll() or [("", "")], ["key", "value"])
+        key, sep, value = text.partition("=")
+        if sep:
+            session.conf.set(key.strip(), value.strip())
+            return session.createDataFrame([(key.strip(), value.strip())], ["key", "value"])
+        return session.createDataFrame([(key.strip(), session.conf.get(key.strip(), "<undefined>"))], ["key", "value"])
+    elif p.kw("explain"):
+        p.kw("extended")
+        _parse_select(p, session).explain()
+        return session.createDataFrame([("see stdout",)], ["plan"])
+    elif p.kw("values"):
+        rows = []
+        while True:
+            p.expect_op("(")
+            row = [p.expr()]
+            while p.op(","):
+                row.append(p.expr())
+            p.expect_op(")")
+            rows.append(tuple(session.range(1).select(*[c.alias(f"col{i + 1}") for i, c in enumerate(row)]).collect()[0]))
+            if not p.op(","):
+                break
+        return session.createDataFrame(rows, [f"col{i + 1}" for i in range(len(rows[0]))])
     else:
         raise SqlError(f"unsupported SQL statement: {query.strip()[:60]!r} (see raydp_b200/sql/sqlparser.py)")
     if not p.done():

@@ -160,3 +160,29 @@ def test_catalog_api(spark, tmp_path, monkeypatch):
     cat.clearCache()
     spark.sql("drop table cat_managed")
     assert cat.dropTempView("cat_v") and not cat.tableExists("cat_v")
+
+
+def test_sql_ddl_and_dml_statements(spark, tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+
+    def q(text):
+        return [tuple(r) for r in spark.sql(text).collect()]
+    q("create table ddl_people (id int, name string, tags array<string>) using parquet")
+    q("insert into ddl_people values (1, 'al', array('x')), (2, upper('bo'), array())")
+    assert q("select * from ddl_people order by id") == [(1, "al", ["x"]), (2, "BO", [])]
+    q("create or replace temp view ddl_young as select id, name from ddl_people where id < 2")
+    assert q("select * from ddl_young") == [(1, "al")]
+    assert q("describe ddl_people") == [("id", "int", None), ("name", "string", None), ("tags", "array<string>", None)]
+    assert q("show columns in ddl_people") == [("id",), ("name",), ("tags",)]
+    q("insert overwrite ddl_people select id + 10, name, tags from ddl_people")     # reads the table it replaces
+    assert q("select id from ddl_people order by id") == [(11,), (12,)]
+    assert dict(spark.table("ddl_people").dtypes)["id"] == "int"                     # typed by the table
+    q("truncate table ddl_people")
+    assert q("select count(*) from ddl_people") == [(0,)]
+    q("create table if not exists ddl_people (id int)")                               # no-op
+    assert q("set spark.sql.shuffle.partitions=7") == [("spark.sql.shuffle.partitions", "7")]
+    assert q("set spark.sql.shuffle.partitions") == [("spark.sql.shuffle.partitions", "7")]
+    assert q("values (1, 'a'), (2, 'b')") == [(1, "a"), (2, "b")]
+    q("cache table ddl_young")
+    q("drop table ddl_people")
+    assert not spark.catalog.tableExists("ddl_people")
