@@ -642,5 +642,45 @@ def _rows_to_table(rows: List[Any], names: Optional[List[str]], schema: Optional
     for i, name in enumerate(names):
         typ = schema.field(name).type if schema is not None else None
         values = list(cols[i]) if rows else []
+        if typ is None and any(isinstance(v, (dict, T.Row)) or (isinstance(v, (list, tuple)) and v and
+                                                                 isinstance(v[0], (dict, T.Row))) for v in values):
+            typ = _infer_nested(values)          # PySpark's inference: dict -> map, Row -> struct
+        if typ is not None and (pa.types.is_map(typ) or pa.types.is_struct(typ) or pa.types.is_list(typ)):
+            values = [_arrow_ready(v, typ) for v in values]
         arrays.append(pa.array(values, type=typ))
     return pa.table(arrays, names=names)
+
+
+def _infer_nested(values: List[Any]) -> pa.DataType:
+    live = [v for v in values if v is not None]
+    if not live:
+        return pa.null()
+    head = live[0]
+    if isinstance(head, T.Row) and head.__fields__:
+        return pa.struct([pa.field(f, _infer_nested([v[j] for v in live if isinstance(v, T.Row) and len(v) > j]))
+                          for j, f in enumerate(head.__fields__)])
+    if isinstance(head, dict):
+        keys = [k for v in live if isinstance(v, dict) for k in v]
+        items = [x for v in live if isinstance(v, dict) for x in v.values()]
+        return pa.map_(_infer_nested(keys) if keys else pa.string(), _infer_nested(items) if items else pa.null())
+    if isinstance(head, (list, tuple)):
+        return pa.list_(_infer_nested([x for v in live if isinstance(v, (list, tuple)) for x in v]))
+    return pa.array(live).type
+
+
+def _arrow_ready(value, typ: pa.DataType):
+    """Python value -> the shape ``pa.array`` wants for ``typ`` (Row -> dict, dict -> key/value pairs)."""
+    if value is None:
+        return None
+    if pa.types.is_struct(typ):
+        if isinstance(value, T.Row) and value.__fields__:
+            value = value.asDict()
+        elif isinstance(value, (tuple, list)):
+            value = {f.name: v for f, v in zip(typ, value)}
+        return {f.name: _arrow_ready(value.get(f.name), f.type) for f in typ}
+    if pa.types.is_map(typ):
+        pairs = value.items() if isinstance(value, dict) else value
+        return [(_arrow_ready(k, typ.key_type), _arrow_ready(v, typ.item_type)) for k, v in pairs]
+    if pa.types.is_list(typ) or pa.types.is_large_list(typ):
+        return [_arrow_ready(v, typ.value_type) for v in value]
+    return value

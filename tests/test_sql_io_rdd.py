@@ -186,3 +186,20 @@ def test_sql_ddl_and_dml_statements(spark, tmp_path, monkeypatch):
     q("cache table ddl_young")
     q("drop table ddl_people")
     assert not spark.catalog.tableExists("ddl_people")
+
+
+def test_nested_type_inference_from_python_objects(spark):
+    import datetime as dt
+    from raydp_b200.sql import functions as F
+    df = spark.createDataFrame([Row(a=1, t=dt.datetime(2020, 1, 1), m={"k": 1.0}, l=[Row(z=1), Row(z=2)],
+                                    s=Row(p="x", q=[1, 2]))])
+    assert dict(df.dtypes) == {"a": "bigint", "t": "timestamp", "m": "map<string,double>",
+                               "l": "array<struct<z:bigint>>", "s": "struct<p:string,q:array<bigint>>"}
+    row = df.collect()[0]
+    assert row.m == {"k": 1.0} and row.l == [Row(z=1), Row(z=2)] and row.s.q == [1, 2]
+    d2 = spark.createDataFrame([{"a": 1, "b": {"c": [1, 2]}}, {"a": 2, "b": {"d": []}}])
+    assert dict(d2.dtypes)["b"] == "map<string,array<bigint>>"
+    assert [tuple(r) for r in d2.select(F.col("b")["c"].alias("c"), F.map_keys("b").alias("k")).collect()] == \
+        [([1, 2], ["c"]), (None, ["d"])]
+    d3 = spark.createDataFrame([(1, ("x", 2))], "id int, s struct<a:string,b:int>")
+    assert d3.collect() == [Row(id=1, s=Row(a="x", b=2))] and tuple(d3.select("s.*").collect()[0]) == ("x", 2)
