@@ -24,6 +24,7 @@ from raydp_b200.sql.plan import (CsvSource, FuncSource, LocalSource, ParquetSour
 
 _active_lock = threading.RLock()
 _active_session: Optional["SparkSession"] = None
+_live_sessions: List[Any] = []          # weak references, oldest first (the "default session" fallback)
 _builder_options: Dict[str, str] = {}
 
 
@@ -498,11 +499,20 @@ class SparkSession:
         self.version = "3.5.0-raydp-b200"
         self._registered_udfs: Dict[str, Any] = {}
         self.udf = UDFRegistration(self)
+        import weakref
+        _live_sessions[:] = [r for r in _live_sessions if r() is not None and not r()._stopped]
+        _live_sessions.append(weakref.ref(self))
 
     # ------------------------------------------------------------------ factories
     @classmethod
     def getActiveSession(cls) -> Optional["SparkSession"]:
-        return _active_session if _active_session is not None and not _active_session._stopped else None
+        if _active_session is not None and not _active_session._stopped:
+            return _active_session
+        for ref in reversed(_live_sessions):                 # another session that is still running
+            other = ref()
+            if other is not None and not other._stopped:
+                return other
+        return None
 
     @classmethod
     def active(cls) -> "SparkSession":
