@@ -248,15 +248,47 @@ class Dataset:
             yield from table.to_pylist()
 
     def iter_batches(self, batch_size: Optional[int] = 256, batch_format: str = "pyarrow",
-                     drop_last: bool = False, prefetch_batches: int = 0) -> Iterator[Any]:
+                     drop_last: bool = False, prefetch_batches: int = 0,
+                     local_shuffle_buffer_size: Optional[int] = None,
+                     local_shuffle_seed: Optional[int] = None, **_ignored) -> Iterator[Any]:
+        def column_numpy(col):
+            arr = col.combine_chunks() if isinstance(col, pa.ChunkedArray) else col
+            if pa.types.is_list(arr.type) or pa.types.is_large_list(arr.type) or pa.types.is_fixed_size_list(arr.type):
+                rows = arr.to_pylist()                      # vectors: [n, width] when the rows share a width
+                try:
+                    return np.asarray(rows)
+                except ValueError:
+                    return np.asarray(rows, dtype=object)
+            return arr.to_numpy(zero_copy_only=False)
+
         def convert(table: pa.Table):
             if batch_format in ("pyarrow", "arrow", "default"):
                 return table
             if batch_format == "pandas":
                 return table.to_pandas()
             if batch_format == "numpy":
-                return {n: table.column(n).to_numpy(zero_copy_only=False) for n in table.column_names}
+                return {n: column_numpy(table.column(n)) for n in table.column_names}
             raise ValueError(f"unknown batch_format {batch_format!r}")
+        if local_shuffle_buffer_size:
+            # rows are drawn at random from a buffer of at least this many rows (plus the batch being cut)
+            rng = np.random.default_rng(local_shuffle_seed)
+            size = batch_size or 256
+            pool: Optional[pa.Table] = None
+            for table in self.iter_tables():
+                pool = table if pool is None else pa.concat_tables([pool, table])
+                while pool.num_rows >= local_shuffle_buffer_size + size:
+                    pick = rng.choice(pool.num_rows, size, replace=False)
+                    mask = np.ones(pool.num_rows, dtype=bool)
+                    mask[pick] = False
+                    yield convert(pool.take(pa.array(pick)))
+                    pool = pool.filter(pa.array(mask))
+            if pool is not None and pool.num_rows:
+                pool = pool.take(pa.array(rng.permutation(pool.num_rows)))
+                for off in builtins_range(0, pool.num_rows, size):
+                    piece = pool.slice(off, size)
+                    if piece.num_rows == size or not drop_last:
+                        yield convert(piece)
+            return
         if batch_size is None:
             for table in self.iter_tables():
                 yield convert(table)
@@ -277,9 +309,17 @@ class Dataset:
             yield convert(carry[0] if len(carry) == 1 else pa.concat_tables(carry))
 
     def iter_torch_batches(self, batch_size: int = 256, dtypes=None, device: Optional[str] = None,
-                           drop_last: bool = False) -> Iterator[Dict[str, Any]]:
+                           drop_last: bool = False, collate_fn: Optional[Callable] = None,
+                           local_shuffle_buffer_size: Optional[int] = None,
+                           local_shuffle_seed: Optional[int] = None, prefetch_batches: int = 0,
+                           **_ignored) -> Iterator[Dict[str, Any]]:
         import torch
-        for batch in self.iter_batches(batch_size, "numpy", drop_last):
+        for batch in self.iter_batches(batch_size, "numpy", drop_last,
+                                       local_shuffle_buffer_size=local_shuffle_buffer_size,
+                                       local_shuffle_seed=local_shuffle_seed):
+            if collate_fn is not None:
+                yield collate_fn(batch)
+                continue
             out = {}
             for k, v in batch.items():
                 t = torch.as_tensor(np.ascontiguousarray(v))

@@ -156,3 +156,18 @@ def test_preprocessors(ray_cluster):
     assert enc.inverse_transform(enc.transform(ds)).take(1)[0]["y"] == "p"
     with pytest.raises(PreprocessorNotFittedException):
         StandardScaler(["v"]).transform(ds)
+
+
+def test_batch_iteration_options(ray_cluster):
+    import numpy as np
+    import torch
+    from raydp_b200 import data
+    ds = data.from_items([{"i": i, "f": [float(i), float(-i)]} for i in range(100)], parallelism=4)
+    batches = list(ds.iter_batches(batch_size=16, batch_format="numpy", local_shuffle_buffer_size=32,
+                                   local_shuffle_seed=0))
+    seen = np.concatenate([b["i"] for b in batches])
+    assert sorted(seen.tolist()) == list(range(100)) and seen[:16].tolist() != list(range(16))     # all rows, shuffled
+    assert batches[0]["f"].shape == (16, 2)                                       # vector column -> [n, width]
+    first = next(iter(ds.iter_torch_batches(batch_size=8, dtypes={"i": torch.float32, "f": torch.float32})))
+    assert first["f"].shape == (8, 2) and first["i"].dtype == torch.float32
+    assert next(iter(ds.iter_torch_batches(batch_size=4, collate_fn=lambda b: int(b["i"].sum())))) == 6
