@@ -165,6 +165,10 @@ class DataFrame(DataFrameExtras):
             cols = tuple(cols[0])
         exprs = [as_column(c) for c in cols]
         exprs = self._expand_star(exprs)
+        known = self.columns
+        exprs = [e.alias(e._args[0].rsplit(".", 1)[1])          # select("s.a") / select("t.k") shows up as a / k
+                 if e._kind == "col" and e._name is None and "." in e._args[0] and e._args[0] not in known else e
+                 for e in exprs]
         gens = [i for i, e in enumerate(exprs) if e._kind in ("posexplode", "explode", "inline")]
         if len(gens) > 1:
             raise ValueError("only one generator (explode / posexplode) is allowed per select")
