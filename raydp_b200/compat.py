@@ -28,13 +28,25 @@ from typing import Dict, List
 _INSTALLED: List[str] = []
 
 
+class _ExistingModuleLoader:
+    """Hands the import system the module :func:`install` has just registered under this name."""
+
+    def create_module(self, spec):
+        return sys.modules[spec.name]
+
+    def exec_module(self, module) -> None:
+        pass
+
+
 def _module(name: str, doc: str, **attrs) -> types.ModuleType:
     mod = types.ModuleType(name, doc)
     mod.__dict__.update(attrs)
     mod.__raydp_b200_alias__ = True
     # a spec keeps ``importlib.util.find_spec(name)`` (used by other libraries to probe for optional
     # dependencies) from raising on a module that sits in sys.modules without one
-    mod.__spec__ = importlib.machinery.ModuleSpec(name, loader=None)
+    # the loader matters when the module is registered WHILE an import of its name is in flight
+    # (install_lazy): importlib then loads through sys.modules[name].__spec__
+    mod.__spec__ = importlib.machinery.ModuleSpec(name, loader=_ExistingModuleLoader())
     mod.__path__ = []           # lets ``import <alias>.<child>`` resolve children registered in sys.modules
     return mod
 
@@ -292,6 +304,38 @@ def install(ray: bool = True, pyspark: bool = True, force: bool = False) -> List
         import os
         os.environ["RAYDP_B200_COMPAT_ALIASES"] = "1"      # worker processes install the same aliases
     return added
+
+
+class _LazyAliasFinder:
+    """Installs the aliases the first time something imports ``ray`` / ``pyspark`` (or a sub-module).  Worker
+    processes use this: most of them never touch the alias names, and building the alias trees imports
+    torch, pandas and the whole DataFrame engine, which would slow every worker start."""
+
+    _busy = False
+
+    def find_spec(self, name, path=None, target=None):
+        root = name.partition(".")[0]
+        if root not in ("ray", "pyspark") or _LazyAliasFinder._busy:
+            return None
+        _LazyAliasFinder._busy = True
+        try:
+            if self in sys.meta_path:
+                sys.meta_path.remove(self)
+            install()
+        finally:
+            _LazyAliasFinder._busy = False
+        if name not in sys.modules:
+            return None
+        return importlib.machinery.ModuleSpec(name, _ExistingModuleLoader())
+
+
+def install_lazy() -> None:
+    """Arrange for :func:`install` to run on the first import of an alias name."""
+    if any(isinstance(f, _LazyAliasFinder) for f in sys.meta_path):
+        return
+    if getattr(sys.modules.get("ray"), "__raydp_b200_alias__", False):
+        return
+    sys.meta_path.insert(0, _LazyAliasFinder())
 
 
 def uninstall() -> None:

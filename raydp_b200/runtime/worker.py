@@ -32,7 +32,7 @@ def main() -> None:
         # modules by those names
         try:
             from raydp_b200 import compat
-            compat.install()
+            compat.install_lazy()               # on first use: building the alias trees imports torch & co
         except Exception:  # noqa: BLE001
             traceback.print_exc()
     head = os.environ[P.ENV_HEAD]

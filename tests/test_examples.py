@@ -99,12 +99,12 @@ def test_reference_unit_tests_pass_unchanged(tmp_path):
             shutil.copy(f, tmp_path)
     code = ("from raydp_b200 import compat; compat.install(); import raydp, pytest, sys; "
             "sys.exit(pytest.main(['-x', '-q', '-p', 'no:cacheprovider', 'test_spark_utils.py', "
-            "'test_from_spark.py', 'test_spark_master_memory.py']))")
+            "'test_from_spark.py', 'test_spark_master_memory.py', 'test_mpi.py']))")
     env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
     proc = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, capture_output=True,
                           text=True, timeout=600)
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-2000:]
-    assert "7 passed" in proc.stdout
+    assert "15 passed" in proc.stdout        # test_mpi's 10 s limits also guard the start-up time of worker processes
 
 
 _DOC_SNIPPETS = '''
