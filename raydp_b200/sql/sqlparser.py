@@ -80,8 +80,13 @@ class _Parser:
         """``( SELECT ... )`` with the opening parenthesis already consumed; consumes the closing one."""
         if self.session is None:
             raise SqlError("sub-queries need a session: use spark.sql(...)")
-        df = _parse_query(self, self.session)
-        self.expect_op(")")
+        try:
+            df = _parse_query(self, self.session)
+            self.expect_op(")")
+            df.columns                      # resolves the plan: an outer reference cannot be found here
+        except KeyError as exc:
+            raise SqlError(f"correlated sub-queries are not supported (the sub-query refers to a column of the outer "
+                           f"query: {exc}); rewrite it as a join (LEFT SEMI / LEFT ANTI for EXISTS / NOT EXISTS)") from exc
         return df
 
     # ---- token helpers

@@ -408,3 +408,13 @@ def test_second_batch_of_functions_and_generators(spark):
         [(1, "p")]
     assert tuple(spark.sql("select extract('year', to_timestamp('2020-03-04 05:06:07')) y, ceiling(1.5) c, power(2, 3) p, "
                            "ucase('a') u").collect()[0]) == (2020, 2, 8.0, "A")
+
+
+def test_correlated_subquery_is_named_as_unsupported(spark):
+    from raydp_b200.sql.sqlparser import SqlError
+    spark.range(5).createOrReplaceTempView("corr_a")
+    spark.range(3).withColumnRenamed("id", "k").createOrReplaceTempView("corr_b")
+    with pytest.raises(SqlError, match="correlated sub-queries"):
+        spark.sql("select * from corr_a where exists (select 1 from corr_b where corr_b.k = corr_a.id)")
+    assert spark.sql("select corr_a.id from corr_a left semi join corr_b on corr_a.id = corr_b.k").count() == 3
+    assert spark.sql("select * from corr_a where id not in (select k from corr_b)").count() == 2
