@@ -26,9 +26,11 @@ def pytest_collection_modifyitems(config, items):
 
 
 @pytest.fixture(scope="session")
-def spark_session():
+def spark_session(tmp_path_factory):
     from raydp_b200.sql import SparkSession
-    spark = SparkSession.builder.master("local[2]").appName("RayDP test").getOrCreate()
+    warehouse = str(tmp_path_factory.mktemp("warehouse"))       # tables of the tests stay out of the repo
+    spark = SparkSession.builder.master("local[2]").appName("RayDP test") \
+        .config("spark.sql.warehouse.dir", warehouse).getOrCreate()
     yield spark
     spark.stop()
 
