@@ -21,8 +21,6 @@ from __future__ import annotations
 import os
 from typing import Dict, List, Optional
 
-import os
-
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -64,12 +62,15 @@ class _Bucket:
                 p.data = self.flat[o:o + p.numel()].view(p.shape)
                 p.grad = self.grads[o:o + p.numel()].view(p.shape)
             self.shadow.copy_(self.flat)
-
-    def shadow_of(self, p: nn.Parameter) -> torch.Tensor:
-        o = self.offsets[[id(q) for q in self.params].index(id(p))]
-        return self.shadow[o:o + p.numel()].view(p.shape)
         self.pending = len(params)
         self.done_event: Optional[torch.cuda.Event] = None
+
+    def offset_of(self, p: nn.Parameter) -> int:
+        return self.offsets[[id(q) for q in self.params].index(id(p))]
+
+    def shadow_of(self, p: nn.Parameter) -> torch.Tensor:
+        o = self.offset_of(p)
+        return self.shadow[o:o + p.numel()].view(p.shape)
 
 
 class FusedDataParallel(nn.Module):
@@ -81,16 +82,21 @@ class FusedDataParallel(nn.Module):
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.overlap = overlap
         g = optimizer.param_groups[0]
-        if type(optimizer) in (torch.optim.Adam, torch.optim.AdamW):
+        plain = len(optimizer.param_groups) == 1 and not g.get("maximize") and not g.get("amsgrad")
+        if plain and type(optimizer) in (torch.optim.Adam, torch.optim.AdamW):
             self.kind = 1
             self.hp = dict(betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
                            adamw=type(optimizer) is torch.optim.AdamW)
-        elif type(optimizer) is torch.optim.SGD:
+        elif plain and type(optimizer) is torch.optim.SGD:
             self.kind = 2
             self.hp = dict(weight_decay=g["weight_decay"], momentum=g["momentum"], dampening=g["dampening"],
                            nesterov=g["nesterov"])
         else:
-            raise TypeError("FusedDataParallel fuses Adam / AdamW / SGD; wrap other optimizers with stock DDP")
+            # any other torch.optim.Optimizer (the reference accepts all of them, torch/estimator.py:190-202):
+            # the bucket kernels only average the gradients over the ranks and the user's own
+            # optimizer.step() runs afterwards on the re-homed parameters
+            self.kind = 0
+            self.hp = {}
         self.optimizer = optimizer
         params = [p for p in module.parameters() if p.requires_grad]
         if self.world > 1:
@@ -120,10 +126,35 @@ class FusedDataParallel(nn.Module):
         fused_b = {id(m.bias) for m in self._fused_linears if m.bias is not None}
         for m in self._fused_linears:
             m._grad_ready_hooks.append(self._fused_linear_ready)
-            m.use_external_shadow(self._bucket_of[id(m.weight)].shadow_of(m.weight))
+            if self.kind != 0 and not m.padded:
+                m.use_external_shadow(self._bucket_of[id(m.weight)].shadow_of(m.weight))
+        self._seed_state(params)
         for p in params:
             if id(p) not in fused_w and id(p) not in fused_b:
                 p.register_post_accumulate_grad_hook(self._param_ready)
+
+    def _seed_state(self, params) -> None:
+        """An optimizer instance may arrive with state (Adam moments of an earlier fit): carry it over."""
+        if self.kind == 0 or not self.optimizer.state:
+            return
+        step = 0.0
+        with torch.no_grad():
+            for p in params:
+                st = self.optimizer.state.get(p)
+                if not st:
+                    continue
+                b = self._bucket_of[id(p)]
+                o, n = b.offset_of(p), p.numel()
+                if "exp_avg" in st:
+                    b.m[o:o + n].copy_(st["exp_avg"].reshape(-1))
+                    b.v[o:o + n].copy_(st["exp_avg_sq"].reshape(-1))
+                elif st.get("momentum_buffer") is not None:
+                    b.m[o:o + n].copy_(st["momentum_buffer"].reshape(-1))
+                    step = max(step, 1.0)
+                if "step" in st:
+                    step = max(step, float(st["step"]))
+        if step:
+            self.step_dev.fill_(step)
 
     # ------------------------------------------------------------------ hooks
     def _fused_linear_ready(self, layer) -> None:
@@ -153,7 +184,10 @@ class FusedDataParallel(nn.Module):
             ready.record(compute)
             stream.wait_event(ready)
         with torch.cuda.stream(stream):
-            if b.reducer is not None:
+            if self.kind == 0:
+                if b.reducer is not None:
+                    b.reducer.allreduce_(1.0 / self.world)
+            elif b.reducer is not None:
                 if getattr(b.reducer, "kind", "") == "nvls":
                     b.reducer.allreduce_step_(self._opt_args(b), 1.0 / self.world, overlap=stream is not compute)
                 else:
@@ -166,7 +200,8 @@ class FusedDataParallel(nn.Module):
                 ops.sgd_step(b.flat, b.grads, b.m if self.hp["momentum"] else None, 0.0, self.hp["momentum"],
                              self.hp["dampening"], self.hp["weight_decay"], self.hp["nesterov"], False, 1.0,
                              self.lr_dev, self.step_dev, shadow=b.shadow)
-            b.grads.zero_()
+            if self.kind != 0:
+                b.grads.zero_()
             b.done_event = torch.cuda.Event()
             b.done_event.record(stream)
 
@@ -189,6 +224,10 @@ class FusedDataParallel(nn.Module):
                 self._reduce_and_update(b)
             if b.done_event is not None:
                 compute.wait_event(b.done_event)
+        if self.kind == 0:
+            self.optimizer.step()                   # gradients are the rank average by now
+            for b in self.buckets:
+                b.grads.zero_()
         for m in self._fused_linears:
             m.invalidate_shadow()                   # parameters were updated by our kernel, not by torch
 

@@ -97,14 +97,19 @@ class FusedDLRM:
         _, b, c = self.slices[li]
         return (self.grads if grad else self.params)[b:c]
 
-    def load_from_module(self, module) -> None:
+    def load_from_module(self, module, plan=None) -> None:
+        """``plan`` (:class:`raydp_b200.torch.lowering.DLRMPlan`) names the layers of a user-defined module;
+        without it the module is ``raydp_b200.models.DLRM`` (``bottom`` / ``top`` / ``embeddings`` lists)."""
+        if plan is not None:
+            bottom, top, embs = plan.modules(module)
+        else:
+            bottom, top, embs = list(module.bottom), list(module.top), list(module.embeddings)
         with torch.no_grad():
-            lins = list(module.bottom) + list(module.top)
-            for li, lin in enumerate(lins):
+            for li, lin in enumerate(list(bottom) + list(top)):
                 self.weight(li).copy_(lin.weight)
                 self.bias(li).copy_(lin.bias)
             for t in self.owned:
-                self.tables[t].copy_(module.embeddings[t].weight)
+                self.tables[t].copy_(embs[t].weight)
 
     def dense_state_dict(self) -> Dict[str, torch.Tensor]:
         out = {}
@@ -225,9 +230,9 @@ class LocalWorld:
             r.peer_dfeats = [q.dfeats.data_ptr() for q in self.ranks]
             r.peer_batch = [q.B for q in self.ranks]
 
-    def load_from_module(self, module) -> None:
+    def load_from_module(self, module, plan=None) -> None:
         for r in self.ranks:
-            r.load_from_module(module)
+            r.load_from_module(module, plan)
 
     def train_step(self, dense: Sequence[torch.Tensor], idx: Sequence[torch.Tensor],
                    target: Sequence[torch.Tensor], lr: float) -> None:

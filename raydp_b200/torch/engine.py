@@ -46,6 +46,12 @@ class StockEngine:
         # The optimizer was built around the CPU parameters; .to(device) moves them in place
         # (Module.to keeps Parameter identity), so the optimizer keeps pointing at live tensors.
         self.model = prepare_model(model)
+        # state that came in with an optimizer instance (e.g. Adam moments of an earlier fit) was loaded
+        # next to the CPU parameters: it has to follow them to the device ("step" stays a host scalar)
+        for st in optimizer.state.values():
+            for k, v in list(st.items()):
+                if torch.is_tensor(v) and v.dim() > 0 and v.device != self.device:
+                    st[k] = v.to(self.device)
         self.autocast_dtype = config.get("compute_dtype") if self.device.type == "cuda" else None
 
     def _loader(self, shard):
@@ -109,16 +115,25 @@ class StockEngine:
 
 
 def make_engine(config, sess, model, optimizer, criterion, scheduler, metrics):
+    """Pick the step engine.  CUDA workers never run the stock loop unless ``engine="stock"`` asks for
+    the baseline: a module the lowering recognises (``raydp_b200.torch.lowering``: the reference's own
+    ``NYC_Model`` / notebook ``Dlrm`` classes included) runs on the whole-step fused engines, anything
+    else on :class:`GenericGpuEngine` (tcgen05 Linear layers + fused NVLink data parallelism + GPU ingest)."""
     choice = config.get("engine", "auto")
-    if sess.device.type == "cuda" and choice in ("auto", "fused"):
-        from raydp_b200.torch.fused_engine import DLRMEngine, FusedEngine, _is_dlrm, fused_supported
-        ok, why = fused_supported(config, model, optimizer, criterion)
-        if ok and _is_dlrm(model):
-            return DLRMEngine(config, sess, model, optimizer, criterion, scheduler, metrics)
-        if ok:
-            return FusedEngine(config, sess, model, optimizer, criterion, scheduler, metrics)
+    if choice not in ("auto", "fused", "generic", "stock"):
+        raise ValueError(f"engine={choice!r}: expected auto | fused | generic | stock")
+    if sess.device.type == "cuda" and choice != "stock":
+        from raydp_b200.torch.fused_engine import DLRMEngine, FusedEngine, select_fused
+        from raydp_b200.torch.generic_engine import GenericGpuEngine
+        plan, why = (None, "engine='generic' was requested") if choice == "generic" else \
+            select_fused(config, model, optimizer, criterion)
+        if plan is not None and plan.kind == "dlrm":
+            return DLRMEngine(config, sess, model, optimizer, criterion, scheduler, metrics, plan)
+        if plan is not None:
+            return FusedEngine(config, sess, model, optimizer, criterion, scheduler, metrics, plan)
         if choice == "fused":
             raise RuntimeError(f"engine='fused' was requested but is not applicable: {why}")
-    elif choice == "fused":
-        raise RuntimeError("engine='fused' needs CUDA workers (resources_per_worker={'GPU': 1})")
+        return GenericGpuEngine(config, sess, model, optimizer, criterion, scheduler, metrics, why)
+    if choice in ("fused", "generic"):
+        raise RuntimeError(f"engine={choice!r} needs CUDA workers (resources_per_worker={{'GPU': 1}})")
     return StockEngine(config, sess, model, optimizer, criterion, scheduler, metrics)

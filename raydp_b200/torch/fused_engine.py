@@ -19,6 +19,7 @@ import torch.distributed as dist
 from raydp_b200 import ops
 from raydp_b200.ops.fused_mlp import FusedMLP
 from raydp_b200.ops.ingest import ArrowGpuLoader
+from raydp_b200.utils.profiling import nvtx_range
 
 _LOSSES = {torch.nn.MSELoss: "mse", torch.nn.SmoothL1Loss: "smooth_l1", torch.nn.BCEWithLogitsLoss: "bce_logits"}
 
@@ -51,41 +52,71 @@ def _optimizer_kind(optimizer) -> Optional[str]:
     return None
 
 
-def _is_dlrm(model) -> bool:
-    from raydp_b200.models.dlrm import DLRMSpec
-    return hasattr(model, "fused_spec") and isinstance(model.fused_spec(), DLRMSpec)
+def select_fused(config, model, optimizer, criterion) -> Tuple[Optional[Any], str]:
+    """Decide whether one of the fully fused engines can run this (model, loss, optimizer).
+
+    Returns ``(plan, "")`` -- an ``MLPPlan`` for :class:`FusedEngine` or a ``DLRMPlan`` for
+    :class:`DLRMEngine` -- or ``(None, why)``; the caller then uses the generic GPU engine.  The model
+    may be ANY ``nn.Module`` (the reference takes arbitrary modules, ``torch/estimator.py:180-187``):
+    the plan is derived from the module itself by :mod:`raydp_b200.torch.lowering`."""
+    from raydp_b200.torch.lowering import lower_module
+    plan, why = lower_module(model)
+    if plan is None:
+        return None, why
+    if not ops.kernels_available():
+        raise RuntimeError("CUDA worker without librdp_kernels.so: run __graft_entry__.build() first")
+    if plan.kind == "dlrm":
+        if type(criterion) is not torch.nn.BCEWithLogitsLoss or _loss_kind(criterion) != "bce_logits":
+            return None, "the fused DLRM path needs BCEWithLogitsLoss(mean)"
+        if _optimizer_kind(optimizer) != "sgd" or optimizer.param_groups[0].get("nesterov"):
+            return None, "the fused DLRM path needs torch.optim.SGD (sparse embedding updates are SGD)"
+        n_cols = len(config.get("feature_columns") or [])
+        if n_cols != plan.spec.num_dense + len(plan.spec.table_sizes):
+            return None, "feature_columns must be the dense columns followed by one column per embedding table"
+        return plan, ""
+    if isinstance(config.get("feature_types"), (list, tuple)):
+        return None, "per-column feature dtypes feed model(*columns): generic path"
+    if _loss_kind(criterion) is None:
+        return None, f"loss {type(criterion).__name__} is not one of MSE / SmoothL1(beta=1) / BCEWithLogits (mean)"
+    if _optimizer_kind(optimizer) is None:
+        return None, f"optimizer {type(optimizer).__name__} is not Adam / AdamW / SGD with one param group"
+    if len(config.get("feature_columns") or []) != plan.spec.in_features:
+        return None, "the number of feature columns differs from the first layer's in_features"
+    return plan, ""
 
 
 def fused_supported(config, model, optimizer, criterion) -> Tuple[bool, str]:
-    if not hasattr(model, "fused_spec"):
-        return False, "model does not describe a fusable layer chain (no fused_spec())"
-    if _is_dlrm(model):
-        if type(criterion) is not torch.nn.BCEWithLogitsLoss or _loss_kind(criterion) != "bce_logits":
-            return False, "the fused DLRM path needs BCEWithLogitsLoss(mean)"
-        if _optimizer_kind(optimizer) != "sgd" or optimizer.param_groups[0].get("nesterov"):
-            return False, "the fused DLRM path needs torch.optim.SGD (sparse embedding updates are SGD)"
-        if not ops.kernels_available():
-            raise RuntimeError("CUDA worker without librdp_kernels.so: run __graft_entry__.build() first")
-        return True, ""
-    if isinstance(config.get("feature_types"), (list, tuple)):
-        return False, "per-column feature dtypes need the generic path"
-    if _loss_kind(criterion) is None:
-        return False, f"loss {type(criterion).__name__} is not one of MSE / SmoothL1(beta=1) / BCEWithLogits (mean)"
-    if _optimizer_kind(optimizer) is None:
-        return False, f"optimizer {type(optimizer).__name__} is not Adam / AdamW / SGD with one param group"
-    try:
-        model.fused_spec()
-    except ValueError as exc:
-        return False, str(exc)
-    if not ops.kernels_available():
-        raise RuntimeError("CUDA worker without librdp_kernels.so: run __graft_entry__.build() first")
-    return True, ""
+    plan, why = select_fused(config, model, optimizer, criterion)
+    return plan is not None, why
+
+
+def _seed_moments(optimizer, named_params: Dict[str, torch.nn.Parameter], targets, m, v, step_dev) -> None:
+    """Carry optimizer state that came in with a pre-trained optimizer instance (Adam moments, SGD
+    momentum buffers, step count) over into the flat fused buffers.  ``targets``: iterable of
+    ``(parameter name, offset, numel)`` into ``m`` / ``v``."""
+    step = 0.0
+    with torch.no_grad():
+        for name, off, n in targets:
+            p = named_params.get(name)
+            st = optimizer.state.get(p) if p is not None else None
+            if not st:
+                continue
+            if "exp_avg" in st:
+                m[off:off + n].copy_(st["exp_avg"].reshape(-1))
+                v[off:off + n].copy_(st["exp_avg_sq"].reshape(-1))
+            elif st.get("momentum_buffer") is not None:
+                m[off:off + n].copy_(st["momentum_buffer"].reshape(-1))
+                step = max(step, 1.0)
+            if "step" in st:
+                step = max(step, float(st["step"]))
+        if step:
+            step_dev.fill_(step)
 
 
 class FusedEngine:
     name = "fused"
 
-    def __init__(self, config, sess, model, optimizer, criterion, scheduler, metrics):
+    def __init__(self, config, sess, model, optimizer, criterion, scheduler, metrics, plan=None):
         self.config = config
         self.sess = sess
         self.device = sess.device
@@ -95,7 +126,12 @@ class FusedEngine:
         self.world = sess.world_size
         self.batch = int(config["batch_size"])
         self.opt_kind = _optimizer_kind(optimizer)
-        spec = model.fused_spec()
+        if plan is None:
+            plan, why = select_fused(config, model, optimizer, criterion)
+            if plan is None:
+                raise RuntimeError(f"FusedEngine cannot run this model: {why}")
+        self.plan = plan
+        spec = plan.spec
         self.fused = FusedMLP(spec, self.batch, self.device, loss=_loss_kind(criterion))
         self.fused.load_state_dict({k: v.to(self.device) for k, v in model.state_dict().items()})
         if self.world > 1 and dist.is_initialized():
@@ -108,6 +144,18 @@ class FusedEngine:
         self.v = torch.zeros(n, **f32)
         self.step_dev = torch.zeros(1, **f32)
         self.lr_dev = torch.zeros(1, **f32)
+        if optimizer.state:
+            sl = self.fused._slices
+            L = self.fused.L
+            names = []
+            for l in range(L):
+                names += [(f"{spec.linear_names[l]}.weight", f"W{l}"), (f"{spec.linear_names[l]}.bias", f"b{l}")]
+                if spec.batch_norm:
+                    names += [(f"{spec.bn_names[l]}.weight", f"g{l}"), (f"{spec.bn_names[l]}.bias", f"be{l}")]
+            names += [(f"{spec.linear_names[L]}.weight", "Wh"), (f"{spec.linear_names[L]}.bias", "bh")]
+            _seed_moments(optimizer, dict(model.named_parameters()),
+                          [(pn, sl[k][0], int(torch.tensor(sl[k][1]).prod())) for pn, k in names],
+                          self.m, self.v, self.step_dev)
         self._lr_host = None
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._eager_steps = 0
@@ -220,7 +268,8 @@ class FusedEngine:
         steps = samples = 0
         h2d0 = loader.h2d_bytes
         for x, y in loader:
-            self._train_step(x, y)
+            with nvtx_range("rdp.fused.step"):
+                self._train_step(x, y)
             if extra_metrics:
                 for n in extra_metrics:
                     self.metrics.get(n).update(self.fused.pred[:x.shape[0]].unsqueeze(1), y.unsqueeze(1))
@@ -275,17 +324,22 @@ class DLRMEngine:
 
     name = "fused-dlrm"
 
-    def __init__(self, config, sess, model, optimizer, criterion, scheduler, metrics):
+    def __init__(self, config, sess, model, optimizer, criterion, scheduler, metrics, plan=None):
         from raydp_b200.parallel.hybrid import DistributedDLRM
         self.config, self.sess, self.device = config, sess, sess.device
         self.optimizer, self.scheduler, self.metrics = optimizer, scheduler, metrics
         self.batch = int(config["batch_size"])
         g = optimizer.param_groups[0]
-        self.spec = model.fused_spec()
+        if plan is None:
+            plan, why = select_fused(config, model, optimizer, criterion)
+            if plan is None or plan.kind != "dlrm":
+                raise RuntimeError(f"DLRMEngine cannot run this model: {why}")
+        self.plan = plan
+        self.spec = plan.spec
         self.dlrm = DistributedDLRM(self.spec, self.batch, self.device, momentum=g.get("momentum", 0.0),
                                     weight_decay=g.get("weight_decay", 0.0))
-        self.dlrm.core.load_from_module(model.to(self.device))
-        model.to("cpu")
+        # each rank copies the dense layers and ONLY the tables it owns straight from the host module
+        self.dlrm.core.load_from_module(model, plan)
         cols = list(config["feature_columns"])
         self.dense_cols = cols[:self.spec.num_dense]
         self.sparse_cols = cols[self.spec.num_dense:]
@@ -320,7 +374,8 @@ class DLRMEngine:
         steps = samples = 0
         h2d0 = loader.h2d_bytes
         for dense, idx, y in loader:
-            self.dlrm.train_step(dense, idx, y, float(self.optimizer.param_groups[0]["lr"]))
+            with nvtx_range("rdp.dlrm.step"):
+                self.dlrm.train_step(dense, idx, y, float(self.optimizer.param_groups[0]["lr"]))
             if self.scheduler is not None:
                 self.scheduler.step()
             self._accum_host.copy_(core.accum, non_blocking=True)
@@ -346,7 +401,8 @@ class DLRMEngine:
 
     def state_dict(self):
         torch.cuda.current_stream().synchronize()
-        return self.dlrm.full_state_dict()
+        state = self.dlrm.full_state_dict()
+        return self.plan.rename_state(state) if state else state
 
     def close(self):
         self.dlrm.close()

@@ -245,10 +245,21 @@ class TorchTrainer:
             shards = self._shards_for(n)
             refs = [w.run.remote(self._fn, self._config, addr, port, backend, use_gpu, shards[r],
                                  run_name, storage) for r, w in enumerate(workers)]
-            try:
-                all_reports = runtime.get(refs)
-            except runtime.TaskError as exc:
-                raise TrainingFailedError(str(exc)) from exc
+            # Take the results in COMPLETION order: if any rank fails while the others sit in a
+            # collective (a peer-flag spin, an NCCL/gloo wait), the failure must surface at once so the
+            # `finally` below kills the survivors and FailureConfig can restart the group.  Waiting on
+            # rank 0 first would block on a rank that can never finish.
+            done: Dict[int, Any] = {}
+            index = {ref._id: r for r, ref in enumerate(refs)}
+            pending = list(refs)
+            while pending:
+                ready, pending = runtime.wait(pending, num_returns=1, timeout=None)
+                for ref in ready:
+                    try:
+                        done[index[ref._id]] = runtime.get(ref)
+                    except (runtime.TaskError, runtime.ActorDiedError) as exc:
+                        raise TrainingFailedError(f"rank {index[ref._id]} failed: {exc}") from exc
+            all_reports = [done[r] for r in range(n)]
             self._all_reports = all_reports                 # every rank's reports (legacy Trainer.run)
             return all_reports[0]
         finally:

@@ -98,3 +98,31 @@ def test_trainer_resumes_from_last_reported_checkpoint(ray_cluster, tmp_path):
                          run_config=RunConfig(storage_path=str(tmp_path), name="seeded"),
                          resume_from_checkpoint=Checkpoint.from_dict({"epoch": 2})).fit()
     assert [m["epoch"] for m in again.metrics_history] == [3] and again.checkpoint.to_dict() == {"epoch": 3}
+
+
+def test_failure_of_a_non_zero_rank_surfaces_at_once_and_the_group_restarts(ray_cluster, tmp_path):
+    """Rank 1 raises while rank 0 is inside a collective that can no longer complete.  The driver must
+    see the failure without waiting on rank 0 (which would block until the backend's timeout), tear the
+    group down and let ``FailureConfig`` start the next attempt."""
+    import os
+    import time
+    from raydp_b200.train import FailureConfig, RunConfig, ScalingConfig, TorchTrainer, get_context, report
+    flag = str(tmp_path / "rank1_failed_once")
+
+    def loop(config):
+        import torch
+        import torch.distributed as dist
+        rank = get_context().get_world_rank()
+        if rank == 1 and not os.path.exists(config["flag"]):
+            open(config["flag"], "w").close()
+            raise RuntimeError("boom on rank 1")
+        t = torch.ones(1)
+        dist.all_reduce(t)              # first attempt: rank 0 waits here for a peer that is gone
+        report({"sum": float(t.item()), "rank": rank})
+
+    t0 = time.time()
+    result = TorchTrainer(loop, train_loop_config={"flag": flag}, scaling_config=ScalingConfig(num_workers=2),
+                          run_config=RunConfig(storage_path=str(tmp_path), name="rank1",
+                                               failure_config=FailureConfig(max_failures=1))).fit()
+    assert result.metrics["sum"] == 2.0 and os.path.exists(flag)
+    assert time.time() - t0 < 120, "the driver waited for the stuck rank instead of the failed one"
