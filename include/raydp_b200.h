@@ -103,6 +103,21 @@ int rdp_ingest_pack(const void* const* cols, const int* dtypes, int n_cols, int6
 int rdp_ingest_indices(const void* const* cols, const int* dtypes, int n_cols, int64_t rows, int64_t src_offset,
                        const int* table_rows, int n_cross, const int* cross_a, const int* cross_b,
                        const int* cross_rows, int* out, void* stream);
+// v2: `cols[s]` is the value buffer of SOURCE column s holding `widths[s]` consecutive features per row
+// (1 = scalar column; w = fixed-width vector column, child values row-major [rows, w]); `valid[s]` is the
+// column's Arrow validity bitmap (device copy; NULL = no nulls) whose bit `vbit0[s] + row` belongs to `row`
+// of the staged range.  A null feature / label becomes `null_value` (pass NAN for the reference's
+// pandas semantics, 0 for fill-with-zero); a null index becomes row 0.  ld >= sum(widths).
+int rdp_ingest_pack_v2(const void* const* cols, const void* const* valid, const int* vbit0, const int* widths,
+                       const int* dtypes, int n_src, int64_t rows, int64_t src_offset, void* out, int ld,
+                       int out_f32, const float* shift, const float* scale, float null_value, const void* label,
+                       const void* label_valid, int label_vbit0, int label_dtype, float* label_out, void* stream);
+int rdp_ingest_indices_v2(const void* const* cols, const void* const* valid, const int* vbit0, const int* dtypes,
+                          int n_cols, int64_t rows, int64_t src_offset, const int* table_rows, int n_cross,
+                          const int* cross_a, const int* cross_b, const int* cross_rows, int* out, void* stream);
+// All host->device copies of one chunk in one call: dst[i] (device address), src_host[i] (pinned host
+// address), bytes[i]; one cudaMemcpyAsync per entry on `stream`.
+int rdp_ingest_stage(const uint64_t* dst, const uint64_t* src_host, const uint64_t* bytes, int n, void* stream);
 
 // ---- K1 / K2: peer-memory gradient all-reduce fused with the optimizer ---------------------------
 // (NCCL all-reduce issued by DDP + torch.optim step; reference torch/estimator.py:243, :284-286)

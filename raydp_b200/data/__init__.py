@@ -332,16 +332,19 @@ class Dataset:
                  feature_columns: Optional[Union[List[str], List[List[str]], Dict[str, List[str]]]] = None,
                  label_column_dtype=None, feature_column_dtypes=None, batch_size: int = 1,
                  prefetch_batches: int = 1, drop_last: bool = False, unsqueeze_label_tensor: bool = True,
-                 unsqueeze_feature_tensors: bool = True):
+                 unsqueeze_feature_tensors: bool = True, null_fill: float = float("nan")):
         """Iterable of ``(features, label)`` torch tensors.
 
         Single dtype (or None) -> features is one ``[B, F]`` tensor; a list of per-column
-        dtypes -> a list of ``[B, 1]`` tensors.
+        dtypes -> a list of ``[B, 1]`` tensors.  A NULL in a column that
+        ends up as a floating tensor becomes ``null_fill`` -- NaN by default, which is what the
+        reference's Arrow -> pandas -> numpy path yields; integer tensors get 0.  The GPU loader
+        (``raydp_b200.ops.ingest``) follows the same rule inside its kernel.
         """
         from raydp_b200.data.torch_iter import TorchBatchIterable
         return TorchBatchIterable(self, label_column, feature_columns, label_column_dtype,
                                   feature_column_dtypes, batch_size, drop_last,
-                                  unsqueeze_label_tensor)
+                                  unsqueeze_label_tensor, null_fill=null_fill)
 
     # ------------------------------------------------------------------ transforms
     def split(self, n: int, equal: bool = False, locality_hints=None) -> List["Dataset"]:

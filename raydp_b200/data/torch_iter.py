@@ -15,15 +15,22 @@ import numpy as np
 import pyarrow as pa
 
 
-def _column_numpy(table: pa.Table, name: str) -> np.ndarray:
+def _column_numpy(table: pa.Table, name: str, null_fill: float = 0.0, floating: bool = False) -> np.ndarray:
+    """One column as a numpy array.  NULLs: ``null_fill`` when the consumer wants a floating tensor
+    (``floating=True``; NaN reproduces the reference's pandas path), else 0."""
     col = table.column(name)
-    if col.null_count:
-        col = col.fill_null(0)
     arr = col.combine_chunks() if isinstance(col, pa.ChunkedArray) else col
     if pa.types.is_timestamp(arr.type) or pa.types.is_date(arr.type):
         arr = arr.cast(pa.int64())
     if pa.types.is_boolean(arr.type):
         arr = arr.cast(pa.int8())
+    if arr.null_count:
+        if floating:
+            mask = arr.is_null().to_numpy(zero_copy_only=False)
+            out = arr.fill_null(0).to_numpy(zero_copy_only=False).astype(np.float64, copy=True)
+            out[mask] = null_fill
+            return out
+        arr = arr.fill_null(0)
     return arr.to_numpy(zero_copy_only=False)
 
 
@@ -60,31 +67,36 @@ def _np_dtype(torch_dtype):
             torch.bfloat16: np.float32}.get(torch_dtype, None)
 
 
+def _is_float_np(dt) -> bool:
+    return dt is not None and np.issubdtype(dt, np.floating)
+
+
 def block_to_arrays(table: pa.Table, feature_columns: Sequence[str], feature_dtype,
-                    label_column: Optional[str], label_dtype):
+                    label_column: Optional[str], label_dtype, null_fill: float = float("nan")):
     """One Arrow block -> ``([n, F] features, [n, 1] label)`` numpy arrays."""
     f_np = _np_dtype(feature_dtype) or np.float32
+    ffl = _is_float_np(f_np)
     if any(_is_vector(table, name) for name in feature_columns):
         # vector columns contribute their width: [scalar | vector(k) | ...] -> [n, 1 + k + ...]
-        parts = [_column_matrix(table, name) if _is_vector(table, name) else _column_numpy(table, name).reshape(-1, 1)
-                 for name in feature_columns]
+        parts = [_column_matrix(table, name) if _is_vector(table, name)
+                 else _column_numpy(table, name, null_fill, ffl).reshape(-1, 1) for name in feature_columns]
         feats = np.concatenate([p.astype(f_np, copy=False) for p in parts], axis=1) if table.num_rows else \
             np.empty((0, len(feature_columns)), dtype=f_np)
     else:
         feats = np.empty((table.num_rows, len(feature_columns)), dtype=f_np)
         for j, name in enumerate(feature_columns):
-            feats[:, j] = _column_numpy(table, name)
+            feats[:, j] = _column_numpy(table, name, null_fill, ffl)
     label = None
     if label_column is not None:
         l_np = _np_dtype(label_dtype) or np.float32
-        label = _column_numpy(table, label_column).astype(l_np, copy=False).reshape(-1, 1)
+        label = _column_numpy(table, label_column, null_fill, _is_float_np(l_np)).astype(l_np, copy=False).reshape(-1, 1)
     return feats, label
 
 
 class TorchBatchIterable:
     def __init__(self, dataset, label_column, feature_columns, label_column_dtype,
                  feature_column_dtypes, batch_size: int, drop_last: bool,
-                 unsqueeze_label: bool = True):
+                 unsqueeze_label: bool = True, null_fill: float = float("nan")):
         import torch
         self._ds = dataset
         self._label = label_column
@@ -100,6 +112,7 @@ class TorchBatchIterable:
         self._batch = int(batch_size)
         self._drop_last = drop_last
         self._unsqueeze = unsqueeze_label
+        self._null_fill = float(null_fill)
         self._torch = torch
 
     def __len__(self) -> int:
@@ -114,16 +127,20 @@ class TorchBatchIterable:
                 if _is_vector(table, name):
                     t = torch.as_tensor(np.ascontiguousarray(_column_matrix(table, name)))
                 else:
-                    t = torch.as_tensor(np.ascontiguousarray(_column_numpy(table, name))).reshape(-1, 1)
+                    fl = dt is None or dt.is_floating_point
+                    t = torch.as_tensor(np.ascontiguousarray(
+                        _column_numpy(table, name, self._null_fill, fl))).reshape(-1, 1)
                 feats.append(t.to(dt) if dt is not None else t)
             label = None
             if self._label is not None:
-                label = torch.as_tensor(np.ascontiguousarray(_column_numpy(table, self._label)))
+                lfl = self._label_dtype is None or self._label_dtype.is_floating_point
+                label = torch.as_tensor(np.ascontiguousarray(
+                    _column_numpy(table, self._label, self._null_fill, lfl)))
                 label = label.to(self._label_dtype) if self._label_dtype is not None else label
                 label = label.reshape(-1, 1) if self._unsqueeze else label
             return feats, label
         f, l = block_to_arrays(table, self._features, self._feature_dtypes, self._label,
-                               self._label_dtype)
+                               self._label_dtype, self._null_fill)
         ft = torch.from_numpy(f)
         if self._feature_dtypes is not None and ft.dtype != self._feature_dtypes:
             ft = ft.to(self._feature_dtypes)

@@ -243,6 +243,56 @@ def ingest_indices(col_ptrs, dtype_codes, rows, src_offset, table_rows, out: tor
     _check(lib().rdp_ingest_indices(ptrs, codes, n, rows, src_offset, trows, nc, ca, cb, cr, _ptr(out), _stream()))
 
 
+def ingest_pack_v2(col_ptrs: Sequence[int], valid_ptrs: Sequence[int], vbit0: Sequence[int], widths: Sequence[int],
+                   dtype_codes: Sequence[int], rows: int, src_offset: int, out: torch.Tensor, shift=None, scale=None,
+                   null_value: float = float("nan"), label_ptr: int = 0, label_valid_ptr: int = 0,
+                   label_vbit0: int = 0, label_code: int = 0, label_out: Optional[torch.Tensor] = None,
+                   stream: Optional[torch.cuda.Stream] = None) -> None:
+    """Pack staged Arrow columns (scalar or fixed-width vector, with validity bitmaps) into ``out[rows, ld]``."""
+    n = len(col_ptrs)
+    m = max(1, n)
+    ptrs = (ctypes.c_void_p * m)(*col_ptrs)
+    valid = (ctypes.c_void_p * m)(*[v or None for v in valid_ptrs])
+    vb = (ctypes.c_int * m)(*vbit0)
+    ws = (ctypes.c_int * m)(*widths)
+    codes = (ctypes.c_int * m)(*dtype_codes)
+    s = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _stream()
+    _check(lib().rdp_ingest_pack_v2(ptrs, valid, vb, ws, codes, n, rows, src_offset, _ptr(out), _pitch(out),
+                                    1 if out.dtype == torch.float32 else 0, _ptr(shift), _ptr(scale),
+                                    float(null_value), ctypes.c_void_p(label_ptr) if label_ptr else None,
+                                    ctypes.c_void_p(label_valid_ptr) if label_valid_ptr else None, label_vbit0,
+                                    label_code, _ptr(label_out), s))
+
+
+def ingest_indices_v2(col_ptrs, valid_ptrs, vbit0, dtype_codes, rows, src_offset, table_rows, out: torch.Tensor,
+                      crosses: Sequence = (), stream: Optional[torch.cuda.Stream] = None) -> None:
+    n = len(col_ptrs)
+    ptrs = (ctypes.c_void_p * n)(*col_ptrs)
+    valid = (ctypes.c_void_p * n)(*[v or None for v in valid_ptrs])
+    vb = (ctypes.c_int * n)(*vbit0)
+    codes = (ctypes.c_int * n)(*dtype_codes)
+    trows = (ctypes.c_int * n)(*[int(t) for t in table_rows])
+    nc = len(crosses)
+    ca = (ctypes.c_int * max(1, nc))(*[c[0] for c in crosses])
+    cb = (ctypes.c_int * max(1, nc))(*[c[1] for c in crosses])
+    cr = (ctypes.c_int * max(1, nc))(*[c[2] for c in crosses])
+    s = ctypes.c_void_p(stream.cuda_stream) if stream is not None else _stream()
+    _check(lib().rdp_ingest_indices_v2(ptrs, valid, vb, codes, n, rows, src_offset, trows, nc, ca, cb, cr,
+                                       _ptr(out), s))
+
+
+def ingest_stage(dst: Sequence[int], src: Sequence[int], nbytes: Sequence[int], stream: torch.cuda.Stream) -> None:
+    """Issue every host->device copy of a chunk from one native call (``cudaMemcpyAsync`` per span)."""
+    global _launches
+    n = len(dst)
+    if n == 0:
+        return
+    arr = ctypes.c_uint64 * n
+    rc = lib().rdp_ingest_stage(arr(*dst), arr(*src), arr(*nbytes), n, ctypes.c_void_p(stream.cuda_stream))
+    if rc != 0:
+        raise KernelError(f"rdp_ingest_stage failed ({rc}): {kernels_lib().rdp_last_error().decode()}")
+
+
 # ---- DLRM: embedding exchange, dot interaction, BCE loss ------------------------------------------
 def _vp_arr(ptrs):
     return (ctypes.c_void_p * max(1, len(ptrs)))(*[ctypes.c_void_p(int(x)) for x in ptrs])

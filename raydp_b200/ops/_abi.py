@@ -26,6 +26,9 @@ SIGNATURES = {
     "rdp_memcpy_d2h_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_ingest_pack": (I, [VP, VP, I, I64, I64, VP, I, I, VP, VP, VP, I, VP, VP]),
     "rdp_ingest_indices": (I, [VP, VP, I, I64, I64, VP, I, VP, VP, VP, VP, VP]),
+    "rdp_ingest_pack_v2": (I, [VP, VP, VP, VP, VP, I, I64, I64, VP, I, I, VP, VP, F, VP, VP, I, I, VP, VP]),
+    "rdp_ingest_indices_v2": (I, [VP, VP, VP, VP, I, I64, I64, VP, I, VP, VP, VP, VP, VP]),
+    "rdp_ingest_stage": (I, [VP, VP, VP, I, VP]),
 }
 
 class OptArgs(C.Structure):

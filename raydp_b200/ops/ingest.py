@@ -5,20 +5,29 @@ pandas -> numpy -> ``torch.as_tensor`` -> concat/cast on the CPU, then a blockin
 GPU-patched loop).  Here the host only *addresses* data:
 
 1. every block of the shard is mapped from the object store and page-locked once
-   (``cudaHostRegister`` on the shared-memory mapping, so Arrow column buffers are DMA-able
-   in place);
-2. per chunk of rows, one ``cudaMemcpyAsync`` per column moves the raw column bytes to a
-   double-buffered device staging area on a side stream;
-3. the ingest kernel (``rdp_ingest_pack`` / ``rdp_ingest_indices``) decodes the mixed-dtype
-   columns, normalises, zero-pads and writes the row-major bf16 feature matrix that the
-   tcgen05 GEMM reads through TMA, plus the fp32 label vector, on the compute stream.
+   (``cudaHostRegister`` on the shared-memory mapping, so Arrow buffers are DMA-able in place) and
+   the copy plan of every chunk -- (device offset, host address, bytes) of each value buffer and
+   validity bitmap -- is computed ONCE; later epochs replay it;
+2. per chunk of rows ONE native call (``rdp_ingest_stage``) issues all ``cudaMemcpyAsync`` of the chunk
+   on a side stream into a double-buffered device staging area;
+3. the ingest kernel (``rdp_ingest_pack_v2`` / ``rdp_ingest_indices_v2``), also on the side stream,
+   decodes the mixed-dtype columns -- validity bitmaps included: a null feature becomes ``null_fill``
+   (default NaN, which is what the reference's pandas/numpy path produces for a null float; pass
+   ``null_fill=0.0`` to train through missing values), vector columns (``fixed_size_list`` /
+   uniform ``list``, e.g. a ``VectorAssembler`` output) contribute their width -- normalises, zero-pads
+   and writes the row-major bf16 feature matrix that the tcgen05 GEMM reads through TMA, plus the
+   fp32 label vector, into one of TWO output slots;
+4. the compute stream waits for the slot's "ready" event, the consumer trains on it, and the side
+   stream only refills a slot after the "free" event recorded behind the consumer's work: batch i+1
+   is copied and packed while step i runs.
 
 Batches may straddle chunk and block boundaries; they are assembled directly in the output
-buffer by packing at a row offset, so there is no concat.
+slot by packing at a row offset, so there is no concat.
 """
 from __future__ import annotations
 
-from typing import Iterator, List, Optional, Sequence, Tuple
+import ctypes
+from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 import pyarrow as pa
@@ -30,59 +39,88 @@ _ARROW_CODES = {pa.float32(): (0, 4), pa.float64(): (1, 8), pa.int32(): (2, 4), 
                 pa.int16(): (4, 2), pa.int8(): (5, 1), pa.uint8(): (5, 1)}
 
 
-def _plain_array(col: pa.ChunkedArray) -> List[pa.Array]:
-    """Fixed-width, null-free chunks whose data buffer can be copied as raw bytes."""
-    out = []
-    for chunk in col.chunks:
-        t = chunk.type
-        if pa.types.is_boolean(t):
-            chunk = chunk.cast(pa.int8())
-        elif pa.types.is_timestamp(t) or pa.types.is_date64(t):
-            chunk = chunk.cast(pa.int64())
-        elif pa.types.is_date32(t) or pa.types.is_uint16(t):
-            chunk = chunk.cast(pa.int32())
-        elif pa.types.is_uint32(t) or pa.types.is_uint64(t):
-            chunk = chunk.cast(pa.int64())
-        elif pa.types.is_float16(t):
-            chunk = chunk.cast(pa.float32())
-        if chunk.null_count:
-            chunk = chunk.fill_null(0)
-        if chunk.type not in _ARROW_CODES:
-            raise TypeError(f"column type {chunk.type} cannot be ingested; encode it on the executors "
-                            "(strings/dictionaries must become numeric ids before training)")
-        out.append(chunk)
-    return out
+def _raw_copyable(chunk: pa.Array) -> pa.Array:
+    """Bring a scalar chunk to a fixed-width type whose value buffer can be copied as raw bytes
+    (casts of views such as timestamp -> int64 are zero-copy; bool / unsigned / half are re-encoded)."""
+    t = chunk.type
+    if pa.types.is_boolean(t):
+        chunk = chunk.cast(pa.int8())
+    elif pa.types.is_timestamp(t) or pa.types.is_date64(t) or pa.types.is_duration(t) or pa.types.is_time64(t):
+        chunk = chunk.cast(pa.int64())
+    elif pa.types.is_date32(t) or pa.types.is_uint16(t) or pa.types.is_time32(t):
+        chunk = chunk.cast(pa.int32())
+    elif pa.types.is_uint32(t) or pa.types.is_uint64(t):
+        chunk = chunk.cast(pa.int64())
+    elif pa.types.is_float16(t):
+        chunk = chunk.cast(pa.float32())
+    elif pa.types.is_decimal(t):
+        chunk = chunk.cast(pa.float64())
+    if chunk.type not in _ARROW_CODES:
+        raise TypeError(f"column type {chunk.type} cannot be ingested; encode it on the executors "
+                        "(strings/dictionaries must become numeric ids before training)")
+    return chunk
 
 
-class _ColumnSpan:
-    """A run of rows of one column that is contiguous in (pinned) host memory."""
-    __slots__ = ("address", "rows", "code", "width", "keep")
+class _Span:
+    """Rows of one column that are contiguous in (pinned) host memory: value buffer + validity bitmap."""
+    __slots__ = ("address", "rows", "code", "elem", "width", "valid_address", "valid_bit0", "keep")
 
     def __init__(self, arr: pa.Array):
-        if arr.type not in _ARROW_CODES:
-            raise TypeError(f"the GPU ingest path reads fixed-width numeric columns, not {arr.type}: expand vector "
-                            "columns into scalar columns (F.col('features')[i]) or use a model without fused_spec()")
-        code, width = _ARROW_CODES[arr.type]
-        buf = arr.buffers()[1]
-        self.address = buf.address + arr.offset * width
-        self.rows = len(arr)
-        self.code, self.width = code, width
-        self.keep = arr            # keeps the Arrow buffer (and the shm mapping) alive
+        t = arr.type
+        width, first = 1, arr.offset
+        top = arr
+        if pa.types.is_fixed_size_list(t):
+            width = t.list_size
+            values = arr.values
+            first = arr.offset * width
+        elif pa.types.is_list(t) or pa.types.is_large_list(t):
+            offs = np.asarray(arr.offsets)                 # zero-copy view of the offsets (already sliced)
+            width = int(offs[1] - offs[0]) if len(arr) else 1
+            if len(arr) and (width <= 0 or not np.array_equal(offs, offs[0] + width * np.arange(len(offs), dtype=offs.dtype))):
+                raise TypeError("a vector feature column must hold vectors of ONE length (no empty or ragged rows)")
+            values = arr.values
+            first = int(offs[0]) if len(arr) else 0
+        else:
+            values = None
+        if values is not None:
+            if values.null_count:
+                raise TypeError("a vector feature column must not have nulls inside its vectors")
+            values = _raw_copyable(values)
+            code, elem = _ARROW_CODES[values.type]
+            buf = values.buffers()[1]
+            self.address = buf.address + (values.offset + first) * elem
+            self.keep = (arr, values)
+        else:
+            top = _raw_copyable(arr)
+            code, elem = _ARROW_CODES[top.type]
+            buf = top.buffers()[1]
+            self.address = buf.address + top.offset * elem
+            self.keep = (arr, top)
+        self.rows, self.code, self.elem, self.width = len(arr), code, elem, max(1, width)
+        vbuf = top.buffers()[0] if top.null_count else None
+        self.valid_address = vbuf.address if vbuf is not None else 0
+        self.valid_bit0 = top.offset if vbuf is not None else 0
+
+
+class _Chunk:
+    """One staged row range: the prebuilt copy plan (per staging slot) and the kernel descriptors."""
+    __slots__ = ("rows", "src", "nbytes", "dst_off", "n_copies", "total", "cols", "bytes_total")
 
 
 class ArrowGpuLoader:
     """Iterable of ``(features, label)`` device tensors for one dataset shard.
 
-    ``features`` is bf16 ``[B, ld]`` (zero padded to ``ld``), or int32 ``[B, n_sparse]`` index rows
-    when ``sparse_columns`` is given the iterator yields ``(dense, sparse, label)``.
-    Output tensors are reused between iterations (consume them before the next ``next()``).
+    ``features`` is bf16 (or fp32) ``[B, ld]``, zero padded to ``ld``; when ``sparse_columns`` is given
+    the iterator yields ``(dense, sparse, label)`` with int32 ``[B, n_sparse]`` index rows.
+    Output tensors alternate between two slots: consume a batch before asking for the one after next.
     """
 
     def __init__(self, dataset, feature_columns: Sequence[str], label_column: Optional[str], batch_size: int,
                  drop_last: bool, device: torch.device, ld: Optional[int] = None,
                  out_dtype: torch.dtype = torch.bfloat16, chunk_rows: Optional[int] = None,
                  sparse_columns: Optional[Sequence[str]] = None, table_rows: Optional[Sequence[int]] = None,
-                 shift: Optional[torch.Tensor] = None, scale: Optional[torch.Tensor] = None):
+                 shift: Optional[torch.Tensor] = None, scale: Optional[torch.Tensor] = None,
+                 null_fill: float = float("nan")):
         self.ds = dataset
         self.features = list(feature_columns)
         self.sparse = list(sparse_columns or [])
@@ -91,125 +129,178 @@ class ArrowGpuLoader:
         self.batch = int(batch_size)
         self.drop_last = drop_last
         self.device = device
-        self.ld = ld or (max(8, len(self.features)) + 7) // 8 * 8
+        self._ld_arg = ld
         self.out_dtype = out_dtype
         self.chunk_rows = int(chunk_rows or max(self.batch, 1 << 18))   # staging granularity of the DMA pipeline
         self.shift, self.scale = shift, scale
-        self.copy_stream = torch.cuda.Stream(device=device)
+        self.null_fill = float(null_fill)
+        self.copy_stream = torch.cuda.Stream(device=device) if device.type == "cuda" else None
         self._cols = self.features + self.sparse + ([self.label] if self.label else [])
-        self._blocks: Optional[List[List[List[_ColumnSpan]]]] = None   # [block][col][span]
-        self._stage = [None, None]
-        self._stage_free = [None, None]        # events: compute done reading slot
-        self._x = torch.zeros(self.batch, self.ld, dtype=out_dtype, device=device)
-        self._y = torch.zeros(self.batch, dtype=torch.float32, device=device)
-        self._s = torch.zeros(self.batch, max(1, len(self.sparse)), dtype=torch.int32, device=device) \
-            if self.sparse else None
+        self._chunks: Optional[List[_Chunk]] = None
+        self._stage: List[Optional[torch.Tensor]] = [None, None]
+        self._slots = None
+        self._ready = [torch.cuda.Event(), torch.cuda.Event()] if device.type == "cuda" else [None, None]
+        self._free: List[Optional[torch.cuda.Event]] = [None, None]
         self.h2d_bytes = 0
         self.rows_total = dataset.count()
+        self.n_features: Optional[int] = None
+        self.ld: Optional[int] = ld
 
     def __len__(self) -> int:
         n = self.rows_total
         return n // self.batch if self.drop_last else -(-n // self.batch)
 
-    # ------------------------------------------------------------------ host side
+    # ------------------------------------------------------------------ host side, once
     def _prepare(self) -> None:
-        """Map + pin every block once; later epochs reuse the mappings."""
-        if self._blocks is not None:
+        """Map + pin every block once, build the copy plan of every chunk, allocate the device buffers;
+        epochs replay the plan."""
+        if self._slots is not None:
             return
-        blocks = []
+        stage_bytes = self._build_plan()
+        for slot in range(2):
+            self._stage[slot] = torch.empty(max(stage_bytes, 1 << 20), dtype=torch.uint8, device=self.device)
+        B, ns = self.batch, len(self.sparse)
+        self._slots = [(torch.zeros(B, self.ld, dtype=self.out_dtype, device=self.device),
+                        torch.zeros(B, dtype=torch.float32, device=self.device) if self.label else None,
+                        torch.zeros(B, max(1, ns), dtype=torch.int32, device=self.device) if ns else None)
+                       for _ in range(2)]
+
+    def _build_plan(self) -> int:
+        """Host-only part of :meth:`_prepare`: returns the staging bytes one chunk needs at most."""
+        chunks: List[_Chunk] = []
+        self._keep = []                 # spans own the Arrow arrays, which own the pinned mappings
+        stage_bytes = 0
+        widths_seen = None
         for blk in self.ds._blocks:
-            table = blk.load(pin=True).select(self._cols)
-            cols = []
-            for name in self._cols:
-                cols.append([_ColumnSpan(a) for a in _plain_array(table.column(name))])
-            blocks.append(cols)
-        self._blocks = blocks
-
-    def _chunks(self) -> Iterator[Tuple[List[Tuple[int, int, int, int]], int]]:
-        """Yield (per-column copy lists, rows) for successive row ranges of <= chunk_rows."""
-        for cols in self._blocks:
-            total = sum(s.rows for s in cols[0])
-            start = 0
-            while start < total:
-                rows = min(self.chunk_rows, total - start)
-                plan = []
+            table = blk.load(pin=self.device.type == "cuda").select(self._cols)
+            if table.num_rows == 0:
+                continue
+            cols = [[_Span(a) for a in table.column(name).chunks if len(a)] for name in self._cols]
+            self._keep.append(cols)
+            widths = [spans[0].width for spans in cols]
+            for spans in cols:
+                if any(s.width != spans[0].width or s.code != spans[0].code for s in spans):
+                    raise TypeError("a column changes its vector width or type between record batches")
+            if widths_seen is None:
+                widths_seen = widths
+            elif widths != widths_seen:
+                raise TypeError("a vector column changes its width between blocks")
+            # chunk boundaries: every span boundary of every column, then at most chunk_rows apart,
+            # so each chunk lies inside exactly one span of each column (one copy per buffer)
+            cuts = {0, table.num_rows}
+            for spans in cols:
+                pos = 0
+                for s in spans:
+                    pos += s.rows
+                    cuts.add(pos)
+            edges = sorted(cuts)
+            bounds = []
+            for lo, hi in zip(edges, edges[1:]):
+                start = lo
+                while start < hi:
+                    bounds.append((start, min(hi, start + self.chunk_rows)))
+                    start += self.chunk_rows
+            for lo, hi in bounds:
+                ch = _Chunk()
+                ch.rows = hi - lo
+                src, nbytes, dst_off, descr, total = [], [], [], [], 0
                 for spans in cols:
-                    pieces, off, need, pos = [], start, rows, 0
+                    pos = 0
                     for s in spans:
-                        if off >= s.rows:
-                            off -= s.rows
-                            continue
-                        take = min(s.rows - off, need)
-                        pieces.append((s.address + off * s.width, take * s.width, pos * s.width, s.code, s.width))
-                        pos += take
-                        need -= take
-                        off = 0
-                        if need == 0:
+                        if lo < pos + s.rows:
                             break
-                    plan.append(pieces)
-                yield plan, rows
-                start += rows
-
-    def _staging(self, slot: int, nbytes: int) -> torch.Tensor:
-        buf = self._stage[slot]
-        if buf is None or buf.numel() < nbytes:
-            buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=self.device)
-            self._stage[slot] = buf
-        return buf
+                        pos += s.rows
+                    off = lo - pos                                   # first row inside span s
+                    vb = ch.rows * s.width * s.elem
+                    src.append(s.address + off * s.width * s.elem)
+                    nbytes.append(vb)
+                    dst_off.append(total)
+                    val_off, vbit0 = -1, 0
+                    total += (vb + 255) // 256 * 256
+                    if s.valid_address:
+                        bit = s.valid_bit0 + off
+                        nb = (bit % 8 + ch.rows + 7) // 8
+                        src.append(s.valid_address + bit // 8)
+                        nbytes.append(nb)
+                        dst_off.append(total)
+                        val_off, vbit0 = total, bit % 8
+                        total += (nb + 255) // 256 * 256
+                    descr.append((dst_off[-1] if val_off < 0 else dst_off[-2], val_off, vbit0, s.width, s.code))
+                ch.src, ch.nbytes, ch.dst_off, ch.cols, ch.total = src, nbytes, dst_off, descr, total
+                ch.n_copies = len(src)
+                ch.bytes_total = sum(nbytes)
+                stage_bytes = max(stage_bytes, total)
+                chunks.append(ch)
+        self._chunks = chunks
+        nf = len(self.features)
+        self.n_features = sum((widths_seen or [1] * len(self._cols))[:nf])
+        if self.sparse and widths_seen and any(w != 1 for w in widths_seen[nf:nf + len(self.sparse)]):
+            raise TypeError("categorical (index) columns must be scalar integer columns")
+        self.ld = self._ld_arg or (max(8, self.n_features) + 7) // 8 * 8
+        if self.ld < self.n_features:
+            raise ValueError(f"the model takes {self.ld} input features but the feature columns provide "
+                             f"{self.n_features}")
+        return stage_bytes
 
     # ------------------------------------------------------------------ iteration
     def __iter__(self):
         self._prepare()
         compute = torch.cuda.current_stream(self.device)
+        side = self.copy_stream
         nf, ns = len(self.features), len(self.sparse)
-        filled = 0
-        slot = 0
-        for plan, rows in self._chunks():
-            # ---- stage the chunk (side stream) ----
-            offsets, total = [], 0
-            for pieces in plan:
-                width = pieces[0][4]
-                offsets.append(total)
-                total += (rows * width + 255) // 256 * 256
-            stage = self._staging(slot, total)
-            if self._stage_free[slot] is not None:
-                self.copy_stream.wait_event(self._stage_free[slot])
-            base = stage.data_ptr()
-            for pieces, off in zip(plan, offsets):
-                for src, nbytes, dst_off, _code, _w in pieces:
-                    ops.memcpy_h2d_async(base + off + dst_off, src, nbytes, self.copy_stream)
-                    self.h2d_bytes += nbytes
-            ready = torch.cuda.Event()
-            ready.record(self.copy_stream)
-            compute.wait_event(ready)
-            col_ptrs = [base + off for off in offsets]
-            codes = [pieces[0][3] for pieces in plan]
-            # ---- carve batches out of the staged chunk (compute stream) ----
+        out, filled = 0, 0
+        if self._free[out] is not None:
+            side.wait_event(self._free[out])
+        for ci, ch in enumerate(self._chunks):
+            base = self._stage[ci & 1].data_ptr()
+            # staging slot reuse needs no event: its readers (the pack kernels) run on this same stream
+            ops.ingest_stage([base + o for o in ch.dst_off], ch.src, ch.nbytes, side)
+            self.h2d_bytes += ch.bytes_total
+            cols = ch.cols
+            f_ptr = [base + c[0] for c in cols[:nf]]
+            f_val = [base + c[1] if c[1] >= 0 else 0 for c in cols[:nf]]
+            f_vb = [c[2] for c in cols[:nf]]
+            f_w = [c[3] for c in cols[:nf]]
+            f_code = [c[4] for c in cols[:nf]]
+            lab = cols[nf + ns] if self.label else None
             done = 0
-            while done < rows:
-                take = min(self.batch - filled, rows - done)
-                label_ptr = col_ptrs[nf + ns] if self.label else 0
-                label_code = codes[nf + ns] if self.label else 0
-                ops.ingest_pack(col_ptrs[:nf], codes[:nf], take, done, self._x[filled:], self.shift, self.scale,
-                                label_ptr, label_code, self._y[filled:] if self.label else None)
+            while done < ch.rows:
+                take = min(self.batch - filled, ch.rows - done)
+                x, y, s = self._slots[out]
+                ops.ingest_pack_v2(f_ptr, f_val, f_vb, f_w, f_code, take, done, x[filled:], self.shift, self.scale,
+                                   self.null_fill, base + lab[0] if lab else 0,
+                                   base + lab[1] if (lab and lab[1] >= 0) else 0, lab[2] if lab else 0,
+                                   lab[4] if lab else 0, y[filled:] if lab else None, stream=side)
                 if ns:
-                    ops.ingest_indices(col_ptrs[nf:nf + ns], codes[nf:nf + ns], take, done, self.table_rows,
-                                       self._s[filled:])
+                    sc = cols[nf:nf + ns]
+                    ops.ingest_indices_v2([base + c[0] for c in sc], [base + c[1] if c[1] >= 0 else 0 for c in sc],
+                                          [c[2] for c in sc], [c[4] for c in sc], take, done, self.table_rows,
+                                          s[filled:], stream=side)
                 filled += take
                 done += take
                 if filled == self.batch:
-                    yield self._emit(filled)
-                    filled = 0
-            free = torch.cuda.Event()
-            free.record(compute)
-            self._stage_free[slot] = free
-            slot ^= 1
+                    yield self._emit(out, filled, compute, side)
+                    out, filled = self._release(out, compute, side)
         if filled and not self.drop_last:
-            yield self._emit(filled)
+            yield self._emit(out, filled, compute, side)
+            self._release(out, compute, side)
 
-    def _emit(self, rows: int):
-        x = self._x[:rows]
-        y = self._y[:rows] if self.label else None
+    def _emit(self, slot: int, rows: int, compute, side):
+        self._ready[slot].record(side)
+        compute.wait_event(self._ready[slot])
+        x, y, s = self._slots[slot]
+        xv = x[:rows]
+        yv = y[:rows] if y is not None else None
         if self.sparse:
-            return x, self._s[:rows], y
-        return x, y
+            return xv, s[:rows], yv
+        return xv, yv
+
+    def _release(self, slot: int, compute, side) -> Tuple[int, int]:
+        """The consumer's work on ``slot`` has been enqueued: mark it, move to the other slot."""
+        if self._free[slot] is None:
+            self._free[slot] = torch.cuda.Event()
+        self._free[slot].record(compute)
+        other = slot ^ 1
+        if self._free[other] is not None:
+            side.wait_event(self._free[other])
+        return other, 0

@@ -262,7 +262,16 @@ class Column:
         if k == "cast":
             return _cast(a[0].evaluate(table, ctx), a[1].arrow, n)
         if k == "isin":
-            return pc.is_in(a[0].evaluate(table, ctx), value_set=pa.array(list(a[1])))
+            # SQL three-valued IN: NULL IN (...) is NULL; a miss against a list that holds NULL is NULL
+            # (so NOT IN over such a list selects nothing); only a real match is TRUE
+            value = _full(a[0].evaluate(table, ctx), n)
+            items = list(a[1])
+            present = [v for v in items if v is not None]
+            hit = pc.is_in(value, value_set=pa.array(present, type=value.type if not present else None)) \
+                if present else pa.array(np.zeros(n, dtype=bool))
+            if len(present) != len(items):
+                hit = pc.if_else(hit, pa.scalar(True), pa.scalar(None, pa.bool_()))
+            return pc.if_else(pc.is_valid(value), hit, pa.scalar(None, pa.bool_()))
         if k == "call":
             return _call(a[0], [x.evaluate(table, ctx) if isinstance(x, Column) else x for x in a[1]],
                          n, ctx)
@@ -302,8 +311,9 @@ class Column:
             branches, otherwise = a
             result = otherwise.evaluate(table, ctx) if otherwise is not None else pa.scalar(None)
             for cond, value in reversed(branches):
-                result = pc.if_else(_full(cond.evaluate(table, ctx), n),
-                                    value.evaluate(table, ctx), result)
+                # a NULL condition is "not matched": the next branch (or ELSE) decides, as in Spark
+                taken = pc.fill_null(_full(cond.evaluate(table, ctx), n), False)
+                result = pc.if_else(taken, value.evaluate(table, ctx), result)
             return result
         raise NotImplementedError(f"expression kind {k!r} cannot be evaluated per partition")
 

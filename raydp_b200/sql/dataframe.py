@@ -360,6 +360,9 @@ class DataFrame(DataFrameExtras):
                 pairs = _equi_join_pairs(on)
             except NotImplementedError:
                 return self._theta_join(other, on, how)
+            la, ra = getattr(self, "_alias", None), getattr(other, "_alias", None)
+            if (la or ra) and any("." in n for pair in pairs for n in pair):
+                return self._join_aliased(other, pairs, how, la, ra)
             keys, right_keys = [p[0] for p in pairs], [p[1] for p in pairs]
         else:
             keys = [on] if isinstance(on, str) else [k if isinstance(k, str) else k._output_name() for k in on]
@@ -370,6 +373,46 @@ class DataFrame(DataFrameExtras):
         right = other._collect_table()
         how = {"rightouter": "right_outer", "fullouter": "full_outer"}.get(how, how)
         return left._derive(("join", right, keys, how, right_keys))
+
+    def _join_aliased(self, other: "DataFrame", pairs, how: str, la: Optional[str], ra: Optional[str]) -> "DataFrame":
+        """``df.alias("a").join(df.alias("b"), col("a.k") == col("b.k"))`` (self-joins included): qualified key
+        names are assigned to their side by alias; right-hand columns that collide with left-hand ones stay
+        reachable as ``<right alias>.<column>``, left-hand ones as ``<left alias>.<column>`` or bare."""
+        def side(name: str):
+            if "." in name:
+                qual, bare = name.split(".", 1)
+                if qual == la and bare in self.columns:
+                    return "l", bare
+                if qual == ra and bare in other.columns:
+                    return "r", bare
+            if name in self.columns and name not in other.columns:
+                return "l", name
+            if name in other.columns and name not in self.columns:
+                return "r", name
+            raise ValueError(f"join key {name!r} is ambiguous or unknown: qualify it with "
+                             f"{la or '<left alias>'}. / {ra or '<right alias>'}.")
+        left_keys, right_keys = [], []
+        for a, b in pairs:
+            (sa, na), (sb, nb) = side(a), side(b)
+            if sa == sb:
+                raise ValueError(f"join condition {a} == {b} does not relate the two sides")
+            left_keys.append(na if sa == "l" else nb)
+            right_keys.append(nb if sa == "l" else na)
+        tag = ra or "right"
+        renamed = other
+        semi = how in ("left_semi", "leftsemi", "semi", "left_anti", "leftanti", "anti")
+        for c in other.columns:
+            if c in self.columns and c not in right_keys and not semi:
+                renamed = renamed.withColumnRenamed(c, f"{tag}.{c}")
+        for lk, rk in zip(left_keys, right_keys):
+            if lk != rk:
+                if lk in renamed.columns:
+                    renamed = renamed.withColumnRenamed(lk, f"{tag}.{lk}")
+                renamed = renamed.withColumnRenamed(rk, lk)
+        how = {"semi": "left_semi", "anti": "left_anti"}.get(how, how)
+        out = self.join(renamed, left_keys, how)
+        out._alias = None
+        return out
 
     def _theta_join(self, other: "DataFrame", condition: Column, how: str) -> "DataFrame":
         """A join on an arbitrary predicate (``a.x > b.y``, ranges, mixed conditions): the pairs are formed

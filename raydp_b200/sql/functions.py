@@ -143,7 +143,9 @@ def stddev(c): return _agg("stddev", c)
 def variance(c): return _agg("variance", c)
 def countDistinct(c, *cols): return count_distinct(c, *cols)
 def first(c, ignorenulls: bool = False):
-    return Column("agg", ("first_value", as_column(c), True)) if _plain(ignorenulls) else _agg("first", c)
+    # ignorenulls=False (the default) returns the first ROW's value even when it is NULL, as Spark does
+    col = as_column(c)
+    return Column("agg", ("first_value", col, bool(_plain(ignorenulls))), f"first({col._output_name()})")
 
 
 def row_number() -> Column:

@@ -402,6 +402,12 @@ def _apply(op: tuple, table: pa.Table, ctx: EvalContext) -> pa.Table:
         wanted = [c for c in list(keys) + rest_left + rest_right if c in out.column_names]
         return out.select(wanted) if wanted != out.column_names else out
     if kind == "distinct":
+        # Spark's equality for DISTINCT: NaN equals NaN and -0.0 equals 0.0
+        for i, f in enumerate(table.schema):
+            if pa.types.is_floating(f.type) and table.num_rows:
+                col = table.column(i)
+                col = pc.if_else(pc.is_nan(col), pa.scalar(float("nan"), f.type), pc.add(col, pa.scalar(0.0, f.type)))
+                table = table.set_column(i, f, col)
         try:
             return table.group_by(table.column_names, use_threads=False).aggregate([])
         except (pa.ArrowNotImplementedError, pa.ArrowInvalid):

@@ -251,6 +251,8 @@ class _Parser:
                 left = left / self.unary()
             elif self.op("%"):
                 left = left % self.unary()
+            elif self.kw("div"):            # integral division: 7 div 2 = 3, -7 div 2 = -3 (truncates)
+                left = (left / self.unary()).cast("long")
             else:
                 return left
 

@@ -34,6 +34,10 @@ class ObjectLostError(StoreError):
     """The segment backing an object is gone (its node was removed / data was cleaned up)."""
 
 
+pin_failures = 0       # objects whose mapping could not be page-locked (CUDA absent, or the registration failed)
+pinned_objects = 0
+
+
 class Mapping:
     """Owns one mapped segment; closing unmaps (and unpins) it."""
 
@@ -168,8 +172,18 @@ def get(name: str, pin: bool = False) -> Any:
 
 def get_with_mapping(name: str, pin: bool = False) -> Tuple[Any, Mapping]:
     mapping = open_mapping(name, writable=pin)
-    if pin:
-        mapping.pin()
+    if pin and not mapping.pin():
+        # pageable memory still works with cudaMemcpyAsync, but the copy is staged by the driver and
+        # blocks the calling thread: say so once instead of silently losing the DMA overlap
+        global pin_failures
+        pin_failures += 1
+        if pin_failures == 1:
+            import logging
+            logging.getLogger(__name__).warning(
+                "cudaHostRegister failed for object %s: host->device copies from it will not be asynchronous", name)
+    elif pin:
+        global pinned_objects
+        pinned_objects += 1
     meta = mapping.meta()
     kind = meta.get("kind", KIND_BYTES)
     buf = mapping.buffer()

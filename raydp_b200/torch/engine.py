@@ -32,6 +32,16 @@ def _to_device(obj, device, non_blocking: bool = False):
     return obj.to(device, non_blocking=non_blocking)
 
 
+def move_optimizer_state(optimizer, device) -> None:
+    """Optimizer state created or loaded next to the CPU parameters (Adagrad's sums exist from
+    construction on; Adam moments arrive with a pre-trained optimizer instance) has to follow the
+    parameters to the device; 0-dim "step" counters stay host scalars, as torch.optim expects."""
+    for st in optimizer.state.values():
+        for k, v in list(st.items()):
+            if torch.is_tensor(v) and v.dim() > 0 and v.device != device:
+                st[k] = v.to(device)
+
+
 class StockEngine:
     name = "stock"
 
@@ -46,12 +56,7 @@ class StockEngine:
         # The optimizer was built around the CPU parameters; .to(device) moves them in place
         # (Module.to keeps Parameter identity), so the optimizer keeps pointing at live tensors.
         self.model = prepare_model(model)
-        # state that came in with an optimizer instance (e.g. Adam moments of an earlier fit) was loaded
-        # next to the CPU parameters: it has to follow them to the device ("step" stays a host scalar)
-        for st in optimizer.state.values():
-            for k, v in list(st.items()):
-                if torch.is_tensor(v) and v.dim() > 0 and v.device != self.device:
-                    st[k] = v.to(self.device)
+        move_optimizer_state(optimizer, self.device)
         self.autocast_dtype = config.get("compute_dtype") if self.device.type == "cuda" else None
 
     def _loader(self, shard):
@@ -59,7 +64,8 @@ class StockEngine:
         return shard.to_torch(feature_columns=c["feature_columns"],
                               feature_column_dtypes=c["feature_types"],
                               label_column=c["label_column"], label_column_dtype=c["label_type"],
-                              batch_size=c["batch_size"], drop_last=c["drop_last"])
+                              batch_size=c["batch_size"], drop_last=c["drop_last"],
+                              null_fill=float(c.get("extra", {}).get("null_fill", float("nan"))))
 
     def train_epoch(self, shard) -> Tuple[Dict[str, float], float, Dict[str, float]]:
         self.model.train()

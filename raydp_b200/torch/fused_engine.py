@@ -80,8 +80,6 @@ def select_fused(config, model, optimizer, criterion) -> Tuple[Optional[Any], st
         return None, f"loss {type(criterion).__name__} is not one of MSE / SmoothL1(beta=1) / BCEWithLogits (mean)"
     if _optimizer_kind(optimizer) is None:
         return None, f"optimizer {type(optimizer).__name__} is not Adam / AdamW / SGD with one param group"
-    if len(config.get("feature_columns") or []) != plan.spec.in_features:
-        return None, "the number of feature columns differs from the first layer's in_features"
     return plan, ""
 
 
@@ -157,7 +155,8 @@ class FusedEngine:
                           [(pn, sl[k][0], int(torch.tensor(sl[k][1]).prod())) for pn, k in names],
                           self.m, self.v, self.step_dev)
         self._lr_host = None
-        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
+        self._graph_launches = 0
         self._eager_steps = 0
         self.use_graph = bool(config.get("extra", {}).get("cuda_graph", True))
         self._accum_host = torch.zeros(8, dtype=torch.float32).pin_memory()
@@ -210,24 +209,36 @@ class FusedEngine:
         self._update()
 
     def _train_step(self, x, y) -> None:
+        """Full batches replay a captured CUDA graph.  The loader alternates between two output slots
+        (batch i+1 is copied and packed while step i runs), so there is one graph per input buffer."""
         self._sync_lr()
         full = x.shape[0] == self.batch
+        key = (x.data_ptr(), y.data_ptr())
+        graph = self._graphs.get(key) if (self.use_graph and full) else None
         if not (self.use_graph and full):
             self._step_body(x, y)
-        elif self._graph is not None:
-            self._graph.replay()
+        elif graph is not None:
+            graph.replay()
             ops.add_launches(self._graph_launches)
+            if self.fused.spec.batch_norm:
+                self.fused.num_batches_tracked += 1        # host-side counter: a replay does not run train_step
         elif self._eager_steps < 1:
             self._step_body(x, y)                          # first step warms lazy CUDA state
             self._eager_steps += 1
+        elif len(self._graphs) >= 4:
+            self._step_body(x, y)                          # a caller that keeps changing buffers: stay eager
         else:
             graph = torch.cuda.CUDAGraph()
             before = ops.launch_count()
             with torch.cuda.graph(graph):
                 self._step_body(x, y)                      # x / y are the loader's fixed buffers
             self._graph_launches = ops.launch_count() - before
-            self._graph = graph
+            self._graphs[key] = graph
+            if self.fused.spec.batch_norm:
+                self.fused.num_batches_tracked -= 1        # the capture pass ran the Python body without stepping
             graph.replay()
+            if self.fused.spec.batch_norm:
+                self.fused.num_batches_tracked += 1
         if self.scheduler is not None:
             self.scheduler.step()
 
@@ -239,8 +250,15 @@ class FusedEngine:
             cache = self._loaders = {}
         key = id(shard)
         if key not in cache:
-            cache[key] = ArrowGpuLoader(shard, c["feature_columns"], c["label_column"], self.batch,
-                                        c["drop_last"], self.device, ld=self.fused.kpad)
+            loader = ArrowGpuLoader(shard, c["feature_columns"], c["label_column"], self.batch,
+                                    c["drop_last"], self.device, ld=self.fused.kpad,
+                                    null_fill=float(c.get("extra", {}).get("null_fill", float("nan"))))
+            loader._prepare()
+            if loader.n_features != self.fused.spec.in_features:
+                raise ValueError(f"the feature columns provide {loader.n_features} values per row (vector columns "
+                                 f"count with their width) but the model's first layer takes "
+                                 f"{self.fused.spec.in_features}")
+            cache[key] = loader
         return cache[key]
 
     def _results(self, acc, steps: int) -> Tuple[Dict[str, float], float]:
@@ -353,7 +371,8 @@ class DLRMEngine:
             self._loaders[id(shard)] = ArrowGpuLoader(
                 shard, self.dense_cols, c["label_column"], self.batch, c["drop_last"] or self.sess.world_size > 1,
                 self.device, ld=self.dlrm.core.kpad, sparse_columns=self.sparse_cols,
-                table_rows=list(self.spec.table_sizes))
+                table_rows=list(self.spec.table_sizes),
+                null_fill=float(c.get("extra", {}).get("null_fill", float("nan"))))
         return self._loaders[id(shard)]
 
     def _results(self, acc, steps):

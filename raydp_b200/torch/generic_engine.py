@@ -49,7 +49,12 @@ class GenericGpuEngine:
         if not ops.kernels_available():
             raise RuntimeError("CUDA worker without librdp_kernels.so: run __graft_entry__.build() first")
         model = model.to(self.device)             # keeps Parameter identity: the optimizer stays attached
+        from raydp_b200.torch.engine import move_optimizer_state
+        move_optimizer_state(optimizer, self.device)
         self.n_fused_linears = swap_linears(model)
+        for m in model.modules():                 # gradients live in dense flat buckets (peer-reducible)
+            if isinstance(m, (torch.nn.Embedding, torch.nn.EmbeddingBag)) and m.sparse:
+                m.sparse = False
         self.model = model
         self.dp = FusedDataParallel(model, optimizer, self.device,
                                     bucket_mb=int(config.get("extra", {}).get("bucket_mb", 512)))
@@ -87,7 +92,9 @@ class GenericGpuEngine:
             self._loaders[key] = ArrowGpuLoader(
                 shard, self.float_cols, c["label_column"], self.batch, c["drop_last"], self.device,
                 out_dtype=torch.float32, sparse_columns=self.int_cols or None,
-                table_rows=[0] * len(self.int_cols) if self.int_cols else None)
+                table_rows=[0] * len(self.int_cols) if self.int_cols else None,
+                null_fill=float(c.get("extra", {}).get("null_fill", float("nan"))))
+            self._loaders[key]._prepare()
         return self._loaders[key]
 
     def _inputs(self, item):
@@ -96,7 +103,7 @@ class GenericGpuEngine:
             x, s, y = item
         else:
             (x, y), s = item, None
-        nf = len(self.float_cols)
+        nf = self._loaders[next(iter(self._loaders))].n_features if self._loaders else len(self.float_cols)
         if self.per_column:
             inputs: List[torch.Tensor] = []
             for is_int, pos, dt in self.col_plan:

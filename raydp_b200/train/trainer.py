@@ -74,6 +74,8 @@ def run_worker(train_func: Callable, config: Optional[dict], rank: int, world: i
         index = local_rank if torch.cuda.device_count() > local_rank else 0
         torch.cuda.set_device(index)
         device = torch.device("cuda", index)
+        from raydp_b200.utils.affinity import bind_to_gpu
+        bind_to_gpu(index, local_rank if local_rank < world else rank % max(1, world), world)
     created_pg = False
     if init_pg and world > 1 and not dist.is_initialized():
         os.environ["MASTER_ADDR"] = master_addr

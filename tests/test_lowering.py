@@ -162,7 +162,6 @@ def test_select_fused_checks_loss_optimizer_and_columns():
         assert fe.select_fused(cfg, model, adam, nn.SmoothL1Loss())[0] is not None
         assert "loss" in fe.select_fused(cfg, model, adam, nn.L1Loss())[1]
         assert "optimizer" in fe.select_fused(cfg, model, torch.optim.RMSprop(model.parameters()), nn.MSELoss())[1]
-        assert "feature columns" in fe.select_fused(dict(cfg, feature_columns=["a"]), model, adam, nn.MSELoss())[1]
         assert "per-column" in fe.select_fused(dict(cfg, feature_types=[torch.float] * 20), model, adam, nn.MSELoss())[1]
     finally:
         fe.ops.kernels_available = orig

@@ -279,3 +279,50 @@ def test_frequency_dictionary_recipe(spark_session):
     d0 = ranked.filter(col("column_id") == 0).select("value", "id").withColumnRenamed("value", "c0")
     enc = df.join(d0.filter(col("id") <= 1), "c0", "left").drop("c0").withColumnRenamed("id", "c0").fillna(0, ["c0"])
     assert sorted(r.c0 for r in enc.collect()) == [0, 0, 1, 1, 1]
+
+
+def test_null_conditions_follow_sql_three_valued_logic(spark_session):
+    """A NULL condition in when()/CASE is "not matched"; IN / NOT IN over NULLs is NULL, never TRUE."""
+    from raydp_b200.sql import functions as F
+    spark = spark_session
+    df = spark.createDataFrame([(1, 4.0), (2, None), (3, 2.0), (None, 7.0)], ["k", "v"])
+    got = [r[0] for r in df.select(F.when(F.col("v") > 3, 1).otherwise(0).alias("w")).collect()]
+    assert got == [1, 0, 0, 1]
+    chained = df.select(F.when(F.col("v") > 3, "hi").when(F.col("v").isNull(), "n").alias("c")).collect()
+    assert [r[0] for r in chained] == ["hi", "n", None, "hi"]
+    df.createOrReplaceTempView("null_logic")
+    rows = spark.sql("SELECT CASE WHEN v > 3 THEN 'hi' WHEN v IS NULL THEN 'n' END AS c FROM null_logic").collect()
+    assert [r[0] for r in rows] == ["hi", "n", None, "hi"]
+    assert df.filter(F.col("k").isin(1, None)).count() == 1          # NULL = NULL is not TRUE
+    assert df.filter(~F.col("k").isin(1, None)).count() == 0         # 2 NOT IN (1, NULL) is NULL
+    assert df.filter(~F.col("k").isin(1, 2)).count() == 1            # only k=3; the NULL key stays out
+    assert spark.sql("SELECT * FROM null_logic WHERE k NOT IN (SELECT k FROM null_logic)").count() == 0
+    assert spark.sql("SELECT * FROM null_logic WHERE k IN (SELECT k FROM null_logic)").count() == 3
+
+
+def test_self_join_through_aliases(spark_session):
+    from raydp_b200.sql import functions as F
+    df = spark_session.createDataFrame([(1, 4.0), (2, 5.0), (3, 2.0)], ["k", "v"])
+    a, b = df.alias("a"), df.alias("b")
+    j = a.join(b, F.col("a.k") == F.col("b.k"))
+    assert j.count() == 3 and j.columns == ["k", "v", "b.v"]
+    assert sorted((r[0], r[1]) for r in j.select("a.v", "b.v").collect()) == [(2.0, 2.0), (4.0, 4.0), (5.0, 5.0)]
+    shifted = a.join(b.withColumn("k", F.col("k") + 1).alias("b"), F.col("a.k") == F.col("b.k"), "left")
+    rows = {r["k"]: r["b.v"] for r in shifted.collect()}
+    assert rows == {1: None, 2: 4.0, 3: 5.0}
+    other = spark_session.createDataFrame([(1, "x")], ["id", "tag"]).alias("o")
+    assert a.join(other, F.col("a.k") == F.col("o.id")).select("k", "tag").collect()[0]["tag"] == "x"
+    with pytest.raises(ValueError, match="does not relate"):
+        a.join(b, F.col("a.k") == F.col("a.v"))
+
+
+def test_div_first_and_distinct_details(spark_session):
+    from raydp_b200.sql import functions as F
+    spark = spark_session
+    assert tuple(spark.sql("SELECT 7 div 2 AS a, -7 div 2 AS b").collect()[0]) == (3, -3)
+    df = spark.createDataFrame([(1, None), (1, 2.0), (2, 3.0)], ["k", "v"]).coalesce(1)
+    rows = df.groupBy("k").agg(F.first("v").alias("f"), F.first("v", True).alias("g")).orderBy("k").collect()
+    assert [(r["f"], r["g"]) for r in rows] == [(None, 2.0), (3.0, 3.0)]
+    assert df.agg(F.first("v")).columns == ["first(v)"]
+    d = spark.createDataFrame([(float("nan"),), (float("nan"),), (0.0,), (-0.0,), (None,)], ["x"])
+    assert d.distinct().count() == 3                                   # NaN, 0.0, NULL
