@@ -234,11 +234,7 @@ class FusedEngine:
                 self._step_body(x, y)                      # x / y are the loader's fixed buffers
             self._graph_launches = ops.launch_count() - before
             self._graphs[key] = graph
-            if self.fused.spec.batch_norm:
-                self.fused.num_batches_tracked -= 1        # the capture pass ran the Python body without stepping
-            graph.replay()
-            if self.fused.spec.batch_norm:
-                self.fused.num_batches_tracked += 1
+            graph.replay()                                 # (the capture pass counted this step already)
         if self.scheduler is not None:
             self.scheduler.step()
 

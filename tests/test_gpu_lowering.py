@@ -116,7 +116,7 @@ def test_arbitrary_module_runs_on_the_generic_gpu_engine_and_matches_fp32_torch(
     torch.manual_seed(11)
     model = GeluNet(F, width=64, p=0.0)
     init = copy.deepcopy(model.state_dict())
-    make_opt = lambda m: torch.optim.SGD(m.parameters(), lr=0.02, momentum=0.9)   # noqa: E731
+    make_opt = lambda m: torch.optim.SGD(m.parameters(), lr=0.005, momentum=0.9)  # noqa: E731
     ref_model = copy.deepcopy(model)
     ref_losses = _torch_reference(ref_model, make_opt, nn.MSELoss(), cols, 2048, 2)
     est = _fit(model, make_opt, nn.MSELoss(), cols, 2048, 2)
