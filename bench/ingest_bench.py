@@ -36,6 +36,8 @@ def main():
     ap.add_argument("--batch", type=int, default=131072)
     ap.add_argument("--gpus", type=int, default=int(os.environ.get("WORLD_SIZE", "1")))
     ap.add_argument("--json", default=None)
+    ap.add_argument("--timeline", default=None, help="write a chrome trace of 8 end-to-end steps (torch profiler; "
+                                                     "the steps under the profiler are not timed)")
     args = ap.parse_args()
     args.warmup = 5
     rank, world, local = hb.dist_setup(args.gpus)
@@ -50,7 +52,7 @@ def main():
     runtime.init(num_cpus=2, num_gpus=0)
     dev = torch.device("cuda", local)
     B, steps = args.batch, args.steps
-    rows = (steps + args.warmup) * B
+    rows = (steps + args.warmup + (8 if args.timeline else 0)) * B
     feats, label = hb.synthetic_columns(rows, seed=100 + rank)
     names = [f"f{i}" for i in range(hb.FEATURES)]
     per = rows // 4
@@ -132,11 +134,17 @@ def main():
 
     def step_e2e():
         xb, yb = next(it2)
-        engine._train_step(xb, yb)
-        engine._accum_host.copy_(engine.fused.accum, non_blocking=True)
+        engine._train_step(xb, yb)            # publishes the 32-byte result to pinned host memory itself
     ms, host, clocks = timed(step_e2e, steps, args.warmup)
     out["step_e2e"] = {"ms_per_step": ms, "host_us_per_batch": host * 1e3, "clocks": clocks}
     out["e2e_over_device"] = out["step_device"]["ms_per_step"] / out["step_e2e"]["ms_per_step"]
+    if args.timeline and rank == 0:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(8):
+                step_e2e()
+            torch.cuda.synchronize()
+        prof.export_chrome_trace(args.timeline)
     engine.close()
     if rank == 0:
         print(json.dumps(out), flush=True)

@@ -506,6 +506,17 @@ struct SgdParams {
   __nv_bfloat16* shadow;   // optional bf16 copy of the updated parameters
 };
 
+// The step's result (running loss / metric sums) goes to the host by a STORE from the device into
+// page-locked, device-mapped host memory -- not by a cudaMemcpyAsync.  A device->host memcpy queued behind
+// a training step sits in the copy queue until that step is done, and the host->device copies of the NEXT
+// batches, issued after it, were observed to wait behind it (profiles/ingest_timeline.md): the per-step
+// result read-back was what exposed the input copies.  A kernel store has no place in that queue.
+__global__ void publish_host_kernel(const float* __restrict__ src, volatile float* dst_host, int n) {
+  const int i = threadIdx.x;
+  if (i < n) dst_host[i] = src[i];
+  __threadfence_system();
+}
+
 __global__ void add_scalar_kernel(float* x, float v) { *x += v; }
 
 __device__ __forceinline__ float sgd_update(float p, float g, float* buf, int64_t i, const SgdParams& s) {
@@ -633,6 +644,15 @@ int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const floa
 int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, int N, int K, void* stream) {
   const int total = N * K;
   grad_fixup_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(dw, db, a, c, N, K);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_publish_host(const float* src, float* host_pinned, int n, void* stream) {
+  RDP_REQUIRE(n > 0 && n <= 256, "rdp_publish_host: n=%d (1..256 floats)", n);
+  void* mapped = nullptr;
+  RDP_CHECK_CUDA(cudaHostGetDevicePointer(&mapped, host_pinned, 0));
+  publish_host_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, static_cast<float*>(mapped), n);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -205,6 +205,12 @@ def add_scalar(x: torch.Tensor, v: float) -> None:
     _check(lib().rdp_add_scalar(_ptr(x), float(v), _stream()))
 
 
+def publish_host(src: torch.Tensor, host_pinned: torch.Tensor) -> None:
+    """``host_pinned[:] = src`` by a device-side store into pinned host memory (no memcpy in the copy queue)."""
+    assert host_pinned.is_pinned() and src.dtype == torch.float32 and host_pinned.dtype == torch.float32
+    _check(lib().rdp_publish_host(_ptr(src), ctypes.c_void_p(host_pinned.data_ptr()), src.numel(), _stream()))
+
+
 def memcpy_h2d_async(dst_ptr: int, src_host_ptr: int, nbytes: int, stream: Optional[torch.cuda.Stream] = None) -> None:
     s = ctypes.c_void_p((stream or torch.cuda.current_stream()).cuda_stream)
     _check(lib().rdp_memcpy_h2d_async(ctypes.c_void_p(dst_ptr), ctypes.c_void_p(src_host_ptr), nbytes, s))

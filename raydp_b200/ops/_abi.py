@@ -22,6 +22,7 @@ SIGNATURES = {
     "rdp_relu_bwd_bias": (I, [VP, VP, VP, VP, I, I, I, VP]),
     "rdp_gemm2_nn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP]),
     "rdp_add_scalar": (I, [VP, F, VP]),
+    "rdp_publish_host": (I, [VP, VP, I, VP]),
     "rdp_memcpy_h2d_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_memcpy_d2h_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_ingest_pack": (I, [VP, VP, I, I64, I64, VP, I, I, VP, VP, VP, I, VP, VP]),

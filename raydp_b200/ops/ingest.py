@@ -131,10 +131,17 @@ class ArrowGpuLoader:
         self.device = device
         self._ld_arg = ld
         self.out_dtype = out_dtype
-        self.chunk_rows = int(chunk_rows or max(self.batch, 1 << 18))   # staging granularity of the DMA pipeline
+        # staging granularity of the DMA pipeline: >= 1 MB per fp32 column copy (0.5 MB copies reach 36 GB/s on
+        # this box, 1 MB copies 44.6 GB/s; profiles/ingest_timeline.md)
+        self.chunk_rows = int(chunk_rows or max(self.batch, 1 << 18))
         self.shift, self.scale = shift, scale
         self.null_fill = float(null_fill)
-        self.copy_stream = torch.cuda.Stream(device=device) if device.type == "cuda" else None
+        import os
+        # the side stream outranks the training stream: its short pack kernels must not wait for a gap
+        # between the persistent GEMM kernels of the step that is running
+        prio = -1 if os.environ.get("RAYDP_B200_INGEST_PRIO", "1") != "0" else 0
+        self.copy_stream = torch.cuda.Stream(device=device, priority=prio) if device.type == "cuda" else None
+        self.pack_on_side = os.environ.get("RAYDP_B200_INGEST_PACK", "side") != "compute"
         self._cols = self.features + self.sparse + ([self.label] if self.label else [])
         self._chunks: Optional[List[_Chunk]] = None
         self._stage: List[Optional[torch.Tensor]] = [None, None]
@@ -263,6 +270,12 @@ class ArrowGpuLoader:
             f_w = [c[3] for c in cols[:nf]]
             f_code = [c[4] for c in cols[:nf]]
             lab = cols[nf + ns] if self.label else None
+            pack_stream = side
+            if not self.pack_on_side:            # experiment switch: copies on the side stream, pack on the training stream
+                staged = torch.cuda.Event()
+                staged.record(side)
+                compute.wait_event(staged)
+                pack_stream = compute
             done = 0
             while done < ch.rows:
                 take = min(self.batch - filled, ch.rows - done)
@@ -270,12 +283,12 @@ class ArrowGpuLoader:
                 ops.ingest_pack_v2(f_ptr, f_val, f_vb, f_w, f_code, take, done, x[filled:], self.shift, self.scale,
                                    self.null_fill, base + lab[0] if lab else 0,
                                    base + lab[1] if (lab and lab[1] >= 0) else 0, lab[2] if lab else 0,
-                                   lab[4] if lab else 0, y[filled:] if lab else None, stream=side)
+                                   lab[4] if lab else 0, y[filled:] if lab else None, stream=pack_stream)
                 if ns:
                     sc = cols[nf:nf + ns]
                     ops.ingest_indices_v2([base + c[0] for c in sc], [base + c[1] if c[1] >= 0 else 0 for c in sc],
                                           [c[2] for c in sc], [c[4] for c in sc], take, done, self.table_rows,
-                                          s[filled:], stream=side)
+                                          s[filled:], stream=pack_stream)
                 filled += take
                 done += take
                 if filled == self.batch:
@@ -286,8 +299,9 @@ class ArrowGpuLoader:
             self._release(out, compute, side)
 
     def _emit(self, slot: int, rows: int, compute, side):
-        self._ready[slot].record(side)
-        compute.wait_event(self._ready[slot])
+        if self.pack_on_side:
+            self._ready[slot].record(side)
+            compute.wait_event(self._ready[slot])
         x, y, s = self._slots[slot]
         xv = x[:rows]
         yv = y[:rows] if y is not None else None

@@ -207,6 +207,9 @@ class FusedEngine:
     def _step_body(self, x, y) -> None:
         self.fused.train_step(x, y)
         self._update()
+        # the step's result (running loss / metric sums, 32 bytes) goes to pinned host memory from inside
+        # the step -- part of the replayed graph -- by a device store, not a memcpy (ops.publish_host)
+        ops.publish_host(self.fused.accum, self._accum_host)
 
     def _train_step(self, x, y) -> None:
         """Full batches replay a captured CUDA graph.  The loader alternates between two output slots
@@ -287,9 +290,7 @@ class FusedEngine:
             if extra_metrics:
                 for n in extra_metrics:
                     self.metrics.get(n).update(self.fused.pred[:x.shape[0]].unsqueeze(1), y.unsqueeze(1))
-            # the step's result (running loss / metric sums) goes to pinned host memory, async
-            self._accum_host.copy_(self.fused.accum, non_blocking=True)
-            self.d2h_bytes += 32
+            self.d2h_bytes += 32                 # written by the step itself (see _step_body)
             steps += 1
             samples += x.shape[0]
         end.record()
@@ -393,7 +394,7 @@ class DLRMEngine:
                 self.dlrm.train_step(dense, idx, y, float(self.optimizer.param_groups[0]["lr"]))
             if self.scheduler is not None:
                 self.scheduler.step()
-            self._accum_host.copy_(core.accum, non_blocking=True)
+            ops.publish_host(core.accum, self._accum_host)
             steps += 1
             samples += dense.shape[0]
         end.record()

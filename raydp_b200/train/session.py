@@ -61,7 +61,30 @@ class TrainSession:
         entry: Dict[str, Any] = {"metrics": dict(metrics), "checkpoint": None}
         if checkpoint is not None and self.world_rank == 0:
             entry["checkpoint"] = checkpoint._persist(self.storage_dir).path
+            self._prune_checkpoints()
         self.reports.append(entry)
+
+    def _prune_checkpoints(self) -> None:
+        """``CheckpointConfig(num_to_keep=k)``: the trainer leaves ``k`` in ``<storage>/.num_to_keep``; only the
+        newest ``k`` persisted checkpoints stay on disk (the reference's XGBoost estimator keeps 1)."""
+        import os
+        import shutil
+        marker = os.path.join(self.storage_dir, ".num_to_keep")
+        if not os.path.exists(marker):
+            return
+        try:
+            keep = int(open(marker, "r", encoding="utf-8").read().strip())
+        except ValueError:
+            return
+        mine = [r["checkpoint"] for r in self.reports if r.get("checkpoint")]
+        found = sorted((os.path.join(self.storage_dir, d) for d in os.listdir(self.storage_dir)
+                        if d.startswith("checkpoint_")), key=os.path.getmtime)
+        for path in found[:-keep] if keep > 0 else []:
+            shutil.rmtree(path, ignore_errors=True)
+            for r in self.reports:
+                if r.get("checkpoint") == path:
+                    r["checkpoint"] = None
+        del mine
 
 
 def _set_session(sess: Optional[TrainSession]) -> None:

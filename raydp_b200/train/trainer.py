@@ -159,6 +159,10 @@ class TorchTrainer:
     def fit(self) -> Result:
         storage = self._storage()
         run_name = os.path.basename(storage)
+        keep = self._run.checkpoint_config.num_to_keep
+        if keep:
+            with open(os.path.join(storage, ".num_to_keep"), "w", encoding="utf-8") as fh:
+                fh.write(str(int(keep)))
         max_failures = self._run.failure_config.max_failures
         attempt, last_error = 0, None
         while True:

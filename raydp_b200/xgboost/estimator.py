@@ -1,24 +1,25 @@
-"""``XGBoostEstimator``: gradient-boosted trees from Spark data.
+"""``XGBoostEstimator``: gradient-boosted trees from Spark data, trained data-parallel.
 
 Parity: reference ``python/raydp/xgboost/estimator.py:29-119`` -- ctor ``(xgboost_params,
-label_column, dmatrix_params=None, num_workers=1, resources_per_worker=None, shuffle=True)``,
+label_column, num_workers=1, resources_per_worker=None, shuffle=True)``,
 ``fit(train_ds, evaluate_ds=None, max_retries=3)``, ``fit_on_spark(train_df, evaluate_df=None,
-fs_directory=None, compression=None, max_retries=3, stop_spark_after_conversion=False)`` which
-converts with ``parallelism=num_workers`` (``:105-112``), checkpoint kept per iteration
-(``CheckpointConfig(checkpoint_frequency=1, num_to_keep=1)`` ``:60-68``), ``get_model()``.
+max_retries=3, fs_directory=None, compression=None, stop_spark_after_conversion=False)`` which
+converts with ``parallelism=num_workers`` (``:105-112``), ``get_model()``.  The reference runs
+``XGBoostTrainer`` over ``num_workers`` workers with ``CheckpointConfig(checkpoint_frequency=1,
+num_to_keep=1)`` and ``FailureConfig(max_failures=max_retries)`` (``:58-81``).
 
-Backends: the ``xgboost`` package when importable (same params pass straight through); otherwise
-scikit-learn's histogram gradient boosting with the common xgboost parameter names mapped
-(``objective``, ``eta``/``learning_rate``, ``max_depth``, ``lambda``, ``num_boost_round``), so the
-estimator stays usable in images without xgboost.  Training runs in one runtime task; the
-reference's rabit all-reduce of histograms has no counterpart here (``num_workers`` only sets the
-conversion parallelism).
+Here the boosting runs on this framework's own worker group (``TorchTrainer`` actors, gloo):
+:mod:`raydp_b200.xgboost.hist_gbt` grows every tree from histograms that are all-reduced across the
+``num_workers`` row shards -- the algorithm of XGBoost's distributed ``hist`` method -- rank 0 writes a
+checkpoint after EVERY boosting round (only the newest is kept) and a worker group restarted by
+``FailureConfig`` resumes after the last checkpointed round.  When the ``xgboost`` package is importable
+and ``num_workers == 1`` the package itself trains (same parameters, ``model.json`` in xgboost's own
+format); ``backend`` in the result says which one ran.
 """
 from __future__ import annotations
 
 import logging
 import os
-import pickle
 import tempfile
 from typing import Any, Dict, List, Optional
 
@@ -39,46 +40,72 @@ def _to_xy(table, label_column: str):
     return x, y, cols
 
 
+def _have_xgboost() -> bool:
+    import importlib.util
+    return importlib.util.find_spec("xgboost") is not None
+
+
 def _train_task(params: Dict[str, Any], label_column: str, num_boost_round: int, train_table, eval_table,
                 out_dir: str) -> Dict[str, Any]:
+    """Single-worker training with the xgboost package itself."""
+    import xgboost as xgb  # type: ignore
     x, y, cols = _to_xy(train_table, label_column)
-    result: Dict[str, Any] = {"features": cols}
     os.makedirs(out_dir, exist_ok=True)
-    try:
-        import xgboost as xgb  # type: ignore
-        dtrain = xgb.DMatrix(x, label=y, feature_names=cols)
-        evals = [(dtrain, "train")]
-        if eval_table is not None:
-            xe, ye, _ = _to_xy(eval_table, label_column)
-            evals.append((xgb.DMatrix(xe, label=ye, feature_names=cols), "valid"))
-        history: Dict[str, Any] = {}
-        booster = xgb.train(params, dtrain, num_boost_round=num_boost_round, evals=evals,
-                            evals_result=history, verbose_eval=False)
-        booster.save_model(os.path.join(out_dir, "model.json"))
-        result.update(backend="xgboost", history=history)
-        return result
-    except ImportError:
-        pass
-    from sklearn.ensemble import HistGradientBoostingClassifier, HistGradientBoostingRegressor
-    objective = str(params.get("objective", "reg:squarederror"))
-    common = dict(learning_rate=float(params.get("eta", params.get("learning_rate", 0.3))),
-                  max_depth=int(params["max_depth"]) if params.get("max_depth") else None,
-                  max_iter=int(num_boost_round), l2_regularization=float(params.get("lambda", 0.0)),
-                  random_state=int(params.get("seed", 0)))
-    if objective.startswith(("binary:", "multi:")):
-        model = HistGradientBoostingClassifier(**common)
-    else:
-        loss = "absolute_error" if objective == "reg:absoluteerror" else "squared_error"
-        model = HistGradientBoostingRegressor(loss=loss, **common)
-    model.fit(x, y)
-    metrics = {"train-score": float(model.score(x, y))}
+    dtrain = xgb.DMatrix(x, label=y, feature_names=cols)
+    evals = [(dtrain, "train")]
     if eval_table is not None:
         xe, ye, _ = _to_xy(eval_table, label_column)
-        metrics["valid-score"] = float(model.score(xe, ye))
-    with open(os.path.join(out_dir, "model.pkl"), "wb") as fh:
-        pickle.dump(model, fh)
-    result.update(backend="sklearn-hist-gbt", history=metrics)
-    return result
+        evals.append((xgb.DMatrix(xe, label=ye, feature_names=cols), "valid"))
+    history: Dict[str, Any] = {}
+    booster = xgb.train(params, dtrain, num_boost_round=num_boost_round, evals=evals,
+                        evals_result=history, verbose_eval=False)
+    booster.save_model(os.path.join(out_dir, "model.json"))
+    return {"features": cols, "backend": "xgboost", "history": history}
+
+
+def _boost_loop(config: Dict[str, Any]) -> None:
+    """Body of one boosting worker (rank r of num_workers): boost on the local row shard, histograms
+    all-reduced across the group, one checkpoint per round from rank 0, resume after a restart."""
+    from raydp_b200.train import get_checkpoint, get_context, get_dataset_shard, report
+    from raydp_b200.xgboost import hist_gbt
+    label = config["label_column"]
+    x, y, cols = _to_xy(get_dataset_shard("train").to_arrow(), label)
+    evals = []
+    if config["evaluate"]:
+        xe, ye, _ = _to_xy(get_dataset_shard("evaluate").to_arrow(), label)
+        evals.append((xe, ye, "valid"))
+    rank = get_context().get_world_rank()
+    resume = None
+    ckpt = get_checkpoint()
+    if ckpt is not None and os.path.exists(os.path.join(ckpt.path, MODEL_FILE)):
+        resume = hist_gbt.HistGBTModel.load_model(os.path.join(ckpt.path, MODEL_FILE))
+
+    def after_round(rnd: int, model, metrics: Dict[str, float]) -> None:
+        checkpoint = None
+        tmp = None
+        if rank == 0:
+            tmp = tempfile.mkdtemp(prefix="raydp_b200_gbt_")
+            model.save_model(os.path.join(tmp, MODEL_FILE))
+            checkpoint = Checkpoint.from_directory(tmp)
+        report(dict(metrics, training_iteration=rnd + 1, features=cols), checkpoint=checkpoint)
+        if tmp is not None:
+            import shutil
+            shutil.rmtree(tmp, ignore_errors=True)
+
+    train_fn = config.get("train_fn") or hist_gbt.train
+    train_fn(config["params"], x, y, config["num_boost_round"], evals=evals, feature_names=cols,
+             resume=resume, callback=after_round)
+
+
+MODEL_FILE = "model.gbt.json"
+
+
+class BoostResult(dict):
+    """What ``fit`` returns: a dict (``features``, ``backend``, ``history`` ...) that also carries the
+    trainer result's ``checkpoint`` / ``metrics`` / ``metrics_history`` attributes."""
+    checkpoint = None
+    metrics: Dict[str, Any] = {}
+    metrics_history: List[Dict[str, Any]] = []
 
 
 class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
@@ -100,18 +127,52 @@ class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
             train_ds = train_ds.random_shuffle()
             if evaluate_ds is not None:
                 evaluate_ds = evaluate_ds.random_shuffle()
-        if self._num_workers > 1:
-            logger.warning("XGBoostEstimator trains in one process here; num_workers=%d only sets the "
-                           "conversion parallelism", self._num_workers)
+        if self._num_workers <= 1 and _have_xgboost():
+            return self._fit_with_xgboost_package(train_ds, evaluate_ds, max_retries)
+        from raydp_b200.train import (CheckpointConfig, FailureConfig, RunConfig, ScalingConfig, TorchConfig,
+                                      TorchTrainer)
+        res = dict(self._resources_per_worker or {})
+        res.pop("GPU", None)                      # histogram boosting is a CPU algorithm here
+        datasets = {"train": train_ds}
+        if evaluate_ds is not None:
+            datasets["evaluate"] = evaluate_ds
+        config = {"params": self._xgboost_params, "label_column": self._label_column,
+                  "num_boost_round": self._num_boost_round, "evaluate": evaluate_ds is not None,
+                  "train_fn": getattr(self, "_train_fn", None)}
+        trainer = TorchTrainer(_boost_loop, train_loop_config=config,
+                               scaling_config=ScalingConfig(num_workers=max(1, self._num_workers), use_gpu=False,
+                                                            resources_per_worker=res or None),
+                               run_config=RunConfig(checkpoint_config=CheckpointConfig(checkpoint_frequency=1,
+                                                                                       num_to_keep=1),
+                                                    failure_config=FailureConfig(max_failures=max_retries)),
+                               torch_config=TorchConfig(backend="gloo"), datasets=datasets)
+        result = trainer.fit()
+        self._checkpoint = result.checkpoint
+        history: Dict[str, Dict[str, List[float]]] = {}
+        for m in result.metrics_history:
+            for key, value in m.items():
+                if "-" in key and isinstance(value, float):
+                    name, metric = key.split("-", 1)
+                    history.setdefault(name, {}).setdefault(metric, []).append(value)
+        self._results = BoostResult(features=result.metrics.get("features"), backend="raydp_b200-hist-gbt",
+                                    history=history, num_workers=max(1, self._num_workers),
+                                    rounds=result.metrics.get("training_iteration"))
+        self._results.checkpoint, self._results.metrics = result.checkpoint, result.metrics
+        self._results.metrics_history = result.metrics_history
+        return self._results
+
+    def _fit_with_xgboost_package(self, train_ds, evaluate_ds, max_retries: int):
         out_dir = tempfile.mkdtemp(prefix="raydp_b200_xgb_")
         cpus = float((self._resources_per_worker or {}).get("CPU", 1))
         task = runtime.remote(_train_task).options(num_cpus=cpus, max_retries=max_retries)
         train_ref = runtime.put(train_ds.to_arrow())
         eval_ref = runtime.put(evaluate_ds.to_arrow()) if evaluate_ds is not None else None
-        self._results = runtime.get(task.remote(self._xgboost_params, self._label_column, self._num_boost_round,
-                                                train_ref, eval_ref, out_dir))
+        out = runtime.get(task.remote(self._xgboost_params, self._label_column, self._num_boost_round,
+                                      train_ref, eval_ref, out_dir))
         runtime.free([r for r in (train_ref, eval_ref) if r is not None])
         self._checkpoint = Checkpoint.from_directory(out_dir)
+        self._results = BoostResult(**out)
+        self._results.checkpoint, self._results.metrics, self._results.metrics_history = self._checkpoint, out, [out]
         return self._results
 
     def fit_on_spark(self, train_df, evaluate_df=None, fs_directory: Optional[str] = None,
@@ -142,17 +203,13 @@ class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
     def get_model(self):
         assert self._checkpoint is not None, "Must call fit first"
         path = self._checkpoint.path
-        if os.path.exists(os.path.join(path, "model.json")):
-            import xgboost as xgb  # type: ignore
-            booster = xgb.Booster()
-            booster.load_model(os.path.join(path, "model.json"))
-            return booster
-        with open(os.path.join(path, "model.pkl"), "rb") as fh:
-            model = pickle.load(fh)
-        # code written for xgboost.Booster calls inplace_predict(ndarray); give the fallback model that name
-        if not hasattr(model, "inplace_predict"):
-            model.inplace_predict = model.predict
-        return model
+        if os.path.exists(os.path.join(path, MODEL_FILE)):
+            from raydp_b200.xgboost.hist_gbt import HistGBTModel
+            return HistGBTModel.load_model(os.path.join(path, MODEL_FILE))
+        import xgboost as xgb  # type: ignore
+        booster = xgb.Booster()
+        booster.load_model(os.path.join(path, "model.json"))
+        return booster
 
     @property
     def results(self):
