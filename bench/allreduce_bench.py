@@ -35,7 +35,7 @@ def timed(fn, iters, warm=5):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--check", action="store_true")
-    ap.add_argument("--sizes", default="256,4096,48516,262144,1048576,4194304,16777216,67108864,268435456")
+    ap.add_argument("--sizes", default="256,4096,16384,48516,131072,262144,1048576,4194304,16777216,67108864,268435456")
     ap.add_argument("--json", default=None)
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -55,8 +55,10 @@ def main():
         if args.check:
             ref = x.clone()
             dist.all_reduce(ref)
-            for algo in ("one_shot", "two_shot"):
+            for algo in ("one_shot", "two_shot", "ll"):
                 if algo == "one_shot" and n > (1 << 22):
+                    continue
+                if algo == "ll" and n > (1 << 20):
                     continue
                 red = P2PReducer(x.clone(), torch.device("cuda", local), algo=algo)
                 for rep in range(3):
@@ -88,8 +90,10 @@ def main():
         buf = x.clone()
         t_nccl = timed(lambda: dist.all_reduce(buf), iters)
         res = {"floats": n, "bytes": n * 4, "nccl_us": t_nccl}
-        for algo in ("one_shot", "two_shot"):
+        for algo in ("one_shot", "two_shot", "ll"):
             if algo == "one_shot" and n > (1 << 22):
+                continue
+            if algo == "ll" and n > (1 << 20):
                 continue
             red = P2PReducer(x.clone(), torch.device("cuda", local), algo=algo)
             res[f"{algo}_us"] = timed(lambda: red.allreduce_(), iters)

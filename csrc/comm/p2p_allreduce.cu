@@ -82,6 +82,50 @@ __device__ __forceinline__ float4 ld_peer(const float* p) {
   return v;
 }
 
+// ---- bounded waits -------------------------------------------------------------------------------
+// A wait on a peer's flag must not outlive the peer: a rank that died (or never reached the collective)
+// would otherwise leave this GPU spinning until the process is killed, and nothing above -- FailureConfig
+// restarts, the trainer's failure detection -- could ever run.  Every spin checks %globaltimer now and
+// then; past the deadline it records a code in a host-mapped status word, raises a device-wide "failed"
+// flag (so every later wait of this process returns at once) and RETURNS: the kernel finishes with a
+// meaningless result, the host sees the status at its next check and raises (raydp_b200.comm.check_status).
+__device__ unsigned long long g_spin_timeout_ns = 0ull;     // 0 = wait forever
+__device__ uint32_t* g_comm_status = nullptr;               // page-locked host word, device-mapped
+__device__ int g_comm_failed = 0;
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __noinline__ void report_wait_timeout(uint32_t code) {
+  atomicExch(&g_comm_failed, 1);
+  uint32_t* st = g_comm_status;
+  if (st != nullptr) {
+    *reinterpret_cast<volatile uint32_t*>(st) = code;
+    __threadfence_system();
+  }
+}
+
+// true when *f reached epoch e; false on timeout / after an earlier failure
+__device__ __forceinline__ bool wait_epoch(const uint32_t* f, uint32_t e, uint32_t code) {
+  uint32_t spins = 0;
+  unsigned long long t0 = 0ull;
+  while (int32_t(ld_acquire_sys(f) - e) < 0) {
+    if ((++spins & 1023u) == 0u) {
+      if (*reinterpret_cast<volatile int*>(&g_comm_failed)) return false;
+      const unsigned long long lim = g_spin_timeout_ns;
+      if (lim) {
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0ull) t0 = now;
+        else if (now - t0 > lim) { report_wait_timeout(code); return false; }
+      }
+    }
+  }
+  return true;
+}
+
 // All blocks of this rank's grid have finished their part -> the last one signals `slot` on every
 // peer; then every block waits until all ranks have signalled epoch e on OUR flag array.
 __device__ __forceinline__ void grid_signal_and_wait(const RankArgs& a, int my_rank, int world, uint32_t e,
@@ -98,8 +142,7 @@ __device__ __forceinline__ void grid_signal_and_wait(const RankArgs& a, int my_r
   }
   if (int(threadIdx.x) < world) {
     const uint32_t* f = a.flags[my_rank] + slot * kMaxRanks + threadIdx.x;
-    while (int32_t(ld_acquire_sys(f) - e) < 0) {
-    }
+    wait_epoch(f, e, 0x100u + uint32_t(slot));
   }
   __syncthreads();
 }
@@ -240,6 +283,113 @@ allreduce_kernel(const __grid_constant__ ArParams P) {
   }
 }
 
+// ---- LL: one-round all-reduce for latency-bound messages (<= ~1 MB) ---------------------------------
+// The one-shot kernel above needs a flag round (copy -> signal -> wait) before anybody may pull.  Here the
+// flag travels WITH the data: rank r pushes its gradient into slot r of every peer's receive area as 16-byte
+// packets {v0, e, v1, e} (two floats, each sharing an 8-byte word with the epoch number e, so a packet that
+// arrives torn in halves is still self-validating), then polls ITS OWN receive area until the packets of all
+// ranks carry e, sums them in rank order (bit-identical replicas) and applies the optimizer.  No signal
+// round, no inter-block synchronisation, twice the bytes -- the right trade below ~1 MB on NVSwitch.
+// Receive areas alternate on epoch parity: a rank can be at most one collective ahead of the slowest rank
+// (it needs that rank's packets to finish), so the area of epoch e is never overwritten before every rank
+// has consumed it.  Layout of a rank's region (floats): ll[parity 0..1][source rank][2 * slot_floats].
+struct LlRankArgs {
+  const float* in;
+  float* out;
+  float* base[kMaxRanks];          // base[q]: rank q's region as mapped here
+  uint32_t* epoch;
+  uint32_t* counters;              // [1] finished
+  OptSpec opt;
+};
+
+struct LlParams {
+  LlRankArgs rank[kMaxRanks];
+  int rank_base, world;
+  int64_t n;                       // floats, multiple of 4
+  int64_t slot_floats;
+  float scale;
+};
+
+__device__ __forceinline__ void st_packet(float* p, float v0, float v1, uint32_t e) {
+  asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1, %2, %3, %2};"
+               ::"l"(p), "r"(__float_as_uint(v0)), "r"(e), "r"(__float_as_uint(v1)) : "memory");
+}
+__device__ __forceinline__ uint4 ld_packet(const float* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kArThreads)
+allreduce_ll_kernel(const __grid_constant__ LlParams P) {
+  const LlRankArgs& a = P.rank[blockIdx.y];
+  const int my_rank = P.rank_base + blockIdx.y;
+  const int world = P.world;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(a.epoch) + 1u;
+  const int64_t area = 2 * P.slot_floats;                       // floats per (parity, source) slot
+  const int64_t par_off = int64_t(e & 1u) * kMaxRanks * area;   // slots are laid out for kMaxRanks sources
+  const int64_t n4 = P.n / 4;
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  const int64_t nthreads = int64_t(gridDim.x) * blockDim.x;
+  float lr = a.opt.lr, bc1 = 1.f, bc2 = 1.f;
+  bool first_step = false;
+  if (a.opt.kind) {
+    if (a.opt.lr_ptr) lr = *a.opt.lr_ptr;
+    const float t = a.opt.step_ptr ? *a.opt.step_ptr : 1.f;
+    bc1 = 1.f - powf(a.opt.beta1, t);
+    bc2 = 1.f - powf(a.opt.beta2, t);
+    first_step = t <= 1.f;
+  }
+  // push: my four floats -> two packets in slot `my_rank` of every rank (own region included)
+  for (int64_t i = tid; i < n4; i += nthreads) {
+    const float4 g = reinterpret_cast<const float4*>(a.in)[i];
+#pragma unroll 8
+    for (int q = 0; q < world; ++q) {
+      float* dst = a.base[(my_rank + q) % world] + par_off + int64_t(my_rank) * area + i * 8;
+      st_packet(dst, g.x, g.y, e);
+      st_packet(dst + 4, g.z, g.w, e);
+    }
+  }
+  // pull locally: wait for every rank's packets, sum in rank order
+  bool ok = true;
+  for (int64_t i = tid; i < n4; i += nthreads) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < world; ++q) {
+      const float* src = a.base[my_rank] + par_off + int64_t(q) * area + i * 8;
+      uint4 p0 = ld_packet(src), p1 = ld_packet(src + 4);
+      uint32_t spins = 0;
+      unsigned long long t0 = 0ull;
+      while (ok && (p0.y != e || p0.w != e || p1.y != e || p1.w != e)) {
+        p0 = ld_packet(src);
+        p1 = ld_packet(src + 4);
+        if ((++spins & 1023u) == 0u) {
+          if (*reinterpret_cast<volatile int*>(&g_comm_failed)) { ok = false; break; }
+          const unsigned long long lim = g_spin_timeout_ns;
+          if (lim) {
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0ull) t0 = now;
+            else if (now - t0 > lim) { report_wait_timeout(0x400u + uint32_t(q)); ok = false; }
+          }
+        }
+      }
+      s.x += __uint_as_float(p0.x); s.y += __uint_as_float(p0.z);
+      s.z += __uint_as_float(p1.x); s.w += __uint_as_float(p1.z);
+    }
+    s.x *= P.scale; s.y *= P.scale; s.z *= P.scale; s.w *= P.scale;
+    apply_update(a.opt, i * 4, s, bc1, bc2, lr, first_step, a.out);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(a.counters + 1, 1u);
+    if (prev == uint32_t(gridDim.x - 1)) {
+      a.counters[1] = 0;
+      *a.epoch = e;
+    }
+  }
+}
+
 // One flag round between all ranks (slot 2 of the flag area): everything this GPU wrote before the
 // barrier kernel started -- including peer stores of earlier kernels on the stream -- is ordered
 // before the flag, and the kernel returns only after every rank has signalled the same epoch.
@@ -255,8 +405,7 @@ __global__ void barrier_kernel(const __grid_constant__ BarrierParams p) {
   if (int(threadIdx.x) < p.world) {
     st_release_sys(p.flags[threadIdx.x] + 2 * kMaxRanks + p.rank, e);
     const uint32_t* f = p.flags[p.rank] + 2 * kMaxRanks + threadIdx.x;
-    while (int32_t(ld_acquire_sys(f) - e) < 0) {
-    }
+    wait_epoch(f, e, 0x200u);
   }
   __syncthreads();
   if (threadIdx.x == 0) *p.epoch = e;
@@ -384,6 +533,63 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
   return 0;
 }
 
+// LL one-round all-reduce (latency-bound sizes).  Region of one rank: 2 * 8 * 2 * slot_floats floats
+// (parity x source-rank slots x {value, epoch} packets); zero-initialised; epochs[l] / counters[l] as for
+// rdp_allreduce.  n <= slot_floats, n % 4 == 0.
+int rdp_allreduce_ll(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
+                     const float* const* ins, float* const* outs, uint32_t* const* epochs,
+                     uint32_t* const* counters, const rdp_opt_args* opts, int64_t n, float scale, void* stream) {
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks, "rdp_allreduce_ll: world=%d (max %d)", world, kMaxRanks);
+  RDP_REQUIRE(n_local_ranks == 1 || n_local_ranks == world, "rdp_allreduce_ll: bad n_local_ranks");
+  RDP_REQUIRE(n > 0 && n % 4 == 0 && uint64_t(n) <= slot_floats && slot_floats % 4 == 0,
+              "rdp_allreduce_ll: n=%lld must be a multiple of 4 within the slot (%llu floats)", (long long)n,
+              (unsigned long long)slot_floats);
+  LlParams P;
+  memset(&P, 0, sizeof(P));
+  P.rank_base = n_local_ranks == 1 ? rank : 0;
+  P.world = world; P.n = n; P.slot_floats = int64_t(slot_floats); P.scale = scale;
+  for (int l = 0; l < n_local_ranks; ++l) {
+    LlRankArgs& a = P.rank[l];
+    a.in = ins[l]; a.out = outs[l]; a.epoch = epochs[l]; a.counters = counters[l];
+    for (int q = 0; q < world; ++q) a.base[q] = static_cast<float*>(bases[q]);
+    if (opts != nullptr) {
+      const rdp_opt_args& o = opts[l];
+      a.opt = OptSpec{o.kind, o.p, o.m, o.v, o.lr, o.beta1, o.beta2, o.eps, o.weight_decay, o.momentum,
+                      o.dampening, o.adamw, o.nesterov, o.lr_ptr, o.step_ptr,
+                      static_cast<__nv_bfloat16*>(o.shadow)};
+    }
+  }
+  int blocks = int((n / 4 + kArThreads - 1) / kArThreads);
+  int cap = num_sms();
+  if (n_local_ranks > 1) cap = max(1, (num_sms() / 2) / world);
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  dim3 grid(blocks, n_local_ranks);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  void* args[] = {&P};
+  if (n_local_ranks > 1) {
+    RDP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)allreduce_ll_kernel, grid, dim3(kArThreads), args, 0, s));
+  } else {
+    allreduce_ll_kernel<<<grid, kArThreads, 0, s>>>(P);
+  }
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Bounded peer waits: after `seconds` (0 = forever) a wait on a peer's flag gives up, stores a code (!= 0)
+// into *host_status (page-locked host memory) and every later wait of this process returns at once.
+int rdp_comm_set_timeout(double seconds, uint32_t* host_status) {
+  unsigned long long ns = seconds > 0 ? (unsigned long long)(seconds * 1e9) : 0ull;
+  void* mapped = nullptr;
+  if (host_status != nullptr) RDP_CHECK_CUDA(cudaHostGetDevicePointer(&mapped, host_status, 0));
+  uint32_t* st = static_cast<uint32_t*>(mapped);
+  int zero = 0;
+  RDP_CHECK_CUDA(cudaMemcpyToSymbol(g_spin_timeout_ns, &ns, sizeof(ns)));
+  RDP_CHECK_CUDA(cudaMemcpyToSymbol(g_comm_status, &st, sizeof(st)));
+  RDP_CHECK_CUDA(cudaMemcpyToSymbol(g_comm_failed, &zero, sizeof(zero)));
+  return 0;
+}
+
 }  // extern "C"
 
 // ================================================================================================
@@ -425,8 +631,7 @@ __device__ __forceinline__ void flags_signal_and_wait(uint32_t* const* flags, in
   }
   if (int(threadIdx.x) < world) {
     const uint32_t* f = flags[my_rank] + slot * kMaxRanks + threadIdx.x;
-    while (int32_t(ld_acquire_sys(f) - e) < 0) {
-    }
+    wait_epoch(f, e, 0x300u + uint32_t(slot));
   }
   __syncthreads();
 }

@@ -19,16 +19,17 @@ void set_error(const char* fmt, ...) {
 }
 const char* get_error() { return g_err; }
 
-static int g_num_sms = 0;
+static int g_num_sms[64] = {0};
 int num_sms() {
-  if (g_num_sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess) {
-      cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-    }
-    if (g_num_sms <= 0) g_num_sms = 148;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+  int n = __atomic_load_n(&g_num_sms[dev], __ATOMIC_RELAXED);
+  if (n == 0) {
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+    __atomic_store_n(&g_num_sms[dev], n, __ATOMIC_RELAXED);
   }
-  return g_num_sms;
+  return n;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,

@@ -38,7 +38,20 @@ const char* get_error();
     }                                                                                    \
   } while (0)
 
-int num_sms();
+int num_sms();      // of the CURRENT device (cached per device)
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: a process that
+// launches on a second GPU must set it there too.  `done` is one bit per device ordinal.
+#define RDP_SMEM_ATTR_ONCE_PER_DEVICE(kernel, bytes)                                                    \
+  do {                                                                                                  \
+    static unsigned long long _done = 0ull;                                                             \
+    int _dev = 0;                                                                                       \
+    RDP_CHECK_CUDA(cudaGetDevice(&_dev));                                                               \
+    if (_dev >= 64 || !((__atomic_load_n(&_done, __ATOMIC_ACQUIRE) >> _dev) & 1ull)) {                  \
+      RDP_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes)); \
+      if (_dev < 64) __atomic_fetch_or(&_done, 1ull << _dev, __ATOMIC_RELEASE);                         \
+    }                                                                                                   \
+  } while (0)
 
 // TMA descriptor for a row-major [rows, cols] bf16 matrix (pitch in elements), box
 // [box_rows, box_cols], 128-byte swizzle.  Out-of-bounds elements read as zero.

@@ -457,14 +457,8 @@ void gemm2_set_dynamic_tiles(int on) { g_dynamic_tiles = on ? 1 : 0; }
 template <int kMode, int kMH>
 static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, Gemm2Params p,
                        cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<kMode, kMH, true>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_pair_kernel<kMode, kMH, false>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  RDP_SMEM_ATTR_ONCE_PER_DEVICE((gemm_pair_kernel<kMode, kMH, true>), 227 * 1024);
+  RDP_SMEM_ATTR_ONCE_PER_DEVICE((gemm_pair_kernel<kMode, kMH, false>), 227 * 1024);
   constexpr bool kWgrad = kMode == 1;
   constexpr int kS = (kMH == 1) ? 6 : 4;
   const size_t smem = size_t(kS) * (kMH + 1) * k2HalfBytes + (kWgrad ? 0 : 2 * k2StoreBytes) + 512 + 1024;

@@ -17,6 +17,7 @@
 //                    both operands MN-major straight out of the row-major activations, split
 //                    over CTAs along the batch, fp32 atomics into D).
 #include "common.cuh"
+#include <stdlib.h>
 #include "raydp_b200.h"
 
 #include <mutex>
@@ -45,7 +46,26 @@ struct GemmTnParams {
   int aux_relu_mask;
   int stats_mode;   // 0 none | 1: sum(v), sum(v*v) | 2: sum(v), sum(v*aux)
   float* stats;     // [2, N]
+  // fast kernel only: second statistics row (default stats + N; null = not wanted) and the fused
+  // BatchNorm+ReLU backward of the layer below (see rdp_gemm_tn_bnbwd): with aux = that layer's ReLU
+  // output r, the stored value is (r > 0) ? alpha[n] * acc + beta[n] * r + delta[n] : 0
+  float* stats1;
+  const float* bn_alpha;
+  const float* bn_beta;
+  const float* bn_delta;
+  long long* dbg;   // diagnostics (RDP_GEMM_DBG=1): per-tile timestamps of CTA 0, else null
 };
+
+#define RDP_DBG_STAMP(slot)                                                                         \
+  do {                                                                                              \
+    if (p.dbg != nullptr && blockIdx.x == 0 && dbg_tile < 32) {                                     \
+      long long _t;                                                                                 \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t));                                        \
+      p.dbg[dbg_tile * 16 + (slot)] = _t;                                                           \
+    }                                                                                               \
+  } while (0)
+
+constexpr int kBnCoefCols = 256;     // widest layer the fused BN-backward epilogue keeps coefficients for
 
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -361,9 +381,18 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   uint64_t* stats_final = stats_done + 2;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(stats_final + 1);
   float* s_bias = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(tmem_ptr + 4) + 15) & ~uintptr_t(15));
+  float* s_coef = s_bias + kStatsCols;                                 // [3][kBnCoefCols] (kAux only)
+  const bool bn_bwd = kAux && p.bn_alpha != nullptr;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (bn_bwd) {
+    for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
+      s_coef[i] = p.bn_alpha[i];
+      s_coef[kBnCoefCols + i] = p.bn_beta[i];
+      s_coef[2 * kBnCoefCols + i] = p.bn_delta[i];
+    }
+  }
   if (kStats) {
     uint32_t* o32 = reinterpret_cast<uint32_t*>(ones);
     for (int i = threadIdx.x; i < int(kChunkTileBytes / 4); i += blockDim.x) o32[i] = 0x3F803F80u;
@@ -402,8 +431,11 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (lane == 0) {
       int stage = 0, xb = 0;
       uint32_t phase = 0, x_phase = 0;
+      int dbg_tile = -1;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        ++dbg_tile;
         const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
+        RDP_DBG_STAMP(0);                     // producer reaches the tile
         // operands first: the MMA of this tile must never wait behind the aux buffer, whose release
         // depends on the epilogue + statistics MMAs of two tiles ago
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
@@ -414,6 +446,7 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           tma_load_2d(a_dst + a_bytes, &tmap_b, &full_bar[stage], kb * kBlockK, n_blk * p.n_tile);
           if (++stage == kS) { stage = 0; phase ^= 1; }
         }
+        RDP_DBG_STAMP(1);                     // operand loads issued
         if (kAux) {
           mbar_wait(&x_empty[xb], x_phase ^ 1);
           mbar_expect_tx(&x_full[xb], uint32_t(n_chunks64) * kChunkTileBytes);
@@ -452,9 +485,13 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       int done = 0;
+      int dbg_tile = -1;
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        ++dbg_tile;
+        RDP_DBG_STAMP(2);                     // MMA warp reaches the tile
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
+        RDP_DBG_STAMP(3);                     // accumulator free
         const uint32_t d_tmem = tmem_base + uint32_t(acc) * kFastNTile;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
@@ -469,6 +506,7 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if (kb == p.num_k_blocks - 1) umma_commit(&tmem_full[acc]);
           if (++stage == kS) { stage = 0; phase ^= 1; }
         }
+        RDP_DBG_STAMP(4);                     // operands arrived, MMAs issued
         if (kStats && done > 0) {
           // statistics of the previous tile, whose staged output the epilogue has finished by now
           const int pacc = acc ^ 1;
@@ -500,19 +538,25 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const uint32_t piece0 = uint32_t((c & 63) >> 3);
     int acc = 0;
     uint32_t acc_phase = 0;
+    int dbg_tile = -1;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      ++dbg_tile;
       const int m_blk = t / p.num_n_tiles, n_blk = t % p.num_n_tiles;
       const bool row_ok = (m_blk * kBlockM + r) < p.M;
       const int n0 = n_blk * p.n_tile;
       uint8_t* cbuf = c_stage + acc * c_bytes;
       // the TMA store (and the statistics MMAs) that last read this staging buffer, two tiles ago,
       // must have drained it
+      if (storer) { RDP_DBG_STAMP(5); }
       if (storer) tma_store_wait_read<1>();
+      if (storer) { RDP_DBG_STAMP(6); }       // staging buffer drained by the store of two tiles ago
       if (kStats) mbar_wait(&stats_done[acc], acc_phase ^ 1);
       mbar_wait(&tmem_full[acc], acc_phase);
       if (kAux) mbar_wait(&x_full[acc], acc_phase);
       tc_fence_after();
+      if (storer) { RDP_DBG_STAMP(7); }       // accumulator (and aux) ready
       epi_barrier();
+      if (storer) { RDP_DBG_STAMP(8); }
       if (active) {
         const int col0 = n0 + c;
         uint32_t raw[32];
@@ -539,7 +583,21 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
-        if (kAux && mask) {
+        if (kAux && bn_bwd) {
+          // dgrad fused with the BatchNorm + ReLU backward of the layer it feeds: acc is dL/dy (grad wrt the
+          // BN output), aux is r (the ReLU output = BN input); per-column alpha/beta/delta carry the batch
+          // statistics of dy, which the caller derived from the layer's weight gradient (no pass over dy)
+          const uint32_t* au = reinterpret_cast<const uint32_t*>(ua);
+          const float* al = s_coef + col0;
+          const float* be = s_coef + kBnCoefCols + col0;
+          const float* de = s_coef + 2 * kBnCoefCols + col0;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float a0 = __uint_as_float(au[i] << 16), a1 = __uint_as_float(au[i] & 0xffff0000u);
+            v[2 * i] = a0 > 0.f ? fmaf(al[2 * i], v[2 * i], fmaf(be[2 * i], a0, de[2 * i])) : 0.f;
+            v[2 * i + 1] = a1 > 0.f ? fmaf(al[2 * i + 1], v[2 * i + 1], fmaf(be[2 * i + 1], a1, de[2 * i + 1])) : 0.f;
+          }
+        } else if (kAux && mask) {
           const uint32_t* au = reinterpret_cast<const uint32_t*>(ua);
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
@@ -557,16 +615,20 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           *reinterpret_cast<uint4*>(crow + (((piece0 + q) ^ uint32_t(r & 7)) << 4)) =
               make_uint4(packed[q * 4], packed[q * 4 + 1], packed[q * 4 + 2], packed[q * 4 + 3]);
       }
+      if (storer) { RDP_DBG_STAMP(9); }       // tile converted and staged (this warp)
       tc_fence_before();
       mbar_arrive(&tmem_empty[acc]);
       if (kAux && kStats != 2) mbar_arrive(&x_empty[acc]);
       fence_async_smem();                       // generic-proxy smem writes -> visible to TMA / UMMA
+      if (storer) { RDP_DBG_STAMP(10); }
       epi_barrier();
+      if (storer) { RDP_DBG_STAMP(11); }
       if (storer) {
         for (int ch = 0; ch < n_chunks64; ++ch)
           tma_store_2d(&tmap_c, cbuf + ch * kChunkTileBytes, n0 + ch * 64, m_blk * kBlockM);
         tma_store_commit();
         if (kStats) mbar_arrive(&c_ready[acc]);
+        RDP_DBG_STAMP(12);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -591,7 +653,7 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         const int col = n0 + quad * 32 + lane;
         atomicAdd(&p.stats[col], s0);
-        atomicAdd(&p.stats[p.N + col], s1);
+        if (p.stats1 != nullptr) atomicAdd(&p.stats1[col], s1);
       }
     }
   }
@@ -606,21 +668,41 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 template <int kStats, bool kAux>
 static int launch_fast(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
                        const GemmTnParams& p, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_fast_kernel<kStats, kAux>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  RDP_SMEM_ATTR_ONCE_PER_DEVICE((gemm_tn_fast_kernel<kStats, kAux>), 227 * 1024);
   const size_t smem = size_t(kAux ? 2 : 3) * (16384 + kFastNTile * 128) + (kAux ? 4 : 2) * 2 * kChunkTileBytes +
-                      (kStats ? kChunkTileBytes : 0) + 256 + kStatsCols * sizeof(float) + 1024;
+                      (kStats ? kChunkTileBytes : 0) + 256 + kStatsCols * sizeof(float) +
+                      (kAux ? 3 * kBnCoefCols * sizeof(float) : 0) + 1024;
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   // a CTA must only ever see one n_blk (its TMEM statistics accumulators are per column block)
   int grid = (num_sms() / p.num_n_tiles) * p.num_n_tiles;
   if (grid < p.num_n_tiles) grid = p.num_n_tiles;
   if (tiles < grid) grid = tiles;
-  gemm_tn_fast_kernel<kStats, kAux><<<grid, kFastThreads, smem, stream>>>(ta, tb, tc, tx, p);
+  static long long* dbg_buf = nullptr;
+  static int dbg_left = -1;
+  if (dbg_left < 0) dbg_left = getenv("RDP_GEMM_DBG") ? atoi(getenv("RDP_GEMM_DBG")) : 0;
+  GemmTnParams q = p;
+  q.dbg = nullptr;
+  if (dbg_left > 0) {
+    if (!dbg_buf) RDP_CHECK_CUDA(cudaMalloc(&dbg_buf, 32 * 16 * sizeof(long long)));
+    RDP_CHECK_CUDA(cudaMemsetAsync(dbg_buf, 0, 32 * 16 * sizeof(long long), stream));
+    q.dbg = dbg_buf;
+  }
+  gemm_tn_fast_kernel<kStats, kAux><<<grid, kFastThreads, smem, stream>>>(ta, tb, tc, tx, q);
   RDP_CHECK_CUDA(cudaGetLastError());
+  if (q.dbg) {
+    --dbg_left;
+    static long long host[32 * 16];
+    RDP_CHECK_CUDA(cudaStreamSynchronize(stream));
+    RDP_CHECK_CUDA(cudaMemcpy(host, dbg_buf, sizeof(host), cudaMemcpyDeviceToHost));
+    long long t0 = host[0];
+    fprintf(stderr, "[rdp gemm dbg] stats=%d aux=%d M=%d N=%d K=%d grid=%d (ns since the producer's first stamp)\n",
+            kStats, int(kAux), p.M, p.N, p.K, grid);
+    for (int t = 0; t < 32 && host[t * 16] != 0; ++t) {
+      fprintf(stderr, "  tile %2d:", t);
+      for (int k = 0; k < 13; ++k) fprintf(stderr, " %6lld", host[t * 16 + k] ? host[t * 16 + k] - t0 : -1);
+      fprintf(stderr, "\n");
+    }
+  }
   return 0;
 }
 
@@ -802,17 +884,14 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
   p.bias = bias; p.relu = relu; p.out = out; p.out_f32 = out_f32; p.ldc = ldc;
   p.aux = static_cast<const __nv_bfloat16*>(aux); p.ld_aux = ld_aux; p.aux_relu_mask = aux_relu_mask;
   p.stats_mode = stats_mode; p.stats = stats;
+  p.stats1 = stats ? stats + N : nullptr; p.bn_alpha = p.bn_beta = p.bn_delta = nullptr; p.dbg = nullptr;
   CUtensorMap ta, tb;
   int rc = make_tmap_2d_bf16(&ta, a, M, K, lda, kBlockM, kBlockK);
   if (rc) return rc;
   rc = make_tmap_2d_bf16(&tb, b, N, K, ldb, p.n_tile, kBlockK);
   if (rc) return rc;
   const size_t smem = gemm_tn_smem_bytes(p.n_tile);
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  RDP_SMEM_ATTR_ONCE_PER_DEVICE(gemm_tn_kernel, 227 * 1024);
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
@@ -846,6 +925,37 @@ int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int l
   return 0;
 }
 
+int rdp_gemm_tn_bnbwd(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
+                      const void* aux, int ld_aux, const float* alpha, const float* beta, const float* delta,
+                      float* colsum, void* stream) {
+  RDP_REQUIRE(M > 0 && N > 0 && K > 0, "rdp_gemm_tn_bnbwd: empty problem %dx%dx%d", M, N, K);
+  RDP_REQUIRE(N % 64 == 0 && N <= kBnCoefCols, "rdp_gemm_tn_bnbwd: N=%d must be a multiple of 64 and <= %d", N,
+              kBnCoefCols);
+  RDP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0 && ld_aux % 8 == 0,
+              "rdp_gemm_tn_bnbwd: pitches must be multiples of 8");
+  RDP_REQUIRE(aux && alpha && beta && delta && colsum, "rdp_gemm_tn_bnbwd: missing operand");
+  GemmTnParams f;
+  f.M = M; f.N = N; f.K = K;
+  f.n_tile = (N % kFastNTile == 0) ? kFastNTile : 64;
+  f.num_m_tiles = (M + kBlockM - 1) / kBlockM;
+  f.num_n_tiles = N / f.n_tile;
+  f.num_k_blocks = (K + kBlockK - 1) / kBlockK;
+  f.bias = nullptr; f.relu = 0; f.out = out; f.out_f32 = 0; f.ldc = ldc;
+  f.aux = static_cast<const __nv_bfloat16*>(aux); f.ld_aux = ld_aux; f.aux_relu_mask = 0;
+  f.stats_mode = 1; f.stats = colsum; f.stats1 = nullptr;
+  f.bn_alpha = alpha; f.bn_beta = beta; f.bn_delta = delta; f.dbg = nullptr;
+  CUtensorMap ta, fb, fc, fx;
+  int rc = make_tmap_2d_bf16(&ta, a, M, K, lda, kBlockM, kBlockK);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&fb, b, N, K, ldb, f.n_tile, kBlockK);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&fc, out, M, N, ldc, kBlockM, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&fx, aux, M, N, ld_aux, kBlockM, 64);
+  if (rc) return rc;
+  return launch_fast<1, true>(ta, fb, fc, fx, f, static_cast<cudaStream_t>(stream));
+}
+
 int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
                    int Mw, int Nw, void* stream) {
   RDP_REQUIRE(rows > 0 && Mw > 0 && Nw > 0, "rdp_gemm_wgrad: empty problem");
@@ -874,11 +984,7 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
   if (rc) return rc;
   const int n_chunks = (n_tile + 63) / 64;
   const size_t smem = size_t(kWgradStages) * (2 + n_chunks) * (kBlockK * 128) + 256 + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CHECK_CUDA(cudaFuncSetAttribute(gemm_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  RDP_SMEM_ATTR_ONCE_PER_DEVICE(gemm_wgrad_kernel, 227 * 1024);
   dim3 grid(splits, m_tiles, n_tiles);
   gemm_wgrad_kernel<<<grid, kWgradThreads, smem, static_cast<cudaStream_t>(stream)>>>(tg, tx, p);
   RDP_CHECK_CUDA(cudaGetLastError());
@@ -971,6 +1077,7 @@ extern "C" int rdp_gemm_tn_bnstats_noalloc(const void* a, int lda, const void* b
   p.bias = bias; p.relu = relu; p.out = out; p.out_f32 = out_f32; p.ldc = ldc;
   p.aux = nullptr; p.ld_aux = 0; p.aux_relu_mask = 0;
   p.stats_mode = 1; p.stats = scratch;
+  p.stats1 = scratch + N; p.bn_alpha = p.bn_beta = p.bn_delta = nullptr; p.dbg = nullptr;
   CUtensorMap ta, tb;
   int rc = make_tmap_2d_bf16(&ta, a, M, K, lda, kBlockM, kBlockK);
   if (rc) return rc;

@@ -506,6 +506,65 @@ struct SgdParams {
   __nv_bfloat16* shadow;   // optional bf16 copy of the updated parameters
 };
 
+// BatchNorm backward WITHOUT a pass over the batch.  For a hidden layer l-1 (r = relu(pre), y = BN(r)) feeding
+// Linear l, the two batch sums BN backward needs are linear functionals of quantities the step already has:
+//   sum_b dy[b, j]        = sum_i db_l[i]  * W_l[i, j]              (db_l = column sums of dpre_l)
+//   sum_b dy[b, j] r[b,j] = sum_i W_l[i,j] * G_l[i, j]              (G_l = dpre_l^T r: the raw weight gradient)
+// because dy = dpre_l . W_l.  So after wgrad_l this O(N K) kernel yields d(gamma), d(beta) of BN l-1 and the
+// per-column constants of   dpre_{l-1} = (r > 0) ? alpha * dy + beta * r + delta : 0 ,  which the dgrad GEMM
+// applies in its epilogue (rdp_gemm_tn_bnbwd): dy is never written, the separate elementwise
+// BN+ReLU-backward pass over [B, width] (26 % of the step) is gone.  W is read from the bf16 transposed copy the
+// dgrad GEMM multiplies by, so the sums match the dy that GEMM produces.  The same pass rewrites the raw
+// gradient into the gradient of the UNFOLDED weight (y = a r + c was folded into W_l for the forward):
+//   dW[i, j] = a[j] * G[i, j] + c[j] * db[i]         (what rdp_grad_fixup did as its own launch).
+struct BnBwdCoefParams {
+  float* dw; int ldw;                  // [N, K] raw G in, fixed gradient out
+  const float* db;                     // [N]
+  const __nv_bfloat16* w_t; int ldt;   // [K, N] bf16 transposed unfolded weight
+  int N, K;
+  const float* a; const float* c;      // [K] BN fold of layer l-1 (a = gamma * rstd)
+  const float* mean; const float* rstd;
+  float inv_count;
+  float* dgamma; float* dbeta;         // [K] out (=)
+  float* alpha; float* beta; float* delta;   // [K] out
+};
+
+__global__ void __launch_bounds__(256)
+bn_bwd_coef_kernel(const BnBwdCoefParams p) {
+  __shared__ float red[2][8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + tx;
+  float s1 = 0.f, t = 0.f;
+  if (j < p.K) {
+    const float aj = p.a[j], cj = p.c[j];
+    for (int i = ty; i < p.N; i += 8) {
+      const float g = p.dw[size_t(i) * p.ldw + j];
+      const float w = __bfloat162float(p.w_t[size_t(j) * p.ldt + i]);
+      const float dbi = p.db[i];
+      s1 = fmaf(dbi, w, s1);
+      t = fmaf(w, g, t);
+      p.dw[size_t(i) * p.ldw + j] = fmaf(aj, g, cj * dbi);
+    }
+  }
+  red[0][ty][tx] = s1;
+  red[1][ty][tx] = t;
+  __syncthreads();
+  if (ty == 0 && j < p.K) {
+    // fixed summation order: the result does not depend on scheduling
+    float S1 = 0.f, T = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { S1 += red[0][k][tx]; T += red[1][k][tx]; }
+    const float mu = p.mean[j], rs = p.rstd[j], al = p.a[j];
+    const float S2 = rs * (T - mu * S1);                  // sum_b dy * zhat
+    p.dbeta[j] = S1;
+    p.dgamma[j] = S2;
+    const float be = -al * rs * S2 * p.inv_count;
+    p.alpha[j] = al;
+    p.beta[j] = be;
+    p.delta[j] = -al * S1 * p.inv_count - be * mu;
+  }
+}
+
 // The step's result (running loss / metric sums) goes to the host by a STORE from the device into
 // page-locked, device-mapped host memory -- not by a cudaMemcpyAsync.  A device->host memcpy queued behind
 // a training step sits in the copy queue until that step is done, and the host->device copies of the NEXT
@@ -644,6 +703,17 @@ int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const floa
 int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, int N, int K, void* stream) {
   const int total = N * K;
   grad_fixup_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(dw, db, a, c, N, K);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_bn_bwd_coef(float* dw, int ldw, const float* db, const void* w_t, int ldt, int N, int K, const float* a,
+                    const float* c, const float* mean, const float* rstd, float count, float* dgamma,
+                    float* dbeta, float* alpha, float* beta, float* delta, void* stream) {
+  RDP_REQUIRE(N > 0 && K > 0 && count > 0.f, "rdp_bn_bwd_coef: bad shape N=%d K=%d", N, K);
+  BnBwdCoefParams p{dw, ldw, db, static_cast<const __nv_bfloat16*>(w_t), ldt, N, K, a, c, mean, rstd,
+                    1.f / count, dgamma, dbeta, alpha, beta, delta};
+  bn_bwd_coef_kernel<<<(K + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -24,6 +24,13 @@ int rdp_num_sms(void);
 int rdp_gemm_tn(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int out_f32,
                 int M, int N, int K, const float* bias, int relu, const void* aux, int ld_aux,
                 int aux_relu_mask, int stats_mode, float* stats, void* stream);
+// dgrad fused with the BatchNorm + ReLU backward of the layer it feeds (Linear -> ReLU -> BN chains):
+// out[M,N] (bf16) = (aux > 0) ? alpha[n] * (a . b^T)[m,n] + beta[n] * aux[m,n] + delta[n] : 0, and
+// colsum[n] += sum_m out[m,n] (zero it first; = the bias gradient of that layer).  aux is the layer's ReLU
+// output, alpha/beta/delta come from rdp_bn_bwd_coef.  N % 64 == 0, N <= 256.
+int rdp_gemm_tn_bnbwd(const void* a, int lda, const void* b, int ldb, void* out, int ldc, int M, int N, int K,
+                      const void* aux, int ld_aux, const float* alpha, const float* beta, const float* delta,
+                      float* colsum, void* stream);
 // out[Mw,Nw] (fp32, += with atomics; zero it first) = sum_r g[r,:Mw]^T x[r,:Nw].
 int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,
                    int Mw, int Nw, void* stream);
@@ -67,6 +74,13 @@ int rdp_bn_relu_bwd(const void* dy, const void* z, void* dpre, int B, int N, int
                     const float* mean, const float* rstd, const float* a, float* dgamma, float* dbeta,
                     float* dbias, int has_bn, void* stream);
 int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, int N, int K, void* stream);
+// BatchNorm backward without a pass over the batch: from the raw weight gradient dw[N,K] (= dpre^T r) and
+// bias gradient db[N] of Linear l and its bf16 transposed weight w_t[K,N], derive for BN l-1 (count rows):
+// dgamma, dbeta and the per-column constants alpha/beta/delta of rdp_gemm_tn_bnbwd; dw is rewritten in
+// place into the gradient of the unfolded weight (a[j] * dw[i,j] + c[j] * db[i], as rdp_grad_fixup does).
+int rdp_bn_bwd_coef(float* dw, int ldw, const float* db, const void* w_t, int ldt, int N, int K, const float* a,
+                    const float* c, const float* mean, const float* rstd, float count, float* dgamma,
+                    float* dbeta, float* alpha, float* beta, float* delta, void* stream);
 
 // ---- K8: last Linear + loss + dloss + metric sums (ATen losses, torchmetrics, loss.item()) --
 // loss_kind: 0 MSE, 1 SmoothL1(beta=1), 2 BCEWithLogits.  accum[8] += {loss, |err|, err^2, n,
@@ -150,6 +164,19 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
                   const float* const* ins, float* const* outs, uint32_t* const* epochs,
                   uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,
                   int algo, void* stream);
+
+// One-round ("LL") all-reduce for latency-bound sizes: every rank pushes {value, epoch} packets into slot `rank`
+// of every peer's receive area and then only polls its own memory -- no signal round.  Region per rank:
+// 2 (parity) x 8 (source slots) x 2 * slot_floats floats, zero-initialised.  Same argument conventions as
+// rdp_allreduce; sums in rank order (bit-identical replicas); optimizer epilogue optional.
+int rdp_allreduce_ll(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
+                     const float* const* ins, float* const* outs, uint32_t* const* epochs,
+                     uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,
+                     void* stream);
+// Bounded peer waits for every kernel above and below: after `seconds` (0 = wait forever, the default) a spin
+// on a peer's flag gives up, writes a non-zero code into *host_status (page-locked host memory; may be NULL)
+// and all later waits of the process return at once, so the kernels terminate and the host can raise.
+int rdp_comm_set_timeout(double seconds, uint32_t* host_status);
 
 // ---- K3: NVLS all-reduce (multimem.ld_reduce + multimem.st through the NVSwitch) ------------------
 // mc_ptr: multicast mapping of all ranks' buffers; local_ptr: this rank's unicast mapping;

@@ -26,7 +26,64 @@ from raydp_b200 import ops
 from raydp_b200.ops._abi import OptArgs
 
 FLAG_BYTES = 256
-ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2, "two_shot_fixed": 3}
+ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2, "two_shot_fixed": 3, "ll": 4}
+LL_MAX_BYTES = 1 << 20          # "auto" uses the one-round LL protocol up to this message size
+LL_SOURCE_SLOTS = 8             # receive slots per parity in the LL layout (= kMaxRanks of the kernels)
+
+
+class CommTimeoutError(RuntimeError):
+    """A wait on a peer's flag ran past the deadline: a rank died or never entered the collective."""
+
+
+_status_host: Optional[torch.Tensor] = None
+_status_devices = set()
+_sym_counter = 0
+
+
+def enable_timeouts(seconds: Optional[float] = None) -> None:
+    """Arm the bounded peer waits of every communication kernel on the current device (idempotent).
+    ``RAYDP_B200_COMM_TIMEOUT_S`` (default 60; 0 = wait forever) sets the deadline."""
+    import os
+    global _status_host
+    dev = torch.cuda.current_device()
+    if dev in _status_devices and seconds is None:
+        return
+    if seconds is None:
+        seconds = float(os.environ.get("RAYDP_B200_COMM_TIMEOUT_S", "60"))
+    if _status_host is None:
+        _status_host = torch.zeros(16, dtype=torch.int32).pin_memory()
+    ops._check(ops.lib().rdp_comm_set_timeout(ctypes.c_double(seconds), ctypes.c_void_p(_status_host.data_ptr())))
+    _status_devices.add(dev)
+
+
+def comm_failed() -> int:
+    return int(_status_host[0]) if _status_host is not None else 0
+
+
+def check_status() -> None:
+    """Raise if a communication kernel of this process gave up waiting for a peer (call after a stream
+    synchronisation; the training engines do so once per epoch and at close)."""
+    code = comm_failed()
+    if code:
+        raise CommTimeoutError(f"a wait on a peer GPU timed out (code 0x{code:x}): a rank of the group died or "
+                               "did not reach the collective")
+
+
+def _host_barrier(tag: str, world: int, timeout_s: float = 15.0) -> bool:
+    """Rendezvous through the process group's key-value store, on the host, with a deadline: used in
+    teardown, where a collective barrier would hang forever on a peer that is already gone."""
+    import time
+    try:
+        store = dist.distributed_c10d._get_default_store()
+        store.add(tag, 1)
+        t0 = time.time()
+        while int(store.add(tag, 0)) < world:
+            if time.time() - t0 > timeout_s:
+                return False
+            time.sleep(0.005)
+        return True
+    except Exception:  # noqa: BLE001 - store gone: the group is being torn down
+        return False
 
 
 class _RawCudaBuffer:
@@ -65,7 +122,11 @@ class SymmetricMemory:
     """One region per rank, mapped by all ranks.  ``bases[q]`` is rank q's region in this process."""
 
     def __init__(self, nbytes: int, group=None):
+        global _sym_counter
         self.lib = ops.lib()
+        enable_timeouts()
+        _sym_counter += 1                          # same creation order on every rank: names the teardown key
+        self._tag = f"rdp_sym_close_{_sym_counter}"
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.nbytes = int(nbytes)
@@ -93,10 +154,10 @@ class SymmetricMemory:
         if self.local is None:
             return
         torch.cuda.synchronize()
-        try:
-            dist.barrier()
-        except Exception:  # noqa: BLE001
-            pass
+        # nobody may still be reading this region when it is freed -- but a peer that died will never answer:
+        # rendezvous on the host with a deadline instead of a collective barrier
+        if not comm_failed():
+            _host_barrier(self._tag, self.world)
         for ptr in self._opened:
             self.lib.rdp_comm_ipc_close(ctypes.c_void_p(ptr))
         self.lib.rdp_comm_free(ctypes.c_void_p(self.local))
@@ -126,6 +187,19 @@ def _launch(lib, bases: Sequence[int], slot_floats: int, rank: int, world: int, 
                                  vp(torch.cuda.current_stream().cuda_stream)))
 
 
+def _launch_ll(lib, bases: Sequence[int], slot_floats: int, rank: int, world: int, ins, outs, epochs, counters,
+               opts: Optional[Sequence[OptArgs]], n: int, scale: float) -> None:
+    nl = len(ins)
+    vp = ctypes.c_void_p
+    arr = lambda xs: (vp * len(xs))(*[vp(x) for x in xs])  # noqa: E731
+    opt_arr = (OptArgs * nl)(*opts) if opts is not None else None
+    ops._check(lib.rdp_allreduce_ll(arr(bases), slot_floats, rank, world, nl,
+                                    arr([t.data_ptr() for t in ins]),
+                                    arr([t.data_ptr() if t is not None else 0 for t in outs]),
+                                    arr([t.data_ptr() for t in epochs]), arr([t.data_ptr() for t in counters]),
+                                    opt_arr, n, scale, vp(torch.cuda.current_stream().cuda_stream)))
+
+
 class P2PReducer:
     """Gradient all-reduce for one flat fp32 buffer."""
 
@@ -138,8 +212,15 @@ class P2PReducer:
         self.n = grads.numel() if grads is not None else int(n)
         assert self.n % 4 == 0, "flat buffer must be 16-byte granular"
         self.slot = (self.n + 3) // 4 * 4
+        if algo == "auto" and grads is not None and self.n * 4 <= LL_MAX_BYTES:
+            algo = "ll"                            # latency-bound: one round, flag carried with the data
         self.algo = ALGO[algo]
-        self.sym = SymmetricMemory(4 * self.slot * 4 + FLAG_BYTES, group)
+        self.ll = self.algo == ALGO["ll"]
+        if self.ll:
+            assert grads is not None, "the LL protocol reduces a caller-owned buffer"
+            self.sym = SymmetricMemory(2 * LL_SOURCE_SLOTS * 2 * self.slot * 4, group)
+        else:
+            self.sym = SymmetricMemory(4 * self.slot * 4 + FLAG_BYTES, group)
         if grads is None:
             grads = tensor_from_ptr(self.sym.local, (self.n,), torch.float32, device)
             self.recv0 = tensor_from_ptr(self.sym.local + 2 * self.slot * 4, (self.n,), torch.float32, device)
@@ -154,6 +235,10 @@ class P2PReducer:
     def allreduce_(self, scale: float = 1.0) -> None:
         """In-place sum (times ``scale``) of ``grads`` over all ranks."""
         self._calls += 1
+        if self.ll:
+            _launch_ll(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
+                       [self.epoch], [self.counters], None, self.n, scale)
+            return
         _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
                 [self.epoch], [self.counters], None, self.n, scale, self.algo)
 
@@ -161,6 +246,10 @@ class P2PReducer:
         """All-reduce fused with the optimizer update: parameters are updated in the same kernel
         that pulls the peers' gradients; ``grads`` receives the reduced gradient."""
         self._calls += 1
+        if self.ll:
+            _launch_ll(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [self.grads],
+                       [self.epoch], [self.counters], [opt], self.n, scale)
+            return
         out = None if self.algo == ALGO["two_shot_fixed"] else self.grads
         _launch(self.sym.lib, self.sym.bases, self.slot, self.rank, self.world, [self.grads], [out],
                 [self.epoch], [self.counters], [opt], self.n, scale, self.algo)
@@ -198,11 +287,20 @@ class LocalEmulation:
         self.lib = ops.lib()
         words = 4 * self.slot + FLAG_BYTES // 4
         self.regions = [torch.zeros(words, dtype=torch.float32, device=device) for _ in range(world)]
+        self.ll_regions = None
         self.epochs = [torch.zeros(1, dtype=torch.int32, device=device) for _ in range(world)]
         self.counters = [torch.zeros(4, dtype=torch.int32, device=device) for _ in range(world)]
 
     def allreduce(self, ins: Sequence[torch.Tensor], outs: Sequence[torch.Tensor], scale: float = 1.0,
                   algo: str = "auto", opts: Optional[Sequence[OptArgs]] = None) -> None:
+        if algo == "ll":
+            if self.ll_regions is None:
+                words = 2 * LL_SOURCE_SLOTS * 2 * self.slot
+                self.ll_regions = [torch.zeros(words, dtype=torch.float32, device=ins[0].device)
+                                   for _ in range(self.world)]
+            _launch_ll(self.lib, [r.data_ptr() for r in self.ll_regions], self.slot, 0, self.world, list(ins),
+                       list(outs), self.epochs, self.counters, opts, self.n, scale)
+            return
         _launch(self.lib, [r.data_ptr() for r in self.regions], self.slot, 0, self.world, list(ins), list(outs),
                 self.epochs, self.counters, opts, self.n, scale, ALGO[algo])
 

@@ -147,6 +147,28 @@ def bn_relu_bwd(dy, z, dpre, stats2, mean, rstd, a, dgamma, dbeta, dbias, has_bn
                                  1 if has_bn else 0, _stream()))
 
 
+def gemm_tn_bnbwd(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, aux: torch.Tensor, alpha: torch.Tensor,
+                  beta: torch.Tensor, delta: torch.Tensor, colsum: torch.Tensor) -> torch.Tensor:
+    """dgrad fused with the BN + ReLU backward of the layer it feeds: ``out = (aux > 0) ? alpha * (a @ b.T) +
+    beta * aux + delta : 0`` and ``colsum += out.sum(0)``."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and aux.dtype == torch.bfloat16
+    M, K = a.shape
+    N = b.shape[0]
+    _check(lib().rdp_gemm_tn_bnbwd(_ptr(a), _pitch(a), _ptr(b), _pitch(b), _ptr(out), _pitch(out), M, N, K,
+                                   _ptr(aux), _pitch(aux), _ptr(alpha), _ptr(beta), _ptr(delta), _ptr(colsum),
+                                   _stream()))
+    return out
+
+
+def bn_bwd_coef(dw, db, w_t, a, c, mean, rstd, count, dgamma, dbeta, alpha, beta, delta) -> None:
+    """BN backward statistics of layer l-1 from Linear l's raw weight / bias gradients (no batch pass); ``dw`` is
+    rewritten into the gradient of the unfolded weight."""
+    N, K = dw.shape
+    _check(lib().rdp_bn_bwd_coef(_ptr(dw), _pitch(dw), _ptr(db), _ptr(w_t), _pitch(w_t), N, K, _ptr(a), _ptr(c),
+                                 _ptr(mean), _ptr(rstd), float(count), _ptr(dgamma), _ptr(dbeta), _ptr(alpha),
+                                 _ptr(beta), _ptr(delta), _stream()))
+
+
 def grad_fixup(dw, db, a, c) -> None:
     N, K = dw.shape
     _check(lib().rdp_grad_fixup(_ptr(dw), _ptr(db), _ptr(a), _ptr(c), N, K, _stream()))

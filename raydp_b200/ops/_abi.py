@@ -23,6 +23,8 @@ SIGNATURES = {
     "rdp_gemm2_nn": (I, [VP, I, VP, I, VP, I, I, I, I, I, VP]),
     "rdp_add_scalar": (I, [VP, F, VP]),
     "rdp_publish_host": (I, [VP, VP, I, VP]),
+    "rdp_gemm_tn_bnbwd": (I, [VP, I, VP, I, VP, I, I, I, I, VP, I, VP, VP, VP, VP, VP]),
+    "rdp_bn_bwd_coef": (I, [VP, I, VP, VP, I, I, I, VP, VP, VP, VP, F, VP, VP, VP, VP, VP, VP]),
     "rdp_memcpy_h2d_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_memcpy_d2h_async": (I, [VP, VP, C.c_uint64, VP]),
     "rdp_ingest_pack": (I, [VP, VP, I, I64, I64, VP, I, I, VP, VP, VP, I, VP, VP]),
@@ -50,6 +52,9 @@ SIGNATURES.update({
 })
 
 SIGNATURES.update({
+    "rdp_allreduce_ll": (I, [C.POINTER(VP), C.c_uint64, I, I, I, C.POINTER(VP), C.POINTER(VP), C.POINTER(VP),
+                             C.POINTER(VP), C.POINTER(OptArgs), I64, F, VP]),
+    "rdp_comm_set_timeout": (I, [C.c_double, VP]),
     "rdp_comm_barrier": (I, [C.POINTER(VP), C.c_uint64, I, I, VP, VP]),
     "rdp_alltoall": (I, [VP, C.POINTER(VP), C.POINTER(VP), I, I, I64, VP, VP, VP]),
     "rdp_allreduce_nvls": (I, [VP, VP, C.POINTER(VP), I, I, VP, VP, C.POINTER(OptArgs), VP, I64, F, I, VP]),

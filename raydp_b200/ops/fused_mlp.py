@@ -11,8 +11,10 @@ One training step is ~25 kernel launches and no host synchronisation:
   stores bf16 and accumulates the batch statistics; BatchNorm is folded into the next layer's
   weights by a tiny kernel (``rdp_bn_fold``), so normalised activations are never written;
 * head: the last Linear, the loss, its gradient and the metric sums in one pass (``rdp_mlp_head``);
-* backward: per layer one elementwise BN+ReLU backward, one MN-major split-K tcgen05 wgrad and
-  one tcgen05 dgrad whose epilogue emits the sums the next BN backward needs;
+* backward: per layer one MN-major split-K tcgen05 wgrad and one tcgen05 dgrad whose epilogue applies
+  the BatchNorm + ReLU backward of the layer it feeds -- the batch sums BN backward needs are derived from
+  the weight gradient by an O(N K) kernel (``rdp_bn_bwd_coef``), so no elementwise pass over the
+  ``[B, width]`` gradients remains (only the narrow last hidden layer keeps one);
 * update: Adam / SGD over ONE flat fp32 parameter buffer (or the fused all-reduce + optimizer
   kernel of :mod:`raydp_b200.parallel` when world_size > 1).
 
@@ -69,7 +71,11 @@ class FusedMLP:
         self.device = device
         self.loss_kind = ops.LOSS_KINDS[loss]
         self.max_batch = int(max_batch)
-        self.kpad = _round_up(max(spec.in_features, 8), 8)     # TMA needs 16-byte row pitch
+        # Input rows are padded to a multiple of 32 bf16 = 64 bytes: TMA needs a 16-byte pitch, but a 48-byte
+        # pitch (20 features -> 24) made every operand box a bundle of misaligned, mostly out-of-bounds row
+        # fetches and the first-layer GEMM ran at half speed (48 us vs 23 us for [131072, 24|32] x [256, .],
+        # profiles/gemm_tile_timeline.md)
+        self.kpad = _round_up(max(spec.in_features, 8), 32)
         dims = [spec.in_features] + list(spec.hidden)
         self.dims = dims
         L = len(spec.hidden)
@@ -133,6 +139,12 @@ class FusedMLP:
         self.pred = torch.empty(B, **f32)
         self.accum = torch.zeros(8, **f32)
         self._ones = [torch.ones(h, **f32) for h in spec.hidden]
+        # per-column constants of the BN+ReLU backward fused into the dgrad epilogue (ops.bn_bwd_coef)
+        self.bwd_alpha = [torch.zeros(h, **f32) for h in spec.hidden]
+        self.bwd_beta = [torch.zeros(h, **f32) for h in spec.hidden]
+        self.bwd_delta = [torch.zeros(h, **f32) for h in spec.hidden]
+        import os
+        self.fuse_bn_bwd = os.environ.get("RAYDP_B200_FUSE_BN_BWD", "1") != "0"
 
     # ------------------------------------------------------------------ parameter views
     def view(self, name: str, grad: bool = False) -> torch.Tensor:
@@ -230,14 +242,30 @@ class FusedMLP:
         ops.mlp_head(zs[-1], self.bn_a[L - 1] if bn else None, self.bn_c[L - 1] if bn else None,
                      self.view("Wh"), self.view("bh"), target, self.loss_kind, 1.0 / B, self.pred[:B],
                      self.accum, dz[L - 1], self.stats2[L - 1], self.view("Wh", True), self.view("bh", True))
+        # Backward.  dz[l] arrives either as dL/dy_l (gradient w.r.t. the BN output: from the head, or from a
+        # plain dgrad) and is turned into dL/dpre_l by the elementwise BN+ReLU backward -- or, for layers the
+        # fused path covers, ALREADY as dL/dpre_l: the dgrad GEMM of the layer above applied BN+ReLU backward in
+        # its epilogue, with batch statistics derived from that layer's weight gradient (ops.bn_bwd_coef).
+        pre_ready = False
         for l in range(L - 1, -1, -1):
-            # dz[l] holds dL/dy_l (grad w.r.t. the BN output); turn it into dL/dpre_l in place
-            ops.bn_relu_bwd(dz[l], zs[l], dz[l], self.stats2[l], self.bn_mean[l], self.bn_rstd[l],
-                            self.bn_a[l], self.view(f"g{l}", True) if bn else self.bn_a[l],
-                            self.view(f"be{l}", True) if bn else self.bn_c[l], self.view(f"b{l}", True), bn)
+            if not pre_ready:
+                ops.bn_relu_bwd(dz[l], zs[l], dz[l], self.stats2[l], self.bn_mean[l], self.bn_rstd[l],
+                                self.bn_a[l], self.view(f"g{l}", True) if bn else self.bn_a[l],
+                                self.view(f"be{l}", True) if bn else self.bn_c[l], self.view(f"b{l}", True), bn)
             inp = zs[l - 1] if l > 0 else x
             ops.gemm_wgrad(dz[l], inp, self.view(f"W{l}", True), nw=self.dims[l])
+            pre_ready = False
             if l > 0:
+                width = self.dims[l]
+                if bn and self.fuse_bn_bwd and width % 64 == 0 and width <= 256:
+                    ops.bn_bwd_coef(self.view(f"W{l}", True), self.view(f"b{l}", True), self.w_t[l],
+                                    self.bn_a[l - 1], self.bn_c[l - 1], self.bn_mean[l - 1], self.bn_rstd[l - 1], B,
+                                    self.view(f"g{l - 1}", True), self.view(f"be{l - 1}", True),
+                                    self.bwd_alpha[l - 1], self.bwd_beta[l - 1], self.bwd_delta[l - 1])
+                    ops.gemm_tn_bnbwd(dz[l], self.w_t[l], dz[l - 1], zs[l - 1], self.bwd_alpha[l - 1],
+                                      self.bwd_beta[l - 1], self.bwd_delta[l - 1], self.view(f"b{l - 1}", True))
+                    pre_ready = True
+                    continue
                 if bn:
                     ops.grad_fixup(self.view(f"W{l}", True), self.view(f"b{l}", True), self.bn_a[l - 1],
                                    self.bn_c[l - 1])

@@ -295,6 +295,9 @@ class FusedEngine:
             samples += x.shape[0]
         end.record()
         torch.cuda.current_stream().synchronize()
+        if self.world > 1:
+            from raydp_b200.comm import check_status
+            check_status()          # a peer wait that timed out surfaces here -> FailureConfig restarts the group
         dt = time.perf_counter() - t0
         acc = self._accum_host.tolist()
         res, loss = self._results(acc, steps)
@@ -399,6 +402,9 @@ class DLRMEngine:
             samples += dense.shape[0]
         end.record()
         torch.cuda.current_stream().synchronize()
+        if self.sess.world_size > 1:
+            from raydp_b200.comm import check_status
+            check_status()
         res, loss = self._results(self._accum_host.tolist(), steps)
         timing = {"time_this_iter_s": time.perf_counter() - t0, "device_time_s": start.elapsed_time(end) / 1e3,
                   "samples_this_iter": samples, "steps_this_iter": steps, "engine": self.name,

@@ -151,6 +151,9 @@ class GenericGpuEngine:
             samples += target.shape[0]
         end.record()
         torch.cuda.current_stream().synchronize()
+        if self.world > 1:
+            from raydp_b200.comm import check_status
+            check_status()
         dt = time.perf_counter() - t0
         total = float(self._loss_sum.item())          # the ONE device->host read of the epoch
         result = self.metrics.compute()

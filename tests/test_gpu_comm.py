@@ -16,7 +16,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("algo,n", [("one_shot", 48516), ("two_shot", 48516), ("two_shot", 3 * 1024 * 1024 + 8)])
+@pytest.mark.parametrize("algo,n", [("one_shot", 48516), ("two_shot", 48516), ("two_shot", 3 * 1024 * 1024 + 8),
+                                    ("ll", 48516), ("ll", 262144)])
 def test_emulated_allreduce_matches_sum(world, algo, n):
     from raydp_b200.comm import LocalEmulation
     dev = torch.device("cuda")
@@ -48,7 +49,7 @@ def test_flag_protocol_stress_on_one_gpu():
         n = sizes[it % 3]
         for t in ins[n]:
             t.add_(1.0)                              # new data every call, enqueued on the same stream
-        emu[n].allreduce(ins[n], outs[n], scale=1.0, algo="one_shot" if it % 2 else "two_shot")
+        emu[n].allreduce(ins[n], outs[n], scale=1.0, algo=("one_shot", "two_shot", "ll", "ll")[it % 4])
         if it % 50 == 49:
             ref = torch.stack(ins[n]).sum(0)
             for o in outs[n]:
@@ -56,7 +57,8 @@ def test_flag_protocol_stress_on_one_gpu():
     torch.cuda.synchronize()
 
 
-def test_emulated_allreduce_fused_adam_matches_torch():
+@pytest.mark.parametrize("algo", ["one_shot", "ll"])
+def test_emulated_allreduce_fused_adam_matches_torch(algo):
     from raydp_b200.comm import LocalEmulation, make_opt_args
     dev = torch.device("cuda")
     world, n = 4, 48516
@@ -76,11 +78,49 @@ def test_emulated_allreduce_fused_adam_matches_torch():
         opt.step()
         step_dev.fill_(float(step))
         opts = [make_opt_args(1, params[r], ms[r], vs[r], lr_dev=lr_dev, step_dev=step_dev) for r in range(world)]
-        emu.allreduce(grads, grads, scale=1.0 / world, algo="one_shot", opts=opts)
+        emu.allreduce(grads, grads, scale=1.0 / world, algo=algo, opts=opts)
         torch.cuda.synchronize()
     for r in range(world):
         assert torch.allclose(params[r], p_ref.detach(), rtol=1e-5, atol=1e-6)
         assert torch.equal(params[r], params[0])          # replicas stay bit-identical
+
+
+@pytest.mark.parametrize("algo", ["one_shot", "ll"])
+def test_wait_on_a_missing_peer_times_out_instead_of_hanging(algo):
+    """Bounded peer waits: a 2-rank all-reduce whose "peer" never shows up (its region is plain local memory
+    nobody writes) must end by itself after the deadline, leave a code in the host status word, make later
+    waits return at once, and surface as CommTimeoutError on the host."""
+    import ctypes
+    import time
+    from raydp_b200 import comm, ops
+    dev = torch.device("cuda", 0)
+    n = 4096
+    comm.enable_timeouts(seconds=0.3)
+    try:
+        words = 2 * comm.LL_SOURCE_SLOTS * 2 * n if algo == "ll" else 4 * n + 64
+        mine, ghost = torch.zeros(words, device=dev), torch.zeros(words, device=dev)
+        x = torch.ones(n, device=dev)
+        epoch = torch.zeros(1, dtype=torch.int32, device=dev)
+        counters = torch.zeros(4, dtype=torch.int32, device=dev)
+        t0 = time.time()
+        launch = comm._launch_ll if algo == "ll" else comm._launch
+        extra = () if algo == "ll" else (comm.ALGO["one_shot"],)
+        launch(ops.lib(), [mine.data_ptr(), ghost.data_ptr()], n, 0, 2, [x], [x], [epoch], [counters], None, n, 1.0,
+               *extra)
+        torch.cuda.synchronize()
+        assert 0.25 < time.time() - t0 < 10.0
+        assert comm.comm_failed() != 0
+        with pytest.raises(comm.CommTimeoutError):
+            comm.check_status()
+        t0 = time.time()                              # after a failure nothing waits any more
+        launch(ops.lib(), [mine.data_ptr(), ghost.data_ptr()], n, 0, 2, [x], [x], [epoch], [counters], None, n, 1.0,
+               *extra)
+        torch.cuda.synchronize()
+        assert time.time() - t0 < 0.25
+    finally:
+        comm._status_host.zero_()
+        comm.enable_timeouts(seconds=60.0)            # re-arms and clears the device-side failure flag
+    assert comm.comm_failed() == 0
 
 
 @pytest.mark.multigpu

@@ -24,7 +24,9 @@ def _rel(a, b):
 
 @pytest.mark.parametrize("loss_name,crit", [("smooth_l1", nn.SmoothL1Loss()), ("mse", nn.MSELoss())])
 def test_forward_backward_matches_autograd(loss_name, crit):
-    model, fused, x, y = _setup(loss=loss_name)
+    # B = 16384: bias / beta gradients in front of a BatchNorm are near-cancelling sums whose relative error
+    # against an fp32 model falls with 1/sqrt(B) (bf16 activations); the flagship batch is 8x larger still
+    model, fused, x, y = _setup(B=16384, loss=loss_name)
     xb = fused.pack_input(x)
     fused.train_step(xb, y)
     # the reference sees the same bf16-rounded inputs
@@ -45,8 +47,7 @@ def test_forward_backward_matches_autograd(loss_name, crit):
         worst[f"be{l}"] = _rel(fused.view(f"be{l}", True), sd[f"bn{l + 1}.bias"].grad)
     worst["Wh"] = _rel(fused.view("Wh", True).reshape(-1), sd["fc5.weight"].grad.reshape(-1))
     worst["bh"] = _rel(fused.view("bh", True), sd["fc5.bias"].grad)
-    # bias / beta gradients in front of a BatchNorm are near-cancelling sums: looser bound
-    bad = {k: v for k, v in worst.items() if not v < (6e-2 if k.startswith(("W", "g")) else 0.15)}
+    bad = {k: v for k, v in worst.items() if not v < 5e-2}
     assert not bad, worst
     for l in range(4):
         bn = getattr(model, f"bn{l + 1}")
@@ -200,3 +201,44 @@ def test_cast_weight_plain_and_transposed():
         only = torch.zeros(N, K, dtype=torch.bfloat16, device="cuda")
         ops.cast_weight(w, only)
         assert torch.equal(only, w.to(torch.bfloat16))
+
+
+def test_bn_backward_without_a_batch_pass_matches_fp32():
+    """rdp_bn_bwd_coef + rdp_gemm_tn_bnbwd against the textbook BN+ReLU backward in fp32 PyTorch: the batch sums
+    come from the weight gradient (sum_b dy = db . W, sum_b dy*r = sum_i W * G), never from a pass over dy."""
+    from raydp_b200 import ops
+    torch.manual_seed(3)
+    B, K, N = 3000, 128, 64            # layer l: K inputs (width of layer l-1), N outputs; B not a tile multiple
+    dev = "cuda"
+    r = torch.relu(torch.randn(B, K, device=dev)).to(torch.bfloat16)                 # ReLU output of layer l-1
+    dpre = (0.1 * torch.randn(B, N, device=dev)).to(torch.bfloat16)                  # dL/dpre of layer l
+    W = (torch.randn(N, K, device=dev) / K ** 0.5)
+    w_t = W.t().contiguous().to(torch.bfloat16)                                      # [K, N] dgrad operand
+    gamma = 1 + 0.1 * torch.randn(K, device=dev)
+    bn_bias = 0.1 * torch.randn(K, device=dev)
+    rf = r.float()
+    mean, var = rf.mean(0), rf.var(0, unbiased=False)
+    rstd = (var + 1e-5).rsqrt()
+    a, c = gamma * rstd, bn_bias - gamma * rstd * mean
+    # reference: dy = dpre @ W(bf16), textbook BN backward, ReLU mask
+    dy = dpre.float() @ w_t.float().t()
+    zhat = (rf - mean) * rstd
+    s1, s2 = dy.sum(0), (dy * zhat).sum(0)
+    dr = gamma * rstd * (dy - s1 / B - zhat * s2 / B)
+    want = torch.where(rf > 0, dr, torch.zeros_like(dr))
+    G = dpre.float().t() @ rf                                                        # raw wgrad of layer l
+    db = dpre.float().sum(0)
+    dw = G.clone()
+    dgamma, dbeta = torch.zeros(K, device=dev), torch.zeros(K, device=dev)
+    al, be, de = torch.zeros(K, device=dev), torch.zeros(K, device=dev), torch.zeros(K, device=dev)
+    ops.bn_bwd_coef(dw, db, w_t, a, c, mean, rstd, B, dgamma, dbeta, al, be, de)
+    assert _rel(dbeta, s1) < 1e-4 and _rel(dgamma, s2) < 1e-3
+    assert _rel(dw, a[None, :] * G + c[None, :] * db[:, None]) < 1e-5
+    out = torch.empty(B, K, dtype=torch.bfloat16, device=dev)
+    colsum = torch.zeros(K, device=dev)
+    ops.gemm_tn_bnbwd(dpre, w_t, out, r, al, be, de, colsum)
+    torch.cuda.synchronize()
+    assert _rel(out.float(), want) < 1e-2
+    assert torch.equal(out.float() == 0, ~(rf > 0) | (want.to(torch.bfloat16).float() == 0))
+    assert _rel(colsum, out.float().sum(0)) < 1e-4          # tensor-core column sums of the stored tile
+    assert _rel(colsum, want.sum(0)) < 5e-2
