@@ -235,7 +235,11 @@ def run_replica_check(args, rank, world, local, steps=6):
             engine._train_step(pool_x[i % 2], pool_y[i % 2])
         torch.cuda.synchronize()
         finals[how] = engine.fused.params.detach().clone()
-        kind = engine.reducer.kind if engine.reducer is not None else "none"
+        if getattr(engine, "group_reducers", None):
+            kind = f"p2p per-layer x{len(engine.group_reducers)} (" + \
+                   ("ll" if engine.group_reducers[0].ll else "one/two-shot") + "), overlapped with backward"
+        else:
+            kind = engine.reducer.kind if engine.reducer is not None else "none"
         finals[how + "_kind"] = kind
         engine.close()
         _set_session(None)

@@ -228,9 +228,17 @@ class FusedMLP:
             ops.cast_weight(w, w_folded, w_t)
             b_folded.copy_(b)
 
-    def train_step(self, x: torch.Tensor, target: torch.Tensor) -> None:
+    def group_ranges(self) -> List[Tuple[int, int]]:
+        """``[lo, hi)`` of every layer's parameters in the flat buffers, layer 0 first; the last range also holds
+        the head.  Gradients of range ``l`` are final when ``train_step`` calls ``on_group_ready(l)``."""
+        starts = [self._slices[f"W{l}"][0] for l in range(self.L)]
+        return [(starts[l], starts[l + 1] if l + 1 < self.L else self.n_params) for l in range(self.L)]
+
+    def train_step(self, x: torch.Tensor, target: torch.Tensor, on_group_ready=None) -> None:
         """Forward + backward for one batch; gradients land in ``self.grads`` (sum over the local
-        batch of d(mean loss)); loss / metric sums are added to ``self.accum``."""
+        batch of d(mean loss)); loss / metric sums are added to ``self.accum``.  ``on_group_ready(l)`` is
+        called as soon as every gradient of layer ``l`` (see :meth:`group_ranges`) is final -- last layer
+        first -- so a data-parallel caller can reduce and update that layer while backward goes on."""
         B = x.shape[0]
         assert B <= self.max_batch and x.dtype == torch.bfloat16 and x.shape[1] == self.kpad
         sp = self.spec
@@ -262,6 +270,8 @@ class FusedMLP:
                                     self.bn_a[l - 1], self.bn_c[l - 1], self.bn_mean[l - 1], self.bn_rstd[l - 1], B,
                                     self.view(f"g{l - 1}", True), self.view(f"be{l - 1}", True),
                                     self.bwd_alpha[l - 1], self.bwd_beta[l - 1], self.bwd_delta[l - 1])
+                    if on_group_ready is not None:
+                        on_group_ready(l)
                     ops.gemm_tn_bnbwd(dz[l], self.w_t[l], dz[l - 1], zs[l - 1], self.bwd_alpha[l - 1],
                                       self.bwd_beta[l - 1], self.bwd_delta[l - 1], self.view(f"b{l - 1}", True))
                     pre_ready = True
@@ -269,9 +279,13 @@ class FusedMLP:
                 if bn:
                     ops.grad_fixup(self.view(f"W{l}", True), self.view(f"b{l}", True), self.bn_a[l - 1],
                                    self.bn_c[l - 1])
+                if on_group_ready is not None:
+                    on_group_ready(l)
                 ops.gemm_tn(dz[l], self.w_t[l], dz[l - 1], aux=zs[l - 1],
                             stats_mode=2 if bn else 0, stats=self.stats2[l - 1],
                             aux_relu_mask=False)
+            elif on_group_ready is not None:
+                on_group_ready(0)
         if bn:
             self.num_batches_tracked += 1
 

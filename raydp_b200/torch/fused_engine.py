@@ -161,9 +161,22 @@ class FusedEngine:
         self.use_graph = bool(config.get("extra", {}).get("cuda_graph", True))
         self._accum_host = torch.zeros(8, dtype=torch.float32).pin_memory()
         self.reducer = None
+        self.group_reducers = None
         if self.world > 1:
             from raydp_b200.parallel import make_gradient_reducer
-            self.reducer = make_gradient_reducer(self.fused.grads, self.device, config.get("extra", {}))
+            extra = config.get("extra", {})
+            self.reducer = make_gradient_reducer(self.fused.grads, self.device, extra)
+            ranges = self.fused.group_ranges()
+            if self.reducer.kind == "p2p" and extra.get("overlap_allreduce", True) and len(ranges) > 1 \
+                    and all(lo % 4 == 0 and hi % 4 == 0 for lo, hi in ranges):
+                # one reducer per layer: backward finishes the layers last-first, and each layer's
+                # all-reduce + optimizer runs on a side stream while the earlier layers are still in backward
+                from raydp_b200.comm import P2PReducer
+                self.reducer.close()
+                self.reducer = None
+                self.group_ranges = ranges
+                self.group_reducers = [P2PReducer(self.fused.grads[lo:hi], self.device) for lo, hi in ranges]
+                self.comm_stream = torch.cuda.Stream(device=self.device, priority=-1)
         self.gpu_launches = 0
         self.d2h_bytes = 0
 
@@ -204,7 +217,42 @@ class FusedEngine:
                          g["momentum"], g["dampening"], g["weight_decay"], g["nesterov"], False, scale,
                          self.lr_dev, self.step_dev)
 
+    def _group_opt(self, lo: int, hi: int):
+        from raydp_b200.comm import make_opt_args
+        g = self.optimizer.param_groups[0]
+        p, m, v = self.fused.params[lo:hi], self.m[lo:hi], self.v[lo:hi]
+        if self.opt_kind in ("adam", "adamw"):
+            return make_opt_args(1, p, m, v, betas=g["betas"], eps=g["eps"], weight_decay=g["weight_decay"],
+                                 adamw=self.opt_kind == "adamw", lr_dev=self.lr_dev, step_dev=self.step_dev)
+        return make_opt_args(2, p, m if g["momentum"] else None, None, weight_decay=g["weight_decay"],
+                             momentum=g["momentum"], dampening=g["dampening"], nesterov=g["nesterov"],
+                             lr_dev=self.lr_dev, step_dev=self.step_dev)
+
+    def _step_body_overlapped(self, x, y) -> None:
+        """Data-parallel step with the gradient reduction off the critical path: when the last gradient of a
+        layer is final, its all-reduce + optimizer kernel goes to the communication stream (behind an event)
+        and backward continues; only the first layer's small reduction is left after backward ends."""
+        compute = torch.cuda.current_stream(self.device)
+        comm = self.comm_stream
+        scale = 1.0 / self.world
+        ops.add_scalar(self.step_dev, 1.0)
+
+        def ready(l: int) -> None:
+            ev = torch.cuda.Event()
+            ev.record(compute)
+            comm.wait_event(ev)
+            lo, hi = self.group_ranges[l]
+            with torch.cuda.stream(comm):
+                self.group_reducers[l].allreduce_step_(self._group_opt(lo, hi), scale)
+        self.fused.train_step(x, y, on_group_ready=ready)
+        done = torch.cuda.Event()
+        done.record(comm)
+        compute.wait_event(done)
+        ops.publish_host(self.fused.accum, self._accum_host)
+
     def _step_body(self, x, y) -> None:
+        if self.group_reducers is not None:
+            return self._step_body_overlapped(x, y)
         self.fused.train_step(x, y)
         self._update()
         # the step's result (running loss / metric sums, 32 bytes) goes to pinned host memory from inside
@@ -334,6 +382,8 @@ class FusedEngine:
     def close(self) -> None:
         if self.reducer is not None:
             self.reducer.close()
+        for r in self.group_reducers or []:
+            r.close()
 
 
 class DLRMEngine:
