@@ -477,7 +477,7 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           const uint64_t c_desc = umma_smem_desc(c_addr + k * 2048, kChunkTileBytes, 1024);
           const uint64_t o_desc = umma_smem_desc(o_addr + k * 2048, kChunkTileBytes, 1024);
           umma_bf16(d_sum, ones_desc, c_desc, idesc_s, !(first && k == 0));
-          umma_bf16(d_gram, c_desc, o_desc, idesc_g, !(first && k == 0));
+          if (kStats != 3) umma_bf16(d_gram, c_desc, o_desc, idesc_g, !(first && k == 0));
         }
         umma_commit(&stats_done[sacc]);
         if (kStats == 2) umma_commit(&x_empty[sacc]);
@@ -588,14 +588,18 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           // BN output), aux is r (the ReLU output = BN input); per-column alpha/beta/delta carry the batch
           // statistics of dy, which the caller derived from the layer's weight gradient (no pass over dy)
           const uint32_t* au = reinterpret_cast<const uint32_t*>(ua);
-          const float* al = s_coef + col0;
-          const float* be = s_coef + kBnCoefCols + col0;
-          const float* de = s_coef + 2 * kBnCoefCols + col0;
+          const float4* al4 = reinterpret_cast<const float4*>(s_coef + col0);
+          const float4* be4 = reinterpret_cast<const float4*>(s_coef + kBnCoefCols + col0);
+          const float4* de4 = reinterpret_cast<const float4*>(s_coef + 2 * kBnCoefCols + col0);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const float a0 = __uint_as_float(au[i] << 16), a1 = __uint_as_float(au[i] & 0xffff0000u);
-            v[2 * i] = a0 > 0.f ? fmaf(al[2 * i], v[2 * i], fmaf(be[2 * i], a0, de[2 * i])) : 0.f;
-            v[2 * i + 1] = a1 > 0.f ? fmaf(al[2 * i + 1], v[2 * i + 1], fmaf(be[2 * i + 1], a1, de[2 * i + 1])) : 0.f;
+          for (int q = 0; q < 8; ++q) {
+            const float4 al = al4[q], be = be4[q], de = de4[q];
+            const float a0 = __uint_as_float(au[2 * q] << 16), a1 = __uint_as_float(au[2 * q] & 0xffff0000u);
+            const float a2 = __uint_as_float(au[2 * q + 1] << 16), a3 = __uint_as_float(au[2 * q + 1] & 0xffff0000u);
+            v[4 * q + 0] = a0 > 0.f ? fmaf(al.x, v[4 * q + 0], fmaf(be.x, a0, de.x)) : 0.f;
+            v[4 * q + 1] = a1 > 0.f ? fmaf(al.y, v[4 * q + 1], fmaf(be.y, a1, de.y)) : 0.f;
+            v[4 * q + 2] = a2 > 0.f ? fmaf(al.z, v[4 * q + 2], fmaf(be.z, a2, de.z)) : 0.f;
+            v[4 * q + 3] = a3 > 0.f ? fmaf(al.w, v[4 * q + 3], fmaf(be.w, a3, de.w)) : 0.f;
           }
         } else if (kAux && mask) {
           const uint32_t* au = reinterpret_cast<const uint32_t*>(ua);
@@ -644,16 +648,16 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         uint32_t ds[32], dg[32];
         const uint32_t lanes = uint32_t(quad * 32) << 16;
         tmem_ld_32x32(tmem_base + lanes + 2 * kFastNTile + uint32_t(quad * 32), ds);
-        tmem_ld_32x32(tmem_base + lanes + 3 * kFastNTile + uint32_t(quad * 32), dg);
+        if (kStats != 3) tmem_ld_32x32(tmem_base + lanes + 3 * kFastNTile + uint32_t(quad * 32), dg);
         tmem_ld_wait();
         float s0 = 0.f, s1 = 0.f;
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          if (lane == j) { s0 = __uint_as_float(ds[j]); s1 = __uint_as_float(dg[j]); }
+          if (lane == j) { s0 = __uint_as_float(ds[j]); s1 = (kStats != 3) ? __uint_as_float(dg[j]) : 0.f; }
         }
         const int col = n0 + quad * 32 + lane;
         atomicAdd(&p.stats[col], s0);
-        if (p.stats1 != nullptr) atomicAdd(&p.stats1[col], s1);
+        if (kStats != 3 && p.stats1 != nullptr) atomicAdd(&p.stats1[col], s1);
       }
     }
   }
@@ -953,7 +957,7 @@ int rdp_gemm_tn_bnbwd(const void* a, int lda, const void* b, int ldb, void* out,
   if (rc) return rc;
   rc = make_tmap_2d_bf16(&fx, aux, M, N, ld_aux, kBlockM, 64);
   if (rc) return rc;
-  return launch_fast<1, true>(ta, fb, fc, fx, f, static_cast<cudaStream_t>(stream));
+  return launch_fast<3, true>(ta, fb, fc, fx, f, static_cast<cudaStream_t>(stream));    // column sums only
 }
 
 int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows,

@@ -529,15 +529,17 @@ struct BnBwdCoefParams {
   float* alpha; float* beta; float* delta;   // [K] out
 };
 
-__global__ void __launch_bounds__(256)
+constexpr int kCoefRows = 32;       // row phases per block: 32 columns x 32 phases = 1024 threads
+
+__global__ void __launch_bounds__(32 * kCoefRows)
 bn_bwd_coef_kernel(const BnBwdCoefParams p) {
-  __shared__ float red[2][8][33];
+  __shared__ float red[2][kCoefRows][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int j = blockIdx.x * 32 + tx;
   float s1 = 0.f, t = 0.f;
   if (j < p.K) {
     const float aj = p.a[j], cj = p.c[j];
-    for (int i = ty; i < p.N; i += 8) {
+    for (int i = ty; i < p.N; i += kCoefRows) {
       const float g = p.dw[size_t(i) * p.ldw + j];
       const float w = __bfloat162float(p.w_t[size_t(j) * p.ldt + i]);
       const float dbi = p.db[i];
@@ -553,7 +555,7 @@ bn_bwd_coef_kernel(const BnBwdCoefParams p) {
     // fixed summation order: the result does not depend on scheduling
     float S1 = 0.f, T = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { S1 += red[0][k][tx]; T += red[1][k][tx]; }
+    for (int k = 0; k < kCoefRows; ++k) { S1 += red[0][k][tx]; T += red[1][k][tx]; }
     const float mu = p.mean[j], rs = p.rstd[j], al = p.a[j];
     const float S2 = rs * (T - mu * S1);                  // sum_b dy * zhat
     p.dbeta[j] = S1;
@@ -713,7 +715,7 @@ int rdp_bn_bwd_coef(float* dw, int ldw, const float* db, const void* w_t, int ld
   RDP_REQUIRE(N > 0 && K > 0 && count > 0.f, "rdp_bn_bwd_coef: bad shape N=%d K=%d", N, K);
   BnBwdCoefParams p{dw, ldw, db, static_cast<const __nv_bfloat16*>(w_t), ldt, N, K, a, c, mean, rstd,
                     1.f / count, dgamma, dbeta, alpha, beta, delta};
-  bn_bwd_coef_kernel<<<(K + 31) / 32, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  bn_bwd_coef_kernel<<<(K + 31) / 32, 32 * kCoefRows, 0, static_cast<cudaStream_t>(stream)>>>(p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -9,8 +9,8 @@ GPU-patched loop).  Here the host only *addresses* data:
    the copy plan of every chunk -- (device offset, host address, bytes) of each value buffer and
    validity bitmap -- is computed ONCE; later epochs replay it;
 2. per chunk of rows ONE native call (``rdp_ingest_stage``) issues all ``cudaMemcpyAsync`` of the chunk
-   on a side stream into a double-buffered device staging area;
-3. the ingest kernel (``rdp_ingest_pack_v2`` / ``rdp_ingest_indices_v2``), also on the side stream,
+   on a copy stream into a double-buffered device staging area, one chunk ahead of the packing;
+3. the ingest kernel (``rdp_ingest_pack_v2`` / ``rdp_ingest_indices_v2``), on a second side stream,
    decodes the mixed-dtype columns -- validity bitmaps included: a null feature becomes ``null_fill``
    (default NaN, which is what the reference's pandas/numpy path produces for a null float; pass
    ``null_fill=0.0`` to train through missing values), vector columns (``fixed_size_list`` /
@@ -141,7 +141,9 @@ class ArrowGpuLoader:
         # between the persistent GEMM kernels of the step that is running
         prio = -1 if os.environ.get("RAYDP_B200_INGEST_PRIO", "1") != "0" else 0
         self.copy_stream = torch.cuda.Stream(device=device, priority=prio) if device.type == "cuda" else None
-        self.pack_on_side = os.environ.get("RAYDP_B200_INGEST_PACK", "side") != "compute"
+        self.pack_stream = torch.cuda.Stream(device=device, priority=prio) if device.type == "cuda" else None
+        self._stage_ready = [torch.cuda.Event(), torch.cuda.Event()] if device.type == "cuda" else [None, None]
+        self._stage_free: List[Optional[torch.cuda.Event]] = [None, None]
         self._cols = self.features + self.sparse + ([self.label] if self.label else [])
         self._chunks: Optional[List[_Chunk]] = None
         self._stage: List[Optional[torch.Tensor]] = [None, None]
@@ -250,19 +252,39 @@ class ArrowGpuLoader:
         return stage_bytes
 
     # ------------------------------------------------------------------ iteration
+    def _stage_chunk(self, ci: int) -> None:
+        """All host->device copies of chunk ``ci`` (copy stream), one chunk ahead of the packing."""
+        ch = self._chunks[ci]
+        slot = ci & 1
+        if self._stage_free[slot] is not None:            # the packs that read this staging slot (chunk ci-2)
+            self.copy_stream.wait_event(self._stage_free[slot])
+        base = self._stage[slot].data_ptr()
+        ops.ingest_stage([base + o for o in ch.dst_off], ch.src, ch.nbytes, self.copy_stream)
+        self._stage_ready[slot].record(self.copy_stream)
+        self.h2d_bytes += ch.bytes_total
+
     def __iter__(self):
+        """Three streams.  The COPY stream only ever waits for a staging slot to be drained, so the DMA of
+        chunk c+1 runs while chunk c is packed and trained on; the PACK stream waits for staged data and for a
+        free output slot; the consumer's stream waits for a packed batch.  (With copies and packs on one
+        stream, the next chunk's DMA sat behind a pack that was waiting for an output slot, i.e. behind a whole
+        training step -- profiles/ingest_timeline.md.)"""
         self._prepare()
         compute = torch.cuda.current_stream(self.device)
-        side = self.copy_stream
+        pack = self.pack_stream
         nf, ns = len(self.features), len(self.sparse)
         out, filled = 0, 0
         if self._free[out] is not None:
-            side.wait_event(self._free[out])
+            pack.wait_event(self._free[out])
+        n_chunks = len(self._chunks)
+        if n_chunks:
+            self._stage_chunk(0)
         for ci, ch in enumerate(self._chunks):
-            base = self._stage[ci & 1].data_ptr()
-            # staging slot reuse needs no event: its readers (the pack kernels) run on this same stream
-            ops.ingest_stage([base + o for o in ch.dst_off], ch.src, ch.nbytes, side)
-            self.h2d_bytes += ch.bytes_total
+            if ci + 1 < n_chunks:
+                self._stage_chunk(ci + 1)
+            slot = ci & 1
+            base = self._stage[slot].data_ptr()
+            pack.wait_event(self._stage_ready[slot])
             cols = ch.cols
             f_ptr = [base + c[0] for c in cols[:nf]]
             f_val = [base + c[1] if c[1] >= 0 else 0 for c in cols[:nf]]
@@ -270,12 +292,6 @@ class ArrowGpuLoader:
             f_w = [c[3] for c in cols[:nf]]
             f_code = [c[4] for c in cols[:nf]]
             lab = cols[nf + ns] if self.label else None
-            pack_stream = side
-            if not self.pack_on_side:            # experiment switch: copies on the side stream, pack on the training stream
-                staged = torch.cuda.Event()
-                staged.record(side)
-                compute.wait_event(staged)
-                pack_stream = compute
             done = 0
             while done < ch.rows:
                 take = min(self.batch - filled, ch.rows - done)
@@ -283,25 +299,28 @@ class ArrowGpuLoader:
                 ops.ingest_pack_v2(f_ptr, f_val, f_vb, f_w, f_code, take, done, x[filled:], self.shift, self.scale,
                                    self.null_fill, base + lab[0] if lab else 0,
                                    base + lab[1] if (lab and lab[1] >= 0) else 0, lab[2] if lab else 0,
-                                   lab[4] if lab else 0, y[filled:] if lab else None, stream=pack_stream)
+                                   lab[4] if lab else 0, y[filled:] if lab else None, stream=pack)
                 if ns:
                     sc = cols[nf:nf + ns]
                     ops.ingest_indices_v2([base + c[0] for c in sc], [base + c[1] if c[1] >= 0 else 0 for c in sc],
                                           [c[2] for c in sc], [c[4] for c in sc], take, done, self.table_rows,
-                                          s[filled:], stream=pack_stream)
+                                          s[filled:], stream=pack)
                 filled += take
                 done += take
+                if done == ch.rows:                       # last reader of this staging slot is enqueued
+                    if self._stage_free[slot] is None:
+                        self._stage_free[slot] = torch.cuda.Event()
+                    self._stage_free[slot].record(pack)
                 if filled == self.batch:
-                    yield self._emit(out, filled, compute, side)
-                    out, filled = self._release(out, compute, side)
+                    yield self._emit(out, filled, compute, pack)
+                    out, filled = self._release(out, compute, pack)
         if filled and not self.drop_last:
-            yield self._emit(out, filled, compute, side)
-            self._release(out, compute, side)
+            yield self._emit(out, filled, compute, pack)
+            self._release(out, compute, pack)
 
-    def _emit(self, slot: int, rows: int, compute, side):
-        if self.pack_on_side:
-            self._ready[slot].record(side)
-            compute.wait_event(self._ready[slot])
+    def _emit(self, slot: int, rows: int, compute, pack):
+        self._ready[slot].record(pack)
+        compute.wait_event(self._ready[slot])
         x, y, s = self._slots[slot]
         xv = x[:rows]
         yv = y[:rows] if y is not None else None
@@ -309,12 +328,12 @@ class ArrowGpuLoader:
             return xv, s[:rows], yv
         return xv, yv
 
-    def _release(self, slot: int, compute, side) -> Tuple[int, int]:
+    def _release(self, slot: int, compute, pack) -> Tuple[int, int]:
         """The consumer's work on ``slot`` has been enqueued: mark it, move to the other slot."""
         if self._free[slot] is None:
             self._free[slot] = torch.cuda.Event()
         self._free[slot].record(compute)
         other = slot ^ 1
         if self._free[other] is not None:
-            side.wait_event(self._free[other])
+            pack.wait_event(self._free[other])
         return other, 0
