@@ -573,9 +573,10 @@ bn_bwd_coef_kernel(const BnBwdCoefParams p) {
 // batches, issued after it, were observed to wait behind it (profiles/ingest_timeline.md): the per-step
 // result read-back was what exposed the input copies.  A kernel store has no place in that queue.
 __global__ void publish_host_kernel(const float* __restrict__ src, volatile float* dst_host, int n) {
+  // posted writes: no system-scope fence here -- waiting for the PCIe acknowledgement under a saturated
+  // host->device stream cost up to 15 us per step; the host only reads after a stream synchronisation
   const int i = threadIdx.x;
   if (i < n) dst_host[i] = src[i];
-  __threadfence_system();
 }
 
 __global__ void add_scalar_kernel(float* x, float v) { *x += v; }
@@ -721,10 +722,10 @@ int rdp_bn_bwd_coef(float* dw, int ldw, const float* db, const void* w_t, int ld
 }
 
 int rdp_publish_host(const float* src, float* host_pinned, int n, void* stream) {
-  RDP_REQUIRE(n > 0 && n <= 256, "rdp_publish_host: n=%d (1..256 floats)", n);
+  RDP_REQUIRE(n > 0 && n <= 32, "rdp_publish_host: n=%d (1..32 floats)", n);
   void* mapped = nullptr;
   RDP_CHECK_CUDA(cudaHostGetDevicePointer(&mapped, host_pinned, 0));
-  publish_host_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(src, static_cast<float*>(mapped), n);
+  publish_host_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(src, static_cast<float*>(mapped), n);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -104,7 +104,7 @@ int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, floa
 // dbias[N] += column sums of the result, one pass over the [M, N] bf16 matrices.
 int rdp_relu_bwd_bias(const void* g, const void* act, void* g_out, float* dbias, int M, int N, int ld, void* stream);
 int rdp_add_scalar(float* x, float v, void* stream);
-// host_pinned[0..n) = src[0..n) by a device store into page-locked host memory (n <= 256): the per-step
+// host_pinned[0..n) = src[0..n) by a device store into page-locked host memory (n <= 32): the per-step
 // result read-back without a device->host memcpy in the copy queue (see profiles/ingest_timeline.md).
 int rdp_publish_host(const float* src, float* host_pinned, int n, void* stream);
 // host (pinned or pageable) -> device async copy on `stream`

@@ -163,6 +163,12 @@ class Head:
                  resources: Optional[Dict[str, float]] = None, namespace: Optional[str] = None,
                  object_store_memory: Optional[int] = None, memory: Optional[int] = None):
         self.session = P.new_id()[:10]
+        _reap_dead_sessions()
+        self._marker = _session_marker(self.session, os.getpid())
+        try:
+            open(self._marker, "w").close()
+        except OSError:
+            self._marker = None
         self.namespace = namespace or f"ns-{self.session}"
         self.job_id = P.new_id()[:8]
         self.dir = tempfile.mkdtemp(prefix=f"raydp_b200_{self.session}_")
@@ -1005,8 +1011,56 @@ class Head:
         for obj in list(self._objects.values()):
             obj.event.set()
         store.delete_prefix(f"rdp_{self.session}_")
+        if self._marker:
+            try:
+                os.unlink(self._marker)
+            except OSError:
+                pass
         self._pool.shutdown(wait=False, cancel_futures=True)
         shutil.rmtree(self.dir, ignore_errors=True)
+
+
+_SHM_DIR = "/dev/shm"
+
+
+def _session_marker(session: str, pid: int) -> str:
+    # not an object of the store (different prefix), so delete_prefix("rdp_<session>_") leaves it alone
+    return os.path.join(_SHM_DIR, f"rdphead_{session}_{pid}")
+
+
+def _reap_dead_sessions() -> int:
+    """Objects are shared-memory segments that outlive their creator.  A driver that is killed (SIGKILL,
+    ``os._exit``, a test timeout) never runs ``shutdown`` and would leave its whole session behind in /dev/shm.
+    Every head leaves a marker carrying its pid; a new head removes the segments of sessions whose head is
+    gone.  Returns the number of segments removed."""
+    removed = 0
+    try:
+        names = os.listdir(_SHM_DIR)
+    except OSError:
+        return 0
+    for name in names:
+        if not name.startswith("rdphead_"):
+            continue
+        try:
+            _, session, pid = name.split("_")
+            pid = int(pid)
+        except ValueError:
+            continue
+        alive = True
+        try:
+            os.kill(pid, 0)
+        except ProcessLookupError:
+            alive = False
+        except PermissionError:
+            alive = True
+        if alive:
+            continue
+        removed += max(0, store.delete_prefix(f"rdp_{session}_"))
+        try:
+            os.unlink(os.path.join(_SHM_DIR, name))
+        except OSError:
+            pass
+    return removed
 
 
 def _fits_take(avail, need) -> bool:

@@ -161,3 +161,44 @@ def test_actor_pool_and_queue(ray_cluster):
     runtime.get(producer.remote(shared))
     assert [shared.get() for _ in range(3)] == [0, 1, 2]
     shared.shutdown()
+
+
+def _shm_segments(prefix="rdp_"):
+    import os
+    return [n for n in os.listdir("/dev/shm") if n.startswith(prefix)]
+
+
+def test_shared_memory_is_clean_after_shutdown_and_after_a_killed_driver(tmp_path):
+    """Objects are POSIX shared-memory segments: ``shutdown`` must remove every one of the session, and a
+    session whose driver was killed (no shutdown ran) must be reaped by the next ``init``."""
+    import subprocess
+    import sys
+    import numpy as np
+    from raydp_b200 import runtime
+    runtime.shutdown()
+    runtime.init(num_cpus=2)
+    session = runtime._head.session
+    refs = [runtime.put(np.arange(200000 + i)) for i in range(5)]
+
+    @runtime.remote
+    def produce(i):
+        return np.full(150000, i)
+    refs += [produce.remote(i) for i in range(4)]
+    assert int(runtime.get(refs)[-1][0]) == 3
+    assert len(_shm_segments(f"rdp_{session}_")) >= 9
+    runtime.shutdown()
+    assert _shm_segments(f"rdp_{session}_") == [] and _shm_segments(f"rdphead_{session}_") == []
+    # a driver that dies without shutting down
+    code = "\n".join(["import os, numpy as np", "from raydp_b200 import runtime", "runtime.init(num_cpus=1)",
+                      "refs = [runtime.put(np.arange(200000)) for _ in range(7)]",
+                      "print(runtime._head.session, flush=True)", "os._exit(3)"])
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root, timeout=120)
+    assert out.returncode == 3, out.stderr[-1000:]
+    dead = out.stdout.strip().splitlines()[-1]
+    assert len(_shm_segments(f"rdp_{dead}_")) == 7           # leaked, as expected
+    runtime.init(num_cpus=1)                                  # the next head reaps them
+    try:
+        assert _shm_segments(f"rdp_{dead}_") == [] and _shm_segments(f"rdphead_{dead}_") == []
+    finally:
+        runtime.shutdown()

@@ -68,6 +68,7 @@ def _run_pair(lib, M, N, K, seed):
     full = torch.relu(a.float() @ b.float().t() + bias)
     assert (out_new.float() - full).abs().max().item() < 0.05
     assert torch.allclose(mean, full.mean(0), rtol=2e-2, atol=2e-2)
+    assert torch.allclose(var, full.var(0, unbiased=False), rtol=3e-2, atol=2e-2)
 
 
 def test_noalloc_matches_existing_entry_point_twice_in_a_row():
