@@ -178,6 +178,27 @@ int rdp_allreduce_ll(void* const* bases, uint64_t slot_floats, int rank, int wor
 // and all later waits of the process return at once, so the kernels terminate and the host can raise.
 int rdp_comm_set_timeout(double seconds, uint32_t* host_status);
 
+// ---- S2: symmetric memory and multicast objects from the driver's virtual-memory API ---------------------
+// (cuMemCreate + POSIX file descriptors + cuMulticast*: no CUDA IPC, no dependency on another library's
+// allocator.)  rdp_symm_supported: 0 = unsupported, 1 = symmetric memory, 2 = symmetric memory + multicast.
+// Sizes must be multiples of rdp_symm_granularity(device, multicast, n_devices).  The fd of
+// rdp_symm_export_fd / rdp_mc_export_fd goes to the peers over a unix socket (SCM_RIGHTS); the receiver
+// imports it, which maps the peer's memory for its own device, and closes the fd.  Multicast: rank 0 creates
+// the object, every rank imports it, calls rdp_mc_add_device, then (after all have) rdp_mc_bind with its
+// own allocation and rdp_mc_map.  rdp_symm_free unmaps and releases without any cooperation of peers.
+int rdp_symm_supported(int device);
+int rdp_symm_granularity(int device, int multicast, int n_devices, uint64_t* out);
+int rdp_symm_alloc(uint64_t bytes, int device, void** handle_out, void** ptr_out);
+int rdp_symm_export_fd(void* handle, int* fd_out);
+int rdp_symm_import_fd(int fd, uint64_t bytes, int device, void** handle_out, void** ptr_out);
+int rdp_symm_free(void* handle);
+int rdp_mc_create(uint64_t bytes, int n_devices, void** handle_out);
+int rdp_mc_import_fd(int fd, uint64_t bytes, void** handle_out);
+int rdp_mc_add_device(void* mc, int device);
+int rdp_mc_bind(void* mc, void* symm);
+int rdp_mc_map(void* mc, int device, void** ptr_out);
+int rdp_close_fd(int fd);
+
 // ---- K3: NVLS all-reduce (multimem.ld_reduce + multimem.st through the NVSwitch) ------------------
 // mc_ptr: multicast mapping of all ranks' buffers; local_ptr: this rank's unicast mapping;
 // flag_ptrs[q]: 256 zero-initialised bytes inside rank q's buffer (unicast, peer-mapped).

@@ -118,25 +118,169 @@ def p2p_available() -> bool:
     return bool(flag.item())
 
 
-class SymmetricMemory:
-    """One region per rank, mapped by all ranks.  ``bases[q]`` is rank q's region in this process."""
+def _exchange_fds(offered: List[int], rank: int, world: int, group, tag: str) -> List[List[int]]:
+    """Pass file descriptors between the ranks' processes over unix sockets (``SCM_RIGHTS``).  Every rank
+    serves ``offered`` to each peer and collects what the peers offer; the socket paths travel through the
+    process group.  Returns ``fds[q]`` = descriptors received from rank q (``offered`` itself for q == rank)."""
+    import os
+    import socket
+    import tempfile
+    import threading
+    path = os.path.join(tempfile.gettempdir(), f"rdp_fd_{os.getpid()}_{tag}.sock")
+    if os.path.exists(path):
+        os.unlink(path)
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    srv.bind(path)
+    srv.listen(world)
+    srv.settimeout(60.0)
+    errors: List[BaseException] = []
 
-    def __init__(self, nbytes: int, group=None):
+    def serve() -> None:
+        try:
+            for _ in range(world - 1):
+                conn, _ = srv.accept()
+                with conn:
+                    socket.send_fds(conn, [len(offered).to_bytes(4, "little")], list(offered))
+        except BaseException as exc:  # noqa: BLE001
+            errors.append(exc)
+    thread = threading.Thread(target=serve, name="rdp-fd-serve", daemon=True)
+    thread.start()
+    paths: List[Optional[str]] = [None] * world
+    dist.all_gather_object(paths, path, group=group)
+    out: List[List[int]] = []
+    try:
+        for q in range(world):
+            if q == rank:
+                out.append(list(offered))
+                continue
+            with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+                c.settimeout(60.0)
+                c.connect(paths[q])
+                msg, fds, _flags, _addr = socket.recv_fds(c, 4, 8)
+                if len(fds) != int.from_bytes(msg, "little"):
+                    raise RuntimeError(f"rank {q} announced {int.from_bytes(msg, 'little')} descriptors, got {len(fds)}")
+                out.append(list(fds))
+        thread.join(90.0)
+        if errors:
+            raise RuntimeError(f"descriptor exchange failed: {errors[0]}")
+    finally:
+        srv.close()
+        try:
+            os.unlink(path)
+        except OSError:
+            pass
+    return out
+
+
+def symm_support(device: Optional[int] = None) -> int:
+    """0: only CUDA IPC; 1: driver-API symmetric memory (cuMemCreate + fd exchange); 2: + NVLS multicast."""
+    import os
+    if os.environ.get("RAYDP_B200_SYMM", "vmm") == "ipc":
+        return 0
+    dev = torch.cuda.current_device() if device is None else device
+    return int(ops.lib().rdp_symm_supported(dev))
+
+
+class SymmetricMemory:
+    """One region per rank, mapped by all ranks.  ``bases[q]`` is rank q's region in this process.
+
+    Preferred plumbing: every rank ``cuMemCreate``s its region as an allocation
+    shareable by POSIX file descriptor, the descriptors cross process boundaries over unix sockets, and each
+    rank maps all peers' allocations (``rdp_symm_*`` in ``csrc/comm/symmem.cu``).  With ``multicast=True``
+    rank 0 also creates a multicast object over all devices, every rank binds its region to it and maps it:
+    ``mc_ptr`` is the address ``multimem.ld_reduce`` / ``multimem.st`` operate on (NVLS).  CUDA IPC
+    (``cudaIpcGetMemHandle``) remains as the fallback where the driver lacks the virtual-memory API
+    (``RAYDP_B200_SYMM=ipc`` forces it).  Teardown never needs a peer's cooperation."""
+
+    def __init__(self, nbytes: int, group=None, multicast: bool = False):
         global _sym_counter
         self.lib = ops.lib()
         enable_timeouts()
-        _sym_counter += 1                          # same creation order on every rank: names the teardown key
+        _sym_counter += 1                          # same creation order on every rank: names keys and sockets
         self._tag = f"rdp_sym_close_{_sym_counter}"
+        self._group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
         self.nbytes = int(nbytes)
+        self.mc_ptr = 0
+        self._handles: List[int] = []
+        self._mc_handle = 0
+        self.device = torch.cuda.current_device()
+        support = symm_support(self.device)
+        # all ranks must take the same path
+        flag = torch.tensor([support], device="cuda", dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        support = int(flag.item())
+        if multicast and support < 2:
+            raise RuntimeError("this system exposes no NVLS multicast support")
+        self.mode = "vmm" if support >= 1 else "ipc"
+        if self.mode == "vmm":
+            self._init_vmm(multicast)
+        else:
+            self._init_ipc()
+
+    # ---- driver virtual-memory API + fd exchange ------------------------------------------------
+    def _init_vmm(self, multicast: bool) -> None:
+        lib, vp = self.lib, ctypes.c_void_p
+        gran = ctypes.c_uint64()
+        ops._check(lib.rdp_symm_granularity(self.device, 1 if multicast else 0, self.world, ctypes.byref(gran)))
+        size = (self.nbytes + gran.value - 1) // gran.value * gran.value
+        self.size = size
+        handle, ptr = vp(), vp()
+        ops._check(lib.rdp_symm_alloc(size, self.device, ctypes.byref(handle), ctypes.byref(ptr)))
+        self.local = ptr.value
+        self._own_handle = handle.value
+        fd = ctypes.c_int(-1)
+        ops._check(lib.rdp_symm_export_fd(vp(self._own_handle), ctypes.byref(fd)))
+        offered = [fd.value]
+        if multicast and self.rank == 0:
+            mc = vp()
+            ops._check(lib.rdp_mc_create(size, self.world, ctypes.byref(mc)))
+            self._mc_handle = mc.value
+            mfd = ctypes.c_int(-1)
+            ops._check(lib.rdp_symm_export_fd(vp(self._mc_handle), ctypes.byref(mfd)))
+            offered.append(mfd.value)
+        fds = _exchange_fds(offered, self.rank, self.world, self._group, f"{_sym_counter}")
+        self.bases = []
+        for q in range(self.world):
+            if q == self.rank:
+                self.bases.append(self.local)
+                continue
+            h, p = vp(), vp()
+            ops._check(lib.rdp_symm_import_fd(fds[q][0], size, self.device, ctypes.byref(h), ctypes.byref(p)))
+            self._handles.append(h.value)
+            self.bases.append(p.value)
+        if multicast:
+            if self.rank != 0:
+                mc = vp()
+                ops._check(lib.rdp_mc_import_fd(fds[0][1], size, ctypes.byref(mc)))
+                self._mc_handle = mc.value
+            ops._check(lib.rdp_mc_add_device(vp(self._mc_handle), self.device))
+            if not _host_barrier(self._tag + "_added", self.world, 60.0):
+                raise RuntimeError("multicast set-up: not every rank added its device")
+            ops._check(lib.rdp_mc_bind(vp(self._mc_handle), vp(self._own_handle)))
+            if not _host_barrier(self._tag + "_bound", self.world, 60.0):
+                raise RuntimeError("multicast set-up: not every rank bound its memory")
+            mptr = vp()
+            ops._check(lib.rdp_mc_map(vp(self._mc_handle), self.device, ctypes.byref(mptr)))
+            self.mc_ptr = mptr.value
+        for per_rank in fds:                       # the mappings keep the memory alive; the fds can go
+            for f in per_rank:
+                lib.rdp_close_fd(int(f))
+        torch.cuda.synchronize()
+        if not _host_barrier(self._tag + "_ready", self.world, 60.0):
+            raise RuntimeError("symmetric memory set-up: a rank did not finish mapping")
+
+    # ---- CUDA IPC fallback ------------------------------------------------------------------------
+    def _init_ipc(self) -> None:
         ptr = ctypes.c_void_p()
         ops._check(self.lib.rdp_comm_alloc(self.nbytes, ctypes.byref(ptr)))
         self.local = ptr.value
+        self.size = self.nbytes
         handle = ctypes.create_string_buffer(64)
         ops._check(self.lib.rdp_comm_ipc_handle(ctypes.c_void_p(self.local), handle))
         gathered: List[Optional[bytes]] = [None] * self.world
-        dist.all_gather_object(gathered, bytes(handle.raw), group=group)
+        dist.all_gather_object(gathered, bytes(handle.raw), group=self._group)
         self.bases: List[int] = []
         self._opened: List[int] = []
         for q, blob in enumerate(gathered):
@@ -148,7 +292,7 @@ class SymmetricMemory:
             ops._check(self.lib.rdp_comm_ipc_open(buf, ctypes.byref(out)))
             self.bases.append(out.value)
             self._opened.append(out.value)
-        dist.barrier(group)
+        dist.barrier(self._group)
 
     def close(self) -> None:
         if self.local is None:
@@ -158,9 +302,17 @@ class SymmetricMemory:
         # rendezvous on the host with a deadline instead of a collective barrier
         if not comm_failed():
             _host_barrier(self._tag, self.world)
-        for ptr in self._opened:
-            self.lib.rdp_comm_ipc_close(ctypes.c_void_p(ptr))
-        self.lib.rdp_comm_free(ctypes.c_void_p(self.local))
+        vp = ctypes.c_void_p
+        if self.mode == "vmm":
+            if self._mc_handle:
+                self.lib.rdp_symm_free(vp(self._mc_handle))
+            for h in self._handles:
+                self.lib.rdp_symm_free(vp(h))
+            self.lib.rdp_symm_free(vp(self._own_handle))
+        else:
+            for ptr in self._opened:
+                self.lib.rdp_comm_ipc_close(vp(ptr))
+            self.lib.rdp_comm_free(vp(self.local))
         self.local = None
 
 
@@ -318,24 +470,36 @@ class NvlsReducer:
     kind = "nvls"
 
     def __init__(self, n: int, device: torch.device, group=None):
-        import torch.distributed._symmetric_memory as symm_mem
         assert n % 4 == 0
         self.n = n
         self.lib = ops.lib()
-        group = group or dist.group.WORLD
-        self._t = symm_mem.empty(n + FLAG_BYTES // 4, dtype=torch.float32, device=device)
-        self._t.zero_()
-        self._hdl = symm_mem.rendezvous(self._t, group)
-        self.rank, self.world = self._hdl.rank, self._hdl.world_size
-        self.mc_ptr = int(self._hdl.multicast_ptr or 0)
-        if not self.mc_ptr:
-            raise RuntimeError("this system exposes no NVLS multicast mapping")
-        self.buffer = self._t[:n]
-        self.flag_ptrs = [int(p) + n * 4 for p in self._hdl.buffer_ptrs]
+        self.sym = None
+        nbytes = n * 4 + FLAG_BYTES
+        if symm_support(device.index or 0) >= 2:
+            # own plumbing: cuMemCreate + fd exchange + cuMulticastCreate/AddDevice/BindMem (csrc/comm/symmem.cu)
+            self.sym = SymmetricMemory(nbytes, group, multicast=True)
+            self.rank, self.world = self.sym.rank, self.sym.world
+            self.mc_ptr = int(self.sym.mc_ptr)
+            self.buffer = tensor_from_ptr(self.sym.local, (n,), torch.float32, device)
+            self.flag_ptrs = [int(b) + n * 4 for b in self.sym.bases]
+            self.plumbing = "own (cuMulticast*)"
+        else:
+            import torch.distributed._symmetric_memory as symm_mem
+            group = group or dist.group.WORLD
+            self._t = symm_mem.empty(n + FLAG_BYTES // 4, dtype=torch.float32, device=device)
+            self._t.zero_()
+            self._hdl = symm_mem.rendezvous(self._t, group)
+            self.rank, self.world = self._hdl.rank, self._hdl.world_size
+            self.mc_ptr = int(self._hdl.multicast_ptr or 0)
+            if not self.mc_ptr:
+                raise RuntimeError("this system exposes no NVLS multicast mapping")
+            self.buffer = self._t[:n]
+            self.flag_ptrs = [int(p) + n * 4 for p in self._hdl.buffer_ptrs]
+            self.plumbing = "torch symmetric memory"
+            torch.cuda.synchronize()
+            dist.barrier(group)
         self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
         self.counters = torch.zeros(4, dtype=torch.int32, device=device)
-        torch.cuda.synchronize()
-        dist.barrier(group)
 
     def allreduce_(self, scale: float = 1.0, opt: Optional[OptArgs] = None, out: Optional[torch.Tensor] = None,
                    overlap: bool = False) -> None:
@@ -359,9 +523,14 @@ class NvlsReducer:
 
     def close(self) -> None:
         torch.cuda.synchronize()
+        if self.sym is not None:
+            self.sym.close()
+            self.sym = None
 
 
 def nvls_available(device: torch.device) -> bool:
+    if symm_support(device.index or 0) >= 2:
+        return True
     try:
         from torch._C._autograd import DeviceType
         from torch._C._distributed_c10d import _SymmetricMemory

@@ -67,6 +67,21 @@ SIGNATURES.update({
     "rdp_bce_logits": (I, [VP, I, VP, VP, I, I, VP, I, F, VP, VP]),
 })
 
+SIGNATURES.update({
+    "rdp_symm_supported": (I, [I]),
+    "rdp_symm_granularity": (I, [I, I, I, C.POINTER(C.c_uint64)]),
+    "rdp_symm_alloc": (I, [C.c_uint64, I, C.POINTER(VP), C.POINTER(VP)]),
+    "rdp_symm_export_fd": (I, [VP, C.POINTER(I)]),
+    "rdp_symm_import_fd": (I, [I, C.c_uint64, I, C.POINTER(VP), C.POINTER(VP)]),
+    "rdp_symm_free": (I, [VP]),
+    "rdp_mc_create": (I, [C.c_uint64, I, C.POINTER(VP)]),
+    "rdp_mc_import_fd": (I, [I, C.c_uint64, C.POINTER(VP)]),
+    "rdp_mc_add_device": (I, [VP, I]),
+    "rdp_mc_bind": (I, [VP, VP]),
+    "rdp_mc_map": (I, [VP, I, C.POINTER(VP)]),
+    "rdp_close_fd": (I, [I]),
+})
+
 OPTIONAL = {}
 
 

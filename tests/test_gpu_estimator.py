@@ -126,3 +126,52 @@ def test_dlrm_estimator_single_gpu(ray_cluster):
     evals = [h for h in est.results.metrics_history if "eval_res" in h]
     assert abs(acc - evals[-1]["eval_res"]["Accuracy"]) < 0.02, (acc, evals[-1]["eval_res"])
     assert acc > 0.5
+
+
+@pytest.mark.multigpu
+def test_rank_killed_mid_training_is_detected_and_the_group_restarts(ray_cluster, tmp_path):
+    """Failure path of the peer-memory collectives: rank 1 dies in the middle of an epoch.  Rank 0's next
+    all-reduce must not hang on the dead peer (bounded waits), the trainer must see the failure, tear the group
+    down and -- ``max_retries=1`` -- run the fit again to completion (reference recovery semantics:
+    ``FailureConfig(max_failures=max_retries)``, torch/estimator.py:334)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import time
+    import raydp_b200 as raydp
+    from raydp_b200 import runtime
+    from raydp_b200.torch import TorchEstimator
+    from user_models import NYC_Model
+    os.environ["RAYDP_B200_COMM_TIMEOUT_S"] = "5"
+    runtime.shutdown()
+    runtime.init(num_cpus=6, num_gpus=2)
+    flag = str(tmp_path / "rank1_died")
+    try:
+        spark = raydp.init_spark("gpu-kill", 1, 1, "1GB")
+        df = _frame(spark, 64 * 2048)
+
+        def scheduler_that_kills_rank_1(optimizer, config):
+            from raydp_b200.train import get_context
+
+            class Sched(torch.optim.lr_scheduler.LambdaLR):
+                def step(self, *a, **kw):
+                    super().step(*a, **kw)
+                    if self.last_epoch == 9 and get_context().get_world_rank() == 1 and not os.path.exists(flag):
+                        open(flag, "w").close()
+                        os._exit(7)
+            return Sched(optimizer, lambda step: 1.0)
+        model = NYC_Model(20)
+        est = TorchEstimator(num_workers=2, resources_per_worker={"GPU": 1}, model=model,
+                             optimizer=torch.optim.Adam(model.parameters(), lr=3e-3), loss=nn.SmoothL1Loss(),
+                             feature_columns=[f"f{i}" for i in range(20)], feature_types=torch.float,
+                             label_column="fare_amount", label_type=torch.float, batch_size=2048, num_epochs=3,
+                             shuffle=False, drop_last=True, lr_scheduler_creator=scheduler_that_kills_rank_1)
+        t0 = time.time()
+        est.fit_on_spark(df, max_retries=1)
+        assert os.path.exists(flag), "the failure was never injected"
+        assert time.time() - t0 < 240
+        train = [h for h in est.results.metrics_history if "train_loss" in h]
+        assert len(train) == 3 and train[0]["engine"] == "fused"
+        assert train[-1]["train_loss"] < train[0]["train_loss"]
+        raydp.stop_spark()
+    finally:
+        os.environ.pop("RAYDP_B200_COMM_TIMEOUT_S", None)
