@@ -647,7 +647,12 @@ class Head:
         node, holds = got
         ngpu = int(actor.resources.get("GPU", 0))
         with self._lock:
-            gpus = [node.gpu_free.pop(0) for _ in range(min(ngpu, len(node.gpu_free)))]
+            short = ngpu > len(node.gpu_free)
+            gpus = [] if short else [node.gpu_free.pop(0) for _ in range(ngpu)]
+        if short:                                   # ids of a dying actor are not back yet: try again later
+            self._release(actor.resources, holds)
+            return False
+        with self._lock:
             actor.gpus = gpus
             actor.holds = holds
             actor.node_id = node.node_id
@@ -750,12 +755,15 @@ class Head:
         actor = self._actors.get(worker.actor_id)
         if actor is None or actor.worker is not worker:
             return
-        self._release(actor.resources, actor.holds)
+        # device ids go back BEFORE the GPU resource count does: a new actor that wins the freed resource
+        # must also find a free device id (else two ranks ended up on one GPU after a group restart)
         with self._lock:
             node = worker.node
             node.gpu_free.extend(actor.gpus)
             node.gpu_free.sort()
             actor.gpus = []
+        self._release(actor.resources, actor.holds)
+        with self._lock:
             actor.holds = None
         can_restart = (not actor.intentional_exit and
                        (actor.max_restarts < 0 or actor.num_restarts < actor.max_restarts))
