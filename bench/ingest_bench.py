@@ -138,13 +138,16 @@ def main():
     ms, host, clocks = timed(step_e2e, steps, args.warmup)
     out["step_e2e"] = {"ms_per_step": ms, "host_us_per_batch": host * 1e3, "clocks": clocks}
     out["e2e_over_device"] = out["step_device"]["ms_per_step"] / out["step_e2e"]["ms_per_step"]
-    if args.timeline and rank == 0:
+    if args.timeline:                       # every rank steps (collectives); rank 0 records
+        import contextlib
         from torch.profiler import ProfilerActivity, profile
-        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        hb.barrier(world)
+        with (profile(activities=[ProfilerActivity.CUDA]) if rank == 0 else contextlib.nullcontext()) as prof:
             for _ in range(8):
                 step_e2e()
             torch.cuda.synchronize()
-        prof.export_chrome_trace(args.timeline)
+        if rank == 0:
+            prof.export_chrome_trace(args.timeline)
     engine.close()
     if rank == 0:
         print(json.dumps(out), flush=True)
