@@ -48,6 +48,11 @@ def main():
     if rank == 0:
         print(f"# NVLS multicast support: {use_nvls}", flush=True)
     rows = []
+    sampler = None
+    if not args.check:
+        from raydp_b200.utils.profiling import ClockSampler
+        sampler = ClockSampler(local)
+        sampler.start()
     for n in [int(x) for x in args.sizes.split(",")]:
         n = (n + 3) // 4 * 4
         g = torch.Generator(device="cuda").manual_seed(1000 + rank)
@@ -76,6 +81,21 @@ def main():
                 err = (got - ref).abs().max().item()
                 assert err <= 1e-4 * max(1.0, ref.abs().max().item()), ("registered", n, rep, err)
             red.close()
+            # bf16 on the wire: compare with the fp32 sum of the bf16-rounded inputs (what the kernels promise:
+            # one rounding of the input, fp32 accumulation, one rounding of the result)
+            n8 = n // 8 * 8
+            xq = x[:n8].to(torch.bfloat16).float()
+            refq = xq.clone()
+            dist.all_reduce(refq)
+            tol = 2.0 ** -8 * max(1.0, refq.abs().max().item())
+            red = P2PReducer(x[:n8].clone(), torch.device("cuda", local), algo="bf16")
+            for rep in range(3):
+                red.grads.copy_(x[:n8])
+                red.allreduce_()
+                torch.cuda.synchronize()
+                err = (red.grads - refq).abs().max().item()
+                assert err <= tol, ("bf16", n, rep, err)
+            red.close()
             if use_nvls:
                 nv = NvlsReducer(n, torch.device("cuda", local))
                 for rep in range(3):
@@ -85,11 +105,36 @@ def main():
                     err = (nv.buffer - ref).abs().max().item()
                     assert err <= 1e-4 * max(1.0, ref.abs().max().item()), ("nvls", n, rep, err)
                 nv.close()
+                nv = NvlsReducer(n8, torch.device("cuda", local), wire="bf16")
+                for rep in range(3):
+                    nv.buffer.copy_(x[:n8])
+                    nv.allreduce_()
+                    torch.cuda.synchronize()
+                    err = (nv.buffer - refq).abs().max().item()
+                    assert err <= tol, ("nvls bf16", n, rep, err)
+                nv.close()
             continue
         iters = 200 if n <= (1 << 20) else (50 if n <= (1 << 24) else 10)
         buf = x.clone()
         t_nccl = timed(lambda: dist.all_reduce(buf), iters)
         res = {"floats": n, "bytes": n * 4, "nccl_us": t_nccl}
+        if n >= (1 << 18):
+            # bf16 on the wire (fp32 gradients in, fp32 result out): NCCL's side of it is cast -> all_reduce(bf16)
+            # -> cast back, which is what DDP's bf16 compression hook does
+            def nccl_bf16():
+                h = buf.to(torch.bfloat16)
+                dist.all_reduce(h)
+                buf.copy_(h)
+            res["nccl_bf16_us"] = timed(nccl_bf16, iters)
+            n8 = n // 8 * 8
+            red = P2PReducer(x[:n8].clone(), torch.device("cuda", local), algo="bf16")
+            res["bf16_two_shot_us"] = timed(lambda: red.allreduce_(), iters)
+            red.close()
+            if use_nvls:
+                nv = NvlsReducer(n8, torch.device("cuda", local), wire="bf16")
+                nv.buffer.copy_(x[:n8])
+                res["nvls_bf16_us"] = timed(lambda: nv.allreduce_(), iters)
+                nv.close()
         for algo in ("one_shot", "two_shot", "ll"):
             if algo == "one_shot" and n > (1 << 22):
                 continue
@@ -109,7 +154,10 @@ def main():
             res["nvls_us"] = timed(lambda: nv.allreduce_(), iters)
             res["nvls_overlap_shape_us"] = timed(lambda: nv.allreduce_(overlap=True), iters)
             nv.close()
-        best = min(v for k, v in res.items() if k.endswith("_us") and k != "nccl_us")
+        best = min(v for k, v in res.items() if k.endswith("_us") and not k.startswith("nccl") and "bf16" not in k)
+        wire16 = [v for k, v in res.items() if k.endswith("_us") and not k.startswith("nccl") and "bf16" in k]
+        if wire16:
+            res["bf16_best_us"] = min(wire16)
         factor = 2 * (world - 1) / world * n * 4
         res["p2p_best_us"] = best
         res["nccl_busbw_GBs"] = factor / t_nccl / 1e3
@@ -119,9 +167,12 @@ def main():
             print(json.dumps(res), flush=True)
     if args.check and rank == 0:
         print("CHECK OK", flush=True)
+    clocks = sampler.stop() if sampler is not None else None
+    if rank == 0 and clocks is not None:
+        print(json.dumps({"clocks": clocks}), flush=True)
     if args.json and rank == 0 and rows:
         with open(args.json, "w") as fh:
-            json.dump({"world": world, "rows": rows}, fh, indent=1)
+            json.dump({"world": world, "clocks": clocks, "rows": rows}, fh, indent=1)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -30,17 +30,27 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     from raydp_b200.comm import P2PAllToAll
     rows = []
+    sampler = None
+    if not args.check:
+        from raydp_b200.utils.profiling import ClockSampler
+        sampler = ClockSampler(local)
+        sampler.start()
     for total in [int(x) for x in args.sizes.split(",")]:
         per = max(4, (total // world + 3) // 4 * 4)
         x = torch.arange(world * per, device="cuda", dtype=torch.float32) + 1e6 * rank
         ref = torch.empty_like(x)
         a2a = P2PAllToAll(per, torch.device("cuda", local))
         if args.check:
-            dist.all_to_all_single(ref, x)
-            for _ in range(3):
+            prev = None
+            for it in range(5):                          # new data every call: the parity buffers must not mix
+                x.add_(1.0)
+                dist.all_to_all_single(ref, x)
                 got = a2a(x)
                 torch.cuda.synchronize()
-                assert torch.equal(got.reshape(-1), ref), (total, rank)
+                assert torch.equal(got.reshape(-1), ref), (total, rank, it)
+                if prev is not None:                     # the previous result stays readable for one more call
+                    assert torch.equal(prev[0].reshape(-1), prev[1]), (total, rank, it, "previous buffer clobbered")
+                prev = (got, ref.clone())
             a2a.close()
             continue
         iters = 200 if total <= (1 << 22) else 20
@@ -56,8 +66,11 @@ def main():
             print(json.dumps(row), flush=True)
     if args.check and rank == 0:
         print("CHECK OK", flush=True)
+    clocks = sampler.stop() if sampler is not None else None
+    if rank == 0 and clocks is not None:
+        print(json.dumps({"clocks": clocks}), flush=True)
     if args.json and rank == 0 and rows:
-        json.dump({"world": world, "rows": rows}, open(args.json, "w"), indent=1)
+        json.dump({"world": world, "clocks": clocks, "rows": rows}, open(args.json, "w"), indent=1)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -128,10 +128,22 @@ def bigmlp_record(rank: int, world: int, local: int, steps: int = 6, warmup: int
         dp.backward_and_step(loss)
     r = _timed(ours, steps, warmup, world, local)
     out["params"] = nparams
-    out["ours"] = {"ms_per_step": r["ms"], "tflops_per_gpu": flops / (r["ms"] / 1e3) / 1e12, "clocks": r["clocks"]}
+    out["ours"] = {"ms_per_step": r["ms"], "tflops_per_gpu": flops / (r["ms"] / 1e3) / 1e12, "clocks": r["clocks"],
+                   "grad_wire": "fp32"}
     dp.close()
     del dp, model
     _release()
+    if world > 1:
+        # same step with bf16 gradients on the wire (fp32 accumulate): the counterpart of DDP's bf16 compression hook
+        with torch.device(dev):
+            model = BigMLP(width, hidden, depth, fused=True)
+        dp = FusedDataParallel(model, torch.optim.Adam(model.parameters(), lr=1e-3), dev, grad_wire="bf16")
+        r = _timed(ours, steps, warmup, world, local)
+        out["ours_bf16_wire"] = {"ms_per_step": r["ms"], "tflops_per_gpu": flops / (r["ms"] / 1e3) / 1e12,
+                                 "clocks": r["clocks"], "grad_wire": "bf16"}
+        dp.close()
+        del dp, model
+        _release()
     with torch.device(dev):
         model = BigMLP(width, hidden, depth, fused=False)
     ddp = nn.parallel.DistributedDataParallel(model, device_ids=[local]) if world > 1 else model
@@ -187,6 +199,22 @@ def allreduce_record(rank: int, world: int, local: int, sizes: List[int] = (1638
         best = min(v for k, v in row.items() if k.endswith("_us") and k != "nccl_us")
         factor = 2 * (world - 1) / world * n * 4
         row.update(ours_best_us=best, nccl_busbw_GBs=factor / row["nccl_us"] / 1e3, ours_busbw_GBs=factor / best / 1e3)
+        if n >= (1 << 22) and n % 8 == 0:
+            # bf16 on the wire, fp32 gradients in and out (not part of ours_best_us, which is fp32 end to end)
+            def nccl_bf16(i):
+                h = buf.to(torch.bfloat16)
+                dist.all_reduce(h)
+                buf.copy_(h)
+            wire = {"nccl_cast_allreduce_cast_us": _timed(nccl_bf16, iters, 5, world, local)["ms"] * 1e3}
+            red = P2PReducer(x.clone(), dev, algo="bf16")
+            wire["two_shot_us"] = _timed(lambda i: red.allreduce_(), iters, 5, world, local)["ms"] * 1e3
+            red.close()
+            if use_nvls:
+                nv = NvlsReducer(n, dev, wire="bf16")
+                nv.buffer.copy_(x)
+                wire["nvls_us"] = _timed(lambda i: nv.allreduce_(), iters, 5, world, local)["ms"] * 1e3
+                nv.close()
+            row["bf16_wire"] = wire
         rows.append(row)
         del x, buf
         _release()

@@ -283,6 +283,95 @@ allreduce_kernel(const __grid_constant__ ArParams P) {
   }
 }
 
+// ---- bf16 on the wire, fp32 accumulate (large gradient buckets) -------------------------------------
+// Two-shot all-reduce whose NVLink traffic is bf16: the fp32 gradient is rounded once into the bf16 send
+// buffer, every rank pulls its slice of all W copies (16 bytes = 8 values per load), sums them in fp32 in a
+// fixed rank order, scales, rounds the average once and pushes it as bf16 into every rank's receive buffer;
+// the optimizer epilogue reads the local bf16 copy.  Half the link bytes of the fp32 kernel; the same
+// precision contract as DDP's bf16 compression hook, with the sum kept in fp32 (python/raydp/torch/estimator.py
+// trains through DDP's fp32 buckets -- this is an opt-in trade for link-bound buckets).
+__device__ __forceinline__ uint4 ld_peer_b128(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.relaxed.sys.v4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void acc_bf16x8(float (&s)[8], const uint4 v) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    s[2 * k] += __uint_as_float(w[k] << 16);
+    s[2 * k + 1] += __uint_as_float(w[k] & 0xffff0000u);
+  }
+}
+__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+__global__ void __launch_bounds__(kArThreads)
+allreduce_bf16_kernel(const __grid_constant__ ArParams P) {
+  const RankArgs& a = P.rank[blockIdx.y];
+  const int my_rank = P.rank_base + blockIdx.y;
+  const int world = P.world;
+  const int nblocks = gridDim.x;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(a.epoch) + 1u;
+  const int64_t n8 = P.n / 8;                      // n is a multiple of 8 (host)
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  const int64_t nthreads = int64_t(nblocks) * blockDim.x;
+  float lr = a.opt.lr, bc1 = 1.f, bc2 = 1.f;
+  bool first_step = false;
+  if (a.opt.kind) {
+    if (a.opt.lr_ptr) lr = *a.opt.lr_ptr;
+    const float t = a.opt.step_ptr ? *a.opt.step_ptr : 1.f;
+    bc1 = 1.f - powf(a.opt.beta1, t);
+    bc2 = 1.f - powf(a.opt.beta2, t);
+    first_step = t <= 1.f;
+  }
+  // phase 1: round my gradient into my bf16 send buffer
+  uint4* mine = reinterpret_cast<uint4*>(a.send[0][my_rank]);
+  for (int64_t i = tid; i < n8; i += nthreads) {
+    const float4 g0 = reinterpret_cast<const float4*>(a.in)[2 * i], g1 = reinterpret_cast<const float4*>(a.in)[2 * i + 1];
+    mine[i] = make_uint4(pack2_bf16(g0.x, g0.y), pack2_bf16(g0.z, g0.w), pack2_bf16(g1.x, g1.y), pack2_bf16(g1.z, g1.w));
+  }
+  grid_signal_and_wait(a, my_rank, world, e, 0, a.counters + 0, nblocks);
+  // phase 2: reduce-scatter by pull (slice my_rank, fp32 sums in rank order), all-gather by bf16 push
+  const int64_t per = (n8 + world - 1) / world;
+  const int64_t lo = per * my_rank, hi = min(n8, lo + per);
+  for (int64_t i = lo + tid; i < hi; i += nthreads) {
+    float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < world) v[q] = ld_peer_b128(reinterpret_cast<const uint4*>(a.send[0][q]) + i);
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < world) acc_bf16x8(s, v[q]);
+    const uint4 r = make_uint4(pack2_bf16(s[0] * P.scale, s[1] * P.scale), pack2_bf16(s[2] * P.scale, s[3] * P.scale),
+                               pack2_bf16(s[4] * P.scale, s[5] * P.scale), pack2_bf16(s[6] * P.scale, s[7] * P.scale));
+#pragma unroll 4
+    for (int q = 0; q < world; ++q) reinterpret_cast<uint4*>(a.recv[0][(my_rank + q) % world])[i] = r;
+  }
+  grid_signal_and_wait(a, my_rank, world, e, 1, a.counters + 2, nblocks);
+  // phase 3: optimizer epilogue (or fp32 copy-out) from the locally complete bf16 receive buffer
+  const uint4* full = reinterpret_cast<const uint4*>(a.recv[0][my_rank]);
+  for (int64_t i = tid; i < n8; i += nthreads) {
+    float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    acc_bf16x8(s, full[i]);
+    apply_update(a.opt, i * 8, make_float4(s[0], s[1], s[2], s[3]), bc1, bc2, lr, first_step, a.out);
+    apply_update(a.opt, i * 8 + 4, make_float4(s[4], s[5], s[6], s[7]), bc1, bc2, lr, first_step, a.out);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(a.counters + 1, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      a.counters[1] = 0;
+      *a.epoch = e;
+    }
+  }
+}
+
 // ---- LL: one-round all-reduce for latency-bound messages (<= ~1 MB) ---------------------------------
 // The one-shot kernel above needs a flag round (copy -> signal -> wait) before anybody may pull.  Here the
 // flag travels WITH the data: rank r pushes its gradient into slot r of every peer's receive area as 16-byte
@@ -533,6 +622,58 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
   return 0;
 }
 
+// bf16-wire two-shot all-reduce (algo 5): same region layout and arguments as rdp_allreduce; the send / recv
+// buffers are used as bf16 (send[0] / recv[0] only, as algo 3).  n % 8 == 0; `ins` must not alias the region.
+int rdp_allreduce_bf16(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
+                       const float* const* ins, float* const* outs, uint32_t* const* epochs,
+                       uint32_t* const* counters, const rdp_opt_args* opts, int64_t n, float scale, void* stream) {
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks, "rdp_allreduce_bf16: world=%d (max %d)", world, kMaxRanks);
+  RDP_REQUIRE(n_local_ranks == 1 || n_local_ranks == world, "rdp_allreduce_bf16: bad n_local_ranks");
+  RDP_REQUIRE(n > 0 && n % 8 == 0 && uint64_t(n) <= 2 * slot_floats && slot_floats % 4 == 0,
+              "rdp_allreduce_bf16: n=%lld must be a multiple of 8 within the slot (%llu bf16 values)", (long long)n,
+              (unsigned long long)(2 * slot_floats));
+  ArParams P;
+  memset(&P, 0, sizeof(P));
+  P.rank_base = n_local_ranks == 1 ? rank : 0;
+  P.world = world; P.n = n; P.scale = scale; P.fixed_buffer = 1;
+  for (int l = 0; l < n_local_ranks; ++l) {
+    RankArgs& a = P.rank[l];
+    a.in = ins[l]; a.out = outs[l]; a.epoch = epochs[l]; a.counters = counters[l];
+    for (int q = 0; q < world; ++q) {
+      float* base = static_cast<float*>(bases[q]);
+      a.send[0][q] = base;
+      a.send[1][q] = base + slot_floats;
+      a.recv[0][q] = base + 2 * slot_floats;
+      a.recv[1][q] = base + 3 * slot_floats;
+      a.flags[q] = reinterpret_cast<uint32_t*>(base + 4 * slot_floats);
+      RDP_REQUIRE(q != P.rank_base + l || static_cast<const void*>(a.in) != static_cast<const void*>(base),
+                  "rdp_allreduce_bf16: the gradient may not live in the send buffer (it is rewritten as bf16)");
+    }
+    if (opts != nullptr) {
+      const rdp_opt_args& o = opts[l];
+      a.opt = OptSpec{o.kind, o.p, o.m, o.v, o.lr, o.beta1, o.beta2, o.eps, o.weight_decay, o.momentum,
+                      o.dampening, o.adamw, o.nesterov, o.lr_ptr, o.step_ptr,
+                      static_cast<__nv_bfloat16*>(o.shadow)};
+    }
+  }
+  int64_t work = n / 8 / world;
+  int blocks = int((work + kArThreads - 1) / kArThreads);
+  int cap = num_sms();
+  if (n_local_ranks > 1) cap = max(1, (num_sms() / 2) / world);
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  dim3 grid(blocks, n_local_ranks);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  void* args[] = {&P};
+  if (n_local_ranks > 1) {
+    RDP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)allreduce_bf16_kernel, grid, dim3(kArThreads), args, 0, s));
+  } else {
+    allreduce_bf16_kernel<<<grid, kArThreads, 0, s>>>(P);
+  }
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // LL one-round all-reduce (latency-bound sizes).  Region of one rank: 2 * 8 * 2 * slot_floats floats
 // (parity x source-rank slots x {value, epoch} packets); zero-initialised; epochs[l] / counters[l] as for
 // rdp_allreduce.  n <= slot_floats, n % 4 == 0.
@@ -705,6 +846,87 @@ constexpr int kArOverlapThreads = 256;
 __global__ void __launch_bounds__(kArOverlapThreads, 6)
 nvls_allreduce_overlap_kernel(const __grid_constant__ NvlsParams p) { nvls_allreduce_body(p); }
 
+// bf16 on the wire through the switch: the multicast buffer holds bf16.  The fp32 gradient `in` is rounded into
+// the local buffer, `multimem.ld_reduce ... .acc::f32.v4.bf16x2` sums the W copies of 8 values in the switch with
+// fp32 accumulation, the scaled average is rounded once and broadcast with `multimem.st`; the optimizer epilogue
+// reads the local bf16 copy.  Half the NVLink bytes of the fp32 kernel above.
+struct NvlsBf16Params {
+  NvlsParams base;                 // mc / local address the bf16 buffer; n counts VALUES (multiple of 8)
+  const float* in;                 // fp32 gradient (not inside the multicast buffer)
+};
+
+__device__ __forceinline__ void nvls_allreduce_bf16_body(const NvlsBf16Params& P) {
+  const NvlsParams& p = P.base;
+  const int nblocks = gridDim.x;
+  const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
+  const int64_t n8 = p.n / 8;
+  const int64_t per = (n8 + p.world - 1) / p.world;
+  const int64_t lo = per * p.rank, hi = min(n8, lo + per);
+  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
+  const int64_t nthreads = int64_t(nblocks) * blockDim.x;
+  float lr = p.opt.lr, bc1 = 1.f, bc2 = 1.f;
+  bool first_step = false;
+  if (p.opt.kind) {
+    if (p.opt.lr_ptr) lr = *p.opt.lr_ptr;
+    const float t = p.opt.step_ptr ? *p.opt.step_ptr : 1.f;
+    bc1 = 1.f - powf(p.opt.beta1, t);
+    bc2 = 1.f - powf(p.opt.beta2, t);
+    first_step = t <= 1.f;
+  }
+  uint4* local = reinterpret_cast<uint4*>(p.local);
+  for (int64_t i = tid; i < n8; i += nthreads) {
+    const float4 g0 = reinterpret_cast<const float4*>(P.in)[2 * i], g1 = reinterpret_cast<const float4*>(P.in)[2 * i + 1];
+    local[i] = make_uint4(pack2_bf16(g0.x, g0.y), pack2_bf16(g0.z, g0.w), pack2_bf16(g1.x, g1.y), pack2_bf16(g1.z, g1.w));
+  }
+  flags_signal_and_wait(p.flags, p.rank, p.world, e, 0, p.counters + 0, nblocks);
+  constexpr int kU = 4;
+  uint4* mc = reinterpret_cast<uint4*>(p.mc);
+  for (int64_t i0 = lo + tid; i0 < hi; i0 += nthreads * kU) {
+    uint4 v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t i = i0 + u * nthreads;
+      if (i < hi)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(mc + i) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int64_t i = i0 + u * nthreads;
+      if (i < hi) {
+        float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        acc_bf16x8(s, v[u]);
+        const uint32_t r0 = pack2_bf16(s[0] * p.scale, s[1] * p.scale), r1 = pack2_bf16(s[2] * p.scale, s[3] * p.scale),
+                       r2 = pack2_bf16(s[4] * p.scale, s[5] * p.scale), r3 = pack2_bf16(s[6] * p.scale, s[7] * p.scale);
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                     ::"l"(mc + i), "f"(__uint_as_float(r0)), "f"(__uint_as_float(r1)), "f"(__uint_as_float(r2)),
+                       "f"(__uint_as_float(r3)) : "memory");
+      }
+    }
+  }
+  flags_signal_and_wait(p.flags, p.rank, p.world, e, 1, p.counters + 2, nblocks);
+  for (int64_t i = tid; i < n8; i += nthreads) {
+    float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    acc_bf16x8(s, local[i]);
+    apply_update(p.opt, i * 8, make_float4(s[0], s[1], s[2], s[3]), bc1, bc2, lr, first_step, p.out);
+    apply_update(p.opt, i * 8 + 4, make_float4(s[4], s[5], s[6], s[7]), bc1, bc2, lr, first_step, p.out);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t prev = atomicAdd(p.counters + 1, 1u);
+    if (prev == uint32_t(nblocks - 1)) {
+      p.counters[1] = 0;
+      *p.epoch = e;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kArThreads)
+nvls_allreduce_bf16_kernel(const __grid_constant__ NvlsBf16Params p) { nvls_allreduce_bf16_body(p); }
+__global__ void __launch_bounds__(kArOverlapThreads, 6)
+nvls_allreduce_bf16_overlap_kernel(const __grid_constant__ NvlsBf16Params p) { nvls_allreduce_bf16_body(p); }
+
 }  // namespace rdp
 
 extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
@@ -735,6 +957,40 @@ extern "C" int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* fl
   return 0;
 }
 
+// bf16-wire NVLS all-reduce: the multicast buffer (mc_ptr / local_ptr) holds n bf16 values; `in` is the fp32
+// gradient; the averaged result goes through the optimizer epilogue and / or to `out` (fp32).  n % 8 == 0.
+extern "C" int rdp_allreduce_nvls_bf16(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
+                                       uint32_t* epoch, uint32_t* counters, const rdp_opt_args* opt, const float* in,
+                                       float* out, int64_t n, float scale, int overlap_shape, void* stream) {
+  using namespace rdp;
+  RDP_REQUIRE(mc_ptr != nullptr, "rdp_allreduce_nvls_bf16: no multicast mapping (NVLS unsupported on this system)");
+  RDP_REQUIRE(world >= 1 && world <= kMaxRanks && n > 0 && n % 8 == 0, "rdp_allreduce_nvls_bf16: bad world/n");
+  RDP_REQUIRE(in != nullptr && (opt != nullptr || out != nullptr), "rdp_allreduce_nvls_bf16: missing in / out");
+  NvlsBf16Params P;
+  memset(&P, 0, sizeof(P));
+  NvlsParams& p = P.base;
+  p.mc = static_cast<float*>(mc_ptr);
+  p.local = static_cast<float*>(local_ptr);
+  for (int q = 0; q < world; ++q) p.flags[q] = static_cast<uint32_t*>(flag_ptrs[q]);
+  p.rank = rank; p.world = world; p.n = n; p.scale = scale; p.epoch = epoch; p.counters = counters; p.out = out;
+  P.in = in;
+  if (opt != nullptr)
+    p.opt = OptSpec{opt->kind, opt->p, opt->m, opt->v, opt->lr, opt->beta1, opt->beta2, opt->eps, opt->weight_decay,
+                    opt->momentum, opt->dampening, opt->adamw, opt->nesterov, opt->lr_ptr, opt->step_ptr,
+                    static_cast<__nv_bfloat16*>(opt->shadow)};
+  int64_t work = n / 8 / world / 4;
+  const int threads = overlap_shape ? kArOverlapThreads : kArThreads;
+  int blocks = int((work + threads - 1) / threads);
+  const int cap = num_sms();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (overlap_shape) nvls_allreduce_bf16_overlap_kernel<<<blocks, threads, 0, s>>>(P);
+  else nvls_allreduce_bf16_kernel<<<blocks, threads, 0, s>>>(P);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // ================================================================================================
 // All-to-all over peer memory (the standalone form of the K4 exchange)
 // ================================================================================================
@@ -748,8 +1004,9 @@ struct A2AParams {
   uint32_t* flags[kMaxRanks];
   int rank, world;
   int64_t chunk4;                  // float4 vectors per (src, dst) pair
+  int64_t parity_stride;           // floats between the two receive buffers (0: one buffer + a "consumed" round)
   uint32_t* epoch;
-  uint32_t* counters;
+  uint32_t* counters;              // 16 words: [0] round A, [1] finished, [4 + q] blocks done with destination slot q
 };
 
 __global__ void __launch_bounds__(kArThreads)
@@ -758,17 +1015,23 @@ alltoall_kernel(const __grid_constant__ A2AParams p) {
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
   const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
   const int64_t nthreads = int64_t(nblocks) * blockDim.x;
-  // round A (slot 3): every rank has entered the call, so last call's receive buffers are consumed
-  flags_signal_and_wait(p.flags, p.rank, p.world, e, 3, p.counters + 0, nblocks);
+  // Receive buffers alternate on epoch parity (parity_stride != 0), which makes an "everybody has consumed the
+  // last result" round unnecessary: this rank can only finish call e after every rank has ENTERED call e (it
+  // needs their pushes), i.e. after their streams ran past the consumers of call e-1; so when it starts call
+  // e+1 -- writing the buffers of call e-1 -- nobody reads them any more.  One flag round per call.
+  const int64_t parity_off = int64_t(e & 1u) * p.parity_stride;
+  if (p.parity_stride == 0)      // single buffer: round A (slot 3) says last call's receive buffers are consumed
+    flags_signal_and_wait(p.flags, p.rank, p.world, e, 3, p.counters + 0, nblocks);
   // The grid is a multiple of `world` blocks: block b pushes to destination (rank + b % world) % world, so
   // all destinations are in flight at once (the switch gives every pair full bandwidth) and ranks start on
-  // different peers.
+  // different peers.  The last block to finish a destination signals THAT destination; nobody waits for the
+  // slowest destination before signalling the others.
   {
     const int q = blockIdx.x % p.world;
     const int sub = blockIdx.x / p.world, nsub = nblocks / p.world;
     const int dst = (p.rank + q) % p.world;
     const float4* src = p.in + int64_t(dst) * p.chunk4;
-    float4* out = reinterpret_cast<float4*>(p.recv[dst]) + int64_t(p.rank) * p.chunk4;
+    float4* out = reinterpret_cast<float4*>(p.recv[dst] + parity_off) + int64_t(p.rank) * p.chunk4;
     const int64_t stride = int64_t(nsub) * blockDim.x;
     for (int64_t i0 = int64_t(sub) * blockDim.x + threadIdx.x; i0 < p.chunk4; i0 += 4 * stride) {
       float4 v[4];
@@ -777,9 +1040,20 @@ alltoall_kernel(const __grid_constant__ A2AParams p) {
 #pragma unroll
       for (int u = 0; u < 4; ++u) if (i0 + u * stride < p.chunk4) out[i0 + u * stride] = v[u];
     }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t prev = atomicAdd(p.counters + 4 + q, 1u);
+      if (prev == uint32_t(nsub - 1)) {
+        p.counters[4 + q] = 0;
+        __threadfence_system();
+        st_release_sys(p.flags[dst] + 4 * kMaxRanks + p.rank, e);
+      }
+    }
   }
-  // round B (slot 4): all pushes have landed
-  flags_signal_and_wait(p.flags, p.rank, p.world, e, 4, p.counters + 2, nblocks);
+  // round B (slot 4): the pushes of every rank have landed here
+  if (int(threadIdx.x) < p.world) wait_epoch(p.flags[p.rank] + 4 * kMaxRanks + threadIdx.x, e, 0x304u);
+  __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     const uint32_t prev = atomicAdd(p.counters + 1, 1u);
@@ -793,7 +1067,8 @@ alltoall_kernel(const __grid_constant__ A2AParams p) {
 }  // namespace rdp
 
 extern "C" int rdp_alltoall(const void* in, void* const* recv_bases, void* const* flag_ptrs, int rank, int world,
-                            int64_t floats_per_pair, uint32_t* epoch, uint32_t* counters, void* stream) {
+                            int64_t floats_per_pair, int64_t parity_stride_floats, uint32_t* epoch,
+                            uint32_t* counters, void* stream) {
   using namespace rdp;
   RDP_REQUIRE(world >= 1 && world <= kMaxRanks && floats_per_pair > 0 && floats_per_pair % 4 == 0,
               "rdp_alltoall: bad world / chunk (%lld floats per pair must be a multiple of 4)", (long long)floats_per_pair);
@@ -805,6 +1080,7 @@ extern "C" int rdp_alltoall(const void* in, void* const* recv_bases, void* const
     p.flags[q] = static_cast<uint32_t*>(flag_ptrs[q]);
   }
   p.rank = rank; p.world = world; p.chunk4 = floats_per_pair / 4; p.epoch = epoch; p.counters = counters;
+  p.parity_stride = parity_stride_floats;
   const int64_t work = p.chunk4 / 4;                       // 4 vectors per thread, per destination
   int per_dst = int((work + kArThreads - 1) / kArThreads);
   const int cap = num_sms() / world > 0 ? num_sms() / world : 1;

@@ -721,6 +721,10 @@ struct WgradParams {
   float* out;          // [Mw_total, ldo] fp32, accumulated with atomics
   int ldo;
   float* colsum;       // optional [Mw_total]: sum over rows of G (bias gradient), or null
+  // deterministic mode: every split STORES its tile at partial + split * partial_stride (same [m, ldo] layout as
+  // `out`); wgrad_reduce_kernel then adds the splits in order.  With one split the tile is stored into `out`.
+  float* partial;
+  long long partial_stride;
 };
 
 constexpr int kWgradThreads = 192;
@@ -822,7 +826,19 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
         uint32_t raw[32];
         tmem_ld_32x32(t_row + uint32_t(c), raw);
         tmem_ld_wait();
-        if (m < p.Mw) {
+        if (m < p.Mw && p.partial != nullptr) {
+          float* dst = p.partial + size_t(split) * p.partial_stride + size_t(m) * p.ldo + col0;
+          const int ncols = min(32, min(p.n_tile - c, p.Nw - col0));
+          if ((p.ldo & 3) == 0 && ncols == 32) {
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+              *reinterpret_cast<uint4*>(dst + q * 4) = make_uint4(raw[q * 4], raw[q * 4 + 1], raw[q * 4 + 2], raw[q * 4 + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < ncols) dst[j] = __uint_as_float(raw[j]);
+          }
+        } else if (m < p.Mw) {
           float* dst = p.out + size_t(m) * p.ldo + col0;
           const int ncols = min(32, min(p.n_tile - c, p.Nw - col0));
           if ((p.ldo & 3) == 0) {
@@ -854,6 +870,26 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<256>(tmem_base);
+  }
+}
+
+// out[i] = partial[0][i] + partial[1][i] + ... in split order: the same bits whatever the schedule was
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ partial, long long stride, int splits, float* __restrict__ out,
+                    long long n4, long long n) {
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  for (long long i = tid; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 acc = *reinterpret_cast<const float4*>(partial + i * 4);
+    for (int s = 1; s < splits; ++s) {
+      const float4 v = *reinterpret_cast<const float4*>(partial + s * stride + i * 4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    *reinterpret_cast<float4*>(out + i * 4) = acc;
+  }
+  for (long long i = n4 * 4 + tid; i < n; i += (long long)gridDim.x * blockDim.x) {   // tail (n4 == 0 if unaligned)
+    float acc = partial[i];
+    for (int s = 1; s < splits; ++s) acc += partial[s * stride + i];
+    out[i] = acc;
   }
 }
 
@@ -980,7 +1016,7 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
   if (rps < 4 * kBlockK) rps = 4 * kBlockK;
   splits = (rows + rps - 1) / rps;
   p.rows_per_split = rps;
-  p.out = out; p.ldo = ldo; p.colsum = nullptr;
+  p.out = out; p.ldo = ldo; p.colsum = nullptr; p.partial = nullptr; p.partial_stride = 0;
   CUtensorMap tg, tx;
   int rc = make_tmap_2d_bf16(&tg, g, rows, Mw, ldg, kBlockK, 64);
   if (rc) return rc;
@@ -992,6 +1028,59 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
   dim3 grid(splits, m_tiles, n_tiles);
   gemm_wgrad_kernel<<<grid, kWgradThreads, smem, static_cast<cudaStream_t>(stream)>>>(tg, tx, p);
   RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Deterministic wgrad: out[Mw, Nw] (contiguous, ldo == Nw, Nw % 4 == 0) = G^T X, bit-identical run to run.
+// The batch is split over CTAs as above, but each split stores its tile into `ws` and the splits are added
+// in order; the number of splits is limited by ws_floats (>= Mw * Nw: one split, stored straight into out).
+int rdp_gemm_wgrad_det(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
+                       int Nw, float* ws, long long ws_floats, void* stream) {
+  RDP_REQUIRE(rows > 0 && Mw > 0 && Nw > 0, "rdp_gemm_wgrad_det: empty problem");
+  RDP_REQUIRE(ldg % 8 == 0 && ldx % 8 == 0, "rdp_gemm_wgrad_det: pitches must be multiples of 8");
+  RDP_REQUIRE(ldo == Nw, "rdp_gemm_wgrad_det: out must be contiguous (ldo=%d Nw=%d)", ldo, Nw);
+  WgradParams p;
+  p.rows = rows; p.Mw = Mw; p.Nw = Nw;
+  int n_tile = ((Nw + 15) / 16) * 16;
+  if (n_tile > 256) n_tile = 256;
+  p.n_tile = n_tile;
+  const int m_tiles = (Mw + 127) / 128;
+  const int n_tiles = (Nw + n_tile - 1) / n_tile;
+  const long long elems = (long long)Mw * Nw;
+  int splits = num_sms() / (m_tiles * n_tiles);
+  const long long cap = ws != nullptr ? ws_floats / elems : 1;
+  if (splits > cap) splits = int(cap);
+  if (splits < 1) splits = 1;
+  int rps = (rows + splits - 1) / splits;
+  rps = ((rps + kBlockK - 1) / kBlockK) * kBlockK;
+  if (rps < 4 * kBlockK) rps = 4 * kBlockK;
+  splits = (rows + rps - 1) / rps;
+  p.rows_per_split = rps;
+  p.out = out; p.ldo = ldo; p.colsum = nullptr;
+  p.partial = splits == 1 ? out : ws;
+  p.partial_stride = elems;
+  CUtensorMap tg, tx;
+  int rc = make_tmap_2d_bf16(&tg, g, rows, Mw, ldg, kBlockK, 64);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tx, x, rows, Nw, ldx, kBlockK, 64);
+  if (rc) return rc;
+  const int n_chunks = (n_tile + 63) / 64;
+  const size_t smem = size_t(kWgradStages) * (2 + n_chunks) * (kBlockK * 128) + 256 + 1024;
+  RDP_SMEM_ATTR_ONCE_PER_DEVICE(gemm_wgrad_kernel, 227 * 1024);
+  cudaStream_t cs = static_cast<cudaStream_t>(stream);
+  dim3 grid(splits, m_tiles, n_tiles);
+  gemm_wgrad_kernel<<<grid, kWgradThreads, smem, cs>>>(tg, tx, p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  if (splits > 1) {
+    // vector path only when every split's base stays 16-byte aligned
+    const bool vec = elems % 4 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0 &&
+                     (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    const long long n4 = vec ? elems / 4 : 0;
+    int rgrid = int(((vec ? n4 : elems) + 255) / 256);
+    if (rgrid > num_sms() * 8) rgrid = num_sms() * 8;
+    wgrad_reduce_kernel<<<rgrid, 256, 0, cs>>>(ws, elems, splits, out, n4, elems);
+    RDP_CHECK_CUDA(cudaGetLastError());
+  }
   return 0;
 }
 

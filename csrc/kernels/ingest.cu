@@ -119,7 +119,8 @@ struct IndexParams {
   int n_cols;
   int64_t rows;
   int64_t src_offset;
-  int32_t table_rows[kMaxCols]; // modulo per output column (0 = no modulo)
+  int32_t table_rows[kMaxCols]; // > 0: modulo (negatives wrap, null -> row 0); 0: as is; < 0: multi-hot bag column of a
+                                // table with -table_rows rows: negative or null -> -1 (padding), else modulo
   int n_cross;                  // hashed crosses appended after the plain columns
   uint8_t cross_a[16], cross_b[16];
   int32_t cross_rows[16];
@@ -155,7 +156,12 @@ ingest_indices_kernel(const __grid_constant__ IndexParams p) {
     int* o = p.out + r * width;
     for (int c = 0; c < p.n_cols; ++c) {
       long long x = index_value(p, c, src);
-      if (p.table_rows[c] > 0) { x %= p.table_rows[c]; if (x < 0) x += p.table_rows[c]; }
+      const int tr = p.table_rows[c];
+      if (tr > 0) { x %= tr; if (x < 0) x += tr; }
+      else if (tr < 0) {
+        const bool null = p.valid[c] != nullptr && !bit_set(p.valid[c], src + p.vbit0[c]);
+        x = (null || x < 0) ? -1 : x % (-tr);
+      }
       o[c] = int(x);
     }
     for (int k = 0; k < p.n_cross; ++k) {

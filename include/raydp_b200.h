@@ -165,6 +165,12 @@ int rdp_allreduce(void* const* bases, uint64_t slot_floats, int rank, int world,
                   uint32_t* const* counters, const struct rdp_opt_args* opts, int64_t n, float scale,
                   int algo, void* stream);
 
+// bf16 on the wire, fp32 accumulate: two-shot all-reduce for link-bound gradient buckets.  Same region and
+// arguments as rdp_allreduce (the send / recv slots are used as bf16); n % 8 == 0; ins[] may not alias the region.
+int rdp_allreduce_bf16(void* const* bases, uint64_t slot_floats, int rank, int world, int n_local_ranks,
+                       const float* const* ins, float* const* outs, uint32_t* const* epochs,
+                       uint32_t* const* counters, const rdp_opt_args* opts, int64_t n, float scale, void* stream);
+
 // One-round ("LL") all-reduce for latency-bound sizes: every rank pushes {value, epoch} packets into slot `rank`
 // of every peer's receive area and then only polls its own memory -- no signal round.  Region per rank:
 // 2 (parity) x 8 (source slots) x 2 * slot_floats floats, zero-initialised.  Same argument conventions as
@@ -207,13 +213,22 @@ int rdp_close_fd(int fd);
 int rdp_allreduce_nvls(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
                        uint32_t* epoch, uint32_t* counters, const struct rdp_opt_args* opt, float* out,
                        int64_t n, float scale, int overlap_shape, void* stream);
+// bf16 wire through the switch (multimem.ld_reduce ... .acc::f32.v4.bf16x2): the multicast buffer holds n bf16
+// values, `in` is the fp32 gradient, the average goes to the optimizer epilogue and / or `out` (fp32).  n % 8 == 0.
+int rdp_allreduce_nvls_bf16(void* mc_ptr, void* local_ptr, void* const* flag_ptrs, int rank, int world,
+                            uint32_t* epoch, uint32_t* counters, const rdp_opt_args* opt, const float* in,
+                            float* out, int64_t n, float scale, int overlap_shape, void* stream);
 // overlap_shape != 0: launch 256-thread, <= 40-register blocks (one per SM) that fit beside a resident
 // tcgen05 GEMM CTA, for all-reduces meant to run concurrently with backward GEMMs.
 
 // All-to-all over peer memory: chunk q of `in` ([world][floats_per_pair]) lands in slot `rank` of rank q's
 // receive buffer (recv_bases[q], [world][floats_per_pair]); flag_ptrs[q] as for rdp_allreduce_nvls.
+// parity_stride_floats != 0: every rank has TWO receive buffers that far apart, used alternately (call parity =
+// (epoch + 1) & 1), and the call costs one flag round; 0: one buffer and a second ("consumed") round.
+// counters: 16 zero-initialised words.
 int rdp_alltoall(const void* in, void* const* recv_bases, void* const* flag_ptrs, int rank, int world,
-                 int64_t floats_per_pair, uint32_t* epoch, uint32_t* counters, void* stream);
+                 int64_t floats_per_pair, int64_t parity_stride_floats, uint32_t* epoch, uint32_t* counters,
+                 void* stream);
 
 // One flag round between all ranks on `stream`; the flag area (>= 256 bytes, zero-initialised) sits at
 // bases[q] + flag_offset_bytes in every rank's symmetric region; `epoch` is a local device uint32.
@@ -231,6 +246,36 @@ int rdp_embedding_fwd(float* const* tables, const int* slots, const int* cols, i
 int rdp_embedding_bwd_sgd(float* const* tables, const int* slots, const int* cols, int n_tables,
                           const int* const* idx, void* const* dfeats, const int* batch, int n_src, int idx_ld,
                           int S, int D, float lr, float grad_scale, const float* lr_ptr, void* stream);
+// K4 v2 (csrc/kernels/embedding_bag.cu): pooled bags, vector index dispatch, uneven batches, deterministic
+// duplicate combine and row-wise optimizers.  idx_t[s]: rank s' TRANSPOSED int32 index matrix [n_cols, ldb]
+// (ldb % 4 == 0, negative index = padding); lens[t]: bag length of table t (null = 1); batch[s]: capacity of rank
+// s' batch, batch_ptr[s] (optional, may be a peer pointer): its actual batch this step; mean: 0 sum, 1 mean.
+int rdp_embedding_bag_fwd(float* const* tables, const int* slots, const int* cols, const int* lens, int n_tables,
+                          const int* const* idx_t, void* const* feats, const int* batch, const int* const* batch_ptr,
+                          int n_src, int ldb, int S, int D, int mean, void* stream);
+// Backward + update.  A claim pass gives every touched row of every local table a slot (flag[t]: [rows_t] int32,
+// zero between steps; list: [acc_rows] (table, row) int pairs; count: one int); the combine pass adds every
+// gradient row into acc ([acc_rows, D] 64-bit fixed point, zero between steps; acc_rows >= indices of a step =
+// sum over sources and tables of batch * bag length); the update pass touches every listed row once.
+// kind 0: SGD; 1: row-wise Adagrad, state[t] [rows_t]; 2: lazy Adam,
+// state[t] = m then v ([2, rows_t, D], state_stride[t] = rows_t * D), bias correction from *step_ptr.
+int rdp_embedding_bag_bwd(float* const* tables, const int* slots, const int* cols, const int* lens, int n_tables,
+                          const int* const* idx_t, void* const* dfeats, const int* batch, const int* const* batch_ptr,
+                          int n_src, int ldb, int S, int D, int mean, float grad_scale,
+                          unsigned long long* acc, long long acc_rows, int* const* flag, int* list, int* count,
+                          float* const* state, const int64_t* state_stride, int kind, float lr, float eps, float beta1,
+                          float beta2, float weight_decay, const float* lr_ptr, const float* step_ptr, void* stream);
+// Deterministic reductions (bit-reproducible training).  rdp_gemm_wgrad_det: out[Mw, Nw] = G^T X (out contiguous,
+// ldo == Nw; OVERWRITES out): batch splits store into ws ([splits, Mw, Nw] fp32, splits limited by
+// ws_floats) and are added in split order.  rdp_colsum_ordered: out[i][0..n[i]) = column sums of the bf16
+// matrices src[i] ([rows, ld[i]]) by a fixed summation tree (bias gradients); up to 16 matrices per launch.
+int rdp_gemm_wgrad_det(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
+                       int Nw, float* ws, long long ws_floats, void* stream);
+// ws / counters: scratch for the two-level tree (rows are cut into up to 32 chunks; ws holds chunks x groups x 64
+// floats with groups = sum ceil(n[i] / 64); the first `groups` words of counters are zero on entry and on exit);
+// without scratch one CTA per 64 columns walks all rows.
+int rdp_colsum_ordered(const void* const* src, const int* ld, const int* n, float* const* out, int n_seg, int rows,
+                       float* ws, long long ws_floats, unsigned int* counters, int n_counters, void* stream);
 // ---- K9: DLRM dot interaction (torch.bmm + tril gather + cat + pad) ---------------------------------
 // feats [B, S, D] bf16 -> out [B, ld_out] bf16 = [row 0 (D) | S(S-1)/2 pair dots, i > j row-major | 0 pad].
 int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, int ld_out, void* stream);

@@ -26,7 +26,8 @@ from raydp_b200 import ops
 from raydp_b200.ops._abi import OptArgs
 
 FLAG_BYTES = 256
-ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2, "two_shot_fixed": 3, "ll": 4}
+ALGO = {"auto": 0, "one_shot": 1, "two_shot": 2, "two_shot_fixed": 3, "ll": 4, "bf16": 5}
+# "bf16": two-shot with bf16 on the wire and fp32 accumulation (half the NVLink bytes; for link-bound buckets)
 LL_MAX_BYTES = 1 << 20          # "auto" uses the one-round LL protocol up to this message size
 LL_SOURCE_SLOTS = 8             # receive slots per parity in the LL layout (= kMaxRanks of the kernels)
 
@@ -331,6 +332,14 @@ def _launch(lib, bases: Sequence[int], slot_floats: int, rank: int, world: int, 
     vp = ctypes.c_void_p
     arr = lambda xs: (vp * len(xs))(*[vp(x) for x in xs])  # noqa: E731
     opt_arr = (OptArgs * nl)(*opts) if opts is not None else None
+    if algo == ALGO["bf16"]:
+        assert n % 8 == 0, "the bf16-wire all-reduce moves 8 values per 16-byte load: pad the buffer to 8"
+        ops._check(lib.rdp_allreduce_bf16(arr(bases), slot_floats, rank, world, nl,
+                                          arr([t.data_ptr() for t in ins]),
+                                          arr([t.data_ptr() if t is not None else 0 for t in outs]),
+                                          arr([t.data_ptr() for t in epochs]), arr([t.data_ptr() for t in counters]),
+                                          opt_arr, n, scale, vp(torch.cuda.current_stream().cuda_stream)))
+        return
     ops._check(lib.rdp_allreduce(arr(bases), slot_floats, rank, world, nl,
                                  arr([t.data_ptr() for t in ins]),
                                  arr([t.data_ptr() if t is not None else 0 for t in outs]),
@@ -371,6 +380,11 @@ class P2PReducer:
         if self.ll:
             assert grads is not None, "the LL protocol reduces a caller-owned buffer"
             self.sym = SymmetricMemory(2 * LL_SOURCE_SLOTS * 2 * self.slot * 4, group)
+        elif self.algo == ALGO["bf16"]:
+            # the four slots keep their offsets but hold bf16: half the slot size is enough
+            assert grads is not None and self.n % 8 == 0, "bf16 wire: caller-owned buffer, multiple of 8 values"
+            self.slot = (self.n // 2 + 3) // 4 * 4
+            self.sym = SymmetricMemory(4 * self.slot * 4 + FLAG_BYTES, group)
         else:
             self.sym = SymmetricMemory(4 * self.slot * 4 + FLAG_BYTES, group)
         if grads is None:
@@ -469,35 +483,44 @@ class NvlsReducer:
 
     kind = "nvls"
 
-    def __init__(self, n: int, device: torch.device, group=None):
-        assert n % 4 == 0
+    def __init__(self, n: int, device: torch.device, group=None, wire: str = "fp32"):
+        """``wire="bf16"``: the multicast buffer holds bf16 (half the NVLink bytes, fp32 accumulation in the
+        switch); ``buffer`` is then a plain fp32 tensor that is rounded into it by the kernel."""
+        assert n % 4 == 0 and wire in ("fp32", "bf16")
         self.n = n
+        self.wire16 = wire == "bf16"
+        assert not self.wire16 or n % 8 == 0, "bf16 wire: pad the buffer to a multiple of 8 values"
         self.lib = ops.lib()
         self.sym = None
-        nbytes = n * 4 + FLAG_BYTES
+        data_bytes = (n * 2 + 15) // 16 * 16 if self.wire16 else n * 4
+        nbytes = data_bytes + FLAG_BYTES
         if symm_support(device.index or 0) >= 2:
             # own plumbing: cuMemCreate + fd exchange + cuMulticastCreate/AddDevice/BindMem (csrc/comm/symmem.cu)
             self.sym = SymmetricMemory(nbytes, group, multicast=True)
             self.rank, self.world = self.sym.rank, self.sym.world
             self.mc_ptr = int(self.sym.mc_ptr)
-            self.buffer = tensor_from_ptr(self.sym.local, (n,), torch.float32, device)
-            self.flag_ptrs = [int(b) + n * 4 for b in self.sym.bases]
+            self.buffer = tensor_from_ptr(self.sym.local, (n,), torch.float32, device) if not self.wire16 else None
+            self._wire_ptr = int(self.sym.local)
+            self.flag_ptrs = [int(b) + data_bytes for b in self.sym.bases]
             self.plumbing = "own (cuMulticast*)"
         else:
             import torch.distributed._symmetric_memory as symm_mem
             group = group or dist.group.WORLD
-            self._t = symm_mem.empty(n + FLAG_BYTES // 4, dtype=torch.float32, device=device)
+            self._t = symm_mem.empty(data_bytes // 4 + FLAG_BYTES // 4, dtype=torch.float32, device=device)
             self._t.zero_()
             self._hdl = symm_mem.rendezvous(self._t, group)
             self.rank, self.world = self._hdl.rank, self._hdl.world_size
             self.mc_ptr = int(self._hdl.multicast_ptr or 0)
             if not self.mc_ptr:
                 raise RuntimeError("this system exposes no NVLS multicast mapping")
-            self.buffer = self._t[:n]
-            self.flag_ptrs = [int(p) + n * 4 for p in self._hdl.buffer_ptrs]
+            self.buffer = self._t[:n] if not self.wire16 else None
+            self._wire_ptr = int(self._t.data_ptr())
+            self.flag_ptrs = [int(p) + data_bytes for p in self._hdl.buffer_ptrs]
             self.plumbing = "torch symmetric memory"
             torch.cuda.synchronize()
             dist.barrier(group)
+        if self.wire16:
+            self.buffer = torch.zeros(n, dtype=torch.float32, device=device)
         self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
         self.counters = torch.zeros(4, dtype=torch.int32, device=device)
 
@@ -506,6 +529,18 @@ class NvlsReducer:
         """``overlap=True`` launches the register-capped 256-thread shape that co-resides with GEMM CTAs."""
         vp = ctypes.c_void_p
         flags = (vp * self.world)(*[vp(p) for p in self.flag_ptrs])
+        if self.wire16:
+            if out is None and opt is None:
+                out = self.buffer                     # plain all-reduce: result back in place, as fp32
+            ops._check(self.lib.rdp_allreduce_nvls_bf16(vp(self.mc_ptr), vp(self._wire_ptr), flags, self.rank,
+                                                        self.world, vp(self.epoch.data_ptr()),
+                                                        vp(self.counters.data_ptr()),
+                                                        ctypes.byref(opt) if opt is not None else None,
+                                                        vp(self.buffer.data_ptr()),
+                                                        vp(out.data_ptr()) if out is not None else None, self.n,
+                                                        scale, 1 if overlap else 0,
+                                                        vp(torch.cuda.current_stream().cuda_stream)))
+            return
         ops._check(self.lib.rdp_allreduce_nvls(vp(self.mc_ptr), vp(self.buffer.data_ptr()), flags, self.rank,
                                                self.world, vp(self.epoch.data_ptr()), vp(self.counters.data_ptr()),
                                                ctypes.byref(opt) if opt is not None else None,
@@ -540,29 +575,39 @@ def nvls_available(device: torch.device) -> bool:
 
 
 class P2PAllToAll:
-    """All-to-all of fp32 chunks by direct peer stores (``rdp_alltoall``).  ``recv`` is this rank's
-    receive buffer ``[world, floats_per_pair]`` inside symmetric memory."""
+    """All-to-all of fp32 chunks by direct peer stores (``rdp_alltoall``).  Every rank owns two receive
+    buffers ``[world, floats_per_pair]`` in symmetric memory, used alternately, so a call costs ONE flag round;
+    the returned view is valid until the call after next."""
 
     def __init__(self, floats_per_pair: int, device: torch.device, group=None):
         assert floats_per_pair % 4 == 0
         self.chunk = floats_per_pair
         self.lib = ops.lib()
         world = dist.get_world_size(group)
-        self.sym = SymmetricMemory(world * floats_per_pair * 4 + FLAG_BYTES, group)
+        self.stride = (world * floats_per_pair + 63) // 64 * 64            # floats between the parity buffers
+        self.sym = SymmetricMemory(2 * self.stride * 4 + FLAG_BYTES, group)
         self.rank, self.world = self.sym.rank, self.sym.world
-        self.recv = tensor_from_ptr(self.sym.local, (world, floats_per_pair), torch.float32, device)
-        self._flag_ptrs = [b + world * floats_per_pair * 4 for b in self.sym.bases]
+        self._recv = [tensor_from_ptr(self.sym.local + b * self.stride * 4, (world, floats_per_pair), torch.float32,
+                                      device) for b in range(2)]
+        self._flag_ptrs = [b + 2 * self.stride * 4 for b in self.sym.bases]
         self.epoch = torch.zeros(1, dtype=torch.int32, device=device)
-        self.counters = torch.zeros(4, dtype=torch.int32, device=device)
+        self.counters = torch.zeros(16, dtype=torch.int32, device=device)
+        self._calls = 0                 # host mirror of the device epoch
+
+    @property
+    def recv(self) -> torch.Tensor:
+        """Receive buffer of the most recent call."""
+        return self._recv[self._calls & 1]
 
     def __call__(self, send: torch.Tensor) -> torch.Tensor:
         assert send.dtype == torch.float32 and send.numel() == self.world * self.chunk and send.is_contiguous()
         vp = ctypes.c_void_p
         arr = lambda xs: (vp * len(xs))(*[vp(x) for x in xs])  # noqa: E731
         ops._check(self.lib.rdp_alltoall(vp(send.data_ptr()), arr(self.sym.bases), arr(self._flag_ptrs), self.rank,
-                                         self.world, self.chunk, vp(self.epoch.data_ptr()),
+                                         self.world, self.chunk, self.stride, vp(self.epoch.data_ptr()),
                                          vp(self.counters.data_ptr()), vp(torch.cuda.current_stream().cuda_stream)))
-        return self.recv
+        self._calls += 1
+        return self._recv[self._calls & 1]
 
     def close(self) -> None:
         self.sym.close()

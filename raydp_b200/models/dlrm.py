@@ -10,7 +10,7 @@ sharded table-wise with the all-to-all fused into the lookup).
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import List, Sequence
+from typing import List, Optional, Sequence
 
 import torch
 import torch.nn as nn
@@ -24,13 +24,25 @@ class DLRMSpec:
     embedding_dim: int
     bottom: Sequence[int]
     top: Sequence[int]
+    # multi-hot tables: table t reads bag_sizes[t] consecutive index columns per sample (negative = padding)
+    # and pools them ("sum" or "mean"); None = one index per table, as in the reference notebook
+    bag_sizes: Optional[Sequence[int]] = None
+    pooling: str = "sum"
+
+    @property
+    def index_columns(self) -> int:
+        return sum(self.bag_sizes) if self.bag_sizes else len(self.table_sizes)
 
 
 class DLRM(nn.Module):
     def __init__(self, num_dense: int = 13, table_sizes: Sequence[int] = (1000,) * 26, embedding_dim: int = 32,
                  bottom: Sequence[int] = (512, 128, 32), top: Sequence[int] = (1024, 1024, 512, 256, 1),
-                 sparse_grad: bool = True):
+                 sparse_grad: bool = True, bag_sizes: Optional[Sequence[int]] = None, pooling: str = "sum"):
         super().__init__()
+        assert pooling in ("sum", "mean")
+        assert bag_sizes is None or len(bag_sizes) == len(table_sizes)
+        self.bag_sizes = tuple(int(b) for b in bag_sizes) if bag_sizes else None
+        self.pooling = pooling
         assert bottom[-1] == embedding_dim, "the bottom MLP must end at the embedding width"
         self.num_dense, self.table_sizes, self.embedding_dim = num_dense, tuple(table_sizes), embedding_dim
         self.bottom_dims, self.top_dims = tuple(bottom), tuple(top)
@@ -54,7 +66,18 @@ class DLRM(nn.Module):
         x = dense
         for lin in self.bottom:
             x = F.relu(lin(x))
-        emb = [e(sparse[:, t].long()) for t, e in enumerate(self.embeddings)]
+        if self.bag_sizes is None:
+            emb = [e(sparse[:, t].long()) for t, e in enumerate(self.embeddings)]
+        else:
+            emb, col = [], 0
+            for e, n in zip(self.embeddings, self.bag_sizes):
+                bag = sparse[:, col:col + n].long()
+                col += n
+                keep = (bag >= 0).to(x.dtype).unsqueeze(-1)
+                pooled = (e(bag.clamp_min(0)) * keep).sum(1)
+                if self.pooling == "mean":
+                    pooled = pooled / keep.sum(1).clamp_min(1.0)
+                emb.append(pooled)
         feats = torch.stack([x] + emb, dim=1)
         inter = torch.bmm(feats, feats.transpose(1, 2))
         flat = inter[:, self._li, self._lj]
@@ -67,4 +90,5 @@ class DLRM(nn.Module):
         return z
 
     def fused_spec(self) -> DLRMSpec:
-        return DLRMSpec(self.num_dense, self.table_sizes, self.embedding_dim, self.bottom_dims, self.top_dims)
+        return DLRMSpec(self.num_dense, self.table_sizes, self.embedding_dim, self.bottom_dims, self.top_dims,
+                        self.bag_sizes, self.pooling)

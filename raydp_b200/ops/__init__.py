@@ -96,6 +96,36 @@ def gemm_wgrad(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, *, mw: Optio
     return out
 
 
+def gemm_wgrad_det(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, ws: Optional[torch.Tensor], *,
+                   mw: Optional[int] = None, nw: Optional[int] = None) -> torch.Tensor:
+    """``out[Mw,Nw] = g[:, :Mw].T @ x[:, :Nw]``, bit-reproducible: batch splits are stored into ``ws`` (fp32
+    scratch, any size >= 0; it bounds the number of splits) and added in split order.  Overwrites ``out``."""
+    global _launches
+    assert g.dtype == torch.bfloat16 and x.dtype == torch.bfloat16 and out.dtype == torch.float32
+    rows = g.shape[0]
+    Mw = mw if mw is not None else g.shape[1]
+    Nw = nw if nw is not None else x.shape[1]
+    _check(lib().rdp_gemm_wgrad_det(_ptr(g), _pitch(g), _ptr(x), _pitch(x), _ptr(out), _pitch(out), rows, Mw, Nw,
+                                    _ptr(ws), ws.numel() if ws is not None else 0, _stream()))
+    _launches += 1
+    return out
+
+
+def colsum_ordered(mats: Sequence[torch.Tensor], widths: Sequence[int], outs: Sequence[torch.Tensor],
+                   ws: Optional[torch.Tensor] = None, counters: Optional[torch.Tensor] = None) -> None:
+    """``outs[i][:widths[i]] = mats[i][:, :widths[i]].sum(0)`` with a fixed summation order (bias gradients of a
+    bit-reproducible step); bf16 matrices with the same number of rows, up to 16 per launch.  ``ws`` (fp32) and
+    ``counters`` (int32, zero) let the rows be split over CTAs (two-level ordered tree)."""
+    rows = mats[0].shape[0]
+    for i in range(0, len(mats), 16):
+        m, w, o = mats[i:i + 16], widths[i:i + 16], outs[i:i + 16]
+        assert all(t.dtype == torch.bfloat16 and t.shape[0] == rows for t in m)
+        _check(lib().rdp_colsum_ordered(_vp_arr([t.data_ptr() for t in m]), _i_arr([_pitch(t) for t in m]),
+                                        _i_arr(w), _vp_arr([t.data_ptr() for t in o]), len(m), rows, _ptr(ws),
+                                        ws.numel() if ws is not None else 0, _ptr(counters),
+                                        counters.numel() if counters is not None else 0, _stream()))
+
+
 def set_dynamic_tiles(on: bool) -> None:
     """Large-GEMM tile schedule: hardware work stealing (``True``) for GEMMs that overlap with an
     all-reduce kernel, static persistent loop (``False``, default) otherwise.  Process-wide."""
@@ -341,6 +371,41 @@ def embedding_bwd_sgd(table_ptrs, slots, cols, idx_ptrs, dfeats_ptrs, batches, i
     _check(lib().rdp_embedding_bwd_sgd(_vp_arr(table_ptrs), _i_arr(slots), _i_arr(cols), len(table_ptrs),
                                        _vp_arr(idx_ptrs), _vp_arr(dfeats_ptrs), _i_arr(batches), len(idx_ptrs),
                                        idx_ld, S, D, float(lr), float(grad_scale), _ptr(lr_dev), _stream()))
+
+
+def embedding_bag_fwd(table_ptrs, slots, cols, lens, idx_t_ptrs, feats_ptrs, batches, batch_ptrs, ldb: int, S: int,
+                      D: int, mean: bool) -> None:
+    """K4 v2 forward: pooled lookup + dispatch (``rdp_embedding_bag_fwd``).  ``batch_ptrs`` may be None."""
+    _check(lib().rdp_embedding_bag_fwd(_vp_arr(table_ptrs), _i_arr(slots), _i_arr(cols), _i_arr(lens), len(table_ptrs),
+                                       _vp_arr(idx_t_ptrs), _vp_arr(feats_ptrs), _i_arr(batches),
+                                       _vp_arr(batch_ptrs) if batch_ptrs else None, len(idx_t_ptrs), int(ldb), S, D,
+                                       1 if mean else 0, _stream()))
+
+
+EMB_OPT_KINDS = {"sgd": 0, "adagrad": 1, "rowwise_adagrad": 1, "adam": 2}
+
+
+def embedding_bag_bwd(table_ptrs, slots, cols, lens, idx_t_ptrs, dfeats_ptrs, batches, batch_ptrs, ldb: int, S: int,
+                      D: int, mean: bool, grad_scale: float, acc: torch.Tensor, flag_ptrs, touched: torch.Tensor,
+                      count: torch.Tensor, state_ptrs, state_strides, kind: int, lr: float, eps: float = 1e-8,
+                      beta1: float = 0.9,
+                      beta2: float = 0.999, weight_decay: float = 0.0, lr_dev: Optional[torch.Tensor] = None,
+                      step_dev: Optional[torch.Tensor] = None) -> None:
+    """K4 v2 backward: deterministic duplicate combine + one update per touched row (three kernels).
+    ``acc``: int64 ``[slots, D]`` (zero), ``touched``: int32 ``[slots, 2]``, ``count``: int32 ``[1]``;
+    ``slots`` >= number of indices a step can carry for the local tables."""
+    global _launches
+    n = len(table_ptrs)
+    strides = (ctypes.c_int64 * max(1, n))(*[int(v) for v in (state_strides or [0] * n)])
+    _check(lib().rdp_embedding_bag_bwd(_vp_arr(table_ptrs), _i_arr(slots), _i_arr(cols), _i_arr(lens), n,
+                                       _vp_arr(idx_t_ptrs), _vp_arr(dfeats_ptrs), _i_arr(batches),
+                                       _vp_arr(batch_ptrs) if batch_ptrs else None, len(idx_t_ptrs), int(ldb), S, D,
+                                       1 if mean else 0, float(grad_scale), _ptr(acc), acc.shape[0],
+                                       _vp_arr(flag_ptrs), _ptr(touched), _ptr(count),
+                                       _vp_arr(state_ptrs) if state_ptrs else None,
+                                       strides, int(kind), float(lr), float(eps), float(beta1), float(beta2),
+                                       float(weight_decay), _ptr(lr_dev), _ptr(step_dev), _stream()))
+    _launches += 2          # claim + combine + update (the counter reset is a memset node)
 
 
 def dot_interaction_fwd(feats: torch.Tensor, out: torch.Tensor) -> None:

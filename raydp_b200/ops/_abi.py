@@ -54,14 +54,26 @@ SIGNATURES.update({
 SIGNATURES.update({
     "rdp_allreduce_ll": (I, [C.POINTER(VP), C.c_uint64, I, I, I, C.POINTER(VP), C.POINTER(VP), C.POINTER(VP),
                              C.POINTER(VP), C.POINTER(OptArgs), I64, F, VP]),
+    "rdp_allreduce_bf16": (I, [C.POINTER(VP), C.c_uint64, I, I, I, C.POINTER(VP), C.POINTER(VP), C.POINTER(VP),
+                               C.POINTER(VP), C.POINTER(OptArgs), I64, F, VP]),
     "rdp_comm_set_timeout": (I, [C.c_double, VP]),
     "rdp_comm_barrier": (I, [C.POINTER(VP), C.c_uint64, I, I, VP, VP]),
-    "rdp_alltoall": (I, [VP, C.POINTER(VP), C.POINTER(VP), I, I, I64, VP, VP, VP]),
+    "rdp_alltoall": (I, [VP, C.POINTER(VP), C.POINTER(VP), I, I, I64, I64, VP, VP, VP]),
     "rdp_allreduce_nvls": (I, [VP, VP, C.POINTER(VP), I, I, VP, VP, C.POINTER(OptArgs), VP, I64, F, I, VP]),
+    "rdp_allreduce_nvls_bf16": (I, [VP, VP, C.POINTER(VP), I, I, VP, VP, C.POINTER(OptArgs), VP, VP, I64, F, I, VP]),
     "rdp_embedding_fwd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),
                               C.POINTER(I), I, I, I, I, VP]),
     "rdp_embedding_bwd_sgd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP), C.POINTER(VP),
                                   C.POINTER(I), I, I, I, I, F, F, VP, VP]),
+    "rdp_embedding_bag_fwd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP),
+                                  C.POINTER(VP), C.POINTER(I), C.POINTER(VP), I, I, I, I, I, VP]),
+    "rdp_embedding_bag_bwd": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), C.POINTER(I), I, C.POINTER(VP),
+                                  C.POINTER(VP), C.POINTER(I), C.POINTER(VP), I, I, I, I, I, F,
+                                  VP, C.c_longlong, C.POINTER(VP), VP, VP, C.POINTER(VP), C.POINTER(I64),
+                                  I, F, F, F, F, F, VP, VP, VP]),
+    "rdp_gemm_wgrad_det": (I, [VP, I, VP, I, VP, I, I, I, I, VP, C.c_longlong, VP]),
+    "rdp_colsum_ordered": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), C.POINTER(VP), I, I, VP, C.c_longlong, VP, I,
+                               VP]),
     "rdp_dot_interaction_fwd": (I, [VP, VP, I, I, I, I, VP]),
     "rdp_dot_interaction_bwd": (I, [VP, VP, VP, I, I, I, I, VP]),
     "rdp_bce_logits": (I, [VP, I, VP, VP, I, I, VP, I, F, VP, VP]),

@@ -29,7 +29,7 @@ from raydp_b200 import ops
 
 
 class _Bucket:
-    def __init__(self, params: List[nn.Parameter], device: torch.device, world: int):
+    def __init__(self, params: List[nn.Parameter], device: torch.device, world: int, grad_wire: str = "fp32"):
         self.params = params
         self.offsets, off = [], 0
         for p in params:
@@ -48,7 +48,15 @@ class _Bucket:
             from raydp_b200.comm import NvlsReducer, P2PReducer, nvls_available
             # Measured (profiles/README.md): the in-switch reduction wins from 4 ranks up (8 GPUs, 1 GB:
             # 2.28 ms vs 3.20 ms two-shot); with 2 ranks the peer-memory two-shot is faster (1.69 vs 2.7 ms).
-            if world >= 4 and nvls_available(device) and os.environ.get("RAYDP_B200_NO_NVLS") != "1":
+            use_nvls = world >= 4 and nvls_available(device) and os.environ.get("RAYDP_B200_NO_NVLS") != "1"
+            if grad_wire == "bf16":
+                # bf16 on the wire, fp32 accumulate: gradients stay in a local fp32 buffer and are rounded once
+                # into the (half-size) symmetric buffer by the reduction kernel itself
+                if use_nvls:
+                    self.reducer = NvlsReducer(self.n, device, wire="bf16")
+                else:
+                    self.reducer = P2PReducer(torch.zeros(self.n, **f32), device, algo="bf16")
+            elif use_nvls:
                 # reduction inside the NVSwitch (multimem): gradients live in the multicast-mapped buffer
                 self.reducer = NvlsReducer(self.n, device)
             else:
@@ -75,8 +83,13 @@ class _Bucket:
 
 class FusedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, optimizer: torch.optim.Optimizer, device: Optional[torch.device] = None,
-                 bucket_mb: int = 512, overlap: bool = True):
+                 bucket_mb: int = 512, overlap: bool = True, grad_wire: Optional[str] = None):
+        """``grad_wire``: ``"fp32"`` (default, what DDP's buckets carry) or ``"bf16"`` -- gradients cross NVLink as
+        bf16 and are summed in fp32 (half the link bytes; the counterpart of DDP's bf16 compression hook).
+        Environment default: ``RAYDP_B200_GRAD_WIRE``."""
         super().__init__()
+        self.grad_wire = grad_wire or os.environ.get("RAYDP_B200_GRAD_WIRE", "fp32")
+        assert self.grad_wire in ("fp32", "bf16"), self.grad_wire
         self.module = module
         self.device = device or next(module.parameters()).device
         self.world = dist.get_world_size() if dist.is_initialized() else 1
@@ -107,12 +120,12 @@ class FusedDataParallel(nn.Module):
         cur, size = [], 0
         for p in reversed(params):
             if cur and size + p.numel() > limit:
-                self.buckets.append(_Bucket(cur, self.device, self.world))
+                self.buckets.append(_Bucket(cur, self.device, self.world, self.grad_wire))
                 cur, size = [], 0
             cur.append(p)
             size += p.numel()
         if cur:
-            self.buckets.append(_Bucket(cur, self.device, self.world))
+            self.buckets.append(_Bucket(cur, self.device, self.world, self.grad_wire))
         self._bucket_of: Dict[int, _Bucket] = {id(p): b for b in self.buckets for p in b.params}
         f32 = dict(dtype=torch.float32, device=self.device)
         self.step_dev = torch.zeros(1, **f32)

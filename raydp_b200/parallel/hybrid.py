@@ -4,10 +4,14 @@ New capability relative to the reference (the reference k
 replicated under DDP, ``examples/pytorch_dlrm.ipynb`` cell 9; ``BASELINE.json`` config 3 asks for
 table-wise sharding with the all-to-all fused into the lookup).
 
-* Tables are dealt round-robin to ranks.  Forward: the owner reads each requesting rank's index
-  column over NVLink, gathers from its shard and stores rows straight into that rank's feature slab
-  (``rdp_embedding_fwd``); backward: the owner pulls gradient rows from every rank's slab and applies
-  sparse SGD (``rdp_embedding_bwd_sgd``).  Three flag rounds per step delimit the phases.
+* Tables are dealt round-robin to ranks.  Every rank publishes its indices transposed ([column, sample]).
+  Forward: the owner reads each requesting rank's indices over NVLink with 16-byte loads, gathers from its
+  shard, pools multi-hot bags (sum / mean) and stores one vector per (sample, table) straight into that
+  rank's feature slab (``rdp_embedding_bag_fwd``); backward: the owner pulls gradient rows from every rank's
+  slab, combines duplicate rows in 64-bit fixed point (bit-reproducible) and updates every touched row once
+  with SGD, row-wise Adagrad or lazy Adam (``rdp_embedding_bag_bwd``).  The batch of every rank is read from
+  that rank's memory, so ranks may hold different (even empty) batches.  Three flag rounds per step delimit
+  the phases.
 * Bottom / top MLPs run on the tcgen05 GEMM with bias+ReLU epilogues; the backward dgrad GEMM applies
   the ReLU mask in its epilogue and its tensor-core column sums are the bias gradients.
 * Interaction: ``rdp_dot_interaction_fwd/bwd``; loss: ``rdp_bce_logits``.
@@ -33,17 +37,50 @@ def _r8(v: int) -> int:
 class FusedDLRM:
     """One rank's share of the model plus its workspaces."""
 
-    def __init__(self, spec: DLRMSpec, batch: int, device: torch.device, rank: int = 0, world: int = 1):
+    def __init__(self, spec: DLRMSpec, batch: int, device: torch.device, rank: int = 0, world: int = 1,
+                 table_optimizer: str = "sgd", table_opt_args: Optional[dict] = None,
+                 deterministic: Optional[bool] = None):
+        import os
         self.spec, self.B, self.device, self.rank, self.world = spec, int(batch), device, rank, world
+        # bit-reproducible steps: weight gradients by ordered split sums, bias gradients by ordered column sums
+        # (the table update is always order-independent); RAYDP_B200_DETERMINISTIC=0 selects the atomic epilogues
+        self.deterministic = (os.environ.get("RAYDP_B200_DETERMINISTIC", "1") != "0") if deterministic is None \
+            else bool(deterministic)
         D, T = spec.embedding_dim, len(spec.table_sizes)
         self.D, self.T, self.S = D, T, T + 1
+        self.lens = [int(v) for v in (getattr(spec, "bag_sizes", None) or [1] * T)]
+        self.col0 = [sum(self.lens[:t]) for t in range(T)]
+        self.C = sum(self.lens)                       # index columns per sample
+        self.mean = getattr(spec, "pooling", "sum") == "mean"
+        self.ldb = (self.B + 3) // 4 * 4              # pitch of the transposed index matrix
         self.kpad = _r8(spec.num_dense)
-        self.inter_w = _r8(self.S * (self.S - 1) // 2 + D + 1)
+        # width of the interaction vector: the module pads it to 8 (models/dlrm.py), the GEMMs want 16
+        self.inter_w_model = _r8(self.S * (self.S - 1) // 2 + D + 1)
+        self.inter_w = (self.inter_w_model + 15) // 16 * 16
         f32 = dict(dtype=torch.float32, device=device)
         bf = dict(dtype=torch.bfloat16, device=device)
         # ---- sharded tables ------------------------------------------------------------------
         self.owned = [t for t in range(T) if t % world == rank]
         self.tables: Dict[int, torch.Tensor] = {t: torch.zeros(spec.table_sizes[t], D, **f32) for t in self.owned}
+        # sparse update: compact fixed-point accumulators (a slot per touched row), row -> slot map, touched list
+        if table_optimizer not in ops.EMB_OPT_KINDS:
+            raise ValueError(f"table_optimizer must be one of {sorted(ops.EMB_OPT_KINDS)}, got {table_optimizer!r}")
+        self.table_opt = ops.EMB_OPT_KINDS[table_optimizer]
+        self.table_opt_args = dict(eps=1e-8 if self.table_opt == 2 else 1e-10, beta1=0.9, beta2=0.999,
+                                   weight_decay=0.0)
+        self.table_opt_args.update(table_opt_args or {})
+        i32 = dict(dtype=torch.int32, device=device)
+        slots = max(1, sum(world * self.B * self.lens[t] for t in self.owned))      # indices of one step
+        self.acc = torch.zeros(slots, D, dtype=torch.int64, device=device)
+        self.row_slot = {t: torch.zeros(spec.table_sizes[t], **i32) for t in self.owned}
+        self.touched = torch.zeros(slots, 2, **i32)
+        self.touched_count = torch.zeros(1, **i32)
+        if self.table_opt == 1:
+            self.table_state = {t: torch.zeros(spec.table_sizes[t], **f32) for t in self.owned}
+        elif self.table_opt == 2:
+            self.table_state = {t: torch.zeros(2, spec.table_sizes[t], D, **f32) for t in self.owned}
+        else:
+            self.table_state = {}
         # ---- dense parameters: flat fp32 [W, b] per layer, bottom then top --------------------
         bdims = [spec.num_dense] + list(spec.bottom)
         tdims = [self.inter_w] + list(spec.top)
@@ -71,7 +108,8 @@ class FusedDLRM:
         B = self.B
         self.feats = torch.zeros(B, self.S, D, **bf)
         self.dfeats = torch.zeros(B, self.S, D, **bf)
-        self.idx = torch.zeros(B, T, dtype=torch.int32, device=device)
+        self.idx = torch.zeros(self.C, self.ldb, dtype=torch.int32, device=device)      # transposed
+        self.batch_dev = torch.full((1,), B, dtype=torch.int32, device=device)         # read by the owners
         self.act = [torch.zeros(B, self.npad[i], **bf) for i in range(len(self.layers))]
         self.dact = [torch.zeros(B, self.npad[i], **bf) for i in range(len(self.layers))]
         self.zint = torch.zeros(B, self.inter_w, **bf)
@@ -79,6 +117,11 @@ class FusedDLRM:
         self.stats = [torch.zeros(2, max(self.npad[i], 64), **f32) for i in range(len(self.layers))]
         self.stats_bottom_last = torch.zeros(2, max(D, 8), **f32)
         self.accum = torch.zeros(8, **f32)
+        biggest = max(n * k for _, _, k, n in self.layers)
+        self.wgrad_ws = torch.empty(max(biggest, min(16 * biggest, 16 << 20)), **f32) if self.deterministic else None
+        groups = sum((n + 63) // 64 for _, _, _, n in self.layers) + 1
+        self.colsum_ws = torch.empty(32 * groups * 64, **f32) if self.deterministic else None
+        self.colsum_counters = torch.zeros(groups, dtype=torch.int32, device=device) if self.deterministic else None
         self.ones32 = torch.ones(D, **f32)
         self.zeros32 = torch.zeros(D, **f32)
         # peers (filled by the owner of the world: symmetric memory or LocalWorld)
@@ -86,6 +129,8 @@ class FusedDLRM:
         self.peer_feats: List[int] = [self.feats.data_ptr()]
         self.peer_dfeats: List[int] = [self.dfeats.data_ptr()]
         self.peer_batch: List[int] = [B]
+        self.peer_batch_ptr: List[int] = [self.batch_dev.data_ptr()]
+        self.step_dev = torch.zeros(1, **f32)          # optimizer step count for the tables (Adam bias correction)
 
     # ------------------------------------------------------------------ parameters
     def weight(self, li: int, grad: bool = False) -> torch.Tensor:
@@ -106,7 +151,10 @@ class FusedDLRM:
             bottom, top, embs = list(module.bottom), list(module.top), list(module.embeddings)
         with torch.no_grad():
             for li, lin in enumerate(list(bottom) + list(top)):
-                self.weight(li).copy_(lin.weight)
+                w = self.weight(li)
+                if w.shape[1] != lin.in_features:          # first top layer: interaction width padded to 16
+                    w.zero_()
+                w[:, :lin.in_features].copy_(lin.weight)
                 self.bias(li).copy_(lin.bias)
             for t in self.owned:
                 self.tables[t].copy_(embs[t].weight)
@@ -114,7 +162,8 @@ class FusedDLRM:
     def dense_state_dict(self) -> Dict[str, torch.Tensor]:
         out = {}
         for li, (part, i, _, _) in enumerate(self.layers):
-            out[f"{part}.{i}.weight"] = self.weight(li).detach().cpu().clone()
+            k = self.inter_w_model if li == self.nb else self.layers[li][2]
+            out[f"{part}.{i}.weight"] = self.weight(li)[:, :k].detach().cpu().clone()
             out[f"{part}.{i}.bias"] = self.bias(li).detach().cpu().clone()
         return out
 
@@ -127,6 +176,35 @@ class FusedDLRM:
             _, _, k, n = self.layers[li]
             ops.cast_weight(self.weight(li), self.w_bf[li], self.w_t[li])
             self.bias_pad[li][:n].copy_(self.bias(li))
+
+    def _wgrad(self, g: torch.Tensor, inp: torch.Tensor, li: int) -> None:
+        _, _, k, n = self.layers[li]
+        if self.deterministic:
+            ops.gemm_wgrad_det(g, inp, self.weight(li, True), self.wgrad_ws, mw=n, nw=k)
+        else:
+            ops.gemm_wgrad(g, inp, self.weight(li, True), mw=n, nw=k)
+
+    def _dgrad(self, g: torch.Tensor, li: int, prev: int, B: int, k: int) -> None:
+        """dact[prev] = (g @ W_li) masked by ReLU of act[prev]; bias gradient of `prev` from the tensor-core column
+        sums (atomic across CTAs) or, deterministic, left to :meth:`_bias_grads`."""
+        if self.deterministic:
+            ops.gemm_tn(g, self.w_t[li], self.dact[prev][:B], aux=self.act[prev][:B], aux_relu_mask=True,
+                        n=self.npad[prev], k=k)
+            return
+        self.stats[prev].zero_()
+        ops.gemm_tn(g, self.w_t[li], self.dact[prev][:B], aux=self.act[prev][:B], aux_relu_mask=True,
+                    stats_mode=1, stats=self.stats[prev], n=self.npad[prev], k=k)
+        self.bias(prev, True).copy_(self.stats[prev][0, :self.layers[prev][3]])
+
+    def _bias_grads(self, layers: Sequence[int], B: int, extra=None) -> None:
+        """Ordered column sums of the layers' output gradients -> bias gradients (one launch)."""
+        mats = [self.dact[li][:B] for li in layers]
+        widths = [self.layers[li][3] for li in layers]
+        outs = [self.bias(li, True) for li in layers]
+        if extra is not None:
+            mats.append(extra[0]); widths.append(extra[1]); outs.append(extra[2])
+        if mats:
+            ops.colsum_ordered(mats, widths, outs, self.colsum_ws, self.colsum_counters)
 
     def _gemm_fwd(self, li: int, x: torch.Tensor, out: torch.Tensor, relu: bool) -> None:
         ops.gemm_tn(x, self.w_bf[li], out, bias=self.bias_pad[li], relu=relu, n=self.npad[li],
@@ -142,10 +220,24 @@ class FusedDLRM:
             self._gemm_fwd(li, x, out, relu=True)
             x = out
 
+    def set_indices(self, idx: torch.Tensor) -> None:
+        """idx [B, C] (any integer dtype) -> this rank's transposed int32 index matrix and batch count."""
+        B = idx.shape[0]
+        if B:
+            self.idx[:, :B].copy_(idx.t())
+        self.batch_dev.fill_(B)
+
+    def _owned_args(self):
+        return ([self.tables[t].data_ptr() for t in self.owned], [t + 1 for t in self.owned],
+                [self.col0[t] for t in self.owned], [self.lens[t] for t in self.owned])
+
     def embedding_forward(self) -> None:
-        """Push rows of the tables this rank owns into every rank's feature slab."""
-        ops.embedding_fwd([self.tables[t].data_ptr() for t in self.owned], [t + 1 for t in self.owned],
-                          self.owned, self.peer_idx, self.peer_feats, self.peer_batch, self.T, self.S, self.D)
+        """Pool and push rows of the tables this rank owns into every rank's feature slab."""
+        if not self.owned:
+            return
+        tables, slots, cols, lens = self._owned_args()
+        ops.embedding_bag_fwd(tables, slots, cols, lens, self.peer_idx, self.peer_feats, self.peer_batch,
+                              self.peer_batch_ptr, self.ldb, self.S, self.D, self.mean)
 
     def top_forward_backward(self, target: Optional[torch.Tensor], B: int, train: bool) -> torch.Tensor:
         ops.dot_interaction_fwd(self.feats[:B], self.zint[:B])
@@ -162,30 +254,38 @@ class FusedDLRM:
             return logits
         self.grads.zero_()
         dl = self.dact[-1][:B]
-        ops.bce_logits(logits, target, dl, self.accum, 1.0 / B, self.bias(n_layers - 1, True))
+        ops.bce_logits(logits, target, dl, self.accum, 1.0 / B,
+                       None if self.deterministic else self.bias(n_layers - 1, True))
         # ---- top backward ----
         for li in range(n_layers - 1, self.nb - 1, -1):
             inp = self.zint[:B] if li == self.nb else self.act[li - 1][:B]
             g = self.dact[li][:B]
-            _, _, k, n = self.layers[li]
-            ops.gemm_wgrad(g, inp, self.weight(li, True), mw=n, nw=k)
+            self._wgrad(g, inp, li)
             if li > self.nb:
-                prev = li - 1
-                self.stats[prev].zero_()
                 # dgrad with the ReLU mask of the previous activation fused in the epilogue; the
                 # tensor-core column sums of the result are that layer's bias gradient
-                ops.gemm_tn(g, self.w_t[li], self.dact[prev][:B], aux=self.act[prev][:B], aux_relu_mask=True,
-                            stats_mode=1, stats=self.stats[prev], n=self.npad[prev], k=self.npad[li])
-                self.bias(prev, True).copy_(self.stats[prev][0, :self.layers[prev][3]])
+                self._dgrad(g, li, li - 1, B, self.npad[li])
             else:
                 ops.gemm_tn(g, self.w_t[li], self.dzint[:B], n=self.inter_w, k=self.npad[li])
+        if self.deterministic:
+            self._bias_grads(range(self.nb, n_layers), B)
         ops.dot_interaction_bwd(self.feats[:B], self.dzint[:B], self.dfeats[:B])
         return logits
 
-    def embedding_backward(self, lr: float, grad_scale: float, lr_dev: Optional[torch.Tensor] = None) -> None:
-        ops.embedding_bwd_sgd([self.tables[t].data_ptr() for t in self.owned], [t + 1 for t in self.owned],
-                              self.owned, self.peer_idx, self.peer_dfeats, self.peer_batch, self.T, self.S, self.D,
-                              lr, grad_scale, lr_dev)
+    def embedding_backward(self, lr: float, grad_scale: float, lr_dev: Optional[torch.Tensor] = None,
+                           step_dev: Optional[torch.Tensor] = None) -> None:
+        if not self.owned:
+            return
+        tables, slots, cols, lens = self._owned_args()
+        a = self.table_opt_args
+        state = [self.table_state[t].data_ptr() for t in self.owned] if self.table_state else None
+        strides = [self.spec.table_sizes[t] * self.D for t in self.owned] if self.table_opt == 2 else None
+        ops.embedding_bag_bwd(tables, slots, cols, lens, self.peer_idx, self.peer_dfeats, self.peer_batch,
+                              self.peer_batch_ptr, self.ldb, self.S, self.D, self.mean, grad_scale,
+                              self.acc, [self.row_slot[t].data_ptr() for t in self.owned],
+                              self.touched, self.touched_count,
+                              state, strides, self.table_opt, lr, a["eps"], a["beta1"], a["beta2"],
+                              a["weight_decay"], lr_dev, step_dev)
 
     def bottom_backward(self, dense: torch.Tensor) -> None:
         B = dense.shape[0]
@@ -199,16 +299,13 @@ class FusedDLRM:
         g = dy
         for li in range(last, -1, -1):
             inp = dense if li == 0 else self.act[li - 1][:B]
-            _, _, k, n = self.layers[li]
-            ops.gemm_wgrad(g, inp, self.weight(li, True), mw=n, nw=k)
+            self._wgrad(g, inp, li)
             if li > 0:
                 prev = li - 1
-                self.stats[prev].zero_()
-                ops.gemm_tn(g, self.w_t[li], self.dact[prev][:B], aux=self.act[prev][:B], aux_relu_mask=True,
-                            stats_mode=1, stats=self.stats[prev], n=self.npad[prev],
-                            k=self.npad[li] if li != last else self.D)
-                self.bias(prev, True).copy_(self.stats[prev][0, :self.layers[prev][3]])
+                self._dgrad(g, li, prev, B, self.npad[li] if li != last else self.D)
                 g = self.dact[prev][:B]
+        if self.deterministic:
+            self._bias_grads(range(0, last), B, extra=(dy, self.D, self.bias(last, True)))
 
     def sgd(self, lr: float, scale: float = 1.0, momentum: float = 0.0, weight_decay: float = 0.0,
             lr_dev: Optional[torch.Tensor] = None, step_dev: Optional[torch.Tensor] = None) -> None:
@@ -221,14 +318,18 @@ class FusedDLRM:
 class LocalWorld:
     """W model-parallel ranks on one device, stepped in lock step (single-GPU tests / emulation)."""
 
-    def __init__(self, spec: DLRMSpec, batch_per_rank: int, world: int, device: torch.device):
+    def __init__(self, spec: DLRMSpec, batch_per_rank: int, world: int, device: torch.device,
+                 table_optimizer: str = "sgd", table_opt_args: Optional[dict] = None,
+                 deterministic: Optional[bool] = None):
         self.world = world
-        self.ranks = [FusedDLRM(spec, batch_per_rank, device, r, world) for r in range(world)]
+        self.ranks = [FusedDLRM(spec, batch_per_rank, device, r, world, table_optimizer, table_opt_args,
+                                deterministic) for r in range(world)]
         for r in self.ranks:
             r.peer_idx = [q.idx.data_ptr() for q in self.ranks]
             r.peer_feats = [q.feats.data_ptr() for q in self.ranks]
             r.peer_dfeats = [q.dfeats.data_ptr() for q in self.ranks]
             r.peer_batch = [q.B for q in self.ranks]
+            r.peer_batch_ptr = [q.batch_dev.data_ptr() for q in self.ranks]
 
     def load_from_module(self, module, plan=None) -> None:
         for r in self.ranks:
@@ -236,19 +337,26 @@ class LocalWorld:
 
     def train_step(self, dense: Sequence[torch.Tensor], idx: Sequence[torch.Tensor],
                    target: Sequence[torch.Tensor], lr: float) -> None:
+        """Ranks may hold different batch sizes (0 included): every owner reads them from ``batch_dev``."""
         W = self.world
         for r, d, i in zip(self.ranks, dense, idx):
             r._refresh_weights()
-            r.idx[:i.shape[0]].copy_(i)
-            r.bottom_forward(d)
+            r.set_indices(i)
+            r.step_dev.add_(1.0)
+            if d.shape[0]:
+                r.bottom_forward(d)
         for r in self.ranks:                       # (flag round 1 in the multi-GPU engine)
             r.embedding_forward()
         for r, d, t in zip(self.ranks, dense, target):   # (flag round 2)
-            r.top_forward_backward(t, d.shape[0], True)
+            if d.shape[0]:
+                r.top_forward_backward(t, d.shape[0], True)
+            else:
+                r.grads.zero_()
         for r in self.ranks:                       # (flag round 3)
-            r.embedding_backward(lr, 1.0 / W)
+            r.embedding_backward(lr, 1.0 / W, None, r.step_dev)
         for r, d in zip(self.ranks, dense):
-            r.bottom_backward(d)
+            if d.shape[0]:
+                r.bottom_backward(d)
         # dense gradients: average over ranks (all-reduce), identical SGD on every replica
         total = torch.stack([r.grads for r in self.ranks]).sum(0)
         for r in self.ranks:
@@ -258,7 +366,7 @@ class LocalWorld:
     def predict(self, dense: Sequence[torch.Tensor], idx: Sequence[torch.Tensor]) -> List[torch.Tensor]:
         for r, d, i in zip(self.ranks, dense, idx):
             r._refresh_weights()
-            r.idx[:i.shape[0]].copy_(i)
+            r.set_indices(i)
             r.bottom_forward(d)
         for r in self.ranks:
             r.embedding_forward()
@@ -271,7 +379,8 @@ class DistributedDLRM:
     phases, peer-memory all-reduce fused with SGD for the dense gradients."""
 
     def __init__(self, spec: DLRMSpec, batch: int, device: torch.device, group=None, momentum: float = 0.0,
-                 weight_decay: float = 0.0, use_graph: bool = True):
+                 weight_decay: float = 0.0, use_graph: bool = True, table_optimizer: str = "sgd",
+                 table_opt_args: Optional[dict] = None, deterministic: Optional[bool] = None):
         import os
         import torch.distributed as dist
         self.use_graph = use_graph and os.environ.get("RAYDP_B200_DLRM_GRAPH", "1") != "0"
@@ -282,7 +391,8 @@ class DistributedDLRM:
         self._lr_host = None
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.core = FusedDLRM(spec, batch, device, self.rank, self.world)
+        self.core = FusedDLRM(spec, batch, device, self.rank, self.world, table_optimizer, table_opt_args,
+                              deterministic)
         self.device = device
         self.momentum, self.weight_decay = momentum, weight_decay
         self.step_count = 0
@@ -293,10 +403,11 @@ class DistributedDLRM:
         if self.world > 1:
             from raydp_b200.comm import P2PReducer, SymmetricMemory, tensor_from_ptr
             c = self.core
-            B, T, S, D = c.B, c.T, c.S, c.D
-            idx_bytes = (B * T * 4 + 255) // 256 * 256
+            B, S, D = c.B, c.S, c.D
+            idx_bytes = (c.C * c.ldb * 4 + 255) // 256 * 256
             slab_bytes = (B * S * D * 2 + 255) // 256 * 256
-            per_parity = idx_bytes + 2 * slab_bytes
+            count_off = idx_bytes + 2 * slab_bytes             # this rank's batch of the step (int32)
+            per_parity = count_off + 256
             self.flag_off = 2 * per_parity
             self.sym = SymmetricMemory(self.flag_off + 256, group)
             self.barrier_epoch = torch.zeros(1, dtype=torch.int32, device=device)
@@ -304,20 +415,22 @@ class DistributedDLRM:
             for p in range(2):
                 base = p * per_parity
                 local = self.sym.local + base
-                self.views.append((tensor_from_ptr(local, (B, T), torch.int32, device),
+                self.views.append((tensor_from_ptr(local, (c.C, c.ldb), torch.int32, device),
                                    tensor_from_ptr(local + idx_bytes, (B, S, D), torch.bfloat16, device),
-                                   tensor_from_ptr(local + idx_bytes + slab_bytes, (B, S, D), torch.bfloat16, device)))
+                                   tensor_from_ptr(local + idx_bytes + slab_bytes, (B, S, D), torch.bfloat16, device),
+                                   tensor_from_ptr(local + count_off, (1,), torch.int32, device)))
                 self.peer_ptrs.append(([b + base for b in self.sym.bases],
                                        [b + base + idx_bytes for b in self.sym.bases],
-                                       [b + base + idx_bytes + slab_bytes for b in self.sym.bases]))
+                                       [b + base + idx_bytes + slab_bytes for b in self.sym.bases],
+                                       [b + base + count_off for b in self.sym.bases]))
             self.core.peer_batch = [B] * self.world
             self.reducer = P2PReducer(self.core.grads, device, group, algo="auto")
             dist.broadcast(self.core.params, src=0)
 
     def _select(self, parity: int) -> None:
         c = self.core
-        c.idx, c.feats, c.dfeats = self.views[parity]
-        c.peer_idx, c.peer_feats, c.peer_dfeats = self.peer_ptrs[parity]
+        c.idx, c.feats, c.dfeats, c.batch_dev = self.views[parity]
+        c.peer_idx, c.peer_feats, c.peer_dfeats, c.peer_batch_ptr = self.peer_ptrs[parity]
 
     def _barrier(self) -> None:
         ops.comm_barrier(self.sym.bases, self.flag_off, self.rank, self.world, self.barrier_epoch)
@@ -332,18 +445,23 @@ class DistributedDLRM:
             self._select(parity)
         ops.add_scalar(self.step_dev, 1.0)
         c._refresh_weights()
-        c.idx[:B].copy_(idx)
-        c.bottom_forward(dense)
+        c.set_indices(idx)
+        if B:
+            c.bottom_forward(dense)
         if multi:
             self._barrier()
         c.embedding_forward()
         if multi:
             self._barrier()
-        c.top_forward_backward(target, B, True)
+        if B:
+            c.top_forward_backward(target, B, True)
+        else:                   # this rank ran out of data: it still serves its tables and joins the reduction
+            c.grads.zero_()
         if multi:
             self._barrier()
-        c.embedding_backward(0.0, 1.0 / self.world, self.lr_dev)
-        c.bottom_backward(dense)
+        c.embedding_backward(0.0, 1.0 / self.world, self.lr_dev, self.step_dev)
+        if B:
+            c.bottom_backward(dense)
         if multi:
             from raydp_b200.comm import make_opt_args
             opt = make_opt_args(2, c.params, c.momentum_buf if self.momentum else None, None,
@@ -359,8 +477,7 @@ class DistributedDLRM:
         Inputs are staged into fixed device buffers so the graphs can read them."""
         c = self.core
         B = dense.shape[0]
-        if self.world > 1:
-            assert B == c.B, "model-parallel embeddings need equal, full batches on every rank (drop_last=True)"
+        assert B <= c.B, f"batch {B} exceeds the capacity {c.B} the workspaces were sized for"
         parity = self.step_count & 1
         self.step_count += 1
         if self.momentum and c.momentum_buf is None:
@@ -399,18 +516,18 @@ class DistributedDLRM:
         B = dense.shape[0]
         multi = self.world > 1
         if multi:
-            assert B == c.B
             self._select(self.step_count & 1)
         self.step_count += 1
         c._refresh_weights()
-        c.idx[:B].copy_(idx)
-        c.bottom_forward(dense)
+        c.set_indices(idx)
+        if B:
+            c.bottom_forward(dense)
         if multi:
             self._barrier()
         c.embedding_forward()
         if multi:
             self._barrier()
-        out = c.top_forward_backward(target, B, False)
+        out = c.top_forward_backward(target, B, False) if B else c.act[-1][:0]
         if multi:
             self._barrier()          # keeps the parity protocol's three rounds per step
         return out

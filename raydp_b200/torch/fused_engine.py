@@ -404,14 +404,20 @@ class DLRMEngine:
                 raise RuntimeError(f"DLRMEngine cannot run this model: {why}")
         self.plan = plan
         self.spec = plan.spec
+        extra = config.get("extra", {}) or {}
+        # the tables may use their own sparse optimizer: extra={"embedding_optimizer": "adagrad" | "adam" | "sgd",
+        # "embedding_optimizer_args": {"eps": ..., "beta1": ..., "beta2": ..., "weight_decay": ...}}
         self.dlrm = DistributedDLRM(self.spec, self.batch, self.device, momentum=g.get("momentum", 0.0),
-                                    weight_decay=g.get("weight_decay", 0.0))
+                                    weight_decay=g.get("weight_decay", 0.0),
+                                    table_optimizer=extra.get("embedding_optimizer", "sgd"),
+                                    table_opt_args=extra.get("embedding_optimizer_args"))
         # each rank copies the dense layers and ONLY the tables it owns straight from the host module
         self.dlrm.core.load_from_module(model, plan)
         cols = list(config["feature_columns"])
         self.dense_cols = cols[:self.spec.num_dense]
         self.sparse_cols = cols[self.spec.num_dense:]
-        assert len(self.sparse_cols) == len(self.spec.table_sizes), "one categorical column per embedding table"
+        assert len(self.sparse_cols) == self.spec.index_columns, \
+            "one categorical column per embedding table (bag_sizes[t] columns for a multi-hot table)"
         self._accum_host = torch.zeros(8, dtype=torch.float32).pin_memory()
         self._loaders = {}
 
@@ -419,11 +425,33 @@ class DLRMEngine:
         if id(shard) not in self._loaders:
             c = self.config
             self._loaders[id(shard)] = ArrowGpuLoader(
-                shard, self.dense_cols, c["label_column"], self.batch, c["drop_last"] or self.sess.world_size > 1,
+                shard, self.dense_cols, c["label_column"], self.batch, c["drop_last"],
                 self.device, ld=self.dlrm.core.kpad, sparse_columns=self.sparse_cols,
-                table_rows=list(self.spec.table_sizes),
+                table_rows=self._column_rows(),
                 null_fill=float(c.get("extra", {}).get("null_fill", float("nan"))))
         return self._loaders[id(shard)]
+
+    def _column_rows(self):
+        lens = self.spec.bag_sizes or [1] * len(self.spec.table_sizes)
+        # bag columns keep negative / NULL entries as padding (-1); single columns wrap into the table
+        return [rows if n == 1 else -rows for rows, n in zip(self.spec.table_sizes, lens) for _ in range(n)]
+
+    def _common_steps(self, loader) -> int:
+        """Ranks own tables of every other rank's lookups, so all of them take the same number of steps: the
+        longest shard decides, ranks that run out of rows join with an empty batch."""
+        n = len(loader)
+        if self.sess.world_size > 1:
+            import torch.distributed as dist
+            t = torch.tensor([n], dtype=torch.int64, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            n = int(t.item())
+        return n
+
+    def _empty_batch(self):
+        core = self.dlrm.core
+        return (torch.empty(0, core.kpad, dtype=torch.bfloat16, device=self.device),
+                torch.empty(0, core.C, dtype=torch.int32, device=self.device),
+                torch.empty(0, dtype=torch.float32, device=self.device))
 
     def _results(self, acc, steps):
         count = max(1.0, acc[3])
@@ -442,6 +470,7 @@ class DLRMEngine:
         start.record()
         steps = samples = 0
         h2d0 = loader.h2d_bytes
+        total_steps = self._common_steps(loader)
         for dense, idx, y in loader:
             with nvtx_range("rdp.dlrm.step"):
                 self.dlrm.train_step(dense, idx, y, float(self.optimizer.param_groups[0]["lr"]))
@@ -450,12 +479,18 @@ class DLRMEngine:
             ops.publish_host(core.accum, self._accum_host)
             steps += 1
             samples += dense.shape[0]
+        own_steps = steps
+        while steps < total_steps:
+            self.dlrm.train_step(*self._empty_batch(), float(self.optimizer.param_groups[0]["lr"]))
+            if self.scheduler is not None:
+                self.scheduler.step()
+            steps += 1
         end.record()
         torch.cuda.current_stream().synchronize()
         if self.sess.world_size > 1:
             from raydp_b200.comm import check_status
             check_status()
-        res, loss = self._results(self._accum_host.tolist(), steps)
+        res, loss = self._results(self._accum_host.tolist(), own_steps)
         timing = {"time_this_iter_s": time.perf_counter() - t0, "device_time_s": start.elapsed_time(end) / 1e3,
                   "samples_this_iter": samples, "steps_this_iter": steps, "engine": self.name,
                   "h2d_bytes_this_iter": loader.h2d_bytes - h2d0, "d2h_bytes_this_iter": 32 * steps}
@@ -466,10 +501,15 @@ class DLRMEngine:
         core = self.dlrm.core
         core.accum.zero_()
         steps = 0
+        total_steps = self._common_steps(loader)
         for dense, idx, y in loader:
             self.dlrm.eval_step(dense, idx, y)
             steps += 1
-        return self._results(core.accum.tolist(), steps)
+        own_steps = steps
+        while steps < total_steps:
+            self.dlrm.eval_step(*self._empty_batch()[:2], None)
+            steps += 1
+        return self._results(core.accum.tolist(), own_steps)
 
     def state_dict(self):
         torch.cuda.current_stream().synchronize()

@@ -33,6 +33,29 @@ def test_emulated_allreduce_matches_sum(world, algo, n):
             assert torch.allclose(o, ref, rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("n", [48520, 3 * 1024 * 1024 + 8])
+def test_emulated_bf16_wire_allreduce_rounds_once_in_and_once_out(world, n):
+    """bf16 on the wire, fp32 accumulate: the result is the bf16 rounding of the fp32 sum of the bf16-rounded
+    inputs -- compared against exactly that, computed in fp32 by PyTorch."""
+    from raydp_b200.comm import LocalEmulation
+    dev = torch.device("cuda")
+    emu = LocalEmulation(world, n, dev)
+    for step in range(3):
+        g = torch.Generator(device=dev).manual_seed(7 * step + world)
+        ins = [torch.randn(n, device=dev, generator=g) for _ in range(world)]
+        outs = [torch.empty(n, device=dev) for _ in range(world)]
+        acc = torch.zeros(n, device=dev)
+        for t in ins:                                 # rank order, like the kernel
+            acc += t.to(torch.bfloat16).float()
+        ref = (acc * (1.0 / world)).to(torch.bfloat16).float()
+        emu.allreduce(ins, outs, scale=1.0 / world, algo="bf16")
+        torch.cuda.synchronize()
+        for o in outs:
+            assert torch.equal(o, ref)
+            assert (o - torch.stack(ins).mean(0)).abs().max().item() < 2e-2     # and close to the fp32 mean
+
+
 def test_flag_protocol_stress_on_one_gpu():
     """Epoch-flag protocol under churn: 300 back-to-back all-reduces on emulated ranks, alternating
     one-shot / two-shot and message sizes without any host synchronisation in between (the parity

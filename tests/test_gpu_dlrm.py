@@ -117,7 +117,7 @@ def test_hybrid_step_matches_torch_sgd(world):
 
 def test_graph_replayed_step_tracks_the_eager_step():
     """DistributedDLRM replays one CUDA graph per slab parity; parameters and tables must follow the
-    eager step (differences only from atomic accumulation order), including an lr change mid-way
+    eager step, including an lr change mid-way
     (lr is a device scalar inside the graph)."""
     from raydp_b200.models import DLRM
     from raydp_b200.parallel.hybrid import DistributedDLRM
@@ -159,3 +159,204 @@ def test_multigpu_hybrid_dlrm_graph_vs_eager():
            "--check"]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "CHECK OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+# ---- K4 v2: bags, uneven batches, deterministic combine, row-wise optimizers -----------------------------
+def _bag_setup(seed=0):
+    torch.manual_seed(seed)
+    D = 32
+    sizes, lens = [50, 600, 7, 90], [1, 3, 4, 2]
+    tables = [torch.randn(n, D, device="cuda") for n in sizes]
+    col0 = [sum(lens[:t]) for t in range(len(lens))]
+    return D, sizes, lens, col0, tables
+
+
+def _bag_indices(B, sizes, lens, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    cols = []
+    for n, L in zip(sizes, lens):
+        bag = torch.randint(0, n, (B, L), device="cuda", generator=g)
+        if L > 1:                                  # ragged bags: pad some positions (never position 0)
+            pad = torch.rand(B, L, device="cuda", generator=g) < 0.3
+            pad[:, 0] = False
+            bag[pad] = -1
+        cols.append(bag)
+    return torch.cat(cols, 1).int()
+
+
+def _pool_ref(table, bag, mean):
+    keep = (bag >= 0).float().unsqueeze(-1)
+    out = (table[bag.clamp_min(0).long()] * keep).sum(1)
+    return out / keep.sum(1).clamp_min(1.0) if mean else out
+
+
+@pytest.mark.parametrize("mean", [False, True])
+def test_embedding_bag_forward_pools_like_torch_with_uneven_batches(mean):
+    """Two 'requesting ranks' with different batches (capacity 256; 250 and 37 valid rows, read from device
+    memory), two owners; transposed index matrices read with 16-byte loads; negative index = padding."""
+    from raydp_b200 import ops
+    D, sizes, lens, col0, tables = _bag_setup()
+    T, cap = len(sizes), 256
+    batches = [250, 37]
+    idx = [_bag_indices(b, sizes, lens, 5 + i) for i, b in enumerate(batches)]
+    idx_t = [torch.full((sum(lens), cap), 12345, dtype=torch.int32, device="cuda") for _ in batches]   # stale tail
+    for it, i in zip(idx_t, idx):
+        it[:, :i.shape[0]] = i.t()
+    feats = [torch.zeros(cap, T + 1, D, device="cuda", dtype=torch.bfloat16) for _ in batches]
+    counts = [torch.tensor([b], dtype=torch.int32, device="cuda") for b in batches]
+    for owned in ([0, 2], [1, 3]):
+        ops.embedding_bag_fwd([tables[t].data_ptr() for t in owned], [t + 1 for t in owned],
+                              [col0[t] for t in owned], [lens[t] for t in owned],
+                              [t.data_ptr() for t in idx_t], [f.data_ptr() for f in feats], [cap, cap],
+                              [c.data_ptr() for c in counts], cap, T + 1, D, mean)
+    for f, i, b in zip(feats, idx, batches):
+        for t in range(T):
+            ref = _pool_ref(tables[t], i[:, col0[t]:col0[t] + lens[t]], mean)
+            assert _rel(f[:b, t + 1], ref) < 4e-3
+        assert (f[b:] == 0).all()                   # rows past the valid batch are never written
+
+
+@pytest.mark.parametrize("kind", ["sgd", "adagrad", "adam"])
+def test_embedding_bag_backward_combines_duplicates_then_updates_each_row_once(kind):
+    from raydp_b200 import ops
+    D, sizes, lens, col0, tables = _bag_setup(1)
+    T, cap, B, mean = len(sizes), 512, 509, True
+    idx = _bag_indices(B, sizes, lens, 9)           # table 2 has 7 rows: heavy duplication
+    idx_t = torch.zeros(sum(lens), cap, dtype=torch.int32, device="cuda")
+    idx_t[:, :B] = idx.t()
+    g = (torch.randn(cap, T + 1, D, device="cuda") * 0.1).to(torch.bfloat16)
+    count = torch.tensor([B], dtype=torch.int32, device="cuda")
+    lr, scale, eps, b1, b2 = 0.05, 0.5, 1e-8, 0.9, 0.999
+    start = [t.clone() for t in tables]
+    acc = torch.zeros(cap * sum(lens), D, dtype=torch.int64, device="cuda")
+    flag = [torch.zeros(n, dtype=torch.int32, device="cuda") for n in sizes]
+    lst = torch.zeros(cap * sum(lens), 2, dtype=torch.int32, device="cuda")
+    cnt = torch.zeros(1, dtype=torch.int32, device="cuda")
+    state = {"sgd": None, "adagrad": [torch.zeros(n, device="cuda") for n in sizes],
+             "adam": [torch.zeros(2, n, D, device="cuda") for n in sizes]}[kind]
+    step = torch.zeros(1, device="cuda")
+
+    def run():
+        step.add_(1.0)
+        own = list(range(T))
+        ops.embedding_bag_bwd([tables[t].data_ptr() for t in own], [t + 1 for t in own], col0, lens,
+                              [idx_t.data_ptr()], [g.data_ptr()], [cap], [count.data_ptr()], cap, T + 1, D, mean,
+                              scale, acc, [f.data_ptr() for f in flag], lst, cnt,
+                              [s.data_ptr() for s in state] if state else None,
+                              [n * D for n in sizes] if kind == "adam" else None, ops.EMB_OPT_KINDS[kind], lr, eps,
+                              b1, b2, 0.0, None, step)
+
+    # reference: dense gradient per table by index_add, then the optimizer on touched rows only
+    ref = [t.clone() for t in start]
+    ref_state = [torch.zeros(n, device="cuda") for n in sizes] if kind == "adagrad" else \
+        [torch.zeros(2, n, D, device="cuda") for n in sizes]
+    for it in range(1, 3):
+        run()
+        n_touched = 0
+        for t in range(T):
+            bag = idx[:, col0[t]:col0[t] + lens[t]]
+            keep = bag >= 0
+            gt = g[:B, t + 1].float() * scale / keep.sum(1, keepdim=True).clamp_min(1).float()
+            G = torch.zeros(sizes[t], D, device="cuda")
+            G.index_add_(0, bag.clamp_min(0).long().reshape(-1),
+                         (gt.unsqueeze(1) * keep.unsqueeze(-1).float()).reshape(-1, D))
+            touched = torch.zeros(sizes[t], dtype=torch.bool, device="cuda")
+            touched[bag[keep].long()] = True
+            if kind == "sgd":
+                ref[t] -= lr * G
+            elif kind == "adagrad":
+                ref_state[t][touched] += (G[touched] ** 2).mean(1)
+                ref[t][touched] -= lr * G[touched] / (ref_state[t][touched].sqrt().unsqueeze(1) + 1e-8)
+            else:
+                m, v = ref_state[t][0], ref_state[t][1]
+                m[touched] = b1 * m[touched] + (1 - b1) * G[touched]
+                v[touched] = b2 * v[touched] + (1 - b2) * G[touched] ** 2
+                mh, vh = m[touched] / (1 - b1 ** it), v[touched] / (1 - b2 ** it)
+                ref[t][touched] -= lr * mh / (vh.sqrt() + eps)
+            n_touched += int(touched.sum())
+        assert int(cnt[0]) == n_touched
+    assert (acc == 0).all()                                            # scratch is clean for the next step
+    for t in range(T):
+        assert _rel(tables[t] - start[t], ref[t] - start[t]) < (5e-3 if kind == "adam" else 2e-3), (kind, t)
+        assert (flag[t] == 0).all()
+    # order independence: the same update again from the same start gives the same BITS
+    first = [t.clone() for t in tables]
+    for t in range(T):
+        tables[t].copy_(start[t])
+    if state:
+        for s_ in state:
+            s_.zero_()
+    step.zero_()
+    run(); run()
+    for t in range(T):
+        assert torch.equal(tables[t], first[t])
+
+
+def _bag_model(pooling="mean"):
+    from raydp_b200.models import DLRM
+    sizes = [97, 1000, 13, 512, 64, 300]
+    return DLRM(13, sizes, 32, bottom=(64, 32), top=(128, 64, 1), sparse_grad=False, bag_sizes=[1, 3, 2, 1, 4, 1],
+                pooling=pooling).cuda(), sizes
+
+
+def _bag_batch(model, sizes, B, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    dense = torch.randn(B, 13, device="cuda", generator=g)
+    idx = _bag_indices(B, sizes, list(model.bag_sizes), seed + 1000)
+    y = (torch.rand(B, device="cuda", generator=g) < 0.3).float()
+    return dense, idx, y
+
+
+def test_hybrid_step_with_bags_and_uneven_rank_batches_matches_torch():
+    """Three model-parallel ranks with 256, 131 and 0 rows: DDP semantics (mean of the per-rank mean losses over
+    the ranks; an empty rank contributes zero gradients but still serves its tables)."""
+    from raydp_b200.parallel.hybrid import LocalWorld
+    torch.manual_seed(0)
+    model, sizes = _bag_model()
+    world, cap = 3, 256
+    emu = LocalWorld(model.fused_spec(), cap, world, torch.device("cuda"))
+    emu.load_from_module(model)
+    opt = torch.optim.SGD(model.parameters(), lr=0.05)
+    crit = nn.BCEWithLogitsLoss()
+    batches = [256, 131, 0]
+    for step in range(5):
+        parts = [_bag_batch(model, sizes, b, 100 * step + r) for r, b in enumerate(batches)]
+        opt.zero_grad()
+        loss = sum(crit(model(d.to(torch.bfloat16).float(), i.long())[:, 0], y) for d, i, y in parts if d.shape[0])
+        (loss / world).backward()
+        opt.step()
+        emu.train_step([_pack_dense(d) for d, _, _ in parts], [i for _, i, _ in parts], [y for _, _, y in parts],
+                       lr=0.05)
+    r0 = emu.ranks[0]
+    assert _rel(r0.weight(0), model.bottom[0].weight.detach()) < 2e-2
+    assert _rel(r0.weight(len(r0.layers) - 1), model.top[-1].weight.detach()) < 2e-2
+    for r in emu.ranks:
+        for t in r.owned:
+            assert _rel(r.tables[t], model.embeddings[t].weight.detach()) < 2e-2
+    for r in emu.ranks[1:]:
+        assert torch.equal(r.params, r0.params)
+
+
+@pytest.mark.parametrize("table_optimizer", ["sgd", "adagrad"])
+def test_dlrm_steps_with_momentum_are_bit_reproducible(table_optimizer):
+    """Two runs of the same graph-replayed steps (momentum SGD on the dense layers, heavy index duplication)
+    end in the same BITS: ordered split sums for weight gradients, ordered column sums for bias gradients,
+    fixed-point combine for table rows."""
+    from raydp_b200.parallel.hybrid import DistributedDLRM
+    finals = []
+    for run in range(2):
+        torch.manual_seed(3)
+        model, sizes = _bag_model("sum")
+        eng = DistributedDLRM(model.fused_spec(), 512, torch.device("cuda"), momentum=0.9, use_graph=True,
+                              table_optimizer=table_optimizer, deterministic=True)
+        eng.core.load_from_module(model)
+        for step in range(8):
+            dense, idx, y = _bag_batch(model, sizes, 512, 50 + step)
+            eng.train_step(_pack_dense(dense), idx, y, 0.05)
+        torch.cuda.synchronize()
+        assert eng._graphs[0] is not None
+        finals.append((eng.core.params.clone(), {t: w.clone() for t, w in eng.core.tables.items()}))
+        eng.close()
+    assert torch.equal(finals[0][0], finals[1][0])
+    for t in finals[0][1]:
+        assert torch.equal(finals[0][1][t], finals[1][1][t])
