@@ -13,6 +13,7 @@
 // K9  dot interaction: per sample the 27x27 Gram of the feature vectors, lower triangle (351
 //     values, row-major i > j like torch.tril_indices(offset=-1)), concatenated after the dense
 //     vector and zero-padded to 384 -- written in the layout the top-MLP GEMM reads through TMA.
+#include <stdlib.h>
 #include "common.cuh"
 #include "raydp_b200.h"
 
@@ -131,6 +132,11 @@ embedding_bwd_sgd_vec_kernel(const __grid_constant__ EmbParams p, int lanes_per_
 
 // ---- dot interaction ---------------------------------------------------------------------------
 constexpr int kMaxS = 32;
+// tensor-core path for D = 32 (dot_interaction_mma.cu); the kernels below serve every other shape
+bool dot_interaction_mma_ok(int S, int D, int ld_out, const void* a, const void* b, const void* c);
+int dot_interaction_fwd_mma(const void* feats, void* out, int B, int S, int ld_out, cudaStream_t stream);
+int dot_interaction_bwd_mma(const void* feats, const void* dout, void* dfeats, int B, int S, int ld_out,
+                            cudaStream_t stream);
 
 __global__ void __launch_bounds__(128)
 dot_interaction_fwd_kernel(const __nv_bfloat16* __restrict__ feats, __nv_bfloat16* __restrict__ out, int B,
@@ -341,6 +347,8 @@ int rdp_embedding_bwd_sgd(float* const* tables, const int* slots, const int* col
 
 int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, int ld_out, void* stream) {
   RDP_REQUIRE(S <= kMaxS && D <= 128 && ld_out >= D + S * (S - 1) / 2, "dot_interaction: bad shape S=%d D=%d ld=%d", S, D, ld_out);
+  if (dot_interaction_mma_ok(S, D, ld_out, feats, out, out) && !getenv("RAYDP_B200_DOT_SCALAR"))
+    return dot_interaction_fwd_mma(feats, out, B, S, ld_out, static_cast<cudaStream_t>(stream));
   int grid = B < num_sms() * 8 ? B : num_sms() * 8;
   dot_interaction_fwd_kernel<<<grid, 128, S * (D + 1) * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(feats), static_cast<__nv_bfloat16*>(out), B, S, D, ld_out);
@@ -351,6 +359,8 @@ int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, i
 int rdp_dot_interaction_bwd(const void* feats, const void* dout, void* dfeats, int B, int S, int D, int ld_out,
                             void* stream) {
   RDP_REQUIRE(S <= kMaxS && D <= 128, "dot_interaction: bad shape S=%d D=%d", S, D);
+  if (dot_interaction_mma_ok(S, D, ld_out, feats, dout, dfeats) && !getenv("RAYDP_B200_DOT_SCALAR"))
+    return dot_interaction_bwd_mma(feats, dout, dfeats, B, S, ld_out, static_cast<cudaStream_t>(stream));
   int grid = B < num_sms() * 4 ? B : num_sms() * 4;      // 4 resident blocks per SM (64 registers x 256 threads)
   const size_t smem = (kDotSP * kDotSP + kDotSP * (D + 1)) * sizeof(float);
   dot_interaction_bwd_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(

@@ -260,62 +260,86 @@ embedding_bag_update_kernel(const __grid_constant__ BagUpdateParams p, int lanes
   float bc1 = 1.f, bc2 = 1.f;
   if (p.kind == 2) { bc1 = 1.f - powf(p.beta1, step); bc2 = 1.f - powf(p.beta2, step); }
   const int n = *p.count;
-  for (int64_t i0 = warp * rows_per_warp; i0 < n; i0 += nwarps * rows_per_warp) {
-    const int64_t i = i0 + sub;
-    const bool live = i < n;
-    const int2 tr = live ? p.list[i] : make_int2(0, 0);
-    const int t = tr.x, row = tr.y;
-    float g[4] = {0.f, 0.f, 0.f, 0.f};
-    if (live) {
-      ulonglong2* a = reinterpret_cast<ulonglong2*>(p.acc + size_t(i) * p.D + part * 4);
-      const ulonglong2 a0 = a[0], a1 = a[1];
-      a[0] = make_ulonglong2(0ull, 0ull);
-      a[1] = make_ulonglong2(0ull, 0ull);
-      g[0] = float(double(static_cast<long long>(a0.x)) * (1.0 / kFixScale));
-      g[1] = float(double(static_cast<long long>(a0.y)) * (1.0 / kFixScale));
-      g[2] = float(double(static_cast<long long>(a1.x)) * (1.0 / kFixScale));
-      g[3] = float(double(static_cast<long long>(a1.y)) * (1.0 / kFixScale));
-      if (part == 0) p.flag[t][row] = 0;
-    }
-    float* wptr = p.table[t] + size_t(row) * p.D + part * 4;
-    const float4 w4 = live ? *reinterpret_cast<float4*>(wptr) : make_float4(0.f, 0.f, 0.f, 0.f);
-    float w[4] = {w4.x, w4.y, w4.z, w4.w};
-    if (p.weight_decay != 0.f) {
+  // Two rows per sub-warp and iteration, and every load of an iteration issued before its first store: the loop
+  // is a chain of dependent DRAM round trips (list -> accumulator / table row), so memory-level parallelism is
+  // what it runs on (ncu, before: 13 % of DRAM bandwidth, 336 cycles of scoreboard stall per issue).
+  constexpr int kU = 2;
+  for (int64_t i0 = warp * rows_per_warp * kU; i0 < n; i0 += nwarps * rows_per_warp * kU) {
+    int64_t i[kU];
+    bool live[kU];
+    int2 tr[kU];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) g[k] += p.weight_decay * w[k];
+    for (int u = 0; u < kU; ++u) {
+      i[u] = i0 + u * rows_per_warp + sub;
+      live[u] = i[u] < n;
+      tr[u] = live[u] ? __ldg(p.list + i[u]) : make_int2(0, 0);
     }
-    if (p.kind == 1) {
-      // row-wise Adagrad: ONE accumulator per row, fed with the mean squared gradient of the row
-      float sq = g[0] * g[0] + g[1] * g[1] + g[2] * g[2] + g[3] * g[3];
-      for (int o = lanes_per_row / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(sub_mask, sq, o);
-      float acc = 0.f;
-      if (live) {
-        acc = p.state[t][row] + sq / float(p.D);
-        if (part == 0) p.state[t][row] = acc;
+    ulonglong2 a0[kU], a1[kU];
+    float4 w4[kU];
+    float* wptr[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const ulonglong2* a = reinterpret_cast<const ulonglong2*>(p.acc + size_t(i[u]) * p.D + part * 4);
+      wptr[u] = p.table[tr[u].x] + size_t(tr[u].y) * p.D + part * 4;
+      a0[u] = a1[u] = make_ulonglong2(0ull, 0ull);
+      w4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (live[u]) {
+        a0[u] = a[0]; a1[u] = a[1];
+        w4[u] = *reinterpret_cast<const float4*>(wptr[u]);
       }
-      const float inv = lr / (sqrtf(acc) + p.eps);
+    }
 #pragma unroll
-      for (int k = 0; k < 4; ++k) w[k] -= inv * g[k];
-    } else if (p.kind == 2) {
-      if (live) {
-        float4* mp = reinterpret_cast<float4*>(p.state[t] + size_t(row) * p.D + part * 4);
-        float4* vp = reinterpret_cast<float4*>(p.state[t] + p.state_stride[t] + size_t(row) * p.D + part * 4);
-        const float4 m4 = *mp, v4 = *vp;
-        float m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
+    for (int u = 0; u < kU; ++u) {
+      const int t = tr[u].x, row = tr[u].y;
+      float g[4];
+      g[0] = float(double(static_cast<long long>(a0[u].x)) * (1.0 / kFixScale));
+      g[1] = float(double(static_cast<long long>(a0[u].y)) * (1.0 / kFixScale));
+      g[2] = float(double(static_cast<long long>(a1[u].x)) * (1.0 / kFixScale));
+      g[3] = float(double(static_cast<long long>(a1[u].y)) * (1.0 / kFixScale));
+      if (live[u]) {
+        ulonglong2* a = reinterpret_cast<ulonglong2*>(p.acc + size_t(i[u]) * p.D + part * 4);
+        a[0] = make_ulonglong2(0ull, 0ull);
+        a[1] = make_ulonglong2(0ull, 0ull);
+        if (part == 0) p.flag[t][row] = 0;
+      }
+      float w[4] = {w4[u].x, w4[u].y, w4[u].z, w4[u].w};
+      if (p.weight_decay != 0.f) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          m[k] = p.beta1 * m[k] + (1.f - p.beta1) * g[k];
-          v[k] = p.beta2 * v[k] + (1.f - p.beta2) * g[k] * g[k];
-          w[k] -= (lr / bc1) * (m[k] / (sqrtf(v[k]) / sqrtf(bc2) + p.eps));
+        for (int k = 0; k < 4; ++k) g[k] += p.weight_decay * w[k];
+      }
+      if (p.kind == 1) {
+        // row-wise Adagrad: ONE accumulator per row, fed with the mean squared gradient of the row
+        float sq = g[0] * g[0] + g[1] * g[1] + g[2] * g[2] + g[3] * g[3];
+        for (int o = lanes_per_row / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(sub_mask, sq, o);
+        float acc = 0.f;
+        if (live[u]) {
+          acc = p.state[t][row] + sq / float(p.D);
+          if (part == 0) p.state[t][row] = acc;
         }
-        *mp = make_float4(m[0], m[1], m[2], m[3]);
-        *vp = make_float4(v[0], v[1], v[2], v[3]);
-      }
-    } else {
+        const float inv = lr / (sqrtf(acc) + p.eps);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) w[k] -= lr * g[k];
+        for (int k = 0; k < 4; ++k) w[k] -= inv * g[k];
+      } else if (p.kind == 2) {
+        if (live[u]) {
+          float4* mp = reinterpret_cast<float4*>(p.state[t] + size_t(row) * p.D + part * 4);
+          float4* vp = reinterpret_cast<float4*>(p.state[t] + p.state_stride[t] + size_t(row) * p.D + part * 4);
+          const float4 m4 = *mp, v4 = *vp;
+          float m[4] = {m4.x, m4.y, m4.z, m4.w}, v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            m[k] = p.beta1 * m[k] + (1.f - p.beta1) * g[k];
+            v[k] = p.beta2 * v[k] + (1.f - p.beta2) * g[k] * g[k];
+            w[k] -= (lr / bc1) * (m[k] / (sqrtf(v[k]) / sqrtf(bc2) + p.eps));
+          }
+          *mp = make_float4(m[0], m[1], m[2], m[3]);
+          *vp = make_float4(v[0], v[1], v[2], v[3]);
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) w[k] -= lr * g[k];
+      }
+      if (live[u]) *reinterpret_cast<float4*>(wptr[u]) = make_float4(w[0], w[1], w[2], w[3]);
     }
-    if (live) *reinterpret_cast<float4*>(wptr) = make_float4(w[0], w[1], w[2], w[3]);
   }
 }
 

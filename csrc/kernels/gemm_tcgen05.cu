@@ -873,24 +873,79 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
   }
 }
 
-// out[i] = partial[0][i] + partial[1][i] + ... in split order: the same bits whatever the schedule was
+// out[i] = partial[0][i] + partial[1][i] + ... in split order: the same bits whatever the schedule was.
+// Several weight matrices (all layers of a step) per launch; four split loads in flight per thread.
+constexpr int kReduceMaxSeg = 16;
+struct WgradReduceParams {
+  const float* partial[kReduceMaxSeg];
+  float* out[kReduceMaxSeg];
+  long long elems[kReduceMaxSeg];     // = stride between splits
+  int splits[kReduceMaxSeg];
+  int first_block[kReduceMaxSeg + 1];
+  int n_seg;
+};
+
 __global__ void __launch_bounds__(256)
-wgrad_reduce_kernel(const float* __restrict__ partial, long long stride, int splits, float* __restrict__ out,
-                    long long n4, long long n) {
-  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  for (long long i = tid; i < n4; i += (long long)gridDim.x * blockDim.x) {
+wgrad_reduce_kernel(const __grid_constant__ WgradReduceParams p) {
+  int seg = 0;
+  while (seg + 1 < p.n_seg && int(blockIdx.x) >= p.first_block[seg + 1]) ++seg;
+  const float* __restrict__ partial = p.partial[seg];
+  float* __restrict__ out = p.out[seg];
+  const long long n = p.elems[seg], stride = n;
+  const int splits = p.splits[seg];
+  const int nblk = p.first_block[seg + 1] - p.first_block[seg];
+  const long long tid = (blockIdx.x - p.first_block[seg]) * (long long)blockDim.x + threadIdx.x;
+  const long long nthreads = (long long)nblk * blockDim.x;
+  const bool vec = (n & 3) == 0 && (reinterpret_cast<uintptr_t>(partial) & 15) == 0 &&
+                   (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+  const long long n4 = vec ? n / 4 : 0;
+  for (long long i = tid; i < n4; i += nthreads) {
     float4 acc = *reinterpret_cast<const float4*>(partial + i * 4);
-    for (int s = 1; s < splits; ++s) {
+    int s = 1;
+    for (; s + 3 < splits; s += 4) {
+      const float4 v0 = *reinterpret_cast<const float4*>(partial + (s + 0) * stride + i * 4);
+      const float4 v1 = *reinterpret_cast<const float4*>(partial + (s + 1) * stride + i * 4);
+      const float4 v2 = *reinterpret_cast<const float4*>(partial + (s + 2) * stride + i * 4);
+      const float4 v3 = *reinterpret_cast<const float4*>(partial + (s + 3) * stride + i * 4);
+      acc.x += v0.x; acc.y += v0.y; acc.z += v0.z; acc.w += v0.w;
+      acc.x += v1.x; acc.y += v1.y; acc.z += v1.z; acc.w += v1.w;
+      acc.x += v2.x; acc.y += v2.y; acc.z += v2.z; acc.w += v2.w;
+      acc.x += v3.x; acc.y += v3.y; acc.z += v3.z; acc.w += v3.w;
+    }
+    for (; s < splits; ++s) {
       const float4 v = *reinterpret_cast<const float4*>(partial + s * stride + i * 4);
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
     }
     *reinterpret_cast<float4*>(out + i * 4) = acc;
   }
-  for (long long i = n4 * 4 + tid; i < n; i += (long long)gridDim.x * blockDim.x) {   // tail (n4 == 0 if unaligned)
+  for (long long i = n4 * 4 + tid; i < n; i += nthreads) {   // scalar route (unaligned or odd sizes)
     float acc = partial[i];
     for (int s = 1; s < splits; ++s) acc += partial[s * stride + i];
     out[i] = acc;
   }
+}
+
+static int launch_wgrad_reduce(const float* const* ws, const long long* elems, const int* splits, float* const* outs,
+                               int n, cudaStream_t stream) {
+  WgradReduceParams p;
+  memset(&p, 0, sizeof(p));
+  int blocks = 0, seg = 0;
+  for (int i = 0; i < n; ++i) {
+    if (splits[i] <= 1) continue;                 // a single split was stored straight into its output
+    p.partial[seg] = ws[i]; p.out[seg] = outs[i]; p.elems[seg] = elems[i]; p.splits[seg] = splits[i];
+    p.first_block[seg] = blocks;
+    long long b = (elems[i] / 4 + 255) / 256;
+    if (b < 1) b = 1;
+    if (b > 1024) b = 1024;
+    blocks += int(b);
+    ++seg;
+  }
+  if (seg == 0) return 0;
+  p.first_block[seg] = blocks;
+  p.n_seg = seg;
+  wgrad_reduce_kernel<<<blocks, 256, 0, stream>>>(p);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 static size_t gemm_tn_smem_bytes(int n_tile) {
@@ -1031,11 +1086,11 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
   return 0;
 }
 
-// Deterministic wgrad: out[Mw, Nw] (contiguous, ldo == Nw, Nw % 4 == 0) = G^T X, bit-identical run to run.
+// Deterministic wgrad: out[Mw, Nw] (contiguous, ldo == Nw) = G^T X, bit-identical run to run.
 // The batch is split over CTAs as above, but each split stores its tile into `ws` and the splits are added
 // in order; the number of splits is limited by ws_floats (>= Mw * Nw: one split, stored straight into out).
-int rdp_gemm_wgrad_det(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
-                       int Nw, float* ws, long long ws_floats, void* stream) {
+static int wgrad_det_impl(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
+                          int Nw, float* ws, long long ws_floats, int* splits_out, bool reduce_now, void* stream) {
   RDP_REQUIRE(rows > 0 && Mw > 0 && Nw > 0, "rdp_gemm_wgrad_det: empty problem");
   RDP_REQUIRE(ldg % 8 == 0 && ldx % 8 == 0, "rdp_gemm_wgrad_det: pitches must be multiples of 8");
   RDP_REQUIRE(ldo == Nw, "rdp_gemm_wgrad_det: out must be contiguous (ldo=%d Nw=%d)", ldo, Nw);
@@ -1071,17 +1126,32 @@ int rdp_gemm_wgrad_det(const void* g, int ldg, const void* x, int ldx, float* ou
   dim3 grid(splits, m_tiles, n_tiles);
   gemm_wgrad_kernel<<<grid, kWgradThreads, smem, cs>>>(tg, tx, p);
   RDP_CHECK_CUDA(cudaGetLastError());
-  if (splits > 1) {
-    // vector path only when every split's base stays 16-byte aligned
-    const bool vec = elems % 4 == 0 && (reinterpret_cast<uintptr_t>(ws) & 15) == 0 &&
-                     (reinterpret_cast<uintptr_t>(out) & 15) == 0;
-    const long long n4 = vec ? elems / 4 : 0;
-    int rgrid = int(((vec ? n4 : elems) + 255) / 256);
-    if (rgrid > num_sms() * 8) rgrid = num_sms() * 8;
-    wgrad_reduce_kernel<<<rgrid, 256, 0, cs>>>(ws, elems, splits, out, n4, elems);
-    RDP_CHECK_CUDA(cudaGetLastError());
+  if (splits_out != nullptr) *splits_out = splits;
+  if (reduce_now && splits > 1) {
+    const float* wsp = ws;
+    return launch_wgrad_reduce(&wsp, &elems, &splits, &out, 1, cs);
   }
   return 0;
+}
+
+int rdp_gemm_wgrad_det(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
+                       int Nw, float* ws, long long ws_floats, void* stream) {
+  return wgrad_det_impl(g, ldg, x, ldx, out, ldo, rows, Mw, Nw, ws, ws_floats, nullptr, true, stream);
+}
+
+// Two-phase form for a whole backward pass: every layer stores its split tiles into its own scratch
+// (rdp_gemm_wgrad_partial; *splits_out = number of splits, 1 = already stored into out), then ONE launch adds the
+// splits of all layers in order (rdp_wgrad_reduce_many; up to 16 layers per launch).
+int rdp_gemm_wgrad_partial(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
+                           int Nw, float* ws, long long ws_floats, int* splits_out, void* stream) {
+  return wgrad_det_impl(g, ldg, x, ldx, out, ldo, rows, Mw, Nw, ws, ws_floats, splits_out, false, stream);
+}
+
+int rdp_wgrad_reduce_many(const float* const* ws, const long long* elems, const int* splits, float* const* outs,
+                          int n, void* stream) {
+  RDP_REQUIRE(n >= 0 && n <= kReduceMaxSeg, "rdp_wgrad_reduce_many: at most %d matrices per call (got %d)",
+              kReduceMaxSeg, n);
+  return launch_wgrad_reduce(ws, elems, splits, outs, n, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -128,6 +128,54 @@ __global__ void __launch_bounds__(256) cast_weight_tiled_kernel(const float* __r
   }
 }
 
+// All layers of a model in ONE launch: weights as above plus the fp32 bias copied into its padded operand.
+// A step of the hybrid DLRM refreshes 8 layers: 8 cast launches + 8 bias copies become one kernel.
+constexpr int kCastMaxLayers = 16;
+struct CastManyParams {
+  const float* w[kCastMaxLayers];
+  __nv_bfloat16* out[kCastMaxLayers];
+  __nv_bfloat16* out_t[kCastMaxLayers];
+  const float* bias[kCastMaxLayers];
+  float* bias_out[kCastMaxLayers];
+  int N[kCastMaxLayers], K[kCastMaxLayers], ldo[kCastMaxLayers], ldt[kCastMaxLayers];
+  int first_block[kCastMaxLayers + 1];
+  int n_layers;
+};
+
+__global__ void __launch_bounds__(256) cast_weight_many_kernel(const __grid_constant__ CastManyParams p) {
+  __shared__ float tile[32][33];
+  int l = 0;
+  while (l + 1 < p.n_layers && int(blockIdx.x) >= p.first_block[l + 1]) ++l;
+  const int N = p.N[l], K = p.K[l], ldo = p.ldo[l], ldt = p.ldt[l];
+  const int kb = (K + 31) / 32;
+  const int rel = blockIdx.x - p.first_block[l];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int k0 = (rel % kb) * 32, n0 = (rel / kb) * 32;
+  const float* __restrict__ w = p.w[l];
+  __nv_bfloat16* __restrict__ out = p.out[l];
+  __nv_bfloat16* __restrict__ out_t = p.out_t[l];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int n = n0 + ty + r * 8, k = k0 + tx;
+    float v = 0.f;
+    if (n < N && k < K) {
+      v = w[size_t(n) * K + k];
+      out[size_t(n) * ldo + k] = __float2bfloat16_rn(v);
+    }
+    tile[ty + r * 8][tx] = v;
+  }
+  __syncthreads();
+  if (out_t != nullptr) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int k = k0 + ty + r * 8, n = n0 + tx;
+      if (k < K && n < N) out_t[size_t(k) * ldt + n] = __float2bfloat16_rn(tile[tx][ty + r * 8]);
+    }
+  }
+  if (k0 == 0 && p.bias[l] != nullptr && threadIdx.x < 32 && n0 + int(threadIdx.x) < N)
+    p.bias_out[l][n0 + threadIdx.x] = p.bias[l][n0 + threadIdx.x];
+}
+
 // contiguous fp32 -> bf16, 8 elements per thread (no transposed copy)
 __global__ void cast_bf16_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ out, int64_t n8) {
   for (int64_t i = blockIdx.x * int64_t(blockDim.x) + threadIdx.x; i < n8; i += int64_t(gridDim.x) * blockDim.x) {
@@ -665,6 +713,29 @@ int rdp_cast_weight(const float* w, int N, int K, void* out, int ldo, void* out_
   }
   cast_weight_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       w, N, K, static_cast<__nv_bfloat16*>(out), ldo, static_cast<__nv_bfloat16*>(out_t), ldt);
+  RDP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int rdp_cast_weight_many(const float* const* w, const int* N, const int* K, void* const* out, const int* ldo,
+                         void* const* out_t, const int* ldt, const float* const* bias, float* const* bias_out,
+                         int n_layers, void* stream) {
+  RDP_REQUIRE(n_layers >= 1 && n_layers <= kCastMaxLayers, "rdp_cast_weight_many: 1..%d layers (got %d)",
+              kCastMaxLayers, n_layers);
+  CastManyParams p;
+  memset(&p, 0, sizeof(p));
+  int blocks = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    p.w[l] = w[l]; p.out[l] = static_cast<__nv_bfloat16*>(out[l]);
+    p.out_t[l] = out_t ? static_cast<__nv_bfloat16*>(out_t[l]) : nullptr;
+    p.bias[l] = bias ? bias[l] : nullptr; p.bias_out[l] = bias_out ? bias_out[l] : nullptr;
+    p.N[l] = N[l]; p.K[l] = K[l]; p.ldo[l] = ldo[l]; p.ldt[l] = ldt ? ldt[l] : 0;
+    p.first_block[l] = blocks;
+    blocks += ((K[l] + 31) / 32) * ((N[l] + 31) / 32);
+  }
+  p.first_block[n_layers] = blocks;
+  p.n_layers = n_layers;
+  cast_weight_many_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

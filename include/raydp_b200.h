@@ -70,6 +70,11 @@ int rdp_bn_fold(const float* stats, float count, const float* gamma, const float
                 float* a, float* c, float* mean, float* rstd, const float* w, const float* b, int N, int K,
                 void* w_folded, int ldw, void* w_folded_t, int ldwt, float* b_folded, void* stream);
 int rdp_cast_weight(const float* w, int N, int K, void* out, int ldo, void* out_t, int ldt, void* stream);
+// The same for up to 16 layers in one launch; bias[l] (fp32, N[l]) is copied to bias_out[l] (padded operand) too.
+// out_t / ldt / bias / bias_out may be null.
+int rdp_cast_weight_many(const float* const* w, const int* N, const int* K, void* const* out, const int* ldo,
+                         void* const* out_t, const int* ldt, const float* const* bias, float* const* bias_out,
+                         int n_layers, void* stream);
 int rdp_bn_relu_bwd(const void* dy, const void* z, void* dpre, int B, int N, int ld, const float* stats2,
                     const float* mean, const float* rstd, const float* a, float* dgamma, float* dbeta,
                     float* dbias, int has_bn, void* stream);
@@ -271,8 +276,14 @@ int rdp_embedding_bag_bwd(float* const* tables, const int* slots, const int* col
 // matrices src[i] ([rows, ld[i]]) by a fixed summation tree (bias gradients); up to 16 matrices per launch.
 int rdp_gemm_wgrad_det(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
                        int Nw, float* ws, long long ws_floats, void* stream);
-// ws / counters: scratch for the two-level tree (rows are cut into up to 32 chunks; ws holds chunks x groups x 64
-// floats with groups = sum ceil(n[i] / 64); the first `groups` words of counters are zero on entry and on exit);
+// Two-phase form: rdp_gemm_wgrad_partial stores the split tiles of one layer (*splits_out = splits; 1 means the
+// tile went straight into out), rdp_wgrad_reduce_many adds the splits of up to 16 layers in one launch.
+int rdp_gemm_wgrad_partial(const void* g, int ldg, const void* x, int ldx, float* out, int ldo, int rows, int Mw,
+                           int Nw, float* ws, long long ws_floats, int* splits_out, void* stream);
+int rdp_wgrad_reduce_many(const float* const* ws, const long long* elems, const int* splits, float* const* outs,
+                          int n, void* stream);
+// ws / counters: scratch for the two-level tree (rows are cut into up to 32 chunks; ws holds chunks x groups x 128
+// floats with groups = sum ceil(n[i] / 128); the first `groups` words of counters are zero on entry and on exit);
 // without scratch one CTA per 64 columns walks all rows.
 int rdp_colsum_ordered(const void* const* src, const int* ld, const int* n, float* const* out, int n_seg, int rows,
                        float* ws, long long ws_floats, unsigned int* counters, int n_counters, void* stream);

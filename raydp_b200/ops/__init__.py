@@ -111,6 +111,30 @@ def gemm_wgrad_det(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, ws: Opti
     return out
 
 
+def gemm_wgrad_partial(g: torch.Tensor, x: torch.Tensor, out: torch.Tensor, ws: torch.Tensor, *,
+                       mw: Optional[int] = None, nw: Optional[int] = None) -> int:
+    """First phase of the deterministic wgrad: split tiles of ``g[:, :Mw].T @ x[:, :Nw]`` stored into ``ws``;
+    returns the number of splits (1: the product is already in ``out``).  See :func:`wgrad_reduce_many`."""
+    rows = g.shape[0]
+    Mw = mw if mw is not None else g.shape[1]
+    Nw = nw if nw is not None else x.shape[1]
+    splits = ctypes.c_int(0)
+    _check(lib().rdp_gemm_wgrad_partial(_ptr(g), _pitch(g), _ptr(x), _pitch(x), _ptr(out), _pitch(out), rows, Mw, Nw,
+                                        _ptr(ws), ws.numel(), ctypes.byref(splits), _stream()))
+    return splits.value
+
+
+def wgrad_reduce_many(wss: Sequence[torch.Tensor], splits: Sequence[int], outs: Sequence[torch.Tensor]) -> None:
+    """Second phase: ``outs[l] = sum over splits of wss[l]`` in split order, all layers in one launch."""
+    for i in range(0, len(outs), 16):
+        w, s_, o = wss[i:i + 16], splits[i:i + 16], outs[i:i + 16]
+        if all(v <= 1 for v in s_):
+            continue
+        elems = (ctypes.c_longlong * len(o))(*[t.numel() for t in o])
+        _check(lib().rdp_wgrad_reduce_many(_vp_arr([t.data_ptr() for t in w]), elems, _i_arr(s_),
+                                           _vp_arr([t.data_ptr() for t in o]), len(o), _stream()))
+
+
 def colsum_ordered(mats: Sequence[torch.Tensor], widths: Sequence[int], outs: Sequence[torch.Tensor],
                    ws: Optional[torch.Tensor] = None, counters: Optional[torch.Tensor] = None) -> None:
     """``outs[i][:widths[i]] = mats[i][:, :widths[i]].sum(0)`` with a fixed summation order (bias gradients of a
@@ -168,6 +192,18 @@ def cast_weight(w: torch.Tensor, out: torch.Tensor, out_t: Optional[torch.Tensor
     N, K = w.shape
     _check(lib().rdp_cast_weight(_ptr(w), N, K, _ptr(out), _pitch(out), _ptr(out_t),
                                  _pitch(out_t) if out_t is not None else 0, _stream()))
+
+
+def cast_weight_many(ws, outs, outs_t, biases, bias_outs) -> None:
+    """fp32 weights ``ws[l]`` [N, K] -> bf16 operands ``outs[l]`` (and transposes ``outs_t[l]``), biases copied into
+    their padded operands, for up to 16 layers per launch."""
+    for i in range(0, len(ws), 16):
+        w, o, t, b, bo = ws[i:i + 16], outs[i:i + 16], outs_t[i:i + 16], biases[i:i + 16], bias_outs[i:i + 16]
+        _check(lib().rdp_cast_weight_many(_vp_arr([x.data_ptr() for x in w]), _i_arr([x.shape[0] for x in w]),
+                                          _i_arr([x.shape[1] for x in w]), _vp_arr([x.data_ptr() for x in o]),
+                                          _i_arr([_pitch(x) for x in o]), _vp_arr([x.data_ptr() for x in t]),
+                                          _i_arr([_pitch(x) for x in t]), _vp_arr([x.data_ptr() for x in b]),
+                                          _vp_arr([x.data_ptr() for x in bo]), len(w), _stream()))
 
 
 def bn_relu_bwd(dy, z, dpre, stats2, mean, rstd, a, dgamma, dbeta, dbias, has_bn: bool = True) -> None:

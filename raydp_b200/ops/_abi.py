@@ -72,8 +72,12 @@ SIGNATURES.update({
                                   VP, C.c_longlong, C.POINTER(VP), VP, VP, C.POINTER(VP), C.POINTER(I64),
                                   I, F, F, F, F, F, VP, VP, VP]),
     "rdp_gemm_wgrad_det": (I, [VP, I, VP, I, VP, I, I, I, I, VP, C.c_longlong, VP]),
+    "rdp_gemm_wgrad_partial": (I, [VP, I, VP, I, VP, I, I, I, I, VP, C.c_longlong, C.POINTER(I), VP]),
+    "rdp_wgrad_reduce_many": (I, [C.POINTER(VP), C.POINTER(C.c_longlong), C.POINTER(I), C.POINTER(VP), I, VP]),
     "rdp_colsum_ordered": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), C.POINTER(VP), I, I, VP, C.c_longlong, VP, I,
                                VP]),
+    "rdp_cast_weight_many": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), C.POINTER(VP), C.POINTER(I), C.POINTER(VP),
+                                 C.POINTER(I), C.POINTER(VP), C.POINTER(VP), I, VP]),
     "rdp_dot_interaction_fwd": (I, [VP, VP, I, I, I, I, VP]),
     "rdp_dot_interaction_bwd": (I, [VP, VP, VP, I, I, I, I, VP]),
     "rdp_bce_logits": (I, [VP, I, VP, VP, I, I, VP, I, F, VP, VP]),

@@ -117,10 +117,21 @@ class FusedDLRM:
         self.stats = [torch.zeros(2, max(self.npad[i], 64), **f32) for i in range(len(self.layers))]
         self.stats_bottom_last = torch.zeros(2, max(D, 8), **f32)
         self.accum = torch.zeros(8, **f32)
-        biggest = max(n * k for _, _, k, n in self.layers)
-        self.wgrad_ws = torch.empty(max(biggest, min(16 * biggest, 16 << 20)), **f32) if self.deterministic else None
-        groups = sum((n + 63) // 64 for _, _, _, n in self.layers) + 1
-        self.colsum_ws = torch.empty(32 * groups * 64, **f32) if self.deterministic else None
+        # deterministic wgrad: per-layer scratch for the batch splits (at most 8 per layer, 192 MB in total);
+        # the splits of all layers are added in order by one launch at the end of the backward pass
+        self.wgrad_ws: List[torch.Tensor] = []
+        self._wgrad_splits = [1] * len(self.layers)
+        if self.deterministic:
+            mult = 8
+            while mult > 1 and sum(n * k for _, _, k, n in self.layers) * mult > (48 << 20):
+                mult //= 2
+            pool = torch.empty(sum((n * k * mult + 3) // 4 * 4 for _, _, k, n in self.layers), **f32)
+            off = 0
+            for _, _, k, n in self.layers:
+                self.wgrad_ws.append(pool[off:off + n * k * mult])
+                off += (n * k * mult + 3) // 4 * 4
+        groups = sum((n + 127) // 128 for _, _, _, n in self.layers) + 1
+        self.colsum_ws = torch.empty(32 * groups * 128, **f32) if self.deterministic else None
         self.colsum_counters = torch.zeros(groups, dtype=torch.int32, device=device) if self.deterministic else None
         self.ones32 = torch.ones(D, **f32)
         self.zeros32 = torch.zeros(D, **f32)
@@ -172,15 +183,16 @@ class FusedDLRM:
 
     # ------------------------------------------------------------------ pieces of a step
     def _refresh_weights(self) -> None:
-        for li in range(len(self.layers)):
-            _, _, k, n = self.layers[li]
-            ops.cast_weight(self.weight(li), self.w_bf[li], self.w_t[li])
-            self.bias_pad[li][:n].copy_(self.bias(li))
+        """bf16 GEMM operands (plain and transposed) and padded biases of every layer, one launch."""
+        L = range(len(self.layers))
+        ops.cast_weight_many([self.weight(li) for li in L], self.w_bf, self.w_t, [self.bias(li) for li in L],
+                             self.bias_pad)
 
     def _wgrad(self, g: torch.Tensor, inp: torch.Tensor, li: int) -> None:
         _, _, k, n = self.layers[li]
         if self.deterministic:
-            ops.gemm_wgrad_det(g, inp, self.weight(li, True), self.wgrad_ws, mw=n, nw=k)
+            self._wgrad_splits[li] = ops.gemm_wgrad_partial(g, inp, self.weight(li, True), self.wgrad_ws[li],
+                                                            mw=n, nw=k)
         else:
             ops.gemm_wgrad(g, inp, self.weight(li, True), mw=n, nw=k)
 
@@ -306,6 +318,8 @@ class FusedDLRM:
                 g = self.dact[prev][:B]
         if self.deterministic:
             self._bias_grads(range(0, last), B, extra=(dy, self.D, self.bias(last, True)))
+            L = range(len(self.layers))          # top and bottom layers: one ordered reduction for all of them
+            ops.wgrad_reduce_many(self.wgrad_ws, self._wgrad_splits, [self.weight(li, True) for li in L])
 
     def sgd(self, lr: float, scale: float = 1.0, momentum: float = 0.0, weight_decay: float = 0.0,
             lr_dev: Optional[torch.Tensor] = None, step_dev: Optional[torch.Tensor] = None) -> None:

@@ -27,19 +27,24 @@ def _pack_dense(dense):
     return out
 
 
-def test_dot_interaction_matches_bmm_tril():
+@pytest.mark.parametrize("S,D", [(27, 32), (7, 32), (32, 32), (27, 16)])
+def test_dot_interaction_matches_bmm_tril(S, D):
+    """D = 32 runs on the tensor cores (mma.sync + ldmatrix, one warp per sample); other widths on the scalar
+    kernels.  Both against torch.bmm + tril gather in fp32."""
     from raydp_b200 import ops
-    B, S, D = 777, 27, 32
+    B = 777
+    pairs = S * (S - 1) // 2
+    ld = (D + pairs + 1 + 7) // 8 * 8
     feats = (torch.randn(B, S, D, device="cuda") * 0.5).to(torch.bfloat16)
-    out = torch.empty(B, 384, device="cuda", dtype=torch.bfloat16)
+    out = torch.full((B, ld), 7.0, device="cuda", dtype=torch.bfloat16)
     ops.dot_interaction_fwd(feats, out)
     f = feats.float().requires_grad_(True)
     inter = torch.bmm(f, f.transpose(1, 2))
     li, lj = torch.tril_indices(S, S, offset=-1)
-    ref = torch.cat([f[:, 0, :], inter[:, li, lj], torch.zeros(B, 1, device="cuda")], 1)
-    assert _rel(out, ref.detach()) < 1e-2 and (out[:, 383] == 0).all()
-    dout = (torch.randn(B, 384, device="cuda") * 0.1).to(torch.bfloat16)
-    dfeats = torch.empty_like(feats)
+    ref = torch.cat([f[:, 0, :], inter[:, li, lj], torch.zeros(B, ld - D - pairs, device="cuda")], 1)
+    assert _rel(out, ref.detach()) < 1e-2 and (out[:, D + pairs:] == 0).all()
+    dout = (torch.randn(B, ld, device="cuda") * 0.1).to(torch.bfloat16)
+    dfeats = torch.full_like(feats, 3.0)
     ops.dot_interaction_bwd(feats, dout, dfeats)
     ref.backward(dout.float())
     assert _rel(dfeats, f.grad) < 1.5e-2

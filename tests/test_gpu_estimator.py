@@ -128,6 +128,52 @@ def test_dlrm_estimator_single_gpu(ray_cluster):
     assert acc > 0.5
 
 
+def test_dlrm_estimator_with_momentum_is_bit_reproducible(ray_cluster):
+    """Two fits from the same initialisation (SGD momentum 0.9 on the dense layers, row-wise Adagrad on the
+    tables, a multi-hot table, a ragged last batch) write the same BITS into model.pt: weight gradients are
+    ordered split sums, bias gradients ordered column sums, duplicate table rows are combined in fixed point."""
+    import numpy as np
+    import pyarrow as pa
+    import raydp_b200 as raydp  # noqa: F401
+    from raydp_b200 import data as rdata
+    from raydp_b200.models import DLRM
+    from raydp_b200.torch import TorchEstimator
+    rng = np.random.default_rng(1)
+    n, sizes, bags = 5000, [11, 300, 57, 1000, 8], [1, 3, 1, 1, 2]
+    cols = {f"d{i}": rng.standard_normal(n).astype(np.float32) for i in range(13)}
+    names = []
+    for t, (s, L) in enumerate(zip(sizes, bags)):
+        for l in range(L):
+            v = rng.integers(0, s, n).astype(np.int64)
+            if l > 0:
+                v[rng.random(n) < 0.3] = -1                      # ragged bags
+            cols[f"c{t}_{l}"] = v
+            names.append(f"c{t}_{l}")
+    logit = cols["d0"] * 1.5 - cols["d1"] + (cols["c0_0"] % 2) * 2.0 - 1.0
+    cols["label"] = (rng.random(n) < 1 / (1 + np.exp(-logit))).astype(np.float32)
+    ds = rdata.from_arrow([pa.table({k: v[i::2] for k, v in cols.items()}) for i in range(2)])
+    features = [f"d{i}" for i in range(13)] + names
+    states = []
+    for run in range(2):
+        torch.manual_seed(0)
+        model = DLRM(13, sizes, 32, bottom=(64, 32), top=(128, 64, 1), sparse_grad=False, bag_sizes=bags,
+                     pooling="mean")
+        est = TorchEstimator(num_workers=1, resources_per_worker={"GPU": 1}, model=model,
+                             optimizer=torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9),
+                             loss=nn.BCEWithLogitsLoss(), feature_columns=features,
+                             feature_types=[torch.float] * 13 + [torch.long] * len(names), label_column="label",
+                             label_type=torch.float, batch_size=512, num_epochs=4, shuffle=False, drop_last=False,
+                             metrics_name=["Accuracy"], embedding_optimizer="adagrad")
+        est.fit(ds)
+        train = [h for h in est.results.metrics_history if "train_loss" in h]
+        assert train[0]["engine"] == "fused-dlrm" and train[-1]["train_loss"] < train[0]["train_loss"]
+        states.append(torch.load(os.path.join(est.results.checkpoint.path, "model.pt"), weights_only=True))
+    assert states[0].keys() == states[1].keys()
+    for k in states[0]:
+        assert torch.equal(states[0][k], states[1][k]), k
+    assert not torch.equal(states[0]["embeddings.1.weight"], model.embeddings[1].weight.detach().cpu())   # it trained
+
+
 @pytest.mark.multigpu
 def test_rank_killed_mid_training_is_detected_and_the_group_restarts(ray_cluster, tmp_path):
     """Failure path of the peer-memory collectives: rank 1 dies in the middle of an epoch.  Rank 0's next
