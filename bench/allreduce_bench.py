@@ -111,7 +111,7 @@ def main():
                     nv.allreduce_()
                     torch.cuda.synchronize()
                     err = (nv.buffer - refq).abs().max().item()
-                    assert err <= tol, ("nvls bf16", n, rep, err)
+                    assert err <= 2 * tol, ("nvls bf16", n, rep, err)     # the switch returns bf16: up to 1 ulp
                 nv.close()
             continue
         iters = 200 if n <= (1 << 20) else (50 if n <= (1 << 24) else 10)
