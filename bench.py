@@ -71,6 +71,9 @@ def parse_args():
     ap.add_argument("--no-actor", action="store_true", help="skip the init_spark -> fit_on_spark actor-mode run")
     ap.add_argument("--no-extras", action="store_true", help="skip the DLRM / BigMLP / collective records")
     ap.add_argument("--lean", action="store_true", help="only the two headline numbers (device + e2e)")
+    ap.add_argument("--budget-s", type=float, default=float(os.environ.get("RAYDP_B200_BENCH_BUDGET_S", 540)),
+                    help="wall-clock budget for the auxiliary phases (stand-ins, replica check, actor run, extras): a "
+                         "phase that would not fit is skipped and listed under 'skipped'")
     return ap.parse_args()
 
 
@@ -316,6 +319,7 @@ def run_actor_e2e(args, world):
     from raydp_b200.sql.functions import col, rand
     from raydp_b200.torch import TorchEstimator
     os.environ["RAYDP_B200_SPMD"] = "0"
+    os.environ.setdefault("RAYDP_B200_PG_TIMEOUT_S", "120")     # a worker group that cannot form fails in 2 minutes
     runtime.shutdown()
     n_exec = max(2, min(8, 2 * world))
     runtime.init(num_cpus=n_exec + world + 2, num_gpus=world)
@@ -443,6 +447,9 @@ def run_standin(args, rank, world, local):
                     "d2h_bytes_per_step": 4}}
 
 
+_T0 = 0.0
+
+
 def _guard(errors, name, fn, *a, **kw):
     """Auxiliary phases must never cost the headline line: record the failure and go on."""
     try:
@@ -456,6 +463,8 @@ def _guard(errors, name, fn, *a, **kw):
 
 
 def main():
+    global _T0
+    _T0 = time.perf_counter()
     args = parse_args()
     if args.impl == "reference":
         print(json.dumps({"impl": "reference", "unavailable":
@@ -490,35 +499,39 @@ def main():
                 "clocks": dev["clocks"], "e2e": e2e, "gpu_launches": dev["gpu_launches"],
                 "final_loss": dev["final_loss"], "engine": dev["engine"]}
         torch.cuda.empty_cache()
-        if not args.no_standin:
-            standin = {"device_eager": _guard(errors, "standin_device_eager", run_standin_device, args, rank, world, local)}
-            if not args.no_compile:
-                standin["device_compiled"] = _guard(errors, "standin_device_compiled", run_standin_device,
-                                                    args, rank, world, local, compiled=True)
-            se = _guard(errors, "standin_e2e", run_standin, args, rank, world, local)
-            standin["e2e"] = {k: se[k] for k in ("ms_per_step", "value", "clocks", "what")} if se else None
-            line["standin"] = standin
-            dev_best = max([s["value"] for s in (standin.get("device_eager"), standin.get("device_compiled")) if s],
-                           default=None)
-            detail = {"device": dev["value"] / dev_best if dev_best else None,
-                      "e2e": (e2e["value"] / standin["e2e"]["value"]) if (e2e and standin["e2e"]) else None,
-                      "note": "ours / reference-equivalent stand-in on stock torch+NCCL+cuBLAS, same invocation; "
-                              "the reference itself publishes no number and cannot be installed here"}
-            line["vs_baseline"] = detail["device"]
-            line["vs_baseline_detail"] = detail
-            torch.cuda.empty_cache()
-        if world > 1:
-            line["replica_check"] = _guard(errors, "replica_check", run_replica_check, args, rank, world, local)
-        if not args.no_extras:
-            sys.path.insert(0, os.path.join(ROOT, "bench"))
-            import extras
-            extra = {"dlrm": _guard(errors, "extra_dlrm", extras.dlrm_record, rank, world, local),
-                     "bigmlp": _guard(errors, "extra_bigmlp", extras.bigmlp_record, rank, world, local)}
+        # ---- auxiliary phases, most important first, inside a wall-clock budget (same decision on every rank)
+        t_start = _T0
+        phase_s, skipped = {}, []
+
+        def fits(name, estimate):
+            elapsed = time.perf_counter() - t_start
             if world > 1:
-                extra["allreduce"] = _guard(errors, "extra_allreduce", extras.allreduce_record, rank, world, local)
-                extra["alltoall"] = _guard(errors, "extra_alltoall", extras.alltoall_record, rank, world, local)
-            line["extra"] = extra
-        if not args.no_actor:
+                import torch.distributed as dist
+                t = torch.tensor([elapsed], device=torch.device("cuda", local))
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                elapsed = float(t.item())
+            if elapsed + estimate > args.budget_s:
+                skipped.append(name)
+                return False
+            return True
+
+        def phase(name, fn, *a, **kw):
+            t0 = time.perf_counter()
+            out = _guard(errors, name, fn, *a, **kw)
+            phase_s[name] = round(time.perf_counter() - t0, 1)
+            torch.cuda.empty_cache()
+            return out
+
+        standin = {}
+        if not args.no_standin:
+            if fits("standin_device_eager", 20):
+                standin["device_eager"] = phase("standin_device_eager", run_standin_device, args, rank, world, local)
+            if fits("standin_e2e", 40):
+                se = phase("standin_e2e", run_standin, args, rank, world, local)
+                standin["e2e"] = {k: se[k] for k in ("ms_per_step", "value", "clocks", "what")} if se else None
+        if world > 1 and fits("replica_check", 15):
+            line["replica_check"] = phase("replica_check", run_replica_check, args, rank, world, local)
+        if not args.no_actor and fits("e2e_actor", 90):
             # rank 0 drives an actor-mode fit on all GPUs; the other ranks wait on the host (no kernel
             # of theirs may spin on the GPUs the actors are using)
             store = None
@@ -529,12 +542,41 @@ def main():
                 torch.cuda.synchronize()
                 store = dist.distributed_c10d._get_default_store()
             if rank == 0:
-                line["e2e_actor"] = _guard(errors, "e2e_actor", run_actor_e2e, args, world)
+                line["e2e_actor"] = phase("e2e_actor", run_actor_e2e, args, world)
                 if store is not None:
                     store.set("bench_actor_phase_done", "1")
             elif store is not None:
                 import datetime
-                store.wait(["bench_actor_phase_done"], datetime.timedelta(minutes=25))
+                store.wait(["bench_actor_phase_done"], datetime.timedelta(minutes=12))
+        if not args.no_extras:
+            sys.path.insert(0, os.path.join(ROOT, "bench"))
+            import extras
+            extra = {}
+            if fits("extra_dlrm", 40):
+                extra["dlrm"] = phase("extra_dlrm", extras.dlrm_record, rank, world, local)
+            if world > 1 and fits("extra_allreduce", 40):
+                extra["allreduce"] = phase("extra_allreduce", extras.allreduce_record, rank, world, local)
+            if world > 1 and fits("extra_alltoall", 20):
+                extra["alltoall"] = phase("extra_alltoall", extras.alltoall_record, rank, world, local)
+            if fits("extra_bigmlp", 150):
+                extra["bigmlp"] = phase("extra_bigmlp", extras.bigmlp_record, rank, world, local)
+            line["extra"] = extra
+        if not args.no_standin and not args.no_compile and fits("standin_device_compiled", 90):
+            standin["device_compiled"] = phase("standin_device_compiled", run_standin_device, args, rank, world, local,
+                                               compiled=True)
+        if standin:
+            line["standin"] = standin
+            dev_best = max([s["value"] for s in (standin.get("device_eager"), standin.get("device_compiled")) if s],
+                           default=None)
+            detail = {"device": dev["value"] / dev_best if dev_best else None,
+                      "e2e": (e2e["value"] / standin["e2e"]["value"]) if (e2e and standin.get("e2e")) else None,
+                      "note": "ours / reference-equivalent stand-in on stock torch+NCCL+cuBLAS, same invocation; "
+                              "the reference itself publishes no number and cannot be installed here"}
+            line["vs_baseline"] = detail["device"]
+            line["vs_baseline_detail"] = detail
+        line["phase_seconds"] = phase_s
+        if skipped:
+            line["skipped"] = {"phases": skipped, "why": f"auxiliary-phase budget of {args.budget_s:.0f} s (--budget-s)"}
         if errors:
             line["errors"] = errors
     if rank == 0:

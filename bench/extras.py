@@ -191,6 +191,13 @@ def allreduce_record(rank: int, world: int, local: int, sizes: List[int] = (1638
                 continue
             row[f"{algo}_us"] = _timed(lambda i: red.allreduce_(), iters, 5, world, local)["ms"] * 1e3
             red.close()
+        if n >= (1 << 22):
+            # registered mode: the gradient is produced in the symmetric send buffer, no copy-in / copy-out
+            # (what FusedDataParallel's buckets use below 4 ranks)
+            red = P2PReducer(x.clone(), dev, algo="two_shot")
+            red.next_send_buffer().copy_(x)
+            row["two_shot_registered_us"] = _timed(lambda i: red.allreduce_registered_(), iters, 5, world, local)["ms"] * 1e3
+            red.close()
         if use_nvls and n >= (1 << 16):
             nv = NvlsReducer(n, dev)
             nv.buffer.copy_(x)

@@ -78,6 +78,14 @@ def run_worker(train_func: Callable, config: Optional[dict], rank: int, world: i
         bind_to_gpu(index, local_rank if local_rank < world else rank % max(1, world), world)
     created_pg = False
     if init_pg and world > 1 and not dist.is_initialized():
+        # A driver that itself runs under torchrun hands its environment down to the actors: with
+        # TORCHELASTIC_USE_AGENT_STORE set, env:// rendezvous makes EVERY rank a client of the launcher's store at
+        # MASTER_ADDR:MASTER_PORT -- ours is a fresh port nobody serves, so the group would wait out the store
+        # timeout.  This group is ours: rank 0 serves the store.
+        for var in ("TORCHELASTIC_USE_AGENT_STORE", "TORCHELASTIC_RUN_ID", "TORCHELASTIC_RESTART_COUNT",
+                    "TORCHELASTIC_MAX_RESTARTS", "TORCHELASTIC_ERROR_FILE", "GROUP_RANK", "ROLE_RANK",
+                    "ROLE_WORLD_SIZE", "GROUP_WORLD_SIZE", "LOCAL_WORLD_SIZE"):
+            os.environ.pop(var, None)
         os.environ["MASTER_ADDR"] = master_addr
         os.environ["MASTER_PORT"] = str(master_port)
         os.environ["RANK"], os.environ["WORLD_SIZE"] = str(rank), str(world)
@@ -85,6 +93,10 @@ def run_worker(train_func: Callable, config: Optional[dict], rank: int, world: i
         kwargs = {}
         if backend == "nccl":
             kwargs["device_id"] = device
+        pg_timeout = os.environ.get("RAYDP_B200_PG_TIMEOUT_S")
+        if pg_timeout:
+            import datetime
+            kwargs["timeout"] = datetime.timedelta(seconds=float(pg_timeout))
         dist.init_process_group(backend=backend, rank=rank, world_size=world, **kwargs)
         created_pg = True
     sess = TrainSession(rank, world, local_rank, world, shards, device, run_name, storage_dir, backend)
