@@ -1,3 +1,4 @@
+#include <stdlib.h>
 // Host-side plumbing shared by all kernels: error string, device init, TMA descriptor encode.
 #include "common.cuh"
 
@@ -18,6 +19,15 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("RAYDP_B200_PDL");
+    on = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
 
 static int g_num_sms[64] = {0};
 int num_sms() {

@@ -9,6 +9,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
+#include <string.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -39,6 +40,33 @@ const char* get_error();
   } while (0)
 
 int num_sms();      // of the CURRENT device (cached per device)
+
+// ---- programmatic dependent launch ------------------------------------------------------------------
+// A training step is ~25 short kernels back to back inside one CUDA graph; each pays launch latency, a prologue
+// (barrier init, TMEM allocation, descriptor prefetch) and a tail (last stores draining) -- ~7 us of a 25 us GEMM
+// (profiles/gemm_tile_timeline.md).  Kernels launched with launch_pdl() may START while their predecessor in the
+// stream is still finishing: everything before pdl_wait() overlaps the predecessor's tail, pdl_wait() returns once
+// the predecessor has completed and its memory is visible.  Rules for a kernel launched this way:
+//   * no global-memory access (loads, stores, TMA, atomics) before pdl_wait(), by any thread;
+//   * pdl_trigger() early, so the NEXT kernel can do the same.
+// Without the launch attribute both instructions are no-ops.  RAYDP_B200_PDL=0 launches everything normally.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+
+template <typename Kernel, typename... Args>
+inline cudaError_t launch_pdl(Kernel kernel, dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr;
+  memset(&attr, 0, sizeof(attr));
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: a process that
 // launches on a second GPU must set it there too.  `done` is one bit per device ordinal.

@@ -386,19 +386,12 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  if (bn_bwd) {
-    for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
-      s_coef[i] = p.bn_alpha[i];
-      s_coef[kBnCoefCols + i] = p.bn_beta[i];
-      s_coef[2 * kBnCoefCols + i] = p.bn_delta[i];
-    }
-  }
+  pdl_trigger();                     // the next kernel of the stream may start its own prologue
   if (kStats) {
     uint32_t* o32 = reinterpret_cast<uint32_t*>(ones);
     for (int i = threadIdx.x; i < int(kChunkTileBytes / 4); i += blockDim.x) o32[i] = 0x3F803F80u;
     fence_async_smem();
   }
-  for (int i = threadIdx.x; i < p.N; i += blockDim.x) s_bias[i] = p.bias ? p.bias[i] : 0.f;
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
@@ -423,6 +416,18 @@ gemm_tn_fast_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  // Everything above touched only shared memory, TMEM and kernel parameters: it overlaps the tail of the previous
+  // kernel.  From here on global memory is read (operands, bias, BN constants produced by that kernel).
+  pdl_wait();
+  if (bn_bwd) {
+    for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
+      s_coef[i] = p.bn_alpha[i];
+      s_coef[kBnCoefCols + i] = p.bn_beta[i];
+      s_coef[2 * kBnCoefCols + i] = p.bn_delta[i];
+    }
+  }
+  for (int i = threadIdx.x; i < p.N; i += blockDim.x) s_bias[i] = p.bias ? p.bias[i] : 0.f;
+  __syncthreads();
   const uint32_t tmem_base = *tmem_ptr;
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
 
@@ -691,7 +696,8 @@ static int launch_fast(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     RDP_CHECK_CUDA(cudaMemsetAsync(dbg_buf, 0, 32 * 16 * sizeof(long long), stream));
     q.dbg = dbg_buf;
   }
-  gemm_tn_fast_kernel<kStats, kAux><<<grid, kFastThreads, smem, stream>>>(ta, tb, tc, tx, q);
+  RDP_CHECK_CUDA(launch_pdl(gemm_tn_fast_kernel<kStats, kAux>, dim3(grid), dim3(kFastThreads), smem, stream, ta, tb,
+                            tc, tx, q));
   RDP_CHECK_CUDA(cudaGetLastError());
   if (q.dbg) {
     --dbg_left;
@@ -748,6 +754,7 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  pdl_trigger();
   const int split = blockIdx.x;
   const int m_blk = blockIdx.y;
   const int n_blk = blockIdx.z;
@@ -769,6 +776,7 @@ gemm_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_g, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                         // operands and the gradient buffer belong to earlier kernels
   const uint32_t tmem_base = *tmem_ptr;
 
   if (num_kb > 0) {
@@ -1081,8 +1089,8 @@ int rdp_gemm_wgrad(const void* g, int ldg, const void* x, int ldx, float* out, i
   const size_t smem = size_t(kWgradStages) * (2 + n_chunks) * (kBlockK * 128) + 256 + 1024;
   RDP_SMEM_ATTR_ONCE_PER_DEVICE(gemm_wgrad_kernel, 227 * 1024);
   dim3 grid(splits, m_tiles, n_tiles);
-  gemm_wgrad_kernel<<<grid, kWgradThreads, smem, static_cast<cudaStream_t>(stream)>>>(tg, tx, p);
-  RDP_CHECK_CUDA(cudaGetLastError());
+  RDP_CHECK_CUDA(launch_pdl(gemm_wgrad_kernel, grid, dim3(kWgradThreads), smem, static_cast<cudaStream_t>(stream), tg,
+                            tx, p));
   return 0;
 }
 
@@ -1124,8 +1132,7 @@ static int wgrad_det_impl(const void* g, int ldg, const void* x, int ldx, float*
   RDP_SMEM_ATTR_ONCE_PER_DEVICE(gemm_wgrad_kernel, 227 * 1024);
   cudaStream_t cs = static_cast<cudaStream_t>(stream);
   dim3 grid(splits, m_tiles, n_tiles);
-  gemm_wgrad_kernel<<<grid, kWgradThreads, smem, cs>>>(tg, tx, p);
-  RDP_CHECK_CUDA(cudaGetLastError());
+  RDP_CHECK_CUDA(launch_pdl(gemm_wgrad_kernel, grid, dim3(kWgradThreads), smem, cs, tg, tx, p));
   if (splits_out != nullptr) *splits_out = splits;
   if (reduce_now && splits > 1) {
     const float* wsp = ws;

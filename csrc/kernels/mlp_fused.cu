@@ -41,6 +41,8 @@ struct BnFoldParams {
 };
 
 __global__ void bn_fold_kernel(const BnFoldParams p) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   // one block per output row n of the next layer (+ extra blocks are not needed: N >= 1)
   extern __shared__ float sh[];
   float* s_a = sh;
@@ -258,6 +260,8 @@ struct BnReluBwdParams {
 
 __global__ void __launch_bounds__(256)
 bn_relu_bwd_kernel(const BnReluBwdParams p) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   // thread -> 8 consecutive columns (one 16-byte vector); blockDim.x = 256
   const int vec_per_row = p.N / 8;
   const int tcol = threadIdx.x % vec_per_row;
@@ -373,6 +377,8 @@ struct HeadParams {
 template <int kK>
 __global__ void __launch_bounds__(256)
 mlp_head_kernel(const HeadParams p) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   float wf[kK], cw = 0.f;          // folded weight w*a and constant c.w
 #pragma unroll
   for (int k = 0; k < kK; ++k) {
@@ -476,6 +482,8 @@ mlp_head_kernel(const HeadParams p) {
 
 // dW[n,k] = dWraw[n,k] * a[k] + db[n] * c[k]   (gradient taken against z mapped to y = a z + c)
 __global__ void grad_fixup_kernel(float* dw, const float* db, const float* a, const float* c, int N, int K) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= N * K) return;
   const int n = idx / K, k = idx % K;
@@ -509,6 +517,8 @@ __device__ __forceinline__ float adam_update(float p, float g, float& m, float& 
 // kVec: 4 elements per thread with 16-byte accesses (pointers 16-byte aligned; the host checks)
 template <bool kVec>
 __global__ void adam_kernel(AdamParams a) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   if (a.lr_ptr != nullptr) a.lr = *a.lr_ptr;
   if (a.step_ptr != nullptr) {
     const float t = *a.step_ptr;
@@ -581,6 +591,8 @@ constexpr int kCoefRows = 32;       // row phases per block: 32 columns x 32 pha
 
 __global__ void __launch_bounds__(32 * kCoefRows)
 bn_bwd_coef_kernel(const BnBwdCoefParams p) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   __shared__ float red[2][kCoefRows][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int j = blockIdx.x * 32 + tx;
@@ -621,6 +633,8 @@ bn_bwd_coef_kernel(const BnBwdCoefParams p) {
 // batches, issued after it, were observed to wait behind it (profiles/ingest_timeline.md): the per-step
 // result read-back was what exposed the input copies.  A kernel store has no place in that queue.
 __global__ void publish_host_kernel(const float* __restrict__ src, volatile float* dst_host, int n) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   // posted writes: no system-scope fence here -- waiting for the PCIe acknowledgement under a saturated
   // host->device stream cost up to 15 us per step; the host only reads after a stream synchronisation
   const int i = threadIdx.x;
@@ -642,6 +656,8 @@ __device__ __forceinline__ float sgd_update(float p, float g, float* buf, int64_
 
 template <bool kVec>
 __global__ void sgd_kernel(SgdParams s) {
+  pdl_trigger();      // see common.cuh: programmatic dependent launch
+  pdl_wait();
   if (s.lr_ptr != nullptr) s.lr = *s.lr_ptr;
   if (s.step_ptr != nullptr) s.first_step = (*s.step_ptr <= 1.f) ? 1 : 0;
   const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x, nth = int64_t(gridDim.x) * blockDim.x;
@@ -688,7 +704,7 @@ int rdp_bn_fold(const float* stats, float count, const float* gamma, const float
                  a, c, mean, rstd, w, b, N, K, static_cast<__nv_bfloat16*>(w_folded), ldw,
                  static_cast<__nv_bfloat16*>(w_folded_t), ldwt, b_folded};
   const int threads = K >= 256 ? 256 : (K >= 128 ? 128 : 64);
-  bn_fold_kernel<<<N, threads, 2 * K * sizeof(float), static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(launch_pdl(bn_fold_kernel, dim3(N), dim3(threads), 2 * K * sizeof(float), static_cast<cudaStream_t>(stream), p));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -752,7 +768,7 @@ int rdp_bn_relu_bwd(const void* dy, const void* z, void* dpre, int B, int N, int
   const int cap = num_sms() * 8;
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
-  bn_relu_bwd_kernel<<<grid, 256, N * sizeof(float), static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(launch_pdl(bn_relu_bwd_kernel, dim3(grid), dim3(256), N * sizeof(float), static_cast<cudaStream_t>(stream), p));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -767,16 +783,16 @@ int rdp_mlp_head(const void* z, int B, int K, int ld, const float* a, const floa
   const int cap = num_sms() * 2;
   if (grid > cap) grid = cap;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (K == 16) mlp_head_kernel<16><<<grid, 256, 0, s>>>(p);
-  else if (K == 32) mlp_head_kernel<32><<<grid, 256, 0, s>>>(p);
-  else mlp_head_kernel<64><<<grid, 256, 0, s>>>(p);
+  if (K == 16) RDP_CHECK_CUDA(launch_pdl(mlp_head_kernel<16>, dim3(grid), dim3(256), 0, s, p));
+  else if (K == 32) RDP_CHECK_CUDA(launch_pdl(mlp_head_kernel<32>, dim3(grid), dim3(256), 0, s, p));
+  else RDP_CHECK_CUDA(launch_pdl(mlp_head_kernel<64>, dim3(grid), dim3(256), 0, s, p));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
 int rdp_grad_fixup(float* dw, const float* db, const float* a, const float* c, int N, int K, void* stream) {
   const int total = N * K;
-  grad_fixup_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(dw, db, a, c, N, K);
+  RDP_CHECK_CUDA(launch_pdl(grad_fixup_kernel, dim3((total + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream), dw, db, a, c, N, K));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -787,7 +803,7 @@ int rdp_bn_bwd_coef(float* dw, int ldw, const float* db, const void* w_t, int ld
   RDP_REQUIRE(N > 0 && K > 0 && count > 0.f, "rdp_bn_bwd_coef: bad shape N=%d K=%d", N, K);
   BnBwdCoefParams p{dw, ldw, db, static_cast<const __nv_bfloat16*>(w_t), ldt, N, K, a, c, mean, rstd,
                     1.f / count, dgamma, dbeta, alpha, beta, delta};
-  bn_bwd_coef_kernel<<<(K + 31) / 32, 32 * kCoefRows, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  RDP_CHECK_CUDA(launch_pdl(bn_bwd_coef_kernel, dim3((K + 31) / 32), dim3(32 * kCoefRows), 0, static_cast<cudaStream_t>(stream), p));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -796,7 +812,7 @@ int rdp_publish_host(const float* src, float* host_pinned, int n, void* stream) 
   RDP_REQUIRE(n > 0 && n <= 32, "rdp_publish_host: n=%d (1..32 floats)", n);
   void* mapped = nullptr;
   RDP_CHECK_CUDA(cudaHostGetDevicePointer(&mapped, host_pinned, 0));
-  publish_host_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(src, static_cast<float*>(mapped), n);
+  RDP_CHECK_CUDA(launch_pdl(publish_host_kernel, dim3(1), dim3(32), 0, static_cast<cudaStream_t>(stream), src, static_cast<volatile float*>(static_cast<float*>(mapped)), n));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -817,8 +833,8 @@ int rdp_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float
   int grid = int(((vec ? n / 4 : n) + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   if (grid < 1) grid = 1;
-  if (vec) adam_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
-  else adam_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  if (vec) RDP_CHECK_CUDA(launch_pdl(adam_kernel<true>, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), a));
+  else RDP_CHECK_CUDA(launch_pdl(adam_kernel<false>, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), a));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -832,8 +848,8 @@ int rdp_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, floa
   int grid = int(((vec ? n / 4 : n) + 255) / 256);
   if (grid > num_sms() * 8) grid = num_sms() * 8;
   if (grid < 1) grid = 1;
-  if (vec) sgd_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);
-  else sgd_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(s);
+  if (vec) RDP_CHECK_CUDA(launch_pdl(sgd_kernel<true>, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), s));
+  else RDP_CHECK_CUDA(launch_pdl(sgd_kernel<false>, dim3(grid), dim3(256), 0, static_cast<cudaStream_t>(stream), s));
   RDP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
