@@ -374,7 +374,11 @@ class P2PReducer:
         assert self.n % 4 == 0, "flat buffer must be 16-byte granular"
         self.slot = (self.n + 3) // 4 * 4
         if algo == "auto" and grads is not None and self.n * 4 <= LL_MAX_BYTES:
-            algo = "ll"                            # latency-bound: one round, flag carried with the data
+            # latency-bound: one round, flag carried with the data.  LL moves twice the bytes to every peer, so its
+            # range shrinks with the world size (8 GPUs: LL 25 us vs one-shot 30 us at 194 KB, 36 vs 33 us at 512 KB,
+            # 60 vs 44 us at 1 MB; 2 GPUs: LL wins up to 1 MB -- profiles/r2/allreduce_{2,8}gpu.json)
+            world = dist.get_world_size(group) if dist.is_initialized() else 1
+            algo = "ll" if self.n * 4 * world <= 2 * LL_MAX_BYTES else "one_shot"
         self.algo = ALGO[algo]
         self.ll = self.algo == ALGO["ll"]
         if self.ll:

@@ -69,10 +69,12 @@ def select_fused(config, model, optimizer, criterion) -> Tuple[Optional[Any], st
         if type(criterion) is not torch.nn.BCEWithLogitsLoss or _loss_kind(criterion) != "bce_logits":
             return None, "the fused DLRM path needs BCEWithLogitsLoss(mean)"
         if _optimizer_kind(optimizer) != "sgd" or optimizer.param_groups[0].get("nesterov"):
-            return None, "the fused DLRM path needs torch.optim.SGD (sparse embedding updates are SGD)"
+            return None, ("the fused DLRM path needs torch.optim.SGD for the dense layers (the tables choose "
+                          "SGD / row-wise Adagrad / Adam through embedding_optimizer=)")
         n_cols = len(config.get("feature_columns") or [])
-        if n_cols != plan.spec.num_dense + len(plan.spec.table_sizes):
-            return None, "feature_columns must be the dense columns followed by one column per embedding table"
+        if n_cols != plan.spec.num_dense + plan.spec.index_columns:
+            return None, ("feature_columns must be the dense columns followed by one column per embedding table "
+                          "(bag_sizes[t] columns for a multi-hot table)")
         return plan, ""
     if isinstance(config.get("feature_types"), (list, tuple)):
         return None, "per-column feature dtypes feed model(*columns): generic path"
