@@ -59,8 +59,13 @@ def main():
         rd, wr = to_mb("dram__bytes_read.sum"), to_mb("dram__bytes_write.sum")
         dram_pct = fnum(d, "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
                         fnum(d, "dram__throughput.avg.pct_of_peak_sustained_elapsed"))
-        tensor = max(fnum(d, k) for k in hdr if k.startswith("sm__pipe_tensor") and "pct_of_peak" in k) \
-            if any(k.startswith("sm__pipe_tensor") and "pct_of_peak" in k for k in hdr) else 0.0
+        tensor = 0.0
+        for key in ("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+                    "TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+                    "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed"):
+            if key in d and d[key] not in ("", "n/a"):
+                tensor = fnum(d, key)
+                break
         warps = fnum(d, "sm__warps_active.avg.pct_of_peak_sustained_active")
         regs = int(fnum(d, "launch__registers_per_thread"))
         grid = d.get("launch__grid_size", "?")
