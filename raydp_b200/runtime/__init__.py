@@ -27,7 +27,7 @@ __all__ = [
     "kill", "available_resources", "cluster_resources", "nodes", "get_node_ip_address",
     "get_runtime_context", "ObjectRef", "ActorHandle", "placement_group",
     "remove_placement_group", "placement_group_table", "get_placement_group", "list_actors",
-    "TaskError", "ActorDiedError", "GetTimeoutError", "ObjectLostError", "exit_actor",
+    "TaskError", "ActorDiedError", "GetTimeoutError", "ObjectLostError", "exit_actor", "worker_logs",
 ]
 
 _state_lock = threading.RLock()
@@ -60,7 +60,7 @@ def init(address: Optional[str] = None, num_cpus: Optional[int] = None,
          num_gpus: Optional[int] = None, resources: Optional[Dict[str, float]] = None,
          namespace: Optional[str] = None, ignore_reinit_error: bool = False,
          include_dashboard: bool = False, object_store_memory: Optional[int] = None,
-         _memory: Optional[int] = None, **_ignored):
+         _memory: Optional[int] = None, log_to_driver: Optional[bool] = None, **_ignored):
     """Start (``address in (None, "local")``) or join (``"auto"`` / worker env) a runtime."""
     global _head, _client, _info
     with _state_lock:
@@ -77,7 +77,7 @@ def init(address: Optional[str] = None, num_cpus: Optional[int] = None,
         from raydp_b200.runtime.head import Head
         _head = Head(num_cpus=num_cpus, num_gpus=num_gpus, resources=resources,
                      namespace=namespace, object_store_memory=object_store_memory,
-                     memory=_memory)
+                     memory=_memory, log_to_driver=log_to_driver)
         _client = _LocalClient(_head)
         _info = _client.request("session_info")
         _info.update({"node_id": _head.head_node, "node_ip": _info["head_node_ip"],
@@ -445,6 +445,14 @@ def cluster_resources() -> Dict[str, float]:
 
 def nodes() -> List[dict]:
     return _rpc("nodes")
+
+
+def worker_logs(name: Optional[str] = None, tail_bytes: int = 16384) -> Dict[str, dict]:
+    """Tails of the per-worker log files of this session (stdout / stderr of every actor and task worker; each
+    file starts with a ``:job_id:<id>`` header, as the reference's Java agent writes it).  ``name`` filters on the
+    worker tag (``actor-<name>`` / ``task``).  ``init(log_to_driver=True)`` or ``RAYDP_B200_LOG_TO_DRIVER=1``
+    additionally echoes the files on the driver's stderr while the workers run."""
+    return _rpc("worker_logs", name=name, tail_bytes=tail_bytes)
 
 
 def get_node_ip_address() -> str:

@@ -161,7 +161,8 @@ def _give(avail: Dict[str, float], need: Dict[str, float]) -> None:
 class Head:
     def __init__(self, num_cpus: Optional[int] = None, num_gpus: Optional[int] = None,
                  resources: Optional[Dict[str, float]] = None, namespace: Optional[str] = None,
-                 object_store_memory: Optional[int] = None, memory: Optional[int] = None):
+                 object_store_memory: Optional[int] = None, memory: Optional[int] = None,
+                 log_to_driver: Optional[bool] = None):
         self.session = P.new_id()[:10]
         _reap_dead_sessions()
         self._marker = _session_marker(self.session, os.getpid())
@@ -206,6 +207,18 @@ class Head:
         self._accept_thread = threading.Thread(target=self._accept_loop, name="rdp-head-accept",
                                                daemon=True)
         self._accept_thread.start()
+        # Worker output (the capability of the reference's Java agent, core/agent/.../Agent.java:49-97: stdout / stderr
+        # of every worker go to a per-process log file that starts with a ":job_id:<id>" header).  With
+        # log_to_driver the files are also followed and echoed on the driver's stderr, each line prefixed with the
+        # worker it came from.
+        if log_to_driver is None:
+            log_to_driver = os.environ.get("RAYDP_B200_LOG_TO_DRIVER", "0") not in ("0", "", "false")
+        self.log_to_driver = bool(log_to_driver)
+        self._log_files: Dict[str, Tuple[str, str, int]] = {}      # path -> (tag, worker id, pid)
+        self._log_thread = None
+        if self.log_to_driver:
+            self._log_thread = threading.Thread(target=self._log_monitor, name="rdp-head-logs", daemon=True)
+            self._log_thread.start()
 
     # ------------------------------------------------------------------ nodes
     def add_node(self, resources: Dict[str, float], is_head: bool = False) -> str:
@@ -545,7 +558,11 @@ class Head:
         driver_path = [p for p in sys.path if p and os.path.isdir(p)]
         env["PYTHONPATH"] = os.pathsep.join([root] + driver_path + [env.get("PYTHONPATH", "")])
         tag = f"actor-{actor.name or actor.actor_id[:8]}" if actor else "task"
-        log = open(os.path.join(self.log_dir, f"worker-{tag}-{worker_id}.log"), "ab")
+        log_path = os.path.join(self.log_dir, f"worker-{tag}-{worker_id}.log")
+        log = open(log_path, "ab")
+        header = f":job_id:{self.job_id}\n" + (f":actor_name:{actor.name or actor.class_name}\n" if actor else ":task_worker:\n")
+        log.write(header.encode())
+        log.flush()
         proc = subprocess.Popen([sys.executable, "-m", "raydp_b200.runtime.worker"],
                                 env=env, stdin=subprocess.DEVNULL,
                                 stdout=None if os.environ.get("RAYDP_B200_WORKER_STDOUT") else log,
@@ -554,9 +571,59 @@ class Head:
                                 start_new_session=True)
         log.close()
         worker = _Worker(worker_id, node, proc, actor.actor_id if actor else None)
+        worker.log_path = log_path
         with self._lock:
             self._workers[worker_id] = worker
+            self._log_files[log_path] = (tag, worker_id, proc.pid)
         return worker
+
+    # ------------------------------------------------------------------ worker logs
+    def _log_monitor(self) -> None:
+        """Follow every worker log file and echo new lines on the driver's stderr as ``(tag pid=N) line``."""
+        offsets: Dict[str, int] = {}
+        while True:
+            with self._lock:
+                files = dict(self._log_files)
+            for path, (tag, _wid, pid) in files.items():
+                try:
+                    with open(path, "rb") as fh:
+                        fh.seek(offsets.get(path, 0))
+                        chunk = fh.read()
+                        # only whole lines: a partial last line is picked up on the next round
+                        cut = chunk.rfind(b"\n") + 1
+                        offsets[path] = offsets.get(path, 0) + cut
+                        chunk = chunk[:cut]
+                except OSError:
+                    continue
+                for line in chunk.decode("utf-8", "replace").splitlines():
+                    if line.startswith((":job_id:", ":actor_name:", ":task_worker:")):
+                        continue
+                    try:
+                        sys.stderr.write(f"({tag} pid={pid}) {line}\n")
+                    except (OSError, ValueError):
+                        return
+            if self._shutdown:
+                return
+            time.sleep(0.2)
+
+    def op_worker_logs(self, info, name=None, tail_bytes=16384):
+        """``{log file: {"tag", "worker_id", "pid", "job_id", "text"}}`` for workers whose tag contains ``name``."""
+        out = {}
+        with self._lock:
+            files = dict(self._log_files)
+        for path, (tag, wid, pid) in files.items():
+            if name and name not in tag:
+                continue
+            try:
+                with open(path, "rb") as fh:
+                    fh.seek(0, os.SEEK_END)
+                    size = fh.tell()
+                    fh.seek(max(0, size - int(tail_bytes)))
+                    text = fh.read().decode("utf-8", "replace")
+            except OSError:
+                continue
+            out[path] = {"tag": tag, "worker_id": wid, "pid": pid, "job_id": self.job_id, "text": text}
+        return out
 
     def _try_start_task(self, task: _Task) -> bool:
         prefer = None

@@ -202,3 +202,34 @@ def test_shared_memory_is_clean_after_shutdown_and_after_a_killed_driver(tmp_pat
         assert _shm_segments(f"rdp_{dead}_") == [] and _shm_segments(f"rdphead_{dead}_") == []
     finally:
         runtime.shutdown()
+
+
+def test_worker_logs_have_a_job_header_and_can_be_followed_from_the_driver(tmp_path):
+    """Capability of the reference's Java agent (core/agent/.../Agent.java:49-97): worker stdout / stderr land in
+    per-process log files that start with a ``:job_id:`` header; ``log_to_driver`` echoes them on the driver."""
+    import subprocess
+    import sys
+    code = "\n".join([
+        "import sys, time",
+        "from raydp_b200 import runtime",
+        "runtime.init(num_cpus=2, log_to_driver=True)",
+        "@runtime.remote",
+        "class Talker:",
+        "    def say(self, what):",
+        "        print('worker says', what, flush=True)",
+        "        return what",
+        "t = Talker.options(name='talker').remote()",
+        "assert runtime.get(t.say.remote('hello-42')) == 'hello-42'",
+        "logs = runtime.worker_logs('talker')",
+        "assert len(logs) == 1, logs",
+        "rec = next(iter(logs.values()))",
+        "assert rec['text'].startswith(':job_id:' + rec['job_id']), rec['text'][:80]",
+        "assert ':actor_name:talker' in rec['text'] and 'worker says hello-42' in rec['text']",
+        "time.sleep(0.8)",
+        "runtime.shutdown()",
+        "print('OK')",
+    ])
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120,
+                         cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert out.returncode == 0 and "OK" in out.stdout, out.stdout[-800:] + out.stderr[-1500:]
+    assert "(actor-talker pid=" in out.stderr and "worker says hello-42" in out.stderr, out.stderr[-800:]
