@@ -60,6 +60,18 @@ def _spmd_world() -> Optional[int]:
     return None
 
 
+def _worker_log_tail(worker, limit: int = 2000) -> str:
+    try:
+        logs = runtime.worker_logs(str(getattr(worker, "_actor_id", ""))[:8], tail_bytes=limit)
+        for rec in logs.values():
+            lines = [ln for ln in rec["text"].splitlines() if not ln.startswith((":job_id:", ":actor_name:"))]
+            if lines:
+                return "\n--- last output of the worker (" + rec["tag"] + ") ---\n" + "\n".join(lines[-25:])
+    except Exception:  # noqa: BLE001 - diagnostics must not mask the failure
+        pass
+    return ""
+
+
 def run_worker(train_func: Callable, config: Optional[dict], rank: int, world: int,
                local_rank: int, master_addr: str, master_port: int, backend: str, use_gpu: bool,
                shards: Dict[str, Any], run_name: str, storage_dir: str,
@@ -276,7 +288,12 @@ class TorchTrainer:
                     try:
                         done[index[ref._id]] = runtime.get(ref)
                     except (runtime.TaskError, runtime.ActorDiedError) as exc:
-                        raise TrainingFailedError(f"rank {index[ref._id]} failed: {exc}") from exc
+                        # a rank that died without raising (killed, out of memory, a native crash) leaves no
+                        # traceback: the tail of its log file is the evidence
+                        tail = ""
+                        if isinstance(exc, runtime.ActorDiedError):
+                            tail = _worker_log_tail(workers[index[ref._id]])
+                        raise TrainingFailedError(f"rank {index[ref._id]} failed: {exc}{tail}") from exc
             all_reports = [done[r] for r in range(n)]
             self._all_reports = all_reports                 # every rank's reports (legacy Trainer.run)
             return all_reports[0]

@@ -126,3 +126,26 @@ def test_failure_of_a_non_zero_rank_surfaces_at_once_and_the_group_restarts(ray_
                                                failure_config=FailureConfig(max_failures=1))).fit()
     assert result.metrics["sum"] == 2.0 and os.path.exists(flag)
     assert time.time() - t0 < 120, "the driver waited for the stuck rank instead of the failed one"
+
+
+def test_a_rank_that_dies_without_raising_reports_the_tail_of_its_log(ray_cluster, tmp_path):
+    """A worker process that disappears (here: ``os._exit``) leaves no traceback; the error carries the last
+    lines the worker printed (per-worker log files, ``runtime.worker_logs``)."""
+    import os
+    import pytest
+    from raydp_b200.train import RunConfig, ScalingConfig, TorchTrainer, get_context
+    from raydp_b200.train.trainer import TrainingFailedError
+
+    def loop(config):
+        import torch
+        import torch.distributed as dist
+        if get_context().get_world_rank() == 1:
+            print("about to crash: marker-7f3a", flush=True)
+            os._exit(3)
+        t = torch.ones(1)
+        dist.all_reduce(t)
+
+    with pytest.raises(TrainingFailedError) as err:
+        TorchTrainer(loop, train_loop_config={}, scaling_config=ScalingConfig(num_workers=2),
+                     run_config=RunConfig(storage_path=str(tmp_path), name="dies")).fit()
+    assert "rank 1 failed" in str(err.value) and "marker-7f3a" in str(err.value), str(err.value)[-600:]
