@@ -208,7 +208,8 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
                              world_size=lambda: session.get_context().get_world_size()),
         "ray.train.torch": _module("ray.train.torch", "", TorchTrainer=trainer.TorchTrainer,
                                    TorchConfig=config.TorchConfig, TorchCheckpoint=checkpoint.TorchCheckpoint,
-                                   prepare_model=torch_utils.prepare_model, get_device=torch_utils.get_device),
+                                   prepare_model=torch_utils.prepare_model, get_device=torch_utils.get_device,
+                                   prepare_data_loader=torch_utils.prepare_data_loader),
         "ray.air": _module("ray.air", "", session=session, Checkpoint=checkpoint.Checkpoint,
                            ScalingConfig=config.ScalingConfig, RunConfig=config.RunConfig,
                            FailureConfig=config.FailureConfig, CheckpointConfig=config.CheckpointConfig),
