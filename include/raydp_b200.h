@@ -287,6 +287,16 @@ int rdp_wgrad_reduce_many(const float* const* ws, const long long* elems, const 
 // without scratch one CTA per 64 columns walks all rows.
 int rdp_colsum_ordered(const void* const* src, const int* ld, const int* n, float* const* out, int n_seg, int rows,
                        float* ws, long long ws_floats, unsigned int* counters, int n_counters, void* stream);
+// ---- histogram gradient boosting (XGBoostEstimator, tree_method "gpu_hist") -------------------------------------
+// binned_t: uint16 bin ids, FEATURE-major [F, n]; slot[r]: histogram slot of row r's node in this level (-1: skip);
+// hist: fp64 [n_slots, 2 (g, h), F, n_bins], zeroed by the caller.
+int rdp_gbt_hist(const void* binned_t, const float* g, const float* h, const int* slot, double* hist, long long n,
+                 int F, int n_bins, int n_slots, void* stream);
+// After the splits of a level: node_of[r] moves to the child (rows whose bin == miss_bin follow default_left), and
+// slot[r] = in_sample[r] ? next_slot[node] : -1.  feat[node] < 0 means the node was not split.
+int rdp_gbt_partition(const void* binned_t, int* node_of, int* slot, const void* in_sample, const int* feat,
+                      const int* thr_bin, const int* left, const int* right, const void* default_left,
+                      const int* next_slot, long long n, int miss_bin, void* stream);
 // ---- K9: DLRM dot interaction (torch.bmm + tril gather + cat + pad) ---------------------------------
 // feats [B, S, D] bf16 -> out [B, ld_out] bf16 = [row 0 (D) | S(S-1)/2 pair dots, i > j row-major | 0 pad].
 int rdp_dot_interaction_fwd(const void* feats, void* out, int B, int S, int D, int ld_out, void* stream);

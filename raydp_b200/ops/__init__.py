@@ -444,6 +444,29 @@ def embedding_bag_bwd(table_ptrs, slots, cols, lens, idx_t_ptrs, dfeats_ptrs, ba
     _launches += 2          # claim + combine + update (the counter reset is a memset node)
 
 
+def gbt_hist(binned_t: torch.Tensor, g: torch.Tensor, h: torch.Tensor, slot: torch.Tensor, hist: torch.Tensor) -> None:
+    """``hist[slot, 0|1, f, bin] += g|h`` over all rows with ``slot >= 0`` (``binned_t``: uint16-as-int16 ``[F, n]``;
+    ``hist``: fp64 ``[n_slots, 2, F, n_bins]``, zeroed by the caller)."""
+    F, n = binned_t.shape
+    n_slots, _, F2, n_bins = hist.shape
+    assert F2 == F and binned_t.element_size() == 2 and hist.dtype == torch.float64 and slot.dtype == torch.int32
+    assert g.dtype == torch.float32 and h.dtype == torch.float32 and hist.is_contiguous() and binned_t.is_contiguous()
+    _check(lib().rdp_gbt_hist(_ptr(binned_t), _ptr(g), _ptr(h), _ptr(slot), _ptr(hist), n, F, n_bins, n_slots,
+                              _stream()))
+
+
+def gbt_partition(binned_t: torch.Tensor, node_of: torch.Tensor, slot: torch.Tensor, in_sample: torch.Tensor,
+                  feat: torch.Tensor, thr_bin: torch.Tensor, left: torch.Tensor, right: torch.Tensor,
+                  default_left: torch.Tensor, next_slot: torch.Tensor, miss_bin: int) -> None:
+    """Rows move to the child node chosen by their level's split; ``slot`` becomes the next level's histogram slot."""
+    F, n = binned_t.shape
+    assert node_of.dtype == torch.int32 and slot.dtype == torch.int32 and in_sample.element_size() == 1
+    assert all(t.dtype == torch.int32 for t in (feat, thr_bin, left, right, next_slot)) and default_left.element_size() == 1
+    _check(lib().rdp_gbt_partition(_ptr(binned_t), _ptr(node_of), _ptr(slot), _ptr(in_sample), _ptr(feat),
+                                   _ptr(thr_bin), _ptr(left), _ptr(right), _ptr(default_left), _ptr(next_slot), n,
+                                   int(miss_bin), _stream()))
+
+
 def dot_interaction_fwd(feats: torch.Tensor, out: torch.Tensor) -> None:
     B, S, D = feats.shape
     _check(lib().rdp_dot_interaction_fwd(_ptr(feats), _ptr(out), B, S, D, _pitch(out), _stream()))

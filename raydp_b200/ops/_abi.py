@@ -78,6 +78,8 @@ SIGNATURES.update({
                                VP]),
     "rdp_cast_weight_many": (I, [C.POINTER(VP), C.POINTER(I), C.POINTER(I), C.POINTER(VP), C.POINTER(I), C.POINTER(VP),
                                  C.POINTER(I), C.POINTER(VP), C.POINTER(VP), I, VP]),
+    "rdp_gbt_hist": (I, [VP, VP, VP, VP, VP, C.c_longlong, I, I, I, VP]),
+    "rdp_gbt_partition": (I, [VP, VP, VP, VP, VP, VP, VP, VP, VP, VP, C.c_longlong, I, VP]),
     "rdp_dot_interaction_fwd": (I, [VP, VP, I, I, I, I, VP]),
     "rdp_dot_interaction_bwd": (I, [VP, VP, VP, I, I, I, I, VP]),
     "rdp_bce_logits": (I, [VP, I, VP, VP, I, I, VP, I, F, VP, VP]),

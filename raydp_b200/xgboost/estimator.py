@@ -87,7 +87,8 @@ def _boost_loop(config: Dict[str, Any]) -> None:
             tmp = tempfile.mkdtemp(prefix="raydp_b200_gbt_")
             model.save_model(os.path.join(tmp, MODEL_FILE))
             checkpoint = Checkpoint.from_directory(tmp)
-        report(dict(metrics, training_iteration=rnd + 1, features=cols), checkpoint=checkpoint)
+        report(dict(metrics, training_iteration=rnd + 1, features=cols,
+                    tree_method=model.attributes.get("tree_method", "hist")), checkpoint=checkpoint)
         if tmp is not None:
             import shutil
             shutil.rmtree(tmp, ignore_errors=True)
@@ -132,7 +133,9 @@ class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
         from raydp_b200.train import (CheckpointConfig, FailureConfig, RunConfig, ScalingConfig, TorchConfig,
                                       TorchTrainer)
         res = dict(self._resources_per_worker or {})
-        res.pop("GPU", None)                      # histogram boosting is a CPU algorithm here
+        # a worker that was given a GPU builds its histograms with the CUDA kernels (csrc/kernels/gbt.cu); the
+        # per-level histogram all-reduce between workers stays on the host (gloo): it is a few hundred KB
+        use_gpu = float(res.get("GPU", 0) or 0) > 0
         datasets = {"train": train_ds}
         if evaluate_ds is not None:
             datasets["evaluate"] = evaluate_ds
@@ -140,7 +143,7 @@ class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
                   "num_boost_round": self._num_boost_round, "evaluate": evaluate_ds is not None,
                   "train_fn": getattr(self, "_train_fn", None)}
         trainer = TorchTrainer(_boost_loop, train_loop_config=config,
-                               scaling_config=ScalingConfig(num_workers=max(1, self._num_workers), use_gpu=False,
+                               scaling_config=ScalingConfig(num_workers=max(1, self._num_workers), use_gpu=use_gpu,
                                                             resources_per_worker=res or None),
                                run_config=RunConfig(checkpoint_config=CheckpointConfig(checkpoint_frequency=1,
                                                                                        num_to_keep=1),
@@ -156,7 +159,8 @@ class XGBoostEstimator(EstimatorInterface, SparkEstimatorInterface):
                     history.setdefault(name, {}).setdefault(metric, []).append(value)
         self._results = BoostResult(features=result.metrics.get("features"), backend="raydp_b200-hist-gbt",
                                     history=history, num_workers=max(1, self._num_workers),
-                                    rounds=result.metrics.get("training_iteration"))
+                                    rounds=result.metrics.get("training_iteration"),
+                                    tree_method=result.metrics.get("tree_method", "hist"))
         self._results.checkpoint, self._results.metrics = result.checkpoint, result.metrics
         self._results.metrics_history = result.metrics_history
         return self._results

@@ -116,6 +116,7 @@ class HistGBTModel:
         self.feature_names = list(feature_names) if feature_names is not None else None
         self.trees: List[Dict[str, list]] = []
         self.best_iteration = 0
+        self.attributes: Dict[str, Any] = {}          # e.g. {"tree_method": "gpu_hist"}: how the model was grown
 
     # xgboost.Booster-flavoured surface ------------------------------------------------------------
     def num_boosted_rounds(self) -> int:
@@ -138,7 +139,7 @@ class HistGBTModel:
     def save_model(self, path: str) -> None:
         with open(path, "w", encoding="utf-8") as fh:
             json.dump({"format": "raydp_b200.hist_gbt/1", "objective": self.objective, "base_margin": self.base_margin,
-                       "feature_names": self.feature_names, "trees": self.trees}, fh)
+                       "feature_names": self.feature_names, "trees": self.trees, "attributes": self.attributes}, fh)
 
     @classmethod
     def load_model(cls, path: str) -> "HistGBTModel":
@@ -148,6 +149,7 @@ class HistGBTModel:
             raise ValueError(f"{path} is not a raydp_b200 hist_gbt model")
         model = cls(blob["objective"], blob["base_margin"], blob["feature_names"])
         model.trees = blob["trees"]
+        model.attributes = dict(blob.get("attributes") or {})
         return model
 
     def get_dump(self) -> List[str]:
@@ -225,13 +227,61 @@ def _bin(x: np.ndarray, cuts: List[np.ndarray]) -> Tuple[np.ndarray, int]:
     return out, nb + 1
 
 
+def _split_level(hist: np.ndarray, level: List[int], tree: Dict[str, list], depth: int, cuts: List[np.ndarray],
+                 n_bins: int, p: Dict[str, float]) -> List[Tuple[int, int, int, bool, int, int]]:
+    """Leaf values and best splits of one level from its (already all-reduced) histogram
+    ``[len(level), 2, F, n_bins]``.  Appends the children to ``tree``; returns ``(node, feature, bin, default_left,
+    left child, right child)`` for every node that was split."""
+    lam, gamma, mcw, eta = p["lambda"], p["gamma"], p["min_child_weight"], p["eta"]
+    miss = n_bins - 1
+    F = hist.shape[2]
+    splits = []
+    for i, nid in enumerate(level):
+        hg, hh = hist[i, 0], hist[i, 1]
+        G, H = hg[0].sum(), hh[0].sum()                                      # any feature's bins sum to the node total
+        tree["value"][nid] = float(-eta * G / (H + lam))
+        if depth == int(p["max_depth"]) or H < 2 * mcw:
+            continue
+        parent = G * G / (H + lam)
+        gm, hm = hg[:, miss], hh[:, miss]
+        cg, chh = np.cumsum(hg[:, :miss], axis=1), np.cumsum(hh[:, :miss], axis=1)    # left sums for "x < cut[b]" after bin b
+        best = (0.0, -1, -1, True)
+        for default_left in (True, False):
+            GL = cg[:, :-1] + (gm[:, None] if default_left else 0.0)
+            HL = chh[:, :-1] + (hm[:, None] if default_left else 0.0)
+            GR, HR = G - GL, H - HL
+            gain = 0.5 * (GL * GL / (HL + lam) + GR * GR / (HR + lam) - parent) - gamma
+            ok = (HL >= mcw) & (HR >= mcw)
+            for f in range(F):                                                  # bins beyond this feature's cuts are empty
+                ok[f, len(cuts[f]):] = False
+            gain = np.where(ok, gain, -np.inf)
+            k = int(np.argmax(gain))
+            f, b = divmod(k, gain.shape[1])
+            if gain[f, b] > best[0] + 1e-12:
+                best = (float(gain[f, b]), f, b, default_left)
+        if best[1] < 0:
+            continue
+        _, f, b, default_left = best
+        li, ri = len(tree["feature"]), len(tree["feature"]) + 1
+        for key, val in (("feature", -1), ("threshold", 0.0), ("left", -1), ("right", -1), ("default_left", True),
+                         ("value", 0.0)):
+            tree[key] += [val, val]
+        tree["feature"][nid], tree["threshold"][nid] = int(f), float(cuts[f][b])
+        tree["left"][nid], tree["right"][nid], tree["default_left"][nid] = li, ri, bool(default_left)
+        splits.append((nid, int(f), int(b), bool(default_left), li, ri))
+    return splits
+
+
+def _new_tree() -> Dict[str, list]:
+    return {"feature": [-1], "threshold": [0.0], "left": [-1], "right": [-1], "default_left": [True], "value": [0.0]}
+
+
 def _grow_tree(binned: np.ndarray, n_bins: int, cuts: List[np.ndarray], g: np.ndarray, h: np.ndarray,
                rows: np.ndarray, p: Dict[str, float], comm: _Comm) -> Tuple[Dict[str, list], np.ndarray]:
     """One tree, level-wise.  Returns the tree and the leaf index of every LOCAL row (all rows, so the
     margin update needs no second traversal)."""
     n, F = binned.shape
-    lam, gamma, mcw, eta = p["lambda"], p["gamma"], p["min_child_weight"], p["eta"]
-    tree = {"feature": [-1], "threshold": [0.0], "left": [-1], "right": [-1], "default_left": [True], "value": [0.0]}
+    tree = _new_tree()
     node_of = np.zeros(n, dtype=np.int64)
     in_sample = np.zeros(n, dtype=bool)
     in_sample[rows] = True
@@ -254,38 +304,7 @@ def _grow_tree(binned: np.ndarray, n_bins: int, cuts: List[np.ndarray], g: np.nd
             hist[:, 1, :] = hh.reshape(len(level), F * n_bins)
         hist = comm.allreduce(hist).reshape(len(level), 2, F, n_bins)         # ONE collective per level
         nxt = []
-        for nid in level:
-            hg, hh = hist[slot[nid], 0], hist[slot[nid], 1]
-            G, H = hg[0].sum(), hh[0].sum()                                      # any feature's bins sum to the node total
-            tree["value"][nid] = float(-eta * G / (H + lam))
-            if depth == int(p["max_depth"]) or H < 2 * mcw:
-                continue
-            parent = G * G / (H + lam)
-            gm, hm = hg[:, miss], hh[:, miss]
-            cg, chh = np.cumsum(hg[:, :miss], axis=1), np.cumsum(hh[:, :miss], axis=1)    # left sums for "x < cut[b]" after bin b
-            best = (0.0, -1, -1, True)
-            for default_left in (True, False):
-                GL = cg[:, :-1] + (gm[:, None] if default_left else 0.0)
-                HL = chh[:, :-1] + (hm[:, None] if default_left else 0.0)
-                GR, HR = G - GL, H - HL
-                gain = 0.5 * (GL * GL / (HL + lam) + GR * GR / (HR + lam) - parent) - gamma
-                ok = (HL >= mcw) & (HR >= mcw)
-                for f in range(F):                                                  # bins beyond this feature's cuts are empty
-                    ok[f, len(cuts[f]):] = False
-                gain = np.where(ok, gain, -np.inf)
-                k = int(np.argmax(gain))
-                f, b = divmod(k, gain.shape[1])
-                if gain[f, b] > best[0] + 1e-12:
-                    best = (float(gain[f, b]), f, b, default_left)
-            if best[1] < 0:
-                continue
-            _, f, b, default_left = best
-            li, ri = len(tree["feature"]), len(tree["feature"]) + 1
-            for key, val in (("feature", -1), ("threshold", 0.0), ("left", -1), ("right", -1), ("default_left", True),
-                             ("value", 0.0)):
-                tree[key] += [val, val]
-            tree["feature"][nid], tree["threshold"][nid] = int(f), float(cuts[f][b])
-            tree["left"][nid], tree["right"][nid], tree["default_left"][nid] = li, ri, bool(default_left)
+        for nid, f, b, default_left, li, ri in _split_level(hist, level, tree, depth, cuts, n_bins, p):
             here = np.nonzero(node_of == nid)[0]
             bins = binned[here, f]
             go_left = np.where(bins == miss, default_left, bins <= b)
@@ -295,14 +314,100 @@ def _grow_tree(binned: np.ndarray, n_bins: int, cuts: List[np.ndarray], g: np.nd
     return tree, node_of
 
 
+class _GpuRows:
+    """The row-sized state of the booster on the GPU (``tree_method="gpu_hist"``): feature-major bin ids, sampled
+    mask, node and histogram-slot of every row.  The two passes over the rows of every tree level -- histogram
+    build and row partition -- run as CUDA kernels (``csrc/kernels/gbt.cu``); the small per-level histogram comes
+    back to the host for the fp64 split search and the cross-worker all-reduce."""
+
+    def __init__(self, binned: np.ndarray, n_bins: int, device):
+        import torch
+        self.torch = torch
+        self.device = device
+        self.n, self.F = binned.shape
+        self.n_bins = n_bins
+        self.binned_t = torch.from_numpy(np.ascontiguousarray(binned.T).view(np.int16)).to(device)
+        self.node_of = torch.zeros(self.n, dtype=torch.int32, device=device)
+        self.slot = torch.zeros(self.n, dtype=torch.int32, device=device)
+        self.in_sample = torch.ones(self.n, dtype=torch.uint8, device=device)
+
+    def grow(self, cuts: List[np.ndarray], g: np.ndarray, h: np.ndarray, rows: np.ndarray, p: Dict[str, float],
+             comm: _Comm) -> Tuple[Dict[str, list], np.ndarray]:
+        from raydp_b200 import ops
+        torch = self.torch
+        dev = self.device
+        tree = _new_tree()
+        gd = torch.from_numpy(np.ascontiguousarray(g, dtype=np.float32)).to(dev)
+        hd = torch.from_numpy(np.ascontiguousarray(h, dtype=np.float32)).to(dev)
+        if len(rows) == self.n:
+            self.in_sample.fill_(1)
+        else:
+            mask = np.zeros(self.n, dtype=np.uint8)
+            mask[rows] = 1
+            self.in_sample.copy_(torch.from_numpy(mask))
+        self.node_of.zero_()
+        self.slot.copy_(self.in_sample.to(torch.int32) - 1)         # level 0: slot 0 for sampled rows, -1 otherwise
+        level = [0]
+        miss = self.n_bins - 1
+        i32 = dict(dtype=torch.int32, device=dev)
+        for depth in range(int(p["max_depth"]) + 1):
+            if not level:
+                break
+            hist_d = torch.zeros(len(level), 2, self.F, self.n_bins, dtype=torch.float64, device=dev)
+            if self.n:
+                ops.gbt_hist(self.binned_t, gd, hd, self.slot, hist_d)
+            hist = comm.allreduce(hist_d.cpu().numpy().reshape(len(level), 2, self.F * self.n_bins))
+            hist = hist.reshape(len(level), 2, self.F, self.n_bins)
+            splits = _split_level(hist, level, tree, depth, cuts, self.n_bins, p)
+            nodes = len(tree["feature"])
+            feat = np.full(nodes, -1, dtype=np.int32)
+            thr = np.zeros(nodes, dtype=np.int32)
+            left = np.zeros(nodes, dtype=np.int32)
+            right = np.zeros(nodes, dtype=np.int32)
+            dl = np.zeros(nodes, dtype=np.uint8)
+            nxt_slot = np.full(nodes, -1, dtype=np.int32)
+            nxt = []
+            for nid, f, b, default_left, li, ri in splits:
+                feat[nid], thr[nid], left[nid], right[nid], dl[nid] = f, b, li, ri, int(default_left)
+                nxt_slot[li], nxt_slot[ri] = len(nxt), len(nxt) + 1
+                nxt += [li, ri]
+            if self.n:
+                up = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
+                ops.gbt_partition(self.binned_t, self.node_of, self.slot, self.in_sample, up(feat), up(thr), up(left),
+                                  up(right), up(dl), up(nxt_slot), miss)
+            level = nxt
+        return tree, self.node_of.cpu().numpy().astype(np.int64)
+
+
+def _gpu_device(p: Dict[str, Any]):
+    """The CUDA device to boost on, or None.  A GPU is demanded by ``tree_method="gpu_hist"`` or ``device="cuda"``
+    (the xgboost 1.x and 2.x spellings) and refused by ``device="cpu"``; otherwise the histogram kernels are used
+    whenever this worker process has a CUDA device and the kernels library."""
+    method, where = str(p.get("tree_method") or "auto"), str(p.get("device") or "").lower()
+    wanted = method == "gpu_hist" or where.startswith(("cuda", "gpu"))
+    if where == "cpu" and not wanted:
+        return None
+    try:
+        import torch
+        from raydp_b200 import ops
+        if torch.cuda.is_available() and ops.kernels_available():
+            return torch.device("cuda", torch.cuda.current_device())
+    except Exception:  # noqa: BLE001 - no torch / no driver: CPU path
+        pass
+    if wanted:
+        raise RuntimeError('tree_method="gpu_hist" / device="cuda" need a CUDA device and the built kernels library')
+    return None
+
+
 def normalise_params(params: Dict[str, Any]) -> Dict[str, Any]:
     unknown = sorted(set(params) - _KNOWN)
     if unknown:
         raise ValueError(f"xgboost parameters {unknown} are not supported by the built-in distributed booster")
-    tm = params.get("tree_method", "hist")
-    if tm not in ("hist", "auto", "approx"):
-        raise ValueError(f"tree_method={tm!r}: the built-in distributed booster implements 'hist'")
-    return {"objective": str(params.get("objective", "reg:squarederror")),
+    tm = params.get("tree_method", "auto")
+    if tm not in ("hist", "auto", "approx", "gpu_hist"):
+        raise ValueError(f"tree_method={tm!r}: the built-in distributed booster implements 'hist' / 'gpu_hist'")
+    return {"tree_method": str(tm), "device": str(params.get("device") or ""),
+            "objective": str(params.get("objective", "reg:squarederror")),
             "eta": float(params.get("eta", params.get("learning_rate", 0.3))),
             "max_depth": int(params.get("max_depth", 6)),
             "lambda": float(params.get("lambda", params.get("reg_lambda", 1.0))),
@@ -341,6 +446,9 @@ def train(params: Dict[str, Any], x: np.ndarray, y: np.ndarray, num_boost_round:
         model = HistGBTModel(p["objective"], base, feature_names)
     cuts = _global_cuts(x, p["max_bin"], comm)
     binned, n_bins = _bin(x, cuts)
+    device = _gpu_device(p)
+    gpu_rows = _GpuRows(binned, n_bins, device) if device is not None else None
+    model.attributes["tree_method"] = "gpu_hist" if gpu_rows is not None else "hist"
     margin = model.margin(x)
     eval_margins = [model.margin(np.asarray(ex, dtype=np.float32)) for ex, _, _ in evals]
     history: Dict[str, Dict[str, List[float]]] = {}
@@ -352,7 +460,10 @@ def train(params: Dict[str, Any], x: np.ndarray, y: np.ndarray, num_boost_round:
             rows = np.nonzero(rng.random(len(y)) < p["subsample"])[0]
         else:
             rows = np.arange(len(y))
-        tree, leaf = _grow_tree(binned, n_bins, cuts, g, h, rows, p, comm)
+        if gpu_rows is not None:
+            tree, leaf = gpu_rows.grow(cuts, g, h, rows, p, comm)
+        else:
+            tree, leaf = _grow_tree(binned, n_bins, cuts, g, h, rows, p, comm)
         model.trees.append(tree)
         margin += np.asarray(tree["value"])[leaf]
         round_metrics: Dict[str, float] = {}
