@@ -323,7 +323,13 @@ def run_actor_e2e(args, world):
     runtime.shutdown()
     n_exec = max(2, min(8, 2 * world))
     runtime.init(num_cpus=n_exec + world + 2, num_gpus=world)
-    steps_per_rank = 16
+    # BASELINE.json config 2 names a 100 M-row frame on 8 GPUs: 12.5 M rows (95 steps of 131072) per GPU, if the
+    # shared-memory object store has room for it (84 bytes per row, x3 for the conversion's transient copies)
+    steps_per_rank = 95
+    import shutil
+    free = shutil.disk_usage("/dev/shm").free
+    if steps_per_rank * args.batch * world * (FEATURES + 1) * 4 * 3 > free:
+        steps_per_rank = 16
     rows = steps_per_rank * args.batch * world
     t0 = time.perf_counter()
     spark = raydp.init_spark("bench-actor", n_exec, 1, "4GB")
