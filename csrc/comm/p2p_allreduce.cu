@@ -1013,8 +1013,6 @@ __global__ void __launch_bounds__(kArThreads)
 alltoall_kernel(const __grid_constant__ A2AParams p) {
   const int nblocks = gridDim.x;
   const uint32_t e = *reinterpret_cast<volatile uint32_t*>(p.epoch) + 1u;
-  const int64_t tid = blockIdx.x * int64_t(blockDim.x) + threadIdx.x;
-  const int64_t nthreads = int64_t(nblocks) * blockDim.x;
   // Receive buffers alternate on epoch parity (parity_stride != 0), which makes an "everybody has consumed the
   // last result" round unnecessary: this rank can only finish call e after every rank has ENTERED call e (it
   // needs their pushes), i.e. after their streams ran past the consumers of call e-1; so when it starts call
