@@ -188,12 +188,37 @@ def _tree_predict(tree: Dict[str, list], x: np.ndarray) -> np.ndarray:
 
 
 # --------------------------------------------------------------------------------------------- training
-def _global_cuts(x: np.ndarray, max_bin: int, comm: _Comm) -> List[np.ndarray]:
-    """Per-feature bin edges shared by all workers: merge of every worker's local quantile proposals."""
+def _local_quantiles_gpu(xd, qs: np.ndarray) -> List[Tuple[np.ndarray, int]]:
+    """``np.quantile(col[~isnan], qs)`` (linear interpolation) for every column of the device matrix ``xd``: one
+    device sort per feature instead of a host sort (the host sorts of a 1 M x 28 table take longer than 50
+    boosting rounds on the GPU)."""
+    import torch
+    out = []
+    q = torch.from_numpy(qs).to(xd.device)
+    for f in range(xd.shape[1]):
+        col = xd[:, f]
+        col = torch.sort(col[~torch.isnan(col)]).values.double()
+        m = col.numel()
+        if m == 0:
+            out.append((np.zeros(0), 0))
+            continue
+        pos = q * (m - 1)
+        lo = pos.floor().long()
+        hi = torch.clamp(lo + 1, max=m - 1)
+        vals = col[lo] + (col[hi] - col[lo]) * (pos - lo.double())
+        out.append((vals.cpu().numpy(), m))
+    return out
+
+
+def _global_cuts(x: np.ndarray, max_bin: int, comm: _Comm, xd=None) -> List[np.ndarray]:
+    """Per-feature bin edges shared by all workers: merge of every worker's local quantile proposals
+    (computed on the device when ``xd``, the feature matrix on the GPU, is given)."""
     F = x.shape[1]
     qs = np.linspace(0.0, 1.0, 2 * max_bin + 1)[1:-1]
     local = []
-    for f in range(F):
+    if xd is not None:
+        local = _local_quantiles_gpu(xd, qs)
+    for f in range(F if xd is None else 0):
         col = x[:, f]
         col = col[~np.isnan(col)]
         local.append((np.quantile(col, qs) if len(col) else np.zeros(0), len(col)))
@@ -320,13 +345,28 @@ class _GpuRows:
     build and row partition -- run as CUDA kernels (``csrc/kernels/gbt.cu``); the small per-level histogram comes
     back to the host for the fp64 split search and the cross-worker all-reduce."""
 
-    def __init__(self, binned: np.ndarray, n_bins: int, device):
+    def __init__(self, binned: Optional[np.ndarray], n_bins: int, device, x: Optional[np.ndarray] = None,
+                 cuts: Optional[List[np.ndarray]] = None):
+        """From host bin ids (``binned`` [n, F] uint16), or -- ``binned=None`` -- straight from the raw features:
+        ``x`` goes to the device once and is binned there (``torch.bucketize`` per feature, NaN -> the missing bin),
+        feature-major, so the host never builds or transposes the bin matrix."""
         import torch
         self.torch = torch
         self.device = device
-        self.n, self.F = binned.shape
         self.n_bins = n_bins
-        self.binned_t = torch.from_numpy(np.ascontiguousarray(binned.T).view(np.int16)).to(device)
+        if binned is not None:
+            self.n, self.F = binned.shape
+            self.binned_t = torch.from_numpy(np.ascontiguousarray(binned.T).view(np.int16)).to(device)
+        else:
+            self.n, self.F = x.shape
+            xd = x if torch.is_tensor(x) else torch.from_numpy(x).to(device)
+            self.binned_t = torch.empty(self.F, self.n, dtype=torch.int16, device=device)
+            for f, c in enumerate(cuts):
+                col = xd[:, f].contiguous()
+                b = torch.bucketize(col, torch.from_numpy(np.asarray(c, dtype=np.float32)).to(device), right=True)
+                b = torch.where(torch.isnan(col), torch.full_like(b, n_bins - 1), b)
+                self.binned_t[f] = b.to(torch.int16)
+            del xd
         self.node_of = torch.zeros(self.n, dtype=torch.int32, device=device)
         self.slot = torch.zeros(self.n, dtype=torch.int32, device=device)
         self.in_sample = torch.ones(self.n, dtype=torch.uint8, device=device)
@@ -444,10 +484,18 @@ def train(params: Dict[str, Any], x: np.ndarray, y: np.ndarray, num_boost_round:
             base = min(max(base, 1e-6), 1 - 1e-6)
             base = float(np.log(base / (1 - base)))
         model = HistGBTModel(p["objective"], base, feature_names)
-    cuts = _global_cuts(x, p["max_bin"], comm)
-    binned, n_bins = _bin(x, cuts)
     device = _gpu_device(p)
-    gpu_rows = _GpuRows(binned, n_bins, device) if device is not None else None
+    if device is not None:
+        import torch
+        xd = torch.from_numpy(x).to(device)                                     # the features go to the GPU once
+        cuts = _global_cuts(x, p["max_bin"], comm, xd=xd)
+        binned, n_bins = None, max((len(c) for c in cuts), default=0) + 2       # same bin count as _bin()
+        gpu_rows = _GpuRows(None, n_bins, device, x=xd, cuts=cuts)
+        del xd
+    else:
+        cuts = _global_cuts(x, p["max_bin"], comm)
+        binned, n_bins = _bin(x, cuts)
+        gpu_rows = None
     model.attributes["tree_method"] = "gpu_hist" if gpu_rows is not None else "hist"
     margin = model.margin(x)
     eval_margins = [model.margin(np.asarray(ex, dtype=np.float32)) for ex, _, _ in evals]

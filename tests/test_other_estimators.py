@@ -119,3 +119,24 @@ def test_cluster_resources(ray_cluster):
     assert len(ClusterResources.satisfy({"CPU": 2})) == 1
     assert ClusterResources.satisfy({"CPU": 10_000}) == []
     assert rt.cluster_resources()["CPU"] == 6
+
+
+def test_device_side_quantiles_and_binning_match_the_host_code():
+    """The GPU booster computes its quantile proposals and bin ids with torch ops on the device; the same helpers
+    on CPU tensors must reproduce numpy's quantiles and the host binning bit for bit."""
+    import numpy as np
+    import torch
+    from raydp_b200.xgboost import hist_gbt
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((5000, 4)).astype(np.float32)
+    x[rng.random(x.shape) < 0.05] = np.nan
+    qs = np.linspace(0, 1, 2 * 16 + 1)[1:-1]
+    got = hist_gbt._local_quantiles_gpu(torch.from_numpy(x), qs)
+    for f in range(4):
+        col = x[:, f]
+        col = col[~np.isnan(col)]
+        assert got[f][1] == len(col) and np.allclose(got[f][0], np.quantile(col.astype(np.float64), qs), atol=1e-6)
+    cuts = hist_gbt._global_cuts(x, 16, hist_gbt._Comm())
+    binned, n_bins = hist_gbt._bin(x, cuts)
+    rows = hist_gbt._GpuRows(None, max(len(c) for c in cuts) + 2, torch.device("cpu"), x=torch.from_numpy(x), cuts=cuts)
+    assert rows.n_bins == n_bins and np.array_equal(rows.binned_t.numpy().T.astype(np.uint16), binned)
