@@ -32,11 +32,61 @@ def timed(fn, iters, warm=5):
     return float(t.item()) * 1e3     # microseconds
 
 
+def stress(iters, rank, world, local):
+    """Flag / epoch / parity protocols under skew: every rank delays each call by a different random time (a spin
+    kernel on the stream), algorithms and sizes alternate, nothing synchronises with the host between calls.  Values
+    are small integers, so every expected result is exact (also through the bf16 wire)."""
+    import numpy as np
+    from raydp_b200.comm import P2PAllToAll, P2PReducer
+    dev = torch.device("cuda", local)
+    rng = np.random.default_rng(1234 + rank)
+    sizes = (1024, 48520, 1 << 20)
+    algos = ("ll", "one_shot", "two_shot", "bf16")
+    red = {(n, a): P2PReducer(torch.zeros(n, device=dev), dev, algo=a) for n in sizes for a in algos
+           if not (a == "ll" and n * 4 > (1 << 20))}
+    a2a = {c: P2PAllToAll(c, dev) for c in (256, 65536)}
+    send = {c: torch.empty(world, c, device=dev) for c in a2a}
+    dst_ids = torch.arange(world, device=dev, dtype=torch.float32).view(world, 1)
+    keys = list(red)
+    pending = []
+    for it in range(iters):
+        torch.cuda._sleep(int(rng.integers(0, 3_000_000)))            # up to ~1.5 ms of skew between the ranks
+        if it % 5 == 4:
+            c = (256, 65536)[(it // 5) % 2]
+            send[c].copy_((rank * 1000.0 + dst_ids + (it % 8)).expand(world, c))
+            got = a2a[c](send[c])
+            want = torch.arange(world, device=dev, dtype=torch.float32).view(world, 1) * 1000.0 + rank + (it % 8)
+            pending.append(("a2a", it, got.clone(), want.expand(world, c)))
+        else:
+            n, a = keys[it % len(keys)]
+            r = red[(n, a)]
+            r.grads.fill_(float(rank + 1 + (it % 8)))
+            r.allreduce_()
+            want = float(world * (world + 1) // 2 + world * (it % 8))
+            pending.append((a, it, r.grads.clone(), want))
+        if it % 20 == 19 or it == iters - 1:
+            torch.cuda.synchronize()
+            for name, i, got, want in pending:
+                ok = torch.equal(got, want) if torch.is_tensor(want) else bool((got == want).all())
+                assert ok, (name, i, rank, got.flatten()[:4].tolist(), want if not torch.is_tensor(want) else want.flatten()[:4].tolist())
+            pending = []
+    for r in red.values():
+        r.close()
+    for a in a2a.values():
+        a.close()
+    if rank == 0:
+        print(f"STRESS OK {iters} calls", flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--sizes", default="256,4096,16384,48516,131072,262144,1048576,4194304,16777216,67108864,268435456")
     ap.add_argument("--json", default=None)
+    ap.add_argument("--stress", type=int, default=0,
+                    help="N back-to-back collectives (LL / one-shot / two-shot / bf16 all-reduce and the one-round "
+                         "all-to-all, three sizes) with a random device-side delay on every rank before each call, "
+                         "no host synchronisation in between; results checked exactly every 20 calls")
     args = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -47,6 +97,11 @@ def main():
     use_nvls = nvls_available(torch.device("cuda", local))
     if rank == 0:
         print(f"# NVLS multicast support: {use_nvls}", flush=True)
+    if args.stress:
+        stress(args.stress, rank, world, local)
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     rows = []
     sampler = None
     if not args.check:

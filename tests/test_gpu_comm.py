@@ -161,6 +161,22 @@ def test_multigpu_allreduce():
 
 
 @pytest.mark.multigpu
+def test_multigpu_collectives_stress_with_random_delays():
+    """the flag / epoch / parity protocols on real peers under skew -- 300 back-to-back calls
+    (LL, one-shot, two-shot, bf16-wire all-reduce, one-round all-to-all; three sizes), every rank delayed by a
+    different random spin before each call, no host synchronisation in between, exact results."""
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(n_gpus, 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "bench", "allreduce_bench.py"),
+           "--stress", "300"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "STRESS OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@pytest.mark.multigpu
 def test_multigpu_alltoall():
     n_gpus = torch.cuda.device_count()
     if n_gpus < 2:
