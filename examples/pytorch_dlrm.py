@@ -112,6 +112,8 @@ def main() -> None:
     ap.add_argument("--batch-size", type=int, default=128)
     ap.add_argument("--lr", type=float, default=0.01)
     ap.add_argument("--gpu", action="store_true")
+    ap.add_argument("--table-optimizer", default="sgd", choices=["sgd", "adagrad", "adam"],
+                    help="sparse optimizer of the embedding tables on the GPU engine (row-wise Adagrad / lazy Adam)")
     ap.add_argument("--dictionary", action="store_true",
                     help="frequency-ranked dictionary encoding (the notebook's recipe) instead of hashing")
     args = ap.parse_args()
@@ -136,7 +138,7 @@ def main() -> None:
                                label_column=LABEL, label_type=torch.float, batch_size=args.batch_size,
                                num_epochs=args.epochs, drop_last=True, use_gpu=args.gpu,
                                resources_per_worker={"GPU": 1} if args.gpu else None,
-                               metrics_name=["Accuracy"])
+                               metrics_name=["Accuracy"], embedding_optimizer=args.table_optimizer)
     t0 = time.perf_counter()
     estimator.fit_on_spark(train_df, test_df)
     wall = time.perf_counter() - t0
