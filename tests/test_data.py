@@ -171,3 +171,34 @@ def test_batch_iteration_options(ray_cluster):
     first = next(iter(ds.iter_torch_batches(batch_size=8, dtypes={"i": torch.float32, "f": torch.float32})))
     assert first["f"].shape == (8, 2) and first["i"].dtype == torch.float32
     assert next(iter(ds.iter_torch_batches(batch_size=4, collate_fn=lambda b: int(b["i"].sum())))) == 6
+
+
+def test_to_torch_batches_straddle_blocks_in_row_order(ray_cluster):
+    """Batches are slices of per-block tensors; a batch that spans two (or three) blocks is stitched in row order,
+    for the single-matrix and the per-column (list of dtypes) conventions alike."""
+    import numpy as np
+    import pyarrow as pa
+    import torch
+    from raydp_b200 import data as rdata
+    sizes = [7, 0, 3, 25, 1, 10]                               # uneven blocks, one empty, one smaller than a batch
+    start, tables = 0, []
+    for n in sizes:
+        ids = np.arange(start, start + n, dtype=np.float32)
+        tables.append(pa.table({"a": ids, "b": ids * 2, "y": ids + 0.5}))
+        start += n
+    ds = rdata.from_arrow(tables)
+    for drop_last in (False, True):
+        for dtypes in (torch.float, [torch.float, torch.long]):
+            it = ds.to_torch(label_column="y", feature_columns=["a", "b"], batch_size=8, drop_last=drop_last,
+                             feature_column_dtypes=dtypes, label_column_dtype=torch.float)
+            seen, shapes = [], []
+            for feats, label in it:
+                a = feats[0].view(-1) if isinstance(feats, list) else feats[:, 0]
+                b = feats[1].view(-1) if isinstance(feats, list) else feats[:, 1]
+                assert torch.equal(b.float(), a.float() * 2) and torch.equal(label.view(-1), a.float() + 0.5)
+                seen += a.tolist()
+                shapes.append(len(a))
+            total = sum(sizes)
+            want = total // 8 * 8 if drop_last else total
+            assert seen == [float(i) for i in range(want)]
+            assert shapes[:-1] == [8] * (len(shapes) - 1) and len(it) == len(shapes)
