@@ -71,7 +71,7 @@ def parse_args():
     ap.add_argument("--no-actor", action="store_true", help="skip the init_spark -> fit_on_spark actor-mode run")
     ap.add_argument("--no-extras", action="store_true", help="skip the DLRM / BigMLP / collective records")
     ap.add_argument("--lean", action="store_true", help="only the two headline numbers (device + e2e)")
-    ap.add_argument("--budget-s", type=float, default=float(os.environ.get("RAYDP_B200_BENCH_BUDGET_S", 540)),
+    ap.add_argument("--budget-s", type=float, default=float(os.environ.get("RAYDP_B200_BENCH_BUDGET_S", 300)),
                     help="wall-clock budget for the auxiliary phases (stand-ins, replica check, actor run, extras): a "
                          "phase that would not fit is skipped and listed under 'skipped'")
     return ap.parse_args()
