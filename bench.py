@@ -564,10 +564,10 @@ def main():
                 extra["allreduce"] = phase("extra_allreduce", extras.allreduce_record, rank, world, local)
             if world > 1 and fits("extra_alltoall", 20):
                 extra["alltoall"] = phase("extra_alltoall", extras.alltoall_record, rank, world, local)
-            if fits("extra_bigmlp", 150):
+            if fits("extra_bigmlp", 60):
                 extra["bigmlp"] = phase("extra_bigmlp", extras.bigmlp_record, rank, world, local)
             line["extra"] = extra
-        if not args.no_standin and not args.no_compile and fits("standin_device_compiled", 90):
+        if not args.no_standin and not args.no_compile and fits("standin_device_compiled", 60):
             standin["device_compiled"] = phase("standin_device_compiled", run_standin_device, args, rank, world, local,
                                                compiled=True)
         if standin:
