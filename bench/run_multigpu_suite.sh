@@ -19,6 +19,10 @@ step alltoall 200 $RUN --master-port $((port + 2)) bench/alltoall_bench.py --jso
 step bigmlp_ours 200 $RUN --master-port $((port + 3)) bench/bigmlp_bench.py --steps 6 --warmup 3
 step bigmlp_standin 200 $RUN --master-port $((port + 4)) bench/bigmlp_bench.py --steps 6 --warmup 3 --impl standin
 step dlrm_ours 200 $RUN --master-port $((port + 5)) bench/dlrm_bench.py
-step bench_ours 300 $RUN --master-port $((port + 6)) bench.py --gpus "$N" --steps 30 --warmup 5
-grep -h '^{' "$OUT"/bigmlp_ours.log "$OUT"/bigmlp_standin.log "$OUT"/dlrm_ours.log "$OUT"/bench_ours.log > "$OUT/lines.json" 2>/dev/null
+step dlrm_check 200 $RUN --master-port $((port + 7)) bench/dlrm_bench.py --check
+step dlrm_variants 200 $RUN --master-port $((port + 8)) bench/dlrm_variants.py
+step collectives_stress 200 $RUN --master-port $((port + 9)) bench/allreduce_bench.py --stress 300
+step ingest 200 $RUN --master-port $((port + 10)) bench/ingest_bench.py --gpus "$N" --json "$OUT/ingest.json"
+step bench_ours 400 $RUN --master-port $((port + 6)) bench.py --gpus "$N" --steps 30 --warmup 5
+grep -h '^{' "$OUT"/bigmlp_ours.log "$OUT"/bigmlp_standin.log "$OUT"/dlrm_ours.log "$OUT"/dlrm_variants.log "$OUT"/bench_ours.log > "$OUT/lines.json" 2>/dev/null
 echo "suite done -> $OUT"
