@@ -301,6 +301,12 @@ def install(ray: bool = True, pyspark: bool = True, force: bool = False) -> List
             not getattr(sys.modules.get("pyspark"), "__raydp_b200_alias__", False):
         _register(_pyspark_tree())
         added.append("pyspark")
+    if ray and _absent("xgboost_ray") and "xgboost_ray" not in sys.modules:
+        # the reference's XGBoost example talks to xgboost_ray directly (examples/xgboost_ray_nyctaxi.py:5)
+        from raydp_b200.xgboost import ray_api
+        _register({"xgboost_ray": _module("xgboost_ray", "alias of raydp_b200.xgboost.ray_api", RayDMatrix=ray_api.RayDMatrix,
+                                          RayParams=ray_api.RayParams, train=ray_api.train, predict=ray_api.predict)})
+        added.append("xgboost_ray")
     if _INSTALLED:
         import os
         os.environ["RAYDP_B200_COMPAT_ALIASES"] = "1"      # worker processes install the same aliases
@@ -316,7 +322,7 @@ class _LazyAliasFinder:
 
     def find_spec(self, name, path=None, target=None):
         root = name.partition(".")[0]
-        if root not in ("ray", "pyspark") or _LazyAliasFinder._busy:
+        if root not in ("ray", "pyspark", "xgboost_ray") or _LazyAliasFinder._busy:
             return None
         _LazyAliasFinder._busy = True
         try:

@@ -140,3 +140,27 @@ def test_device_side_quantiles_and_binning_match_the_host_code():
     binned, n_bins = hist_gbt._bin(x, cuts)
     rows = hist_gbt._GpuRows(None, max(len(c) for c in cuts) + 2, torch.device("cpu"), x=torch.from_numpy(x), cuts=cuts)
     assert rows.n_bins == n_bins and np.array_equal(rows.binned_t.numpy().T.astype(np.uint16), binned)
+
+
+def test_xgboost_ray_surface_trains_on_two_actors_and_predicts(ray_cluster):
+    """``RayDMatrix`` from numpy / pandas / a Dataset, ``train`` with ``RayParams(num_actors=2)`` filling
+    ``evals_result`` under the caller's names, ``predict``."""
+    import numpy as np
+    import pandas as pd
+    from raydp_b200.xgboost import ray_api
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((4000, 5)).astype(np.float32)
+    y = (x[:, 0] * 2 - x[:, 1] + 0.1 * rng.standard_normal(4000)).astype(np.float32)
+    dtrain = ray_api.RayDMatrix(x[:3000], label=y[:3000])
+    frame = pd.DataFrame({f"f{i}": x[3000:, i] for i in range(5)})
+    frame["target"] = y[3000:]
+    dtest = ray_api.RayDMatrix(frame.rename(columns={"target": "__label__"}), label="__label__")
+    evals_result, extra = {}, {}
+    bst = ray_api.train({"objective": "reg:squarederror", "max_depth": 4, "eval_metric": ["rmse", "mae"]}, dtrain,
+                        num_boost_round=8, evals=[(dtrain, "train"), (dtest, "holdout")], evals_result=evals_result,
+                        additional_results=extra, ray_params=ray_api.RayParams(num_actors=2, cpus_per_actor=1))
+    assert set(evals_result) == {"train", "holdout"} and len(evals_result["holdout"]["rmse"]) == 8
+    assert evals_result["holdout"]["rmse"][-1] < 0.5 * evals_result["holdout"]["rmse"][0]
+    assert extra["num_actors"] == 2 and extra["total_n"] == 3000
+    pred = ray_api.predict(bst, dtest)
+    assert pred.shape == (1000,) and np.sqrt(np.mean((pred - y[3000:]) ** 2)) < 1.1 * evals_result["holdout"]["rmse"][-1] + 1e-6
