@@ -175,3 +175,37 @@ def test_reference_xgboost_ray_example_runs_unchanged(tmp_path):
                           env=env, capture_output=True, text=True, timeout=600)
     assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
     assert "Final validation error:" in proc.stdout
+
+
+def test_reference_dlrm_notebook_code_runs(tmp_path):
+    """The code cells of ``examples/pytorch_dlrm.ipynb``: Criteo preprocessing on the DataFrame engine
+    (``posexplode(array(...))``, window-assigned category ids, broadcast joins, log transforms), the notebook's own
+    ``Dlrm`` module, ``TorchEstimator(num_workers=2)`` with 13 float + 26 long feature columns.  Only the data
+    path (a generated Criteo-format TSV), the proxy ``del os.environ`` lines and the executor size (2 x 4 cores do
+    not leave room for two training workers on an 8-core box) are adjusted."""
+    import json
+    import numpy as np
+    import pytest
+    nb = "/root/reference/examples/pytorch_dlrm.ipynb"
+    if not os.path.exists(nb):
+        pytest.skip("reference examples not mounted")
+    cells = json.load(open(nb))["cells"]
+    code = "\n\n".join("".join(c["source"]) for c in cells if c["cell_type"] == "code")
+    code = "\n".join(line for line in code.splitlines()
+                     if not line.startswith("!") and not line.startswith("del os.environ"))
+    data = tmp_path / "criteo.tsv"
+    assert "/Users/xianyang/datasets/criteo-small/train_1m.txt" in code and "executor_cores=4," in code
+    code = code.replace("/Users/xianyang/datasets/criteo-small/train_1m.txt", str(data))
+    code = code.replace("executor_cores=4,", "executor_cores=2,")
+    rng = np.random.default_rng(0)
+    with open(data, "w") as fh:
+        for _ in range(2000):
+            ints = ["" if rng.random() < 0.1 else str(int(rng.integers(0, 100))) for _ in range(13)]
+            cats = ["" if rng.random() < 0.05 else format(int(rng.integers(0, 50 + 20 * j)), "08x") for j in range(26)]
+            fh.write("\t".join([str(int(rng.random() < 0.25))] + ints + cats) + "\n")
+    script = tmp_path / "pytorch_dlrm.py"
+    script.write_text(code)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.run([sys.executable, "-m", "raydp_b200.compat", str(script)], cwd=str(tmp_path), env=env,
+                          capture_output=True, text=True, timeout=900)
+    assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-3000:]
