@@ -151,6 +151,14 @@ def _ray_tree() -> Dict[str, types.ModuleType]:
     top = {k: getattr(runtime, k) for k in (
         "init", "shutdown", "is_initialized", "get", "put", "wait", "remote", "get_actor", "kill", "nodes",
         "cluster_resources", "available_resources", "get_runtime_context", "ObjectRef")}
+    def ray_init(*args, **kwargs):
+        """``ray.init``: like :func:`raydp_b200.runtime.init`, with Ray's default of echoing worker output on the
+        driver (scripts written against Ray print their training progress from the workers)."""
+        import os
+        if "log_to_driver" not in kwargs and "RAYDP_B200_LOG_TO_DRIVER" not in os.environ:
+            kwargs["log_to_driver"] = True
+        return runtime.init(*args, **kwargs)
+    top["init"] = ray_init
     ray = _module("ray", "alias of raydp_b200.runtime (see raydp_b200.compat)", __version__="2.50.0", **top)
     ray.__path__ = []           # lets ``import ray.data`` style imports resolve through sys.modules
 
@@ -301,6 +309,17 @@ def install(ray: bool = True, pyspark: bool = True, force: bool = False) -> List
             not getattr(sys.modules.get("pyspark"), "__raydp_b200_alias__", False):
         _register(_pyspark_tree())
         added.append("pyspark")
+    if ray and _absent("horovod") and "horovod" not in sys.modules:
+        # examples/horovod_nyctaxi.py: `import horovod.torch as hvd`, `from ray.train.horovod import HorovodTrainer`
+        from raydp_b200.train import horovod_api
+        hvd_root = _module("horovod", "alias package (see raydp_b200.train.horovod_api)")
+        hvd_root.__path__ = []
+        _register({"horovod": hvd_root, "horovod.torch": horovod_api,
+                   "ray.train.horovod": _module("ray.train.horovod", "",
+                                                HorovodTrainer=horovod_api.horovod_trainer_class())})
+        if "ray.train" in sys.modules:
+            sys.modules["ray.train"].horovod = sys.modules["ray.train.horovod"]
+        added.append("horovod")
     if ray and _absent("xgboost_ray") and "xgboost_ray" not in sys.modules:
         # the reference's XGBoost example talks to xgboost_ray directly (examples/xgboost_ray_nyctaxi.py:5)
         from raydp_b200.xgboost import ray_api
@@ -322,7 +341,7 @@ class _LazyAliasFinder:
 
     def find_spec(self, name, path=None, target=None):
         root = name.partition(".")[0]
-        if root not in ("ray", "pyspark", "xgboost_ray") or _LazyAliasFinder._busy:
+        if root not in ("ray", "pyspark", "xgboost_ray", "horovod") or _LazyAliasFinder._busy:
             return None
         _LazyAliasFinder._busy = True
         try:

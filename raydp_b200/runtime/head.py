@@ -215,6 +215,8 @@ class Head:
             log_to_driver = os.environ.get("RAYDP_B200_LOG_TO_DRIVER", "0") not in ("0", "", "false")
         self.log_to_driver = bool(log_to_driver)
         self._log_files: Dict[str, Tuple[str, str, int]] = {}      # path -> (tag, worker id, pid)
+        self._log_offsets: Dict[str, int] = {}
+        self._log_pass_lock = threading.Lock()
         self._log_thread = None
         if self.log_to_driver:
             self._log_thread = threading.Thread(target=self._log_monitor, name="rdp-head-logs", daemon=True)
@@ -578,32 +580,36 @@ class Head:
         return worker
 
     # ------------------------------------------------------------------ worker logs
-    def _log_monitor(self) -> None:
-        """Follow every worker log file and echo new lines on the driver's stderr as ``(tag pid=N) line``."""
-        offsets: Dict[str, int] = {}
-        while True:
-            with self._lock:
-                files = dict(self._log_files)
-            for path, (tag, _wid, pid) in files.items():
-                try:
-                    with open(path, "rb") as fh:
-                        fh.seek(offsets.get(path, 0))
-                        chunk = fh.read()
-                        # only whole lines: a partial last line is picked up on the next round
-                        cut = chunk.rfind(b"\n") + 1
-                        offsets[path] = offsets.get(path, 0) + cut
-                        chunk = chunk[:cut]
-                except OSError:
+    def _log_pass(self, final: bool = False) -> bool:
+        """Echo what the worker log files gained since the last pass as ``(tag pid=N) line`` on the driver's stderr
+        (whole lines; ``final`` also flushes an unterminated last line).  False when stderr is gone."""
+        with self._lock:
+            files = dict(self._log_files)
+        offsets = self._log_offsets
+        for path, (tag, _wid, pid) in files.items():
+            try:
+                with open(path, "rb") as fh:
+                    fh.seek(offsets.get(path, 0))
+                    chunk = fh.read()
+            except OSError:
+                continue
+            cut = len(chunk) if final else chunk.rfind(b"\n") + 1
+            offsets[path] = offsets.get(path, 0) + cut
+            for line in chunk[:cut].decode("utf-8", "replace").splitlines():
+                if line.startswith((":job_id:", ":actor_name:", ":task_worker:")):
                     continue
-                for line in chunk.decode("utf-8", "replace").splitlines():
-                    if line.startswith((":job_id:", ":actor_name:", ":task_worker:")):
-                        continue
-                    try:
-                        sys.stderr.write(f"({tag} pid={pid}) {line}\n")
-                    except (OSError, ValueError):
-                        return
-            if self._shutdown:
-                return
+                try:
+                    sys.stderr.write(f"({tag} pid={pid}) {line}\n")
+                except (OSError, ValueError):
+                    return False
+        return True
+
+    def _log_monitor(self) -> None:
+        """Follow every worker log file until shutdown (which runs the last pass itself, before the files go)."""
+        while not self._shutdown:
+            with self._log_pass_lock:
+                if self._shutdown or not self._log_pass():
+                    return
             time.sleep(0.2)
 
     def op_worker_logs(self, info, name=None, tail_bytes=16384):
@@ -1092,6 +1098,9 @@ class Head:
             except OSError:
                 pass
         self._pool.shutdown(wait=False, cancel_futures=True)
+        if self.log_to_driver:
+            with self._log_pass_lock:            # what the workers printed in their last moments
+                self._log_pass(final=True)
         shutil.rmtree(self.dir, ignore_errors=True)
 
 

@@ -209,3 +209,23 @@ def test_reference_dlrm_notebook_code_runs(tmp_path):
     proc = subprocess.run([sys.executable, "-m", "raydp_b200.compat", str(script)], cwd=str(tmp_path), env=env,
                           capture_output=True, text=True, timeout=900)
     assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-3000:]
+
+
+def test_reference_horovod_example_runs_unchanged(tmp_path):
+    """``examples/horovod_nyctaxi.py`` of the reference: ``import horovod.torch as hvd`` (init / rank / size,
+    ``broadcast_parameters``, ``broadcast_optimizer_state``, ``DistributedOptimizer(op=hvd.Average)``) and
+    ``ray.train.horovod.HorovodTrainer``; the workers' progress lines reach the driver as with Ray."""
+    import glob
+    import shutil
+    import pytest
+    src = "/root/reference/examples"
+    if not os.path.isdir(src):
+        pytest.skip("reference examples not mounted")
+    for f in glob.glob(os.path.join(src, "*.py")) + glob.glob(os.path.join(src, "*.csv")):
+        shutil.copy(f, tmp_path)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    proc = subprocess.run([sys.executable, "-m", "raydp_b200.compat", "horovod_nyctaxi.py", "--epochs", "2"],
+                          cwd=str(tmp_path), env=env, capture_output=True, text=True, timeout=600)
+    assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
+    lines = [ln for ln in proc.stderr.splitlines() if "Train Epoch: 2" in ln]
+    assert len(lines) == 2 and all(ln.startswith("(actor-") for ln in lines), proc.stderr[-1500:]

@@ -149,3 +149,32 @@ def test_a_rank_that_dies_without_raising_reports_the_tail_of_its_log(ray_cluste
         TorchTrainer(loop, train_loop_config={}, scaling_config=ScalingConfig(num_workers=2),
                      run_config=RunConfig(storage_path=str(tmp_path), name="dies")).fit()
     assert "rank 1 failed" in str(err.value) and "marker-7f3a" in str(err.value), str(err.value)[-600:]
+
+
+def test_horovod_surface_averages_gradients_over_the_group(ray_cluster):
+    """``hvd.DistributedOptimizer``: replicas that start from rank 0's parameters and see different data end the
+    step with identical parameters (gradients averaged in ``step()``)."""
+    from raydp_b200 import train
+    from raydp_b200.train import ScalingConfig, TorchTrainer
+
+    def loop():
+        import torch
+        from raydp_b200.train import horovod_api as hvd
+        hvd.init()
+        torch.manual_seed(hvd.rank())                      # different initial weights per rank
+        model = torch.nn.Linear(3, 1)
+        opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
+        hvd.broadcast_parameters(model.state_dict(), root_rank=0)
+        hvd.broadcast_optimizer_state(opt, root_rank=0)
+        opt = hvd.DistributedOptimizer(opt, named_parameters=model.named_parameters(), op=hvd.Average)
+        for step in range(3):
+            x = torch.full((4, 3), float(hvd.rank() + 1 + step))
+            opt.zero_grad()
+            (model(x) ** 2).mean().backward()
+            opt.step()
+        w = model.weight.detach().reshape(-1)
+        spread = hvd.allreduce(w, op=hvd.Average) - w
+        train.report({"spread": float(spread.abs().max()), "size": hvd.size(), "w0": float(w[0])})
+
+    res = TorchTrainer(loop, scaling_config=ScalingConfig(num_workers=2)).fit()
+    assert res.metrics["size"] == 2 and res.metrics["spread"] < 1e-7
