@@ -314,6 +314,58 @@ class Dataset:
                            local_shuffle_seed: Optional[int] = None, prefetch_batches: int = 0,
                            **_ignored) -> Iterator[Dict[str, Any]]:
         import torch
+        if collate_fn is None and not local_shuffle_buffer_size and batch_size:
+            # blocks become tensors once; batches are slices (a batch spanning two blocks is stitched) -- per-batch
+            # Arrow -> numpy conversion of every column dominates the loop at small batch sizes
+            def block_tensors(table):
+                out = {}
+                for name in table.column_names:
+                    col = table.column(name)
+                    arr = col.combine_chunks() if isinstance(col, pa.ChunkedArray) else col
+                    if pa.types.is_list(arr.type) or pa.types.is_large_list(arr.type) or pa.types.is_fixed_size_list(arr.type):
+                        v = np.asarray(arr.to_pylist())
+                    else:
+                        v = arr.to_numpy(zero_copy_only=False)
+                    if v.dtype == object:
+                        return None                      # strings / ragged vectors: the generic path handles them
+                    t = torch.as_tensor(np.ascontiguousarray(v))
+                    if dtypes is not None:
+                        t = t.to(dtypes[name] if isinstance(dtypes, dict) else dtypes)
+                    out[name] = t
+                return out
+
+            def emit(d):
+                return {k: (v.to(device) if device else v) for k, v in d.items()}
+            carry, fallback, started = None, False, False
+            for table in self.iter_tables():
+                if table.num_rows == 0:
+                    continue
+                cur = block_tensors(table)
+                if cur is None:
+                    fallback = True
+                    break
+                started = True
+                n, off = table.num_rows, 0
+                if carry is not None:
+                    have = next(iter(carry.values())).shape[0]
+                    take = min(batch_size - have, n)
+                    carry = {k: torch.cat([carry[k], cur[k][:take]]) for k in cur}
+                    off = take
+                    if have + take < batch_size:
+                        continue
+                    yield emit(carry)
+                    carry = None
+                while n - off >= batch_size:
+                    yield emit({k: v[off:off + batch_size] for k, v in cur.items()})
+                    off += batch_size
+                if off < n:
+                    carry = {k: v[off:] for k, v in cur.items()}
+            if not fallback:
+                if carry is not None and not drop_last:
+                    yield emit(carry)
+                return
+            if started:                                  # cannot resume mid-stream on the generic path
+                raise TypeError("iter_torch_batches: a later block holds non-numeric columns; pass collate_fn")
         for batch in self.iter_batches(batch_size, "numpy", drop_last,
                                        local_shuffle_buffer_size=local_shuffle_buffer_size,
                                        local_shuffle_seed=local_shuffle_seed):

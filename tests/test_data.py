@@ -202,3 +202,18 @@ def test_to_torch_batches_straddle_blocks_in_row_order(ray_cluster):
             want = total // 8 * 8 if drop_last else total
             assert seen == [float(i) for i in range(want)]
             assert shapes[:-1] == [8] * (len(shapes) - 1) and len(it) == len(shapes)
+
+
+def test_iter_torch_batches_slices_blocks_and_keeps_row_order(ray_cluster):
+    import numpy as np
+    import pyarrow as pa
+    import torch
+    from raydp_b200 import data as rdata
+    ds = rdata.from_arrow([pa.table({"a": np.arange(7.0), "i": np.arange(7)}),
+                           pa.table({"a": np.arange(7.0, 10.0), "i": np.arange(7, 10)}),
+                           pa.table({"a": np.arange(10.0, 30.0), "i": np.arange(10, 30)})])
+    got = list(ds.iter_torch_batches(batch_size=8, dtypes={"a": torch.float32, "i": torch.int64}))
+    assert [len(b["a"]) for b in got] == [8, 8, 8, 6]
+    assert torch.equal(torch.cat([b["i"] for b in got]), torch.arange(30)) and got[0]["a"].dtype == torch.float32
+    assert [len(b["a"]) for b in ds.iter_torch_batches(batch_size=8, drop_last=True)] == [8, 8, 8]
+    assert list(ds.iter_torch_batches(batch_size=16, collate_fn=lambda b: int(b["i"].sum()))) == [120, 315]
