@@ -91,7 +91,9 @@ def test_reference_import_names_resolve_to_this_framework():
         import ray
         from ray.train.torch import TorchTrainer
         from ray.util.placement_group import placement_group
-        assert ray.init is runtime.init and ray.data is rdata and placement_group is runtime.placement_group
+        # ray.init is runtime.init with Ray's default of echoing worker output on the driver
+        assert ray.init.__name__ == "ray_init" and ray.shutdown is runtime.shutdown
+        assert ray.data is rdata and placement_group is runtime.placement_group
         assert TorchTrainer.__module__.startswith("raydp_b200.train")
         assert ray.util.client.ray.is_connected() is False
     if "pyspark" in compat.installed():
