@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import queue
 import threading
-from typing import Any, Dict, Iterator, List, Optional, Sequence, Union
+from typing import Any, Iterator, List, Optional, Sequence
 
 import numpy as np
 import pyarrow as pa

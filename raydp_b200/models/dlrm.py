@@ -10,7 +10,7 @@ sharded table-wise with the all-to-all fused into the lookup).
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import List, Optional, Sequence
+from typing import Optional, Sequence
 
 import torch
 import torch.nn as nn

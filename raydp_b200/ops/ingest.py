@@ -26,7 +26,6 @@ slot by packing at a row offset, so there is no concat.
 """
 from __future__ import annotations
 
-import ctypes
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np

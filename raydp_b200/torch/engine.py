@@ -15,7 +15,7 @@ data-parallel gradient all-reduce is fused with the optimizer update over NVLink
 from __future__ import annotations
 
 import time
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Dict, Tuple
 
 import torch
 

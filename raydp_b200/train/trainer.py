@@ -19,7 +19,6 @@ from __future__ import annotations
 import os
 import tempfile
 import time
-import traceback
 import uuid
 from typing import Any, Callable, Dict, List, Optional
 
